@@ -1,0 +1,1038 @@
+// rpt_capi.cu — implementation of the C ABI declared in include/rpt_gpu.h.
+//
+// Host-side responsibilities only: handle lifetime, the sizing / resize arithmetic of the reference
+// (duckdb/src/planner/filter/bloom_filter.cpp:7-27, src/operators/physical_create_bf.cpp:386-406),
+// staging host key columns through chunked, double-buffered H2D/D2H pipelines, and launching the
+// kernels of rpt_kernels.cu.  There is no CPU fallback anywhere in this file: every compute entry
+// point ends in a kernel launch or fails.
+#include <cuda_runtime.h>
+
+#include <atomic>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "../../include/rpt_gpu.h"
+#include "rpt_kernels.cuh"
+
+using namespace rpt;
+
+// ---------------------------------------------------------------------------------------------
+// errors
+// ---------------------------------------------------------------------------------------------
+static thread_local std::string g_last_error;
+
+static int set_error(const char *fmt, ...) {
+	char buf[512];
+	va_list ap;
+	va_start(ap, fmt);
+	vsnprintf(buf, sizeof(buf), fmt, ap);
+	va_end(ap);
+	g_last_error = buf;
+	return 1;
+}
+
+#define RPT_CUDA(expr)                                                                                                 \
+	do {                                                                                                               \
+		cudaError_t _e = (expr);                                                                                       \
+		if (_e != cudaSuccess) {                                                                                       \
+			return set_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, __LINE__);              \
+		}                                                                                                              \
+	} while (0)
+
+#define RPT_TRY(expr)                                                                                                  \
+	do {                                                                                                               \
+		int _rc = (expr);                                                                                              \
+		if (_rc != 0) {                                                                                                \
+			return _rc;                                                                                                \
+		}                                                                                                              \
+	} while (0)
+
+// ---------------------------------------------------------------------------------------------
+// reference sizing arithmetic
+// ---------------------------------------------------------------------------------------------
+// NextPowerOfTwo, duckdb/src/common/constants.cpp:30-47 (returns 0 where the reference throws)
+static uint64_t next_pow2(uint64_t v) {
+	if (v < 1) {
+		return 2;
+	}
+	v--;
+	v |= v >> 1;
+	v |= v >> 2;
+	v |= v >> 4;
+	v |= v >> 8;
+	v |= v >> 16;
+	v |= v >> 32;
+	v++;
+	return v;
+}
+
+// BloomFilter::Initialize, duckdb/src/planner/filter/bloom_filter.cpp:7-9,17-19
+static int sectors_for_rows(uint64_t rows, uint64_t *out) {
+	uint64_t min_bits = rows * 12ULL; // idx_t arithmetic, wraps like the reference
+	if (min_bits < 512ULL) {
+		min_bits = 512ULL;
+	}
+	const uint64_t p2 = next_pow2(min_bits);
+	if (p2 == 0) {
+		return set_error("Can't find next power of 2 for %llu", (unsigned long long)min_bits); // OutOfRangeException
+	}
+	const uint64_t s = p2 >> 6;
+	*out = s < (1ULL << 26) ? s : (1ULL << 26);
+	return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// handle
+// ---------------------------------------------------------------------------------------------
+struct rpt_bf {
+	DeviceInfo dev;
+	uint64_t num_sectors = 0;
+	uint64_t sized_for_rows = 0;
+	uint64_t *words = nullptr;
+	cudaStream_t stream = nullptr;     // handle's own stream
+	cudaStream_t pipe[2] = {nullptr, nullptr}; // host-column pipelines
+	std::atomic<int> has_data {0};
+	std::atomic<int> finalized {0};
+	std::atomic<long long> launches {0};
+	// peer merge state
+	std::vector<uint64_t *> peer_words;
+	std::vector<bool> peer_ipc;
+	int peer_rank = -1;
+};
+
+struct DeviceGuard {
+	int prev = -1;
+	bool ok = false;
+	explicit DeviceGuard(int device) {
+		if (cudaGetDevice(&prev) == cudaSuccess && cudaSetDevice(device) == cudaSuccess) {
+			ok = true;
+		}
+	}
+	~DeviceGuard() {
+		if (prev >= 0) {
+			cudaSetDevice(prev);
+		}
+	}
+};
+
+#define RPT_GUARD(bf)                                                                                                  \
+	DeviceGuard _guard((bf)->dev.device);                                                                              \
+	if (!_guard.ok) {                                                                                                  \
+		return set_error("cannot select CUDA device %d: %s", (bf)->dev.device,                                        \
+		                 cudaGetErrorString(cudaGetLastError()));                                                      \
+	}
+
+static int fill_device_info(int device, DeviceInfo *out) {
+	cudaDeviceProp prop;
+	RPT_CUDA(cudaGetDeviceProperties(&prop, device));
+	if (prop.major < 10) {
+		return set_error("device %d is sm_%d%d; librpt_gpu is built for sm_100a (B200) only", device, prop.major,
+		                 prop.minor);
+	}
+	out->device = device;
+	out->sm_count = prop.multiProcessorCount;
+	out->l2_bytes = prop.l2CacheSize;
+	out->smem_optin = prop.sharedMemPerBlockOptin;
+	return 0;
+}
+
+static size_t type_width(int type) {
+	switch (type) {
+	case RPT_BOOL:
+	case RPT_INT8:
+	case RPT_UINT8:
+		return 1;
+	case RPT_INT16:
+	case RPT_UINT16:
+		return 2;
+	case RPT_INT32:
+	case RPT_UINT32:
+	case RPT_FLOAT:
+		return 4;
+	case RPT_INT64:
+	case RPT_UINT64:
+	case RPT_DOUBLE:
+		return 8;
+	case RPT_INTERVAL:
+	case RPT_INT128:
+	case RPT_UINT128:
+		return 16;
+	default:
+		return 0;
+	}
+}
+
+static int validate_cols(const rpt_col_t *cols, int ncols, uint64_t count, int *mem_out) {
+	if (!cols || ncols < 1 || ncols > RPT_MAX_KEY_COLS) {
+		return set_error("ncols must be in [1, %d]", RPT_MAX_KEY_COLS);
+	}
+	for (int j = 0; j < ncols; j++) {
+		const rpt_col_t &c = cols[j];
+		if (c.mem != cols[0].mem) {
+			return set_error("all key columns of a call must live in the same memory space");
+		}
+		const bool known = type_width(c.type) != 0 || c.type == RPT_VARCHAR || c.type == RPT_STRING_T;
+		if (!known) {
+			return set_error("Invalid type for hash: physical type %d", c.type); // InvalidTypeException
+		}
+		if (c.type == RPT_STRING_T && c.mem != RPT_MEM_HOST) {
+			return set_error("RPT_STRING_T columns are host-only");
+		}
+		if (count > 0 && !c.data) {
+			return set_error("column %d has no data pointer", j);
+		}
+		if (c.type == RPT_VARCHAR && count > 0 && !c.aux && c.aux_bytes > 0) {
+			return set_error("VARCHAR column %d has no bytes buffer", j);
+		}
+	}
+	*mem_out = cols[0].mem;
+	return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// staging of key columns: rpt_col_t (host or device) → DevCols (device pointers)
+// ---------------------------------------------------------------------------------------------
+struct Staged {
+	cudaStream_t stream = nullptr;
+	std::vector<void *> dev_allocs;
+	~Staged() {
+		for (void *p : dev_allocs) {
+			cudaFreeAsync(p, stream);
+		}
+	}
+	int alloc(void **out, size_t bytes) {
+		RPT_CUDA(cudaMallocAsync(out, bytes ? bytes : 8, stream));
+		dev_allocs.push_back(*out);
+		return 0;
+	}
+	int upload(void **out, const void *host, size_t bytes, size_t pad = 0) {
+		RPT_TRY(alloc(out, bytes + pad));
+		if (bytes) {
+			RPT_CUDA(cudaMemcpyAsync(*out, host, bytes, cudaMemcpyHostToDevice, stream));
+		}
+		return 0;
+	}
+};
+
+// Rows of a chunked host upload start at multiples of this (validity words and 128-bit key loads
+// stay aligned; a multiple of every probe tile size).
+static constexpr uint64_t kChunkRows = 1ULL << 24;
+
+static void device_cols_view(const rpt_col_t *cols, int ncols, DevCols *out) {
+	memset(out, 0, sizeof(*out));
+	out->n = ncols;
+	for (int j = 0; j < ncols; j++) {
+		out->c[j].data = cols[j].data;
+		out->c[j].aux = cols[j].aux;
+		out->c[j].sel = cols[j].sel;
+		out->c[j].validity = cols[j].validity;
+		out->c[j].type = cols[j].type;
+	}
+}
+
+static bool any_sel(const rpt_col_t *cols, int ncols) {
+	for (int j = 0; j < ncols; j++) {
+		if (cols[j].sel) {
+			return true;
+		}
+	}
+	return false;
+}
+
+// duckdb::string_t (string_type.hpp:24): uint32 length, then 12 inlined bytes, or a 4-byte prefix
+// followed by a pointer.  Gathers entries [e0, e1) into Arrow-style offsets + bytes.
+static void gather_string_t(const void *data, uint64_t e0, uint64_t e1, std::vector<uint32_t> *offsets,
+                            std::vector<uint8_t> *bytes) {
+	const uint8_t *base = reinterpret_cast<const uint8_t *>(data);
+	offsets->resize(e1 - e0 + 1);
+	uint64_t total = 0;
+	for (uint64_t e = e0; e < e1; e++) {
+		uint32_t len;
+		memcpy(&len, base + e * 16, 4);
+		(*offsets)[e - e0] = static_cast<uint32_t>(total);
+		total += len;
+	}
+	(*offsets)[e1 - e0] = static_cast<uint32_t>(total);
+	bytes->resize(total);
+	for (uint64_t e = e0; e < e1; e++) {
+		uint32_t len;
+		memcpy(&len, base + e * 16, 4);
+		const uint8_t *src;
+		if (len <= 12) {
+			src = base + e * 16 + 4;
+		} else {
+			memcpy(&src, base + e * 16 + 8, sizeof(src));
+		}
+		if (len) {
+			memcpy(bytes->data() + (*offsets)[e - e0], src, len);
+		}
+	}
+}
+
+// Uploads rows [r0, r1) of host columns (r0 % 64 == 0).  When a column carries a selection the
+// caller passes the whole call as one chunk (r0 == 0) and the column's data_len entries are
+// uploaded once.
+static int stage_host_cols(const rpt_col_t *cols, int ncols, uint64_t r0, uint64_t r1, Staged *st, DevCols *out) {
+	memset(out, 0, sizeof(*out));
+	out->n = ncols;
+	const uint64_t n = r1 - r0;
+	for (int j = 0; j < ncols; j++) {
+		const rpt_col_t &c = cols[j];
+		DevCol &d = out->c[j];
+		d.type = c.type == RPT_STRING_T ? RPT_VARCHAR : c.type;
+		uint64_t e0 = r0, e1 = r1; // data entries to upload
+		if (c.sel) {
+			if (r0 != 0) {
+				return set_error("internal: selection columns are not chunked");
+			}
+			void *p;
+			RPT_TRY(st->upload(&p, c.sel, n * sizeof(uint32_t)));
+			d.sel = reinterpret_cast<const uint32_t *>(p);
+			if (c.data_len == 0) {
+				return set_error("column %d: data_len is required when a selection vector is given", j);
+			}
+			e0 = 0;
+			e1 = c.data_len;
+		}
+		const uint64_t ne = e1 - e0;
+		if (c.validity) {
+			void *p;
+			RPT_TRY(st->upload(&p, c.validity + (e0 >> 6), ((ne + 63) >> 6) * sizeof(uint64_t)));
+			d.validity = reinterpret_cast<const uint64_t *>(p);
+		}
+		if (c.type == RPT_VARCHAR) {
+			const uint32_t *off = reinterpret_cast<const uint32_t *>(c.data);
+			void *po, *pb;
+			RPT_TRY(st->upload(&po, off + e0, (ne + 1) * sizeof(uint32_t)));
+			const uint64_t b0 = ne ? off[e0] : 0, b1 = ne ? off[e1] : 0;
+			RPT_TRY(st->upload(&pb, reinterpret_cast<const uint8_t *>(c.aux) + b0, b1 - b0, 8));
+			d.data = po;
+			d.aux = reinterpret_cast<const uint8_t *>(pb) - b0; // offsets stay absolute
+		} else if (c.type == RPT_STRING_T) {
+			std::vector<uint32_t> offsets;
+			std::vector<uint8_t> bytes;
+			gather_string_t(c.data, e0, e1, &offsets, &bytes);
+			void *po, *pb;
+			RPT_TRY(st->upload(&po, offsets.data(), offsets.size() * sizeof(uint32_t)));
+			RPT_TRY(st->upload(&pb, bytes.data(), bytes.size(), 8));
+			// pageable sources: cudaMemcpyAsync returns after the buffer was staged, so the vectors may die here
+			d.data = po;
+			d.aux = pb;
+		} else {
+			const size_t w = type_width(c.type);
+			void *p;
+			RPT_TRY(st->upload(&p, reinterpret_cast<const uint8_t *>(c.data) + e0 * w, ne * w));
+			d.data = p;
+		}
+	}
+	return 0;
+}
+
+static cudaStream_t pick_stream(const rpt_bf *bf, rpt_stream_t s) {
+	return s ? reinterpret_cast<cudaStream_t>(s) : bf->stream;
+}
+
+// ---------------------------------------------------------------------------------------------
+// library
+// ---------------------------------------------------------------------------------------------
+extern "C" {
+
+const char *rpt_gpu_last_error(void) {
+	return g_last_error.c_str();
+}
+
+const char *rpt_gpu_version(void) {
+	return "rpt_gpu 0.1 (sm_100a)";
+}
+
+int rpt_gpu_device_count(int *out) {
+	if (!out) {
+		return set_error("null argument");
+	}
+	RPT_CUDA(cudaGetDeviceCount(out));
+	return 0;
+}
+
+int rpt_host_alloc(void **out, uint64_t bytes) {
+	if (!out) {
+		return set_error("null argument");
+	}
+	RPT_CUDA(cudaMallocHost(out, bytes ? bytes : 1));
+	return 0;
+}
+
+int rpt_host_free(void *ptr) {
+	RPT_CUDA(cudaFreeHost(ptr));
+	return 0;
+}
+
+int rpt_bf_sectors_for_rows(uint64_t rows, uint64_t *out) {
+	if (!out) {
+		return set_error("null argument");
+	}
+	return sectors_for_rows(rows, out);
+}
+
+// ---------------------------------------------------------------------------------------------
+// lifetime
+// ---------------------------------------------------------------------------------------------
+static int allocate_words(rpt_bf *bf, uint64_t rows) {
+	uint64_t s;
+	RPT_TRY(sectors_for_rows(rows, &s));
+	if (s != bf->num_sectors || !bf->words) {
+		if (bf->words) {
+			RPT_CUDA(cudaFree(bf->words)); // implicit device sync: no kernel still touches the old words
+			bf->words = nullptr;
+		}
+		RPT_CUDA(cudaMalloc(&bf->words, s * sizeof(uint64_t)));
+		bf->num_sectors = s;
+	}
+	bf->sized_for_rows = rows;
+	// std::fill_n(bf, num_sectors, 0), bloom_filter.cpp:24
+	RPT_CUDA(cudaMemsetAsync(bf->words, 0, s * sizeof(uint64_t), bf->stream));
+	RPT_CUDA(cudaStreamSynchronize(bf->stream));
+	return 0;
+}
+
+int rpt_bf_create(rpt_bf_t **out, uint64_t est_rows, int device) {
+	if (!out) {
+		return set_error("null argument");
+	}
+	*out = nullptr;
+	int ndev = 0;
+	cudaError_t e = cudaGetDeviceCount(&ndev);
+	if (e != cudaSuccess || ndev == 0) {
+		return set_error("no CUDA device available (%s); librpt_gpu has no CPU fallback",
+		                 e == cudaSuccess ? "device count is 0" : cudaGetErrorString(e));
+	}
+	if (device < 0 || device >= ndev) {
+		return set_error("device %d out of range [0, %d)", device, ndev);
+	}
+	rpt_bf *bf = new rpt_bf();
+	int rc = fill_device_info(device, &bf->dev);
+	if (rc == 0) {
+		DeviceGuard guard(device);
+		if (!guard.ok) {
+			rc = set_error("cannot select CUDA device %d", device);
+		} else {
+			auto make = [&]() -> int {
+				RPT_CUDA(cudaStreamCreateWithFlags(&bf->stream, cudaStreamNonBlocking));
+				RPT_CUDA(cudaStreamCreateWithFlags(&bf->pipe[0], cudaStreamNonBlocking));
+				RPT_CUDA(cudaStreamCreateWithFlags(&bf->pipe[1], cudaStreamNonBlocking));
+				return allocate_words(bf, est_rows);
+			};
+			rc = make();
+		}
+	}
+	if (rc != 0) {
+		rpt_bf_destroy(bf);
+		return rc;
+	}
+	*out = bf;
+	return 0;
+}
+
+int rpt_bf_destroy(rpt_bf_t *bf) {
+	if (!bf) {
+		return 0;
+	}
+	DeviceGuard guard(bf->dev.device);
+	rpt_bf_peer_close(bf);
+	if (bf->words) {
+		cudaFree(bf->words);
+	}
+	for (cudaStream_t s : {bf->stream, bf->pipe[0], bf->pipe[1]}) {
+		if (s) {
+			cudaStreamDestroy(s);
+		}
+	}
+	delete bf;
+	return 0;
+}
+
+#define RPT_GETTER(name, type, expr)                                                                                   \
+	int name(const rpt_bf_t *bf, type *out) {                                                                          \
+		if (!bf || !out) {                                                                                             \
+			return set_error("null argument");                                                                         \
+		}                                                                                                              \
+		*out = (expr);                                                                                                 \
+		return 0;                                                                                                      \
+	}
+RPT_GETTER(rpt_bf_num_sectors, uint64_t, bf->num_sectors)
+RPT_GETTER(rpt_bf_sized_for_rows, uint64_t, bf->sized_for_rows)
+RPT_GETTER(rpt_bf_is_empty, int, bf->has_data.load() ? 0 : 1)
+RPT_GETTER(rpt_bf_is_finalized, int, bf->finalized.load())
+RPT_GETTER(rpt_bf_device, int, bf->dev.device)
+RPT_GETTER(rpt_bf_device_words, uint64_t *, bf->words)
+
+int rpt_bf_launch_count(const rpt_bf_t *bf, long long *out) {
+	if (!bf || !out) {
+		return set_error("null argument");
+	}
+	*out = bf->launches.load();
+	return 0;
+}
+
+int rpt_bf_set_has_data(rpt_bf_t *bf, int has_data) {
+	if (!bf) {
+		return set_error("null argument");
+	}
+	bf->has_data.store(has_data ? 1 : 0);
+	return 0;
+}
+
+int rpt_bf_sync(const rpt_bf_t *bf) {
+	if (!bf) {
+		return set_error("null argument");
+	}
+	RPT_GUARD(bf);
+	RPT_CUDA(cudaStreamSynchronize(bf->stream));
+	RPT_CUDA(cudaStreamSynchronize(bf->pipe[0]));
+	RPT_CUDA(cudaStreamSynchronize(bf->pipe[1]));
+	return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// build
+// ---------------------------------------------------------------------------------------------
+static int insert_impl(rpt_bf *bf, const rpt_col_t *cols, int ncols, uint64_t count, rpt_stream_t stream_in) {
+	int mem = 0;
+	RPT_TRY(validate_cols(cols, ncols, count, &mem));
+	if (count == 0) {
+		return 0; // src/bloom_filter.cpp:71-74: no-op, has_data_ untouched
+	}
+	bf->has_data.store(1); // src/bloom_filter.cpp:75
+	int launches = 0;
+	if (mem == RPT_MEM_DEVICE) {
+		DevCols dc;
+		device_cols_view(cols, ncols, &dc);
+		RPT_CUDA(launch_build(bf->dev, dc, count, bf->words, bf->num_sectors, pick_stream(bf, stream_in), &launches));
+		bf->launches += launches;
+		return 0;
+	}
+	// host columns: chunked upload on two alternating streams so that the copy of chunk c+1
+	// overlaps the insert kernel of chunk c; all chunks OR into the same words
+	if (stream_in) {
+		RPT_CUDA(cudaStreamSynchronize(reinterpret_cast<cudaStream_t>(stream_in)));
+	}
+	const uint64_t chunk = any_sel(cols, ncols) ? count : kChunkRows;
+	int idx = 0;
+	for (uint64_t r0 = 0; r0 < count; r0 += chunk, idx ^= 1) {
+		const uint64_t r1 = r0 + chunk < count ? r0 + chunk : count;
+		Staged st;
+		st.stream = bf->pipe[idx];
+		DevCols dc;
+		RPT_TRY(stage_host_cols(cols, ncols, r0, r1, &st, &dc));
+		RPT_CUDA(launch_build(bf->dev, dc, r1 - r0, bf->words, bf->num_sectors, st.stream, &launches));
+	}
+	bf->launches += launches;
+	RPT_CUDA(cudaStreamSynchronize(bf->pipe[0]));
+	RPT_CUDA(cudaStreamSynchronize(bf->pipe[1]));
+	return 0;
+}
+
+int rpt_bf_insert(rpt_bf_t *bf, const rpt_col_t *cols, int ncols, uint64_t count, rpt_stream_t stream) {
+	if (!bf) {
+		return set_error("null filter handle");
+	}
+	RPT_GUARD(bf);
+	return insert_impl(bf, cols, ncols, count, stream);
+}
+
+// ---------------------------------------------------------------------------------------------
+// finalize
+// ---------------------------------------------------------------------------------------------
+int rpt_bf_needs_rebuild(const rpt_bf_t *bf, uint64_t actual_rows, int *out) {
+	if (!bf || !out) {
+		return set_error("null argument");
+	}
+	*out = 0;
+	if (actual_rows == 0) { // physical_create_bf.cpp:387
+		return 0;
+	}
+	uint64_t min_bits = bf->sized_for_rows * 12ULL; // :394
+	if (min_bits < 512ULL) {
+		min_bits = 512ULL;
+	}
+	const uint64_t allocated_bits = next_pow2(min_bits); // :395 (not capped at 2^32 sectors' worth)
+	if (allocated_bits == 0) {
+		return set_error("Can't find next power of 2 for %llu", (unsigned long long)min_bits);
+	}
+	*out = actual_rows * 8ULL > allocated_bits; // :396
+	return 0;
+}
+
+int rpt_bf_reinitialize_and_rehash(rpt_bf_t *bf, uint64_t actual_rows, const rpt_col_t *cols, int ncols,
+                                   uint64_t count, rpt_stream_t stream) {
+	if (!bf) {
+		return set_error("null filter handle");
+	}
+	RPT_GUARD(bf);
+	if (stream) {
+		RPT_CUDA(cudaStreamSynchronize(reinterpret_cast<cudaStream_t>(stream)));
+	}
+	RPT_TRY(allocate_words(bf, actual_rows));  // src/bloom_filter.cpp:38-39
+	bf->has_data.store(count > 0 ? 1 : 0);     // :40
+	if (count == 0) {                          // :42-44
+		return 0;
+	}
+	return insert_impl(bf, cols, ncols, count, stream); // :46-57
+}
+
+int rpt_bf_finalize(rpt_bf_t *bf, uint64_t actual_rows, const rpt_col_t *cols, int ncols, uint64_t count,
+                    int *rebuilt_out, rpt_stream_t stream) {
+	if (!bf) {
+		return set_error("null filter handle");
+	}
+	int rebuild = 0;
+	RPT_TRY(rpt_bf_needs_rebuild(bf, actual_rows, &rebuild));
+	if (rebuild) {
+		if (!cols) {
+			return set_error("filter sized for %llu rows holds %llu: the resize rule fires but no key columns were "
+			                 "given to rehash from",
+			                 (unsigned long long)bf->sized_for_rows, (unsigned long long)actual_rows);
+		}
+		RPT_TRY(rpt_bf_reinitialize_and_rehash(bf, actual_rows, cols, ncols, count, stream));
+	}
+	if (rebuilt_out) {
+		*rebuilt_out = rebuild;
+	}
+	bf->finalized.store(1); // physical_create_bf.cpp:409-413
+	return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// probe
+// ---------------------------------------------------------------------------------------------
+// translate_col0: emit in_sel[flat] instead of flat (BFTableFilter::Filter, bloom_filter.cpp:117-123);
+// the incoming selection is cols[0].sel.
+static int probe_impl(const rpt_bf *bf, const rpt_col_t *cols, int ncols, uint64_t count, uint32_t *sel_out,
+                      uint64_t *found_out, int out_mem, rpt_stream_t stream_in, bool translate_col0) {
+	int mem = 0;
+	RPT_TRY(validate_cols(cols, ncols, count, &mem));
+	if (!found_out || (count > 0 && !sel_out)) {
+		return set_error("null output argument");
+	}
+	if (count >= (1ULL << 32)) {
+		return set_error("count %llu does not fit the uint32 selection vector; split the batch",
+		                 (unsigned long long)count);
+	}
+	if (out_mem == RPT_MEM_DEVICE && mem != RPT_MEM_DEVICE) {
+		return set_error("device outputs require device key columns");
+	}
+	rpt_bf *mbf = const_cast<rpt_bf *>(bf);
+	int launches = 0;
+
+	if (mem == RPT_MEM_DEVICE) {
+		cudaStream_t s = pick_stream(bf, stream_in);
+		DevCols dc;
+		device_cols_view(cols, ncols, &dc);
+		const uint32_t *translate = translate_col0 ? dc.c[0].sel : nullptr;
+		Staged st;
+		st.stream = s;
+		void *scratch;
+		RPT_TRY(st.alloc(&scratch, probe_scratch_bytes(count)));
+		if (out_mem == RPT_MEM_DEVICE) { // fully asynchronous
+			RPT_CUDA(launch_probe(bf->dev, dc, count, bf->words, bf->num_sectors, sel_out, found_out, 0, translate,
+			                      scratch, s, &launches));
+			mbf->launches += launches;
+			return 0;
+		}
+		void *dsel, *dfound;
+		RPT_TRY(st.alloc(&dsel, count * sizeof(uint32_t)));
+		RPT_TRY(st.alloc(&dfound, sizeof(uint64_t)));
+		RPT_CUDA(launch_probe(bf->dev, dc, count, bf->words, bf->num_sectors, reinterpret_cast<uint32_t *>(dsel),
+		                      reinterpret_cast<uint64_t *>(dfound), 0, translate, scratch, s, &launches));
+		mbf->launches += launches;
+		RPT_CUDA(cudaMemcpyAsync(found_out, dfound, sizeof(uint64_t), cudaMemcpyDeviceToHost, s));
+		RPT_CUDA(cudaStreamSynchronize(s));
+		if (*found_out) {
+			RPT_CUDA(cudaMemcpyAsync(sel_out, dsel, *found_out * sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+			RPT_CUDA(cudaStreamSynchronize(s));
+		}
+		return 0;
+	}
+
+	// host columns → host outputs: chunks alternate between two streams; chunk c's survivors are
+	// copied back (its count is known one step later) while chunk c+1 uploads and runs
+	if (stream_in) {
+		RPT_CUDA(cudaStreamSynchronize(reinterpret_cast<cudaStream_t>(stream_in)));
+	}
+	*found_out = 0;
+	if (count == 0) {
+		return 0;
+	}
+	const uint64_t chunk = any_sel(cols, ncols) ? count : kChunkRows;
+	const uint64_t cap = chunk < count ? chunk : count;
+	struct Slot {
+		uint32_t *dsel = nullptr;
+		uint64_t *dfound = nullptr;
+		uint64_t *hfound = nullptr;
+		cudaEvent_t done = nullptr;
+		bool pending = false;
+	} slot[2];
+	uint64_t total = 0;
+	auto cleanup = [&]() {
+		for (int i = 0; i < 2; i++) {
+			cudaStreamSynchronize(bf->pipe[i]);
+			if (slot[i].dsel) {
+				cudaFree(slot[i].dsel);
+			}
+			if (slot[i].dfound) {
+				cudaFree(slot[i].dfound);
+			}
+			if (slot[i].hfound) {
+				cudaFreeHost(slot[i].hfound);
+			}
+			if (slot[i].done) {
+				cudaEventDestroy(slot[i].done);
+			}
+		}
+	};
+	auto drain = [&](int i) -> int { // chunk in slot i finished its kernel → copy its survivors out
+		if (!slot[i].pending) {
+			return 0;
+		}
+		RPT_CUDA(cudaEventSynchronize(slot[i].done));
+		const uint64_t f = *slot[i].hfound;
+		if (f) {
+			RPT_CUDA(cudaMemcpyAsync(sel_out + total, slot[i].dsel, f * sizeof(uint32_t), cudaMemcpyDeviceToHost,
+			                         bf->pipe[i]));
+		}
+		total += f;
+		slot[i].pending = false;
+		return 0;
+	};
+	auto run = [&]() -> int {
+		const int nslots = chunk < count ? 2 : 1;
+		for (int i = 0; i < nslots; i++) {
+			RPT_CUDA(cudaMalloc(&slot[i].dsel, cap * sizeof(uint32_t)));
+			RPT_CUDA(cudaMalloc(&slot[i].dfound, sizeof(uint64_t)));
+			RPT_CUDA(cudaMallocHost(&slot[i].hfound, sizeof(uint64_t)));
+			RPT_CUDA(cudaEventCreateWithFlags(&slot[i].done, cudaEventDisableTiming));
+		}
+		int idx = 0;
+		for (uint64_t r0 = 0; r0 < count; r0 += chunk, idx ^= 1) {
+			const uint64_t r1 = r0 + chunk < count ? r0 + chunk : count;
+			RPT_TRY(drain(idx)); // slot reuse: chunk c-2's survivors must be on their way out first
+			Staged st;
+			st.stream = bf->pipe[idx];
+			DevCols dc;
+			RPT_TRY(stage_host_cols(cols, ncols, r0, r1, &st, &dc));
+			void *scratch;
+			RPT_TRY(st.alloc(&scratch, probe_scratch_bytes(r1 - r0)));
+			const uint32_t *translate = translate_col0 ? dc.c[0].sel : nullptr;
+			RPT_CUDA(launch_probe(bf->dev, dc, r1 - r0, bf->words, bf->num_sectors, slot[idx].dsel, slot[idx].dfound,
+			                      static_cast<uint32_t>(r0), translate, scratch, st.stream, &launches));
+			RPT_CUDA(cudaMemcpyAsync(slot[idx].hfound, slot[idx].dfound, sizeof(uint64_t), cudaMemcpyDeviceToHost,
+			                         st.stream));
+			RPT_CUDA(cudaEventRecord(slot[idx].done, st.stream));
+			slot[idx].pending = true;
+			RPT_TRY(drain(idx ^ 1)); // previous chunk: in row order, so `total` stays ordered
+		}
+		// the loop drained every chunk but the last one issued
+		RPT_TRY(drain(idx ^ 1));
+		RPT_TRY(drain(idx));
+		RPT_CUDA(cudaStreamSynchronize(bf->pipe[0]));
+		RPT_CUDA(cudaStreamSynchronize(bf->pipe[1]));
+		return 0;
+	};
+	const int rc = run();
+	cleanup();
+	mbf->launches += launches;
+	if (rc == 0) {
+		*found_out = total;
+	}
+	return rc;
+}
+
+int rpt_bf_probe(const rpt_bf_t *bf, const rpt_col_t *cols, int ncols, uint64_t count, uint32_t *sel_out,
+                 uint64_t *found_out, int out_mem, rpt_stream_t stream) {
+	if (!bf) {
+		return set_error("null filter handle");
+	}
+	RPT_GUARD(bf);
+	return probe_impl(bf, cols, ncols, count, sel_out, found_out, out_mem, stream, false);
+}
+
+int rpt_bf_filter_sel(const rpt_bf_t *bf, const rpt_col_t *key, const uint32_t *in_sel, uint64_t approved_count,
+                      uint32_t *sel_out, uint64_t *found_out, int mem, rpt_stream_t stream) {
+	if (!bf || !key) {
+		return set_error("null argument");
+	}
+	RPT_GUARD(bf);
+	rpt_col_t col = *key;
+	if (col.mem != mem) {
+		return set_error("key column and selection vectors must live in the same memory space");
+	}
+	if (in_sel) {
+		if (col.sel) {
+			return set_error("rpt_bf_filter_sel: the key column must not carry its own selection");
+		}
+		col.sel = in_sel; // HashInternal slices the keys by `sel` (bloom_filter.cpp:84-92)
+	}
+	return probe_impl(bf, &col, 1, approved_count, sel_out, found_out, mem, stream, in_sel != nullptr);
+}
+
+int rpt_bf_lookup_hashes_host(const rpt_bf_t *bf, const uint64_t *hashes, uint64_t count, uint8_t *hits) {
+	if (!bf || (count && (!hashes || !hits))) {
+		return set_error("null argument");
+	}
+	RPT_GUARD(bf);
+	if (count == 0) {
+		return 0;
+	}
+	Staged st;
+	st.stream = bf->stream;
+	void *dh, *dhits;
+	RPT_TRY(st.upload(&dh, hashes, count * sizeof(uint64_t)));
+	RPT_TRY(st.alloc(&dhits, count));
+	RPT_CUDA(launch_lookup_hashes(bf->words, bf->num_sectors, reinterpret_cast<const uint64_t *>(dh), count,
+	                              reinterpret_cast<uint8_t *>(dhits), st.stream));
+	const_cast<rpt_bf *>(bf)->launches += 1;
+	RPT_CUDA(cudaMemcpyAsync(hits, dhits, count, cudaMemcpyDeviceToHost, st.stream));
+	RPT_CUDA(cudaStreamSynchronize(st.stream));
+	return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// filter words
+// ---------------------------------------------------------------------------------------------
+int rpt_bf_export_words(const rpt_bf_t *bf, uint64_t *host_dst, uint64_t capacity_words) {
+	if (!bf || !host_dst) {
+		return set_error("null argument");
+	}
+	if (capacity_words < bf->num_sectors) {
+		return set_error("destination holds %llu words, the filter has %llu", (unsigned long long)capacity_words,
+		                 (unsigned long long)bf->num_sectors);
+	}
+	RPT_GUARD(bf);
+	RPT_TRY(rpt_bf_sync(bf));
+	RPT_CUDA(cudaMemcpyAsync(host_dst, bf->words, bf->num_sectors * sizeof(uint64_t), cudaMemcpyDeviceToHost,
+	                         bf->stream));
+	RPT_CUDA(cudaStreamSynchronize(bf->stream));
+	return 0;
+}
+
+int rpt_bf_import_words(rpt_bf_t *bf, const uint64_t *host_src, uint64_t num_words) {
+	if (!bf || !host_src) {
+		return set_error("null argument");
+	}
+	if (num_words != bf->num_sectors) {
+		return set_error("source holds %llu words, the filter has %llu", (unsigned long long)num_words,
+		                 (unsigned long long)bf->num_sectors);
+	}
+	RPT_GUARD(bf);
+	RPT_CUDA(cudaMemcpyAsync(bf->words, host_src, num_words * sizeof(uint64_t), cudaMemcpyHostToDevice, bf->stream));
+	RPT_CUDA(cudaStreamSynchronize(bf->stream));
+	bf->has_data.store(1);
+	return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// multi-GPU OR-merge
+// ---------------------------------------------------------------------------------------------
+int rpt_bf_or_parts(rpt_bf_t *bf, const uint64_t *dev_parts, uint64_t nparts, rpt_stream_t stream) {
+	if (!bf || (nparts && !dev_parts)) {
+		return set_error("null argument");
+	}
+	RPT_GUARD(bf);
+	if (nparts == 0) {
+		return 0;
+	}
+	RPT_CUDA(launch_or_parts(bf->dev, bf->words, dev_parts, bf->num_sectors, nparts, pick_stream(bf, stream)));
+	bf->launches += 1;
+	return 0;
+}
+
+int rpt_bf_ipc_export(const rpt_bf_t *bf, void *handle64) {
+	if (!bf || !handle64) {
+		return set_error("null argument");
+	}
+	static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+	RPT_GUARD(bf);
+	cudaIpcMemHandle_t h;
+	RPT_CUDA(cudaIpcGetMemHandle(&h, bf->words));
+	memcpy(handle64, &h, sizeof(h));
+	return 0;
+}
+
+int rpt_bf_peer_open(rpt_bf_t *bf, const void *handles64, int nranks, int rank) {
+	if (!bf || !handles64) {
+		return set_error("null argument");
+	}
+	if (nranks < 1 || nranks > 16 || rank < 0 || rank >= nranks) {
+		return set_error("nranks must be in [1,16] and rank in [0,nranks)");
+	}
+	RPT_GUARD(bf);
+	RPT_TRY(rpt_bf_peer_close(bf));
+	bf->peer_words.assign(nranks, nullptr);
+	bf->peer_ipc.assign(nranks, false);
+	bf->peer_rank = rank;
+	for (int r = 0; r < nranks; r++) {
+		if (r == rank) {
+			bf->peer_words[r] = bf->words;
+			continue;
+		}
+		cudaIpcMemHandle_t h;
+		memcpy(&h, reinterpret_cast<const uint8_t *>(handles64) + 64 * r, sizeof(h));
+		void *p = nullptr;
+		RPT_CUDA(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+		bf->peer_words[r] = reinterpret_cast<uint64_t *>(p);
+		bf->peer_ipc[r] = true;
+	}
+	return 0;
+}
+
+// slice r of an S-word filter split N ways (even word boundaries for the 128-bit accesses)
+static void peer_slice(uint64_t S, int n, int r, uint64_t *off, uint64_t *len) {
+	const uint64_t a = (S * static_cast<uint64_t>(r) / n) & ~1ULL;
+	const uint64_t b = r + 1 == n ? S : ((S * static_cast<uint64_t>(r + 1) / n) & ~1ULL);
+	*off = a;
+	*len = b - a;
+}
+
+int rpt_bf_peer_merge_phase(rpt_bf_t *bf, int phase, rpt_stream_t stream) {
+	if (!bf) {
+		return set_error("null filter handle");
+	}
+	if (bf->peer_rank < 0) {
+		return set_error("rpt_bf_peer_open has not been called");
+	}
+	RPT_GUARD(bf);
+	cudaStream_t s = pick_stream(bf, stream);
+	const int n = static_cast<int>(bf->peer_words.size());
+	const int rank = bf->peer_rank;
+	if (phase == 0) { // reduce-scatter-OR: my slice |= every peer's copy of my slice, read over NVLink
+		PtrList srcs;
+		srcs.n = 0;
+		for (int r = 0; r < n; r++) {
+			if (r != rank) {
+				srcs.p[srcs.n++] = bf->peer_words[r];
+			}
+		}
+		uint64_t off, len;
+		peer_slice(bf->num_sectors, n, rank, &off, &len);
+		RPT_CUDA(launch_or_ptrs(bf->dev, bf->words, srcs, off, len, s));
+		bf->launches += 1;
+		return 0;
+	}
+	if (phase == 1) { // all-gather: pull every other rank's reduced slice
+		for (int k = 1; k < n; k++) {
+			const int r = (rank + k) % n; // staggered so that ranks do not all read the same peer at once
+			uint64_t off, len;
+			peer_slice(bf->num_sectors, n, r, &off, &len);
+			if (len) {
+				RPT_CUDA(cudaMemcpyAsync(bf->words + off, bf->peer_words[r] + off, len * sizeof(uint64_t),
+				                         cudaMemcpyDeviceToDevice, s));
+			}
+		}
+		return 0;
+	}
+	return set_error("phase must be 0 or 1");
+}
+
+int rpt_bf_peer_close(rpt_bf_t *bf) {
+	if (!bf) {
+		return set_error("null filter handle");
+	}
+	for (size_t r = 0; r < bf->peer_words.size(); r++) {
+		if (bf->peer_ipc[r] && bf->peer_words[r]) {
+			cudaIpcCloseMemHandle(bf->peer_words[r]);
+		}
+	}
+	bf->peer_words.clear();
+	bf->peer_ipc.clear();
+	bf->peer_rank = -1;
+	return 0;
+}
+
+int rpt_bf_allreduce_or(rpt_bf_t **per_gpu, int ngpu) {
+	if (!per_gpu || ngpu < 1 || ngpu > 16) {
+		return set_error("ngpu must be in [1,16]");
+	}
+	for (int i = 0; i < ngpu; i++) {
+		if (!per_gpu[i] || per_gpu[i]->num_sectors != per_gpu[0]->num_sectors) {
+			return set_error("all partial filters must exist and have the same number of sectors");
+		}
+	}
+	if (ngpu == 1) {
+		return 0;
+	}
+	int prev = 0;
+	cudaGetDevice(&prev);
+	auto body = [&]() -> int {
+		for (int i = 0; i < ngpu; i++) {
+			RPT_CUDA(cudaSetDevice(per_gpu[i]->dev.device));
+			RPT_TRY(rpt_bf_sync(per_gpu[i]));
+			for (int j = 0; j < ngpu; j++) {
+				if (per_gpu[j]->dev.device != per_gpu[i]->dev.device) {
+					cudaError_t e = cudaDeviceEnablePeerAccess(per_gpu[j]->dev.device, 0);
+					if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) {
+						return set_error("peer access %d -> %d: %s", per_gpu[i]->dev.device, per_gpu[j]->dev.device,
+						                 cudaGetErrorString(e));
+					}
+					cudaGetLastError();
+				}
+			}
+			per_gpu[i]->peer_words.assign(ngpu, nullptr);
+			per_gpu[i]->peer_ipc.assign(ngpu, false);
+			per_gpu[i]->peer_rank = i;
+			for (int j = 0; j < ngpu; j++) {
+				per_gpu[i]->peer_words[j] = per_gpu[j]->words;
+			}
+		}
+		for (int phase = 0; phase < 2; phase++) {
+			for (int i = 0; i < ngpu; i++) {
+				RPT_TRY(rpt_bf_peer_merge_phase(per_gpu[i], phase, nullptr));
+			}
+			for (int i = 0; i < ngpu; i++) { // every GPU finishes a phase before any starts the next
+				RPT_CUDA(cudaSetDevice(per_gpu[i]->dev.device));
+				RPT_CUDA(cudaStreamSynchronize(per_gpu[i]->stream));
+			}
+		}
+		int any = 0;
+		for (int i = 0; i < ngpu; i++) {
+			any |= per_gpu[i]->has_data.load();
+		}
+		for (int i = 0; i < ngpu; i++) {
+			per_gpu[i]->has_data.store(any);
+			rpt_bf_peer_close(per_gpu[i]);
+		}
+		return 0;
+	};
+	const int rc = body();
+	cudaSetDevice(prev);
+	return rc;
+}
+
+// ---------------------------------------------------------------------------------------------
+// synthetic columns
+// ---------------------------------------------------------------------------------------------
+int rpt_synth_build_keys(uint64_t *dev_out, uint64_t first, uint64_t count, int device, rpt_stream_t stream) {
+	DeviceGuard guard(device);
+	if (!guard.ok) {
+		return set_error("cannot select CUDA device %d", device);
+	}
+	RPT_CUDA(launch_synth_build(dev_out, first, count, reinterpret_cast<cudaStream_t>(stream)));
+	return 0;
+}
+
+int rpt_synth_probe_keys(uint64_t *dev_out, uint64_t first, uint64_t count, uint64_t n_build, uint32_t sel_ppm,
+                         int device, rpt_stream_t stream) {
+	DeviceGuard guard(device);
+	if (!guard.ok) {
+		return set_error("cannot select CUDA device %d", device);
+	}
+	if (n_build == 0) {
+		return set_error("n_build must be positive");
+	}
+	RPT_CUDA(launch_synth_probe(dev_out, first, count, n_build, sel_ppm, reinterpret_cast<cudaStream_t>(stream)));
+	return 0;
+}
+
+} // extern "C"

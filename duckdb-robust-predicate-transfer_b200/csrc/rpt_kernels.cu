@@ -1,0 +1,623 @@
+// rpt_kernels.cu — hand-written sm_100a kernels for the rpt bloom-filter hot path.
+//
+//   build_kernel   PTBloomFilter::Insert  = HashColumns + BloomFilter::InsertHashes
+//                  (reference src/bloom_filter.cpp:70-78, duckdb/src/planner/filter/bloom_filter.cpp:43-48,63-70)
+//   probe_kernel   PTBloomFilter::LookupSel = HashColumns + BloomFilter::LookupHashes
+//                  (src/bloom_filter.cpp:60-68, bloom_filter.cpp:50-61,72-78)
+//   or_*_kernel    the OR-merge of partial filters (multi-GPU)
+//
+// The path is HBM / random-access bound integer work (≈15 integer ops per key, one random 8-byte
+// filter word per key): no tensor cores, no GEMM shape.  What matters is (1) coalesced 128-bit
+// streaming key loads that do not pollute L2, (2) as many independent random filter loads in flight
+// per thread as registers allow, (3) keeping the filter — not the key stream — resident in the
+// 126 MB L2 (createpolicy evict_last / evict_first), and (4) a single-pass, order-stable compaction
+// so the selection vector is written once.
+#include "rpt_kernels.cuh"
+
+namespace rpt {
+
+// ---------------------------------------------------------------------------------------------
+// cache-policy helpers (PTX): keys are read once → L1 no_allocate + L2 evict_first; filter words are
+// re-read at random → L2 evict_last.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint64_t policy_evict_first() {
+	uint64_t p;
+	asm("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
+	return p;
+}
+__device__ __forceinline__ uint64_t policy_evict_last() {
+	uint64_t p;
+	asm("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p));
+	return p;
+}
+__device__ __forceinline__ ulonglong2 ld_stream_v2(const void *ptr, uint64_t pol) {
+	ulonglong2 v;
+	asm("ld.global.nc.L1::no_allocate.L2::cache_hint.v2.u64 {%0, %1}, [%2], %3;"
+	    : "=l"(v.x), "=l"(v.y)
+	    : "l"(ptr), "l"(pol));
+	return v;
+}
+__device__ __forceinline__ uint64_t ld_stream_u64(const void *ptr, uint64_t pol) {
+	uint64_t v;
+	asm("ld.global.nc.L1::no_allocate.L2::cache_hint.u64 %0, [%1], %2;" : "=l"(v) : "l"(ptr), "l"(pol));
+	return v;
+}
+__device__ __forceinline__ uint64_t ld_filter_word(const uint64_t *ptr, uint64_t pol) {
+	uint64_t v;
+	asm("ld.global.nc.L1::no_allocate.L2::cache_hint.u64 %0, [%1], %2;" : "=l"(v) : "l"(ptr), "l"(pol));
+	return v;
+}
+__device__ __forceinline__ uint64_t ld_relaxed_u64(const uint64_t *ptr) {
+	uint64_t v;
+	asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(ptr) : "memory");
+	return v;
+}
+__device__ __forceinline__ void st_relaxed_u64(uint64_t *ptr, uint64_t v) {
+	asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(ptr), "l"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t lanemask_lt() {
+	uint32_t m;
+	asm("mov.u32 %0, %%lanemask_lt;" : "=r"(m));
+	return m;
+}
+
+// ---------------------------------------------------------------------------------------------
+// key sources.  load2(row0, count, h0, h1) hashes rows row0 and row0+1 (row0 is even) and
+// returns a 2-bit validity (rows ≥ count are invalid and must not be read).
+// ---------------------------------------------------------------------------------------------
+struct FlatU64Src { // one flat int64 / uint64 column, no NULLs, base 16-byte aligned
+	const uint64_t *keys;
+	// unchecked: rows row0 + r*stride (+0,+1), r < R, all in range.  All R 128-bit loads are issued
+	// before the first hash so that they are in flight together.
+	template <int R>
+	__device__ __forceinline__ void load_rounds(uint64_t row0, uint64_t stride, uint64_t pol,
+	                                            uint64_t (&h)[2 * R]) const {
+		ulonglong2 k[R];
+#pragma unroll
+		for (int r = 0; r < R; r++) {
+			k[r] = ld_stream_v2(keys + row0 + r * stride, pol);
+		}
+#pragma unroll
+		for (int r = 0; r < R; r++) {
+			h[2 * r] = murmur64(k[r].x);
+			h[2 * r + 1] = murmur64(k[r].y);
+		}
+	}
+	__device__ __forceinline__ uint32_t load2(uint64_t row0, uint64_t count, uint64_t pol, uint64_t &h0,
+	                                          uint64_t &h1) const {
+		if (row0 + 1 < count) {
+			const ulonglong2 k = ld_stream_v2(keys + row0, pol);
+			h0 = murmur64(k.x);
+			h1 = murmur64(k.y);
+			return 3u;
+		}
+		h0 = h1 = 0;
+		if (row0 < count) {
+			h0 = murmur64(ld_stream_u64(keys + row0, pol));
+			return 1u;
+		}
+		return 0u;
+	}
+};
+
+struct GenericSrc { // any type / sel / validity / multi-column combination
+	DevCols cols;
+	template <int R>
+	__device__ __forceinline__ void load_rounds(uint64_t row0, uint64_t stride, uint64_t,
+	                                            uint64_t (&h)[2 * R]) const {
+#pragma unroll
+		for (int r = 0; r < R; r++) {
+			h[2 * r] = hash_row(cols, row0 + r * stride);
+			h[2 * r + 1] = hash_row(cols, row0 + r * stride + 1);
+		}
+	}
+	__device__ __forceinline__ uint32_t load2(uint64_t row0, uint64_t count, uint64_t, uint64_t &h0,
+	                                          uint64_t &h1) const {
+		uint32_t v = 0;
+		h0 = h1 = 0;
+		if (row0 < count) {
+			h0 = hash_row(cols, row0);
+			v = 1u;
+		}
+		if (row0 + 1 < count) {
+			h1 = hash_row(cols, row0 + 1);
+			v |= 2u;
+		}
+		return v;
+	}
+};
+
+// ---------------------------------------------------------------------------------------------
+// build
+// ---------------------------------------------------------------------------------------------
+constexpr int kBuildBlock = 256;
+constexpr int kBuildUnroll = 4;
+
+// AGG: lanes of a warp that hit the same sector OR their masks first and issue one atomic
+// (worth it only for small filters or duplicate-heavy keys).
+template <class Src, bool AGG>
+__global__ void __launch_bounds__(kBuildBlock)
+    build_kernel(const Src src, unsigned long long *__restrict__ filter, const uint64_t sector_mask,
+                 const uint64_t count) {
+	const uint64_t pol = policy_evict_first();
+	const uint64_t step = static_cast<uint64_t>(gridDim.x) * kBuildBlock * 2 * kBuildUnroll;
+	for (uint64_t base = static_cast<uint64_t>(blockIdx.x) * kBuildBlock * 2 * kBuildUnroll; base < count;
+	     base += step) {
+		uint64_t h[2 * kBuildUnroll];
+		uint32_t valid = 0;
+		if (base + static_cast<uint64_t>(kBuildBlock) * 2 * kBuildUnroll <= count) { // block-uniform
+			src.template load_rounds<kBuildUnroll>(base + threadIdx.x * 2, kBuildBlock * 2, pol, h);
+			valid = (1u << (2 * kBuildUnroll)) - 1u;
+		} else {
+#pragma unroll
+			for (int u = 0; u < kBuildUnroll; u++) {
+				const uint64_t row0 = base + static_cast<uint64_t>(u) * kBuildBlock * 2 + threadIdx.x * 2;
+				valid |= src.load2(row0, count, pol, h[2 * u], h[2 * u + 1]) << (2 * u);
+			}
+		}
+#pragma unroll
+		for (int i = 0; i < 2 * kBuildUnroll; i++) {
+			const bool v = (valid >> i) & 1u;
+			const uint64_t sector = h[i] & sector_mask;
+			uint64_t mask = sector_mask_of(h[i]);
+			if (AGG) {
+				// every lane takes part; invalid lanes use a sector id no valid lane can have
+				const uint64_t key = v ? sector : ~0ULL;
+				const uint32_t peers = __match_any_sync(0xffffffffu, key);
+				const uint32_t lo = __reduce_or_sync(peers, static_cast<uint32_t>(mask));
+				const uint32_t hi = __reduce_or_sync(peers, static_cast<uint32_t>(mask >> 32));
+				mask = (static_cast<uint64_t>(hi) << 32) | lo;
+				if (v && (__ffs(peers) - 1) == static_cast<int>(threadIdx.x & 31)) {
+					atomicOr(filter + sector, static_cast<unsigned long long>(mask));
+				}
+			} else if (v) {
+				atomicOr(filter + sector, static_cast<unsigned long long>(mask));
+			}
+		}
+	}
+}
+
+// ---------------------------------------------------------------------------------------------
+// probe: persistent CTAs take tiles in ticket order; per tile every thread owns ROUNDS×2 keys laid
+// out so that each warp reads ROUNDS contiguous 512-byte segments (fully coalesced 128-bit loads);
+// all 2·ROUNDS random filter loads of a thread are independent and in flight together; the tile's
+// survivor count is chained to its predecessors with a decoupled look-back (one 64-bit descriptor
+// per tile: status in bits 63:62, count in the low bits), which makes the compaction single-pass
+// and globally order-stable, as LookupHashes' scalar loop is.
+// ---------------------------------------------------------------------------------------------
+constexpr uint64_t kDescAggregate = 1ULL << 62;
+constexpr uint64_t kDescPrefix = 2ULL << 62;
+constexpr uint64_t kDescValue = (1ULL << 62) - 1;
+
+__device__ __forceinline__ uint32_t tile_lookback(uint64_t *desc, const uint64_t tile, const uint32_t lane,
+                                                  const uint32_t tile_count) {
+	if (lane == 0) {
+		st_relaxed_u64(desc + tile, (tile == 0 ? kDescPrefix : kDescAggregate) | tile_count);
+	}
+	if (tile == 0) {
+		return 0;
+	}
+	uint32_t exclusive = 0;
+	int64_t pos = static_cast<int64_t>(tile) - 1;
+	while (true) {
+		const int64_t idx = pos - static_cast<int64_t>(lane);
+		uint64_t d = kDescPrefix; // virtual predecessor of tile 0: inclusive prefix 0
+		if (idx >= 0) {
+			do {
+				d = ld_relaxed_u64(desc + idx);
+			} while ((d >> 62) == 0);
+		}
+		const uint32_t prefix_lanes = __ballot_sync(0xffffffffu, (d >> 62) == 2);
+		uint32_t v = static_cast<uint32_t>(d & kDescValue);
+		if (prefix_lanes) {
+			const uint32_t first = __ffs(prefix_lanes) - 1;
+			if (lane > first) {
+				v = 0;
+			}
+		}
+		exclusive += __reduce_add_sync(0xffffffffu, v);
+		if (prefix_lanes) {
+			break;
+		}
+		pos -= 32;
+	}
+	if (lane == 0) {
+		st_relaxed_u64(desc + tile, kDescPrefix | (static_cast<uint64_t>(exclusive) + tile_count));
+	}
+	return exclusive;
+}
+
+template <class Src, int ROUNDS, int BLOCK, bool SMEM_FILTER>
+__global__ void __launch_bounds__(BLOCK)
+    probe_kernel(const Src src, const uint64_t *__restrict__ filter, const uint64_t sector_mask, const uint64_t count,
+                 const uint64_t num_tiles, uint32_t *__restrict__ sel_out, uint64_t *__restrict__ found_out,
+                 const uint32_t row_offset, const uint32_t *__restrict__ translate, uint64_t *desc,
+                 unsigned int *ticket) {
+	constexpr int NWARPS = BLOCK / 32;
+	constexpr uint64_t WARP_KEYS = 64ull * ROUNDS;
+	constexpr uint64_t TILE_KEYS = WARP_KEYS * NWARPS;
+
+	extern __shared__ __align__(16) uint64_t s_filter[];
+	__shared__ uint32_t s_warp_off[NWARPS];
+	__shared__ uint32_t s_tile_excl;
+	__shared__ uint32_t s_tile;
+
+	const uint32_t lane = threadIdx.x & 31u;
+	const uint32_t warp = threadIdx.x >> 5;
+	const uint64_t pol_keys = policy_evict_first();
+	const uint64_t pol_filter = policy_evict_last();
+
+	if (SMEM_FILTER) {
+		const uint64_t nvec = (sector_mask + 1) >> 1;
+		const ulonglong2 *g = reinterpret_cast<const ulonglong2 *>(filter);
+		ulonglong2 *s = reinterpret_cast<ulonglong2 *>(s_filter);
+		for (uint64_t i = threadIdx.x; i < nvec; i += BLOCK) {
+			s[i] = __ldg(g + i);
+		}
+	}
+
+	while (true) {
+		if (threadIdx.x == 0) {
+			s_tile = atomicAdd(ticket, 1u);
+		}
+		__syncthreads(); // also publishes s_filter on the first pass
+		const uint64_t tile = s_tile;
+		if (tile >= num_tiles) {
+			break;
+		}
+		const uint64_t warp_base = tile * TILE_KEYS + warp * WARP_KEYS;
+
+		// 1. stream the keys and hash them
+		uint64_t h[2 * ROUNDS];
+		uint32_t valid = 0;
+		if ((tile + 1) * TILE_KEYS <= count) { // block-uniform: every tile but the last
+			src.template load_rounds<ROUNDS>(warp_base + lane * 2, 64, pol_keys, h);
+			valid = static_cast<uint32_t>((1ull << (2 * ROUNDS)) - 1ull);
+		} else {
+#pragma unroll
+			for (int r = 0; r < ROUNDS; r++) {
+				const uint64_t row0 = warp_base + static_cast<uint64_t>(r) * 64 + lane * 2;
+				valid |= src.load2(row0, count, pol_keys, h[2 * r], h[2 * r + 1]) << (2 * r);
+			}
+		}
+		// 2. all random filter loads of this thread, independent of each other
+		uint64_t w[2 * ROUNDS];
+#pragma unroll
+		for (int i = 0; i < 2 * ROUNDS; i++) {
+			const uint64_t sector = h[i] & sector_mask;
+			w[i] = SMEM_FILTER ? s_filter[sector] : ld_filter_word(filter + sector, pol_filter);
+		}
+		// 3. test
+		uint32_t hits = 0;
+#pragma unroll
+		for (int i = 0; i < 2 * ROUNDS; i++) {
+			const uint64_t m = sector_mask_of(h[i]);
+			hits |= static_cast<uint32_t>((w[i] & m) == m) << i;
+		}
+		hits &= valid;
+		// 4. survivors per warp → per tile → global exclusive offset
+		uint32_t warp_count = 0;
+#pragma unroll
+		for (int i = 0; i < 2 * ROUNDS; i++) {
+			warp_count += __popc(__ballot_sync(0xffffffffu, (hits >> i) & 1u));
+		}
+		if (lane == 0) {
+			s_warp_off[warp] = warp_count;
+		}
+		__syncthreads();
+		if (warp == 0) {
+			const uint32_t c = lane < NWARPS ? s_warp_off[lane] : 0u;
+			uint32_t incl = c;
+#pragma unroll
+			for (int d = 1; d < 32; d <<= 1) {
+				const uint32_t t = __shfl_up_sync(0xffffffffu, incl, d);
+				if (lane >= static_cast<uint32_t>(d)) {
+					incl += t;
+				}
+			}
+			const uint32_t tile_count = __shfl_sync(0xffffffffu, incl, 31);
+			if (lane < NWARPS) {
+				s_warp_off[lane] = incl - c;
+			}
+			const uint32_t excl = tile_lookback(desc, tile, lane, tile_count);
+			if (lane == 0) {
+				s_tile_excl = excl;
+				if (tile == num_tiles - 1) {
+					*found_out = static_cast<uint64_t>(excl) + tile_count;
+				}
+			}
+		}
+		__syncthreads();
+		// 5. ordered write: row order inside a warp segment is (round, lane, element)
+		uint32_t run = s_tile_excl + s_warp_off[warp];
+		const uint32_t lt = lanemask_lt();
+		const uint32_t rel_base = static_cast<uint32_t>(warp_base) + row_offset + lane * 2;
+#pragma unroll
+		for (int r = 0; r < ROUNDS; r++) {
+			const uint32_t h0 = (hits >> (2 * r)) & 1u;
+			const uint32_t h1 = (hits >> (2 * r + 1)) & 1u;
+			const uint32_t b0 = __ballot_sync(0xffffffffu, h0);
+			const uint32_t b1 = __ballot_sync(0xffffffffu, h1);
+			uint32_t pos = run + __popc(b0 & lt) + __popc(b1 & lt);
+			const uint32_t rel = rel_base + r * 64;
+			if (h0) {
+				sel_out[pos] = translate ? __ldg(translate + rel) : rel;
+			}
+			pos += h0;
+			if (h1) {
+				sel_out[pos] = translate ? __ldg(translate + rel + 1) : rel + 1;
+			}
+			run += __popc(b0) + __popc(b1);
+		}
+	}
+}
+
+// ---------------------------------------------------------------------------------------------
+// merge / misc kernels
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+    or_parts_kernel(ulonglong2 *__restrict__ words, const ulonglong2 *__restrict__ parts, const uint64_t nvec,
+                    const uint64_t nparts) {
+	const uint64_t step = static_cast<uint64_t>(gridDim.x) * blockDim.x;
+	for (uint64_t i = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < nvec; i += step) {
+		ulonglong2 acc = words[i];
+		for (uint64_t p = 0; p < nparts; p++) {
+			const ulonglong2 v = __ldg(parts + p * nvec + i);
+			acc.x |= v.x;
+			acc.y |= v.y;
+		}
+		words[i] = acc;
+	}
+}
+
+// Peer-memory leg: srcs.p[k] are other GPUs' filters mapped through CUDA IPC / peer access; the
+// loads cross NVLink (they bypass the local L2), the OR happens in registers, one local store.
+__global__ void __launch_bounds__(256)
+    or_ptrs_kernel(uint64_t *__restrict__ words, const PtrList srcs, const uint64_t off, const uint64_t len) {
+	const uint64_t nvec = len >> 1;
+	ulonglong2 *dst = reinterpret_cast<ulonglong2 *>(words + off);
+	const uint64_t step = static_cast<uint64_t>(gridDim.x) * blockDim.x;
+	for (uint64_t i = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < nvec; i += step) {
+		ulonglong2 acc = dst[i];
+		ulonglong2 v[16];
+#pragma unroll
+		for (int k = 0; k < 16; k++) {
+			if (k < srcs.n) {
+				v[k] = *(reinterpret_cast<const ulonglong2 *>(srcs.p[k] + off) + i);
+			}
+		}
+#pragma unroll
+		for (int k = 0; k < 16; k++) {
+			if (k < srcs.n) {
+				acc.x |= v[k].x;
+				acc.y |= v[k].y;
+			}
+		}
+		dst[i] = acc;
+	}
+}
+
+__global__ void __launch_bounds__(256)
+    lookup_hashes_kernel(const uint64_t *__restrict__ words, const uint64_t sector_mask,
+                         const uint64_t *__restrict__ hashes, const uint64_t count, uint8_t *__restrict__ hits) {
+	const uint64_t i = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+	if (i < count) {
+		const uint64_t h = hashes[i];
+		const uint64_t m = sector_mask_of(h);
+		hits[i] = (words[h & sector_mask] & m) == m;
+	}
+}
+
+__host__ __device__ __forceinline__ uint64_t splitmix64(uint64_t x) {
+	uint64_t z = x + 0x9e3779b97f4a7c15ULL;
+	z = (z ^ (z >> 30)) * 0xbf58476d1ce4e5b9ULL;
+	z = (z ^ (z >> 27)) * 0x94d049bb133111ebULL;
+	return z ^ (z >> 31);
+}
+
+__global__ void __launch_bounds__(256) synth_build_kernel(uint64_t *out, const uint64_t first, const uint64_t count) {
+	const uint64_t step = static_cast<uint64_t>(gridDim.x) * blockDim.x;
+	for (uint64_t i = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < count; i += step) {
+		out[i] = splitmix64(0xB10F0001ULL + first + i) & 0x7fffffffffffffffULL;
+	}
+}
+
+__global__ void __launch_bounds__(256) synth_probe_kernel(uint64_t *out, const uint64_t first, const uint64_t count,
+                                                          const uint64_t n_build, const uint32_t sel_ppm) {
+	const uint64_t step = static_cast<uint64_t>(gridDim.x) * blockDim.x;
+	for (uint64_t i = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < count; i += step) {
+		const uint64_t j = first + i;
+		const uint64_t a = splitmix64(0x9B0BE001ULL + 2 * j);
+		const uint64_t b = splitmix64(0x9B0BE001ULL + 2 * j + 1);
+		out[i] = (a % 1000000ULL < sel_ppm) ? (splitmix64(0xB10F0001ULL + (b % n_build)) & 0x7fffffffffffffffULL)
+		                                    : (b | 0x8000000000000000ULL);
+	}
+}
+
+// ---------------------------------------------------------------------------------------------
+// launchers
+// ---------------------------------------------------------------------------------------------
+constexpr int kProbeRounds = 8;    // 16 keys per thread
+constexpr int kProbeBlock = 256;   // global-filter variant: several CTAs per SM
+constexpr int kProbeBlockSmem = 512; // shared-memory variant: ≤128 KiB filter + 1 CTA per SM at the top size
+constexpr uint64_t kProbeTileKeys = 64ull * kProbeRounds * (kProbeBlock / 32);
+
+static inline uint64_t ceil_div(uint64_t a, uint64_t b) {
+	return (a + b - 1) / b;
+}
+
+// A single flat 8-byte integer column, 16-byte aligned, takes the vectorised source.
+static inline bool is_flat_u64(const DevCols &cols) {
+	if (cols.n != 1) {
+		return false;
+	}
+	const DevCol &c = cols.c[0];
+	return (c.type == RPT_INT64 || c.type == RPT_UINT64) && !c.sel && !c.validity &&
+	       (reinterpret_cast<uintptr_t>(c.data) & 15u) == 0;
+}
+
+static inline bool use_smem_filter(const DeviceInfo &dev, uint64_t num_sectors) {
+	return num_sectors <= kSmemFilterMaxSectors && num_sectors * 8 + 1024 <= dev.smem_optin;
+}
+
+size_t probe_scratch_bytes(uint64_t count) {
+	// the smaller tile gives the larger tile count; one extra slot holds the ticket counter
+	return (ceil_div(count, kProbeTileKeys) + 2) * sizeof(uint64_t);
+}
+
+template <class Src, bool AGG>
+static cudaError_t launch_build_t(const DeviceInfo &dev, const Src &src, uint64_t count, uint64_t *words,
+                                  uint64_t num_sectors, cudaStream_t stream) {
+	const uint64_t per_block = static_cast<uint64_t>(kBuildBlock) * 2 * kBuildUnroll;
+	int per_sm = 0;
+	cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, build_kernel<Src, AGG>, kBuildBlock, 0);
+	if (e != cudaSuccess) {
+		return e;
+	}
+	const uint64_t wave = static_cast<uint64_t>(dev.sm_count) * (per_sm > 0 ? per_sm : 1);
+	uint64_t grid = ceil_div(count, per_block);
+	if (grid > wave * 4) {
+		grid = wave * 4; // grid-stride over the rest; a multiple of SMs × resident CTAs
+	}
+	build_kernel<Src, AGG><<<static_cast<unsigned>(grid), kBuildBlock, 0, stream>>>(
+	    src, reinterpret_cast<unsigned long long *>(words), num_sectors - 1, count);
+	return cudaGetLastError();
+}
+
+cudaError_t launch_build(const DeviceInfo &dev, const DevCols &cols, uint64_t count, uint64_t *words,
+                         uint64_t num_sectors, cudaStream_t stream, int *launches) {
+	if (count == 0) {
+		return cudaSuccess;
+	}
+	if (launches) {
+		(*launches)++;
+	}
+	// warp-aggregate only where same-sector collisions inside a warp are likely
+	const bool agg = num_sectors <= 4096;
+	if (is_flat_u64(cols)) {
+		FlatU64Src src {reinterpret_cast<const uint64_t *>(cols.c[0].data)};
+		return agg ? launch_build_t<FlatU64Src, true>(dev, src, count, words, num_sectors, stream)
+		           : launch_build_t<FlatU64Src, false>(dev, src, count, words, num_sectors, stream);
+	}
+	GenericSrc src {cols};
+	return agg ? launch_build_t<GenericSrc, true>(dev, src, count, words, num_sectors, stream)
+	           : launch_build_t<GenericSrc, false>(dev, src, count, words, num_sectors, stream);
+}
+
+template <class Src, int BLOCK, bool SMEM>
+static cudaError_t launch_probe_t(const DeviceInfo &dev, const Src &src, uint64_t count, const uint64_t *words,
+                                  uint64_t num_sectors, uint32_t *sel_out, uint64_t *found_out, uint32_t row_offset,
+                                  const uint32_t *translate, void *scratch, cudaStream_t stream) {
+	auto kern = probe_kernel<Src, kProbeRounds, BLOCK, SMEM>;
+	const uint64_t tile_keys = 64ull * kProbeRounds * (BLOCK / 32);
+	const uint64_t num_tiles = ceil_div(count, tile_keys);
+	const size_t smem = SMEM ? num_sectors * sizeof(uint64_t) : 0;
+	cudaError_t e;
+	if (SMEM) {
+		e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
+		if (e != cudaSuccess) {
+			return e;
+		}
+	}
+	int per_sm = 0;
+	e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, BLOCK, smem);
+	if (e != cudaSuccess) {
+		return e;
+	}
+	if (per_sm < 1) {
+		return cudaErrorLaunchOutOfResources;
+	}
+	uint64_t grid = static_cast<uint64_t>(dev.sm_count) * per_sm; // persistent: every CTA is resident
+	if (grid > num_tiles) {
+		grid = num_tiles;
+	}
+	uint64_t *desc = reinterpret_cast<uint64_t *>(scratch);
+	unsigned int *ticket = reinterpret_cast<unsigned int *>(desc + num_tiles);
+	e = cudaMemsetAsync(scratch, 0, (num_tiles + 1) * sizeof(uint64_t), stream);
+	if (e != cudaSuccess) {
+		return e;
+	}
+	kern<<<static_cast<unsigned>(grid), BLOCK, smem, stream>>>(src, words, num_sectors - 1, count, num_tiles, sel_out,
+	                                                          found_out, row_offset, translate, desc, ticket);
+	return cudaGetLastError();
+}
+
+cudaError_t launch_probe(const DeviceInfo &dev, const DevCols &cols, uint64_t count, const uint64_t *words,
+                         uint64_t num_sectors, uint32_t *sel_out, uint64_t *found_out, uint32_t row_offset,
+                         const uint32_t *translate, void *scratch, cudaStream_t stream, int *launches) {
+	if (count == 0) {
+		return cudaMemsetAsync(found_out, 0, sizeof(uint64_t), stream);
+	}
+	if (launches) {
+		(*launches)++;
+	}
+	const bool smem = use_smem_filter(dev, num_sectors);
+	if (is_flat_u64(cols)) {
+		FlatU64Src src {reinterpret_cast<const uint64_t *>(cols.c[0].data)};
+		return smem ? launch_probe_t<FlatU64Src, kProbeBlockSmem, true>(dev, src, count, words, num_sectors, sel_out,
+		                                                              found_out, row_offset, translate, scratch,
+		                                                              stream)
+		            : launch_probe_t<FlatU64Src, kProbeBlock, false>(dev, src, count, words, num_sectors, sel_out,
+		                                                            found_out, row_offset, translate, scratch, stream);
+	}
+	GenericSrc src {cols};
+	return smem ? launch_probe_t<GenericSrc, kProbeBlockSmem, true>(dev, src, count, words, num_sectors, sel_out,
+	                                                              found_out, row_offset, translate, scratch, stream)
+	            : launch_probe_t<GenericSrc, kProbeBlock, false>(dev, src, count, words, num_sectors, sel_out,
+	                                                            found_out, row_offset, translate, scratch, stream);
+}
+
+static inline unsigned stream_grid(const DeviceInfo &dev, uint64_t items, unsigned block) {
+	const uint64_t want = ceil_div(items, block);
+	const uint64_t cap = static_cast<uint64_t>(dev.sm_count > 0 ? dev.sm_count : 148) * 8;
+	return static_cast<unsigned>(want < cap ? (want ? want : 1) : cap);
+}
+
+cudaError_t launch_or_parts(const DeviceInfo &dev, uint64_t *words, const uint64_t *parts, uint64_t num_sectors,
+                            uint64_t nparts, cudaStream_t stream) {
+	const uint64_t nvec = num_sectors >> 1;
+	or_parts_kernel<<<stream_grid(dev, nvec, 256), 256, 0, stream>>>(
+	    reinterpret_cast<ulonglong2 *>(words), reinterpret_cast<const ulonglong2 *>(parts), nvec, nparts);
+	return cudaGetLastError();
+}
+
+cudaError_t launch_or_ptrs(const DeviceInfo &dev, uint64_t *words, const PtrList &srcs, uint64_t off, uint64_t len,
+                           cudaStream_t stream) {
+	if (len == 0 || srcs.n == 0) {
+		return cudaSuccess;
+	}
+	or_ptrs_kernel<<<stream_grid(dev, len >> 1, 256), 256, 0, stream>>>(words, srcs, off, len);
+	return cudaGetLastError();
+}
+
+cudaError_t launch_lookup_hashes(const uint64_t *words, uint64_t num_sectors, const uint64_t *hashes, uint64_t count,
+                                 uint8_t *hits, cudaStream_t stream) {
+	if (count == 0) {
+		return cudaSuccess;
+	}
+	lookup_hashes_kernel<<<static_cast<unsigned>(ceil_div(count, 256)), 256, 0, stream>>>(words, num_sectors - 1,
+	                                                                                      hashes, count, hits);
+	return cudaGetLastError();
+}
+
+cudaError_t launch_synth_build(uint64_t *out, uint64_t first, uint64_t count, cudaStream_t stream) {
+	if (count == 0) {
+		return cudaSuccess;
+	}
+	const uint64_t want = ceil_div(count, 256);
+	synth_build_kernel<<<static_cast<unsigned>(want < 148 * 16 ? want : 148 * 16), 256, 0, stream>>>(out, first, count);
+	return cudaGetLastError();
+}
+
+cudaError_t launch_synth_probe(uint64_t *out, uint64_t first, uint64_t count, uint64_t n_build, uint32_t sel_ppm,
+                               cudaStream_t stream) {
+	if (count == 0) {
+		return cudaSuccess;
+	}
+	const uint64_t want = ceil_div(count, 256);
+	synth_probe_kernel<<<static_cast<unsigned>(want < 148 * 16 ? want : 148 * 16), 256, 0, stream>>>(
+	    out, first, count, n_build, sel_ppm);
+	return cudaGetLastError();
+}
+
+} // namespace rpt

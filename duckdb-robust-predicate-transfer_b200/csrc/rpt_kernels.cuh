@@ -1,0 +1,58 @@
+// rpt_kernels.cuh — launcher interface between the C ABI (rpt_capi.cu) and the sm_100a kernels
+// (rpt_kernels.cu).  Everything takes device pointers and a stream; nothing synchronises.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstdint>
+
+#include "rpt_hash.cuh"
+
+namespace rpt {
+
+struct DeviceInfo {
+	int device = -1;
+	int sm_count = 0;
+	int l2_bytes = 0;
+	size_t smem_optin = 0;
+};
+
+// Largest filter (in 64-bit sectors) that is staged in shared memory by the probe kernel.
+constexpr uint64_t kSmemFilterMaxSectors = 1ULL << 14; // 128 KiB
+
+// Scratch the probe kernel needs for `count` rows: tile descriptors + ticket counter (bytes).
+size_t probe_scratch_bytes(uint64_t count);
+
+// Build: filter[h & (S-1)] |= GetMask(h) for every row (InsertHashes, bloom_filter.cpp:43-48,63-70).
+cudaError_t launch_build(const DeviceInfo &dev, const DevCols &cols, uint64_t count, uint64_t *words,
+                         uint64_t num_sectors, cudaStream_t stream, int *launches);
+
+// Probe: ascending row ids of passing rows → sel_out, count → *found_out (LookupHashes,
+// bloom_filter.cpp:50-61,72-78).  `scratch` holds probe_scratch_bytes(count) bytes; it is zeroed
+// here.  row_offset is added to every emitted row id; translate (optional) maps a row id through
+// an incoming selection (BFTableFilter::Filter, bloom_filter.cpp:117-123).
+cudaError_t launch_probe(const DeviceInfo &dev, const DevCols &cols, uint64_t count, const uint64_t *words,
+                         uint64_t num_sectors, uint32_t *sel_out, uint64_t *found_out, uint32_t row_offset,
+                         const uint32_t *translate, void *scratch, cudaStream_t stream, int *launches);
+
+// words[i] |= parts[p*S + i] for p < nparts
+cudaError_t launch_or_parts(const DeviceInfo &dev, uint64_t *words, const uint64_t *parts, uint64_t num_sectors,
+                            uint64_t nparts, cudaStream_t stream);
+
+// words[off .. off+len) |= srcs[k][off .. off+len) for k < nsrc (peer-memory reduce-scatter-OR leg)
+struct PtrList {
+	const uint64_t *p[16];
+	int n;
+};
+cudaError_t launch_or_ptrs(const DeviceInfo &dev, uint64_t *words, const PtrList &srcs, uint64_t off, uint64_t len,
+                           cudaStream_t stream);
+
+// LookupOne on pre-hashed values (BFTableFilter::FilterValue / CheckStatistics)
+cudaError_t launch_lookup_hashes(const uint64_t *words, uint64_t num_sectors, const uint64_t *hashes, uint64_t count,
+                                 uint8_t *hits, cudaStream_t stream);
+
+// SURVEY §8(d) synthetic columns
+cudaError_t launch_synth_build(uint64_t *out, uint64_t first, uint64_t count, cudaStream_t stream);
+cudaError_t launch_synth_probe(uint64_t *out, uint64_t first, uint64_t count, uint64_t n_build, uint32_t sel_ppm,
+                               cudaStream_t stream);
+
+} // namespace rpt

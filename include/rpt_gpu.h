@@ -162,6 +162,8 @@ RPT_API int rpt_bf_import_words(rpt_bf_t *bf, const uint64_t *host_src, uint64_t
 RPT_API int rpt_bf_device_words(const rpt_bf_t *bf, uint64_t **dev_ptr_out);
 RPT_API int rpt_bf_sync(const rpt_bf_t *bf); /* wait for all work enqueued on the handle's own stream */
 RPT_API int rpt_bf_set_has_data(rpt_bf_t *bf, int has_data);
+/* Number of kernels this handle has launched so far (bench.py's gpu_launches evidence). */
+RPT_API int rpt_bf_launch_count(const rpt_bf_t *bf, long long *out);
 
 /* ---- multi-GPU OR-merge: partial filters built from row-range shards are merged
  *      with a bitwise OR; fetch_or is commutative/associative/idempotent (bloom_filter.cpp:69) so

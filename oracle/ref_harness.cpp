@@ -69,6 +69,8 @@ struct FakeVector {
 	explicit FakeVector(void *data) {
 		memset(raw, 0, sizeof(raw));
 		get().vector_type = VectorType::FLAT_VECTOR;
+		get().type.id_ = LogicalTypeId::UBIGINT; // LogicalType::HASH
+		get().type.physical_type_ = PhysicalType::UINT64;
 		get().data = reinterpret_cast<data_ptr_t>(data);
 	}
 	Vector &get() {
