@@ -1,0 +1,468 @@
+#!/usr/bin/env python
+"""bench.py — BASELINE.json's metric on BASELINE.json's config 2 (single-key int64 bloom build 100M keys /
+probe 1B keys, synthetic uniform, SURVEY §8d generators).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--sel-ppm 100000] [--impl reference]
+
+A step = one pass of the hot path: zero the filter, build it from the build column, (N>1: OR-merge the partial
+filters over NVLink), probe the probe column into a compacted, ordered selection vector.
+  value   whole-job Gkeys/s = (build keys + probe keys of all ranks) / step time, inputs resident in HBM,
+          CUDA-event timed, max over ranks.
+  e2e     the same step through the C ABI with HOST (pinned) key buffers and host selection-vector output:
+          H2D and D2H copies inside the timed region.
+  roofline  the probe kernel (dominant): algorithmic bytes 8·m + 4·found + F per launch ÷ its CUDA-event duration,
+          against MEASURED_PEAKS.json's HBM copy bandwidth.
+  cpu_baseline  the reference's own loops (oracle/_ref, compiled from the reference sources) or the C oracle port,
+          on the box's host cores, bounded sample (N=1, rank 0 only).
+N>1 (torchrun, one rank per GPU): the 100M-row build column is sharded by row range across ranks (each builds a
+partial filter, OR-merged over NVLink peer memory); every rank probes its own 1B-row shard of an N·1B-row probe
+column against the replicated filter.  Per-GPU probe work is fixed → "weak".
+
+--impl reference times the reference CPU implementation (same metric, bounded sample per step).
+The oracle/ directory is used only as the checker / CPU baseline, never on the measured GPU path.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+METRIC = "bloom build+probe throughput (build 100M int64 keys, probe 1B int64 keys per GPU)"
+UNIT = "Gkeys/s"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--build-rows", type=int, default=100_000_000)
+    ap.add_argument("--probe-rows", type=int, default=1_000_000_000, help="probe rows per GPU")
+    ap.add_argument("--sel-ppm", type=int, default=100_000, help="member fraction of the probe column in ppm (10 %%)")
+    ap.add_argument("--e2e-steps", type=int, default=2)
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--cpu-probe-sample", type=int, default=200_000_000)
+    ap.add_argument("--merge", default="auto", choices=["auto", "peer", "allgather"])
+    ap.add_argument("--sweep", action="store_true", help="also time probe at 1 %% and 50 %% selectivity and the "
+                    "L2-resident companion filter (reported under 'detail'; N=1 only)")
+    return ap.parse_args()
+
+
+def load_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            p = json.load(f)
+        return float(p["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled during the timed region (B200_PROFILING.md's clocks line)."""
+    FIELDS = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+              "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+              "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.FIELDS}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, power, reasons = [], [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            parts = [x.strip() for x in r.split(",")]
+            if len(parts) < 7:
+                continue
+            try:
+                sm.append(float(parts[0]))
+                mx.append(float(parts[1]))
+                power.append(float(parts[2]))
+            except ValueError:
+                continue
+            for name, val in zip(names, parts[3:7]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "power_w_max": max(power) if power else None, "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ---------------------------------------------------------------------------------------------------------
+# CPU arm: the reference's own loops (oracle/_ref) or the oracle port, on the host cores
+# ---------------------------------------------------------------------------------------------------------
+def cpu_run(args, steps, warmup):
+    """Returns (value Gkeys/s for the full workload shape, info dict).  One step = build ALL build rows into a
+    fresh filter + probe a bounded sample of the probe column; the probe time is scaled to the full row count."""
+    import numpy as np
+    import oracle_lib
+    oracle = oracle_lib.oracle()
+    ref = oracle_lib.ref()
+    kind = "reference" if ref is not None else "port"
+    eng = ref if ref is not None else oracle
+    cores = os.cpu_count() or 1
+    n, m = args.build_rows, args.probe_rows
+    ms = min(m, args.cpu_probe_sample)
+    keys = oracle.synth_build_keys(0, n).view(np.int64)
+    probe = oracle.synth_probe_keys(0, ms, n, args.sel_ppm).view(np.int64)
+    S = oracle.num_sectors(n)
+    tb, tp, found = [], [], 0
+    for it in range(warmup + steps):
+        words = np.zeros(S, dtype=np.uint64)
+        t0 = time.perf_counter()
+        b = eng.bench_build(words, keys, cores)
+        p, found = eng.bench_probe(words, probe, cores)
+        _ = time.perf_counter() - t0
+        if it >= warmup:
+            tb.append(b)
+            tp.append(p)
+    tb_med = sorted(tb)[len(tb) // 2]
+    tp_med = sorted(tp)[len(tp) // 2]
+    t_full = tb_med + tp_med * (m / ms)
+    value = (n + m) / t_full / 1e9
+    info = {"value": value, "unit": UNIT, "cores": cores, "kind": kind,
+            "sample": f"build all {n} keys on {cores} threads into one shared {S * 8 >> 20} MiB filter (median "
+                      f"{tb_med:.3f} s) + probe the first {ms} of {m} probe rows (median {tp_med:.3f} s, scaled x"
+                      f"{m / ms:.1f}); 2048-row chunks, relaxed fetch_or, private selection buffers",
+            "build_gkeys_s": n / tb_med / 1e9, "probe_gkeys_s": ms / tp_med / 1e9,
+            "probe_sample_found": int(found)}
+    return value, t_full, info
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    steps, warmup = max(1, args.steps), max(0, args.warmup)
+    value, t_full, info = cpu_run(args, steps, warmup)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": steps, "warmup": warmup,
+        "ms_per_step": t_full * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "u64", "data": "synthetic",
+        "config": workload_config(args, 1), "cpu_baseline": info,
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+    return 0
+
+
+def workload_config(args, world):
+    return {"workload": "config 2: single-key int64 bloom build 100M keys / probe 1B keys, synthetic uniform "
+                        "(SURVEY §8d splitmix64 generators)",
+            "build_rows_total": args.build_rows, "probe_rows_per_gpu": args.probe_rows,
+            "member_fraction_ppm": args.sel_ppm, "filter_sectors": None, "filter_mib": None,
+            "sharding": f"build column row-range sharded over {world} rank(s), OR-merged; probe shard-local",
+            "l2_policy": "inputs larger than L2 (8 GB key column + 256 MiB filter per step); no flush needed"}
+
+
+# ---------------------------------------------------------------------------------------------------------
+# GPU arm
+# ---------------------------------------------------------------------------------------------------------
+def run_b200(args):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+
+    import rpt_b200 as rpt
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus and world > 1:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}")
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: librpt_gpu has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    rpt.lib()  # fails loudly when the extension is missing
+
+    n, m, ppm = args.build_rows, args.probe_rows, args.sel_ppm
+    lo, hi = rpt.shard_range(n, world, rank)
+    n_local = hi - lo
+    probe_first = rank * m
+
+    stream = torch.cuda.current_stream()
+    sh = stream.cuda_stream
+    dk = torch.empty(max(n_local, 2), dtype=torch.int64, device=dev)
+    dp = torch.empty(m, dtype=torch.int64, device=dev)
+    rpt.synth_build_keys(dk, lo, n_local, device=local_rank, stream=sh)
+    rpt.synth_probe_keys(dp, probe_first, m, n, ppm, device=local_rank, stream=sh)
+    dsel = torch.empty(m, dtype=torch.int32, device=dev)
+    dfound = torch.zeros(1, dtype=torch.int64, device=dev)
+    torch.cuda.synchronize()
+
+    sb = rpt.ShardedBloomFilter(device=local_rank, merge=args.merge).Initialize(n)
+    S = sb.num_sectors
+    F = S * 8
+    build_col = rpt.device_col(dk, rpt.INT64)
+    probe_col = rpt.device_col(dp, rpt.INT64)
+
+    def step(ev=None):
+        sb.Reset(n, sh)                       # zero-fill (BloomFilter::Initialize)
+        sb.Insert(build_col, n_local, sh)     # build kernel
+        if ev:
+            ev[1].record(stream)
+        sb.Merge(sh)                          # N>1: OR-allreduce over NVLink
+        if ev:
+            ev[2].record(stream)
+        sb.LookupSelDevice(probe_col, m, dsel, dfound, sh)  # probe kernel
+        if ev:
+            ev[3].record(stream)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        step()
+    barrier()
+    found = int(dfound.item())
+    launches0 = sb.launch_count
+
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    evs = [[torch.cuda.Event(enable_timing=True) for _ in range(4)] for _ in range(args.steps)]
+    t_start = torch.cuda.Event(enable_timing=True)
+    t_end = torch.cuda.Event(enable_timing=True)
+    barrier()
+    t_start.record(stream)
+    for k in range(args.steps):
+        evs[k][0].record(stream)
+        step(evs[k])
+    t_end.record(stream)
+    barrier()
+    clocks = sampler.stop()
+    total_ms = t_start.elapsed_time(t_end)
+    build_ms = sum(e[0].elapsed_time(e[1]) for e in evs) / args.steps
+    merge_ms = sum(e[1].elapsed_time(e[2]) for e in evs) / args.steps
+    probe_ms = sum(e[2].elapsed_time(e[3]) for e in evs) / args.steps
+    launches = sb.launch_count - launches0
+
+    # max over ranks
+    def max_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    total_ms = max_over_ranks(total_ms)
+    probe_ms_max = max_over_ranks(probe_ms)
+    build_ms_max = max_over_ranks(build_ms)
+    merge_ms_max = max_over_ranks(merge_ms)
+    ms_per_step = total_ms / args.steps
+    keys_per_step = n + world * m
+    value = keys_per_step / (ms_per_step * 1e-3) / 1e9
+
+    # ---- parity spot-check inside the bench run (not timed): property checks on this rank's results ----
+    sel = dsel[:found]
+    ordered = bool((sel[1:] > sel[:-1]).all()) if found > 1 else True
+    member = dp >= 0
+    members = int(member.sum().item())
+    members_kept = int(member[sel.long()].sum().item())
+    del member, sel
+    parity = {"sel_strictly_ascending": ordered, "members": members, "members_kept": members_kept,
+              "found": found, "false_positive_rate": (found - members_kept) / max(m - members, 1)}
+    if not ordered or members != members_kept:
+        raise SystemExit(f"bench parity check failed on rank {rank}: {parity}")
+
+    # ---- roofline of the dominant kernel (probe) ----
+    peak, peak_src = load_peaks()
+    algo_bytes = 8 * m + 4 * found + F
+    achieved = algo_bytes / (probe_ms * 1e-3) / 1e9
+    roofline = {"kernel": "probe_kernel<FlatU64Src,8,256,false>", "bound": "hbm", "achieved": achieved, "peak": peak,
+                "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                "algorithmic_bytes_per_launch": algo_bytes, "launch_ms": probe_ms,
+                "bytes_per_key": algo_bytes / m,
+                "build": {"algorithmic_bytes_per_launch": 8 * n_local + 2 * F, "ms": build_ms,
+                          "achieved": (8 * n_local + 2 * F) / (build_ms * 1e-3) / 1e9,
+                          "frac": (8 * n_local + 2 * F) / (build_ms * 1e-3) / 1e9 / peak,
+                          "note": "zero-fill + build kernel; random 8-byte atomics, not a streaming kernel"}}
+    traffic_path = os.path.join(ROOT, "profiles", "probe_traffic.json")
+    if os.path.exists(traffic_path):
+        try:
+            with open(traffic_path) as f:
+                tr = json.load(f)
+            roofline["traffic"] = tr.get("dram_bytes_per_launch")
+            roofline["traffic_source"] = tr.get("source")
+        except Exception:
+            pass
+
+    detail = {"build_ms": build_ms_max, "merge_ms": merge_ms_max, "probe_ms": probe_ms_max,
+              "build_gkeys_s": n / (build_ms_max * 1e-3) / 1e9,
+              "probe_gkeys_s": world * m / (probe_ms_max * 1e-3) / 1e9,
+              "found_rank0": found, "filter_sectors": S, "filter_mib": F >> 20, "parity": parity}
+
+    # ---- optional sweep (N=1): other selectivities, L2-resident companion ----
+    if args.sweep and world == 1:
+        detail["sweep"] = sweep(rpt, torch, dev, local_rank, sb, dp, dsel, dfound, n, m, sh, stream, peak)
+
+    # ---- e2e: host buffers through the C ABI, copies inside the timed region ----
+    e2e = None
+    if not args.no_e2e:
+        e2e = run_e2e(args, rpt, torch, dist, dev, local_rank, world, rank, sb, dk, dp, n, m, n_local, sh, barrier,
+                      max_over_ranks, found)
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        del dk, dp, dsel
+        torch.cuda.empty_cache()
+        try:
+            _, _, cpu = cpu_run(args, steps=1, warmup=0)
+        except Exception as exc:  # the baseline must not take the GPU numbers down with it
+            cpu = {"value": None, "unit": UNIT, "cores": os.cpu_count(), "kind": "port", "sample": f"failed: {exc}"}
+
+    if rank == 0:
+        cfg = workload_config(args, world)
+        cfg["filter_sectors"], cfg["filter_mib"] = S, F >> 20
+        cfg["merge"] = sb.merge if world > 1 else "none"
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "u64", "data": "synthetic", "config": cfg,
+            "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline,
+            "cpu_baseline": cpu, "detail": detail,
+        }
+        print(json.dumps(line))
+    sb.close()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+def sweep(rpt, torch, dev, local_rank, sb, dp, dsel, dfound, n, m, sh, stream, peak):
+    out = {}
+    probe_col = rpt.device_col(dp, rpt.INT64)
+    F = sb.num_sectors * 8
+
+    def time_probe(bf, reps=5):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        for _ in range(2):
+            bf.LookupSelDevice(probe_col, m, dsel, dfound, sh)
+        torch.cuda.synchronize()
+        e0.record(stream)
+        for _ in range(reps):
+            bf.LookupSelDevice(probe_col, m, dsel, dfound, sh)
+        e1.record(stream)
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / reps, int(dfound.item())
+
+    for ppm in (10_000, 500_000):
+        rpt.synth_probe_keys(dp, 0, m, n, ppm, device=local_rank, stream=sh)
+        ms, found = time_probe(sb)
+        b = 8 * m + 4 * found + F
+        out[f"probe_sel_{ppm // 10000}pct"] = {"ms": ms, "gkeys_s": m / ms / 1e6, "found": found,
+                                               "achieved_gbs": b / ms / 1e6, "frac": b / ms / 1e6 / peak}
+    # L2-resident companion (SURVEY §8d "2-L2"): n = 10^7 → S = 2^21, F = 16 MiB
+    n2 = 10_000_000
+    dk2 = torch.empty(n2, dtype=torch.int64, device=dev)
+    rpt.synth_build_keys(dk2, 0, n2, device=local_rank, stream=sh)
+    rpt.synth_probe_keys(dp, 0, m, n2, 100_000, device=local_rank, stream=sh)
+    small = rpt.PTBloomFilter(local_rank).Initialize(n2)
+    small.Insert(rpt.device_col(dk2, rpt.INT64), n2, sh)
+    ms, found = time_probe(small)
+    b = 8 * m + 4 * found + small.num_sectors * 8
+    out["probe_l2_resident_16MiB_10pct"] = {"ms": ms, "gkeys_s": m / ms / 1e6, "found": found,
+                                            "achieved_gbs": b / ms / 1e6, "frac": b / ms / 1e6 / peak}
+    small.close()
+    rpt.synth_probe_keys(dp, 0, m, n, 100_000, device=local_rank, stream=sh)
+    torch.cuda.synchronize()
+    return out
+
+
+def run_e2e(args, rpt, torch, dist, dev, local_rank, world, rank, sb, dk, dp, n, m, n_local, sh, barrier,
+            max_over_ranks, found_device):
+    """Host (pinned) key buffers in, host selection vector out, every step: the call a DuckDB operator makes."""
+    import numpy as np
+    hk = rpt.PinnedArray(max(n_local, 1), np.int64)
+    hp = rpt.PinnedArray(m, np.int64)
+    hsel = rpt.PinnedArray(m, np.uint32)
+    # fill the host buffers from the device-generated columns (not timed)
+    cudart = torch.cuda.cudart()
+    torch.cuda.synchronize()
+    hk_t = torch.from_numpy(hk.array)
+    hp_t = torch.from_numpy(hp.array)
+    if n_local:
+        hk_t.copy_(dk[:n_local])
+    hp_t.copy_(dp)
+    torch.cuda.synchronize()
+    del cudart
+    build_col = rpt.host_col(hk.array[:n_local] if n_local else hk.array[:0])
+    probe_col = rpt.KeyCol(rpt.RptCol(hp.ptr, None, None, None, m, 0, rpt.INT64, rpt.MEM_HOST), (hp,))
+    import ctypes as C
+    found = C.c_uint64(0)
+
+    def step():
+        sb.Reset(n, sh)
+        torch.cuda.current_stream().synchronize()
+        sb.Insert(build_col, n_local)                 # H2D of the build shard + build kernels
+        sb.Merge(None)
+        rpt._check(rpt.lib().rpt_bf_probe(sb.bf._h, C.byref(probe_col.raw), 1, m, hsel.ptr, C.addressof(found),
+                                          rpt.MEM_HOST, None))  # H2D keys, probe kernels, D2H selection vector
+
+    step()  # warm-up (pinned staging, allocator pools)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.e2e_steps):
+        step()
+    barrier()
+    dt = (time.perf_counter() - t0) / args.e2e_steps
+    dt = max_over_ranks(dt)
+    if found.value != found_device:
+        raise SystemExit(f"e2e parity: host path found {found.value}, device path {found_device}")
+    keys_per_step = n + world * m
+    out = {"value": keys_per_step / dt / 1e9, "unit": UNIT, "ms_per_step": dt * 1e3,
+           "h2d_bytes_per_step": 8 * n_local + 8 * m, "d2h_bytes_per_step": 4 * int(found.value) + 8,
+           "steps": args.e2e_steps,
+           "note": "per rank: pinned host key columns → rpt_bf_insert / rpt_bf_probe (C ABI, RPT_MEM_HOST) → host "
+                   "selection vector; PCIe-bound"}
+    hk.free()
+    hp.free()
+    hsel.free()
+    return out
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+    return run_b200(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -52,6 +52,7 @@ _SIGNATURES = {
     "rpt_host_free": (C.c_int, [C.c_void_p]),
     "rpt_bf_create": (C.c_int, [C.POINTER(C.c_void_p), C.c_uint64, C.c_int]),
     "rpt_bf_destroy": (C.c_int, [C.c_void_p]),
+    "rpt_bf_reset": (C.c_int, [C.c_void_p, C.c_uint64, C.c_void_p]),
     "rpt_bf_num_sectors": (C.c_int, [C.c_void_p, C.POINTER(C.c_uint64)]),
     "rpt_bf_sized_for_rows": (C.c_int, [C.c_void_p, C.POINTER(C.c_uint64)]),
     "rpt_bf_is_empty": (C.c_int, [C.c_void_p, C.POINTER(C.c_int)]),
@@ -192,6 +193,11 @@ class PTBloomFilter:
         self.close()
         est = int(est_num_rows) & 0xFFFFFFFF  # the reference's parameter is uint32_t: estimates wrap
         _check(lib().rpt_bf_create(C.byref(self._h), est, self.device))
+        return self
+
+    def Reset(self, est_num_rows, stream=None):
+        """Initialize again on the live handle (zero-fill is asynchronous when the size is unchanged)."""
+        _check(lib().rpt_bf_reset(self._h, int(est_num_rows) & 0xFFFFFFFF, stream))
         return self
 
     def close(self):
@@ -352,3 +358,6 @@ class PinnedArray:
             self.array = None
             lib().rpt_host_free(self.ptr)
             self.ptr = None
+
+
+from .sharded import ShardedBloomFilter, shard_range  # noqa: E402,F401

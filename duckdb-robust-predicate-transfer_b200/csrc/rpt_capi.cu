@@ -454,6 +454,27 @@ int rpt_bf_destroy(rpt_bf_t *bf) {
 	return 0;
 }
 
+int rpt_bf_reset(rpt_bf_t *bf, uint64_t est_rows, rpt_stream_t stream) {
+	if (!bf) {
+		return set_error("null filter handle");
+	}
+	RPT_GUARD(bf);
+	uint64_t s;
+	RPT_TRY(sectors_for_rows(est_rows, &s));
+	if (s != bf->num_sectors || !bf->words) {
+		if (stream) {
+			RPT_CUDA(cudaStreamSynchronize(reinterpret_cast<cudaStream_t>(stream)));
+		}
+		RPT_TRY(allocate_words(bf, est_rows));
+	} else {
+		bf->sized_for_rows = est_rows;
+		RPT_CUDA(cudaMemsetAsync(bf->words, 0, s * sizeof(uint64_t), pick_stream(bf, stream)));
+	}
+	bf->has_data.store(0);
+	bf->finalized.store(0);
+	return 0;
+}
+
 #define RPT_GETTER(name, type, expr)                                                                                   \
 	int name(const rpt_bf_t *bf, type *out) {                                                                          \
 		if (!bf || !out) {                                                                                             \

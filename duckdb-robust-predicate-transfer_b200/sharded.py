@@ -1,0 +1,218 @@
+"""Row-range sharded build / replicated probe across ranks: one process per GPU.
+
+The reference has no distributed path (single process, N sink threads sharing one filter through relaxed
+fetch_or, duckdb/src/planner/filter/bloom_filter.cpp:63-70).  fetch_or is commutative, associative and
+idempotent, so the same words result when every rank inserts its contiguous row range into a private
+full-size filter and the partial filters are OR-merged:
+
+    rank r: Insert(rows [n·r/N, n·(r+1)/N))  →  OR-allreduce of the S words  →  every rank holds the
+    filter a single process would have built  →  each rank probes its own row range; selection vectors
+    are row-ordered inside a shard, and shards are contiguous, so concatenating them with the shard's base
+    row offset reproduces LookupHashes' ascending order (bloom_filter.cpp:56-59).
+
+The resize rule (physical_create_bf.cpp:386-406) needs the GLOBAL row count: a SUM all-reduce of one scalar.
+
+torch.distributed is plumbing only (rendezvous, barriers, the scalar all-reduce, the handle exchange).
+The merge itself is the library's: `peer` = two-phase reduce-scatter-OR + all-gather over NVLink peer
+memory (rpt_bf_peer_*), `allgather` = NCCL all-gather of the partial filters + one OR kernel
+(rpt_bf_or_parts).  NCCL has no bitwise-OR reduction, hence no plain all_reduce.
+
+`engine` is the object that provides PTBloomFilter; the default is this package (CUDA, no CPU fallback).
+The CPU test-suite injects an oracle-backed stand-in so that the host logic here runs under gloo.
+"""
+import numpy as np
+
+
+def shard_range(total_rows, world_size, rank):
+    """Contiguous row range [lo, hi) of `rank`; lo is a multiple of 64 (validity words, 128-bit key loads and
+    probe tiles stay aligned) except that the last shard ends at total_rows."""
+    if not 0 <= rank < world_size:
+        raise ValueError("rank out of range")
+    def cut(r):
+        if r >= world_size:
+            return total_rows
+        return min(total_rows, (total_rows * r // world_size) & ~63)
+    return cut(rank), cut(rank + 1)
+
+
+class _DeviceWords:
+    """Zero-copy view of the filter words for torch (CUDA array interface)."""
+
+    def __init__(self, ptr, n):
+        self.__cuda_array_interface__ = {"shape": (int(n),), "typestr": "<i8", "data": (int(ptr), False),
+                                         "version": 2}
+
+
+class ShardedBloomFilter:
+    """One rank's replica of a filter that is built from row-range shards and probed shard-locally.
+    Method names follow the reference's PTBloomFilter (src/include/bloom_filter.hpp:22-57)."""
+
+    def __init__(self, group=None, device=0, engine=None, merge="auto"):
+        import torch.distributed as dist
+        self.dist = dist
+        self.group = group
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        if engine is None:
+            import importlib
+            engine = importlib.import_module(__package__)
+        self.engine = engine
+        self.device = device
+        self.bf = engine.PTBloomFilter(device)
+        if merge == "auto":
+            merge = "peer" if (self.world > 1 and dist.get_backend(group) == "nccl") else "allgather"
+        if merge not in ("peer", "allgather"):
+            raise ValueError("merge must be 'auto', 'peer' or 'allgather'")
+        self.merge = merge
+        self._peer_open_for = None
+        self.merged = False
+
+    # -- plumbing ------------------------------------------------------------------------------------
+    def _scalar_device(self):
+        import torch
+        return torch.device("cuda", self.device) if self.dist.get_backend(self.group) == "nccl" else torch.device("cpu")
+
+    def _allreduce_sum(self, value):
+        if self.world == 1:
+            return int(value)
+        import torch
+        t = torch.tensor([int(value)], dtype=torch.int64, device=self._scalar_device())
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.SUM, group=self.group)
+        return int(t.item())
+
+    def device_barrier(self):
+        """Cross-rank barrier ordered on the current torch stream, without blocking the host: every rank's
+        earlier stream work is complete before any rank's later stream work starts."""
+        if self.world == 1:
+            return
+        import torch
+        if not hasattr(self, "_token"):
+            self._token = torch.zeros(1, dtype=torch.int32, device=self._scalar_device())
+        self.dist.all_reduce(self._token, group=self.group)
+
+    # -- PTBloomFilter surface ------------------------------------------------------------------------
+    def Initialize(self, est_num_rows):
+        """est_num_rows is the GLOBAL estimate (the optimizer's cardinality), the same on every rank, so S is too."""
+        self.bf.Initialize(est_num_rows)
+        self._peer_open_for = None
+        self.merged = False
+        return self
+
+    def Reset(self, est_num_rows, stream=None):
+        before = self.bf.device_words if hasattr(self.bf, "device_words") else None
+        self.bf.Reset(est_num_rows, stream)
+        after = self.bf.device_words if hasattr(self.bf, "device_words") else None
+        if before != after:
+            self._peer_open_for = None
+        self.merged = False
+        return self
+
+    def Insert(self, cols, count, stream=None):
+        """Inserts this rank's shard of the build column."""
+        self.bf.Insert(cols, count, stream)
+        self.merged = False
+
+    def Merge(self, stream=None):
+        """OR-allreduce of the partial filters.  `stream` must be the current torch stream (or None when the
+        caller synchronises): the barriers are enqueued on torch's current stream."""
+        if self.world == 1:
+            self.merged = True
+            return
+        import torch
+        any_data = self._allreduce_sum(0 if self.bf.IsEmpty() else 1)
+        on_gpu = self.dist.get_backend(self.group) == "nccl"
+        blocking = stream is None
+        if blocking and on_gpu:
+            self.bf.Sync()  # work enqueued on the handle's own stream
+            stream = torch.cuda.current_stream().cuda_stream
+        if self.merge == "peer":
+            words = self.bf.device_words
+            if self._peer_open_for != words:
+                blob = torch.frombuffer(bytearray(self.bf.IpcExport()), dtype=torch.uint8).cuda(self.device)
+                allb = torch.empty(self.world * 64, dtype=torch.uint8, device=blob.device)
+                self.dist.all_gather_into_tensor(allb, blob, group=self.group)
+                raw = allb.cpu().numpy().tobytes()
+                self.bf.PeerOpen([raw[64 * r:64 * (r + 1)] for r in range(self.world)], self.rank)
+                self._peer_open_for = words
+            self.device_barrier()                 # every partial filter is complete
+            self.bf.PeerMergePhase(0, stream)     # my slice |= peers' copies of my slice (NVLink reads)
+            self.device_barrier()                 # every slice is reduced
+            self.bf.PeerMergePhase(1, stream)     # pull the other ranks' reduced slices
+            self.device_barrier()                 # nobody still reads my words
+        else:
+            mine = self._words_tensor()
+            parts = torch.empty(self.world * mine.numel(), dtype=mine.dtype, device=mine.device)
+            self.dist.all_gather_into_tensor(parts, mine, group=self.group)
+            self.bf.OrParts(parts, self.world, stream)
+            self._parts = parts  # keep alive until the OR kernel has run
+        if blocking and on_gpu:
+            torch.cuda.current_stream().synchronize()
+        if any_data:
+            self.bf.SetHasData(True)
+        self.merged = True
+
+    def _words_tensor(self):
+        """The S words as a tensor the collective backend can send (device view for NCCL; engines that keep
+        their words on the host expose `words_tensor`)."""
+        if hasattr(self.bf, "words_tensor"):
+            return self.bf.words_tensor()
+        import torch
+        self.bf.Sync()
+        return torch.as_tensor(_DeviceWords(self.bf.device_words, self.bf.num_sectors),
+                               device=torch.device("cuda", self.device))
+
+    def Finalize(self, local_rows, cols=None, count=0, stream=None):
+        """Resize rule on the GLOBAL row count, rebuild of every shard when it fires, merge, finalize.
+        Returns True when the filter was rebuilt (rpt_bf_finalize's rebuilt_out)."""
+        actual_rows = self._allreduce_sum(local_rows)
+        rebuilt = self.bf.NeedsRebuild(actual_rows)
+        if rebuilt:
+            if cols is None:
+                raise self.engine.RptError("the resize rule fires but no key columns were given to rehash from")
+            # ReinitializeAndRehash(actual_rows) on every rank: same new S everywhere
+            self.bf.ReinitializeAndRehash(actual_rows, cols, count, stream)
+            self._peer_open_for = None
+            self.merged = False
+        if not self.merged:
+            self.Merge(stream)
+        self.bf.Finalize(actual_rows)  # rule cannot fire any more; sets finalized_
+        return rebuilt
+
+    def LookupSel(self, cols, count):
+        """Shard-local probe: row ids relative to the shard."""
+        return self.bf.LookupSel(cols, count)
+
+    def GatherSelection(self, local_sel, row_base):
+        """Concatenates the shards' selection vectors in rank order with their base offsets → the global
+        ascending selection (as uint64 row ids; the global row count may exceed sel_t's 2^32)."""
+        import torch
+        mine = torch.from_numpy(np.asarray(local_sel, dtype=np.int64) + int(row_base))
+        if self.world == 1:
+            return mine.numpy().astype(np.uint64)
+        dev = self._scalar_device()
+        counts = torch.zeros(self.world, dtype=torch.int64, device=dev)
+        counts[self.rank] = mine.numel()
+        self.dist.all_reduce(counts, group=self.group)
+        counts = counts.cpu().tolist()
+        cap = max(max(counts), 1)
+        padded = torch.zeros(cap, dtype=torch.int64, device=dev)
+        padded[:mine.numel()] = mine.to(dev)
+        allp = torch.empty(self.world * cap, dtype=torch.int64, device=dev)
+        self.dist.all_gather_into_tensor(allp, padded, group=self.group)
+        allp = allp.cpu().numpy()
+        return np.concatenate([allp[r * cap:r * cap + counts[r]] for r in range(self.world)]).astype(np.uint64)
+
+    # passthroughs
+    def __getattr__(self, name):
+        if name in ("num_sectors", "finalized_", "launch_count", "device_words", "IsEmpty", "SizedForRows",
+                    "ExportWords", "LookupSelDevice", "FilterSel", "LookupHashes", "Sync", "NeedsRebuild"):
+            return getattr(self.bf, name)
+        raise AttributeError(name)
+
+    def close(self):
+        if self._peer_open_for is not None and hasattr(self.bf, "PeerClose"):
+            try:
+                self.bf.PeerClose()
+            except Exception:
+                pass
+        self.bf.close()

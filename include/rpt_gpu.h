@@ -102,6 +102,10 @@ RPT_API int rpt_host_free(void *ptr);
  * the caller wraps, the library sizes: S = min(NextPow2(max(512, 12*est_rows)) >> 6, 2^26). */
 RPT_API int rpt_bf_create(rpt_bf_t **out, uint64_t est_rows, int device);
 RPT_API int rpt_bf_destroy(rpt_bf_t *bf);
+/* PTBloomFilter::Initialize called again on a live object (what ReinitializeAndRehash does first,
+ * src/bloom_filter.cpp:38-40): re-size for est_rows, zero the words, clear has_data_ and finalized_.
+ * When S is unchanged nothing is reallocated and the zero-fill is asynchronous on `stream`. */
+RPT_API int rpt_bf_reset(rpt_bf_t *bf, uint64_t est_rows, rpt_stream_t stream);
 RPT_API int rpt_bf_num_sectors(const rpt_bf_t *bf, uint64_t *out);    /* BloomFilter::num_sectors */
 RPT_API int rpt_bf_sized_for_rows(const rpt_bf_t *bf, uint64_t *out); /* PTBloomFilter::SizedForRows */
 RPT_API int rpt_bf_is_empty(const rpt_bf_t *bf, int *out);            /* PTBloomFilter::IsEmpty (!has_data_) */

@@ -1,0 +1,650 @@
+"""GPU suite (-m gpu): the CUDA path, called through the C ABI (librpt_gpu.so), against the CPU oracle.
+
+Bit-exact everywhere: filter words are compared with array_equal (memcmp), selection vectors element-wise.
+The oracle itself is pinned to the reference by tests/test_oracle_cpu.py; the committed golden vectors
+(tests/golden/ref_vectors.json, produced by the reference's own sources) are checked here directly as well.
+Nothing here reads /root/reference.
+"""
+import numpy as np
+import pytest
+
+from helpers import NP, fnv_words, from_hex, hx, load_json, synth_build_keys, synth_probe_keys
+
+pytestmark = pytest.mark.gpu
+
+KA = load_json("known_answers.json")
+RV = load_json("ref_vectors.json")
+
+
+@pytest.fixture(scope="module")
+def torch_cuda():
+    import torch
+    assert torch.cuda.is_available(), "the gpu suite needs a CUDA device"
+    torch.cuda.set_device(0)
+    return torch
+
+
+def gpu_filter(rpt, est):
+    return rpt.PTBloomFilter(0).Initialize(est)
+
+
+def check_build_probe(rpt, oracle, est, build_cols, n, probe_cols, m):
+    """Insert n rows, compare the words; probe m rows, compare the selection vector."""
+    bf = gpu_filter(rpt, est)
+    words = oracle.new_filter(est & 0xFFFFFFFF)
+    assert bf.num_sectors == words.shape[0]
+    assert bf.IsEmpty()
+    bf.Insert(build_cols, n)
+    oracle.insert(words, build_cols, n)
+    assert bf.IsEmpty() == (n == 0)
+    got = bf.ExportWords()
+    assert np.array_equal(got, words), "filter words differ from the oracle"
+    sel = bf.LookupSel(probe_cols, m)
+    want = oracle.probe(words, probe_cols, m)
+    assert sel.shape == want.shape and np.array_equal(sel, want), "selection vector differs from the oracle"
+    bf.close()
+    return words, want
+
+
+# ---------------------------------------------------------------------------------------------------------
+# known answers and golden vectors of the reference
+# ---------------------------------------------------------------------------------------------------------
+def test_known_masks_single_key(rpt):
+    """One key → exactly GetMask(Hash(key)) in word Hash(key) & (S-1)."""
+    for k, m in KA["mask_int64"].items():
+        h = int(KA["hash_int64"][k], 16)
+        bf = gpu_filter(rpt, 1)  # S = 8
+        bf.Insert(rpt.host_col(np.array([int(k)], dtype=np.int64)), 1)
+        words = bf.ExportWords()
+        want = np.zeros(8, dtype=np.uint64)
+        want[h & 7] = int(m, 16)
+        assert np.array_equal(words, want), k
+        bf.close()
+
+
+def test_known_null_hash(rpt):
+    bf = gpu_filter(rpt, 1)
+    col = rpt.host_col(np.array([7], dtype=np.int64), validity=np.array([0], dtype=np.uint64))
+    bf.Insert(col, 1)
+    words = bf.ExportWords()
+    h = int(KA["null_hash"], 16)
+    hi = h >> 32
+    mask = (1 << (hi & 63)) | (1 << ((hi >> 8) & 63)) | (1 << ((hi >> 16) & 63)) | (1 << ((hi >> 24) & 63))
+    want = np.zeros(8, dtype=np.uint64)
+    want[h & 7] = mask
+    assert np.array_equal(words, want)
+    bf.close()
+
+
+def test_known_filter_100k(rpt, oracle):
+    """est 100000, keys 2i → S=32768; probing 0..10^6-1 leaves 102353 rows."""
+    f = KA["filters"][0]
+    keys = 2 * np.arange(f["n_keys"], dtype=np.int64)
+    probe = np.arange(f["probe_range"], dtype=np.int64)
+    words, sel = check_build_probe(rpt, oracle, f["est_rows"], rpt.host_col(keys), keys.size, rpt.host_col(probe),
+                                   probe.size)
+    assert words.shape[0] == f["num_sectors"]
+    assert sel.size == f["survivors"]
+
+
+def test_golden_filters(rpt):
+    """Filters and selection vectors made by the reference's own InsertHashes/LookupHashes (ref_vectors.json)."""
+    for f in RV["filters"]:
+        keys = synth_build_keys(0, f["n_keys"])
+        probe = synth_probe_keys(0, f["n_probe"], max(f["n_keys"], 1), f["sel_ppm"])
+        bf = gpu_filter(rpt, f["est_rows"])
+        assert bf.num_sectors == f["num_sectors"]
+        bf.Insert(rpt.host_col(keys), keys.size)
+        assert hx(fnv_words(bf.ExportWords())) == f["fnv1a_words"]
+        sel = bf.LookupSel(rpt.host_col(probe), probe.size)
+        assert sel.size == f["survivors"]
+        assert hx(fnv_words(sel.astype(np.uint64))) == f["sel_fnv"]
+        assert sel[:8].tolist() == f["sel_head"] and sel[-8:].tolist() == f["sel_tail"]
+        bf.close()
+
+
+def golden_vector_cols(rpt):
+    v = RV["vector"]
+    n, dlen = v["n"], v["dlen"]
+    c0 = rpt.host_col(from_hex(v["data_i64"], np.int64), sel=from_hex(v["sel"], np.uint32),
+                      validity=from_hex(v["validity"], np.uint64), data_len=dlen)
+    c1 = rpt.host_col(from_hex(v["data_i32"], np.int32), validity=from_hex(v["validity_i32"], np.uint64))
+    c2 = rpt.host_varchar_col(from_hex(v["str_offsets"], np.uint32), from_hex(v["str_bytes"], np.uint8))
+    return n, c0, c1, c2
+
+
+def test_golden_vector_hashes(rpt, oracle):
+    """The reference's TightLoopHash/CombineHash outputs (sel + validity + 3-column combine) → the filter
+    built from those hashes must equal the filter the GPU builds from the raw columns."""
+    v = RV["vector"]
+    n, c0, c1, c2 = golden_vector_cols(rpt)
+    for cols, key in (([c0], "hash_c0"), ([c0, c1], "hash_c0_c1"), ([c2], "hash_c2"), ([c1, c2, c0], "hash_c1_c2_c0")):
+        hashes = from_hex(v[key], np.uint64)
+        want = oracle.new_filter(n)
+        oracle.insert_hashes(want, hashes)
+        bf = gpu_filter(rpt, n)
+        bf.Insert(cols, n)
+        assert np.array_equal(bf.ExportWords(), want), key
+        # and LookupHashes on the pre-hashed values agrees: every inserted hash is found
+        assert bf.LookupHashes(hashes).all()
+        bf.close()
+
+
+def test_golden_scalar_hashes(rpt, oracle):
+    """Per-type Hash<T> golden values: a filter of S=8 sectors built from value i alone has word/mask of hash i."""
+    for t, entry in RV["scalars"].items():
+        t = int(t)
+        raw = bytes.fromhex(entry["bytes"])
+        hashes = np.array([int(h, 16) for h in entry["hashes"]], dtype=np.uint64)
+        if t in NP:
+            vals = np.frombuffer(raw, dtype=NP[t]).copy()
+            col = rpt.host_col(vals, type=t)
+        else:
+            vals = np.frombuffer(raw, dtype=np.uint64).reshape(-1, 2).copy()
+            col = rpt.host_col(vals, type=t)
+        n = vals.shape[0]
+        want = oracle.new_filter(n)
+        oracle.insert_hashes(want, hashes)
+        bf = gpu_filter(rpt, n)
+        bf.Insert(col, n)
+        assert np.array_equal(bf.ExportWords(), want), f"physical type {t}"
+        bf.close()
+
+
+def test_golden_strings(rpt, oracle):
+    strs = [bytes.fromhex(s["hex"]) for s in RV["strings"]]
+    hashes = np.array([int(s["hash"], 16) for s in RV["strings"]], dtype=np.uint64)
+    offs, data = rpt.strings_to_arrow(strs)
+    n = len(strs)
+    want = oracle.new_filter(n)
+    oracle.insert_hashes(want, hashes)
+    bf = gpu_filter(rpt, n)
+    bf.Insert(rpt.host_varchar_col(offs, data), n)
+    assert np.array_equal(bf.ExportWords(), want)
+    bf.close()
+
+
+# ---------------------------------------------------------------------------------------------------------
+# differential against the oracle: every physical type, selections, validity, multi-column keys
+# ---------------------------------------------------------------------------------------------------------
+def random_values(rng, t, n):
+    dt = NP[t]
+    if t == 1:
+        return rng.integers(0, 2, size=n, dtype=np.int8)
+    if np.issubdtype(dt, np.integer):
+        ii = np.iinfo(dt)
+        return rng.integers(ii.min, ii.max, size=n, dtype=dt, endpoint=True)
+    bits = rng.integers(0, 2 ** (8 * np.dtype(dt).itemsize), size=n, dtype=np.uint32 if dt == np.float32 else np.uint64)
+    # random bit patterns include NaNs, denormals, infinities; sprinkle ±0
+    bits[::17] = 0
+    bits[5::17] = 1 << (8 * np.dtype(dt).itemsize - 1)
+    return bits.view(dt)
+
+
+@pytest.mark.parametrize("t", sorted(NP))
+def test_types_flat(rpt, oracle, t):
+    rng = np.random.default_rng(100 + t)
+    n, m = 20011, 50021
+    keys = random_values(rng, t, n)
+    probe = np.concatenate([keys[rng.integers(0, n, size=m // 3)], random_values(rng, t, m - m // 3)])
+    rng.shuffle(probe)
+    check_build_probe(rpt, oracle, n, rpt.host_col(keys, type=t), n, rpt.host_col(probe, type=t), m)
+
+
+@pytest.mark.parametrize("t", [203, 204, 21])
+def test_types_16_byte(rpt, oracle, t):
+    rng = np.random.default_rng(200 + t)
+    n, m = 9001, 30011
+    keys = rng.integers(0, 2**64, size=(n, 2), dtype=np.uint64)
+    if t == 21:
+        iv = np.zeros(n, dtype=[("m", "<i4"), ("d", "<i4"), ("us", "<i8")])
+        iv["m"] = rng.integers(-2**31, 2**31 - 1, n)
+        iv["d"] = rng.integers(-2**31, 2**31 - 1, n)
+        iv["us"] = rng.integers(-2**62, 2**62, n)
+        keys = iv.view(np.uint64).reshape(n, 2).copy()
+    probe = np.concatenate([keys[rng.integers(0, n, size=m // 2)],
+                            rng.integers(0, 2**64, size=(m - m // 2, 2), dtype=np.uint64)])
+    check_build_probe(rpt, oracle, n, rpt.host_col(keys, type=t), n, rpt.host_col(probe, type=t), m)
+
+
+@pytest.mark.parametrize("t", [9, 7, 5, 12])
+def test_sel_and_validity(rpt, oracle, t):
+    """Dictionary-style vectors: rows read data[sel[i]], NULL where the validity bit of sel[i] is clear;
+    NULL rows are inserted and probed with NULL_HASH like any value (vector_hash.cpp:16-23)."""
+    rng = np.random.default_rng(300 + t)
+    dlen, n, m = 777, 10007, 40009
+    data = random_values(rng, t, dlen)
+    sel = rng.integers(0, dlen, size=n, dtype=np.uint32)
+    validity = rng.integers(0, 2**64, size=(dlen + 63) // 64, dtype=np.uint64)
+    build = rpt.host_col(data, type=t, sel=sel, validity=validity, data_len=dlen)
+    pdata = np.concatenate([data, random_values(rng, t, dlen)])
+    psel = rng.integers(0, 2 * dlen, size=m, dtype=np.uint32)
+    pvalid = rng.integers(0, 2**64, size=(2 * dlen + 63) // 64, dtype=np.uint64)
+    probe = rpt.host_col(pdata, type=t, sel=psel, validity=pvalid, data_len=2 * dlen)
+    check_build_probe(rpt, oracle, n, build, n, probe, m)
+    # validity without a selection (flat vector with NULLs), chunk-unaligned sizes
+    v2 = rng.integers(0, 2**64, size=(n + 63) // 64, dtype=np.uint64)
+    k2 = random_values(rng, t, n)
+    check_build_probe(rpt, oracle, n, rpt.host_col(k2, type=t, validity=v2), n, rpt.host_col(k2, type=t), n)
+
+
+def random_strings(rng, n, max_len=40):
+    lens = rng.integers(0, max_len + 1, size=n)
+    blob = rng.integers(0, 256, size=int(lens.sum()), dtype=np.uint8)
+    offs = np.zeros(n + 1, dtype=np.uint32)
+    offs[1:] = np.cumsum(lens)
+    return offs, blob
+
+
+def test_varchar(rpt, oracle):
+    rng = np.random.default_rng(41)
+    n, m = 30011, 60013
+    offs, blob = random_strings(rng, n)
+    poffs, pblob = random_strings(rng, m, max_len=3)  # short strings collide with short build strings
+    check_build_probe(rpt, oracle, n, rpt.host_varchar_col(offs, blob), n, rpt.host_varchar_col(poffs, pblob), m)
+    # probing the build column itself: no false negatives, identity selection
+    bf = gpu_filter(rpt, n)
+    bf.Insert(rpt.host_varchar_col(offs, blob), n)
+    assert np.array_equal(bf.LookupSel(rpt.host_varchar_col(offs, blob), n), np.arange(n, dtype=np.uint32))
+    bf.close()
+
+
+def make_string_t(strs):
+    """duckdb::string_t array (string_type.hpp:24): {uint32 len, char prefix[4], char* ptr} or 12 inlined bytes."""
+    n = len(strs)
+    arr = np.zeros(n * 16, dtype=np.uint8)
+    keep = []
+    for i, s in enumerate(strs):
+        arr[i * 16:i * 16 + 4] = np.frombuffer(np.uint32(len(s)).tobytes(), dtype=np.uint8)
+        if len(s) <= 12:
+            arr[i * 16 + 4:i * 16 + 4 + len(s)] = np.frombuffer(s, dtype=np.uint8)
+        else:
+            buf = np.frombuffer(s, dtype=np.uint8).copy()
+            keep.append(buf)
+            arr[i * 16 + 4:i * 16 + 8] = buf[:4]
+            arr[i * 16 + 8:i * 16 + 16] = np.frombuffer(np.uint64(buf.ctypes.data).tobytes(), dtype=np.uint8)
+    return arr, keep
+
+
+def test_string_t_host_layout(rpt, oracle):
+    """RPT_STRING_T: the library gathers DuckDB's 16-byte string_t entries itself (hash.cpp:115-151 hashes the
+    inlined and the pointer form identically)."""
+    rng = np.random.default_rng(43)
+    n = 5003
+    offs, blob = random_strings(rng, n, max_len=30)
+    strs = [blob[offs[i]:offs[i + 1]].tobytes() for i in range(n)]
+    arr, keep = make_string_t(strs)
+    col = rpt.KeyCol(rpt.RptCol(arr.ctypes.data, None, None, None, n, 0, rpt.STRING_T, rpt.MEM_HOST), (arr, keep))
+    want = oracle.new_filter(n)
+    oracle.insert(want, [rpt.host_varchar_col(offs, blob)], n)
+    bf = gpu_filter(rpt, n)
+    bf.Insert(col, n)
+    assert np.array_equal(bf.ExportWords(), want)
+    assert np.array_equal(bf.LookupSel(col, n), np.arange(n, dtype=np.uint32))
+    bf.close()
+
+
+def test_multi_column_keys(rpt, oracle):
+    """HashColumns with >1 column (src/bloom_filter.cpp:11-24): Hash(col0) then CombineHash per column."""
+    rng = np.random.default_rng(47)
+    n, m = 15013, 45007
+    a = rng.integers(-50, 50, size=n, dtype=np.int64)
+    b = rng.integers(0, 100, size=n, dtype=np.int32)
+    offs, blob = random_strings(rng, n, max_len=2)
+    va = rng.integers(0, 2**64, size=(n + 63) // 64, dtype=np.uint64)
+    build = [rpt.host_col(a, validity=va), rpt.host_col(b), rpt.host_varchar_col(offs, blob)]
+    pa = rng.integers(-50, 50, size=m, dtype=np.int64)
+    pb = rng.integers(0, 100, size=m, dtype=np.int32)
+    poffs, pblob = random_strings(rng, m, max_len=2)
+    probe = [rpt.host_col(pa), rpt.host_col(pb), rpt.host_varchar_col(poffs, pblob)]
+    check_build_probe(rpt, oracle, n, build, n, probe, m)
+    check_build_probe(rpt, oracle, n, build[:2], n, probe[:2], m)
+
+
+# ---------------------------------------------------------------------------------------------------------
+# sizes and edges
+# ---------------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("n", [0, 1, 2, 3, 31, 32, 33, 63, 64, 65, 511, 512, 513, 4095, 4096, 4097, 8191, 8192, 8193])
+def test_ragged_counts(rpt, oracle, n):
+    rng = np.random.default_rng(500 + n)
+    keys = rng.integers(-2**63, 2**63 - 1, size=max(n, 1), dtype=np.int64)[:n]
+    m = n + 5
+    probe = np.concatenate([keys, rng.integers(-2**63, 2**63 - 1, size=5, dtype=np.int64)])
+    check_build_probe(rpt, oracle, 64, rpt.host_col(keys) if n else rpt.host_col(np.zeros(1, np.int64)), n,
+                      rpt.host_col(probe), m)
+
+
+def test_empty_probe_and_empty_filter(rpt):
+    bf = gpu_filter(rpt, 1000)
+    assert bf.IsEmpty() and not bf.finalized_
+    keys = np.arange(100, dtype=np.int64)
+    assert bf.LookupSel(rpt.host_col(keys), 0).size == 0           # count == 0
+    assert bf.LookupSel(rpt.host_col(keys), 100).size == 0         # all-zero words pass nothing
+    bf.Insert(rpt.host_col(keys), 0)                               # no-op keeps has_data_ false
+    assert bf.IsEmpty()
+    assert not bf.Finalize(0)
+    assert bf.finalized_
+    bf.close()
+
+
+@pytest.mark.parametrize("est,n", [(10, 10), (1300, 1300), (21845, 21845), (21846, 21846), (200000, 200000),
+                                   (3000000, 3000000)])
+def test_filter_sizes(rpt, oracle, est, n):
+    """Shared-memory-staged filters (S ≤ 2^14), the boundary to global filters, and L2-sized filters."""
+    keys = synth_build_keys(0, n)
+    m = min(4 * n + 1000, 4000003)
+    probe = synth_probe_keys(0, m, n, 250000)
+    check_build_probe(rpt, oracle, est, rpt.host_col(keys), n, rpt.host_col(probe), m)
+
+
+def test_duplicate_heavy_keys_small_filter(rpt, oracle):
+    """Warp-aggregated atomics path: many lanes of a warp hit the same sector."""
+    rng = np.random.default_rng(59)
+    keys = rng.integers(0, 50, size=100003, dtype=np.int64)
+    probe = rng.integers(0, 200, size=100003, dtype=np.int64)
+    check_build_probe(rpt, oracle, 40, rpt.host_col(keys), keys.size, rpt.host_col(probe), probe.size)
+
+
+def test_host_chunk_boundaries(rpt, oracle):
+    """Host columns are uploaded in 2^24-row chunks; survivors of chunk c are offset by c·2^24."""
+    n = (1 << 24) + 12345
+    keys = synth_build_keys(0, n)
+    m = (1 << 25) + 777
+    probe = synth_probe_keys(0, m, n, 100000)
+    v = np.full((n + 63) // 64, 0xFFFFFFFFFFFFFFFF, dtype=np.uint64)
+    v[::5] = 0xFFFF0000FFFF0000
+    check_build_probe(rpt, oracle, n, rpt.host_col(keys, validity=v), n, rpt.host_col(probe), m)
+
+
+def test_unaligned_key_pointer(rpt, oracle):
+    """An int64 column whose base is only 8-byte aligned cannot take the 128-bit path."""
+    base = synth_build_keys(0, 100001)
+    keys = base[1:]
+    assert keys.ctypes.data % 16 == 8 or base.ctypes.data % 16 == 8
+    check_build_probe(rpt, oracle, keys.size, rpt.host_col(keys), keys.size, rpt.host_col(base[3:]), base.size - 3)
+
+
+# ---------------------------------------------------------------------------------------------------------
+# resize rule, scan-side probe, pre-hashed lookups
+# ---------------------------------------------------------------------------------------------------------
+def test_finalize_resize_rule(rpt, oracle):
+    """physical_create_bf.cpp:386-406 + ReinitializeAndRehash (src/bloom_filter.cpp:34-58)."""
+    n = 50000
+    keys = synth_build_keys(0, n)
+    col = rpt.host_col(keys)
+    bf = gpu_filter(rpt, 1000)                       # under-estimate: 16384 bits < 8 bits/key · 50000
+    bf.Insert(col, n)
+    assert bf.NeedsRebuild(n) == oracle.needs_rebuild(1000, n) == True  # noqa: E712
+    with pytest.raises(rpt.RptError):
+        bf.Finalize(n)                               # the rule fires but there is nothing to rehash from
+    assert bf.Finalize(n, col, n)
+    assert bf.finalized_ and bf.SizedForRows() == n
+    want = oracle.new_filter(n)
+    oracle.insert(want, [col], n)
+    assert bf.num_sectors == want.shape[0]
+    assert np.array_equal(bf.ExportWords(), want)
+    bf.close()
+    bf = gpu_filter(rpt, n)                          # good estimate: untouched
+    bf.Insert(col, n)
+    assert not bf.Finalize(n, col, n)
+    assert np.array_equal(bf.ExportWords(), want)
+    # never shrinks: far fewer rows than estimated keeps the allocation
+    assert not bf.NeedsRebuild(10)
+    bf.close()
+
+
+def test_uint32_estimate_wrap(rpt, oracle):
+    """PTBloomFilter::Initialize takes uint32_t est_num_rows (bloom_filter.hpp:25): 2^32+100 sizes like 100."""
+    bf = gpu_filter(rpt, 2**32 + 100)
+    assert bf.num_sectors == oracle.num_sectors(100) == 32
+    assert bf.SizedForRows() == 100
+    bf.close()
+
+
+def test_filter_sel_scan_side(rpt, oracle):
+    """BFTableFilter::Filter (duckdb bloom_filter.cpp:94-131): keys read through an incoming selection, output
+    translated back through it."""
+    rng = np.random.default_rng(61)
+    n, rows = 20000, 70001
+    keys = synth_build_keys(0, n)
+    bf = gpu_filter(rpt, n)
+    bf.Insert(rpt.host_col(keys), n)
+    words = bf.ExportWords()
+    column = synth_probe_keys(0, rows, n, 300000)
+    in_sel = np.sort(rng.choice(rows, size=30011, replace=False)).astype(np.uint32)
+    got = bf.FilterSel(rpt.host_col(column), in_sel, in_sel.size)
+    flat = oracle.probe(words, [rpt.host_col(column[in_sel])], in_sel.size)
+    assert np.array_equal(got, in_sel[flat])
+    got = bf.FilterSel(rpt.host_col(column), None, rows)
+    assert np.array_equal(got, oracle.probe(words, [rpt.host_col(column)], rows))
+    bf.close()
+
+
+def test_lookup_prehashed(rpt, oracle):
+    """BloomFilter::LookupOne on hashes (BFTableFilter::FilterValue / CheckStatistics :138-169)."""
+    n = 3000
+    keys = np.arange(1000, 1000 + n, dtype=np.int64)
+    bf = gpu_filter(rpt, n)
+    bf.Insert(rpt.host_col(keys), n)
+    words = bf.ExportWords()
+    span = np.arange(0, 2049, dtype=np.int64)
+    hashes = oracle.hash_columns([rpt.host_col(span)], span.size)
+    hits = bf.LookupHashes(hashes)
+    sel = oracle.lookup_hashes(words, hashes)
+    want = np.zeros(span.size, dtype=bool)
+    want[sel] = True
+    assert np.array_equal(hits, want)
+    bf.close()
+
+
+def test_import_export_roundtrip(rpt, oracle):
+    """A filter built by CPU sink threads can be uploaded and probed on the GPU, and vice versa."""
+    n = 40000
+    keys = synth_build_keys(0, n)
+    words = oracle.new_filter(n)
+    oracle.insert(words, [rpt.host_col(keys)], n)
+    bf = gpu_filter(rpt, n)
+    bf.ImportWords(words)
+    assert not bf.IsEmpty()
+    probe = synth_probe_keys(0, 100000, n, 100000)
+    assert np.array_equal(bf.LookupSel(rpt.host_col(probe), probe.size),
+                          oracle.probe(words, [rpt.host_col(probe)], probe.size))
+    assert np.array_equal(bf.ExportWords(), words)
+    bf.close()
+
+
+# ---------------------------------------------------------------------------------------------------------
+# device-resident columns (the benchmark path) and the synthetic generators
+# ---------------------------------------------------------------------------------------------------------
+def test_device_columns_and_generators(rpt, oracle, torch_cuda):
+    torch = torch_cuda
+    n, m = 1000003, 5000011
+    dk = torch.empty(n, dtype=torch.int64, device="cuda")
+    dp = torch.empty(m, dtype=torch.int64, device="cuda")
+    rpt.synth_build_keys(dk, 0, n)
+    rpt.synth_probe_keys(dp, 0, m, n, 100000)
+    torch.cuda.synchronize()
+    keys = dk.cpu().numpy().view(np.uint64)
+    probe = dp.cpu().numpy().view(np.uint64)
+    assert np.array_equal(keys, oracle.synth_build_keys(0, n))
+    assert np.array_equal(probe, oracle.synth_probe_keys(0, m, n, 100000))
+    bf = gpu_filter(rpt, n)
+    bf.Insert(rpt.device_col(dk, rpt.INT64), n)
+    want = oracle.new_filter(n)
+    oracle.insert(want, [rpt.host_col(keys)], n)
+    assert np.array_equal(bf.ExportWords(), want)
+    dsel = torch.empty(m, dtype=torch.int32, device="cuda")
+    dfound = torch.zeros(1, dtype=torch.int64, device="cuda")
+    bf.LookupSelDevice(rpt.device_col(dp, rpt.INT64), m, dsel, dfound)
+    bf.Sync()
+    found = int(dfound.item())
+    sel = dsel[:found].cpu().numpy().view(np.uint32)
+    assert np.array_equal(sel, oracle.probe(want, [rpt.host_col(probe)], m))
+    # device keys → host outputs
+    assert np.array_equal(bf.LookupSel(rpt.device_col(dp, rpt.INT64), m), sel)
+    # a device column whose base is only 8-byte aligned cannot take the 128-bit loads
+    got = bf.LookupSel(rpt.device_col(dp[1:], rpt.INT64), m - 1)
+    assert np.array_equal(got, sel[sel > 0] - 1)
+    bf2 = gpu_filter(rpt, n)
+    bf2.Insert(rpt.device_col(dk[1:], rpt.INT64), n - 1)
+    bf2.Insert(rpt.device_col(dk[:1], rpt.INT64), 1)
+    assert np.array_equal(bf2.ExportWords(), want)
+    bf2.close()
+    bf.close()
+
+
+def test_device_varchar_and_validity(rpt, oracle, torch_cuda):
+    torch = torch_cuda
+    rng = np.random.default_rng(71)
+    n = 200003
+    offs, blob = random_strings(rng, n, max_len=25)
+    valid = rng.integers(0, 2**64, size=(n + 63) // 64, dtype=np.uint64)
+    pad = np.concatenate([blob, np.zeros(8, dtype=np.uint8)])
+    d_off = torch.from_numpy(offs.view(np.int32)).cuda()
+    d_blob = torch.from_numpy(pad).cuda()
+    d_val = torch.from_numpy(valid.view(np.int64)).cuda()
+    col = rpt.device_col(d_off, rpt.VARCHAR, validity=d_val, aux=d_blob, aux_bytes=blob.size, data_len=n)
+    hcol = rpt.host_varchar_col(offs, blob, validity=valid)
+    bf = gpu_filter(rpt, n)
+    bf.Insert(col, n)
+    want = oracle.new_filter(n)
+    oracle.insert(want, [hcol], n)
+    assert np.array_equal(bf.ExportWords(), want)
+    assert np.array_equal(bf.LookupSel(col, n), np.arange(n, dtype=np.uint32))
+    bf.close()
+
+
+# ---------------------------------------------------------------------------------------------------------
+# OR-merge of partial filters (multi-GPU path) on one device
+# ---------------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("nparts", [2, 3, 8])
+def test_sharded_build_equals_single_build(rpt, oracle, torch_cuda, nparts):
+    """N row-range shards → N partial filters → OR → byte-identical to the 1-shard build."""
+    torch = torch_cuda
+    n = 300007
+    keys = synth_build_keys(0, n)
+    want = oracle.new_filter(n)
+    oracle.insert(want, [rpt.host_col(keys)], n)
+    bounds = [n * r // nparts for r in range(nparts + 1)]
+    parts = []
+    for r in range(nparts):
+        p = gpu_filter(rpt, n)
+        shard = keys[bounds[r]:bounds[r + 1]]
+        p.Insert(rpt.host_col(shard), shard.size)
+        parts.append(p)
+    S = want.shape[0]
+    # all-gather layout: nparts·S contiguous words
+    gathered = torch.empty(nparts * S, dtype=torch.int64, device="cuda")
+    for r, p in enumerate(parts):
+        gathered[r * S:(r + 1) * S] = torch.from_numpy(p.ExportWords().view(np.int64)).cuda()
+    merged = gpu_filter(rpt, n)
+    merged.OrParts(gathered, nparts)
+    assert np.array_equal(merged.ExportWords(), want)
+    # in-place peer merge between handles that live on the same device
+    rpt.allreduce_or(parts)
+    for p in parts:
+        assert np.array_equal(p.ExportWords(), want)
+        assert not p.IsEmpty()
+        p.close()
+    merged.close()
+
+
+# ---------------------------------------------------------------------------------------------------------
+# full-size configuration (BASELINE.json config 2): known answer + size-independent properties
+# ---------------------------------------------------------------------------------------------------------
+def test_config2_known_answer_full_size(rpt, torch_cuda):
+    """est n=10^8, keys 2i (i<10^8) → S=2^25; probing 0..2·10^8-1 leaves 100 242 750 rows —
+    a number produced by the compiled reference itself (PTBloomFilter through libduckdb)."""
+    torch = torch_cuda
+    f = KA["filters"][1]
+    n, m = f["n_keys"], f["probe_range"]
+    dk = torch.arange(0, 2 * n, 2, dtype=torch.int64, device="cuda")
+    dp = torch.arange(0, m, dtype=torch.int64, device="cuda")
+    bf = gpu_filter(rpt, f["est_rows"])
+    assert bf.num_sectors == f["num_sectors"]
+    bf.Insert(rpt.device_col(dk, rpt.INT64), n)
+    dsel = torch.empty(m, dtype=torch.int32, device="cuda")
+    dfound = torch.zeros(1, dtype=torch.int64, device="cuda")
+    bf.LookupSelDevice(rpt.device_col(dp, rpt.INT64), m, dsel, dfound)
+    bf.Sync()
+    found = int(dfound.item())
+    assert found == f["survivors"]
+    sel = dsel[:found]
+    # properties: strictly ascending; every member (even row id) survives; probing the survivors again keeps all
+    assert bool((sel[1:] > sel[:-1]).all())
+    assert int((sel % 2 == 0).sum().item()) == n
+    survivors = dp[sel.long()]
+    dsel2 = torch.empty(found, dtype=torch.int32, device="cuda")
+    bf.LookupSelDevice(rpt.device_col(survivors, rpt.INT64), found, dsel2, dfound)
+    bf.Sync()
+    assert int(dfound.item()) == found
+    assert bool((dsel2 == torch.arange(found, dtype=torch.int32, device="cuda")).all())
+    bf.close()
+
+
+def test_config2_full_size_against_oracle(rpt, oracle, torch_cuda):
+    """Config 2 at BASELINE.json's sizes: 10^8-key build compared word for word with the (threaded) oracle;
+    the 10^9-row probe compared exactly on two 2·10^7-row windows, and through properties on the whole."""
+    torch = torch_cuda
+    n, m, ppm = 10**8, 10**9, 100000
+    dk = torch.empty(n, dtype=torch.int64, device="cuda")
+    rpt.synth_build_keys(dk, 0, n)
+    bf = gpu_filter(rpt, n)
+    bf.Insert(rpt.device_col(dk, rpt.INT64), n)
+    got = bf.ExportWords()
+    keys = oracle.synth_build_keys(0, n)
+    want = oracle.new_filter(n)
+    oracle.bench_build(want, keys.view(np.int64), 8)  # same fetch_or loop on 8 threads
+    assert np.array_equal(got, want)
+    del keys
+    # sharded build of the same column (4 row ranges, separate handles, OR-merged) is byte-identical
+    parts = []
+    for r in range(4):
+        p = gpu_filter(rpt, n)
+        lo, hi = n * r // 4, n * (r + 1) // 4
+        p.Insert(rpt.device_col(dk[lo:hi], rpt.INT64), hi - lo)
+        parts.append(p)
+    rpt.allreduce_or(parts)
+    for p in parts:
+        assert np.array_equal(p.ExportWords(), got)
+        p.close()
+    del dk, parts
+    # probe
+    dp = torch.empty(m, dtype=torch.int64, device="cuda")
+    rpt.synth_probe_keys(dp, 0, m, n, ppm)
+    dsel = torch.empty(m, dtype=torch.int32, device="cuda")
+    dfound = torch.zeros(1, dtype=torch.int64, device="cuda")
+    bf.LookupSelDevice(rpt.device_col(dp, rpt.INT64), m, dsel, dfound)
+    bf.Sync()
+    found = int(dfound.item())
+    sel = dsel[:found]
+    assert bool((sel[1:] > sel[:-1]).all())
+    # members (bit 63 clear) all survive; the rest are false positives at the filter's rate (≈0.24 %)
+    member = dp >= 0
+    n_member = int(member.sum().item())
+    assert int(member[sel.long()].sum().item()) == n_member
+    fp = found - n_member
+    assert 0.0015 < fp / (m - n_member) < 0.0035
+    # exact windows against the oracle
+    W = 2 * 10**7
+    for start in (0, m - W):
+        probe = oracle.synth_probe_keys(start, W, n, ppm)
+        want_sel = oracle.probe(want, [rpt.host_col(probe)], W).astype(np.int64) + start
+        sel64 = sel.long() & 0xFFFFFFFF
+        mask = (sel64 >= start) & (sel64 < start + W)
+        got_sel = sel64[mask].cpu().numpy()
+        assert np.array_equal(got_sel, want_sel), start
+    # the whole probe split in two calls concatenates to the same selection vector
+    half = m // 2 + 12345
+    dsel_a = torch.empty(half, dtype=torch.int32, device="cuda")
+    bf.LookupSelDevice(rpt.device_col(dp[:half], rpt.INT64), half, dsel_a, dfound)
+    bf.Sync()
+    fa = int(dfound.item())
+    dsel_b = torch.empty(m - half, dtype=torch.int32, device="cuda")
+    bf.LookupSelDevice(rpt.device_col(dp[half:], rpt.INT64), m - half, dsel_b, dfound)
+    bf.Sync()
+    fb = int(dfound.item())
+    assert fa + fb == found
+    assert bool((dsel_a[:fa] == sel[:fa]).all())
+    assert bool(((dsel_b[:fb].long() & 0xFFFFFFFF) + half == (sel[fa:].long() & 0xFFFFFFFF)).all())
+    bf.close()
