@@ -214,8 +214,11 @@ def run_b200(args):
     n_local = hi - lo
     probe_first = rank * m
 
-    stream = torch.cuda.current_stream()
+    # a non-default stream: a NULL rpt_stream_t would mean "the handle's own stream", which torch events cannot see
+    stream = torch.cuda.Stream(device=dev)
+    torch.cuda.set_stream(stream)
     sh = stream.cuda_stream
+    assert sh != 0
     dk = torch.empty(max(n_local, 2), dtype=torch.int64, device=dev)
     dp = torch.empty(m, dtype=torch.int64, device=dev)
     rpt.synth_build_keys(dk, lo, n_local, device=local_rank, stream=sh)

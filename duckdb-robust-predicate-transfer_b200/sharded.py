@@ -113,8 +113,9 @@ class ShardedBloomFilter:
         self.merged = False
 
     def Merge(self, stream=None):
-        """OR-allreduce of the partial filters.  `stream` must be the current torch stream (or None when the
-        caller synchronises): the barriers are enqueued on torch's current stream."""
+        """OR-allreduce of the partial filters.  stream=None: blocking (returns when the merged words are in
+        place).  Otherwise `stream` must be the raw handle of torch's current, non-default CUDA stream: barriers,
+        kernels and copies are all enqueued on it and nothing blocks the host."""
         if self.world == 1:
             self.merged = True
             return
@@ -122,9 +123,30 @@ class ShardedBloomFilter:
         any_data = self._allreduce_sum(0 if self.bf.IsEmpty() else 1)
         on_gpu = self.dist.get_backend(self.group) == "nccl"
         blocking = stream is None
-        if blocking and on_gpu:
-            self.bf.Sync()  # work enqueued on the handle's own stream
-            stream = torch.cuda.current_stream().cuda_stream
+        if on_gpu:
+            if blocking:
+                # own side stream: a NULL rpt_stream_t means "the handle's stream", which NCCL cannot order against
+                self.bf.Sync()
+                torch.cuda.current_stream().synchronize()
+                if not hasattr(self, "_side"):
+                    self._side = torch.cuda.Stream(device=torch.device("cuda", self.device))
+                run_on = self._side
+            else:
+                run_on = torch.cuda.current_stream()
+                if run_on.cuda_stream != stream:
+                    raise ValueError("Merge(stream): stream must be torch's current (non-default) CUDA stream")
+            with torch.cuda.stream(run_on):
+                self._merge_on(run_on.cuda_stream)
+            if blocking:
+                run_on.synchronize()
+        else:
+            self._merge_on(None)
+        if any_data:
+            self.bf.SetHasData(True)
+        self.merged = True
+
+    def _merge_on(self, stream):
+        import torch
         if self.merge == "peer":
             words = self.bf.device_words
             if self._peer_open_for != words:
@@ -145,11 +167,6 @@ class ShardedBloomFilter:
             self.dist.all_gather_into_tensor(parts, mine, group=self.group)
             self.bf.OrParts(parts, self.world, stream)
             self._parts = parts  # keep alive until the OR kernel has run
-        if blocking and on_gpu:
-            torch.cuda.current_stream().synchronize()
-        if any_data:
-            self.bf.SetHasData(True)
-        self.merged = True
 
     def _words_tensor(self):
         """The S words as a tensor the collective backend can send (device view for NCCL; engines that keep
@@ -157,7 +174,6 @@ class ShardedBloomFilter:
         if hasattr(self.bf, "words_tensor"):
             return self.bf.words_tensor()
         import torch
-        self.bf.Sync()
         return torch.as_tensor(_DeviceWords(self.bf.device_words, self.bf.num_sectors),
                                device=torch.device("cuda", self.device))
 
