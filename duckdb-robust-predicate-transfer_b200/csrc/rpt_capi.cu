@@ -656,7 +656,7 @@ static int probe_impl(const rpt_bf *bf, const rpt_col_t *cols, int ncols, uint64
 		Staged st;
 		st.stream = s;
 		void *scratch;
-		RPT_TRY(st.alloc(&scratch, probe_scratch_bytes(count)));
+		RPT_TRY(st.alloc(&scratch, probe_scratch_bytes(count, bf->num_sectors)));
 		if (out_mem == RPT_MEM_DEVICE) { // fully asynchronous
 			RPT_CUDA(launch_probe(bf->dev, dc, count, bf->words, bf->num_sectors, sel_out, found_out, 0, translate,
 			                      scratch, s, &launches));
@@ -745,7 +745,7 @@ static int probe_impl(const rpt_bf *bf, const rpt_col_t *cols, int ncols, uint64
 			DevCols dc;
 			RPT_TRY(stage_host_cols(cols, ncols, r0, r1, &st, &dc));
 			void *scratch;
-			RPT_TRY(st.alloc(&scratch, probe_scratch_bytes(r1 - r0)));
+			RPT_TRY(st.alloc(&scratch, probe_scratch_bytes(r1 - r0, bf->num_sectors)));
 			const uint32_t *translate = translate_col0 ? dc.c[0].sel : nullptr;
 			RPT_CUDA(launch_probe(bf->dev, dc, r1 - r0, bf->words, bf->num_sectors, slot[idx].dsel, slot[idx].dfound,
 			                      static_cast<uint32_t>(r0), translate, scratch, st.stream, &launches));

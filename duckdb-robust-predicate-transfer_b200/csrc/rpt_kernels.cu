@@ -14,6 +14,8 @@
 // so the selection vector is written once.
 #include "rpt_kernels.cuh"
 
+#include <cstdlib>
+
 namespace rpt {
 
 // ---------------------------------------------------------------------------------------------
@@ -129,17 +131,28 @@ struct GenericSrc { // any type / sel / validity / multi-column combination
 
 // ---------------------------------------------------------------------------------------------
 // build
+//
+// Sector-range passes.  A miss in L2 costs a 128-byte DRAM line for 8 useful bytes (measured:
+// profiles/mem_lab_r1.txt), so a filter that does not fit L2 is built in ceil(F / slice) passes over the
+// key column: pass p only inserts the keys whose sector lies in [lo, lo+len).  The pass's slice of the
+// filter stays L2-resident (evict_last on the reductions) while the keys stream through (evict_first),
+// and re-reading 8 B/key per pass is far cheaper than ≥128 B/key of line fills and write-backs.
 // ---------------------------------------------------------------------------------------------
 constexpr int kBuildBlock = 256;
 constexpr int kBuildUnroll = 4;
 
-// AGG: lanes of a warp that hit the same sector OR their masks first and issue one atomic
+__device__ __forceinline__ void red_or_u64(unsigned long long *ptr, uint64_t mask, uint64_t pol) {
+	asm volatile("red.global.or.L2::cache_hint.b64 [%0], %1, %2;" ::"l"(ptr), "l"(mask), "l"(pol) : "memory");
+}
+
+// AGG: lanes of a warp that hit the same sector OR their masks first and issue one reduction
 // (worth it only for small filters or duplicate-heavy keys).
 template <class Src, bool AGG>
 __global__ void __launch_bounds__(kBuildBlock)
-    build_kernel(const Src src, unsigned long long *__restrict__ filter, const uint64_t sector_mask,
-                 const uint64_t count) {
+    build_kernel(const Src src, unsigned long long *__restrict__ filter, const uint32_t sector_mask,
+                 const uint64_t count, const uint32_t slice_lo, const uint32_t slice_len) {
 	const uint64_t pol = policy_evict_first();
+	const uint64_t pol_filter = policy_evict_last();
 	const uint64_t step = static_cast<uint64_t>(gridDim.x) * kBuildBlock * 2 * kBuildUnroll;
 	for (uint64_t base = static_cast<uint64_t>(blockIdx.x) * kBuildBlock * 2 * kBuildUnroll; base < count;
 	     base += step) {
@@ -157,21 +170,21 @@ __global__ void __launch_bounds__(kBuildBlock)
 		}
 #pragma unroll
 		for (int i = 0; i < 2 * kBuildUnroll; i++) {
-			const bool v = (valid >> i) & 1u;
-			const uint64_t sector = h[i] & sector_mask;
-			uint64_t mask = sector_mask_of(h[i]);
+			const uint32_t sector = static_cast<uint32_t>(h[i]) & sector_mask;
+			const bool v = ((valid >> i) & 1u) && (sector - slice_lo < slice_len);
+			uint64_t mask = sector_mask_fast(static_cast<uint32_t>(h[i] >> 32));
 			if (AGG) {
 				// every lane takes part; invalid lanes use a sector id no valid lane can have
-				const uint64_t key = v ? sector : ~0ULL;
+				const uint32_t key = v ? sector : 0xffffffffu;
 				const uint32_t peers = __match_any_sync(0xffffffffu, key);
 				const uint32_t lo = __reduce_or_sync(peers, static_cast<uint32_t>(mask));
 				const uint32_t hi = __reduce_or_sync(peers, static_cast<uint32_t>(mask >> 32));
 				mask = (static_cast<uint64_t>(hi) << 32) | lo;
 				if (v && (__ffs(peers) - 1) == static_cast<int>(threadIdx.x & 31)) {
-					atomicOr(filter + sector, static_cast<unsigned long long>(mask));
+					red_or_u64(filter + sector, mask, pol_filter);
 				}
 			} else if (v) {
-				atomicOr(filter + sector, static_cast<unsigned long long>(mask));
+				red_or_u64(filter + sector, mask, pol_filter);
 			}
 		}
 	}
@@ -227,12 +240,103 @@ __device__ __forceinline__ uint32_t tile_lookback(uint64_t *desc, const uint64_t
 	return exclusive;
 }
 
-template <class Src, int ROUNDS, int BLOCK, bool SMEM_FILTER>
+// Hash a tile's keys and test them against the filter.  Thread-local result: bit i of the return value is the
+// hit flag of this thread's i-th key (i = 2·round + element).  SLICED: only sectors in [slice_lo, slice_lo +
+// slice_len) are looked up (the other keys' bits stay 0 in this pass).
+template <class Src, int ROUNDS, bool SMEM_FILTER, bool SLICED>
+__device__ __forceinline__ uint32_t probe_tile(const Src &src, const uint64_t *__restrict__ filter,
+                                               const uint64_t *s_filter, const uint32_t sector_mask,
+                                               const uint64_t count, const uint64_t warp_base, const bool full_tile,
+                                               const uint32_t lane, const uint64_t pol_keys, const uint64_t pol_filter,
+                                               const uint32_t slice_lo, const uint32_t slice_len) {
+	// 1. stream the keys and hash them
+	uint64_t h[2 * ROUNDS];
+	uint32_t valid = 0;
+	if (full_tile) { // block-uniform: every tile but the last
+		src.template load_rounds<ROUNDS>(warp_base + lane * 2, 64, pol_keys, h);
+		valid = static_cast<uint32_t>((1ull << (2 * ROUNDS)) - 1ull);
+	} else {
+#pragma unroll
+		for (int r = 0; r < ROUNDS; r++) {
+			const uint64_t row0 = warp_base + static_cast<uint64_t>(r) * 64 + lane * 2;
+			valid |= src.load2(row0, count, pol_keys, h[2 * r], h[2 * r + 1]) << (2 * r);
+		}
+	}
+	// 2. all random filter loads of this thread, independent of each other
+	uint64_t w[2 * ROUNDS];
+#pragma unroll
+	for (int i = 0; i < 2 * ROUNDS; i++) {
+		const uint32_t sector = static_cast<uint32_t>(h[i]) & sector_mask;
+		if (SMEM_FILTER) {
+			w[i] = s_filter[sector];
+		} else if (SLICED) {
+			w[i] = 0; // an all-zero word passes nothing
+			if (sector - slice_lo < slice_len) {
+				w[i] = ld_filter_word(filter + sector, pol_filter);
+			}
+		} else {
+			w[i] = ld_filter_word(filter + sector, pol_filter);
+		}
+	}
+	// 3. test
+	uint32_t hits = 0;
+#pragma unroll
+	for (int i = 0; i < 2 * ROUNDS; i++) {
+		hits |= sector_test(w[i], static_cast<uint32_t>(h[i] >> 32)) << i;
+	}
+	return hits & valid;
+}
+
+// Pulls a slice of the filter into L2 with evict_last priority, one prefetch per 128-byte line, so that the
+// random lookups of the pass start on a resident slice instead of faulting it in line by line.
+__device__ __forceinline__ void warm_slice(const uint64_t *__restrict__ filter, const uint32_t slice_lo,
+                                           const uint32_t slice_len, const uint32_t block) {
+	const char *g = reinterpret_cast<const char *>(filter + slice_lo);
+	const uint64_t nlines = (static_cast<uint64_t>(slice_len) * 8 + 127) >> 7;
+	for (uint64_t i = static_cast<uint64_t>(blockIdx.x) * block + threadIdx.x; i < nlines;
+	     i += static_cast<uint64_t>(gridDim.x) * block) {
+		asm volatile("prefetch.global.L2::evict_last [%0];" ::"l"(g + (i << 7)));
+	}
+}
+
+// Non-final pass of a sliced probe: per-thread hit bits (2·ROUNDS ≤ 16 of them) are ORed into a scratch array
+// laid out exactly like the final pass reads it (one uint16 per thread per tile).
+template <class Src, int ROUNDS, int BLOCK>
 __global__ void __launch_bounds__(BLOCK)
-    probe_kernel(const Src src, const uint64_t *__restrict__ filter, const uint64_t sector_mask, const uint64_t count,
+    probe_slice_kernel(const Src src, const uint64_t *__restrict__ filter, const uint32_t sector_mask,
+                       const uint64_t count, const uint64_t num_tiles, const uint32_t slice_lo,
+                       const uint32_t slice_len, uint16_t *__restrict__ hitbits, const int first_pass) {
+	static_assert(2 * ROUNDS <= 16, "hit bits are kept in a uint16 per thread");
+	constexpr int NWARPS = BLOCK / 32;
+	constexpr uint64_t WARP_KEYS = 64ull * ROUNDS;
+	constexpr uint64_t TILE_KEYS = WARP_KEYS * NWARPS;
+	const uint32_t lane = threadIdx.x & 31u;
+	const uint32_t warp = threadIdx.x >> 5;
+	const uint64_t pol_keys = policy_evict_first();
+	const uint64_t pol_filter = policy_evict_last();
+	warm_slice(filter, slice_lo, slice_len, BLOCK);
+	for (uint64_t tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+		const uint64_t warp_base = tile * TILE_KEYS + warp * WARP_KEYS;
+		uint32_t hits = probe_tile<Src, ROUNDS, false, true>(src, filter, nullptr, sector_mask, count, warp_base,
+		                                                     (tile + 1) * TILE_KEYS <= count, lane, pol_keys,
+		                                                     pol_filter, slice_lo, slice_len);
+		uint16_t *slot = hitbits + tile * BLOCK + threadIdx.x;
+		if (!first_pass) {
+			hits |= *slot;
+		}
+		*slot = static_cast<uint16_t>(hits);
+	}
+}
+
+// Final (or only) pass: persistent CTAs, ticket-ordered tiles, decoupled look-back, ordered write.
+// PRIOR: hit bits of the earlier sector-range passes are ORed in from `hitbits`.
+template <class Src, int ROUNDS, int BLOCK, bool SMEM_FILTER, bool SLICED>
+__global__ void __launch_bounds__(BLOCK)
+    probe_kernel(const Src src, const uint64_t *__restrict__ filter, const uint32_t sector_mask, const uint64_t count,
                  const uint64_t num_tiles, uint32_t *__restrict__ sel_out, uint64_t *__restrict__ found_out,
                  const uint32_t row_offset, const uint32_t *__restrict__ translate, uint64_t *desc,
-                 unsigned int *ticket) {
+                 unsigned int *ticket, const uint32_t slice_lo, const uint32_t slice_len,
+                 const uint16_t *__restrict__ hitbits) {
 	constexpr int NWARPS = BLOCK / 32;
 	constexpr uint64_t WARP_KEYS = 64ull * ROUNDS;
 	constexpr uint64_t TILE_KEYS = WARP_KEYS * NWARPS;
@@ -248,12 +352,15 @@ __global__ void __launch_bounds__(BLOCK)
 	const uint64_t pol_filter = policy_evict_last();
 
 	if (SMEM_FILTER) {
-		const uint64_t nvec = (sector_mask + 1) >> 1;
+		const uint64_t nvec = (static_cast<uint64_t>(sector_mask) + 1) >> 1;
 		const ulonglong2 *g = reinterpret_cast<const ulonglong2 *>(filter);
 		ulonglong2 *s = reinterpret_cast<ulonglong2 *>(s_filter);
 		for (uint64_t i = threadIdx.x; i < nvec; i += BLOCK) {
 			s[i] = __ldg(g + i);
 		}
+	}
+	if (SLICED) {
+		warm_slice(filter, slice_lo, slice_len, BLOCK);
 	}
 
 	while (true) {
@@ -266,41 +373,14 @@ __global__ void __launch_bounds__(BLOCK)
 			break;
 		}
 		const uint64_t warp_base = tile * TILE_KEYS + warp * WARP_KEYS;
-
-		// 1. stream the keys and hash them
-		uint64_t h[2 * ROUNDS];
-		uint32_t valid = 0;
-		if ((tile + 1) * TILE_KEYS <= count) { // block-uniform: every tile but the last
-			src.template load_rounds<ROUNDS>(warp_base + lane * 2, 64, pol_keys, h);
-			valid = static_cast<uint32_t>((1ull << (2 * ROUNDS)) - 1ull);
-		} else {
-#pragma unroll
-			for (int r = 0; r < ROUNDS; r++) {
-				const uint64_t row0 = warp_base + static_cast<uint64_t>(r) * 64 + lane * 2;
-				valid |= src.load2(row0, count, pol_keys, h[2 * r], h[2 * r + 1]) << (2 * r);
-			}
+		uint32_t hits = probe_tile<Src, ROUNDS, SMEM_FILTER, SLICED>(src, filter, s_filter, sector_mask, count, warp_base,
+		                                                             (tile + 1) * TILE_KEYS <= count, lane, pol_keys,
+		                                                             pol_filter, slice_lo, slice_len);
+		if (SLICED) {
+			hits |= hitbits[tile * BLOCK + threadIdx.x];
 		}
-		// 2. all random filter loads of this thread, independent of each other
-		uint64_t w[2 * ROUNDS];
-#pragma unroll
-		for (int i = 0; i < 2 * ROUNDS; i++) {
-			const uint64_t sector = h[i] & sector_mask;
-			w[i] = SMEM_FILTER ? s_filter[sector] : ld_filter_word(filter + sector, pol_filter);
-		}
-		// 3. test
-		uint32_t hits = 0;
-#pragma unroll
-		for (int i = 0; i < 2 * ROUNDS; i++) {
-			const uint64_t m = sector_mask_of(h[i]);
-			hits |= static_cast<uint32_t>((w[i] & m) == m) << i;
-		}
-		hits &= valid;
 		// 4. survivors per warp → per tile → global exclusive offset
-		uint32_t warp_count = 0;
-#pragma unroll
-		for (int i = 0; i < 2 * ROUNDS; i++) {
-			warp_count += __popc(__ballot_sync(0xffffffffu, (hits >> i) & 1u));
-		}
+		uint32_t warp_count = __reduce_add_sync(0xffffffffu, __popc(hits));
 		if (lane == 0) {
 			s_warp_off[warp] = warp_count;
 		}
@@ -332,22 +412,24 @@ __global__ void __launch_bounds__(BLOCK)
 		uint32_t run = s_tile_excl + s_warp_off[warp];
 		const uint32_t lt = lanemask_lt();
 		const uint32_t rel_base = static_cast<uint32_t>(warp_base) + row_offset + lane * 2;
+		if (__any_sync(0xffffffffu, hits != 0)) {
 #pragma unroll
-		for (int r = 0; r < ROUNDS; r++) {
-			const uint32_t h0 = (hits >> (2 * r)) & 1u;
-			const uint32_t h1 = (hits >> (2 * r + 1)) & 1u;
-			const uint32_t b0 = __ballot_sync(0xffffffffu, h0);
-			const uint32_t b1 = __ballot_sync(0xffffffffu, h1);
-			uint32_t pos = run + __popc(b0 & lt) + __popc(b1 & lt);
-			const uint32_t rel = rel_base + r * 64;
-			if (h0) {
-				sel_out[pos] = translate ? __ldg(translate + rel) : rel;
+			for (int r = 0; r < ROUNDS; r++) {
+				const uint32_t h0 = (hits >> (2 * r)) & 1u;
+				const uint32_t h1 = (hits >> (2 * r + 1)) & 1u;
+				const uint32_t b0 = __ballot_sync(0xffffffffu, h0);
+				const uint32_t b1 = __ballot_sync(0xffffffffu, h1);
+				uint32_t pos = run + __popc(b0 & lt) + __popc(b1 & lt);
+				const uint32_t rel = rel_base + r * 64;
+				if (h0) {
+					sel_out[pos] = translate ? __ldg(translate + rel) : rel;
+				}
+				pos += h0;
+				if (h1) {
+					sel_out[pos] = translate ? __ldg(translate + rel + 1) : rel + 1;
+				}
+				run += __popc(b0) + __popc(b1);
 			}
-			pos += h0;
-			if (h1) {
-				sel_out[pos] = translate ? __ldg(translate + rel + 1) : rel + 1;
-			}
-			run += __popc(b0) + __popc(b1);
 		}
 	}
 }
@@ -403,8 +485,7 @@ __global__ void __launch_bounds__(256)
 	const uint64_t i = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
 	if (i < count) {
 		const uint64_t h = hashes[i];
-		const uint64_t m = sector_mask_of(h);
-		hits[i] = (words[h & sector_mask] & m) == m;
+		hits[i] = static_cast<uint8_t>(sector_test(words[h & sector_mask], static_cast<uint32_t>(h >> 32)));
 	}
 }
 
@@ -460,14 +541,36 @@ static inline bool use_smem_filter(const DeviceInfo &dev, uint64_t num_sectors) 
 	return num_sectors <= kSmemFilterMaxSectors && num_sectors * 8 + 1024 <= dev.smem_optin;
 }
 
-size_t probe_scratch_bytes(uint64_t count) {
+// Sector-range slicing (see the build section): filters above the threshold are processed in passes of
+// `slice` sectors.  RPT_SLICE_MIB overrides the slice size (MiB; 0 disables slicing) for experiments.
+static uint64_t slice_sectors_for(uint64_t num_sectors) {
+	static const long env_mib = [] {
+		const char *e = getenv("RPT_SLICE_MIB");
+		return e ? atol(e) : -1L;
+	}();
+	uint64_t slice = kSliceSectors;
+	if (env_mib == 0) {
+		return num_sectors;
+	}
+	if (env_mib > 0) {
+		slice = (static_cast<uint64_t>(env_mib) << 20) / 8;
+	}
+	return num_sectors > slice ? slice : num_sectors;
+}
+
+size_t probe_scratch_bytes(uint64_t count, uint64_t num_sectors) {
 	// the smaller tile gives the larger tile count; one extra slot holds the ticket counter
-	return (ceil_div(count, kProbeTileKeys) + 2) * sizeof(uint64_t);
+	const uint64_t tiles = ceil_div(count, kProbeTileKeys);
+	size_t bytes = (tiles + 2) * sizeof(uint64_t);
+	if (slice_sectors_for(num_sectors) < num_sectors) {
+		bytes += tiles * kProbeBlock * sizeof(uint16_t); // hit bits carried between sector-range passes
+	}
+	return bytes;
 }
 
 template <class Src, bool AGG>
 static cudaError_t launch_build_t(const DeviceInfo &dev, const Src &src, uint64_t count, uint64_t *words,
-                                  uint64_t num_sectors, cudaStream_t stream) {
+                                  uint64_t num_sectors, cudaStream_t stream, int *launches) {
 	const uint64_t per_block = static_cast<uint64_t>(kBuildBlock) * 2 * kBuildUnroll;
 	int per_sm = 0;
 	cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, build_kernel<Src, AGG>, kBuildBlock, 0);
@@ -479,8 +582,16 @@ static cudaError_t launch_build_t(const DeviceInfo &dev, const Src &src, uint64_
 	if (grid > wave * 4) {
 		grid = wave * 4; // grid-stride over the rest; a multiple of SMs × resident CTAs
 	}
-	build_kernel<Src, AGG><<<static_cast<unsigned>(grid), kBuildBlock, 0, stream>>>(
-	    src, reinterpret_cast<unsigned long long *>(words), num_sectors - 1, count);
+	const uint64_t slice = slice_sectors_for(num_sectors);
+	for (uint64_t lo = 0; lo < num_sectors; lo += slice) {
+		const uint64_t len = lo + slice < num_sectors ? slice : num_sectors - lo;
+		build_kernel<Src, AGG><<<static_cast<unsigned>(grid), kBuildBlock, 0, stream>>>(
+		    src, reinterpret_cast<unsigned long long *>(words), static_cast<uint32_t>(num_sectors - 1), count,
+		    static_cast<uint32_t>(lo), static_cast<uint32_t>(len));
+		if (launches) {
+			(*launches)++;
+		}
+	}
 	return cudaGetLastError();
 }
 
@@ -489,26 +600,23 @@ cudaError_t launch_build(const DeviceInfo &dev, const DevCols &cols, uint64_t co
 	if (count == 0) {
 		return cudaSuccess;
 	}
-	if (launches) {
-		(*launches)++;
-	}
 	// warp-aggregate only where same-sector collisions inside a warp are likely
 	const bool agg = num_sectors <= 4096;
 	if (is_flat_u64(cols)) {
 		FlatU64Src src {reinterpret_cast<const uint64_t *>(cols.c[0].data)};
-		return agg ? launch_build_t<FlatU64Src, true>(dev, src, count, words, num_sectors, stream)
-		           : launch_build_t<FlatU64Src, false>(dev, src, count, words, num_sectors, stream);
+		return agg ? launch_build_t<FlatU64Src, true>(dev, src, count, words, num_sectors, stream, launches)
+		           : launch_build_t<FlatU64Src, false>(dev, src, count, words, num_sectors, stream, launches);
 	}
 	GenericSrc src {cols};
-	return agg ? launch_build_t<GenericSrc, true>(dev, src, count, words, num_sectors, stream)
-	           : launch_build_t<GenericSrc, false>(dev, src, count, words, num_sectors, stream);
+	return agg ? launch_build_t<GenericSrc, true>(dev, src, count, words, num_sectors, stream, launches)
+	           : launch_build_t<GenericSrc, false>(dev, src, count, words, num_sectors, stream, launches);
 }
 
-template <class Src, int BLOCK, bool SMEM>
+template <class Src, int BLOCK, bool SMEM, bool SLICED>
 static cudaError_t launch_probe_t(const DeviceInfo &dev, const Src &src, uint64_t count, const uint64_t *words,
                                   uint64_t num_sectors, uint32_t *sel_out, uint64_t *found_out, uint32_t row_offset,
-                                  const uint32_t *translate, void *scratch, cudaStream_t stream) {
-	auto kern = probe_kernel<Src, kProbeRounds, BLOCK, SMEM>;
+                                  const uint32_t *translate, void *scratch, cudaStream_t stream, int *launches) {
+	auto kern = probe_kernel<Src, kProbeRounds, BLOCK, SMEM, SLICED>;
 	const uint64_t tile_keys = 64ull * kProbeRounds * (BLOCK / 32);
 	const uint64_t num_tiles = ceil_div(count, tile_keys);
 	const size_t smem = SMEM ? num_sectors * sizeof(uint64_t) : 0;
@@ -533,13 +641,60 @@ static cudaError_t launch_probe_t(const DeviceInfo &dev, const Src &src, uint64_
 	}
 	uint64_t *desc = reinterpret_cast<uint64_t *>(scratch);
 	unsigned int *ticket = reinterpret_cast<unsigned int *>(desc + num_tiles);
+	uint16_t *hitbits = reinterpret_cast<uint16_t *>(desc + num_tiles + 2);
 	e = cudaMemsetAsync(scratch, 0, (num_tiles + 1) * sizeof(uint64_t), stream);
 	if (e != cudaSuccess) {
 		return e;
 	}
-	kern<<<static_cast<unsigned>(grid), BLOCK, smem, stream>>>(src, words, num_sectors - 1, count, num_tiles, sel_out,
-	                                                          found_out, row_offset, translate, desc, ticket);
+	const uint32_t sector_mask = static_cast<uint32_t>(num_sectors - 1);
+	uint64_t lo = 0, len = num_sectors;
+	if (SLICED) {
+		// every slice but the last goes through the light pass kernel; the last one is fused with the compaction
+		const uint64_t slice = slice_sectors_for(num_sectors);
+		int per_sm_slice = 0;
+		auto slice_kern = probe_slice_kernel<Src, kProbeRounds, BLOCK>;
+		e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_slice, slice_kern, BLOCK, 0);
+		if (e != cudaSuccess) {
+			return e;
+		}
+		uint64_t slice_grid = static_cast<uint64_t>(dev.sm_count) * (per_sm_slice > 0 ? per_sm_slice : 1);
+		if (slice_grid > num_tiles) {
+			slice_grid = num_tiles;
+		}
+		for (; lo + slice < num_sectors; lo += slice) {
+			slice_kern<<<static_cast<unsigned>(slice_grid), BLOCK, 0, stream>>>(
+			    src, words, sector_mask, count, num_tiles, static_cast<uint32_t>(lo), static_cast<uint32_t>(slice),
+			    hitbits, lo == 0 ? 1 : 0);
+			if (launches) {
+				(*launches)++;
+			}
+		}
+		len = num_sectors - lo;
+	}
+	kern<<<static_cast<unsigned>(grid), BLOCK, smem, stream>>>(src, words, sector_mask, count, num_tiles, sel_out,
+	                                                          found_out, row_offset, translate, desc, ticket,
+	                                                          static_cast<uint32_t>(lo), static_cast<uint32_t>(len),
+	                                                          hitbits);
+	if (launches) {
+		(*launches)++;
+	}
 	return cudaGetLastError();
+}
+
+template <class Src>
+static cudaError_t launch_probe_src(const DeviceInfo &dev, const Src &src, uint64_t count, const uint64_t *words,
+                                    uint64_t num_sectors, uint32_t *sel_out, uint64_t *found_out, uint32_t row_offset,
+                                    const uint32_t *translate, void *scratch, cudaStream_t stream, int *launches) {
+	if (use_smem_filter(dev, num_sectors)) {
+		return launch_probe_t<Src, kProbeBlockSmem, true, false>(dev, src, count, words, num_sectors, sel_out, found_out,
+		                                                         row_offset, translate, scratch, stream, launches);
+	}
+	if (slice_sectors_for(num_sectors) < num_sectors) {
+		return launch_probe_t<Src, kProbeBlock, false, true>(dev, src, count, words, num_sectors, sel_out, found_out,
+		                                                     row_offset, translate, scratch, stream, launches);
+	}
+	return launch_probe_t<Src, kProbeBlock, false, false>(dev, src, count, words, num_sectors, sel_out, found_out,
+	                                                      row_offset, translate, scratch, stream, launches);
 }
 
 cudaError_t launch_probe(const DeviceInfo &dev, const DevCols &cols, uint64_t count, const uint64_t *words,
@@ -548,23 +703,14 @@ cudaError_t launch_probe(const DeviceInfo &dev, const DevCols &cols, uint64_t co
 	if (count == 0) {
 		return cudaMemsetAsync(found_out, 0, sizeof(uint64_t), stream);
 	}
-	if (launches) {
-		(*launches)++;
-	}
-	const bool smem = use_smem_filter(dev, num_sectors);
 	if (is_flat_u64(cols)) {
 		FlatU64Src src {reinterpret_cast<const uint64_t *>(cols.c[0].data)};
-		return smem ? launch_probe_t<FlatU64Src, kProbeBlockSmem, true>(dev, src, count, words, num_sectors, sel_out,
-		                                                              found_out, row_offset, translate, scratch,
-		                                                              stream)
-		            : launch_probe_t<FlatU64Src, kProbeBlock, false>(dev, src, count, words, num_sectors, sel_out,
-		                                                            found_out, row_offset, translate, scratch, stream);
+		return launch_probe_src(dev, src, count, words, num_sectors, sel_out, found_out, row_offset, translate, scratch,
+		                        stream, launches);
 	}
 	GenericSrc src {cols};
-	return smem ? launch_probe_t<GenericSrc, kProbeBlockSmem, true>(dev, src, count, words, num_sectors, sel_out,
-	                                                              found_out, row_offset, translate, scratch, stream)
-	            : launch_probe_t<GenericSrc, kProbeBlock, false>(dev, src, count, words, num_sectors, sel_out,
-	                                                            found_out, row_offset, translate, scratch, stream);
+	return launch_probe_src(dev, src, count, words, num_sectors, sel_out, found_out, row_offset, translate, scratch,
+	                        stream, launches);
 }
 
 static inline unsigned stream_grid(const DeviceInfo &dev, uint64_t items, unsigned block) {

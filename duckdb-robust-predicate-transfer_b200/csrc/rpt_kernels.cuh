@@ -18,9 +18,12 @@ struct DeviceInfo {
 
 // Largest filter (in 64-bit sectors) that is staged in shared memory by the probe kernel.
 constexpr uint64_t kSmemFilterMaxSectors = 1ULL << 14; // 128 KiB
+// Filters larger than this are built / probed in sector-range passes of this many sectors, each of which
+// stays L2-resident (64 MiB: measured sweet spot on B200's 126 MB, two-die L2; profiles/mem_lab_r1.txt).
+constexpr uint64_t kSliceSectors = 1ULL << 23;
 
 // Scratch the probe kernel needs for `count` rows: tile descriptors + ticket counter (bytes).
-size_t probe_scratch_bytes(uint64_t count);
+size_t probe_scratch_bytes(uint64_t count, uint64_t num_sectors);
 
 // Build: filter[h & (S-1)] |= GetMask(h) for every row (InsertHashes, bloom_filter.cpp:43-48,63-70).
 cudaError_t launch_build(const DeviceInfo &dev, const DevCols &cols, uint64_t count, uint64_t *words,

@@ -469,12 +469,14 @@ def test_device_columns_and_generators(rpt, oracle, torch_cuda):
     assert np.array_equal(keys, oracle.synth_build_keys(0, n))
     assert np.array_equal(probe, oracle.synth_probe_keys(0, m, n, 100000))
     bf = gpu_filter(rpt, n)
+    torch.cuda.synchronize()  # inputs were produced on torch's stream; the handle's stream is non-blocking
     bf.Insert(rpt.device_col(dk, rpt.INT64), n)
     want = oracle.new_filter(n)
     oracle.insert(want, [rpt.host_col(keys)], n)
     assert np.array_equal(bf.ExportWords(), want)
     dsel = torch.empty(m, dtype=torch.int32, device="cuda")
     dfound = torch.zeros(1, dtype=torch.int64, device="cuda")
+    torch.cuda.synchronize()  # inputs were produced on torch's stream; the handle's stream is non-blocking
     bf.LookupSelDevice(rpt.device_col(dp, rpt.INT64), m, dsel, dfound)
     bf.Sync()
     found = int(dfound.item())
@@ -486,7 +488,9 @@ def test_device_columns_and_generators(rpt, oracle, torch_cuda):
     got = bf.LookupSel(rpt.device_col(dp[1:], rpt.INT64), m - 1)
     assert np.array_equal(got, sel[sel > 0] - 1)
     bf2 = gpu_filter(rpt, n)
+    torch.cuda.synchronize()  # inputs were produced on torch's stream; the handle's stream is non-blocking
     bf2.Insert(rpt.device_col(dk[1:], rpt.INT64), n - 1)
+    torch.cuda.synchronize()  # inputs were produced on torch's stream; the handle's stream is non-blocking
     bf2.Insert(rpt.device_col(dk[:1], rpt.INT64), 1)
     assert np.array_equal(bf2.ExportWords(), want)
     bf2.close()
@@ -562,9 +566,11 @@ def test_config2_known_answer_full_size(rpt, torch_cuda):
     dp = torch.arange(0, m, dtype=torch.int64, device="cuda")
     bf = gpu_filter(rpt, f["est_rows"])
     assert bf.num_sectors == f["num_sectors"]
+    torch.cuda.synchronize()  # inputs were produced on torch's stream; the handle's stream is non-blocking
     bf.Insert(rpt.device_col(dk, rpt.INT64), n)
     dsel = torch.empty(m, dtype=torch.int32, device="cuda")
     dfound = torch.zeros(1, dtype=torch.int64, device="cuda")
+    torch.cuda.synchronize()  # inputs were produced on torch's stream; the handle's stream is non-blocking
     bf.LookupSelDevice(rpt.device_col(dp, rpt.INT64), m, dsel, dfound)
     bf.Sync()
     found = int(dfound.item())
@@ -575,6 +581,7 @@ def test_config2_known_answer_full_size(rpt, torch_cuda):
     assert int((sel % 2 == 0).sum().item()) == n
     survivors = dp[sel.long()]
     dsel2 = torch.empty(found, dtype=torch.int32, device="cuda")
+    torch.cuda.synchronize()  # inputs were produced on torch's stream; the handle's stream is non-blocking
     bf.LookupSelDevice(rpt.device_col(survivors, rpt.INT64), found, dsel2, dfound)
     bf.Sync()
     assert int(dfound.item()) == found
@@ -589,7 +596,9 @@ def test_config2_full_size_against_oracle(rpt, oracle, torch_cuda):
     n, m, ppm = 10**8, 10**9, 100000
     dk = torch.empty(n, dtype=torch.int64, device="cuda")
     rpt.synth_build_keys(dk, 0, n)
+    torch.cuda.synchronize()  # the generators ran on the NULL stream; the handle's stream is non-blocking
     bf = gpu_filter(rpt, n)
+    torch.cuda.synchronize()  # inputs were produced on torch's stream; the handle's stream is non-blocking
     bf.Insert(rpt.device_col(dk, rpt.INT64), n)
     got = bf.ExportWords()
     keys = oracle.synth_build_keys(0, n)
@@ -602,6 +611,7 @@ def test_config2_full_size_against_oracle(rpt, oracle, torch_cuda):
     for r in range(4):
         p = gpu_filter(rpt, n)
         lo, hi = n * r // 4, n * (r + 1) // 4
+        torch.cuda.synchronize()  # inputs were produced on torch's stream; the handle's stream is non-blocking
         p.Insert(rpt.device_col(dk[lo:hi], rpt.INT64), hi - lo)
         parts.append(p)
     rpt.allreduce_or(parts)
@@ -612,8 +622,10 @@ def test_config2_full_size_against_oracle(rpt, oracle, torch_cuda):
     # probe
     dp = torch.empty(m, dtype=torch.int64, device="cuda")
     rpt.synth_probe_keys(dp, 0, m, n, ppm)
+    torch.cuda.synchronize()
     dsel = torch.empty(m, dtype=torch.int32, device="cuda")
     dfound = torch.zeros(1, dtype=torch.int64, device="cuda")
+    torch.cuda.synchronize()  # inputs were produced on torch's stream; the handle's stream is non-blocking
     bf.LookupSelDevice(rpt.device_col(dp, rpt.INT64), m, dsel, dfound)
     bf.Sync()
     found = int(dfound.item())
@@ -637,10 +649,12 @@ def test_config2_full_size_against_oracle(rpt, oracle, torch_cuda):
     # the whole probe split in two calls concatenates to the same selection vector
     half = m // 2 + 12345
     dsel_a = torch.empty(half, dtype=torch.int32, device="cuda")
+    torch.cuda.synchronize()  # inputs were produced on torch's stream; the handle's stream is non-blocking
     bf.LookupSelDevice(rpt.device_col(dp[:half], rpt.INT64), half, dsel_a, dfound)
     bf.Sync()
     fa = int(dfound.item())
     dsel_b = torch.empty(m - half, dtype=torch.int32, device="cuda")
+    torch.cuda.synchronize()  # inputs were produced on torch's stream; the handle's stream is non-blocking
     bf.LookupSelDevice(rpt.device_col(dp[half:], rpt.INT64), m - half, dsel_b, dfound)
     bf.Sync()
     fb = int(dfound.item())
