@@ -133,6 +133,14 @@ static int fill_device_info(int device, DeviceInfo *out) {
 		return set_error("device %d is sm_%d%d; librpt_gpu is built for sm_100a (B200) only", device, prop.major,
 		                 prop.minor);
 	}
+	// scratch comes from the stream-ordered allocator: keep freed blocks in the pool across synchronisations
+	// instead of returning them to the driver (the default release threshold is 0)
+	cudaMemPool_t pool;
+	if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) {
+		uint64_t keep = ~0ULL;
+		cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+	}
+	cudaGetLastError();
 	out->device = device;
 	out->sm_count = prop.multiProcessorCount;
 	out->l2_bytes = prop.l2CacheSize;

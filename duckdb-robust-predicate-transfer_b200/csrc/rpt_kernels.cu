@@ -299,44 +299,181 @@ __device__ __forceinline__ void warm_slice(const uint64_t *__restrict__ filter, 
 	}
 }
 
-// Non-final pass of a sliced probe: per-thread hit bits (2·ROUNDS ≤ 16 of them) are ORed into a scratch array
-// laid out exactly like the final pass reads it (one uint16 per thread per tile).
-template <class Src, int ROUNDS, int BLOCK>
+// ---- large probes: pass kernel(s) → tile-count scan → compaction ---------------------------------------
+// The fused single-kernel probe below chains tiles through a decoupled look-back; with persistent CTAs that
+// puts a ticket fetch, three block barriers and the look-back latency on every tile's critical path (ncu:
+// 46 % barrier + 34 % long-scoreboard stalls, issue slots 22 % busy).  Large probes therefore run as
+// independent phases with no inter-CTA dependency inside any kernel:
+//   probe_pass_kernel   hashes and tests the keys (once per sector-range slice), leaving one uint16 of hit
+//                       bits per thread per tile in scratch; the last pass also leaves each tile's hit count
+//   scan_tiles_kernel   exclusive prefix sum of the tile counts (one CTA; ≤ 2^20 tiles), writes `found`
+//   compact_kernel      turns hit bits + tile offsets into the ordered selection vector
+template <class Src, int ROUNDS, int BLOCK, bool SMEM_FILTER, bool SLICED>
 __global__ void __launch_bounds__(BLOCK)
-    probe_slice_kernel(const Src src, const uint64_t *__restrict__ filter, const uint32_t sector_mask,
-                       const uint64_t count, const uint64_t num_tiles, const uint32_t slice_lo,
-                       const uint32_t slice_len, uint16_t *__restrict__ hitbits, const int first_pass) {
+    probe_pass_kernel(const Src src, const uint64_t *__restrict__ filter, const uint32_t sector_mask,
+                      const uint64_t count, const uint64_t num_tiles, const uint32_t slice_lo,
+                      const uint32_t slice_len, uint16_t *__restrict__ hitbits, const int first_pass,
+                      uint32_t *__restrict__ tile_counts /* non-null on the last pass */) {
 	static_assert(2 * ROUNDS <= 16, "hit bits are kept in a uint16 per thread");
 	constexpr int NWARPS = BLOCK / 32;
 	constexpr uint64_t WARP_KEYS = 64ull * ROUNDS;
 	constexpr uint64_t TILE_KEYS = WARP_KEYS * NWARPS;
+	extern __shared__ __align__(16) uint64_t s_filter[];
+	__shared__ uint32_t s_warp_count[NWARPS];
 	const uint32_t lane = threadIdx.x & 31u;
 	const uint32_t warp = threadIdx.x >> 5;
 	const uint64_t pol_keys = policy_evict_first();
 	const uint64_t pol_filter = policy_evict_last();
-	warm_slice(filter, slice_lo, slice_len, BLOCK);
+	if (SMEM_FILTER) {
+		const uint64_t nvec = (static_cast<uint64_t>(sector_mask) + 1) >> 1;
+		const ulonglong2 *g = reinterpret_cast<const ulonglong2 *>(filter);
+		ulonglong2 *sm = reinterpret_cast<ulonglong2 *>(s_filter);
+		for (uint64_t i = threadIdx.x; i < nvec; i += BLOCK) {
+			sm[i] = __ldg(g + i);
+		}
+		__syncthreads();
+	}
+	if (SLICED) {
+		warm_slice(filter, slice_lo, slice_len, BLOCK);
+	}
 	for (uint64_t tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
 		const uint64_t warp_base = tile * TILE_KEYS + warp * WARP_KEYS;
-		uint32_t hits = probe_tile<Src, ROUNDS, false, true>(src, filter, nullptr, sector_mask, count, warp_base,
-		                                                     (tile + 1) * TILE_KEYS <= count, lane, pol_keys,
-		                                                     pol_filter, slice_lo, slice_len);
+		uint32_t hits = probe_tile<Src, ROUNDS, SMEM_FILTER, SLICED>(src, filter, s_filter, sector_mask, count, warp_base,
+		                                                             (tile + 1) * TILE_KEYS <= count, lane, pol_keys,
+		                                                             pol_filter, slice_lo, slice_len);
 		uint16_t *slot = hitbits + tile * BLOCK + threadIdx.x;
 		if (!first_pass) {
 			hits |= *slot;
 		}
 		*slot = static_cast<uint16_t>(hits);
+		if (tile_counts) { // block-uniform
+			const uint32_t wc = __reduce_add_sync(0xffffffffu, __popc(hits));
+			if (lane == 0) {
+				s_warp_count[warp] = wc;
+			}
+			__syncthreads();
+			if (threadIdx.x == 0) {
+				uint32_t t = 0;
+#pragma unroll
+				for (int w = 0; w < NWARPS; w++) {
+					t += s_warp_count[w];
+				}
+				tile_counts[tile] = t;
+			}
+			__syncthreads();
+		}
 	}
 }
 
-// Final (or only) pass: persistent CTAs, ticket-ordered tiles, decoupled look-back, ordered write.
-// PRIOR: hit bits of the earlier sector-range passes are ORed in from `hitbits`.
-template <class Src, int ROUNDS, int BLOCK, bool SMEM_FILTER, bool SLICED>
+// Exclusive prefix sum of counts[0..n) in place (offsets), total → *found_out.  One CTA of 1024 threads;
+// thread t owns the contiguous chunk [t·c, (t+1)·c).  n ≤ 2^20 tiles (count < 2^32 keys), i.e. ≤ 4 MiB, L2-resident.
+__global__ void __launch_bounds__(1024) scan_tiles_kernel(uint32_t *__restrict__ counts, const uint64_t n,
+                                                          uint64_t *__restrict__ found_out) {
+	__shared__ uint32_t s_part[32];
+	const uint64_t chunk = (n + 1023) / 1024;
+	const uint64_t lo = threadIdx.x * chunk;
+	const uint64_t hi = lo + chunk < n ? lo + chunk : n;
+	uint32_t sum = 0;
+	for (uint64_t i = lo; i < hi; i++) {
+		sum += counts[i];
+	}
+	const uint32_t lane = threadIdx.x & 31u;
+	const uint32_t warp = threadIdx.x >> 5;
+	uint32_t incl = sum;
+#pragma unroll
+	for (int d = 1; d < 32; d <<= 1) {
+		const uint32_t t = __shfl_up_sync(0xffffffffu, incl, d);
+		if (lane >= static_cast<uint32_t>(d)) {
+			incl += t;
+		}
+	}
+	if (lane == 31) {
+		s_part[warp] = incl;
+	}
+	__syncthreads();
+	if (warp == 0) {
+		const uint32_t v = s_part[lane];
+		uint32_t w = v;
+#pragma unroll
+		for (int d = 1; d < 32; d <<= 1) {
+			const uint32_t t = __shfl_up_sync(0xffffffffu, w, d);
+			if (lane >= static_cast<uint32_t>(d)) {
+				w += t;
+			}
+		}
+		s_part[lane] = w - v; // exclusive over warps
+		if (lane == 31) {
+			*found_out = w;
+		}
+	}
+	__syncthreads();
+	uint32_t run = s_part[warp] + incl - sum;
+	for (uint64_t i = lo; i < hi; i++) {
+		const uint32_t c = counts[i];
+		counts[i] = run;
+		run += c;
+	}
+}
+
+// One CTA per tile: ordered write of the tile's survivors.  Row order inside a warp segment is
+// (round, lane, element), the same mapping probe_tile used when it produced the hit bits.
+template <int ROUNDS, int BLOCK>
+__global__ void __launch_bounds__(BLOCK)
+    compact_kernel(const uint16_t *__restrict__ hitbits, const uint32_t *__restrict__ tile_offsets,
+                   const uint64_t num_tiles, uint32_t *__restrict__ sel_out, const uint32_t row_offset,
+                   const uint32_t *__restrict__ translate) {
+	constexpr int NWARPS = BLOCK / 32;
+	constexpr uint64_t WARP_KEYS = 64ull * ROUNDS;
+	constexpr uint64_t TILE_KEYS = WARP_KEYS * NWARPS;
+	__shared__ uint32_t s_warp_count[NWARPS];
+	const uint32_t lane = threadIdx.x & 31u;
+	const uint32_t warp = threadIdx.x >> 5;
+	const uint32_t lt = lanemask_lt();
+	for (uint64_t tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+		const uint32_t hits = hitbits[tile * BLOCK + threadIdx.x];
+		const uint32_t wc = __reduce_add_sync(0xffffffffu, __popc(hits));
+		if (lane == 0) {
+			s_warp_count[warp] = wc;
+		}
+		__syncthreads();
+		uint32_t run = tile_offsets[tile];
+#pragma unroll
+		for (int w = 0; w < NWARPS; w++) {
+			run += w < static_cast<int>(warp) ? s_warp_count[w] : 0u;
+		}
+		__syncthreads();
+		if (wc == 0) {
+			continue; // warp-uniform
+		}
+		const uint32_t rel_base =
+		    static_cast<uint32_t>(tile * TILE_KEYS + warp * WARP_KEYS) + row_offset + lane * 2;
+#pragma unroll
+		for (int r = 0; r < ROUNDS; r++) {
+			const uint32_t h0 = (hits >> (2 * r)) & 1u;
+			const uint32_t h1 = (hits >> (2 * r + 1)) & 1u;
+			const uint32_t b0 = __ballot_sync(0xffffffffu, h0);
+			const uint32_t b1 = __ballot_sync(0xffffffffu, h1);
+			uint32_t pos = run + __popc(b0 & lt) + __popc(b1 & lt);
+			const uint32_t rel = rel_base + r * 64;
+			if (h0) {
+				sel_out[pos] = translate ? __ldg(translate + rel) : rel;
+			}
+			pos += h0;
+			if (h1) {
+				sel_out[pos] = translate ? __ldg(translate + rel + 1) : rel + 1;
+			}
+			run += __popc(b0) + __popc(b1);
+		}
+	}
+}
+
+// Small probes (≤ kFusedMaxKeys): one launch; tiles are chained with a decoupled look-back.
+template <class Src, int ROUNDS, int BLOCK, bool SMEM_FILTER>
 __global__ void __launch_bounds__(BLOCK)
     probe_kernel(const Src src, const uint64_t *__restrict__ filter, const uint32_t sector_mask, const uint64_t count,
                  const uint64_t num_tiles, uint32_t *__restrict__ sel_out, uint64_t *__restrict__ found_out,
                  const uint32_t row_offset, const uint32_t *__restrict__ translate, uint64_t *desc,
-                 unsigned int *ticket, const uint32_t slice_lo, const uint32_t slice_len,
-                 const uint16_t *__restrict__ hitbits) {
+                 unsigned int *ticket) {
 	constexpr int NWARPS = BLOCK / 32;
 	constexpr uint64_t WARP_KEYS = 64ull * ROUNDS;
 	constexpr uint64_t TILE_KEYS = WARP_KEYS * NWARPS;
@@ -359,10 +496,6 @@ __global__ void __launch_bounds__(BLOCK)
 			s[i] = __ldg(g + i);
 		}
 	}
-	if (SLICED) {
-		warm_slice(filter, slice_lo, slice_len, BLOCK);
-	}
-
 	while (true) {
 		if (threadIdx.x == 0) {
 			s_tile = atomicAdd(ticket, 1u);
@@ -373,12 +506,9 @@ __global__ void __launch_bounds__(BLOCK)
 			break;
 		}
 		const uint64_t warp_base = tile * TILE_KEYS + warp * WARP_KEYS;
-		uint32_t hits = probe_tile<Src, ROUNDS, SMEM_FILTER, SLICED>(src, filter, s_filter, sector_mask, count, warp_base,
-		                                                             (tile + 1) * TILE_KEYS <= count, lane, pol_keys,
-		                                                             pol_filter, slice_lo, slice_len);
-		if (SLICED) {
-			hits |= hitbits[tile * BLOCK + threadIdx.x];
-		}
+		const uint32_t hits = probe_tile<Src, ROUNDS, SMEM_FILTER, false>(src, filter, s_filter, sector_mask, count,
+		                                                                  warp_base, (tile + 1) * TILE_KEYS <= count, lane,
+		                                                                  pol_keys, pol_filter, 0u, 0u);
 		// 4. survivors per warp → per tile → global exclusive offset
 		uint32_t warp_count = __reduce_add_sync(0xffffffffu, __popc(hits));
 		if (lane == 0) {
@@ -522,6 +652,7 @@ constexpr int kProbeRounds = 8;    // 16 keys per thread
 constexpr int kProbeBlock = 256;   // global-filter variant: several CTAs per SM
 constexpr int kProbeBlockSmem = 512; // shared-memory variant: ≤128 KiB filter + 1 CTA per SM at the top size
 constexpr uint64_t kProbeTileKeys = 64ull * kProbeRounds * (kProbeBlock / 32);
+constexpr uint64_t kFusedMaxKeys = 1ull << 18; // up to 64 tiles: launch-latency territory, one fused kernel
 
 static inline uint64_t ceil_div(uint64_t a, uint64_t b) {
 	return (a + b - 1) / b;
@@ -558,14 +689,19 @@ static uint64_t slice_sectors_for(uint64_t num_sectors) {
 	return num_sectors > slice ? slice : num_sectors;
 }
 
+static inline uint64_t align_up(uint64_t v, uint64_t a) {
+	return (v + a - 1) / a * a;
+}
+
 size_t probe_scratch_bytes(uint64_t count, uint64_t num_sectors) {
-	// the smaller tile gives the larger tile count; one extra slot holds the ticket counter
+	(void)num_sectors;
+	// block-256 tiles give the larger tile count
 	const uint64_t tiles = ceil_div(count, kProbeTileKeys);
-	size_t bytes = (tiles + 2) * sizeof(uint64_t);
-	if (slice_sectors_for(num_sectors) < num_sectors) {
-		bytes += tiles * kProbeBlock * sizeof(uint16_t); // hit bits carried between sector-range passes
+	if (count <= kFusedMaxKeys) {
+		return (tiles + 2) * sizeof(uint64_t); // look-back descriptors + ticket
 	}
-	return bytes;
+	// tile offsets (uint32, one spare) + hit bits (uint16 per thread per tile)
+	return align_up((tiles + 1) * sizeof(uint32_t), 256) + tiles * kProbeBlock * sizeof(uint16_t);
 }
 
 template <class Src, bool AGG>
@@ -612,11 +748,13 @@ cudaError_t launch_build(const DeviceInfo &dev, const DevCols &cols, uint64_t co
 	           : launch_build_t<GenericSrc, false>(dev, src, count, words, num_sectors, stream, launches);
 }
 
-template <class Src, int BLOCK, bool SMEM, bool SLICED>
-static cudaError_t launch_probe_t(const DeviceInfo &dev, const Src &src, uint64_t count, const uint64_t *words,
-                                  uint64_t num_sectors, uint32_t *sel_out, uint64_t *found_out, uint32_t row_offset,
-                                  const uint32_t *translate, void *scratch, cudaStream_t stream, int *launches) {
-	auto kern = probe_kernel<Src, kProbeRounds, BLOCK, SMEM, SLICED>;
+// Small probes: the fused look-back kernel (one launch + one memset).
+template <class Src, int BLOCK, bool SMEM>
+static cudaError_t launch_probe_fused(const DeviceInfo &dev, const Src &src, uint64_t count, const uint64_t *words,
+                                      uint64_t num_sectors, uint32_t *sel_out, uint64_t *found_out,
+                                      uint32_t row_offset, const uint32_t *translate, void *scratch,
+                                      cudaStream_t stream, int *launches) {
+	auto kern = probe_kernel<Src, kProbeRounds, BLOCK, SMEM>;
 	const uint64_t tile_keys = 64ull * kProbeRounds * (BLOCK / 32);
 	const uint64_t num_tiles = ceil_div(count, tile_keys);
 	const size_t smem = SMEM ? num_sectors * sizeof(uint64_t) : 0;
@@ -641,42 +779,72 @@ static cudaError_t launch_probe_t(const DeviceInfo &dev, const Src &src, uint64_
 	}
 	uint64_t *desc = reinterpret_cast<uint64_t *>(scratch);
 	unsigned int *ticket = reinterpret_cast<unsigned int *>(desc + num_tiles);
-	uint16_t *hitbits = reinterpret_cast<uint16_t *>(desc + num_tiles + 2);
 	e = cudaMemsetAsync(scratch, 0, (num_tiles + 1) * sizeof(uint64_t), stream);
 	if (e != cudaSuccess) {
 		return e;
 	}
-	const uint32_t sector_mask = static_cast<uint32_t>(num_sectors - 1);
-	uint64_t lo = 0, len = num_sectors;
-	if (SLICED) {
-		// every slice but the last goes through the light pass kernel; the last one is fused with the compaction
-		const uint64_t slice = slice_sectors_for(num_sectors);
-		int per_sm_slice = 0;
-		auto slice_kern = probe_slice_kernel<Src, kProbeRounds, BLOCK>;
-		e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_slice, slice_kern, BLOCK, 0);
+	kern<<<static_cast<unsigned>(grid), BLOCK, smem, stream>>>(src, words, static_cast<uint32_t>(num_sectors - 1), count,
+	                                                          num_tiles, sel_out, found_out, row_offset, translate,
+	                                                          desc, ticket);
+	if (launches) {
+		(*launches)++;
+	}
+	return cudaGetLastError();
+}
+
+// Large probes: pass kernel per sector-range slice → scan of tile counts → compaction.
+template <class Src, int BLOCK, bool SMEM, bool SLICED>
+static cudaError_t launch_probe_phased(const DeviceInfo &dev, const Src &src, uint64_t count, const uint64_t *words,
+                                       uint64_t num_sectors, uint32_t *sel_out, uint64_t *found_out,
+                                       uint32_t row_offset, const uint32_t *translate, void *scratch,
+                                       cudaStream_t stream, int *launches) {
+	auto pass = probe_pass_kernel<Src, kProbeRounds, BLOCK, SMEM, SLICED>;
+	auto compact = compact_kernel<kProbeRounds, BLOCK>;
+	const uint64_t tile_keys = 64ull * kProbeRounds * (BLOCK / 32);
+	const uint64_t num_tiles = ceil_div(count, tile_keys);
+	const size_t smem = SMEM ? num_sectors * sizeof(uint64_t) : 0;
+	cudaError_t e;
+	if (SMEM) {
+		e = cudaFuncSetAttribute(pass, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
 		if (e != cudaSuccess) {
 			return e;
 		}
-		uint64_t slice_grid = static_cast<uint64_t>(dev.sm_count) * (per_sm_slice > 0 ? per_sm_slice : 1);
-		if (slice_grid > num_tiles) {
-			slice_grid = num_tiles;
-		}
-		for (; lo + slice < num_sectors; lo += slice) {
-			slice_kern<<<static_cast<unsigned>(slice_grid), BLOCK, 0, stream>>>(
-			    src, words, sector_mask, count, num_tiles, static_cast<uint32_t>(lo), static_cast<uint32_t>(slice),
-			    hitbits, lo == 0 ? 1 : 0);
-			if (launches) {
-				(*launches)++;
-			}
-		}
-		len = num_sectors - lo;
 	}
-	kern<<<static_cast<unsigned>(grid), BLOCK, smem, stream>>>(src, words, sector_mask, count, num_tiles, sel_out,
-	                                                          found_out, row_offset, translate, desc, ticket,
-	                                                          static_cast<uint32_t>(lo), static_cast<uint32_t>(len),
-	                                                          hitbits);
+	int per_sm = 0;
+	e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, pass, BLOCK, smem);
+	if (e != cudaSuccess) {
+		return e;
+	}
+	if (per_sm < 1) {
+		return cudaErrorLaunchOutOfResources;
+	}
+	uint64_t grid = static_cast<uint64_t>(dev.sm_count) * per_sm;
+	if (grid > num_tiles) {
+		grid = num_tiles;
+	}
+	uint32_t *tile_offsets = reinterpret_cast<uint32_t *>(scratch);
+	const uint64_t tiles256 = ceil_div(count, kProbeTileKeys); // layout is sized for the block-256 tile count
+	uint16_t *hitbits = reinterpret_cast<uint16_t *>(reinterpret_cast<char *>(scratch) +
+	                                                 align_up((tiles256 + 1) * sizeof(uint32_t), 256));
+	const uint32_t sector_mask = static_cast<uint32_t>(num_sectors - 1);
+	const uint64_t slice = SLICED ? slice_sectors_for(num_sectors) : num_sectors;
+	for (uint64_t lo = 0; lo < num_sectors; lo += slice) {
+		const uint64_t len = lo + slice < num_sectors ? slice : num_sectors - lo;
+		const bool last = lo + slice >= num_sectors;
+		pass<<<static_cast<unsigned>(grid), BLOCK, smem, stream>>>(src, words, sector_mask, count, num_tiles,
+		                                                          static_cast<uint32_t>(lo), static_cast<uint32_t>(len),
+		                                                          hitbits, lo == 0 ? 1 : 0, last ? tile_offsets : nullptr);
+		if (launches) {
+			(*launches)++;
+		}
+	}
+	scan_tiles_kernel<<<1, 1024, 0, stream>>>(tile_offsets, num_tiles, found_out);
+	const uint64_t cgrid = num_tiles < static_cast<uint64_t>(dev.sm_count) * 64 ? num_tiles
+	                                                                             : static_cast<uint64_t>(dev.sm_count) * 64;
+	compact<<<static_cast<unsigned>(cgrid), BLOCK, 0, stream>>>(hitbits, tile_offsets, num_tiles, sel_out, row_offset,
+	                                                           translate);
 	if (launches) {
-		(*launches)++;
+		(*launches) += 2;
 	}
 	return cudaGetLastError();
 }
@@ -685,16 +853,20 @@ template <class Src>
 static cudaError_t launch_probe_src(const DeviceInfo &dev, const Src &src, uint64_t count, const uint64_t *words,
                                     uint64_t num_sectors, uint32_t *sel_out, uint64_t *found_out, uint32_t row_offset,
                                     const uint32_t *translate, void *scratch, cudaStream_t stream, int *launches) {
-	if (use_smem_filter(dev, num_sectors)) {
-		return launch_probe_t<Src, kProbeBlockSmem, true, false>(dev, src, count, words, num_sectors, sel_out, found_out,
-		                                                         row_offset, translate, scratch, stream, launches);
+#define RPT_PROBE_ARGS dev, src, count, words, num_sectors, sel_out, found_out, row_offset, translate, scratch, stream, launches
+	const bool smem = use_smem_filter(dev, num_sectors);
+	if (count <= kFusedMaxKeys) {
+		return smem ? launch_probe_fused<Src, kProbeBlockSmem, true>(RPT_PROBE_ARGS)
+		            : launch_probe_fused<Src, kProbeBlock, false>(RPT_PROBE_ARGS);
+	}
+	if (smem) {
+		return launch_probe_phased<Src, kProbeBlockSmem, true, false>(RPT_PROBE_ARGS);
 	}
 	if (slice_sectors_for(num_sectors) < num_sectors) {
-		return launch_probe_t<Src, kProbeBlock, false, true>(dev, src, count, words, num_sectors, sel_out, found_out,
-		                                                     row_offset, translate, scratch, stream, launches);
+		return launch_probe_phased<Src, kProbeBlock, false, true>(RPT_PROBE_ARGS);
 	}
-	return launch_probe_t<Src, kProbeBlock, false, false>(dev, src, count, words, num_sectors, sel_out, found_out,
-	                                                      row_offset, translate, scratch, stream, launches);
+	return launch_probe_phased<Src, kProbeBlock, false, false>(RPT_PROBE_ARGS);
+#undef RPT_PROBE_ARGS
 }
 
 cudaError_t launch_probe(const DeviceInfo &dev, const DevCols &cols, uint64_t count, const uint64_t *words,
