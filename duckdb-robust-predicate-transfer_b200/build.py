@@ -5,7 +5,7 @@ import subprocess
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
-LIB = os.path.join(HERE, "librpt_gpu.so")
+LIB = os.environ.get("RPT_GPU_LIB") or os.path.join(HERE, "librpt_gpu.so")
 SOURCES = ["rpt_kernels.cu", "rpt_capi.cu", "rpt_host.cpp"]
 HEADERS = ["rpt_hash.cuh", "rpt_kernels.cuh", "rpt_host.hpp", os.path.join("..", "..", "include", "rpt_gpu.h")]
 
@@ -32,8 +32,17 @@ def needs_build():
     return any(os.path.getmtime(f) > t for f in files)
 
 
-def build(force=False, verbose=False):
-    """Compile every CUDA source for sm_100a into librpt_gpu.so next to this file."""
+def build(force=False, verbose=False, extra_flags=(), out=None):
+    """Compile every CUDA source for sm_100a into librpt_gpu.so next to this file.
+    extra_flags / out build an experimental variant (e.g. -DRPT_PROBE_ROUNDS=4) under another name; RPT_GPU_LIB
+    selects which file the Python driver loads."""
+    if out is not None:
+        srcs = [os.path.join(CSRC, f) for f in SOURCES if os.path.exists(os.path.join(CSRC, f))]
+        cmd = [_nvcc()] + NVCC_FLAGS + list(extra_flags) + ["-o", out] + srcs
+        proc = subprocess.run(cmd, cwd=CSRC, capture_output=True, text=True)
+        if proc.returncode != 0:
+            raise RuntimeError("nvcc failed:\n" + proc.stdout + proc.stderr)
+        return out
     if not force and not needs_build():
         return LIB
     srcs = [os.path.join(CSRC, f) for f in SOURCES if os.path.exists(os.path.join(CSRC, f))]

@@ -68,7 +68,11 @@ __device__ __forceinline__ uint32_t lanemask_lt() {
 // returns a 2-bit validity (rows ≥ count are invalid and must not be read).
 // ---------------------------------------------------------------------------------------------
 struct FlatU64Src { // one flat int64 / uint64 column, no NULLs, base 16-byte aligned
+	static constexpr bool kStageable = true; // a tile is 2·ROUNDS·BLOCK contiguous 8-byte keys: cp.async-able
 	const uint64_t *keys;
+	__device__ __forceinline__ const uint64_t *key_ptr() const {
+		return keys;
+	}
 	// unchecked: rows row0 + r*stride (+0,+1), r < R, all in range.  All R 128-bit loads are issued
 	// before the first hash so that they are in flight together.
 	template <int R>
@@ -103,7 +107,11 @@ struct FlatU64Src { // one flat int64 / uint64 column, no NULLs, base 16-byte al
 };
 
 struct GenericSrc { // any type / sel / validity / multi-column combination
+	static constexpr bool kStageable = false;
 	DevCols cols;
+	__device__ __forceinline__ const uint64_t *key_ptr() const {
+		return nullptr;
+	}
 	template <int R>
 	__device__ __forceinline__ void load_rounds(uint64_t row0, uint64_t stride, uint64_t,
 	                                            uint64_t (&h)[2 * R]) const {
@@ -240,29 +248,15 @@ __device__ __forceinline__ uint32_t tile_lookback(uint64_t *desc, const uint64_t
 	return exclusive;
 }
 
-// Hash a tile's keys and test them against the filter.  Thread-local result: bit i of the return value is the
-// hit flag of this thread's i-th key (i = 2·round + element).  SLICED: only sectors in [slice_lo, slice_lo +
-// slice_len) are looked up (the other keys' bits stay 0 in this pass).
-template <class Src, int ROUNDS, bool SMEM_FILTER, bool SLICED>
-__device__ __forceinline__ uint32_t probe_tile(const Src &src, const uint64_t *__restrict__ filter,
-                                               const uint64_t *s_filter, const uint32_t sector_mask,
-                                               const uint64_t count, const uint64_t warp_base, const bool full_tile,
-                                               const uint32_t lane, const uint64_t pol_keys, const uint64_t pol_filter,
-                                               const uint32_t slice_lo, const uint32_t slice_len) {
-	// 1. stream the keys and hash them
-	uint64_t h[2 * ROUNDS];
-	uint32_t valid = 0;
-	if (full_tile) { // block-uniform: every tile but the last
-		src.template load_rounds<ROUNDS>(warp_base + lane * 2, 64, pol_keys, h);
-		valid = static_cast<uint32_t>((1ull << (2 * ROUNDS)) - 1ull);
-	} else {
-#pragma unroll
-		for (int r = 0; r < ROUNDS; r++) {
-			const uint64_t row0 = warp_base + static_cast<uint64_t>(r) * 64 + lane * 2;
-			valid |= src.load2(row0, count, pol_keys, h[2 * r], h[2 * r + 1]) << (2 * r);
-		}
-	}
-	// 2. all random filter loads of this thread, independent of each other
+// Lookup + test of 2·ROUNDS hashed keys.  Thread-local result: bit i is the hit flag of this thread's i-th key
+// (i = 2·round + element).  SLICED: only sectors in [slice_lo, slice_lo + slice_len) are looked up (the other
+// keys' bits stay 0 in this pass).
+template <int ROUNDS, bool SMEM_FILTER, bool SLICED>
+__device__ __forceinline__ uint32_t test_hashes(const uint64_t (&h)[2 * ROUNDS], const uint64_t *__restrict__ filter,
+                                                const uint64_t *s_filter, const uint32_t sector_mask,
+                                                const uint64_t pol_filter, const uint32_t slice_lo,
+                                                const uint32_t slice_len) {
+	// all random filter loads of this thread, independent of each other
 	uint64_t w[2 * ROUNDS];
 #pragma unroll
 	for (int i = 0; i < 2 * ROUNDS; i++) {
@@ -278,13 +272,35 @@ __device__ __forceinline__ uint32_t probe_tile(const Src &src, const uint64_t *_
 			w[i] = ld_filter_word(filter + sector, pol_filter);
 		}
 	}
-	// 3. test
 	uint32_t hits = 0;
 #pragma unroll
-	for (int i = 0; i < 2 * ROUNDS; i++) {
-		hits |= sector_test(w[i], static_cast<uint32_t>(h[i] >> 32)) << i;
+	for (int i = 2 * ROUNDS - 1; i >= 0; i--) { // hits·2 + bit is one IMAD on the FMA pipe; the ALU pipe is the busy one
+		hits = hits * 2u + sector_test(w[i], static_cast<uint32_t>(h[i] >> 32));
 	}
-	return hits & valid;
+	return hits;
+}
+
+// Hash a tile's keys (read straight from global memory) and test them against the filter.
+template <class Src, int ROUNDS, bool SMEM_FILTER, bool SLICED>
+__device__ __forceinline__ uint32_t probe_tile(const Src &src, const uint64_t *__restrict__ filter,
+                                               const uint64_t *s_filter, const uint32_t sector_mask,
+                                               const uint64_t count, const uint64_t warp_base, const bool full_tile,
+                                               const uint32_t lane, const uint64_t pol_keys, const uint64_t pol_filter,
+                                               const uint32_t slice_lo, const uint32_t slice_len) {
+	uint64_t h[2 * ROUNDS];
+	uint32_t valid = 0;
+	if (full_tile) { // block-uniform: every tile but the last
+		src.template load_rounds<ROUNDS>(warp_base + lane * 2, 64, pol_keys, h);
+		valid = static_cast<uint32_t>((1ull << (2 * ROUNDS)) - 1ull);
+	} else {
+#pragma unroll
+		for (int r = 0; r < ROUNDS; r++) {
+			const uint64_t row0 = warp_base + static_cast<uint64_t>(r) * 64 + lane * 2;
+			valid |= src.load2(row0, count, pol_keys, h[2 * r], h[2 * r + 1]) << (2 * r);
+		}
+	}
+	return test_hashes<ROUNDS, SMEM_FILTER, SLICED>(h, filter, s_filter, sector_mask, pol_filter, slice_lo, slice_len) &
+	       valid;
 }
 
 // Pulls a slice of the filter into L2 with evict_last priority, one prefetch per 128-byte line, so that the
@@ -299,27 +315,49 @@ __device__ __forceinline__ void warm_slice(const uint64_t *__restrict__ filter, 
 	}
 }
 
-// ---- large probes: pass kernel(s) → tile-count scan → compaction ---------------------------------------
+// ---- large probes: pass kernel(s) → segment-count scan → compaction -------------------------------------
 // The fused single-kernel probe below chains tiles through a decoupled look-back; with persistent CTAs that
 // puts a ticket fetch, three block barriers and the look-back latency on every tile's critical path (ncu:
 // 46 % barrier + 34 % long-scoreboard stalls, issue slots 22 % busy).  Large probes therefore run as
-// independent phases with no inter-CTA dependency inside any kernel:
-//   probe_pass_kernel   hashes and tests the keys (once per sector-range slice), leaving one uint16 of hit
-//                       bits per thread per tile in scratch; the last pass also leaves each tile's hit count
-//   scan_tiles_kernel   exclusive prefix sum of the tile counts (one CTA; ≤ 2^20 tiles), writes `found`
-//   compact_kernel      turns hit bits + tile offsets into the ordered selection vector
+// independent phases with no inter-CTA (and no intra-CTA) dependency inside the hot kernels:
+//   probe_pass_kernel     hashes and tests the keys (once per sector-range slice), leaving one uint16 of hit
+//                         bits per thread per tile in scratch; the last pass also leaves the hit count of
+//                         every warp segment (64·ROUNDS consecutive rows)
+//   scan_blocks_kernel    exclusive prefix sum inside blocks of 4096 segment counts + block totals
+//   scan_totals_kernel    exclusive prefix sum of the block totals (one CTA), writes `found`
+//   compact_kernel        warp per segment: hit bits + offsets → ordered selection vector
+//
+// Key staging: for a flat 8-byte column the next tile's keys are fetched with cp.async (LDGSTS, 16 bytes per
+// request, L2 evict_first) into a thread-private shared-memory slot while the current tile is hashed and
+// tested, so the DRAM latency of the key stream is off the critical path; no barrier is involved because
+// every thread reads back exactly the bytes it requested.
+constexpr uint64_t kScanBlock = 4096;
+
+__device__ __forceinline__ void cp_async_16(void *smem_dst, const void *gmem_src, uint64_t pol) {
+	const uint32_t d = static_cast<uint32_t>(__cvta_generic_to_shared(smem_dst));
+	asm volatile("cp.async.cg.shared.global.L2::cache_hint [%0], [%1], 16, %2;" ::"r"(d), "l"(gmem_src), "l"(pol)
+	             : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() {
+	asm volatile("cp.async.commit_group;" ::: "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() {
+	asm volatile("cp.async.wait_group 0;" ::: "memory");
+}
+
 template <class Src, int ROUNDS, int BLOCK, bool SMEM_FILTER, bool SLICED>
 __global__ void __launch_bounds__(BLOCK)
     probe_pass_kernel(const Src src, const uint64_t *__restrict__ filter, const uint32_t sector_mask,
                       const uint64_t count, const uint64_t num_tiles, const uint32_t slice_lo,
                       const uint32_t slice_len, uint16_t *__restrict__ hitbits, const int first_pass,
-                      uint32_t *__restrict__ tile_counts /* non-null on the last pass */) {
+                      uint32_t *__restrict__ seg_counts /* non-null on the last pass */) {
 	static_assert(2 * ROUNDS <= 16, "hit bits are kept in a uint16 per thread");
 	constexpr int NWARPS = BLOCK / 32;
 	constexpr uint64_t WARP_KEYS = 64ull * ROUNDS;
 	constexpr uint64_t TILE_KEYS = WARP_KEYS * NWARPS;
+	constexpr bool STAGED = Src::kStageable && !SMEM_FILTER;
 	extern __shared__ __align__(16) uint64_t s_filter[];
-	__shared__ uint32_t s_warp_count[NWARPS];
+	__shared__ __align__(16) ulonglong2 s_keys[STAGED ? ROUNDS * BLOCK : 1];
 	const uint32_t lane = threadIdx.x & 31u;
 	const uint32_t warp = threadIdx.x >> 5;
 	const uint64_t pol_keys = policy_evict_first();
@@ -333,50 +371,88 @@ __global__ void __launch_bounds__(BLOCK)
 		}
 		__syncthreads();
 	}
+	// thread-private staging slots: round r of this thread lives at s_keys[r·BLOCK + tid] (conflict-free 128-bit)
+	auto stage = [&](uint64_t tile) {
+		if (STAGED && tile < num_tiles && (tile + 1) * TILE_KEYS <= count) {
+			const uint64_t *g = src.key_ptr() + tile * TILE_KEYS + warp * WARP_KEYS + lane * 2;
+#pragma unroll
+			for (int r = 0; r < ROUNDS; r++) {
+				cp_async_16(&s_keys[r * BLOCK + threadIdx.x], g + r * 64, pol_keys);
+			}
+		}
+		cp_async_commit();
+	};
 	if (SLICED) {
 		warm_slice(filter, slice_lo, slice_len, BLOCK);
 	}
-	for (uint64_t tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-		const uint64_t warp_base = tile * TILE_KEYS + warp * WARP_KEYS;
-		uint32_t hits = probe_tile<Src, ROUNDS, SMEM_FILTER, SLICED>(src, filter, s_filter, sector_mask, count, warp_base,
-		                                                             (tile + 1) * TILE_KEYS <= count, lane, pol_keys,
-		                                                             pol_filter, slice_lo, slice_len);
-		uint16_t *slot = hitbits + tile * BLOCK + threadIdx.x;
-		if (!first_pass) {
-			hits |= *slot;
-		}
-		*slot = static_cast<uint16_t>(hits);
-		if (tile_counts) { // block-uniform
-			const uint32_t wc = __reduce_add_sync(0xffffffffu, __popc(hits));
-			if (lane == 0) {
-				s_warp_count[warp] = wc;
+	// Software pipeline with ONE staging call site: iteration i finishes tile `cur` (staged in iteration i-1) and
+	// stages tile `nxt`.  (A separate prologue call made ptxas 12.9 emit LDGSTS with unset uniform registers.)
+	constexpr uint64_t kNone = ~0ULL;
+	uint64_t cur = kNone;
+	for (uint64_t nxt = blockIdx.x;; nxt += gridDim.x) {
+		uint64_t h[2 * ROUNDS];
+		uint32_t prior = 0;
+		uint16_t *slot = nullptr;
+		bool full_tile = false;
+		if (cur != kNone) {
+			full_tile = (cur + 1) * TILE_KEYS <= count;
+			slot = hitbits + cur * BLOCK + threadIdx.x;
+			if (!first_pass) {
+				prior = *slot; // issued before the key / filter latency chain, consumed after it
 			}
-			__syncthreads();
-			if (threadIdx.x == 0) {
-				uint32_t t = 0;
+			if (STAGED && full_tile) {
+				cp_async_wait_all();
 #pragma unroll
-				for (int w = 0; w < NWARPS; w++) {
-					t += s_warp_count[w];
+				for (int r = 0; r < ROUNDS; r++) {
+					const ulonglong2 k = s_keys[r * BLOCK + threadIdx.x];
+					h[2 * r] = murmur64(k.x);
+					h[2 * r + 1] = murmur64(k.y);
 				}
-				tile_counts[tile] = t;
 			}
-			__syncthreads();
 		}
+		if (STAGED) {
+			stage(nxt); // the slots of `cur` were read above (same thread, program order)
+		}
+		if (cur != kNone) {
+			uint32_t hits;
+			if (STAGED && full_tile) {
+				hits = test_hashes<ROUNDS, SMEM_FILTER, SLICED>(h, filter, s_filter, sector_mask, pol_filter, slice_lo,
+				                                                slice_len);
+			} else {
+				hits = probe_tile<Src, ROUNDS, SMEM_FILTER, SLICED>(src, filter, s_filter, sector_mask, count,
+				                                                    cur * TILE_KEYS + warp * WARP_KEYS, full_tile, lane,
+				                                                    pol_keys, pol_filter, slice_lo, slice_len);
+			}
+			hits |= prior;
+			*slot = static_cast<uint16_t>(hits);
+			if (seg_counts) { // kernel-uniform
+				const uint32_t wc = __reduce_add_sync(0xffffffffu, __popc(hits));
+				if (lane == 0) {
+					seg_counts[cur * NWARPS + warp] = wc;
+				}
+			}
+		}
+		if (nxt >= num_tiles) {
+			break;
+		}
+		cur = nxt;
+	}
+	if (STAGED) {
+		cp_async_wait_all();
 	}
 }
 
-// Exclusive prefix sum of counts[0..n) in place (offsets), total → *found_out.  One CTA of 1024 threads;
-// thread t owns the contiguous chunk [t·c, (t+1)·c).  n ≤ 2^20 tiles (count < 2^32 keys), i.e. ≤ 4 MiB, L2-resident.
-__global__ void __launch_bounds__(1024) scan_tiles_kernel(uint32_t *__restrict__ counts, const uint64_t n,
-                                                          uint64_t *__restrict__ found_out) {
+// Exclusive prefix sums inside blocks of kScanBlock counts (in place) and each block's total.
+__global__ void __launch_bounds__(1024) scan_blocks_kernel(uint32_t *__restrict__ counts, const uint64_t n,
+                                                           uint32_t *__restrict__ block_totals) {
 	__shared__ uint32_t s_part[32];
-	const uint64_t chunk = (n + 1023) / 1024;
-	const uint64_t lo = threadIdx.x * chunk;
-	const uint64_t hi = lo + chunk < n ? lo + chunk : n;
-	uint32_t sum = 0;
-	for (uint64_t i = lo; i < hi; i++) {
-		sum += counts[i];
+	const uint64_t base = static_cast<uint64_t>(blockIdx.x) * kScanBlock + threadIdx.x * 4ull;
+	uint32_t v[4];
+#pragma unroll
+	for (int j = 0; j < 4; j++) {
+		v[j] = base + j < n ? counts[base + j] : 0u;
 	}
+	const uint32_t sum = v[0] + v[1] + v[2] + v[3];
 	const uint32_t lane = threadIdx.x & 31u;
 	const uint32_t warp = threadIdx.x >> 5;
 	uint32_t incl = sum;
@@ -392,8 +468,8 @@ __global__ void __launch_bounds__(1024) scan_tiles_kernel(uint32_t *__restrict__
 	}
 	__syncthreads();
 	if (warp == 0) {
-		const uint32_t v = s_part[lane];
-		uint32_t w = v;
+		const uint32_t p = s_part[lane];
+		uint32_t w = p;
 #pragma unroll
 		for (int d = 1; d < 32; d <<= 1) {
 			const uint32_t t = __shfl_up_sync(0xffffffffu, w, d);
@@ -401,68 +477,119 @@ __global__ void __launch_bounds__(1024) scan_tiles_kernel(uint32_t *__restrict__
 				w += t;
 			}
 		}
-		s_part[lane] = w - v; // exclusive over warps
+		s_part[lane] = w - p;
+		if (lane == 31) {
+			block_totals[blockIdx.x] = w;
+		}
+	}
+	__syncthreads();
+	uint32_t run = s_part[warp] + incl - sum;
+#pragma unroll
+	for (int j = 0; j < 4; j++) {
+		if (base + j < n) {
+			counts[base + j] = run;
+		}
+		run += v[j];
+	}
+}
+
+// Exclusive prefix sum of the block totals in place (nblocks ≤ 2048: count < 2^32 keys), total → *found_out.
+__global__ void __launch_bounds__(1024) scan_totals_kernel(uint32_t *__restrict__ block_totals, const uint32_t nblocks,
+                                                           uint64_t *__restrict__ found_out) {
+	__shared__ uint32_t s_part[32];
+	const uint32_t i0 = threadIdx.x * 2u;
+	const uint32_t a = i0 < nblocks ? block_totals[i0] : 0u;
+	const uint32_t b = i0 + 1 < nblocks ? block_totals[i0 + 1] : 0u;
+	const uint32_t sum = a + b;
+	const uint32_t lane = threadIdx.x & 31u;
+	const uint32_t warp = threadIdx.x >> 5;
+	uint32_t incl = sum;
+#pragma unroll
+	for (int d = 1; d < 32; d <<= 1) {
+		const uint32_t t = __shfl_up_sync(0xffffffffu, incl, d);
+		if (lane >= static_cast<uint32_t>(d)) {
+			incl += t;
+		}
+	}
+	if (lane == 31) {
+		s_part[warp] = incl;
+	}
+	__syncthreads();
+	if (warp == 0) {
+		const uint32_t p = s_part[lane];
+		uint32_t w = p;
+#pragma unroll
+		for (int d = 1; d < 32; d <<= 1) {
+			const uint32_t t = __shfl_up_sync(0xffffffffu, w, d);
+			if (lane >= static_cast<uint32_t>(d)) {
+				w += t;
+			}
+		}
+		s_part[lane] = w - p;
 		if (lane == 31) {
 			*found_out = w;
 		}
 	}
 	__syncthreads();
-	uint32_t run = s_part[warp] + incl - sum;
-	for (uint64_t i = lo; i < hi; i++) {
-		const uint32_t c = counts[i];
-		counts[i] = run;
-		run += c;
+	const uint32_t excl = s_part[warp] + incl - sum;
+	if (i0 < nblocks) {
+		block_totals[i0] = excl;
+	}
+	if (i0 + 1 < nblocks) {
+		block_totals[i0 + 1] = excl + a;
 	}
 }
 
-// One CTA per tile: ordered write of the tile's survivors.  Row order inside a warp segment is
-// (round, lane, element), the same mapping probe_tile used when it produced the hit bits.
-template <int ROUNDS, int BLOCK>
-__global__ void __launch_bounds__(BLOCK)
-    compact_kernel(const uint16_t *__restrict__ hitbits, const uint32_t *__restrict__ tile_offsets,
-                   const uint64_t num_tiles, uint32_t *__restrict__ sel_out, const uint32_t row_offset,
-                   const uint32_t *__restrict__ translate) {
-	constexpr int NWARPS = BLOCK / 32;
-	constexpr uint64_t WARP_KEYS = 64ull * ROUNDS;
-	constexpr uint64_t TILE_KEYS = WARP_KEYS * NWARPS;
-	__shared__ uint32_t s_warp_count[NWARPS];
+// One warp per segment, UNROLL segments in flight per warp: ordered write of the survivors.  Row order inside a
+// segment is (round, lane, element), the mapping test_hashes used when it produced the hit bits.  The slot of
+// segment g (tile g / NWARPS, warp g % NWARPS) lane l is hitbits[g·32 + l] for every BLOCK.
+template <int ROUNDS>
+__global__ void __launch_bounds__(256)
+    compact_kernel(const uint16_t *__restrict__ hitbits, const uint32_t *__restrict__ seg_offsets,
+                   const uint32_t *__restrict__ block_offsets, const uint64_t num_segs, uint32_t *__restrict__ sel_out,
+                   const uint32_t row_offset, const uint32_t *__restrict__ translate) {
+	constexpr int UNROLL = 4;
+	constexpr uint64_t SEG_KEYS = 64ull * ROUNDS;
 	const uint32_t lane = threadIdx.x & 31u;
-	const uint32_t warp = threadIdx.x >> 5;
 	const uint32_t lt = lanemask_lt();
-	for (uint64_t tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-		const uint32_t hits = hitbits[tile * BLOCK + threadIdx.x];
-		const uint32_t wc = __reduce_add_sync(0xffffffffu, __popc(hits));
-		if (lane == 0) {
-			s_warp_count[warp] = wc;
-		}
-		__syncthreads();
-		uint32_t run = tile_offsets[tile];
+	const uint64_t warp_global = (static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
+	const uint64_t num_warps = (static_cast<uint64_t>(gridDim.x) * blockDim.x) >> 5;
+	for (uint64_t g0 = warp_global * UNROLL; g0 < num_segs; g0 += num_warps * UNROLL) {
+		uint32_t hits[UNROLL], off[UNROLL];
 #pragma unroll
-		for (int w = 0; w < NWARPS; w++) {
-			run += w < static_cast<int>(warp) ? s_warp_count[w] : 0u;
+		for (int u = 0; u < UNROLL; u++) {
+			const uint64_t g = g0 + u;
+			hits[u] = 0;
+			off[u] = 0;
+			if (g < num_segs) {
+				hits[u] = hitbits[g * 32 + lane];
+				off[u] = __ldg(seg_offsets + g) + __ldg(block_offsets + g / kScanBlock);
+			}
 		}
-		__syncthreads();
-		if (wc == 0) {
-			continue; // warp-uniform
-		}
-		const uint32_t rel_base =
-		    static_cast<uint32_t>(tile * TILE_KEYS + warp * WARP_KEYS) + row_offset + lane * 2;
 #pragma unroll
-		for (int r = 0; r < ROUNDS; r++) {
-			const uint32_t h0 = (hits >> (2 * r)) & 1u;
-			const uint32_t h1 = (hits >> (2 * r + 1)) & 1u;
-			const uint32_t b0 = __ballot_sync(0xffffffffu, h0);
-			const uint32_t b1 = __ballot_sync(0xffffffffu, h1);
-			uint32_t pos = run + __popc(b0 & lt) + __popc(b1 & lt);
-			const uint32_t rel = rel_base + r * 64;
-			if (h0) {
-				sel_out[pos] = translate ? __ldg(translate + rel) : rel;
+		for (int u = 0; u < UNROLL; u++) {
+			if (!__any_sync(0xffffffffu, hits[u] != 0)) {
+				continue; // warp-uniform
 			}
-			pos += h0;
-			if (h1) {
-				sel_out[pos] = translate ? __ldg(translate + rel + 1) : rel + 1;
+			uint32_t run = off[u];
+			const uint32_t rel_base = static_cast<uint32_t>((g0 + u) * SEG_KEYS) + row_offset + lane * 2;
+#pragma unroll
+			for (int r = 0; r < ROUNDS; r++) {
+				const uint32_t h0 = (hits[u] >> (2 * r)) & 1u;
+				const uint32_t h1 = (hits[u] >> (2 * r + 1)) & 1u;
+				const uint32_t b0 = __ballot_sync(0xffffffffu, h0);
+				const uint32_t b1 = __ballot_sync(0xffffffffu, h1);
+				uint32_t pos = run + __popc(b0 & lt) + __popc(b1 & lt);
+				const uint32_t rel = rel_base + r * 64;
+				if (h0) {
+					sel_out[pos] = translate ? __ldg(translate + rel) : rel;
+				}
+				pos += h0;
+				if (h1) {
+					sel_out[pos] = translate ? __ldg(translate + rel + 1) : rel + 1;
+				}
+				run += __popc(b0) + __popc(b1);
 			}
-			run += __popc(b0) + __popc(b1);
 		}
 	}
 }
@@ -648,7 +775,10 @@ __global__ void __launch_bounds__(256) synth_probe_kernel(uint64_t *out, const u
 // ---------------------------------------------------------------------------------------------
 // launchers
 // ---------------------------------------------------------------------------------------------
-constexpr int kProbeRounds = 8;    // 16 keys per thread
+#ifndef RPT_PROBE_ROUNDS
+#define RPT_PROBE_ROUNDS 8
+#endif
+constexpr int kProbeRounds = RPT_PROBE_ROUNDS; // 2·ROUNDS keys per thread
 constexpr int kProbeBlock = 256;   // global-filter variant: several CTAs per SM
 constexpr int kProbeBlockSmem = 512; // shared-memory variant: ≤128 KiB filter + 1 CTA per SM at the top size
 constexpr uint64_t kProbeTileKeys = 64ull * kProbeRounds * (kProbeBlock / 32);
@@ -693,15 +823,28 @@ static inline uint64_t align_up(uint64_t v, uint64_t a) {
 	return (v + a - 1) / a * a;
 }
 
+// Scratch layout of a phased probe: [segment offsets u32 × cap][block totals u32 × blocks][hit bits u16 × cap·32]
+struct PhasedLayout {
+	uint64_t seg_cap;    // segments (64·ROUNDS rows each), with slack for the last partial tile of either block size
+	uint64_t block_cap;  // scan blocks of kScanBlock segments
+	size_t off_totals, off_hitbits, bytes;
+};
+static PhasedLayout phased_layout(uint64_t count) {
+	PhasedLayout l;
+	l.seg_cap = ceil_div(count, 64ull * kProbeRounds) + 32;
+	l.block_cap = ceil_div(l.seg_cap, kScanBlock);
+	l.off_totals = align_up(l.seg_cap * sizeof(uint32_t), 256);
+	l.off_hitbits = l.off_totals + align_up(l.block_cap * sizeof(uint32_t), 256);
+	l.bytes = l.off_hitbits + l.seg_cap * 32 * sizeof(uint16_t);
+	return l;
+}
+
 size_t probe_scratch_bytes(uint64_t count, uint64_t num_sectors) {
 	(void)num_sectors;
-	// block-256 tiles give the larger tile count
-	const uint64_t tiles = ceil_div(count, kProbeTileKeys);
 	if (count <= kFusedMaxKeys) {
-		return (tiles + 2) * sizeof(uint64_t); // look-back descriptors + ticket
+		return (ceil_div(count, kProbeTileKeys) + 2) * sizeof(uint64_t); // look-back descriptors + ticket
 	}
-	// tile offsets (uint32, one spare) + hit bits (uint16 per thread per tile)
-	return align_up((tiles + 1) * sizeof(uint32_t), 256) + tiles * kProbeBlock * sizeof(uint16_t);
+	return phased_layout(count).bytes;
 }
 
 template <class Src, bool AGG>
@@ -792,16 +935,16 @@ static cudaError_t launch_probe_fused(const DeviceInfo &dev, const Src &src, uin
 	return cudaGetLastError();
 }
 
-// Large probes: pass kernel per sector-range slice → scan of tile counts → compaction.
+// Large probes: pass kernel per sector-range slice → two-level scan of segment counts → compaction.
 template <class Src, int BLOCK, bool SMEM, bool SLICED>
 static cudaError_t launch_probe_phased(const DeviceInfo &dev, const Src &src, uint64_t count, const uint64_t *words,
                                        uint64_t num_sectors, uint32_t *sel_out, uint64_t *found_out,
                                        uint32_t row_offset, const uint32_t *translate, void *scratch,
                                        cudaStream_t stream, int *launches) {
 	auto pass = probe_pass_kernel<Src, kProbeRounds, BLOCK, SMEM, SLICED>;
-	auto compact = compact_kernel<kProbeRounds, BLOCK>;
 	const uint64_t tile_keys = 64ull * kProbeRounds * (BLOCK / 32);
 	const uint64_t num_tiles = ceil_div(count, tile_keys);
+	const uint64_t num_segs = num_tiles * (BLOCK / 32);
 	const size_t smem = SMEM ? num_sectors * sizeof(uint64_t) : 0;
 	cudaError_t e;
 	if (SMEM) {
@@ -822,10 +965,11 @@ static cudaError_t launch_probe_phased(const DeviceInfo &dev, const Src &src, ui
 	if (grid > num_tiles) {
 		grid = num_tiles;
 	}
-	uint32_t *tile_offsets = reinterpret_cast<uint32_t *>(scratch);
-	const uint64_t tiles256 = ceil_div(count, kProbeTileKeys); // layout is sized for the block-256 tile count
-	uint16_t *hitbits = reinterpret_cast<uint16_t *>(reinterpret_cast<char *>(scratch) +
-	                                                 align_up((tiles256 + 1) * sizeof(uint32_t), 256));
+	const PhasedLayout lay = phased_layout(count);
+	char *base = reinterpret_cast<char *>(scratch);
+	uint32_t *seg_offsets = reinterpret_cast<uint32_t *>(base);
+	uint32_t *block_totals = reinterpret_cast<uint32_t *>(base + lay.off_totals);
+	uint16_t *hitbits = reinterpret_cast<uint16_t *>(base + lay.off_hitbits);
 	const uint32_t sector_mask = static_cast<uint32_t>(num_sectors - 1);
 	const uint64_t slice = SLICED ? slice_sectors_for(num_sectors) : num_sectors;
 	for (uint64_t lo = 0; lo < num_sectors; lo += slice) {
@@ -833,18 +977,20 @@ static cudaError_t launch_probe_phased(const DeviceInfo &dev, const Src &src, ui
 		const bool last = lo + slice >= num_sectors;
 		pass<<<static_cast<unsigned>(grid), BLOCK, smem, stream>>>(src, words, sector_mask, count, num_tiles,
 		                                                          static_cast<uint32_t>(lo), static_cast<uint32_t>(len),
-		                                                          hitbits, lo == 0 ? 1 : 0, last ? tile_offsets : nullptr);
+		                                                          hitbits, lo == 0 ? 1 : 0, last ? seg_offsets : nullptr);
 		if (launches) {
 			(*launches)++;
 		}
 	}
-	scan_tiles_kernel<<<1, 1024, 0, stream>>>(tile_offsets, num_tiles, found_out);
-	const uint64_t cgrid = num_tiles < static_cast<uint64_t>(dev.sm_count) * 64 ? num_tiles
-	                                                                             : static_cast<uint64_t>(dev.sm_count) * 64;
-	compact<<<static_cast<unsigned>(cgrid), BLOCK, 0, stream>>>(hitbits, tile_offsets, num_tiles, sel_out, row_offset,
-	                                                           translate);
+	const uint64_t nblocks = ceil_div(num_segs, kScanBlock);
+	scan_blocks_kernel<<<static_cast<unsigned>(nblocks), 1024, 0, stream>>>(seg_offsets, num_segs, block_totals);
+	scan_totals_kernel<<<1, 1024, 0, stream>>>(block_totals, static_cast<uint32_t>(nblocks), found_out);
+	const uint64_t want = ceil_div(num_segs, 8ull * 4); // 8 warps per CTA, 4 segments per warp iteration
+	const uint64_t cap = static_cast<uint64_t>(dev.sm_count) * 8 * 4;
+	compact_kernel<kProbeRounds><<<static_cast<unsigned>(want < cap ? want : cap), 256, 0, stream>>>(
+	    hitbits, seg_offsets, block_totals, num_segs, sel_out, row_offset, translate);
 	if (launches) {
-		(*launches) += 2;
+		(*launches) += 3;
 	}
 	return cudaGetLastError();
 }
