@@ -68,10 +68,13 @@ __device__ __forceinline__ uint32_t lanemask_lt() {
 // returns a 2-bit validity (rows ≥ count are invalid and must not be read).
 // ---------------------------------------------------------------------------------------------
 struct FlatU64Src { // one flat int64 / uint64 column, no NULLs, base 16-byte aligned
-	static constexpr bool kStageable = true; // a tile is 2·ROUNDS·BLOCK contiguous 8-byte keys: cp.async-able
+	static constexpr bool kStageable = true; // a segment is 512 contiguous 8-byte keys: cp.async-able
 	const uint64_t *keys;
 	__device__ __forceinline__ const uint64_t *key_ptr() const {
 		return keys;
+	}
+	__device__ __forceinline__ uint64_t hash_at(uint64_t row, uint64_t pol) const {
+		return murmur64(ld_stream_u64(keys + row, pol));
 	}
 	// unchecked: rows row0 + r*stride (+0,+1), r < R, all in range.  All R 128-bit loads are issued
 	// before the first hash so that they are in flight together.
@@ -111,6 +114,9 @@ struct GenericSrc { // any type / sel / validity / multi-column combination
 	DevCols cols;
 	__device__ __forceinline__ const uint64_t *key_ptr() const {
 		return nullptr;
+	}
+	__device__ __forceinline__ uint64_t hash_at(uint64_t row, uint64_t) const {
+		return hash_row(cols, row);
 	}
 	template <int R>
 	__device__ __forceinline__ void load_rounds(uint64_t row0, uint64_t stride, uint64_t,
@@ -315,23 +321,29 @@ __device__ __forceinline__ void warm_slice(const uint64_t *__restrict__ filter, 
 	}
 }
 
-// ---- large probes: pass kernel(s) → segment-count scan → compaction -------------------------------------
-// The fused single-kernel probe below chains tiles through a decoupled look-back; with persistent CTAs that
-// puts a ticket fetch, three block barriers and the look-back latency on every tile's critical path (ncu:
+// ---- large probes: bitmap pass kernel(s) → segment-count scan → compaction ------------------------------
+// The fused single-kernel probe further down chains tiles through a decoupled look-back; with persistent CTAs
+// that puts a ticket fetch, three block barriers and the look-back latency on every tile's critical path (ncu:
 // 46 % barrier + 34 % long-scoreboard stalls, issue slots 22 % busy).  Large probes therefore run as
-// independent phases with no inter-CTA (and no intra-CTA) dependency inside the hot kernels:
-//   probe_pass_kernel     hashes and tests the keys (once per sector-range slice), leaving one uint16 of hit
-//                         bits per thread per tile in scratch; the last pass also leaves the hit count of
-//                         every warp segment (64·ROUNDS consecutive rows)
+// independent phases with no inter-CTA and no intra-CTA dependency inside the hot kernel:
+//   probe_bitmap_kernel   hashes and tests the keys (once per sector-range slice) and ORs the hit flags into a
+//                         ROW-ORDERED bitmap (bit i of the bitmap = row i passes); the last pass also leaves
+//                         the hit count of every segment (512 consecutive rows)
 //   scan_blocks_kernel    exclusive prefix sum inside blocks of 4096 segment counts + block totals
 //   scan_totals_kernel    exclusive prefix sum of the block totals (one CTA), writes `found`
-//   compact_kernel        warp per segment: hit bits + offsets → ordered selection vector
+//   compact_bitmap_kernel bitmap words + offsets → ordered selection vector
 //
-// Key staging: for a flat 8-byte column the next tile's keys are fetched with cp.async (LDGSTS, 16 bytes per
-// request, L2 evict_first) into a thread-private shared-memory slot while the current tile is hashed and
-// tested, so the DRAM latency of the key stream is off the critical path; no barrier is involved because
-// every thread reads back exactly the bytes it requested.
+// Work unit = one warp × one segment of 512 consecutive rows; lane l owns rows 16·l … 16·l+15 of the segment,
+// so its 16 hit flags are one uint16 of the bitmap and a warp stores 64 contiguous bytes.
+//
+// Key staging (flat 8-byte column): the segment's 4 KiB arrive in shared memory through 8 coalesced cp.async
+// (LDGSTS, 16 bytes per lane, L2 evict_first) into a warp-private double buffer while the previous segment is
+// hashed and tested, so the DRAM latency of the key stream is off the critical path and no block barrier
+// exists.  The layout in shared memory is linear; lane l reads its eight 16-byte units in the rotated order
+// (p + l) mod 8, p = 0..7, which makes every quarter-warp's LDS.128 hit eight distinct bank groups.  The hit
+// mask collected in that rotated order is rotated back by 2·(l mod 8) bits at the end.
 constexpr uint64_t kScanBlock = 4096;
+constexpr uint64_t kSegRows = 512;
 
 __device__ __forceinline__ void cp_async_16(void *smem_dst, const void *gmem_src, uint64_t pol) {
 	const uint32_t d = static_cast<uint32_t>(__cvta_generic_to_shared(smem_dst));
@@ -341,23 +353,77 @@ __device__ __forceinline__ void cp_async_16(void *smem_dst, const void *gmem_src
 __device__ __forceinline__ void cp_async_commit() {
 	asm volatile("cp.async.commit_group;" ::: "memory");
 }
-__device__ __forceinline__ void cp_async_wait_all() {
-	asm volatile("cp.async.wait_group 0;" ::: "memory");
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+	asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
 }
 
-template <class Src, int ROUNDS, int BLOCK, bool SMEM_FILTER, bool SLICED>
-__global__ void __launch_bounds__(BLOCK)
-    probe_pass_kernel(const Src src, const uint64_t *__restrict__ filter, const uint32_t sector_mask,
-                      const uint64_t count, const uint64_t num_tiles, const uint32_t slice_lo,
-                      const uint32_t slice_len, uint16_t *__restrict__ hitbits, const int first_pass,
-                      uint32_t *__restrict__ seg_counts /* non-null on the last pass */) {
-	static_assert(2 * ROUNDS <= 16, "hit bits are kept in a uint16 per thread");
+// Bit positions on the FMA pipe: (hi << k) >> 26 as IMAD.SHL + IMAD.HI, leaving the ALU pipe (the busiest one:
+// ncu r1a 55 % vs 18 % FMA) to the four funnel shifts and two LOP3 of the test itself.
+__device__ __forceinline__ uint32_t mul_lo_u32(uint32_t a, uint32_t b) {
+	uint32_t d;
+	asm("mul.lo.u32 %0, %1, %2;" : "=r"(d) : "r"(a), "r"(b));
+	return d;
+}
+__device__ __forceinline__ uint32_t mul_hi_u32(uint32_t a, uint32_t b) {
+	uint32_t d;
+	asm("mul.hi.u32 %0, %1, %2;" : "=r"(d) : "r"(a), "r"(b));
+	return d;
+}
+__device__ __forceinline__ uint32_t sector_test_fma(uint64_t w, uint32_t hi) {
+	const uint32_t p0 = hi & 63u;
+	const uint32_t p1 = mul_hi_u32(mul_lo_u32(hi, 1u << 18), 64u);
+	const uint32_t p2 = mul_hi_u32(mul_lo_u32(hi, 1u << 10), 64u);
+	const uint32_t p3 = mul_hi_u32(mul_lo_u32(hi, 4u), 64u);
+	const uint32_t b = static_cast<uint32_t>(w >> p0) & static_cast<uint32_t>(w >> p1) & static_cast<uint32_t>(w >> p2) &
+	                   static_cast<uint32_t>(w >> p3);
+	return b & 1u;
+}
+
+// Lookup + test of N hashed keys; bit i of the result is the hit flag of h[i].
+template <int N, bool SMEM_FILTER, bool SLICED>
+__device__ __forceinline__ uint32_t test_batch(const uint64_t (&h)[N], const uint64_t *__restrict__ filter,
+                                               const uint64_t *s_filter, const uint32_t sector_mask,
+                                               const uint64_t pol_filter, const uint32_t slice_lo,
+                                               const uint32_t slice_len) {
+	uint64_t w[N];
+#pragma unroll
+	for (int i = 0; i < N; i++) { // all random filter loads of this thread, independent of each other
+		const uint32_t sector = static_cast<uint32_t>(h[i]) & sector_mask;
+		if (SMEM_FILTER) {
+			w[i] = s_filter[sector];
+		} else if (SLICED) {
+			w[i] = 0; // an all-zero word passes nothing
+			if (sector - slice_lo < slice_len) {
+				w[i] = ld_filter_word(filter + sector, pol_filter);
+			}
+		} else {
+			w[i] = ld_filter_word(filter + sector, pol_filter);
+		}
+	}
+	uint32_t hits = 0;
+#pragma unroll
+	for (int i = N - 1; i >= 0; i--) { // hits·2 + bit is one IMAD
+		hits = hits * 2u + sector_test_fma(w[i], static_cast<uint32_t>(h[i] >> 32));
+	}
+	return hits;
+}
+
+// UNITS = 16-byte units (key pairs) per batch: 8 → all 16 keys of a lane in flight at once, 4 → two batches of 8.
+template <class Src, int BLOCK, int MINB, int UNITS, bool SMEM_FILTER, bool SLICED>
+__global__ void __launch_bounds__(BLOCK, MINB)
+    probe_bitmap_kernel(const Src src, const uint64_t *__restrict__ filter, const uint32_t sector_mask,
+                        const uint64_t count, const uint64_t num_segs, const uint32_t slice_lo,
+                        const uint32_t slice_len, uint16_t *__restrict__ bitmap16, const int first_pass,
+                        uint32_t *__restrict__ seg_counts /* non-null on the last pass */) {
+	static_assert(UNITS == 8 || UNITS == 4, "a lane owns 8 units, processed in one or two batches");
 	constexpr int NWARPS = BLOCK / 32;
-	constexpr uint64_t WARP_KEYS = 64ull * ROUNDS;
-	constexpr uint64_t TILE_KEYS = WARP_KEYS * NWARPS;
-	constexpr bool STAGED = Src::kStageable && !SMEM_FILTER;
-	extern __shared__ __align__(16) uint64_t s_filter[];
-	__shared__ __align__(16) ulonglong2 s_keys[STAGED ? ROUNDS * BLOCK : 1];
+	constexpr bool STAGED = Src::kStageable;
+	constexpr int SEG_UNITS = kSegRows / 2; // 256 units of 16 bytes
+	// dynamic shared memory: [warp-private key double buffers (STAGED)][filter copy (SMEM_FILTER)]
+	extern __shared__ __align__(128) unsigned char s_dyn[];
+	ulonglong2 *const s_keys = reinterpret_cast<ulonglong2 *>(s_dyn);
+	uint64_t *const s_filter = reinterpret_cast<uint64_t *>(s_dyn + (STAGED ? NWARPS * 2 * SEG_UNITS * 16 : 0));
 	const uint32_t lane = threadIdx.x & 31u;
 	const uint32_t warp = threadIdx.x >> 5;
 	const uint64_t pol_keys = policy_evict_first();
@@ -371,74 +437,99 @@ __global__ void __launch_bounds__(BLOCK)
 		}
 		__syncthreads();
 	}
-	// thread-private staging slots: round r of this thread lives at s_keys[r·BLOCK + tid] (conflict-free 128-bit)
-	auto stage = [&](uint64_t tile) {
-		if (STAGED && tile < num_tiles && (tile + 1) * TILE_KEYS <= count) {
-			const uint64_t *g = src.key_ptr() + tile * TILE_KEYS + warp * WARP_KEYS + lane * 2;
-#pragma unroll
-			for (int r = 0; r < ROUNDS; r++) {
-				cp_async_16(&s_keys[r * BLOCK + threadIdx.x], g + r * 64, pol_keys);
-			}
-		}
-		cp_async_commit();
-	};
 	if (SLICED) {
 		warm_slice(filter, slice_lo, slice_len, BLOCK);
 	}
-	// Software pipeline with ONE staging call site: iteration i finishes tile `cur` (staged in iteration i-1) and
-	// stages tile `nxt`.  (A separate prologue call made ptxas 12.9 emit LDGSTS with unset uniform registers.)
+	const uint64_t stride = static_cast<uint64_t>(gridDim.x) * NWARPS;
+	const uint64_t full_segs = count / kSegRows; // segments below this one are complete
+	ulonglong2 *const my_buf = s_keys + warp * (2 * SEG_UNITS);
+	const uint32_t rot = lane & 7u;
+
+	// Software pipeline with ONE staging call site: iteration i finishes segment `cur` (staged in iteration
+	// i-1 into buffer `par`) and stages segment `nxt` into the other buffer.  (A separate prologue call made
+	// ptxas 12.9 emit LDGSTS with unset uniform registers.)
 	constexpr uint64_t kNone = ~0ULL;
 	uint64_t cur = kNone;
-	for (uint64_t nxt = blockIdx.x;; nxt += gridDim.x) {
-		uint64_t h[2 * ROUNDS];
-		uint32_t prior = 0;
-		uint16_t *slot = nullptr;
-		bool full_tile = false;
+	uint32_t par = 1;
+	for (uint64_t nxt = static_cast<uint64_t>(blockIdx.x) * NWARPS + warp;; nxt += stride) {
+		if (STAGED) {
+			__syncwarp(); // every lane is done reading the buffer that is overwritten next
+			if (nxt < full_segs) {
+				const ulonglong2 *g = reinterpret_cast<const ulonglong2 *>(src.key_ptr()) + nxt * SEG_UNITS + lane;
+				ulonglong2 *s = my_buf + (par ^ 1u) * SEG_UNITS + lane;
+#pragma unroll
+				for (int k = 0; k < 8; k++) {
+					cp_async_16(s + k * 32, g + k * 32, pol_keys);
+				}
+			}
+			cp_async_commit();
+		}
 		if (cur != kNone) {
-			full_tile = (cur + 1) * TILE_KEYS <= count;
-			slot = hitbits + cur * BLOCK + threadIdx.x;
+			uint16_t *slot = bitmap16 + cur * 32 + lane;
+			uint32_t prior = 0;
 			if (!first_pass) {
 				prior = *slot; // issued before the key / filter latency chain, consumed after it
 			}
-			if (STAGED && full_tile) {
-				cp_async_wait_all();
+			const uint64_t row0 = cur * kSegRows + lane * 16;
+			uint32_t hits = 0;
+			if (STAGED && cur < full_segs) {
+				cp_async_wait<1>();
+				__syncwarp();
+				const ulonglong2 *mine = my_buf + par * SEG_UNITS + lane * 8;
 #pragma unroll
-				for (int r = 0; r < ROUNDS; r++) {
-					const ulonglong2 k = s_keys[r * BLOCK + threadIdx.x];
-					h[2 * r] = murmur64(k.x);
-					h[2 * r + 1] = murmur64(k.y);
+				for (int b = 8 / UNITS - 1; b >= 0; b--) {
+					uint64_t h[2 * UNITS];
+#pragma unroll
+					for (int u = 0; u < UNITS; u++) {
+						const ulonglong2 k = mine[(b * UNITS + u + rot) & 7u];
+						h[2 * u] = murmur64(k.x);
+						h[2 * u + 1] = murmur64(k.y);
+					}
+					hits = (hits << (2 * UNITS)) |
+					       test_batch<2 * UNITS, SMEM_FILTER, SLICED>(h, filter, s_filter, sector_mask, pol_filter,
+					                                                  slice_lo, slice_len);
 				}
-			}
-		}
-		if (STAGED) {
-			stage(nxt); // the slots of `cur` were read above (same thread, program order)
-		}
-		if (cur != kNone) {
-			uint32_t hits;
-			if (STAGED && full_tile) {
-				hits = test_hashes<ROUNDS, SMEM_FILTER, SLICED>(h, filter, s_filter, sector_mask, pol_filter, slice_lo,
-				                                                slice_len);
+				// slot p held logical unit (p + rot) mod 8: rotate the 16-bit mask left by 2·rot
+				const uint32_t twice = hits | (hits << 16);
+				hits = (twice >> (16u - 2u * rot)) & 0xffffu;
 			} else {
-				hits = probe_tile<Src, ROUNDS, SMEM_FILTER, SLICED>(src, filter, s_filter, sector_mask, count,
-				                                                    cur * TILE_KEYS + warp * WARP_KEYS, full_tile, lane,
-				                                                    pol_keys, pol_filter, slice_lo, slice_len);
+				const bool full = cur < full_segs;
+#pragma unroll
+				for (int b = 8 / UNITS - 1; b >= 0; b--) {
+					uint64_t h[2 * UNITS];
+					uint32_t valid = 0;
+#pragma unroll
+					for (int i = 0; i < 2 * UNITS; i++) {
+						const uint64_t row = row0 + b * 2 * UNITS + i;
+						h[i] = 0;
+						if (full || row < count) {
+							h[i] = src.hash_at(row, pol_keys);
+							valid |= 1u << i;
+						}
+					}
+					hits = (hits << (2 * UNITS)) |
+					       (test_batch<2 * UNITS, SMEM_FILTER, SLICED>(h, filter, s_filter, sector_mask, pol_filter,
+					                                                   slice_lo, slice_len) &
+					        valid);
+				}
 			}
 			hits |= prior;
 			*slot = static_cast<uint16_t>(hits);
 			if (seg_counts) { // kernel-uniform
 				const uint32_t wc = __reduce_add_sync(0xffffffffu, __popc(hits));
 				if (lane == 0) {
-					seg_counts[cur * NWARPS + warp] = wc;
+					seg_counts[cur] = wc;
 				}
 			}
 		}
-		if (nxt >= num_tiles) {
+		if (nxt >= num_segs) {
 			break;
 		}
 		cur = nxt;
+		par ^= 1u;
 	}
 	if (STAGED) {
-		cp_async_wait_all();
+		cp_async_wait<0>();
 	}
 }
 
@@ -540,55 +631,56 @@ __global__ void __launch_bounds__(1024) scan_totals_kernel(uint32_t *__restrict_
 	}
 }
 
-// One warp per segment, UNROLL segments in flight per warp: ordered write of the survivors.  Row order inside a
-// segment is (round, lane, element), the mapping test_hashes used when it produced the hit bits.  The slot of
-// segment g (tile g / NWARPS, warp g % NWARPS) lane l is hitbits[g·32 + l] for every BLOCK.
-template <int ROUNDS>
+// Bitmap → ordered selection vector.  A warp takes chunks of 1024 rows (two segments, 32 bitmap words): every
+// lane owns one 32-bit word (32 consecutive rows), a warp scan of the popcounts places it, and the lane emits
+// its set bits in ascending order, so neighbouring lanes write neighbouring runs of sel_out.  UNROLL chunks are
+// loaded up front for memory-level parallelism.
 __global__ void __launch_bounds__(256)
-    compact_kernel(const uint16_t *__restrict__ hitbits, const uint32_t *__restrict__ seg_offsets,
-                   const uint32_t *__restrict__ block_offsets, const uint64_t num_segs, uint32_t *__restrict__ sel_out,
-                   const uint32_t row_offset, const uint32_t *__restrict__ translate) {
+    compact_bitmap_kernel(const uint32_t *__restrict__ bitmap32, const uint32_t *__restrict__ seg_offsets,
+                          const uint32_t *__restrict__ block_offsets, const uint64_t num_segs,
+                          uint32_t *__restrict__ sel_out, const uint32_t row_offset,
+                          const uint32_t *__restrict__ translate) {
 	constexpr int UNROLL = 4;
-	constexpr uint64_t SEG_KEYS = 64ull * ROUNDS;
 	const uint32_t lane = threadIdx.x & 31u;
-	const uint32_t lt = lanemask_lt();
+	const uint64_t num_chunks = (num_segs + 1) >> 1;
 	const uint64_t warp_global = (static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
 	const uint64_t num_warps = (static_cast<uint64_t>(gridDim.x) * blockDim.x) >> 5;
-	for (uint64_t g0 = warp_global * UNROLL; g0 < num_segs; g0 += num_warps * UNROLL) {
-		uint32_t hits[UNROLL], off[UNROLL];
+	for (uint64_t c0 = warp_global * UNROLL; c0 < num_chunks; c0 += num_warps * UNROLL) {
+		uint32_t word[UNROLL], off[UNROLL];
 #pragma unroll
 		for (int u = 0; u < UNROLL; u++) {
-			const uint64_t g = g0 + u;
-			hits[u] = 0;
+			const uint64_t c = c0 + u;
+			word[u] = 0;
 			off[u] = 0;
-			if (g < num_segs) {
-				hits[u] = hitbits[g * 32 + lane];
-				off[u] = __ldg(seg_offsets + g) + __ldg(block_offsets + g / kScanBlock);
+			// a chunk's second segment may not exist (odd num_segs): its words are not initialised
+			if (c < num_chunks && (2 * c + (lane >> 4)) < num_segs) {
+				word[u] = __ldg(bitmap32 + c * 32 + lane);
+			}
+			if (c < num_chunks) {
+				off[u] = __ldg(seg_offsets + 2 * c) + __ldg(block_offsets + (2 * c) / kScanBlock);
 			}
 		}
 #pragma unroll
 		for (int u = 0; u < UNROLL; u++) {
-			if (!__any_sync(0xffffffffu, hits[u] != 0)) {
+			uint32_t w = word[u];
+			if (!__any_sync(0xffffffffu, w != 0)) {
 				continue; // warp-uniform
 			}
-			uint32_t run = off[u];
-			const uint32_t rel_base = static_cast<uint32_t>((g0 + u) * SEG_KEYS) + row_offset + lane * 2;
+			const uint32_t cnt = __popc(w);
+			uint32_t incl = cnt;
 #pragma unroll
-			for (int r = 0; r < ROUNDS; r++) {
-				const uint32_t h0 = (hits[u] >> (2 * r)) & 1u;
-				const uint32_t h1 = (hits[u] >> (2 * r + 1)) & 1u;
-				const uint32_t b0 = __ballot_sync(0xffffffffu, h0);
-				const uint32_t b1 = __ballot_sync(0xffffffffu, h1);
-				uint32_t pos = run + __popc(b0 & lt) + __popc(b1 & lt);
-				const uint32_t rel = rel_base + r * 64;
-				if (h0) {
-					sel_out[pos] = translate ? __ldg(translate + rel) : rel;
+			for (int d = 1; d < 32; d <<= 1) {
+				const uint32_t t = __shfl_up_sync(0xffffffffu, incl, d);
+				if (lane >= static_cast<uint32_t>(d)) {
+					incl += t;
 				}
-				pos += h0;
-				if (h1) {
-					sel_out[pos] = translate ? __ldg(translate + rel + 1) : rel + 1;
-				}
-				run += __popc(b0) + __popc(b1);
+			}
+			uint32_t pos = off[u] + incl - cnt;
+			const uint32_t row_base = static_cast<uint32_t>((c0 + u) * 1024) + lane * 32 + row_offset;
+			while (w) {
+				const uint32_t row = row_base + (__ffs(w) - 1);
+				sel_out[pos++] = translate ? __ldg(translate + row) : row;
+				w &= w - 1;
 			}
 		}
 	}
@@ -799,7 +891,8 @@ static inline bool is_flat_u64(const DevCols &cols) {
 }
 
 static inline bool use_smem_filter(const DeviceInfo &dev, uint64_t num_sectors) {
-	return num_sectors <= kSmemFilterMaxSectors && num_sectors * 8 + 1024 <= dev.smem_optin;
+	// the phased kernel also keeps 64 KiB of key double buffers in shared memory
+	return num_sectors <= kSmemFilterMaxSectors && num_sectors * 8 + 65536 + 1024 <= dev.smem_optin;
 }
 
 // Sector-range slicing (see the build section): filters above the threshold are processed in passes of
@@ -823,15 +916,15 @@ static inline uint64_t align_up(uint64_t v, uint64_t a) {
 	return (v + a - 1) / a * a;
 }
 
-// Scratch layout of a phased probe: [segment offsets u32 × cap][block totals u32 × blocks][hit bits u16 × cap·32]
+// Scratch layout of a phased probe: [segment offsets u32 × cap][block totals u32 × blocks][row bitmap, 64 B × cap]
 struct PhasedLayout {
-	uint64_t seg_cap;    // segments (64·ROUNDS rows each), with slack for the last partial tile of either block size
+	uint64_t seg_cap;    // segments (512 rows each), with slack so that the last compaction chunk stays in bounds
 	uint64_t block_cap;  // scan blocks of kScanBlock segments
 	size_t off_totals, off_hitbits, bytes;
 };
 static PhasedLayout phased_layout(uint64_t count) {
 	PhasedLayout l;
-	l.seg_cap = ceil_div(count, 64ull * kProbeRounds) + 32;
+	l.seg_cap = ceil_div(count, kSegRows) + 32;
 	l.block_cap = ceil_div(l.seg_cap, kScanBlock);
 	l.off_totals = align_up(l.seg_cap * sizeof(uint32_t), 256);
 	l.off_hitbits = l.off_totals + align_up(l.block_cap * sizeof(uint32_t), 256);
@@ -935,23 +1028,21 @@ static cudaError_t launch_probe_fused(const DeviceInfo &dev, const Src &src, uin
 	return cudaGetLastError();
 }
 
-// Large probes: pass kernel per sector-range slice → two-level scan of segment counts → compaction.
-template <class Src, int BLOCK, bool SMEM, bool SLICED>
+// Large probes: bitmap pass kernel per sector-range slice → two-level scan of segment counts → compaction.
+// UNITS/MINB: 16 keys in flight per lane at 2 CTAs/SM, or 8 keys in flight at 3 CTAs/SM (RPT_PROBE_UNITS=8|4).
+template <class Src, int UNITS, int MINB, bool SMEM, bool SLICED>
 static cudaError_t launch_probe_phased(const DeviceInfo &dev, const Src &src, uint64_t count, const uint64_t *words,
                                        uint64_t num_sectors, uint32_t *sel_out, uint64_t *found_out,
                                        uint32_t row_offset, const uint32_t *translate, void *scratch,
                                        cudaStream_t stream, int *launches) {
-	auto pass = probe_pass_kernel<Src, kProbeRounds, BLOCK, SMEM, SLICED>;
-	const uint64_t tile_keys = 64ull * kProbeRounds * (BLOCK / 32);
-	const uint64_t num_tiles = ceil_div(count, tile_keys);
-	const uint64_t num_segs = num_tiles * (BLOCK / 32);
-	const size_t smem = SMEM ? num_sectors * sizeof(uint64_t) : 0;
-	cudaError_t e;
-	if (SMEM) {
-		e = cudaFuncSetAttribute(pass, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
-		if (e != cudaSuccess) {
-			return e;
-		}
+	constexpr int BLOCK = kProbeBlock;
+	auto pass = probe_bitmap_kernel<Src, BLOCK, MINB, UNITS, SMEM, SLICED>;
+	const uint64_t num_segs = ceil_div(count, kSegRows);
+	const size_t smem = (Src::kStageable ? static_cast<size_t>(BLOCK / 32) * 2 * kSegRows * 8 : 0) +
+	                    (SMEM ? num_sectors * sizeof(uint64_t) : 0);
+	cudaError_t e = cudaFuncSetAttribute(pass, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
+	if (e != cudaSuccess) {
+		return e;
 	}
 	int per_sm = 0;
 	e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, pass, BLOCK, smem);
@@ -961,23 +1052,24 @@ static cudaError_t launch_probe_phased(const DeviceInfo &dev, const Src &src, ui
 	if (per_sm < 1) {
 		return cudaErrorLaunchOutOfResources;
 	}
-	uint64_t grid = static_cast<uint64_t>(dev.sm_count) * per_sm;
-	if (grid > num_tiles) {
-		grid = num_tiles;
+	uint64_t grid = static_cast<uint64_t>(dev.sm_count) * per_sm; // persistent warps, a multiple of the SM count
+	const uint64_t want = ceil_div(num_segs, BLOCK / 32);
+	if (grid > want) {
+		grid = want;
 	}
 	const PhasedLayout lay = phased_layout(count);
 	char *base = reinterpret_cast<char *>(scratch);
 	uint32_t *seg_offsets = reinterpret_cast<uint32_t *>(base);
 	uint32_t *block_totals = reinterpret_cast<uint32_t *>(base + lay.off_totals);
-	uint16_t *hitbits = reinterpret_cast<uint16_t *>(base + lay.off_hitbits);
+	uint16_t *bitmap = reinterpret_cast<uint16_t *>(base + lay.off_hitbits);
 	const uint32_t sector_mask = static_cast<uint32_t>(num_sectors - 1);
 	const uint64_t slice = SLICED ? slice_sectors_for(num_sectors) : num_sectors;
 	for (uint64_t lo = 0; lo < num_sectors; lo += slice) {
 		const uint64_t len = lo + slice < num_sectors ? slice : num_sectors - lo;
 		const bool last = lo + slice >= num_sectors;
-		pass<<<static_cast<unsigned>(grid), BLOCK, smem, stream>>>(src, words, sector_mask, count, num_tiles,
+		pass<<<static_cast<unsigned>(grid), BLOCK, smem, stream>>>(src, words, sector_mask, count, num_segs,
 		                                                          static_cast<uint32_t>(lo), static_cast<uint32_t>(len),
-		                                                          hitbits, lo == 0 ? 1 : 0, last ? seg_offsets : nullptr);
+		                                                          bitmap, lo == 0 ? 1 : 0, last ? seg_offsets : nullptr);
 		if (launches) {
 			(*launches)++;
 		}
@@ -985,14 +1077,22 @@ static cudaError_t launch_probe_phased(const DeviceInfo &dev, const Src &src, ui
 	const uint64_t nblocks = ceil_div(num_segs, kScanBlock);
 	scan_blocks_kernel<<<static_cast<unsigned>(nblocks), 1024, 0, stream>>>(seg_offsets, num_segs, block_totals);
 	scan_totals_kernel<<<1, 1024, 0, stream>>>(block_totals, static_cast<uint32_t>(nblocks), found_out);
-	const uint64_t want = ceil_div(num_segs, 8ull * 4); // 8 warps per CTA, 4 segments per warp iteration
-	const uint64_t cap = static_cast<uint64_t>(dev.sm_count) * 8 * 4;
-	compact_kernel<kProbeRounds><<<static_cast<unsigned>(want < cap ? want : cap), 256, 0, stream>>>(
-	    hitbits, seg_offsets, block_totals, num_segs, sel_out, row_offset, translate);
+	const uint64_t cwant = ceil_div((num_segs + 1) / 2, 8ull * 4); // 8 warps per CTA, 4 chunks per warp iteration
+	const uint64_t ccap = static_cast<uint64_t>(dev.sm_count) * 8 * 4;
+	compact_bitmap_kernel<<<static_cast<unsigned>(cwant < ccap ? cwant : ccap), 256, 0, stream>>>(
+	    reinterpret_cast<const uint32_t *>(bitmap), seg_offsets, block_totals, num_segs, sel_out, row_offset, translate);
 	if (launches) {
 		(*launches) += 3;
 	}
 	return cudaGetLastError();
+}
+
+static int probe_units() {
+	static const int units = [] {
+		const char *e = getenv("RPT_PROBE_UNITS");
+		return e && atoi(e) == 4 ? 4 : 8;
+	}();
+	return units;
 }
 
 template <class Src>
@@ -1005,13 +1105,17 @@ static cudaError_t launch_probe_src(const DeviceInfo &dev, const Src &src, uint6
 		return smem ? launch_probe_fused<Src, kProbeBlockSmem, true>(RPT_PROBE_ARGS)
 		            : launch_probe_fused<Src, kProbeBlock, false>(RPT_PROBE_ARGS);
 	}
+	const bool wide = probe_units() == 8;
 	if (smem) {
-		return launch_probe_phased<Src, kProbeBlockSmem, true, false>(RPT_PROBE_ARGS);
+		return wide ? launch_probe_phased<Src, 8, 1, true, false>(RPT_PROBE_ARGS)
+		            : launch_probe_phased<Src, 4, 1, true, false>(RPT_PROBE_ARGS);
 	}
 	if (slice_sectors_for(num_sectors) < num_sectors) {
-		return launch_probe_phased<Src, kProbeBlock, false, true>(RPT_PROBE_ARGS);
+		return wide ? launch_probe_phased<Src, 8, 2, false, true>(RPT_PROBE_ARGS)
+		            : launch_probe_phased<Src, 4, 3, false, true>(RPT_PROBE_ARGS);
 	}
-	return launch_probe_phased<Src, kProbeBlock, false, false>(RPT_PROBE_ARGS);
+	return wide ? launch_probe_phased<Src, 8, 2, false, false>(RPT_PROBE_ARGS)
+	            : launch_probe_phased<Src, 4, 3, false, false>(RPT_PROBE_ARGS);
 #undef RPT_PROBE_ARGS
 }
 
