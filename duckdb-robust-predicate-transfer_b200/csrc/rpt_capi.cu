@@ -10,7 +10,9 @@
 #include <atomic>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
+#include <ctime>
 #include <mutex>
 #include <string>
 #include <vector>
@@ -94,7 +96,20 @@ struct rpt_bf {
 	uint64_t sized_for_rows = 0;
 	uint64_t *words = nullptr;
 	cudaStream_t stream = nullptr;     // handle's own stream
-	cudaStream_t pipe[2] = {nullptr, nullptr}; // host-column pipelines
+	// host-column pipeline (RPT_MEM_HOST calls): uploads, kernels and downloads run on three streams chained by
+	// events, with kPipeSlots chunks in flight; everything here is created once per handle and reused
+	static constexpr int kPipeSlots = 3;
+	struct PipeSlot {
+		uint32_t *dsel = nullptr;   // device selection vector of one chunk (probe)
+		uint64_t sel_cap = 0;       // its capacity in rows
+		uint64_t *dfound = nullptr; // device survivor count
+		uint64_t *hfound = nullptr; // pinned host copy of it
+		cudaEvent_t uploaded = nullptr, computed = nullptr, drained = nullptr;
+		bool pending = false;
+	};
+	std::mutex pipe_mu; // host-column calls on one handle take turns (device-column calls never touch the pipeline)
+	cudaStream_t h2d = nullptr, compute = nullptr, d2h = nullptr;
+	PipeSlot slot[kPipeSlots];
 	std::atomic<int> has_data {0};
 	std::atomic<int> finalized {0};
 	std::atomic<long long> launches {0};
@@ -205,11 +220,12 @@ static int validate_cols(const rpt_col_t *cols, int ncols, uint64_t count, int *
 // staging of key columns: rpt_col_t (host or device) → DevCols (device pointers)
 // ---------------------------------------------------------------------------------------------
 struct Staged {
-	cudaStream_t stream = nullptr;
+	cudaStream_t stream = nullptr;      // allocations and uploads are ordered on this stream
+	cudaStream_t free_stream = nullptr; // releases are ordered on this one (the consumer); default = stream
 	std::vector<void *> dev_allocs;
 	~Staged() {
 		for (void *p : dev_allocs) {
-			cudaFreeAsync(p, stream);
+			cudaFreeAsync(p, free_stream ? free_stream : stream);
 		}
 	}
 	int alloc(void **out, size_t bytes) {
@@ -229,6 +245,25 @@ struct Staged {
 // Rows of a chunked host upload start at multiples of this (validity words and 128-bit key loads
 // stay aligned; a multiple of every probe tile size).
 static constexpr uint64_t kChunkRows = 1ULL << 24;
+// RPT_CHUNK_ROWS overrides the chunk size (rounded down to a multiple of 4096) for experiments.
+static uint64_t chunk_rows() {
+	static const uint64_t rows = [] {
+		const char *e = getenv("RPT_CHUNK_ROWS");
+		const uint64_t v = e ? strtoull(e, nullptr, 10) & ~4095ULL : 0;
+		return v ? v : kChunkRows;
+	}();
+	return rows;
+}
+// RPT_TRACE=1 prints host-side wall times of the host-column pipelines to stderr.
+static bool trace_on() {
+	static const bool on = getenv("RPT_TRACE") != nullptr;
+	return on;
+}
+static double now_ms() {
+	timespec ts;
+	clock_gettime(CLOCK_MONOTONIC, &ts);
+	return ts.tv_sec * 1e3 + ts.tv_nsec * 1e-6;
+}
 
 static void device_cols_view(const rpt_col_t *cols, int ncols, DevCols *out) {
 	memset(out, 0, sizeof(*out));
@@ -429,8 +464,16 @@ int rpt_bf_create(rpt_bf_t **out, uint64_t est_rows, int device) {
 		} else {
 			auto make = [&]() -> int {
 				RPT_CUDA(cudaStreamCreateWithFlags(&bf->stream, cudaStreamNonBlocking));
-				RPT_CUDA(cudaStreamCreateWithFlags(&bf->pipe[0], cudaStreamNonBlocking));
-				RPT_CUDA(cudaStreamCreateWithFlags(&bf->pipe[1], cudaStreamNonBlocking));
+				RPT_CUDA(cudaStreamCreateWithFlags(&bf->h2d, cudaStreamNonBlocking));
+				RPT_CUDA(cudaStreamCreateWithFlags(&bf->compute, cudaStreamNonBlocking));
+				RPT_CUDA(cudaStreamCreateWithFlags(&bf->d2h, cudaStreamNonBlocking));
+				for (auto &sl : bf->slot) {
+					RPT_CUDA(cudaEventCreateWithFlags(&sl.uploaded, cudaEventDisableTiming));
+					RPT_CUDA(cudaEventCreateWithFlags(&sl.computed, cudaEventDisableTiming));
+					RPT_CUDA(cudaEventCreateWithFlags(&sl.drained, cudaEventDisableTiming));
+					RPT_CUDA(cudaMalloc(&sl.dfound, sizeof(uint64_t)));
+					RPT_CUDA(cudaMallocHost(&sl.hfound, sizeof(uint64_t)));
+				}
 				return allocate_words(bf, est_rows);
 			};
 			rc = make();
@@ -453,9 +496,26 @@ int rpt_bf_destroy(rpt_bf_t *bf) {
 	if (bf->words) {
 		cudaFree(bf->words);
 	}
-	for (cudaStream_t s : {bf->stream, bf->pipe[0], bf->pipe[1]}) {
+	for (cudaStream_t s : {bf->stream, bf->h2d, bf->compute, bf->d2h}) {
 		if (s) {
+			cudaStreamSynchronize(s);
 			cudaStreamDestroy(s);
+		}
+	}
+	for (auto &sl : bf->slot) {
+		for (cudaEvent_t ev : {sl.uploaded, sl.computed, sl.drained}) {
+			if (ev) {
+				cudaEventDestroy(ev);
+			}
+		}
+		if (sl.dsel) {
+			cudaFree(sl.dsel);
+		}
+		if (sl.dfound) {
+			cudaFree(sl.dfound);
+		}
+		if (sl.hfound) {
+			cudaFreeHost(sl.hfound);
 		}
 	}
 	delete bf;
@@ -520,8 +580,9 @@ int rpt_bf_sync(const rpt_bf_t *bf) {
 	}
 	RPT_GUARD(bf);
 	RPT_CUDA(cudaStreamSynchronize(bf->stream));
-	RPT_CUDA(cudaStreamSynchronize(bf->pipe[0]));
-	RPT_CUDA(cudaStreamSynchronize(bf->pipe[1]));
+	RPT_CUDA(cudaStreamSynchronize(bf->h2d));
+	RPT_CUDA(cudaStreamSynchronize(bf->compute));
+	RPT_CUDA(cudaStreamSynchronize(bf->d2h));
 	return 0;
 }
 
@@ -543,24 +604,40 @@ static int insert_impl(rpt_bf *bf, const rpt_col_t *cols, int ncols, uint64_t co
 		bf->launches += launches;
 		return 0;
 	}
-	// host columns: chunked upload on two alternating streams so that the copy of chunk c+1
-	// overlaps the insert kernel of chunk c; all chunks OR into the same words
+	// host columns: chunk c is uploaded on the h2d stream while the insert kernel of chunk c-1 runs on the
+	// compute stream (chained by events); at most kPipeSlots chunks are in flight; all chunks OR into the
+	// same words
+	std::lock_guard<std::mutex> lock(bf->pipe_mu);
+	const double t0 = trace_on() ? now_ms() : 0;
 	if (stream_in) {
 		RPT_CUDA(cudaStreamSynchronize(reinterpret_cast<cudaStream_t>(stream_in)));
+	} else {
+		RPT_CUDA(cudaStreamSynchronize(bf->stream)); // a zero-fill enqueued by rpt_bf_reset(NULL stream)
 	}
-	const uint64_t chunk = any_sel(cols, ncols) ? count : kChunkRows;
-	int idx = 0;
-	for (uint64_t r0 = 0; r0 < count; r0 += chunk, idx ^= 1) {
+	const uint64_t chunk = any_sel(cols, ncols) ? count : chunk_rows();
+	uint64_t c = 0;
+	for (uint64_t r0 = 0; r0 < count; r0 += chunk, c++) {
 		const uint64_t r1 = r0 + chunk < count ? r0 + chunk : count;
+		rpt_bf::PipeSlot &sl = bf->slot[c % rpt_bf::kPipeSlots];
+		if (c >= static_cast<uint64_t>(rpt_bf::kPipeSlots)) {
+			RPT_CUDA(cudaEventSynchronize(sl.computed)); // bounds the staging memory in flight
+		}
 		Staged st;
-		st.stream = bf->pipe[idx];
+		st.stream = bf->h2d;
+		st.free_stream = bf->compute;
 		DevCols dc;
 		RPT_TRY(stage_host_cols(cols, ncols, r0, r1, &st, &dc));
-		RPT_CUDA(launch_build(bf->dev, dc, r1 - r0, bf->words, bf->num_sectors, st.stream, &launches));
+		RPT_CUDA(cudaEventRecord(sl.uploaded, bf->h2d));
+		RPT_CUDA(cudaStreamWaitEvent(bf->compute, sl.uploaded, 0));
+		RPT_CUDA(launch_build(bf->dev, dc, r1 - r0, bf->words, bf->num_sectors, bf->compute, &launches));
+		RPT_CUDA(cudaEventRecord(sl.computed, bf->compute));
 	}
 	bf->launches += launches;
-	RPT_CUDA(cudaStreamSynchronize(bf->pipe[0]));
-	RPT_CUDA(cudaStreamSynchronize(bf->pipe[1]));
+	RPT_CUDA(cudaStreamSynchronize(bf->compute));
+	if (trace_on()) {
+		fprintf(stderr, "[rpt trace] insert host: %llu rows, %llu chunk(s), %.3f ms\n", (unsigned long long)count,
+		        (unsigned long long)c, now_ms() - t0);
+	}
 	return 0;
 }
 
@@ -686,92 +763,99 @@ static int probe_impl(const rpt_bf *bf, const rpt_col_t *cols, int ncols, uint64
 		return 0;
 	}
 
-	// host columns → host outputs: chunks alternate between two streams; chunk c's survivors are
-	// copied back (its count is known one step later) while chunk c+1 uploads and runs
+	// host columns → host outputs.  Three streams chained by events: chunk c uploads on h2d while chunk c-1 is
+	// probed on compute and the survivors of chunk c-2 go out on d2h.  The host only learns a chunk's survivor
+	// count two chunks later, so two uploads are always queued behind the one in flight and the H2D copy
+	// engine never idles; `total` advances in chunk order, which keeps the selection vector ordered.
+	std::lock_guard<std::mutex> lock(mbf->pipe_mu);
+	const double t0 = trace_on() ? now_ms() : 0;
 	if (stream_in) {
 		RPT_CUDA(cudaStreamSynchronize(reinterpret_cast<cudaStream_t>(stream_in)));
+	} else {
+		RPT_CUDA(cudaStreamSynchronize(bf->stream));
 	}
 	*found_out = 0;
 	if (count == 0) {
 		return 0;
 	}
-	const uint64_t chunk = any_sel(cols, ncols) ? count : kChunkRows;
+	constexpr int kSlots = rpt_bf::kPipeSlots;
+	const uint64_t chunk = any_sel(cols, ncols) ? count : chunk_rows();
 	const uint64_t cap = chunk < count ? chunk : count;
-	struct Slot {
-		uint32_t *dsel = nullptr;
-		uint64_t *dfound = nullptr;
-		uint64_t *hfound = nullptr;
-		cudaEvent_t done = nullptr;
-		bool pending = false;
-	} slot[2];
-	uint64_t total = 0;
-	auto cleanup = [&]() {
-		for (int i = 0; i < 2; i++) {
-			cudaStreamSynchronize(bf->pipe[i]);
-			if (slot[i].dsel) {
-				cudaFree(slot[i].dsel);
+	for (auto &sl : mbf->slot) { // grow-only device selection buffers, kept for the next call
+		if (sl.sel_cap < cap) {
+			if (sl.dsel) {
+				RPT_CUDA(cudaFree(sl.dsel));
+				sl.dsel = nullptr;
+				sl.sel_cap = 0;
 			}
-			if (slot[i].dfound) {
-				cudaFree(slot[i].dfound);
-			}
-			if (slot[i].hfound) {
-				cudaFreeHost(slot[i].hfound);
-			}
-			if (slot[i].done) {
-				cudaEventDestroy(slot[i].done);
-			}
+			RPT_CUDA(cudaMalloc(&sl.dsel, cap * sizeof(uint32_t)));
+			sl.sel_cap = cap;
 		}
-	};
-	auto drain = [&](int i) -> int { // chunk in slot i finished its kernel → copy its survivors out
-		if (!slot[i].pending) {
+		sl.pending = false;
+		if (chunk >= count) {
+			break; // a single chunk uses slot 0 only
+		}
+	}
+	uint64_t total = 0;
+	auto drain = [&](uint64_t c) -> int { // chunk c's kernel finished → send its survivors out
+		rpt_bf::PipeSlot &sl = mbf->slot[c % kSlots];
+		if (!sl.pending) {
 			return 0;
 		}
-		RPT_CUDA(cudaEventSynchronize(slot[i].done));
-		const uint64_t f = *slot[i].hfound;
+		RPT_CUDA(cudaEventSynchronize(sl.computed));
+		const uint64_t f = *sl.hfound;
 		if (f) {
-			RPT_CUDA(cudaMemcpyAsync(sel_out + total, slot[i].dsel, f * sizeof(uint32_t), cudaMemcpyDeviceToHost,
-			                         bf->pipe[i]));
+			RPT_CUDA(cudaMemcpyAsync(sel_out + total, sl.dsel, f * sizeof(uint32_t), cudaMemcpyDeviceToHost, mbf->d2h));
 		}
+		RPT_CUDA(cudaEventRecord(sl.drained, mbf->d2h));
 		total += f;
-		slot[i].pending = false;
+		sl.pending = false;
 		return 0;
 	};
 	auto run = [&]() -> int {
-		const int nslots = chunk < count ? 2 : 1;
-		for (int i = 0; i < nslots; i++) {
-			RPT_CUDA(cudaMalloc(&slot[i].dsel, cap * sizeof(uint32_t)));
-			RPT_CUDA(cudaMalloc(&slot[i].dfound, sizeof(uint64_t)));
-			RPT_CUDA(cudaMallocHost(&slot[i].hfound, sizeof(uint64_t)));
-			RPT_CUDA(cudaEventCreateWithFlags(&slot[i].done, cudaEventDisableTiming));
-		}
-		int idx = 0;
-		for (uint64_t r0 = 0; r0 < count; r0 += chunk, idx ^= 1) {
+		uint64_t c = 0;
+		for (uint64_t r0 = 0; r0 < count; r0 += chunk, c++) {
 			const uint64_t r1 = r0 + chunk < count ? r0 + chunk : count;
-			RPT_TRY(drain(idx)); // slot reuse: chunk c-2's survivors must be on their way out first
+			rpt_bf::PipeSlot &sl = mbf->slot[c % kSlots];
 			Staged st;
-			st.stream = bf->pipe[idx];
+			st.stream = mbf->h2d;
+			st.free_stream = mbf->compute;
 			DevCols dc;
 			RPT_TRY(stage_host_cols(cols, ncols, r0, r1, &st, &dc));
 			void *scratch;
 			RPT_TRY(st.alloc(&scratch, probe_scratch_bytes(r1 - r0, bf->num_sectors)));
+			RPT_CUDA(cudaEventRecord(sl.uploaded, mbf->h2d));
+			RPT_CUDA(cudaStreamWaitEvent(mbf->compute, sl.uploaded, 0));
+			RPT_CUDA(cudaStreamWaitEvent(mbf->compute, sl.drained, 0)); // dsel of chunk c-3 has left the device
 			const uint32_t *translate = translate_col0 ? dc.c[0].sel : nullptr;
-			RPT_CUDA(launch_probe(bf->dev, dc, r1 - r0, bf->words, bf->num_sectors, slot[idx].dsel, slot[idx].dfound,
-			                      static_cast<uint32_t>(r0), translate, scratch, st.stream, &launches));
-			RPT_CUDA(cudaMemcpyAsync(slot[idx].hfound, slot[idx].dfound, sizeof(uint64_t), cudaMemcpyDeviceToHost,
-			                         st.stream));
-			RPT_CUDA(cudaEventRecord(slot[idx].done, st.stream));
-			slot[idx].pending = true;
-			RPT_TRY(drain(idx ^ 1)); // previous chunk: in row order, so `total` stays ordered
+			RPT_CUDA(launch_probe(bf->dev, dc, r1 - r0, bf->words, bf->num_sectors, sl.dsel, sl.dfound,
+			                      static_cast<uint32_t>(r0), translate, scratch, mbf->compute, &launches));
+			RPT_CUDA(cudaMemcpyAsync(sl.hfound, sl.dfound, sizeof(uint64_t), cudaMemcpyDeviceToHost, mbf->compute));
+			RPT_CUDA(cudaEventRecord(sl.computed, mbf->compute));
+			sl.pending = true;
+			if (c >= static_cast<uint64_t>(kSlots - 1)) {
+				RPT_TRY(drain(c - (kSlots - 1))); // frees the slot the next chunk will use
+			}
 		}
-		// the loop drained every chunk but the last one issued
-		RPT_TRY(drain(idx ^ 1));
-		RPT_TRY(drain(idx));
-		RPT_CUDA(cudaStreamSynchronize(bf->pipe[0]));
-		RPT_CUDA(cudaStreamSynchronize(bf->pipe[1]));
+		for (uint64_t d = c >= static_cast<uint64_t>(kSlots - 1) ? c - (kSlots - 1) : 0; d < c; d++) {
+			RPT_TRY(drain(d));
+		}
+		RPT_CUDA(cudaStreamSynchronize(mbf->d2h));
+		if (trace_on()) {
+			fprintf(stderr, "[rpt trace] probe host: %llu rows, %llu chunk(s), found %llu, %.3f ms\n",
+			        (unsigned long long)count, (unsigned long long)c, (unsigned long long)total, now_ms() - t0);
+		}
 		return 0;
 	};
 	const int rc = run();
-	cleanup();
+	if (rc != 0) { // leave the pipeline idle so that the handle stays usable
+		cudaStreamSynchronize(mbf->h2d);
+		cudaStreamSynchronize(mbf->compute);
+		cudaStreamSynchronize(mbf->d2h);
+		for (auto &sl : mbf->slot) {
+			sl.pending = false;
+		}
+	}
 	mbf->launches += launches;
 	if (rc == 0) {
 		*found_out = total;

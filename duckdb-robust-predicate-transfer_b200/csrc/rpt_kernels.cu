@@ -631,17 +631,19 @@ __global__ void __launch_bounds__(1024) scan_totals_kernel(uint32_t *__restrict_
 	}
 }
 
-// Bitmap → ordered selection vector.  A warp takes chunks of 1024 rows (two segments, 32 bitmap words): every
-// lane owns one 32-bit word (32 consecutive rows), a warp scan of the popcounts places it, and the lane emits
-// its set bits in ascending order, so neighbouring lanes write neighbouring runs of sel_out.  UNROLL chunks are
-// loaded up front for memory-level parallelism.
+// Bitmap → ordered selection vector.  A warp takes chunks of 1024 rows (two segments, 32 bitmap words, one per
+// lane).  Word j of the chunk is broadcast to the warp; lane i stands for row 32·j + i and the survivors of the
+// word are written by ONE store instruction to consecutive addresses (rank inside the word = popcount of the
+// lower lanes), so the selection vector leaves the SM as contiguous runs, never as per-lane scattered stores
+// (a scattered 4-byte store costs an LSU tag cycle per lane: measured 2.6 ms extra at 50 % selectivity).
 __global__ void __launch_bounds__(256)
     compact_bitmap_kernel(const uint32_t *__restrict__ bitmap32, const uint32_t *__restrict__ seg_offsets,
                           const uint32_t *__restrict__ block_offsets, const uint64_t num_segs,
                           uint32_t *__restrict__ sel_out, const uint32_t row_offset,
                           const uint32_t *__restrict__ translate) {
-	constexpr int UNROLL = 4;
+	constexpr int UNROLL = 2;
 	const uint32_t lane = threadIdx.x & 31u;
+	const uint32_t lt = lanemask_lt();
 	const uint64_t num_chunks = (num_segs + 1) >> 1;
 	const uint64_t warp_global = (static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
 	const uint64_t num_warps = (static_cast<uint64_t>(gridDim.x) * blockDim.x) >> 5;
@@ -662,25 +664,18 @@ __global__ void __launch_bounds__(256)
 		}
 #pragma unroll
 		for (int u = 0; u < UNROLL; u++) {
-			uint32_t w = word[u];
-			if (!__any_sync(0xffffffffu, w != 0)) {
-				continue; // warp-uniform
-			}
-			const uint32_t cnt = __popc(w);
-			uint32_t incl = cnt;
-#pragma unroll
-			for (int d = 1; d < 32; d <<= 1) {
-				const uint32_t t = __shfl_up_sync(0xffffffffu, incl, d);
-				if (lane >= static_cast<uint32_t>(d)) {
-					incl += t;
+			uint32_t live = __ballot_sync(0xffffffffu, word[u] != 0); // which words of the chunk have survivors
+			uint32_t run = off[u];
+			const uint32_t row_base = static_cast<uint32_t>((c0 + u) * 1024) + row_offset + lane;
+			while (live) { // warp-uniform
+				const int j = __ffs(live) - 1;
+				live &= live - 1;
+				const uint32_t w = __shfl_sync(0xffffffffu, word[u], j);
+				if ((w >> lane) & 1u) {
+					const uint32_t row = row_base + static_cast<uint32_t>(j) * 32u;
+					sel_out[run + __popc(w & lt)] = translate ? __ldg(translate + row) : row;
 				}
-			}
-			uint32_t pos = off[u] + incl - cnt;
-			const uint32_t row_base = static_cast<uint32_t>((c0 + u) * 1024) + lane * 32 + row_offset;
-			while (w) {
-				const uint32_t row = row_base + (__ffs(w) - 1);
-				sel_out[pos++] = translate ? __ldg(translate + row) : row;
-				w &= w - 1;
+				run += __popc(w);
 			}
 		}
 	}
@@ -1077,7 +1072,7 @@ static cudaError_t launch_probe_phased(const DeviceInfo &dev, const Src &src, ui
 	const uint64_t nblocks = ceil_div(num_segs, kScanBlock);
 	scan_blocks_kernel<<<static_cast<unsigned>(nblocks), 1024, 0, stream>>>(seg_offsets, num_segs, block_totals);
 	scan_totals_kernel<<<1, 1024, 0, stream>>>(block_totals, static_cast<uint32_t>(nblocks), found_out);
-	const uint64_t cwant = ceil_div((num_segs + 1) / 2, 8ull * 4); // 8 warps per CTA, 4 chunks per warp iteration
+	const uint64_t cwant = ceil_div((num_segs + 1) / 2, 8ull * 2); // 8 warps per CTA, 2 chunks per warp iteration
 	const uint64_t ccap = static_cast<uint64_t>(dev.sm_count) * 8 * 4;
 	compact_bitmap_kernel<<<static_cast<unsigned>(cwant < ccap ? cwant : ccap), 256, 0, stream>>>(
 	    reinterpret_cast<const uint32_t *>(bitmap), seg_offsets, block_totals, num_segs, sel_out, row_offset, translate);
