@@ -10,8 +10,8 @@ filters over NVLink), probe the probe column into a compacted, ordered selection
           CUDA-event timed, max over ranks.
   e2e     the same step through the C ABI with HOST (pinned) key buffers and host selection-vector output:
           H2D and D2H copies inside the timed region.
-  roofline  the probe kernel (dominant): algorithmic bytes 8·m + 4·found + F per launch ÷ its CUDA-event duration,
-          against MEASURED_PEAKS.json's HBM copy bandwidth.
+  roofline  the probe (dominant; all launches of one rpt_bf_probe call): algorithmic bytes 8·m + 4·found + F ÷ the
+          CUDA-event duration of the call, against MEASURED_PEAKS.json's HBM copy bandwidth.
   cpu_baseline  the reference's own loops (oracle/_ref, compiled from the reference sources) or the C oracle port,
           on the box's host cores, bounded sample (N=1, rank 0 only).
 N>1 (torchrun, one rank per GPU): the 100M-row build column is sharded by row range across ranks (each builds a
@@ -35,6 +35,7 @@ sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 METRIC = "bloom build+probe throughput (build 100M int64 keys, probe 1B int64 keys per GPU)"
 UNIT = "Gkeys/s"
+_REAL_STDOUT = sys.stdout
 
 
 def parse_args():
@@ -172,7 +173,8 @@ def run_reference(args):
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line))
+    _REAL_STDOUT.write(json.dumps(line) + "\n")
+    _REAL_STDOUT.flush()
     return 0
 
 
@@ -307,7 +309,8 @@ def run_b200(args):
     peak, peak_src = load_peaks()
     algo_bytes = 8 * m + 4 * found + F
     achieved = algo_bytes / (probe_ms * 1e-3) / 1e9
-    roofline = {"kernel": "probe_kernel<FlatU64Src,8,256,false>", "bound": "hbm", "achieved": achieved, "peak": peak,
+    roofline = {"kernel": "rpt_bf_probe = 4 x probe_bitmap_kernel<FlatU64Src,256,2,8,false,true> (sector-range passes) + "
+                          "scan_blocks/scan_totals + compact_bitmap_kernel", "bound": "hbm", "achieved": achieved, "peak": peak,
                 "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": algo_bytes, "launch_ms": probe_ms,
                 "bytes_per_key": algo_bytes / m,
@@ -360,7 +363,8 @@ def run_b200(args):
             "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline,
             "cpu_baseline": cpu, "detail": detail,
         }
-        print(json.dumps(line))
+        _REAL_STDOUT.write(json.dumps(line) + "\n")
+        _REAL_STDOUT.flush()
     sb.close()
     if world > 1:
         dist.barrier()
@@ -461,6 +465,11 @@ def run_e2e(args, rpt, torch, dist, dev, local_rank, world, rank, sb, dk, dp, n,
 
 
 def main():
+    # stdout carries exactly ONE JSON line: libraries that print there (NCCL's version banner) go to stderr
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     args = parse_args()
     if args.impl == "reference":
         return run_reference(args)
