@@ -26,6 +26,7 @@ NUMPY_TYPES = {
     np.dtype(np.int32): INT32, np.dtype(np.uint64): UINT64, np.dtype(np.int64): INT64,
     np.dtype(np.float32): FLOAT, np.dtype(np.float64): DOUBLE,
 }
+_NUMPY_OF_TYPE = {v: k for k, v in NUMPY_TYPES.items()}
 TYPE_WIDTH = {BOOL: 1, UINT8: 1, INT8: 1, UINT16: 2, INT16: 2, UINT32: 4, INT32: 4, UINT64: 8, INT64: 8,
               FLOAT: 4, DOUBLE: 8, INTERVAL: 16, UINT128: 16, INT128: 16}
 
@@ -76,6 +77,9 @@ _SIGNATURES = {
     "rpt_bf_sync": (C.c_int, [C.c_void_p]),
     "rpt_bf_set_has_data": (C.c_int, [C.c_void_p, C.c_int]),
     "rpt_bf_launch_count": (C.c_int, [C.c_void_p, C.POINTER(C.c_longlong)]),
+    "rpt_bf_minmax_begin": (C.c_int, [C.c_void_p, C.c_int]),
+    "rpt_bf_minmax_end": (C.c_int, [C.c_void_p]),
+    "rpt_bf_minmax_get": (C.c_int, [C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_int), C.c_void_p, C.c_void_p]),
     "rpt_bf_or_parts": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p]),
     "rpt_bf_ipc_export": (C.c_int, [C.c_void_p, C.c_void_p]),
     "rpt_bf_peer_open": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int]),
@@ -290,6 +294,22 @@ class PTBloomFilter:
             arr, n = _col_array(cols)
             _check(lib().rpt_bf_finalize(self._h, actual_rows, arr, n, count, C.byref(rebuilt), stream))
         return bool(rebuilt.value)
+
+    # -- UpdateMinMax next to the insert: physical_create_bf.cpp:82-176, 229-239 -----------------
+    def MinMaxBegin(self, type):
+        _check(lib().rpt_bf_minmax_begin(self._h, type))
+        self._mm_type = type
+
+    def MinMaxEnd(self):
+        _check(lib().rpt_bf_minmax_end(self._h))
+
+    def MinMaxGet(self):
+        """Returns (has_value, has_nan, min, max) with min/max as numpy scalars of the column's physical type."""
+        dt = _NUMPY_OF_TYPE[self._mm_type]
+        lo, hi = np.zeros(1, dtype=dt), np.zeros(1, dtype=dt)
+        has, nan = C.c_int(0), C.c_int(0)
+        _check(lib().rpt_bf_minmax_get(self._h, C.byref(has), C.byref(nan), lo.ctypes.data, hi.ctypes.data))
+        return bool(has.value), bool(nan.value), lo[0], hi[0]
 
     # -- filter words ---------------------------------------------------------------------------
     def ExportWords(self):

@@ -113,6 +113,10 @@ struct rpt_bf {
 	std::atomic<int> has_data {0};
 	std::atomic<int> finalized {0};
 	std::atomic<long long> launches {0};
+	// fused column range (rpt_bf_minmax_*)
+	MinMaxState *mm_dev = nullptr;
+	int mm_type = 0;
+	std::atomic<int> mm_active {0};
 	// peer merge state
 	std::vector<uint64_t *> peer_words;
 	std::vector<bool> peer_ipc;
@@ -496,6 +500,9 @@ int rpt_bf_destroy(rpt_bf_t *bf) {
 	if (bf->words) {
 		cudaFree(bf->words);
 	}
+	if (bf->mm_dev) {
+		cudaFree(bf->mm_dev);
+	}
 	for (cudaStream_t s : {bf->stream, bf->h2d, bf->compute, bf->d2h}) {
 		if (s) {
 			cudaStreamSynchronize(s);
@@ -589,6 +596,16 @@ int rpt_bf_sync(const rpt_bf_t *bf) {
 // ---------------------------------------------------------------------------------------------
 // build
 // ---------------------------------------------------------------------------------------------
+// UpdateMinMax next to the insert (physical_create_bf.cpp:229-239): folds the chunk's valid rows into the range.
+static int minmax_hook(rpt_bf *bf, const DevCols &dc, uint64_t count, cudaStream_t stream, int *launches) {
+	if (!bf->mm_active.load() || dc.n != 1 || dc.c[0].type != bf->mm_type) {
+		return 0;
+	}
+	RPT_CUDA(launch_minmax(bf->dev, dc.c[0], count, bf->mm_dev, stream));
+	(*launches)++;
+	return 0;
+}
+
 static int insert_impl(rpt_bf *bf, const rpt_col_t *cols, int ncols, uint64_t count, rpt_stream_t stream_in) {
 	int mem = 0;
 	RPT_TRY(validate_cols(cols, ncols, count, &mem));
@@ -601,6 +618,7 @@ static int insert_impl(rpt_bf *bf, const rpt_col_t *cols, int ncols, uint64_t co
 		DevCols dc;
 		device_cols_view(cols, ncols, &dc);
 		RPT_CUDA(launch_build(bf->dev, dc, count, bf->words, bf->num_sectors, pick_stream(bf, stream_in), &launches));
+		RPT_TRY(minmax_hook(bf, dc, count, pick_stream(bf, stream_in), &launches));
 		bf->launches += launches;
 		return 0;
 	}
@@ -630,6 +648,7 @@ static int insert_impl(rpt_bf *bf, const rpt_col_t *cols, int ncols, uint64_t co
 		RPT_CUDA(cudaEventRecord(sl.uploaded, bf->h2d));
 		RPT_CUDA(cudaStreamWaitEvent(bf->compute, sl.uploaded, 0));
 		RPT_CUDA(launch_build(bf->dev, dc, r1 - r0, bf->words, bf->num_sectors, bf->compute, &launches));
+		RPT_TRY(minmax_hook(bf, dc, r1 - r0, bf->compute, &launches));
 		RPT_CUDA(cudaEventRecord(sl.computed, bf->compute));
 	}
 	bf->launches += launches;
@@ -652,6 +671,92 @@ int rpt_bf_insert(rpt_bf_t *bf, const rpt_col_t *cols, int ncols, uint64_t count
 // ---------------------------------------------------------------------------------------------
 // finalize
 // ---------------------------------------------------------------------------------------------
+static bool minmax_type_ok(int type) {
+	switch (type) {
+	case RPT_BOOL: case RPT_INT8: case RPT_UINT8: case RPT_INT16: case RPT_UINT16: case RPT_INT32: case RPT_UINT32:
+	case RPT_INT64: case RPT_UINT64: case RPT_FLOAT: case RPT_DOUBLE:
+		return true;
+	default:
+		return false;
+	}
+}
+
+int rpt_bf_minmax_begin(rpt_bf_t *bf, int type) {
+	if (!bf) {
+		return set_error("null filter handle");
+	}
+	if (!minmax_type_ok(type)) {
+		return set_error("min/max is tracked for fixed-width numeric key columns only (physical type %d)", type);
+	}
+	RPT_GUARD(bf);
+	if (!bf->mm_dev) {
+		RPT_CUDA(cudaMalloc(&bf->mm_dev, sizeof(MinMaxState)));
+	}
+	MinMaxState init {~0ULL, 0ULL, 0u, 0u};
+	RPT_CUDA(cudaDeviceSynchronize()); // inserts may have been enqueued on caller streams
+	RPT_CUDA(cudaMemcpy(bf->mm_dev, &init, sizeof(init), cudaMemcpyHostToDevice));
+	bf->mm_type = type;
+	bf->mm_active.store(1);
+	return 0;
+}
+
+int rpt_bf_minmax_end(rpt_bf_t *bf) {
+	if (!bf) {
+		return set_error("null filter handle");
+	}
+	bf->mm_active.store(0);
+	return 0;
+}
+
+int rpt_bf_minmax_get(const rpt_bf_t *bf, int *has_value, int *has_nan, void *min_out, void *max_out) {
+	if (!bf || !has_value || !min_out || !max_out) {
+		return set_error("null argument");
+	}
+	if (!bf->mm_dev) {
+		return set_error("rpt_bf_minmax_begin was not called on this filter");
+	}
+	RPT_GUARD(bf);
+	RPT_CUDA(cudaDeviceSynchronize()); // inserts may have been enqueued on caller streams
+	MinMaxState st;
+	RPT_CUDA(cudaMemcpy(&st, bf->mm_dev, sizeof(st), cudaMemcpyDeviceToHost));
+	*has_value = st.has_value ? 1 : 0;
+	if (has_nan) {
+		*has_nan = st.has_nan ? 1 : 0;
+	}
+	if (!st.has_value) {
+		return 0;
+	}
+	constexpr uint64_t kSign = 1ULL << 63;
+	auto decode = [&](uint64_t key, void *out) {
+		switch (bf->mm_type) {
+		case RPT_BOOL: case RPT_UINT8: { uint8_t v = static_cast<uint8_t>(key); memcpy(out, &v, 1); break; }
+		case RPT_INT8: { int8_t v = static_cast<int8_t>(static_cast<int64_t>(key ^ kSign)); memcpy(out, &v, 1); break; }
+		case RPT_UINT16: { uint16_t v = static_cast<uint16_t>(key); memcpy(out, &v, 2); break; }
+		case RPT_INT16: { int16_t v = static_cast<int16_t>(static_cast<int64_t>(key ^ kSign)); memcpy(out, &v, 2); break; }
+		case RPT_UINT32: { uint32_t v = static_cast<uint32_t>(key); memcpy(out, &v, 4); break; }
+		case RPT_INT32: { int32_t v = static_cast<int32_t>(static_cast<int64_t>(key ^ kSign)); memcpy(out, &v, 4); break; }
+		case RPT_UINT64: { memcpy(out, &key, 8); break; }
+		case RPT_INT64: { uint64_t v = key ^ kSign; memcpy(out, &v, 8); break; }
+		case RPT_FLOAT: {
+			const uint32_t o = static_cast<uint32_t>(key);
+			const uint32_t b = (o & 0x80000000u) ? (o & 0x7fffffffu) : ~o;
+			memcpy(out, &b, 4);
+			break;
+		}
+		case RPT_DOUBLE: {
+			const uint64_t b = (key & kSign) ? (key & ~kSign) : ~key;
+			memcpy(out, &b, 8);
+			break;
+		}
+		default:
+			break;
+		}
+	};
+	decode(st.min_key, min_out);
+	decode(st.max_key, max_out);
+	return 0;
+}
+
 int rpt_bf_needs_rebuild(const rpt_bf_t *bf, uint64_t actual_rows, int *out) {
 	if (!bf || !out) {
 		return set_error("null argument");

@@ -849,6 +849,104 @@ __global__ void __launch_bounds__(256)
 	}
 }
 
+// ---------------------------------------------------------------------------------------------
+// min / max of a key column (UpdateMinMax, reference src/operators/physical_create_bf.cpp:82-176): the build
+// side's per-column range, which the reference computes chunk by chunk next to the insert loop (:229-239).
+// Values are mapped to order-preserving unsigned 64-bit keys so that one atomicMin/atomicMax pair serves
+// every numeric type; NULL rows are skipped (:93-95); NaNs are counted, not ordered (see rpt_gpu.h).
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ bool minmax_key(const DevCol &c, uint64_t idx, uint64_t *key, bool *nan) {
+	constexpr uint64_t kSign = 1ULL << 63;
+	*nan = false;
+	switch (c.type) {
+	case RPT_BOOL:
+	case RPT_UINT8:
+		*key = __ldg(reinterpret_cast<const unsigned char *>(c.data) + idx);
+		return true;
+	case RPT_INT8:
+		*key = static_cast<uint64_t>(static_cast<int64_t>(__ldg(reinterpret_cast<const signed char *>(c.data) + idx))) ^ kSign;
+		return true;
+	case RPT_UINT16:
+		*key = __ldg(reinterpret_cast<const unsigned short *>(c.data) + idx);
+		return true;
+	case RPT_INT16:
+		*key = static_cast<uint64_t>(static_cast<int64_t>(__ldg(reinterpret_cast<const short *>(c.data) + idx))) ^ kSign;
+		return true;
+	case RPT_UINT32:
+		*key = __ldg(reinterpret_cast<const uint32_t *>(c.data) + idx);
+		return true;
+	case RPT_INT32:
+		*key = static_cast<uint64_t>(static_cast<int64_t>(__ldg(reinterpret_cast<const int *>(c.data) + idx))) ^ kSign;
+		return true;
+	case RPT_UINT64:
+		*key = __ldg(reinterpret_cast<const unsigned long long *>(c.data) + idx);
+		return true;
+	case RPT_INT64:
+		*key = __ldg(reinterpret_cast<const unsigned long long *>(c.data) + idx) ^ kSign;
+		return true;
+	case RPT_FLOAT: {
+		const uint32_t b = __ldg(reinterpret_cast<const uint32_t *>(c.data) + idx);
+		if ((b & 0x7fffffffu) > 0x7f800000u) {
+			*nan = true;
+			return false;
+		}
+		const uint32_t o = (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+		*key = o;
+		return true;
+	}
+	case RPT_DOUBLE: {
+		const uint64_t b = __ldg(reinterpret_cast<const unsigned long long *>(c.data) + idx);
+		if ((b & ~kSign) > 0x7ff0000000000000ULL) {
+			*nan = true;
+			return false;
+		}
+		*key = (b & kSign) ? ~b : (b | kSign);
+		return true;
+	}
+	default:
+		return false;
+	}
+}
+
+__global__ void __launch_bounds__(256) minmax_kernel(const DevCol col, const uint64_t count, MinMaxState *state) {
+	uint64_t lo = ~0ULL, hi = 0;
+	uint32_t any = 0, nans = 0;
+	const uint64_t step = static_cast<uint64_t>(gridDim.x) * blockDim.x;
+	for (uint64_t row = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x; row < count; row += step) {
+		const uint64_t idx = col.sel ? static_cast<uint64_t>(__ldg(col.sel + row)) : row;
+		if (col.validity && !((__ldg(col.validity + (idx >> 6)) >> (idx & 63)) & 1ULL)) {
+			continue;
+		}
+		uint64_t key;
+		bool nan;
+		if (minmax_key(col, idx, &key, &nan)) {
+			lo = key < lo ? key : lo;
+			hi = key > hi ? key : hi;
+			any = 1;
+		}
+		nans |= nan ? 1u : 0u;
+	}
+#pragma unroll
+	for (int d = 16; d > 0; d >>= 1) {
+		const uint64_t olo = __shfl_xor_sync(0xffffffffu, lo, d);
+		const uint64_t ohi = __shfl_xor_sync(0xffffffffu, hi, d);
+		lo = olo < lo ? olo : lo;
+		hi = ohi > hi ? ohi : hi;
+	}
+	any = __any_sync(0xffffffffu, any);
+	nans = __any_sync(0xffffffffu, nans);
+	if ((threadIdx.x & 31u) == 0) {
+		if (any) {
+			atomicMin(reinterpret_cast<unsigned long long *>(&state->min_key), static_cast<unsigned long long>(lo));
+			atomicMax(reinterpret_cast<unsigned long long *>(&state->max_key), static_cast<unsigned long long>(hi));
+			atomicOr(&state->has_value, 1u);
+		}
+		if (nans) {
+			atomicOr(&state->has_nan, 1u);
+		}
+	}
+}
+
 __host__ __device__ __forceinline__ uint64_t splitmix64(uint64_t x) {
 	uint64_t z = x + 0x9e3779b97f4a7c15ULL;
 	z = (z ^ (z >> 30)) * 0xbf58476d1ce4e5b9ULL;
@@ -1176,6 +1274,15 @@ cudaError_t launch_lookup_hashes(const uint64_t *words, uint64_t num_sectors, co
 	}
 	lookup_hashes_kernel<<<static_cast<unsigned>(ceil_div(count, 256)), 256, 0, stream>>>(words, num_sectors - 1,
 	                                                                                      hashes, count, hits);
+	return cudaGetLastError();
+}
+
+cudaError_t launch_minmax(const DeviceInfo &dev, const DevCol &col, uint64_t count, MinMaxState *state,
+                          cudaStream_t stream) {
+	if (count == 0) {
+		return cudaSuccess;
+	}
+	minmax_kernel<<<stream_grid(dev, count, 256), 256, 0, stream>>>(col, count, state);
 	return cudaGetLastError();
 }
 

@@ -53,6 +53,17 @@ cudaError_t launch_or_ptrs(const DeviceInfo &dev, uint64_t *words, const PtrList
 cudaError_t launch_lookup_hashes(const uint64_t *words, uint64_t num_sectors, const uint64_t *hashes, uint64_t count,
                                  uint8_t *hits, cudaStream_t stream);
 
+// Column range (UpdateMinMax, physical_create_bf.cpp:82-176).  Keys are order-preserving uint64 images of the
+// values (signed: value ^ 2^63 after sign extension; float/double: sign-magnitude flip); the host decodes them.
+struct MinMaxState {
+	uint64_t min_key; // initialised to ~0
+	uint64_t max_key; // initialised to 0
+	uint32_t has_value;
+	uint32_t has_nan;
+};
+cudaError_t launch_minmax(const DeviceInfo &dev, const DevCol &col, uint64_t count, MinMaxState *state,
+                          cudaStream_t stream);
+
 // SURVEY §8(d) synthetic columns
 cudaError_t launch_synth_build(uint64_t *out, uint64_t first, uint64_t count, cudaStream_t stream);
 cudaError_t launch_synth_probe(uint64_t *out, uint64_t first, uint64_t count, uint64_t n_build, uint32_t sel_ppm,

@@ -135,6 +135,21 @@ RPT_API int rpt_bf_reinitialize_and_rehash(rpt_bf_t *bf, uint64_t actual_rows, c
 RPT_API int rpt_bf_finalize(rpt_bf_t *bf, uint64_t actual_rows, const rpt_col_t *cols, int ncols, uint64_t count,
                             int *rebuilt_out, rpt_stream_t stream);
 
+/* ---- build-side column range: UpdateMinMax / ColumnMinMax (src/operators/physical_create_bf.cpp:82-176), which
+ *      PhysicalCreateBF::Sink runs on every chunk next to the insert (:229-239) ----------------------------- */
+/* Starts (or restarts) range tracking for a key column of the given physical type: from now on every
+ * single-column rpt_bf_insert / rehash of that type also folds the column's valid (non-NULL) rows into a running
+ * min / max on the device (one extra streaming kernel on the same stream, no host work per chunk).
+ * Supported: the fixed-width numeric physical types (BOOL…UINT64, FLOAT, DOUBLE; DATE and TIMESTAMP are INT32 /
+ * INT64 physically).  VARCHAR ranges stay on the host. */
+RPT_API int rpt_bf_minmax_begin(rpt_bf_t *bf, int type);
+RPT_API int rpt_bf_minmax_end(rpt_bf_t *bf);
+/* Waits for the handle's work, then: *has_value = any valid row seen (ColumnMinMax::has_value); min_out / max_out
+ * receive one value of the column's physical type.  Floating point: the reference compares with C++ `<` / `>`
+ * chunk by chunk, which is order-dependent when NaNs (or both zeros) occur; here NaNs are left out of the range
+ * and reported through *has_nan (optional) so the caller can widen the range, and -0.0 orders below +0.0. */
+RPT_API int rpt_bf_minmax_get(const rpt_bf_t *bf, int *has_value, int *has_nan, void *min_out, void *max_out);
+
 /* ---- probe: PTBloomFilter::LookupSel (src/bloom_filter.cpp:60-68) = HashColumns +
  *      BloomFilter::LookupHashes (duckdb bloom_filter.cpp:50-61, LookupOne :72-78) ---------- */
 /* Writes the ascending row indices i in [0,count) whose key passes the filter to sel_out[0..found)

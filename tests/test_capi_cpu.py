@@ -72,3 +72,14 @@ def test_product_does_not_reference_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".cpp", ".hpp", ".h")):
                 text = open(os.path.join(base, f), errors="replace").read()
                 assert "rpt_oracle" not in text and "librpt_ref" not in text and "oracle_lib" not in text, f
+
+
+def test_cpp_host_mirror_compiles(rpt):
+    """include/rpt_gpu.hpp (the C++ mirror of PTBloomFilter + the CREATE_BF / USE_BF glue) and its test driver
+    build with g++ alone against the C ABI; the driver itself runs in the gpu suite."""
+    import os
+    import oracle_lib
+    oracle_lib.oracle()  # makes sure oracle/librpt_oracle.so exists (the driver links the checker)
+    from cpp import build_cpp
+    path = build_cpp.build_host_mirror_test(force=True)
+    assert os.path.exists(path) and os.access(path, os.X_OK)

@@ -393,6 +393,57 @@ def test_finalize_resize_rule(rpt, oracle):
     bf.close()
 
 
+@pytest.mark.parametrize("t", sorted(NP))
+def test_minmax_next_to_insert(rpt, t):
+    """UpdateMinMax (physical_create_bf.cpp:82-176): range of the valid rows, accumulated over chunked inserts
+    (host chunks with a validity mask, then a device-style flat chunk), against numpy on the same rows."""
+    rng = np.random.default_rng(1000 + t)
+    dt = NP[t]
+    n = 70_001
+
+    def column(k):
+        if t == 1:  # BOOL, held as one byte 0/1
+            return rng.integers(0, 2, k).astype(dt)
+        if np.issubdtype(dt, np.floating):
+            return (rng.standard_normal(k) * 1e6).astype(dt)
+        info = np.iinfo(dt)
+        return rng.integers(info.min, info.max, k, dtype=dt, endpoint=True)
+
+    bf = gpu_filter(rpt, 2 * n)
+    bf.MinMaxBegin(t)
+    has, nan, _, _ = bf.MinMaxGet()
+    assert not has and not nan                      # ColumnMinMax::has_value starts false
+    a = column(n)
+    valid = rng.random(n) < 0.7
+    validity = np.packbits(valid, bitorder="little")
+    validity = np.concatenate([validity, np.zeros((-len(validity)) % 8, dtype=np.uint8)]).view(np.uint64)
+    bf.Insert(rpt.host_col(a, type=t, validity=validity), n)
+    b = column(n)
+    bf.Insert(rpt.host_col(b, type=t), n)
+    has, nan, lo, hi = bf.MinMaxGet()
+    ref = np.concatenate([a[valid], b])
+    assert has and not nan
+    assert lo == ref.min() and hi == ref.max()
+    assert t == 1 or (lo.dtype == dt and hi.dtype == dt)
+    # an all-NULL chunk changes nothing; after MinMaxEnd inserts are no longer folded in
+    bf.Insert(rpt.host_col(column(64), type=t, validity=np.zeros(1, dtype=np.uint64)), 64)
+    bf.MinMaxEnd()
+    bf.Insert(rpt.host_col(column(n), type=t), n)
+    assert bf.MinMaxGet()[2:] == (lo, hi)
+    bf.close()
+
+
+def test_minmax_nan_and_unsupported(rpt):
+    bf = gpu_filter(rpt, 100)
+    bf.MinMaxBegin(rpt.DOUBLE)
+    bf.Insert(rpt.host_col(np.array([3.0, np.nan, -0.0, 7.5], dtype=np.float64)), 4)
+    has, nan, lo, hi = bf.MinMaxGet()
+    assert has and nan and lo == 0.0 and np.signbit(lo) and hi == 7.5
+    with pytest.raises(rpt.RptError):
+        bf.MinMaxBegin(rpt.VARCHAR)
+    bf.close()
+
+
 def test_uint32_estimate_wrap(rpt, oracle):
     """PTBloomFilter::Initialize takes uint32_t est_num_rows (bloom_filter.hpp:25): 2^32+100 sizes like 100."""
     bf = gpu_filter(rpt, 2**32 + 100)
@@ -662,3 +713,14 @@ def test_config2_full_size_against_oracle(rpt, oracle, torch_cuda):
     assert bool((dsel_a[:fa] == sel[:fa]).all())
     assert bool(((dsel_b[:fb].long() & 0xFFFFFFFF) + half == (sel[fa:].long() & 0xFFFFFFFF)).all())
     bf.close()
+
+
+def test_cpp_host_mirror(rpt, oracle):
+    """tests/cpp/host_mirror_test.cpp: CreateBFBatch / UseBFBatch / PTBloomFilter (include/rpt_gpu.hpp) driven like
+    the reference's Sink / Finalize / ExecuteInternal, compared with the oracle inside the C++ driver."""
+    import subprocess
+    from cpp import build_cpp
+    path = build_cpp.build_host_mirror_test()
+    proc = subprocess.run([path], capture_output=True, text=True, timeout=600)
+    assert proc.returncode == 0, proc.stdout + proc.stderr
+    assert "host mirror ok" in proc.stdout
