@@ -57,6 +57,11 @@ __device__ __forceinline__ uint64_t ld_relaxed_u64(const uint64_t *ptr) {
 __device__ __forceinline__ void st_relaxed_u64(uint64_t *ptr, uint64_t v) {
 	asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(ptr), "l"(v) : "memory");
 }
+__device__ __forceinline__ void st_stream_v4(void *ptr, const uint4 v, uint64_t pol) {
+	asm volatile("st.global.L2::cache_hint.v4.b32 [%0], {%1, %2, %3, %4}, %5;" ::"l"(ptr), "r"(v.x), "r"(v.y), "r"(v.z),
+	             "r"(v.w), "l"(pol)
+	             : "memory");
+}
 __device__ __forceinline__ uint32_t lanemask_lt() {
 	uint32_t m;
 	asm("mov.u32 %0, %%lanemask_lt;" : "=r"(m));
@@ -530,6 +535,299 @@ __global__ void __launch_bounds__(BLOCK, MINB)
 	}
 	if (STAGED) {
 		cp_async_wait<0>();
+	}
+}
+
+// ---- filters beyond one L2-resident slice: partition once, then probe slice by slice -----------------------
+// The sector-range passes above re-read the 8-byte key column once per slice (4× at F = 256 MiB: ncu r1c 42 GB
+// of DRAM traffic for 8.7 GB of algorithmic bytes, each pass DRAM-bound).  This path reads the keys ONCE:
+//   probe_partition_kernel  hashes every key; keys of slice 0 are looked up on the spot (slice 0 is the
+//                           L2-resident one during this kernel); keys of slice s ≥ 1 become 8-byte records
+//                           {sector-in-slice : 23 | row-in-segment : 9 | hash bits 63..32} in bucket s.
+//                           Every (segment, slice) pair owns a fixed region of CAP records (1.5× the expected
+//                           512/P), so no atomics, no directory and no inter-warp dependency exist; the
+//                           records are placed through warp-private shared memory and leave the SM as
+//                           contiguous 16-byte stores.  A key that does not fit its region (skew) is looked up
+//                           on the spot instead — slower, never wrong.
+//   probe_bucket_kernel     once per slice s ≥ 1 (slice prefetched into L2): record → filter word → test →
+//                           RED.OR of the row's bit into the row-ordered bitmap (hits only).
+//   count_segments_kernel   popcount of every segment's 512 bitmap bits → the scan's input.
+// DRAM traffic per key: 8 (keys) + 6 + 6 (records out and in) instead of 32.
+constexpr uint32_t kSliceShift = 23; // log2(kSliceSectors)
+static_assert((1ULL << kSliceShift) == kSliceSectors, "record layout assumes 2^23-sector slices");
+
+template <int P>
+struct PartCfg {
+	static_assert(P == 2 || P == 4 || P == 8, "S is a power of two: 2, 4 or 8 slices of 64 MiB");
+	static constexpr int NREG = (P - 1 + 2) / 3;             // 10-bit counters, three per 32-bit register
+	static constexpr int CAP = P == 2 ? 384 : (P == 4 ? 192 : 96); // records per (segment, slice) region
+};
+
+// counters of slices 1..P-1 packed 10 bits each (a segment has 512 rows: every count fits)
+template <int NREG>
+struct Packed {
+	uint32_t r[NREG];
+};
+template <int NREG>
+__device__ __forceinline__ void packed_add_slice(Packed<NREG> &c, uint32_t s) { // s == 0 adds nothing
+	if (NREG == 1) {
+		c.r[0] += (1u << mul_lo_u32(s, 10u)) >> 10; // asm multiply: nvcc otherwise emits IDP.2A (45 % of stalls)
+	} else {
+		const uint32_t idx = s - 1u; // 0xffffffff for s == 0: matches no register
+		const uint32_t q = (idx * 11u) >> 5; // idx / 3 for idx ≤ 6
+		const uint32_t inc = 1u << mul_lo_u32(idx - 3u * q, 10u);
+#pragma unroll
+		for (int j = 0; j < NREG; j++) {
+			c.r[j] += (s != 0u && q == static_cast<uint32_t>(j)) ? inc : 0u;
+		}
+	}
+}
+template <int NREG>
+__device__ __forceinline__ uint32_t packed_get(const Packed<NREG> &c, uint32_t idx) { // idx = slice - 1
+	if (NREG == 1) {
+		return (c.r[0] >> mul_lo_u32(idx, 10u)) & 1023u;
+	}
+	const uint32_t q = (idx * 11u) >> 5;
+	uint32_t v = c.r[0];
+#pragma unroll
+	for (int j = 1; j < NREG; j++) {
+		v = q == static_cast<uint32_t>(j) ? c.r[j] : v;
+	}
+	return (v >> mul_lo_u32(idx - 3u * q, 10u)) & 1023u;
+}
+
+template <class Src, int BLOCK, int P>
+__global__ void __launch_bounds__(BLOCK, 2)
+    probe_partition_kernel(const Src src, const uint64_t *__restrict__ filter, const uint32_t sector_mask,
+                           const uint64_t count, const uint64_t num_segs, uint16_t *__restrict__ bitmap16,
+                           uint2 *__restrict__ buckets, const uint64_t bucket_stride /* records per slice array */,
+                           uint16_t *__restrict__ bucket_counts /* (P-1) × num_segs */) {
+	constexpr int NWARPS = BLOCK / 32;
+	constexpr bool STAGED = Src::kStageable;
+	constexpr int SEG_UNITS = kSegRows / 2;
+	constexpr int NREG = PartCfg<P>::NREG;
+	constexpr int CAP = PartCfg<P>::CAP;
+	constexpr int KEY_BYTES = STAGED ? NWARPS * 2 * SEG_UNITS * 16 : 0;
+	// dynamic shared memory: [warp-private key double buffers (STAGED)][warp-private record stage, (P-1)·CAP each]
+	extern __shared__ __align__(128) unsigned char s_dyn[];
+	ulonglong2 *const s_keys = reinterpret_cast<ulonglong2 *>(s_dyn);
+	const uint32_t lane = threadIdx.x & 31u;
+	const uint32_t warp = threadIdx.x >> 5;
+	uint2 *const stage = reinterpret_cast<uint2 *>(s_dyn + KEY_BYTES) + warp * ((P - 1) * CAP);
+	const uint64_t pol_keys = policy_evict_first();
+	const uint64_t pol_filter = policy_evict_last();
+	warm_slice(filter, 0u, 1u << kSliceShift, BLOCK);
+	const uint64_t stride = static_cast<uint64_t>(gridDim.x) * NWARPS;
+	const uint64_t full_segs = count / kSegRows;
+	ulonglong2 *const my_buf = s_keys + warp * (2 * SEG_UNITS);
+	const uint32_t rot = lane & 7u;
+
+	constexpr uint64_t kNone = ~0ULL;
+	uint64_t cur = kNone;
+	uint32_t par = 1;
+	for (uint64_t nxt = static_cast<uint64_t>(blockIdx.x) * NWARPS + warp;; nxt += stride) {
+		if (STAGED) {
+			__syncwarp();
+			if (nxt < full_segs) {
+				const ulonglong2 *g = reinterpret_cast<const ulonglong2 *>(src.key_ptr()) + nxt * SEG_UNITS + lane;
+				ulonglong2 *s = my_buf + (par ^ 1u) * SEG_UNITS + lane;
+#pragma unroll
+				for (int k = 0; k < 8; k++) {
+					cp_async_16(s + k * 32, g + k * 32, pol_keys);
+				}
+			}
+			cp_async_commit();
+		}
+		if (cur != kNone) {
+			const bool staged_seg = STAGED && cur < full_segs;
+			uint64_t h[16];
+			uint32_t valid = 0xffffu;
+			if (staged_seg) {
+				cp_async_wait<1>();
+				__syncwarp();
+				const ulonglong2 *mine = my_buf + par * SEG_UNITS + lane * 8;
+#pragma unroll
+				for (int u = 0; u < 8; u++) {
+					const ulonglong2 k = mine[(u + rot) & 7u];
+					h[2 * u] = murmur64(k.x);
+					h[2 * u + 1] = murmur64(k.y);
+				}
+			} else {
+				const bool full = cur < full_segs;
+				const uint64_t row0 = cur * kSegRows + lane * 16;
+				valid = 0;
+#pragma unroll
+				for (int i = 0; i < 16; i++) {
+					h[i] = 0;
+					if (full || row0 + i < count) {
+						h[i] = src.hash_at(row0 + i, pol_keys);
+						valid |= 1u << i;
+					}
+				}
+			}
+			// slot i of a staged segment is row (lane·16 + ((i/2 + rot) mod 8)·2 + i%2) of the segment
+			const uint32_t unit_rot = staged_seg ? rot : 0u;
+
+			// pass 1: slice of every key; slice-0 lookups are issued; the other slices are counted
+			uint64_t w0[16];
+			Packed<NREG> cnt;
+#pragma unroll
+			for (int j = 0; j < NREG; j++) {
+				cnt.r[j] = 0;
+			}
+#pragma unroll
+			for (int i = 0; i < 16; i++) {
+				const uint32_t sector = static_cast<uint32_t>(h[i]) & sector_mask;
+				const uint32_t s = sector >> kSliceShift;
+				const bool v = (valid >> i) & 1u;
+				w0[i] = 0;
+				if (v && s == 0u) {
+					w0[i] = ld_filter_word(filter + sector, pol_filter);
+				}
+				packed_add_slice<NREG>(cnt, v ? s : 0u);
+			}
+			// warp scan of the packed counters (fields cannot carry: a segment has 512 rows)
+			Packed<NREG> incl = cnt;
+#pragma unroll
+			for (int d = 1; d < 32; d <<= 1) {
+#pragma unroll
+				for (int j = 0; j < NREG; j++) {
+					const uint32_t t = __shfl_up_sync(0xffffffffu, incl.r[j], d);
+					incl.r[j] += lane >= static_cast<uint32_t>(d) ? t : 0u;
+				}
+			}
+			Packed<NREG> run, total;
+#pragma unroll
+			for (int j = 0; j < NREG; j++) {
+				run.r[j] = incl.r[j] - cnt.r[j];
+				total.r[j] = __shfl_sync(0xffffffffu, incl.r[j], 31);
+			}
+			// pass 2: records into the warp's stage; keys beyond their region's capacity are kept for later
+			uint32_t late = 0;
+#pragma unroll
+			for (int i = 0; i < 16; i++) {
+				const uint32_t sector = static_cast<uint32_t>(h[i]) & sector_mask;
+				const uint32_t s = sector >> kSliceShift;
+				if (((valid >> i) & 1u) && s != 0u) {
+					const uint32_t pos = packed_get<NREG>(run, s - 1u);
+					packed_add_slice<NREG>(run, s);
+					if (pos < static_cast<uint32_t>(CAP)) {
+						const uint32_t row9 = lane * 16u + ((((i >> 1) + unit_rot) & 7u) << 1) + (i & 1);
+						stage[mul_lo_u32(s - 1u, CAP) + pos] =
+						    make_uint2((sector & ((1u << kSliceShift) - 1u)) | (row9 << kSliceShift),
+						               static_cast<uint32_t>(h[i] >> 32));
+					} else {
+						late |= 1u << i;
+					}
+				}
+			}
+			// slice-0 results
+			uint32_t hits = 0;
+#pragma unroll
+			for (int i = 15; i >= 0; i--) {
+				hits = hits * 2u + sector_test_fma(w0[i], static_cast<uint32_t>(h[i] >> 32));
+			}
+			if (__any_sync(0xffffffffu, late != 0u)) { // skewed keys only
+#pragma unroll
+				for (int i = 0; i < 16; i++) {
+					if ((late >> i) & 1u) {
+						const uint32_t sector = static_cast<uint32_t>(h[i]) & sector_mask;
+						hits |= sector_test(__ldg(filter + sector), static_cast<uint32_t>(h[i] >> 32)) << i;
+					}
+				}
+			}
+			if (staged_seg) {
+				const uint32_t twice = hits | (hits << 16);
+				hits = (twice >> (16u - 2u * rot)) & 0xffffu;
+			}
+			bitmap16[cur * 32 + lane] = static_cast<uint16_t>(hits);
+			// copy-out: the warp's records of every slice leave as contiguous 16-byte stores
+			__syncwarp();
+#pragma unroll
+			for (int idx = 0; idx < P - 1; idx++) {
+				uint32_t c = packed_get<NREG>(total, idx);
+				c = c < static_cast<uint32_t>(CAP) ? c : static_cast<uint32_t>(CAP);
+				const uint4 *sv = reinterpret_cast<const uint4 *>(stage + idx * CAP);
+				uint4 *dv = reinterpret_cast<uint4 *>(buckets + idx * bucket_stride + cur * CAP);
+				for (uint32_t j = lane; 2u * j < c; j += 32u) {
+					// an odd count copies one stale record: it stays inside the region, unread.  evict_first: 6 B/key of
+					// record traffic must not push slice 0 of the filter out of L2
+					st_stream_v4(dv + j, sv[j], pol_keys);
+				}
+				if (lane == 0) {
+					bucket_counts[idx * num_segs + cur] = static_cast<uint16_t>(c);
+				}
+			}
+			__syncwarp(); // the stage is rewritten by the next segment
+		}
+		if (nxt >= num_segs) {
+			break;
+		}
+		cur = nxt;
+		par ^= 1u;
+	}
+	if (STAGED) {
+		cp_async_wait<0>();
+	}
+}
+
+// One slice's bucket: warp per segment region; all record loads, then all filter loads, are issued before the
+// first test.  ITER = CAP / 32 records per lane.
+template <int CAP>
+__global__ void __launch_bounds__(256)
+    probe_bucket_kernel(const uint2 *__restrict__ bucket, const uint16_t *__restrict__ counts, const uint64_t num_segs,
+                        const uint64_t *__restrict__ filter, const uint32_t slice_lo, uint32_t *__restrict__ bitmap32) {
+	constexpr int ITER = CAP / 32;
+	const uint32_t lane = threadIdx.x & 31u;
+	const uint64_t pol_rec = policy_evict_first();
+	const uint64_t pol_filter = policy_evict_last();
+	warm_slice(filter, slice_lo, 1u << kSliceShift, 256);
+	const uint64_t *const slice = filter + slice_lo;
+	const uint64_t warp_global = (static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
+	const uint64_t num_warps = (static_cast<uint64_t>(gridDim.x) * blockDim.x) >> 5;
+	for (uint64_t seg = warp_global; seg < num_segs; seg += num_warps) {
+		const uint32_t c = __ldg(counts + seg);
+		const uint2 *rec_base = bucket + seg * CAP;
+		uint2 rec[ITER];
+#pragma unroll
+		for (int k = 0; k < ITER; k++) {
+			const uint32_t j = lane + 32u * k;
+			rec[k] = make_uint2(0u, 0u);
+			if (j < c) {
+				const uint64_t v = ld_stream_u64(rec_base + j, pol_rec);
+				rec[k] = make_uint2(static_cast<uint32_t>(v), static_cast<uint32_t>(v >> 32));
+			}
+		}
+		uint64_t w[ITER];
+#pragma unroll
+		for (int k = 0; k < ITER; k++) {
+			w[k] = 0;
+			if (lane + 32u * k < c) {
+				w[k] = ld_filter_word(slice + (rec[k].x & ((1u << kSliceShift) - 1u)), pol_filter);
+			}
+		}
+#pragma unroll
+		for (int k = 0; k < ITER; k++) {
+			if (sector_test_fma(w[k], rec[k].y)) { // an all-zero word (no record) passes nothing
+				const uint32_t row9 = rec[k].x >> kSliceShift;
+				atomicOr(bitmap32 + seg * 16 + (row9 >> 5), 1u << (row9 & 31u));
+			}
+		}
+	}
+}
+
+// seg_counts[seg] = number of set bits among the segment's 512 bitmap bits
+__global__ void __launch_bounds__(256)
+    count_segments_kernel(const uint4 *__restrict__ bitmap128, const uint64_t num_segs, uint32_t *__restrict__ seg_counts) {
+	const uint64_t step = static_cast<uint64_t>(gridDim.x) * blockDim.x;
+	for (uint64_t seg = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x; seg < num_segs; seg += step) {
+		uint32_t n = 0;
+#pragma unroll
+		for (int q = 0; q < 4; q++) {
+			const uint4 v = __ldg(bitmap128 + seg * 4 + q);
+			n += __popc(v.x) + __popc(v.y) + __popc(v.z) + __popc(v.w);
+		}
+		seg_counts[seg] = n;
 	}
 }
 
@@ -1025,6 +1323,12 @@ static inline uint64_t align_up(uint64_t v, uint64_t a) {
 	return (v + a - 1) / a * a;
 }
 
+static inline unsigned stream_grid(const DeviceInfo &dev, uint64_t items, unsigned block) {
+	const uint64_t want = ceil_div(items, block);
+	const uint64_t cap = static_cast<uint64_t>(dev.sm_count > 0 ? dev.sm_count : 148) * 8;
+	return static_cast<unsigned>(want < cap ? (want ? want : 1) : cap);
+}
+
 // Scratch layout of a phased probe: [segment offsets u32 × cap][block totals u32 × blocks][row bitmap, 64 B × cap]
 struct PhasedLayout {
 	uint64_t seg_cap;    // segments (512 rows each), with slack so that the last compaction chunk stays in bounds
@@ -1041,12 +1345,42 @@ static PhasedLayout phased_layout(uint64_t count) {
 	return l;
 }
 
+// Which filters take the partitioned probe.  Measured on B200 (profiles/sweep_r1f.txt, 10^9 probe rows):
+//   F = 512 MiB (8 slices): partitioned 10.4 ms vs 15.9 ms for 8 sector-range passes  → partitioned
+//   F = 256 MiB (4 slices): 10.3 ms vs 7.9–8.7 ms;  F = 128 MiB (2 slices): 8.0 ms vs 4.9 ms → passes
+// (the partition kernel is issue/latency-bound at 88 instructions per key, ncu r1f; re-reading 8-byte keys two or
+// four times is cheaper than that).  RPT_PROBE_PARTITION=1 forces it for every sliced filter, =0 disables it.
+static int partition_mode() {
+	static const int mode = [] {
+		const char *e = getenv("RPT_PROBE_PARTITION");
+		if (getenv("RPT_SLICE_MIB") != nullptr) {
+			return 0;
+		}
+		return e ? (atoi(e) != 0 ? 2 : 0) : 1;
+	}();
+	return mode;
+}
+static inline int partition_slices(uint64_t num_sectors) {
+	const int slices = num_sectors > kSliceSectors ? static_cast<int>(num_sectors / kSliceSectors) : 0;
+	const int mode = partition_mode();
+	return (mode == 2 || (mode == 1 && slices == 8)) ? slices : 0;
+}
+static inline int partition_cap(int slices) {
+	return slices == 2 ? PartCfg<2>::CAP : (slices == 4 ? PartCfg<4>::CAP : PartCfg<8>::CAP);
+}
+// extra scratch behind the phased layout: [bucket counts u16 × (P-1)·segs][records 8 B × (P-1)·segs·CAP]
+static size_t partition_scratch_bytes(uint64_t count, int slices) {
+	const uint64_t num_segs = ceil_div(count, kSegRows);
+	return align_up((slices - 1) * num_segs * sizeof(uint16_t), 256) +
+	       (slices - 1) * num_segs * partition_cap(slices) * sizeof(uint2);
+}
+
 size_t probe_scratch_bytes(uint64_t count, uint64_t num_sectors) {
-	(void)num_sectors;
 	if (count <= kFusedMaxKeys) {
 		return (ceil_div(count, kProbeTileKeys) + 2) * sizeof(uint64_t); // look-back descriptors + ticket
 	}
-	return phased_layout(count).bytes;
+	const int slices = partition_slices(num_sectors);
+	return align_up(phased_layout(count).bytes, 256) + (slices ? partition_scratch_bytes(count, slices) : 0);
 }
 
 template <class Src, bool AGG>
@@ -1196,6 +1530,73 @@ static cudaError_t launch_probe_phased(const DeviceInfo &dev, const Src &src, ui
 	return cudaGetLastError();
 }
 
+template <class Src, int P>
+static cudaError_t launch_probe_partitioned(const DeviceInfo &dev, const Src &src, uint64_t count,
+                                            const uint64_t *words, uint64_t num_sectors, uint32_t *sel_out,
+                                            uint64_t *found_out, uint32_t row_offset, const uint32_t *translate,
+                                            void *scratch, cudaStream_t stream, int *launches) {
+	constexpr int BLOCK = kProbeBlock;
+	constexpr int CAP = PartCfg<P>::CAP;
+	auto part = probe_partition_kernel<Src, BLOCK, P>;
+	auto bucket = probe_bucket_kernel<CAP>;
+	const uint64_t num_segs = ceil_div(count, kSegRows);
+	const size_t smem = (Src::kStageable ? static_cast<size_t>(BLOCK / 32) * 2 * kSegRows * 8 : 0) +
+	                    static_cast<size_t>(BLOCK / 32) * (P - 1) * CAP * sizeof(uint2);
+	cudaError_t e = cudaFuncSetAttribute(part, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
+	if (e != cudaSuccess) {
+		return e;
+	}
+	int per_sm = 0;
+	e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, part, BLOCK, smem);
+	if (e != cudaSuccess) {
+		return e;
+	}
+	if (per_sm < 1) {
+		return cudaErrorLaunchOutOfResources;
+	}
+	uint64_t grid = static_cast<uint64_t>(dev.sm_count) * per_sm;
+	const uint64_t want = ceil_div(num_segs, BLOCK / 32);
+	grid = grid < want ? grid : want;
+	const PhasedLayout lay = phased_layout(count);
+	char *base = reinterpret_cast<char *>(scratch);
+	uint32_t *seg_offsets = reinterpret_cast<uint32_t *>(base);
+	uint32_t *block_totals = reinterpret_cast<uint32_t *>(base + lay.off_totals);
+	uint16_t *bitmap = reinterpret_cast<uint16_t *>(base + lay.off_hitbits);
+	char *extra = base + align_up(lay.bytes, 256);
+	uint16_t *bucket_counts = reinterpret_cast<uint16_t *>(extra);
+	uint2 *buckets = reinterpret_cast<uint2 *>(extra + align_up((P - 1) * num_segs * sizeof(uint16_t), 256));
+	const uint64_t bucket_stride = num_segs * CAP;
+	part<<<static_cast<unsigned>(grid), BLOCK, smem, stream>>>(src, words, static_cast<uint32_t>(num_sectors - 1), count,
+	                                                          num_segs, bitmap, buckets, bucket_stride, bucket_counts);
+	int bper_sm = 0;
+	e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bper_sm, bucket, 256, 0);
+	if (e != cudaSuccess) {
+		return e;
+	}
+	uint64_t bgrid = static_cast<uint64_t>(dev.sm_count) * (bper_sm > 0 ? bper_sm : 1);
+	const uint64_t bwant = ceil_div(num_segs, 8);
+	bgrid = bgrid < bwant ? bgrid : bwant;
+	for (int s = 1; s < P; s++) {
+		bucket<<<static_cast<unsigned>(bgrid), 256, 0, stream>>>(buckets + (s - 1) * bucket_stride,
+		                                                        bucket_counts + (s - 1) * num_segs, num_segs, words,
+		                                                        static_cast<uint32_t>(s) << kSliceShift,
+		                                                        reinterpret_cast<uint32_t *>(bitmap));
+	}
+	count_segments_kernel<<<stream_grid(dev, num_segs, 256), 256, 0, stream>>>(
+	    reinterpret_cast<const uint4 *>(bitmap), num_segs, seg_offsets);
+	const uint64_t nblocks = ceil_div(num_segs, kScanBlock);
+	scan_blocks_kernel<<<static_cast<unsigned>(nblocks), 1024, 0, stream>>>(seg_offsets, num_segs, block_totals);
+	scan_totals_kernel<<<1, 1024, 0, stream>>>(block_totals, static_cast<uint32_t>(nblocks), found_out);
+	const uint64_t cwant = ceil_div((num_segs + 1) / 2, 8ull);
+	const uint64_t ccap = static_cast<uint64_t>(dev.sm_count) * 6;
+	compact_bitmap_kernel<<<static_cast<unsigned>(cwant < ccap ? cwant : ccap), 256, 0, stream>>>(
+	    reinterpret_cast<const uint32_t *>(bitmap), seg_offsets, block_totals, num_segs, sel_out, row_offset, translate);
+	if (launches) {
+		(*launches) += P + 4;
+	}
+	return cudaGetLastError();
+}
+
 static int probe_units() {
 	static const int units = [] {
 		const char *e = getenv("RPT_PROBE_UNITS");
@@ -1213,6 +1614,16 @@ static cudaError_t launch_probe_src(const DeviceInfo &dev, const Src &src, uint6
 	if (count <= kFusedMaxKeys) {
 		return smem ? launch_probe_fused<Src, kProbeBlockSmem, true>(RPT_PROBE_ARGS)
 		            : launch_probe_fused<Src, kProbeBlock, false>(RPT_PROBE_ARGS);
+	}
+	switch (smem ? 0 : partition_slices(num_sectors)) {
+	case 2:
+		return launch_probe_partitioned<Src, 2>(RPT_PROBE_ARGS);
+	case 4:
+		return launch_probe_partitioned<Src, 4>(RPT_PROBE_ARGS);
+	case 8:
+		return launch_probe_partitioned<Src, 8>(RPT_PROBE_ARGS);
+	default:
+		break;
 	}
 	const bool wide = probe_units() == 8;
 	if (smem) {
@@ -1242,12 +1653,6 @@ cudaError_t launch_probe(const DeviceInfo &dev, const DevCols &cols, uint64_t co
 	GenericSrc src {cols};
 	return launch_probe_src(dev, src, count, words, num_sectors, sel_out, found_out, row_offset, translate, scratch,
 	                        stream, launches);
-}
-
-static inline unsigned stream_grid(const DeviceInfo &dev, uint64_t items, unsigned block) {
-	const uint64_t want = ceil_div(items, block);
-	const uint64_t cap = static_cast<uint64_t>(dev.sm_count > 0 ? dev.sm_count : 148) * 8;
-	return static_cast<unsigned>(want < cap ? (want ? want : 1) : cap);
 }
 
 cudaError_t launch_or_parts(const DeviceInfo &dev, uint64_t *words, const uint64_t *parts, uint64_t num_sectors,

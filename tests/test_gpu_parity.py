@@ -337,6 +337,32 @@ def test_filter_sizes(rpt, oracle, est, n):
     check_build_probe(rpt, oracle, est, rpt.host_col(keys), n, rpt.host_col(probe), m)
 
 
+@pytest.mark.parametrize("est,slices", [(50_000_000, 2), (100_000_000, 4), (300_000_000, 8)])
+def test_filters_beyond_one_l2_slice(rpt, oracle, est, slices):
+    """F = 128 / 256 / 512 MiB: the build runs in sector-range passes; the probe runs in sector-range passes (2 and
+    4 slices) or partitions the keys by slice (8 slices: probe_partition_kernel / probe_bucket_kernel; the whole
+    suite also runs with RPT_PROBE_PARTITION=1, which partitions for every sliced filter).  Ragged probe length;
+    a probe column whose keys all fall into one slice overflows the fixed (segment, slice) regions and takes the
+    on-the-spot lookups instead."""
+    assert oracle.num_sectors(est) == slices << 23
+    n = 300_001
+    keys = synth_build_keys(0, n)
+    m = 1_300_007
+    probe = synth_probe_keys(0, m, n, 250000)
+    check_build_probe(rpt, oracle, est, rpt.host_col(keys), n, rpt.host_col(probe), m)
+    # skew: many copies of few keys → every key of a segment in the same slice
+    rng = np.random.default_rng(est)
+    few = np.concatenate([keys[:5], rng.integers(-2**62, 2**62, 5)]).astype(np.int64)
+    skew = few[rng.integers(0, few.size, 700_001)]
+    check_build_probe(rpt, oracle, est, rpt.host_col(keys), n, rpt.host_col(skew), skew.size)
+    # other key sources go through the same kernels (generic path): int32 keys with NULLs
+    k32 = rng.integers(-2**31, 2**31 - 1, 200_000).astype(np.int32)
+    p32 = np.concatenate([k32[:50_000], rng.integers(-2**31, 2**31 - 1, 450_003).astype(np.int32)])
+    val = np.packbits(rng.random(p32.size) < 0.9, bitorder="little")
+    val = np.concatenate([val, np.zeros((-len(val)) % 8, dtype=np.uint8)]).view(np.uint64)
+    check_build_probe(rpt, oracle, est, rpt.host_col(k32), k32.size, rpt.host_col(p32, validity=val), p32.size)
+
+
 def test_duplicate_heavy_keys_small_filter(rpt, oracle):
     """Warp-aggregated atomics path: many lanes of a warp hit the same sector."""
     rng = np.random.default_rng(59)
