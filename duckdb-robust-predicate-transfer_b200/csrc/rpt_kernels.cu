@@ -74,7 +74,13 @@ __device__ __forceinline__ uint32_t lanemask_lt() {
 // ---------------------------------------------------------------------------------------------
 struct FlatU64Src { // one flat int64 / uint64 column, no NULLs, base 16-byte aligned
 	static constexpr bool kStageable = true; // a segment is 512 contiguous 8-byte keys: cp.async-able
+	static constexpr int kKeyBytes = 8;
 	const uint64_t *keys;
+	// KPU hashes out of one staged 16-byte unit
+	__device__ __forceinline__ static void hash_unit(const uint4 &v, uint64_t *h) {
+		h[0] = murmur64((static_cast<uint64_t>(v.y) << 32) | v.x);
+		h[1] = murmur64((static_cast<uint64_t>(v.w) << 32) | v.z);
+	}
 	__device__ __forceinline__ const uint64_t *key_ptr() const {
 		return keys;
 	}
@@ -114,8 +120,70 @@ struct FlatU64Src { // one flat int64 / uint64 column, no NULLs, base 16-byte al
 	}
 };
 
+// One flat 4-byte integer column (INT32 / UINT32 — also DATE), no NULLs, base 16-byte aligned.
+// Hash<int32/uint32> = MurmurHash64 of the zero-extended 32-bit pattern (hash.hpp:49-52).
+__device__ __forceinline__ uint2 ld_stream_v2_u32(const void *ptr, uint64_t pol) {
+	uint2 v;
+	asm("ld.global.nc.L1::no_allocate.L2::cache_hint.v2.u32 {%0, %1}, [%2], %3;" : "=r"(v.x), "=r"(v.y) : "l"(ptr), "l"(pol));
+	return v;
+}
+__device__ __forceinline__ uint32_t ld_stream_u32(const void *ptr, uint64_t pol) {
+	uint32_t v;
+	asm("ld.global.nc.L1::no_allocate.L2::cache_hint.u32 %0, [%1], %2;" : "=r"(v) : "l"(ptr), "l"(pol));
+	return v;
+}
+struct FlatU32Src {
+	static constexpr bool kStageable = true; // a segment is 512 contiguous 4-byte keys = 2 KiB
+	static constexpr int kKeyBytes = 4;
+	const uint32_t *keys;
+	__device__ __forceinline__ static void hash_unit(const uint4 &v, uint64_t *h) {
+		h[0] = murmur64(v.x);
+		h[1] = murmur64(v.y);
+		h[2] = murmur64(v.z);
+		h[3] = murmur64(v.w);
+	}
+	__device__ __forceinline__ const uint32_t *key_ptr() const {
+		return keys;
+	}
+	__device__ __forceinline__ uint64_t hash_at(uint64_t row, uint64_t pol) const {
+		return murmur64(ld_stream_u32(keys + row, pol));
+	}
+	template <int R>
+	__device__ __forceinline__ void load_rounds(uint64_t row0, uint64_t stride, uint64_t pol,
+	                                            uint64_t (&h)[2 * R]) const {
+		uint2 k[R];
+#pragma unroll
+		for (int r = 0; r < R; r++) {
+			k[r] = ld_stream_v2_u32(keys + row0 + r * stride, pol);
+		}
+#pragma unroll
+		for (int r = 0; r < R; r++) {
+			h[2 * r] = murmur64(k[r].x);
+			h[2 * r + 1] = murmur64(k[r].y);
+		}
+	}
+	__device__ __forceinline__ uint32_t load2(uint64_t row0, uint64_t count, uint64_t pol, uint64_t &h0,
+	                                          uint64_t &h1) const {
+		if (row0 + 1 < count) {
+			const uint2 k = ld_stream_v2_u32(keys + row0, pol);
+			h0 = murmur64(k.x);
+			h1 = murmur64(k.y);
+			return 3u;
+		}
+		h0 = h1 = 0;
+		if (row0 < count) {
+			h0 = murmur64(ld_stream_u32(keys + row0, pol));
+			return 1u;
+		}
+		return 0u;
+	}
+};
+
 struct GenericSrc { // any type / sel / validity / multi-column combination
 	static constexpr bool kStageable = false;
+	static constexpr int kKeyBytes = 8; // unused (never staged)
+	__device__ __forceinline__ static void hash_unit(const uint4 &, uint64_t *) {
+	}
 	DevCols cols;
 	__device__ __forceinline__ const uint64_t *key_ptr() const {
 		return nullptr;
@@ -350,6 +418,21 @@ __device__ __forceinline__ void warm_slice(const uint64_t *__restrict__ filter, 
 constexpr uint64_t kScanBlock = 4096;
 constexpr uint64_t kSegRows = 512;
 
+// Staging geometry of a flat column with KB-byte keys: a 16-byte unit holds KPU keys, a lane owns U units
+// (its 16 rows), a segment has SEG_UNITS units.  Lane l reads its units in the order (p + rot(l)) mod U:
+//   8-byte keys: U = 8, rot = l mod 8        → unit index mod 8 = (p + l) mod 8, distinct over a quarter-warp
+//   4-byte keys: U = 4, rot = (l / 2) mod 4  → unit index mod 8 = 4·(l mod 2) + (p + l/2) mod 4, distinct too
+template <int KB>
+struct StageGeo {
+	static constexpr int KPU = 16 / KB;
+	static constexpr int U = 16 / KPU;
+	static constexpr int SEG_UNITS = static_cast<int>(kSegRows) / KPU;
+	static constexpr int COPIES = SEG_UNITS / 32; // cp.async per lane and segment
+	__device__ __forceinline__ static uint32_t rot(uint32_t lane) {
+		return KB == 8 ? (lane & 7u) : ((lane >> 1) & 3u);
+	}
+};
+
 __device__ __forceinline__ void cp_async_16(void *smem_dst, const void *gmem_src, uint64_t pol) {
 	const uint32_t d = static_cast<uint32_t>(__cvta_generic_to_shared(smem_dst));
 	asm volatile("cp.async.cg.shared.global.L2::cache_hint [%0], [%1], 16, %2;" ::"r"(d), "l"(gmem_src), "l"(pol)
@@ -424,10 +507,12 @@ __global__ void __launch_bounds__(BLOCK, MINB)
 	static_assert(UNITS == 8 || UNITS == 4, "a lane owns 8 units, processed in one or two batches");
 	constexpr int NWARPS = BLOCK / 32;
 	constexpr bool STAGED = Src::kStageable;
-	constexpr int SEG_UNITS = kSegRows / 2; // 256 units of 16 bytes
+	using Geo = StageGeo<Src::kKeyBytes>;
+	constexpr int SEG_UNITS = Geo::SEG_UNITS; // 16-byte units per segment
+	constexpr int BATCH = 2 * UNITS;          // keys per batch
 	// dynamic shared memory: [warp-private key double buffers (STAGED)][filter copy (SMEM_FILTER)]
 	extern __shared__ __align__(128) unsigned char s_dyn[];
-	ulonglong2 *const s_keys = reinterpret_cast<ulonglong2 *>(s_dyn);
+	uint4 *const s_keys = reinterpret_cast<uint4 *>(s_dyn);
 	uint64_t *const s_filter = reinterpret_cast<uint64_t *>(s_dyn + (STAGED ? NWARPS * 2 * SEG_UNITS * 16 : 0));
 	const uint32_t lane = threadIdx.x & 31u;
 	const uint32_t warp = threadIdx.x >> 5;
@@ -447,8 +532,8 @@ __global__ void __launch_bounds__(BLOCK, MINB)
 	}
 	const uint64_t stride = static_cast<uint64_t>(gridDim.x) * NWARPS;
 	const uint64_t full_segs = count / kSegRows; // segments below this one are complete
-	ulonglong2 *const my_buf = s_keys + warp * (2 * SEG_UNITS);
-	const uint32_t rot = lane & 7u;
+	uint4 *const my_buf = s_keys + warp * (2 * SEG_UNITS);
+	const uint32_t rot = Geo::rot(lane);
 
 	// Software pipeline with ONE staging call site: iteration i finishes segment `cur` (staged in iteration
 	// i-1 into buffer `par`) and stages segment `nxt` into the other buffer.  (A separate prologue call made
@@ -460,10 +545,10 @@ __global__ void __launch_bounds__(BLOCK, MINB)
 		if (STAGED) {
 			__syncwarp(); // every lane is done reading the buffer that is overwritten next
 			if (nxt < full_segs) {
-				const ulonglong2 *g = reinterpret_cast<const ulonglong2 *>(src.key_ptr()) + nxt * SEG_UNITS + lane;
-				ulonglong2 *s = my_buf + (par ^ 1u) * SEG_UNITS + lane;
+				const uint4 *g = reinterpret_cast<const uint4 *>(src.key_ptr()) + nxt * SEG_UNITS + lane;
+				uint4 *s = my_buf + (par ^ 1u) * SEG_UNITS + lane;
 #pragma unroll
-				for (int k = 0; k < 8; k++) {
+				for (int k = 0; k < Geo::COPIES; k++) {
 					cp_async_16(s + k * 32, g + k * 32, pol_keys);
 				}
 			}
@@ -480,23 +565,20 @@ __global__ void __launch_bounds__(BLOCK, MINB)
 			if (STAGED && cur < full_segs) {
 				cp_async_wait<1>();
 				__syncwarp();
-				const ulonglong2 *mine = my_buf + par * SEG_UNITS + lane * 8;
+				const uint4 *mine = my_buf + par * SEG_UNITS + lane * Geo::U;
 #pragma unroll
-				for (int b = 8 / UNITS - 1; b >= 0; b--) {
-					uint64_t h[2 * UNITS];
+				for (int b = 16 / BATCH - 1; b >= 0; b--) {
+					uint64_t h[BATCH];
 #pragma unroll
-					for (int u = 0; u < UNITS; u++) {
-						const ulonglong2 k = mine[(b * UNITS + u + rot) & 7u];
-						h[2 * u] = murmur64(k.x);
-						h[2 * u + 1] = murmur64(k.y);
+					for (int u = 0; u < BATCH / Geo::KPU; u++) {
+						Src::hash_unit(mine[(b * (BATCH / Geo::KPU) + u + rot) & (Geo::U - 1)], h + u * Geo::KPU);
 					}
-					hits = (hits << (2 * UNITS)) |
-					       test_batch<2 * UNITS, SMEM_FILTER, SLICED>(h, filter, s_filter, sector_mask, pol_filter,
-					                                                  slice_lo, slice_len);
+					hits = (hits << BATCH) | test_batch<BATCH, SMEM_FILTER, SLICED>(h, filter, s_filter, sector_mask,
+					                                                              pol_filter, slice_lo, slice_len);
 				}
-				// slot p held logical unit (p + rot) mod 8: rotate the 16-bit mask left by 2·rot
+				// slot p held logical unit (p + rot) mod U: rotate the 16-bit mask left by KPU·rot
 				const uint32_t twice = hits | (hits << 16);
-				hits = (twice >> (16u - 2u * rot)) & 0xffffu;
+				hits = (twice >> (16u - Geo::KPU * rot)) & 0xffffu;
 			} else {
 				const bool full = cur < full_segs;
 #pragma unroll
@@ -604,13 +686,14 @@ __global__ void __launch_bounds__(BLOCK, 2)
                            uint16_t *__restrict__ bucket_counts /* (P-1) × num_segs */) {
 	constexpr int NWARPS = BLOCK / 32;
 	constexpr bool STAGED = Src::kStageable;
-	constexpr int SEG_UNITS = kSegRows / 2;
+	using Geo = StageGeo<Src::kKeyBytes>;
+	constexpr int SEG_UNITS = Geo::SEG_UNITS;
 	constexpr int NREG = PartCfg<P>::NREG;
 	constexpr int CAP = PartCfg<P>::CAP;
 	constexpr int KEY_BYTES = STAGED ? NWARPS * 2 * SEG_UNITS * 16 : 0;
 	// dynamic shared memory: [warp-private key double buffers (STAGED)][warp-private record stage, (P-1)·CAP each]
 	extern __shared__ __align__(128) unsigned char s_dyn[];
-	ulonglong2 *const s_keys = reinterpret_cast<ulonglong2 *>(s_dyn);
+	uint4 *const s_keys = reinterpret_cast<uint4 *>(s_dyn);
 	const uint32_t lane = threadIdx.x & 31u;
 	const uint32_t warp = threadIdx.x >> 5;
 	uint2 *const stage = reinterpret_cast<uint2 *>(s_dyn + KEY_BYTES) + warp * ((P - 1) * CAP);
@@ -619,8 +702,8 @@ __global__ void __launch_bounds__(BLOCK, 2)
 	warm_slice(filter, 0u, 1u << kSliceShift, BLOCK);
 	const uint64_t stride = static_cast<uint64_t>(gridDim.x) * NWARPS;
 	const uint64_t full_segs = count / kSegRows;
-	ulonglong2 *const my_buf = s_keys + warp * (2 * SEG_UNITS);
-	const uint32_t rot = lane & 7u;
+	uint4 *const my_buf = s_keys + warp * (2 * SEG_UNITS);
+	const uint32_t rot = Geo::rot(lane);
 
 	constexpr uint64_t kNone = ~0ULL;
 	uint64_t cur = kNone;
@@ -629,10 +712,10 @@ __global__ void __launch_bounds__(BLOCK, 2)
 		if (STAGED) {
 			__syncwarp();
 			if (nxt < full_segs) {
-				const ulonglong2 *g = reinterpret_cast<const ulonglong2 *>(src.key_ptr()) + nxt * SEG_UNITS + lane;
-				ulonglong2 *s = my_buf + (par ^ 1u) * SEG_UNITS + lane;
+				const uint4 *g = reinterpret_cast<const uint4 *>(src.key_ptr()) + nxt * SEG_UNITS + lane;
+				uint4 *s = my_buf + (par ^ 1u) * SEG_UNITS + lane;
 #pragma unroll
-				for (int k = 0; k < 8; k++) {
+				for (int k = 0; k < Geo::COPIES; k++) {
 					cp_async_16(s + k * 32, g + k * 32, pol_keys);
 				}
 			}
@@ -645,12 +728,10 @@ __global__ void __launch_bounds__(BLOCK, 2)
 			if (staged_seg) {
 				cp_async_wait<1>();
 				__syncwarp();
-				const ulonglong2 *mine = my_buf + par * SEG_UNITS + lane * 8;
+				const uint4 *mine = my_buf + par * SEG_UNITS + lane * Geo::U;
 #pragma unroll
-				for (int u = 0; u < 8; u++) {
-					const ulonglong2 k = mine[(u + rot) & 7u];
-					h[2 * u] = murmur64(k.x);
-					h[2 * u + 1] = murmur64(k.y);
+				for (int u = 0; u < Geo::U; u++) {
+					Src::hash_unit(mine[(u + rot) & (Geo::U - 1)], h + u * Geo::KPU);
 				}
 			} else {
 				const bool full = cur < full_segs;
@@ -665,7 +746,7 @@ __global__ void __launch_bounds__(BLOCK, 2)
 					}
 				}
 			}
-			// slot i of a staged segment is row (lane·16 + ((i/2 + rot) mod 8)·2 + i%2) of the segment
+			// slot i of a staged segment is row (lane·16 + ((i/KPU + rot) mod U)·KPU + i%KPU) of the segment
 			const uint32_t unit_rot = staged_seg ? rot : 0u;
 
 			// pass 1: slice of every key; slice-0 lookups are issued; the other slices are counted
@@ -712,7 +793,8 @@ __global__ void __launch_bounds__(BLOCK, 2)
 					const uint32_t pos = packed_get<NREG>(run, s - 1u);
 					packed_add_slice<NREG>(run, s);
 					if (pos < static_cast<uint32_t>(CAP)) {
-						const uint32_t row9 = lane * 16u + ((((i >> 1) + unit_rot) & 7u) << 1) + (i & 1);
+						const uint32_t row9 =
+						    lane * 16u + (((i / Geo::KPU + unit_rot) & (Geo::U - 1)) * Geo::KPU) + (i % Geo::KPU);
 						stage[mul_lo_u32(s - 1u, CAP) + pos] =
 						    make_uint2((sector & ((1u << kSliceShift) - 1u)) | (row9 << kSliceShift),
 						               static_cast<uint32_t>(h[i] >> 32));
@@ -738,7 +820,7 @@ __global__ void __launch_bounds__(BLOCK, 2)
 			}
 			if (staged_seg) {
 				const uint32_t twice = hits | (hits << 16);
-				hits = (twice >> (16u - 2u * rot)) & 0xffffu;
+				hits = (twice >> (16u - Geo::KPU * rot)) & 0xffffu;
 			}
 			bitmap16[cur * 32 + lane] = static_cast<uint16_t>(hits);
 			// copy-out: the warp's records of every slice leave as contiguous 16-byte stores
@@ -1296,6 +1378,15 @@ static inline bool is_flat_u64(const DevCols &cols) {
 	return (c.type == RPT_INT64 || c.type == RPT_UINT64) && !c.sel && !c.validity &&
 	       (reinterpret_cast<uintptr_t>(c.data) & 15u) == 0;
 }
+// ... and a single flat 4-byte integer column (INT32 / UINT32; DATE is INT32 physically) its own.
+static inline bool is_flat_u32(const DevCols &cols) {
+	if (cols.n != 1) {
+		return false;
+	}
+	const DevCol &c = cols.c[0];
+	return (c.type == RPT_INT32 || c.type == RPT_UINT32) && !c.sel && !c.validity &&
+	       (reinterpret_cast<uintptr_t>(c.data) & 15u) == 0;
+}
 
 static inline bool use_smem_filter(const DeviceInfo &dev, uint64_t num_sectors) {
 	// the phased kernel also keeps 64 KiB of key double buffers in shared memory
@@ -1422,6 +1513,11 @@ cudaError_t launch_build(const DeviceInfo &dev, const DevCols &cols, uint64_t co
 		return agg ? launch_build_t<FlatU64Src, true>(dev, src, count, words, num_sectors, stream, launches)
 		           : launch_build_t<FlatU64Src, false>(dev, src, count, words, num_sectors, stream, launches);
 	}
+	if (is_flat_u32(cols)) {
+		FlatU32Src src {reinterpret_cast<const uint32_t *>(cols.c[0].data)};
+		return agg ? launch_build_t<FlatU32Src, true>(dev, src, count, words, num_sectors, stream, launches)
+		           : launch_build_t<FlatU32Src, false>(dev, src, count, words, num_sectors, stream, launches);
+	}
 	GenericSrc src {cols};
 	return agg ? launch_build_t<GenericSrc, true>(dev, src, count, words, num_sectors, stream, launches)
 	           : launch_build_t<GenericSrc, false>(dev, src, count, words, num_sectors, stream, launches);
@@ -1481,7 +1577,7 @@ static cudaError_t launch_probe_phased(const DeviceInfo &dev, const Src &src, ui
 	constexpr int BLOCK = kProbeBlock;
 	auto pass = probe_bitmap_kernel<Src, BLOCK, MINB, UNITS, SMEM, SLICED>;
 	const uint64_t num_segs = ceil_div(count, kSegRows);
-	const size_t smem = (Src::kStageable ? static_cast<size_t>(BLOCK / 32) * 2 * kSegRows * 8 : 0) +
+	const size_t smem = (Src::kStageable ? static_cast<size_t>(BLOCK / 32) * 2 * kSegRows * Src::kKeyBytes : 0) +
 	                    (SMEM ? num_sectors * sizeof(uint64_t) : 0);
 	cudaError_t e = cudaFuncSetAttribute(pass, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
 	if (e != cudaSuccess) {
@@ -1540,7 +1636,7 @@ static cudaError_t launch_probe_partitioned(const DeviceInfo &dev, const Src &sr
 	auto part = probe_partition_kernel<Src, BLOCK, P>;
 	auto bucket = probe_bucket_kernel<CAP>;
 	const uint64_t num_segs = ceil_div(count, kSegRows);
-	const size_t smem = (Src::kStageable ? static_cast<size_t>(BLOCK / 32) * 2 * kSegRows * 8 : 0) +
+	const size_t smem = (Src::kStageable ? static_cast<size_t>(BLOCK / 32) * 2 * kSegRows * Src::kKeyBytes : 0) +
 	                    static_cast<size_t>(BLOCK / 32) * (P - 1) * CAP * sizeof(uint2);
 	cudaError_t e = cudaFuncSetAttribute(part, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
 	if (e != cudaSuccess) {
@@ -1647,6 +1743,11 @@ cudaError_t launch_probe(const DeviceInfo &dev, const DevCols &cols, uint64_t co
 	}
 	if (is_flat_u64(cols)) {
 		FlatU64Src src {reinterpret_cast<const uint64_t *>(cols.c[0].data)};
+		return launch_probe_src(dev, src, count, words, num_sectors, sel_out, found_out, row_offset, translate, scratch,
+		                        stream, launches);
+	}
+	if (is_flat_u32(cols)) {
+		FlatU32Src src {reinterpret_cast<const uint32_t *>(cols.c[0].data)};
 		return launch_probe_src(dev, src, count, words, num_sectors, sel_out, found_out, row_offset, translate, scratch,
 		                        stream, launches);
 	}

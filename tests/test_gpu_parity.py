@@ -363,6 +363,23 @@ def test_filters_beyond_one_l2_slice(rpt, oracle, est, slices):
     check_build_probe(rpt, oracle, est, rpt.host_col(k32), k32.size, rpt.host_col(p32, validity=val), p32.size)
 
 
+@pytest.mark.parametrize("dt", [np.int32, np.uint32])
+@pytest.mark.parametrize("est,m", [(2000, 300_001), (3_000_000, 2_000_003), (100_000_000, 1_000_001),
+                                   (300_000_000, 700_001)])
+def test_flat_4_byte_keys_every_regime(rpt, oracle, dt, est, m):
+    """Flat INT32 / UINT32 columns take the staged 4-byte path (FlatU32Src): shared-memory filter, L2-resident
+    filter, sector-range passes, partitioned probe; ragged lengths leave a partial last segment."""
+    rng = np.random.default_rng(est + m)
+    info = np.iinfo(dt)
+    n = min(est, 250_000)
+    keys = rng.integers(info.min, info.max, n, dtype=dt, endpoint=True)
+    members = keys[rng.integers(0, n, m // 5)]
+    probe = np.concatenate([members, rng.integers(info.min, info.max, m - members.size, dtype=dt, endpoint=True)])
+    rng.shuffle(probe)
+    assert probe.size == m
+    check_build_probe(rpt, oracle, est, rpt.host_col(keys), n, rpt.host_col(probe), m)
+
+
 def test_duplicate_heavy_keys_small_filter(rpt, oracle):
     """Warp-aggregated atomics path: many lanes of a warp hit the same sector."""
     rng = np.random.default_rng(59)

@@ -13,12 +13,13 @@ m = int(float(sys.argv[1])) if len(sys.argv) > 1 else 1_000_000_000
 reps = int(sys.argv[2]) if len(sys.argv) > 2 else 5
 cases = [int(float(x)) for x in (sys.argv[3] if len(sys.argv) > 3 else "80000,1e7,4e7,1e8").split(",")]
 ppm = int(os.environ.get("SWEEP_PPM", "100000"))
+ktype = os.environ.get("SWEEP_TYPE", "int64")  # int64 | int32 (low 31 bits of the synthetic keys: GenericSrc / 4-byte path)
 dev = torch.device("cuda", 0)
 stream = torch.cuda.Stream(device=dev)
 torch.cuda.set_stream(stream)
 sh = stream.cuda_stream
 knobs = {k: os.environ[k] for k in ("RPT_PROBE_UNITS", "RPT_SLICE_MIB", "RPT_GPU_LIB") if k in os.environ}
-print(f"# m={m} reps={reps} ppm={ppm} knobs={knobs}", flush=True)
+print(f"# m={m} reps={reps} ppm={ppm} type={ktype} knobs={knobs}", flush=True)
 dp = torch.empty(m, dtype=torch.int64, device=dev)
 dsel = torch.empty(m, dtype=torch.int32, device=dev)
 dfound = torch.zeros(1, dtype=torch.int64, device=dev)
@@ -27,7 +28,12 @@ for n in cases:
     rpt.synth_build_keys(dk, 0, n, stream=sh)
     rpt.synth_probe_keys(dp, 0, m, n, ppm, stream=sh)
     bf = rpt.PTBloomFilter(0).Initialize(n)
-    kc, pc = rpt.device_col(dk, rpt.INT64), rpt.device_col(dp, rpt.INT64)
+    if ktype == "int32":
+        dk32, dp32 = (dk & 0x7fffffff).to(torch.int32), (dp & 0x7fffffff).to(torch.int32)
+        torch.cuda.synchronize()
+        kc, pc = rpt.device_col(dk32, rpt.INT32), rpt.device_col(dp32, rpt.INT32)
+    else:
+        kc, pc = rpt.device_col(dk, rpt.INT64), rpt.device_col(dp, rpt.INT64)
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
     for _ in range(2):
         bf.Reset(n, sh)
@@ -48,7 +54,7 @@ for n in cases:
     F = bf.num_sectors * 8
     bm, pm = ev[0].elapsed_time(ev[1]) / reps, ev[2].elapsed_time(ev[3]) / reps
     found = int(dfound.item())
-    algo = 8 * m + 4 * found + F
+    algo = (4 if ktype == "int32" else 8) * m + 4 * found + F
     print(f"n={n:>10} F={F / 2**20:8.3f} MiB  build {bm:7.3f} ms {n / bm / 1e6:7.1f} Gkeys/s | probe {pm:7.3f} ms "
           f"{m / pm / 1e6:7.1f} Gkeys/s  {algo / pm / 1e6:7.1f} GB/s algorithmic  found {found}", flush=True)
     bf.close()
