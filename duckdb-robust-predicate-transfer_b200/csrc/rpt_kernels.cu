@@ -72,10 +72,19 @@ __device__ __forceinline__ uint32_t lanemask_lt() {
 // key sources.  load2(row0, count, h0, h1) hashes rows row0 and row0+1 (row0 is even) and
 // returns a 2-bit validity (rows ≥ count are invalid and must not be read).
 // ---------------------------------------------------------------------------------------------
-struct FlatU64Src { // one flat int64 / uint64 column, no NULLs, base 16-byte aligned
+// Validity of flat columns (bit set = valid, row-indexed): NULL rows hash to NULL_HASH (vector_hash.cpp:16-23).
+__device__ __forceinline__ uint32_t valid_pair(const uint64_t *validity, uint64_t row0) { // rows row0 (even), row0+1
+	return static_cast<uint32_t>(__ldg(validity + (row0 >> 6)) >> (row0 & 63)) & 3u;
+}
+__device__ __forceinline__ bool valid_row(const uint64_t *validity, uint64_t row) {
+	return (__ldg(validity + (row >> 6)) >> (row & 63)) & 1ULL;
+}
+
+struct FlatU64Src { // one flat int64 / uint64 column (optional validity bitmap, no selection), base 16-byte aligned
 	static constexpr bool kStageable = true; // a segment is 512 contiguous 8-byte keys: cp.async-able
 	static constexpr int kKeyBytes = 8;
 	const uint64_t *keys;
+	const uint64_t *validity; // nullptr = all valid
 	// KPU hashes out of one staged 16-byte unit
 	__device__ __forceinline__ static void hash_unit(const uint4 &v, uint64_t *h) {
 		h[0] = murmur64((static_cast<uint64_t>(v.y) << 32) | v.x);
@@ -85,6 +94,9 @@ struct FlatU64Src { // one flat int64 / uint64 column, no NULLs, base 16-byte al
 		return keys;
 	}
 	__device__ __forceinline__ uint64_t hash_at(uint64_t row, uint64_t pol) const {
+		if (validity && !valid_row(validity, row)) {
+			return kNullHash;
+		}
 		return murmur64(ld_stream_u64(keys + row, pol));
 	}
 	// unchecked: rows row0 + r*stride (+0,+1), r < R, all in range.  All R 128-bit loads are issued
@@ -102,21 +114,28 @@ struct FlatU64Src { // one flat int64 / uint64 column, no NULLs, base 16-byte al
 			h[2 * r] = murmur64(k[r].x);
 			h[2 * r + 1] = murmur64(k[r].y);
 		}
+		if (validity) { // kernel-uniform
+#pragma unroll
+			for (int r = 0; r < R; r++) {
+				const uint32_t v = valid_pair(validity, row0 + r * stride);
+				h[2 * r] = (v & 1u) ? h[2 * r] : kNullHash;
+				h[2 * r + 1] = (v & 2u) ? h[2 * r + 1] : kNullHash;
+			}
+		}
 	}
 	__device__ __forceinline__ uint32_t load2(uint64_t row0, uint64_t count, uint64_t pol, uint64_t &h0,
 	                                          uint64_t &h1) const {
-		if (row0 + 1 < count) {
-			const ulonglong2 k = ld_stream_v2(keys + row0, pol);
-			h0 = murmur64(k.x);
-			h1 = murmur64(k.y);
-			return 3u;
-		}
 		h0 = h1 = 0;
+		uint32_t v = 0;
 		if (row0 < count) {
-			h0 = murmur64(ld_stream_u64(keys + row0, pol));
-			return 1u;
+			h0 = hash_at(row0, pol);
+			v = 1u;
 		}
-		return 0u;
+		if (row0 + 1 < count) {
+			h1 = hash_at(row0 + 1, pol);
+			v |= 2u;
+		}
+		return v;
 	}
 };
 
@@ -136,6 +155,7 @@ struct FlatU32Src {
 	static constexpr bool kStageable = true; // a segment is 512 contiguous 4-byte keys = 2 KiB
 	static constexpr int kKeyBytes = 4;
 	const uint32_t *keys;
+	const uint64_t *validity; // nullptr = all valid
 	__device__ __forceinline__ static void hash_unit(const uint4 &v, uint64_t *h) {
 		h[0] = murmur64(v.x);
 		h[1] = murmur64(v.y);
@@ -146,6 +166,9 @@ struct FlatU32Src {
 		return keys;
 	}
 	__device__ __forceinline__ uint64_t hash_at(uint64_t row, uint64_t pol) const {
+		if (validity && !valid_row(validity, row)) {
+			return kNullHash;
+		}
 		return murmur64(ld_stream_u32(keys + row, pol));
 	}
 	template <int R>
@@ -161,27 +184,35 @@ struct FlatU32Src {
 			h[2 * r] = murmur64(k[r].x);
 			h[2 * r + 1] = murmur64(k[r].y);
 		}
+		if (validity) { // kernel-uniform
+#pragma unroll
+			for (int r = 0; r < R; r++) {
+				const uint32_t v = valid_pair(validity, row0 + r * stride);
+				h[2 * r] = (v & 1u) ? h[2 * r] : kNullHash;
+				h[2 * r + 1] = (v & 2u) ? h[2 * r + 1] : kNullHash;
+			}
+		}
 	}
 	__device__ __forceinline__ uint32_t load2(uint64_t row0, uint64_t count, uint64_t pol, uint64_t &h0,
 	                                          uint64_t &h1) const {
-		if (row0 + 1 < count) {
-			const uint2 k = ld_stream_v2_u32(keys + row0, pol);
-			h0 = murmur64(k.x);
-			h1 = murmur64(k.y);
-			return 3u;
-		}
 		h0 = h1 = 0;
+		uint32_t v = 0;
 		if (row0 < count) {
-			h0 = murmur64(ld_stream_u32(keys + row0, pol));
-			return 1u;
+			h0 = hash_at(row0, pol);
+			v = 1u;
 		}
-		return 0u;
+		if (row0 + 1 < count) {
+			h1 = hash_at(row0 + 1, pol);
+			v |= 2u;
+		}
+		return v;
 	}
 };
 
 struct GenericSrc { // any type / sel / validity / multi-column combination
 	static constexpr bool kStageable = false;
 	static constexpr int kKeyBytes = 8; // unused (never staged)
+	static constexpr const uint64_t *validity = nullptr; // NULLs are handled per row by hash_row
 	__device__ __forceinline__ static void hash_unit(const uint4 &, uint64_t *) {
 	}
 	DevCols cols;
@@ -468,6 +499,22 @@ __device__ __forceinline__ uint32_t sector_test_fma(uint64_t w, uint32_t hi) {
 	return b & 1u;
 }
 
+// Staged segments of a nullable flat column: the lane's 16 validity bits (logical row order) are rotated into
+// slot order and NULL rows take NULL_HASH.  N keys starting at slot `first`.
+template <int N>
+__device__ __forceinline__ void null_fix(uint64_t (&h)[N], uint32_t valid_slots, int first) {
+#pragma unroll
+	for (int i = 0; i < N; i++) {
+		h[i] = ((valid_slots >> (first + i)) & 1u) ? h[i] : kNullHash;
+	}
+}
+__device__ __forceinline__ uint32_t valid_slots_of(const uint64_t *validity, uint64_t seg, uint32_t lane,
+                                                   uint32_t rot_bits) {
+	const uint32_t v = __ldg(reinterpret_cast<const unsigned short *>(validity) + seg * 32 + lane);
+	const uint32_t twice = v | (v << 16); // slot i holds logical bit (i + rot_bits) mod 16: rotate right
+	return (twice >> rot_bits) & 0xffffu;
+}
+
 // Lookup + test of N hashed keys; bit i of the result is the hit flag of h[i].
 template <int N, bool SMEM_FILTER, bool SLICED>
 __device__ __forceinline__ uint32_t test_batch(const uint64_t (&h)[N], const uint64_t *__restrict__ filter,
@@ -566,12 +613,16 @@ __global__ void __launch_bounds__(BLOCK, MINB)
 				cp_async_wait<1>();
 				__syncwarp();
 				const uint4 *mine = my_buf + par * SEG_UNITS + lane * Geo::U;
+				const uint32_t vslots = src.validity ? valid_slots_of(src.validity, cur, lane, Geo::KPU * rot) : 0xffffu;
 #pragma unroll
 				for (int b = 16 / BATCH - 1; b >= 0; b--) {
 					uint64_t h[BATCH];
 #pragma unroll
 					for (int u = 0; u < BATCH / Geo::KPU; u++) {
 						Src::hash_unit(mine[(b * (BATCH / Geo::KPU) + u + rot) & (Geo::U - 1)], h + u * Geo::KPU);
+					}
+					if (src.validity) { // kernel-uniform
+						null_fix<BATCH>(h, vslots, b * BATCH);
 					}
 					hits = (hits << BATCH) | test_batch<BATCH, SMEM_FILTER, SLICED>(h, filter, s_filter, sector_mask,
 					                                                              pol_filter, slice_lo, slice_len);
@@ -732,6 +783,9 @@ __global__ void __launch_bounds__(BLOCK, 2)
 #pragma unroll
 				for (int u = 0; u < Geo::U; u++) {
 					Src::hash_unit(mine[(u + rot) & (Geo::U - 1)], h + u * Geo::KPU);
+				}
+				if (src.validity) { // kernel-uniform
+					null_fix<16>(h, valid_slots_of(src.validity, cur, lane, Geo::KPU * rot), 0);
 				}
 			} else {
 				const bool full = cur < full_segs;
@@ -1375,8 +1429,8 @@ static inline bool is_flat_u64(const DevCols &cols) {
 		return false;
 	}
 	const DevCol &c = cols.c[0];
-	return (c.type == RPT_INT64 || c.type == RPT_UINT64) && !c.sel && !c.validity &&
-	       (reinterpret_cast<uintptr_t>(c.data) & 15u) == 0;
+	return (c.type == RPT_INT64 || c.type == RPT_UINT64) && !c.sel &&
+	       (reinterpret_cast<uintptr_t>(c.data) & 15u) == 0 && (reinterpret_cast<uintptr_t>(c.validity) & 7u) == 0;
 }
 // ... and a single flat 4-byte integer column (INT32 / UINT32; DATE is INT32 physically) its own.
 static inline bool is_flat_u32(const DevCols &cols) {
@@ -1384,8 +1438,8 @@ static inline bool is_flat_u32(const DevCols &cols) {
 		return false;
 	}
 	const DevCol &c = cols.c[0];
-	return (c.type == RPT_INT32 || c.type == RPT_UINT32) && !c.sel && !c.validity &&
-	       (reinterpret_cast<uintptr_t>(c.data) & 15u) == 0;
+	return (c.type == RPT_INT32 || c.type == RPT_UINT32) && !c.sel &&
+	       (reinterpret_cast<uintptr_t>(c.data) & 15u) == 0 && (reinterpret_cast<uintptr_t>(c.validity) & 7u) == 0;
 }
 
 static inline bool use_smem_filter(const DeviceInfo &dev, uint64_t num_sectors) {
@@ -1509,12 +1563,12 @@ cudaError_t launch_build(const DeviceInfo &dev, const DevCols &cols, uint64_t co
 	// warp-aggregate only where same-sector collisions inside a warp are likely
 	const bool agg = num_sectors <= 4096;
 	if (is_flat_u64(cols)) {
-		FlatU64Src src {reinterpret_cast<const uint64_t *>(cols.c[0].data)};
+		FlatU64Src src {reinterpret_cast<const uint64_t *>(cols.c[0].data), cols.c[0].validity};
 		return agg ? launch_build_t<FlatU64Src, true>(dev, src, count, words, num_sectors, stream, launches)
 		           : launch_build_t<FlatU64Src, false>(dev, src, count, words, num_sectors, stream, launches);
 	}
 	if (is_flat_u32(cols)) {
-		FlatU32Src src {reinterpret_cast<const uint32_t *>(cols.c[0].data)};
+		FlatU32Src src {reinterpret_cast<const uint32_t *>(cols.c[0].data), cols.c[0].validity};
 		return agg ? launch_build_t<FlatU32Src, true>(dev, src, count, words, num_sectors, stream, launches)
 		           : launch_build_t<FlatU32Src, false>(dev, src, count, words, num_sectors, stream, launches);
 	}
@@ -1742,12 +1796,12 @@ cudaError_t launch_probe(const DeviceInfo &dev, const DevCols &cols, uint64_t co
 		return cudaMemsetAsync(found_out, 0, sizeof(uint64_t), stream);
 	}
 	if (is_flat_u64(cols)) {
-		FlatU64Src src {reinterpret_cast<const uint64_t *>(cols.c[0].data)};
+		FlatU64Src src {reinterpret_cast<const uint64_t *>(cols.c[0].data), cols.c[0].validity};
 		return launch_probe_src(dev, src, count, words, num_sectors, sel_out, found_out, row_offset, translate, scratch,
 		                        stream, launches);
 	}
 	if (is_flat_u32(cols)) {
-		FlatU32Src src {reinterpret_cast<const uint32_t *>(cols.c[0].data)};
+		FlatU32Src src {reinterpret_cast<const uint32_t *>(cols.c[0].data), cols.c[0].validity};
 		return launch_probe_src(dev, src, count, words, num_sectors, sel_out, found_out, row_offset, translate, scratch,
 		                        stream, launches);
 	}

@@ -363,12 +363,19 @@ def test_filters_beyond_one_l2_slice(rpt, oracle, est, slices):
     check_build_probe(rpt, oracle, est, rpt.host_col(k32), k32.size, rpt.host_col(p32, validity=val), p32.size)
 
 
-@pytest.mark.parametrize("dt", [np.int32, np.uint32])
+def random_validity(rng, n, p_valid):
+    bits = np.packbits(rng.random(n) < p_valid, bitorder="little")
+    return np.concatenate([bits, np.zeros((-len(bits)) % 8, dtype=np.uint8)]).view(np.uint64)
+
+
+@pytest.mark.parametrize("nulls", [False, True])
+@pytest.mark.parametrize("dt", [np.int32, np.uint32, np.int64])
 @pytest.mark.parametrize("est,m", [(2000, 300_001), (3_000_000, 2_000_003), (100_000_000, 1_000_001),
                                    (300_000_000, 700_001)])
-def test_flat_4_byte_keys_every_regime(rpt, oracle, dt, est, m):
-    """Flat INT32 / UINT32 columns take the staged 4-byte path (FlatU32Src): shared-memory filter, L2-resident
-    filter, sector-range passes, partitioned probe; ragged lengths leave a partial last segment."""
+def test_flat_columns_every_regime(rpt, oracle, dt, nulls, est, m):
+    """Flat INT32 / UINT32 / INT64 columns, with and without a validity bitmap, take the staged paths (FlatU32Src /
+    FlatU64Src): shared-memory filter, L2-resident filter, sector-range passes, partitioned probe; ragged lengths
+    leave a partial last segment.  NULL rows hash to NULL_HASH on both sides (they are inserted and probed)."""
     rng = np.random.default_rng(est + m)
     info = np.iinfo(dt)
     n = min(est, 250_000)
@@ -377,7 +384,9 @@ def test_flat_4_byte_keys_every_regime(rpt, oracle, dt, est, m):
     probe = np.concatenate([members, rng.integers(info.min, info.max, m - members.size, dtype=dt, endpoint=True)])
     rng.shuffle(probe)
     assert probe.size == m
-    check_build_probe(rpt, oracle, est, rpt.host_col(keys), n, rpt.host_col(probe), m)
+    kv = random_validity(rng, n, 0.95) if nulls else None
+    pv = random_validity(rng, m, 0.8) if nulls else None
+    check_build_probe(rpt, oracle, est, rpt.host_col(keys, validity=kv), n, rpt.host_col(probe, validity=pv), m)
 
 
 def test_duplicate_heavy_keys_small_filter(rpt, oracle):
