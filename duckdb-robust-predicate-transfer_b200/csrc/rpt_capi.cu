@@ -159,6 +159,19 @@ static int fill_device_info(int device, DeviceInfo *out) {
 		uint64_t keep = ~0ULL;
 		cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
 	}
+	// L2 set-aside for persisting (evict_last) lines: the filter slice of a pass lives there, out of reach of the
+	// key stream.  RPT_L2_PERSIST_MIB overrides (0 = leave the device default).
+	{
+		const char *e = getenv("RPT_L2_PERSIST_MIB");
+		const long mib = e ? atol(e) : -1;
+		if (mib > 0) {
+			size_t want = static_cast<size_t>(mib) << 20;
+			if (want > static_cast<size_t>(prop.persistingL2CacheMaxSize)) {
+				want = prop.persistingL2CacheMaxSize;
+			}
+			cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, want);
+		}
+	}
 	cudaGetLastError();
 	out->device = device;
 	out->sm_count = prop.multiProcessorCount;
