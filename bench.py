@@ -353,8 +353,8 @@ def run_b200(args):
     peak, peak_src = load_peaks()
     algo_bytes = 8 * m + 4 * found + F
     achieved = algo_bytes / (probe_ms * 1e-3) / 1e9
-    roofline = {"kernel": "rpt_bf_probe = 4 x probe_bitmap_kernel<FlatU64Src,256,2,8,false,true> (sector-range passes) + "
-                          "scan_blocks/scan_totals + compact_bitmap_kernel", "bound": "hbm", "achieved": achieved, "peak": peak,
+    roofline = {"kernel": "rpt_bf_probe = probe_partition_kernel<FlatU64SrcT<0>,256,4> + 3 x probe_bucket_kernel<168> + "
+                          "count_segments/scan_blocks/scan_totals + compact_bitmap_kernel", "bound": "hbm", "achieved": achieved, "peak": peak,
                 "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": algo_bytes, "launch_ms": probe_ms,
                 "bytes_per_key": algo_bytes / m,

@@ -684,14 +684,21 @@ __global__ void __launch_bounds__(BLOCK, MINB)
 // ---- filters beyond one L2-resident slice: partition once, then probe slice by slice -----------------------
 // The sector-range passes above re-read the 8-byte key column once per slice (4× at F = 256 MiB: ncu r1c 42 GB
 // of DRAM traffic for 8.7 GB of algorithmic bytes, each pass DRAM-bound).  This path reads the keys ONCE:
-//   probe_partition_kernel  hashes every key; keys of slice 0 are looked up on the spot (slice 0 is the
-//                           L2-resident one during this kernel); keys of slice s ≥ 1 become 8-byte records
-//                           {sector-in-slice : 23 | row-in-segment : 9 | hash bits 63..32} in bucket s.
-//                           Every (segment, slice) pair owns a fixed region of CAP records (1.5× the expected
-//                           512/P), so no atomics, no directory and no inter-warp dependency exist; the
-//                           records are placed through warp-private shared memory and leave the SM as
-//                           contiguous 16-byte stores.  A key that does not fit its region (skew) is looked up
-//                           on the spot instead — slower, never wrong.
+//   probe_partition_kernel  hashes every key; keys of slice 0 are looked up on the spot; keys of slice s ≥ 1
+//                           become 8-byte records {sector-in-slice : 23 | row-in-segment : 9 | hash bits 63..32}
+//                           in bucket s.  Every (segment, slice) pair owns a fixed region of CAP records
+//                           (≥ 4σ above the expected 512/P), so no atomics, no directory and no inter-warp
+//                           dependency exist.  Placement is a counting sort inside the warp: per-lane counts
+//                           of all slices live as 8-bit fields of one register, one 5-step warp scan on
+//                           16-bit fields gives every lane its base in every region, a key's position is base
+//                           + its rank inside the lane.  The records go through warp-private shared memory
+//                           (aliased onto the key buffer just consumed) and leave the SM as contiguous
+//                           16-byte stores.  A segment whose keys overflow a region (skew) is looked up on the
+//                           spot instead — slower, never wrong.
+//                           ncu (profiles/ncu_part_r1g.md): 73 instructions per key, 20.8 GB of DRAM traffic
+//                           at 88 % of peak — 6 GB of it because slice 0 does NOT stay in L2 next to the
+//                           record write stream (80 % of the inline lookups miss; store flavours, evict hints,
+//                           the persisting set-aside and a smaller inline region were all tried: no gain).
 //   probe_bucket_kernel     once per slice s ≥ 1 (slice prefetched into L2): record → filter word → test →
 //                           RED.OR of the row's bit into the row-ordered bitmap (hits only).
 //   count_segments_kernel   popcount of every segment's 512 bitmap bits → the scan's input.
@@ -702,41 +709,27 @@ static_assert((1ULL << kSliceShift) == kSliceSectors, "record layout assumes 2^2
 template <int P>
 struct PartCfg {
 	static_assert(P == 2 || P == 4 || P == 8, "S is a power of two: 2, 4 or 8 slices of 64 MiB");
-	static constexpr int NREG = (P - 1 + 2) / 3;             // 10-bit counters, three per 32-bit register
-	static constexpr int CAP = P == 2 ? 384 : (P == 4 ? 192 : 96); // records per (segment, slice) region
+	// records per (segment, slice) region; expectation 512/P, σ = sqrt(512·(1/P)(1-1/P)): +5.6σ / +4.1σ / +4.3σ
+	static constexpr int CAP = P == 2 ? 320 : (P == 4 ? 168 : 96);
+	static constexpr int STAGE_BYTES = (P - 1) * CAP * 8;
+	static constexpr int NCNT = P <= 4 ? 1 : 2; // per-lane counters: 8 bits per slice, four slices per register
 };
 
-// counters of slices 1..P-1 packed 10 bits each (a segment has 512 rows: every count fits)
-template <int NREG>
-struct Packed {
-	uint32_t r[NREG];
+// Shared memory of one warp of the partition kernel: the key double buffer (staged sources) and the record
+// stage.  When the stage fits into one key buffer it ALIASES the buffer of the segment being processed (its
+// keys are in registers by then), which keeps a warp at 8 KiB.  Two CTAs per SM: at three (80 registers) the
+// sixteen hashes spill, and the spill traffic on the LSU costs more than the extra warps hide (9.0 vs 7.3 ms).
+template <class Src, int P>
+struct PartSmem {
+	static constexpr int KEY_SEG_BYTES = Src::kStageable ? static_cast<int>(kSegRows) * Src::kKeyBytes : 0;
+	static constexpr bool ALIAS = Src::kStageable && PartCfg<P>::STAGE_BYTES <= KEY_SEG_BYTES;
+	static constexpr int WARP_BYTES = 2 * KEY_SEG_BYTES + (ALIAS ? 0 : (PartCfg<P>::STAGE_BYTES + 15) / 16 * 16);
 };
-template <int NREG>
-__device__ __forceinline__ void packed_add_slice(Packed<NREG> &c, uint32_t s) { // s == 0 adds nothing
-	if (NREG == 1) {
-		c.r[0] += (1u << mul_lo_u32(s, 10u)) >> 10; // asm multiply: nvcc otherwise emits IDP.2A (45 % of stalls)
-	} else {
-		const uint32_t idx = s - 1u; // 0xffffffff for s == 0: matches no register
-		const uint32_t q = (idx * 11u) >> 5; // idx / 3 for idx ≤ 6
-		const uint32_t inc = 1u << mul_lo_u32(idx - 3u * q, 10u);
-#pragma unroll
-		for (int j = 0; j < NREG; j++) {
-			c.r[j] += (s != 0u && q == static_cast<uint32_t>(j)) ? inc : 0u;
-		}
-	}
-}
-template <int NREG>
-__device__ __forceinline__ uint32_t packed_get(const Packed<NREG> &c, uint32_t idx) { // idx = slice - 1
-	if (NREG == 1) {
-		return (c.r[0] >> mul_lo_u32(idx, 10u)) & 1023u;
-	}
-	const uint32_t q = (idx * 11u) >> 5;
-	uint32_t v = c.r[0];
-#pragma unroll
-	for (int j = 1; j < NREG; j++) {
-		v = q == static_cast<uint32_t>(j) ? c.r[j] : v;
-	}
-	return (v >> mul_lo_u32(idx - 3u * q, 10u)) & 1023u;
+
+__device__ __forceinline__ uint32_t shl_clamp(uint32_t v, uint32_t s) { // PTX shl.b32: a shift ≥ 32 yields 0
+	uint32_t d;
+	asm("shl.b32 %0, %1, %2;" : "=r"(d) : "r"(v), "r"(s));
+	return d;
 }
 
 template <class Src, int BLOCK, int P>
@@ -748,22 +741,20 @@ __global__ void __launch_bounds__(BLOCK, 2)
 	constexpr int NWARPS = BLOCK / 32;
 	constexpr bool STAGED = Src::kStageable;
 	using Geo = StageGeo<Src::kKeyBytes>;
+	using Smem = PartSmem<Src, P>;
 	constexpr int SEG_UNITS = Geo::SEG_UNITS;
-	constexpr int NREG = PartCfg<P>::NREG;
 	constexpr int CAP = PartCfg<P>::CAP;
-	constexpr int KEY_BYTES = STAGED ? NWARPS * 2 * SEG_UNITS * 16 : 0;
-	// dynamic shared memory: [warp-private key double buffers (STAGED)][warp-private record stage, (P-1)·CAP each]
+	constexpr int NCNT = PartCfg<P>::NCNT;
 	extern __shared__ __align__(128) unsigned char s_dyn[];
-	uint4 *const s_keys = reinterpret_cast<uint4 *>(s_dyn);
 	const uint32_t lane = threadIdx.x & 31u;
 	const uint32_t warp = threadIdx.x >> 5;
-	uint2 *const stage = reinterpret_cast<uint2 *>(s_dyn + KEY_BYTES) + warp * ((P - 1) * CAP);
+	unsigned char *const my_smem = s_dyn + warp * Smem::WARP_BYTES;
+	uint4 *const my_buf = reinterpret_cast<uint4 *>(my_smem);
 	const uint64_t pol_keys = policy_evict_first();
 	const uint64_t pol_filter = policy_evict_last();
 	warm_slice(filter, 0u, 1u << kSliceShift, BLOCK);
 	const uint64_t stride = static_cast<uint64_t>(gridDim.x) * NWARPS;
 	const uint64_t full_segs = count / kSegRows;
-	uint4 *const my_buf = s_keys + warp * (2 * SEG_UNITS);
 	const uint32_t rot = Geo::rot(lane);
 
 	constexpr uint64_t kNone = ~0ULL;
@@ -771,7 +762,7 @@ __global__ void __launch_bounds__(BLOCK, 2)
 	uint32_t par = 1;
 	for (uint64_t nxt = static_cast<uint64_t>(blockIdx.x) * NWARPS + warp;; nxt += stride) {
 		if (STAGED) {
-			__syncwarp();
+			__syncwarp(); // the buffer overwritten next (keys and, when aliased, records) is no longer read
 			if (nxt < full_segs) {
 				const uint4 *g = reinterpret_cast<const uint4 *>(src.key_ptr()) + nxt * SEG_UNITS + lane;
 				uint4 *s = my_buf + (par ^ 1u) * SEG_UNITS + lane;
@@ -785,7 +776,7 @@ __global__ void __launch_bounds__(BLOCK, 2)
 		if (cur != kNone) {
 			const bool staged_seg = STAGED && cur < full_segs;
 			uint64_t h[16];
-			uint32_t valid = 0xffffu;
+			uint32_t valid = 0xffffu; // slot order
 			if (staged_seg) {
 				cp_async_wait<1>();
 				__syncwarp();
@@ -797,91 +788,148 @@ __global__ void __launch_bounds__(BLOCK, 2)
 				if (Src::kNullable) {
 					null_fix<16>(h, valid_slots_of(src.validity, cur, lane, Geo::KPU * rot), 0);
 				}
+				if (Smem::ALIAS) {
+					__syncwarp(); // every lane has its keys in registers: the buffer becomes the record stage
+				}
 			} else {
 				const bool full = cur < full_segs;
 				const uint64_t row0 = cur * kSegRows + lane * 16;
 				valid = 0;
 #pragma unroll
 				for (int i = 0; i < 16; i++) {
-					h[i] = 0;
+					h[i] = 0; // a row past the end behaves like a slice-0 key whose hit is masked out below
 					if (full || row0 + i < count) {
 						h[i] = src.hash_at(row0 + i, pol_keys);
 						valid |= 1u << i;
 					}
 				}
 			}
-			// slot i of a staged segment is row (lane·16 + ((i/KPU + rot) mod U)·KPU + i%KPU) of the segment
+			uint2 *const stage = reinterpret_cast<uint2 *>(
+			    my_smem + (Smem::ALIAS ? par * Smem::KEY_SEG_BYTES : 2 * Smem::KEY_SEG_BYTES));
 			const uint32_t unit_rot = staged_seg ? rot : 0u;
 
-			// pass 1: slice of every key; slice-0 lookups are issued; the other slices are counted
-			uint64_t w0[16];
-			Packed<NREG> cnt;
+			// pass 1: per-lane counts of the keys of every slice (8-bit fields); the slice-0 lookups of the first
+			// eight keys are issued (the second eight follow in pass 2, behind the records of the first eight)
+			uint64_t w0[8];
+			auto lookups = [&](const int lo) {
 #pragma unroll
-			for (int j = 0; j < NREG; j++) {
-				cnt.r[j] = 0;
-			}
-#pragma unroll
-			for (int i = 0; i < 16; i++) {
-				const uint32_t sector = static_cast<uint32_t>(h[i]) & sector_mask;
-				const uint32_t s = sector >> kSliceShift;
-				const bool v = (valid >> i) & 1u;
-				w0[i] = 0;
-				if (v && s == 0u) {
-					w0[i] = ld_filter_word(filter + sector, pol_filter);
-				}
-				packed_add_slice<NREG>(cnt, v ? s : 0u);
-			}
-			// warp scan of the packed counters (fields cannot carry: a segment has 512 rows)
-			Packed<NREG> incl = cnt;
-#pragma unroll
-			for (int d = 1; d < 32; d <<= 1) {
-#pragma unroll
-				for (int j = 0; j < NREG; j++) {
-					const uint32_t t = __shfl_up_sync(0xffffffffu, incl.r[j], d);
-					incl.r[j] += lane >= static_cast<uint32_t>(d) ? t : 0u;
-				}
-			}
-			Packed<NREG> run, total;
-#pragma unroll
-			for (int j = 0; j < NREG; j++) {
-				run.r[j] = incl.r[j] - cnt.r[j];
-				total.r[j] = __shfl_sync(0xffffffffu, incl.r[j], 31);
-			}
-			// pass 2: records into the warp's stage; keys beyond their region's capacity are kept for later
-			uint32_t late = 0;
-#pragma unroll
-			for (int i = 0; i < 16; i++) {
-				const uint32_t sector = static_cast<uint32_t>(h[i]) & sector_mask;
-				const uint32_t s = sector >> kSliceShift;
-				if (((valid >> i) & 1u) && s != 0u) {
-					const uint32_t pos = packed_get<NREG>(run, s - 1u);
-					packed_add_slice<NREG>(run, s);
-					if (pos < static_cast<uint32_t>(CAP)) {
-						const uint32_t row9 =
-						    lane * 16u + (((i / Geo::KPU + unit_rot) & (Geo::U - 1)) * Geo::KPU) + (i % Geo::KPU);
-						stage[mul_lo_u32(s - 1u, CAP) + pos] =
-						    make_uint2((sector & ((1u << kSliceShift) - 1u)) | (row9 << kSliceShift),
-						               static_cast<uint32_t>(h[i] >> 32));
-					} else {
-						late |= 1u << i;
+				for (int i = 0; i < 8; i++) {
+					const uint32_t sector = static_cast<uint32_t>(h[lo + i]) & sector_mask;
+					w0[i] = 0;
+					if ((sector >> kSliceShift) == 0u) {
+						w0[i] = ld_filter_word(filter + sector, pol_filter);
 					}
 				}
-			}
-			// slice-0 results
-			uint32_t hits = 0;
+			};
+			auto tests = [&](const int lo) -> uint32_t {
+				uint32_t r = 0;
 #pragma unroll
-			for (int i = 15; i >= 0; i--) {
-				hits = hits * 2u + sector_test_fma(w0[i], static_cast<uint32_t>(h[i] >> 32));
+				for (int i = 7; i >= 0; i--) {
+					r = r * 2u + sector_test_fma(w0[i], static_cast<uint32_t>(h[lo + i] >> 32));
+				}
+				return r << lo;
+			};
+			lookups(0);
+			uint32_t cnt[NCNT];
+#pragma unroll
+			for (int j = 0; j < NCNT; j++) {
+				cnt[j] = 0;
 			}
-			if (__any_sync(0xffffffffu, late != 0u)) { // skewed keys only
+#pragma unroll
+			for (int i = 0; i < 16; i++) {
+				const uint32_t sector = static_cast<uint32_t>(h[i]) & sector_mask;
+				const uint32_t sh = (sector >> (kSliceShift - 3)) & ((P - 1u) << 3); // 8 · slice
+				if (NCNT == 1) {
+					cnt[0] += 1u << sh;
+				} else {
+					cnt[0] += shl_clamp(1u, sh);
+					cnt[1] += shl_clamp(1u, sh ^ 32u);
+				}
+			}
+			// warp scan on 16-bit fields; base[j] = exclusive prefixes of slices 4j..4j+3 as one 64-bit word
+			uint64_t base[NCNT];
+			uint32_t tot[NCNT][2]; // warp totals, 16-bit fields: [j][0] = slices 4j, 4j+2; [j][1] = slices 4j+1, 4j+3
+			bool overflow = false;
+#pragma unroll
+			for (int j = 0; j < NCNT; j++) {
+				const uint32_t own0 = cnt[j] & 0x00ff00ffu, own1 = (cnt[j] >> 8) & 0x00ff00ffu;
+				uint32_t e0 = own0, e1 = own1;
+#pragma unroll
+				for (int d = 1; d < 32; d <<= 1) {
+					const uint32_t t0 = __shfl_up_sync(0xffffffffu, e0, d);
+					const uint32_t t1 = __shfl_up_sync(0xffffffffu, e1, d);
+					e0 += lane >= static_cast<uint32_t>(d) ? t0 : 0u;
+					e1 += lane >= static_cast<uint32_t>(d) ? t1 : 0u;
+				}
+				tot[j][0] = __shfl_sync(0xffffffffu, e0, 31);
+				tot[j][1] = __shfl_sync(0xffffffffu, e1, 31);
+				e0 -= own0;
+				e1 -= own1;
+				base[j] = (static_cast<uint64_t>((e0 >> 16) | (e1 & 0xffff0000u)) << 32) | ((e0 & 0xffffu) | (e1 << 16));
+				cnt[j] = 0; // reused below as the lane's running per-slice rank
+			}
+			// total of slice s (warp-uniform)
+			auto slice_total = [&](int s) -> uint32_t {
+				const uint32_t t = tot[s >> 2][s & 1];
+				return (s & 2) ? t >> 16 : t & 0xffffu;
+			};
+#pragma unroll
+			for (int s = 1; s < P; s++) { // the regions of slices ≥ 1 hold CAP records; slice 0 has none
+				overflow |= slice_total(s) > static_cast<uint32_t>(CAP);
+			}
+			if (lane == 0) {
+#pragma unroll
+				for (int s = 1; s < P; s++) {
+					bucket_counts[(s - 1) * num_segs + cur] = overflow ? uint16_t(0) : static_cast<uint16_t>(slice_total(s));
+				}
+			}
+			uint32_t hits = 0;
+			if (!overflow) { // warp-uniform; the usual case
+				// pass 2: records into the stage.  position = exclusive base of the slice + rank inside the lane
+				auto records = [&](const int lo) {
+#pragma unroll
+					for (int k = 0; k < 8; k++) {
+						const int i = lo + k;
+						const uint32_t sector = static_cast<uint32_t>(h[i]) & sector_mask;
+						const uint32_t sh = (sector >> (kSliceShift - 3)) & ((P - 1u) << 3);
+						const uint32_t shr = sh & 31u;
+						uint32_t rank, pos;
+						if (NCNT == 1) {
+							rank = (cnt[0] >> shr) & 0xffu;
+							cnt[0] += 1u << shr;
+							pos = static_cast<uint32_t>(base[0] >> (2u * shr)) & 0xffffu;
+						} else {
+							const bool up = sh >= 32u;
+							rank = ((up ? cnt[1] : cnt[0]) >> shr) & 0xffu;
+							cnt[0] += up ? 0u : 1u << shr;
+							cnt[1] += up ? 1u << shr : 0u;
+							pos = static_cast<uint32_t>((up ? base[1] : base[0]) >> (2u * shr)) & 0xffffu;
+						}
+						pos += rank;
+						if (sh != 0u) {
+							const uint32_t row9 =
+							    lane * 16u + (((i / Geo::KPU + unit_rot) & (Geo::U - 1)) * Geo::KPU) + (i % Geo::KPU);
+							// byte offset of record `pos` of slice s: ((s-1)·CAP + pos)·8 with 8·s = sh
+							const uint32_t off = mul_lo_u32(sh, CAP) + pos * 8u - CAP * 8u;
+							*reinterpret_cast<uint2 *>(reinterpret_cast<unsigned char *>(stage) + off) =
+							    make_uint2((sector & ((1u << kSliceShift) - 1u)) | (row9 << kSliceShift),
+							               static_cast<uint32_t>(h[i] >> 32));
+						}
+					}
+				};
+				records(0);
+				hits = tests(0);
+				lookups(8);
+				records(8);
+				hits |= tests(8);
+			} else { // skewed keys: some region would overflow — this segment is looked up on the spot instead
 #pragma unroll
 				for (int i = 0; i < 16; i++) {
-					if ((late >> i) & 1u) {
-						const uint32_t sector = static_cast<uint32_t>(h[i]) & sector_mask;
-						hits |= sector_test(__ldg(filter + sector), static_cast<uint32_t>(h[i] >> 32)) << i;
-					}
+					const uint32_t sector = static_cast<uint32_t>(h[i]) & sector_mask;
+					hits |= sector_test(__ldg(filter + sector), static_cast<uint32_t>(h[i] >> 32)) << i;
 				}
 			}
+			hits &= valid;
 			if (staged_seg) {
 				const uint32_t twice = hits | (hits << 16);
 				hits = (twice >> (16u - Geo::KPU * rot)) & 0xffffu;
@@ -889,22 +937,20 @@ __global__ void __launch_bounds__(BLOCK, 2)
 			bitmap16[cur * 32 + lane] = static_cast<uint16_t>(hits);
 			// copy-out: the warp's records of every slice leave as contiguous 16-byte stores
 			__syncwarp();
+			if (!overflow) {
 #pragma unroll
-			for (int idx = 0; idx < P - 1; idx++) {
-				uint32_t c = packed_get<NREG>(total, idx);
-				c = c < static_cast<uint32_t>(CAP) ? c : static_cast<uint32_t>(CAP);
-				const uint4 *sv = reinterpret_cast<const uint4 *>(stage + idx * CAP);
-				uint4 *dv = reinterpret_cast<uint4 *>(buckets + idx * bucket_stride + cur * CAP);
-				for (uint32_t j = lane; 2u * j < c; j += 32u) {
-					// an odd count copies one stale record: it stays inside the region, unread.  evict_first: 6 B/key of
-					// record traffic must not push slice 0 of the filter out of L2
-					st_stream_v4(dv + j, sv[j], pol_keys);
-				}
-				if (lane == 0) {
-					bucket_counts[idx * num_segs + cur] = static_cast<uint16_t>(c);
+				for (int s = 1; s < P; s++) {
+					const uint32_t total = slice_total(s);
+					const uint4 *sv = reinterpret_cast<const uint4 *>(stage + (s - 1) * CAP);
+					uint4 *dv = reinterpret_cast<uint4 *>(buckets + (s - 1) * bucket_stride + cur * CAP);
+					for (uint32_t j = lane; 2u * j < total; j += 32u) {
+						// an odd count copies one stale record: it stays inside the region, unread.  evict_first: the
+						// record traffic must not push slice 0 of the filter out of L2
+						st_stream_v4(dv + j, sv[j], pol_keys);
+					}
 				}
 			}
-			__syncwarp(); // the stage is rewritten by the next segment
+			__syncwarp(); // the stage is rewritten by the next segment (or, aliased, by the key prefetch after it)
 		}
 		if (nxt >= num_segs) {
 			break;
@@ -918,12 +964,12 @@ __global__ void __launch_bounds__(BLOCK, 2)
 }
 
 // One slice's bucket: warp per segment region; all record loads, then all filter loads, are issued before the
-// first test.  ITER = CAP / 32 records per lane.
+// first test.  ITER = ceil(CAP / 32) records per lane.
 template <int CAP>
 __global__ void __launch_bounds__(256)
     probe_bucket_kernel(const uint2 *__restrict__ bucket, const uint16_t *__restrict__ counts, const uint64_t num_segs,
                         const uint64_t *__restrict__ filter, const uint32_t slice_lo, uint32_t *__restrict__ bitmap32) {
-	constexpr int ITER = CAP / 32;
+	constexpr int ITER = (CAP + 31) / 32;
 	const uint32_t lane = threadIdx.x & 31u;
 	const uint64_t pol_rec = policy_evict_first();
 	const uint64_t pol_filter = policy_evict_last();
@@ -1518,7 +1564,7 @@ static int partition_mode() {
 static inline int partition_slices(uint64_t num_sectors) {
 	const int slices = num_sectors > kSliceSectors ? static_cast<int>(num_sectors / kSliceSectors) : 0;
 	const int mode = partition_mode();
-	return (mode == 2 || (mode == 1 && slices == 8)) ? slices : 0;
+	return (mode == 2 || (mode == 1 && slices >= 4)) ? slices : 0;
 }
 static inline int partition_cap(int slices) {
 	return slices == 2 ? PartCfg<2>::CAP : (slices == 4 ? PartCfg<4>::CAP : PartCfg<8>::CAP);
@@ -1709,8 +1755,7 @@ static cudaError_t launch_probe_partitioned(const DeviceInfo &dev, const Src &sr
 	auto part = probe_partition_kernel<Src, BLOCK, P>;
 	auto bucket = probe_bucket_kernel<CAP>;
 	const uint64_t num_segs = ceil_div(count, kSegRows);
-	const size_t smem = (Src::kStageable ? static_cast<size_t>(BLOCK / 32) * 2 * kSegRows * Src::kKeyBytes : 0) +
-	                    static_cast<size_t>(BLOCK / 32) * (P - 1) * CAP * sizeof(uint2);
+	const size_t smem = static_cast<size_t>(BLOCK / 32) * PartSmem<Src, P>::WARP_BYTES;
 	cudaError_t e = cudaFuncSetAttribute(part, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
 	if (e != cudaSuccess) {
 		return e;
@@ -1784,7 +1829,11 @@ static cudaError_t launch_probe_src(const DeviceInfo &dev, const Src &src, uint6
 		return smem ? launch_probe_fused<Src, kProbeBlockSmem, true>(RPT_PROBE_ARGS)
 		            : launch_probe_fused<Src, kProbeBlock, false>(RPT_PROBE_ARGS);
 	}
-	switch (smem ? 0 : partition_slices(num_sectors)) {
+	int part_slices = smem ? 0 : partition_slices(num_sectors);
+	if (part_slices == 4 && partition_mode() == 1 && Src::kStageable && Src::kKeyBytes == 4) {
+		part_slices = 0; // four passes over a 4-byte column re-read 16 B per key: cheaper than 4 + 6 + 6 plus the placement
+	}
+	switch (part_slices) {
 	case 2:
 		return launch_probe_partitioned<Src, 2>(RPT_PROBE_ARGS);
 	case 4:

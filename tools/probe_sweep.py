@@ -18,7 +18,7 @@ dev = torch.device("cuda", 0)
 stream = torch.cuda.Stream(device=dev)
 torch.cuda.set_stream(stream)
 sh = stream.cuda_stream
-knobs = {k: os.environ[k] for k in ("RPT_PROBE_UNITS", "RPT_SLICE_MIB", "RPT_GPU_LIB") if k in os.environ}
+knobs = {k: os.environ[k] for k in ("RPT_PROBE_UNITS", "RPT_SLICE_MIB", "RPT_GPU_LIB", "RPT_PROBE_PARTITION", "RPT_PART_MINB", "RPT_PART_STORE", "RPT_L2_PERSIST_MIB") if k in os.environ}
 print(f"# m={m} reps={reps} ppm={ppm} type={ktype} knobs={knobs}", flush=True)
 dp = torch.empty(m, dtype=torch.int64, device=dev)
 dsel = torch.empty(m, dtype=torch.int32, device=dev)
