@@ -66,6 +66,7 @@ class ShardedBloomFilter:
         self.merge = merge
         self._peer_open_for = None
         self.merged = False
+        self._release_pending = False  # peers may still be pulling my reduced slice (see _release)
 
     # -- plumbing ------------------------------------------------------------------------------------
     def _scalar_device(self):
@@ -90,15 +91,38 @@ class ShardedBloomFilter:
             self._token = torch.zeros(1, dtype=torch.int32, device=self._scalar_device())
         self.dist.all_reduce(self._token, group=self.group)
 
+    def _flag_barrier(self, flag):
+        """device_barrier() that also sums a 0/1 flag over the ranks.  Returns the device tensor holding the sum:
+        reading it (`.item()`) is the only thing that blocks the host, and only a rank whose own flag is 0 has to."""
+        import torch
+        if not hasattr(self, "_flag"):
+            self._flag = torch.zeros(1, dtype=torch.int32, device=self._scalar_device())
+        self._flag.fill_(int(flag))
+        self.dist.all_reduce(self._flag, group=self.group)
+        return self._flag
+
+    def _release(self, stream=None):
+        """The last barrier of a stream-ordered peer merge ("nobody still reads my words") is not needed by the
+        probes that follow — they only read — so it is taken here, right before the next mutation of the words."""
+        if not self._release_pending:
+            return
+        import torch
+        self._release_pending = False
+        self.device_barrier()
+        if stream is None:
+            torch.cuda.current_stream().synchronize()
+
     # -- PTBloomFilter surface ------------------------------------------------------------------------
     def Initialize(self, est_num_rows):
         """est_num_rows is the GLOBAL estimate (the optimizer's cardinality), the same on every rank, so S is too."""
+        self._release(None)
         self.bf.Initialize(est_num_rows)
         self._peer_open_for = None
         self.merged = False
         return self
 
     def Reset(self, est_num_rows, stream=None):
+        self._release(stream)
         before = self.bf.device_words if hasattr(self.bf, "device_words") else None
         self.bf.Reset(est_num_rows, stream)
         after = self.bf.device_words if hasattr(self.bf, "device_words") else None
@@ -109,6 +133,7 @@ class ShardedBloomFilter:
 
     def Insert(self, cols, count, stream=None):
         """Inserts this rank's shard of the build column."""
+        self._release(stream)
         self.bf.Insert(cols, count, stream)
         self.merged = False
 
@@ -120,9 +145,13 @@ class ShardedBloomFilter:
             self.merged = True
             return
         import torch
-        any_data = self._allreduce_sum(0 if self.bf.IsEmpty() else 1)
+        has_local = 0 if self.bf.IsEmpty() else 1
         on_gpu = self.dist.get_backend(self.group) == "nccl"
         blocking = stream is None
+        self._release(stream)
+        # "does any rank hold data": the peer merge sums the flag inside its first barrier (no extra collective, no
+        # host sync for a rank that has rows itself); the all-gather merge asks with a scalar all-reduce
+        self._any_data = None if (on_gpu and self.merge == "peer") else self._allreduce_sum(has_local)
         if on_gpu:
             if blocking:
                 # own side stream: a NULL rpt_stream_t means "the handle's stream", which NCCL cannot order against
@@ -136,16 +165,16 @@ class ShardedBloomFilter:
                 if run_on.cuda_stream != stream:
                     raise ValueError("Merge(stream): stream must be torch's current (non-default) CUDA stream")
             with torch.cuda.stream(run_on):
-                self._merge_on(run_on.cuda_stream)
+                self._merge_on(run_on.cuda_stream, has_local, defer_release=not blocking)
             if blocking:
                 run_on.synchronize()
         else:
-            self._merge_on(None)
-        if any_data:
+            self._merge_on(None, has_local)
+        if self._any_data:
             self.bf.SetHasData(True)
         self.merged = True
 
-    def _merge_on(self, stream):
+    def _merge_on(self, stream, has_local=0, defer_release=False):
         import torch
         if self.merge == "peer":
             words = self.bf.device_words
@@ -156,11 +185,18 @@ class ShardedBloomFilter:
                 raw = allb.cpu().numpy().tobytes()
                 self.bf.PeerOpen([raw[64 * r:64 * (r + 1)] for r in range(self.world)], self.rank)
                 self._peer_open_for = words
-            self.device_barrier()                 # every partial filter is complete
+            if self._any_data is None:            # every partial filter is complete (+ the has-data flag)
+                total = self._flag_barrier(has_local)
+                self._any_data = True if has_local else int(total.item()) > 0
+            else:
+                self.device_barrier()
             self.bf.PeerMergePhase(0, stream)     # my slice |= peers' copies of my slice (NVLink reads)
             self.device_barrier()                 # every slice is reduced
             self.bf.PeerMergePhase(1, stream)     # pull the other ranks' reduced slices
-            self.device_barrier()                 # nobody still reads my words
+            if defer_release:                     # nobody still reads my words: due before my next mutation
+                self._release_pending = True
+            else:
+                self.device_barrier()
         else:
             mine = self._words_tensor()
             parts = torch.empty(self.world * mine.numel(), dtype=mine.dtype, device=mine.device)
@@ -186,6 +222,7 @@ class ShardedBloomFilter:
             if cols is None:
                 raise self.engine.RptError("the resize rule fires but no key columns were given to rehash from")
             # ReinitializeAndRehash(actual_rows) on every rank: same new S everywhere
+            self._release(stream)
             self.bf.ReinitializeAndRehash(actual_rows, cols, count, stream)
             self._peer_open_for = None
             self.merged = False
@@ -226,6 +263,11 @@ class ShardedBloomFilter:
         raise AttributeError(name)
 
     def close(self):
+        if self._release_pending:  # peers may still be pulling my reduced slice: wait for them before freeing it
+            try:
+                self._release(None)
+            except Exception:
+                self._release_pending = False
         if self._peer_open_for is not None and hasattr(self.bf, "PeerClose"):
             try:
                 self.bf.PeerClose()
