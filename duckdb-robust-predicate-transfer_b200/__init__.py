@@ -71,6 +71,8 @@ _SIGNATURES = {
     "rpt_bf_filter_sel": (C.c_int, [C.c_void_p, C.POINTER(RptCol), C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p,
                                     C.c_int, C.c_void_p]),
     "rpt_bf_lookup_hashes_host": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p]),
+    "rpt_bf_check_statistics": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64,
+                                          C.c_void_p]),
     "rpt_bf_export_words": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64]),
     "rpt_bf_import_words": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64]),
     "rpt_bf_device_words": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p)]),
@@ -275,6 +277,28 @@ class PTBloomFilter:
         hits = np.zeros(hashes.shape[0], dtype=np.uint8)
         _check(lib().rpt_bf_lookup_hashes_host(self._h, hashes.ctypes.data, hashes.shape[0], hits.ctypes.data))
         return hits.astype(bool)
+
+    def CheckStatistics(self, type_code, mins, maxs, has_minmax=None):
+        """BFTableFilter::CheckStatistics (duckdb bloom_filter.cpp:138-196) over a batch of row groups.
+        mins/maxs: arrays of the column's physical type (128-bit types: uint64 pairs {lower, upper}, shape (k, 2)).
+        Returns uint8 codes: 0 NO_PRUNING_POSSIBLE, 1 FILTER_ALWAYS_TRUE, 2 FILTER_ALWAYS_FALSE."""
+        mins = np.ascontiguousarray(mins)
+        maxs = np.ascontiguousarray(maxs)
+        count = mins.shape[0]
+        if maxs.shape != mins.shape or mins.dtype != maxs.dtype:
+            raise ValueError("mins and maxs must have the same shape and dtype")
+        width = TYPE_WIDTH.get(type_code)
+        if width is not None and mins.nbytes != count * width:
+            raise ValueError("statistics arrays do not match the physical type's width")
+        has = None
+        if has_minmax is not None:
+            has = np.ascontiguousarray(has_minmax, dtype=np.uint8)
+            if has.shape[0] != count:
+                raise ValueError("has_minmax must have one entry per row group")
+        out = np.zeros(count, dtype=np.uint8)
+        _check(lib().rpt_bf_check_statistics(self._h, int(type_code), mins.ctypes.data, maxs.ctypes.data,
+                                             has.ctypes.data if has is not None else None, count, out.ctypes.data))
+        return out
 
     # -- resize rule + ReinitializeAndRehash: physical_create_bf.cpp:386-406, bloom_filter.cpp:34-58
     def NeedsRebuild(self, actual_rows):

@@ -15,6 +15,7 @@
 #include <ctime>
 #include <mutex>
 #include <string>
+#include <type_traits>
 #include <vector>
 
 #include "../../include/rpt_gpu.h"
@@ -1026,6 +1027,152 @@ int rpt_bf_lookup_hashes_host(const rpt_bf_t *bf, const uint64_t *hashes, uint64
 	                              reinterpret_cast<uint8_t *>(dhits), st.stream));
 	const_cast<rpt_bf *>(bf)->launches += 1;
 	RPT_CUDA(cudaMemcpyAsync(hits, dhits, count, cudaMemcpyDeviceToHost, st.stream));
+	RPT_CUDA(cudaStreamSynchronize(st.stream));
+	return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// zone maps (BFTableFilter::CheckStatistics, duckdb bloom_filter.cpp:138-196)
+// ---------------------------------------------------------------------------------------------
+extern "C++" {
+namespace {
+// The typed part of TemplatedCheckStatistics<T>: min > max, `max - min` has to be representable in T
+// (TrySubtractOperator), at most 2048.  Everything is done on 128-bit two's-complement images of the values.
+struct Wide {
+	unsigned __int128 v;
+	bool is_signed;
+};
+inline bool wide_less(const Wide &a, const Wide &b) {
+	return a.is_signed ? static_cast<__int128>(a.v) < static_cast<__int128>(b.v) : a.v < b.v;
+}
+template <class T>
+inline Wide widen(const void *base, uint64_t i) {
+	T x;
+	memcpy(&x, static_cast<const char *>(base) + i * sizeof(T), sizeof(T));
+	const bool sg = std::is_signed<T>::value;
+	return Wide {sg ? static_cast<unsigned __int128>(static_cast<__int128>(x)) : static_cast<unsigned __int128>(x), sg};
+}
+inline Wide widen128(const void *base, uint64_t i, bool sg) {
+	uint64_t w[2];
+	memcpy(w, static_cast<const char *>(base) + i * 16, 16);
+	return Wide {(static_cast<unsigned __int128>(w[1]) << 64) | w[0], sg};
+}
+// largest difference T can hold, by type
+inline unsigned __int128 max_difference(int type) {
+	switch (type) {
+	case RPT_UINT8:
+		return 0xffu;
+	case RPT_INT8:
+		return 0x7fu;
+	case RPT_UINT16:
+		return 0xffffu;
+	case RPT_INT16:
+		return 0x7fffu;
+	case RPT_UINT32:
+		return 0xffffffffu;
+	case RPT_INT32:
+		return 0x7fffffffu;
+	case RPT_UINT64:
+		return ~0ULL;
+	case RPT_INT64:
+		return ~0ULL >> 1;
+	case RPT_UINT128:
+		return ~static_cast<unsigned __int128>(0);
+	default: // RPT_INT128
+		return ~static_cast<unsigned __int128>(0) >> 1;
+	}
+}
+} // namespace
+} // extern "C++"
+
+int rpt_bf_check_statistics(const rpt_bf_t *bf, int type, const void *mins, const void *maxs,
+                            const uint8_t *has_minmax, uint64_t count, uint8_t *results_out) {
+	if (!bf || (count && (!mins || !maxs || !results_out))) {
+		return set_error("null argument");
+	}
+	RPT_GUARD(bf);
+	if (count == 0) {
+		return 0;
+	}
+	uint32_t hash_class;
+	switch (type) {
+	case RPT_UINT8:
+	case RPT_INT8:
+	case RPT_UINT16:
+	case RPT_INT16:
+	case RPT_UINT32:
+	case RPT_INT32:
+		hash_class = kStatsHash32;
+		break;
+	case RPT_UINT64:
+	case RPT_INT64:
+		hash_class = kStatsHash64;
+		break;
+	case RPT_UINT128:
+	case RPT_INT128:
+		hash_class = kStatsHash128;
+		break;
+	default: // bloom_filter.cpp:193-195: no pruning for any other physical type
+		memset(results_out, RPT_NO_PRUNING_POSSIBLE, count);
+		return 0;
+	}
+	std::vector<StatsRange> ranges(count);
+	const unsigned __int128 limit = max_difference(type);
+	for (uint64_t i = 0; i < count; i++) {
+		Wide lo, hi;
+		switch (type) {
+		case RPT_UINT8:
+			lo = widen<uint8_t>(mins, i), hi = widen<uint8_t>(maxs, i);
+			break;
+		case RPT_INT8:
+			lo = widen<int8_t>(mins, i), hi = widen<int8_t>(maxs, i);
+			break;
+		case RPT_UINT16:
+			lo = widen<uint16_t>(mins, i), hi = widen<uint16_t>(maxs, i);
+			break;
+		case RPT_INT16:
+			lo = widen<int16_t>(mins, i), hi = widen<int16_t>(maxs, i);
+			break;
+		case RPT_UINT32:
+			lo = widen<uint32_t>(mins, i), hi = widen<uint32_t>(maxs, i);
+			break;
+		case RPT_INT32:
+			lo = widen<int32_t>(mins, i), hi = widen<int32_t>(maxs, i);
+			break;
+		case RPT_UINT64:
+			lo = widen<uint64_t>(mins, i), hi = widen<uint64_t>(maxs, i);
+			break;
+		case RPT_INT64:
+			lo = widen<int64_t>(mins, i), hi = widen<int64_t>(maxs, i);
+			break;
+		default:
+			lo = widen128(mins, i, type == RPT_INT128), hi = widen128(maxs, i, type == RPT_INT128);
+			break;
+		}
+		StatsRange &r = ranges[i];
+		r.first_lower = static_cast<uint64_t>(lo.v);
+		r.first_upper = static_cast<uint64_t>(lo.v >> 64);
+		r.range = 0;
+		r.hash_class = kStatsSkip;
+		if ((has_minmax && !has_minmax[i]) || wide_less(hi, lo)) {
+			continue; // no statistics, or invalid ones
+		}
+		const unsigned __int128 diff = hi.v - lo.v; // exact: lo <= hi, modulo 2^128
+		if (diff > limit || diff > 2048) {
+			continue; // the subtraction overflows T, or the range is too wide
+		}
+		r.range = static_cast<uint32_t>(diff);
+		r.hash_class = hash_class;
+	}
+	Staged st;
+	st.stream = bf->stream;
+	void *dr, *dres;
+	RPT_TRY(st.upload(&dr, ranges.data(), count * sizeof(StatsRange)));
+	RPT_TRY(st.alloc(&dres, count));
+	RPT_CUDA(launch_check_statistics(bf->words, bf->num_sectors, reinterpret_cast<const StatsRange *>(dr), count,
+	                                 reinterpret_cast<uint8_t *>(dres), st.stream));
+	const_cast<rpt_bf *>(bf)->launches += 1;
+	RPT_CUDA(cudaMemcpyAsync(results_out, dres, count, cudaMemcpyDeviceToHost, st.stream));
 	RPT_CUDA(cudaStreamSynchronize(st.stream));
 	return 0;
 }

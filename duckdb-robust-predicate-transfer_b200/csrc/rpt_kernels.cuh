@@ -53,6 +53,18 @@ cudaError_t launch_or_ptrs(const DeviceInfo &dev, uint64_t *words, const PtrList
 cudaError_t launch_lookup_hashes(const uint64_t *words, uint64_t num_sectors, const uint64_t *hashes, uint64_t count,
                                  uint8_t *hits, cudaStream_t stream);
 
+// Zone-map pruning (BFTableFilter::CheckStatistics, duckdb bloom_filter.cpp:138-196): one entry per row group
+enum : uint32_t { kStatsHash32 = 0, kStatsHash64 = 1, kStatsHash128 = 2, kStatsSkip = 3 };
+enum : uint8_t { kStatsNoPruning = 0, kStatsAlwaysTrue = 1, kStatsAlwaysFalse = 2 }; // = enum rpt_prune
+struct StatsRange {
+	uint64_t first_lower; // min as a 128-bit two's-complement integer (sign- or zero-extended from its type)
+	uint64_t first_upper;
+	uint32_t range;       // max - min (≤ 2048): range + 1 consecutive values are looked up
+	uint32_t hash_class;  // how the type hashes; kStatsSkip: the host already decided NO_PRUNING_POSSIBLE
+};
+cudaError_t launch_check_statistics(const uint64_t *words, uint64_t num_sectors, const StatsRange *ranges, uint64_t count,
+                                    uint8_t *results, cudaStream_t stream);
+
 // Column range (UpdateMinMax, physical_create_bf.cpp:82-176).  Keys are order-preserving uint64 images of the
 // values (signed: value ^ 2^63 after sign extension; float/double: sign-magnitude flip); the host decodes them.
 struct MinMaxState {

@@ -172,6 +172,17 @@ RPT_API int rpt_bf_filter_sel(const rpt_bf_t *bf, const rpt_col_t *key, const ui
 RPT_API int rpt_bf_lookup_hashes_host(const rpt_bf_t *bf, const uint64_t *hashes, uint64_t count, uint8_t *hits);
 
 /* ---- filter words ------------------------------------------------------------------------ */
+/* Zone-map pruning, batched over row groups: BFTableFilter::CheckStatistics / TemplatedCheckStatistics<T>
+ * (duckdb/src/planner/filter/bloom_filter.cpp:138-196).  Row group i has statistics [mins[i], maxs[i]] of the
+ * column's physical type (`type`; 16-byte {lower, upper} values for the 128-bit types) and has_minmax[i] != 0
+ * (NULL = all have).  Like the reference: no statistics, min > max, a difference that does not fit the type or
+ * exceeds 2048 → RPT_NO_PRUNING_POSSIBLE; otherwise the max-min+1 consecutive values are hashed as the type
+ * hashes and looked up: none hits → RPT_FILTER_ALWAYS_FALSE, all hit → RPT_FILTER_ALWAYS_TRUE.  Types other
+ * than the ten integral ones always give RPT_NO_PRUNING_POSSIBLE (:193-195).  Host arrays in, host array out. */
+enum rpt_prune { RPT_NO_PRUNING_POSSIBLE = 0, RPT_FILTER_ALWAYS_TRUE = 1, RPT_FILTER_ALWAYS_FALSE = 2 };
+RPT_API int rpt_bf_check_statistics(const rpt_bf_t *bf, int type, const void *mins, const void *maxs,
+                                    const uint8_t *has_minmax, uint64_t count, uint8_t *results_out);
+
 /* D2H copy of the S words; byte-identical to DuckDB's bf[] so the scan-side BFTableFilter,
  * zone-map CheckStatistics and passthrough USE_BF keep working on the exported copy. */
 RPT_API int rpt_bf_export_words(const rpt_bf_t *bf, uint64_t *host_dst, uint64_t capacity_words);

@@ -174,6 +174,12 @@ public:
 	void ExportWords(uint64_t *dst, uint64_t capacity_words) const {
 		Check(rpt_bf_export_words(bf_, dst, capacity_words));
 	}
+	// BFTableFilter::CheckStatistics (duckdb bloom_filter.cpp:138-196) for `count` row groups at once: mins/maxs are
+	// arrays of the column's physical type, results receive enum rpt_prune codes
+	void CheckStatistics(int physical_type, const void *mins, const void *maxs, const uint8_t *has_minmax,
+	                     uint64_t count, uint8_t *results) const {
+		Check(rpt_bf_check_statistics(bf_, physical_type, mins, maxs, has_minmax, count, results));
+	}
 	rpt_bf_t *handle() const {
 		return bf_;
 	}

@@ -283,6 +283,89 @@ uint64_t rpto_probe(const uint64_t *words, uint64_t S, const rpto_col_t *cols, i
 	return total;
 }
 
+/* BFTableFilter::CheckStatistics / TemplatedCheckStatistics<T> (duckdb/src/planner/filter/bloom_filter.cpp:138-196):
+ * zone-map pruning of one row group with statistics [min, max] of an integral physical type.  T-typed
+ * subtraction (TrySubtractOperator: the difference has to fit T, so an int8 range of 128..255 is "overflow"),
+ * at most 2049 consecutive values are looked up.  Results: 0 = NO_PRUNING_POSSIBLE, 1 = FILTER_ALWAYS_TRUE,
+ * 2 = FILTER_ALWAYS_FALSE.  min/max point at one value of the type (16 bytes {lower, upper} for the 128-bit ones). */
+static int lookup_one(const uint64_t *words, uint64_t S, uint64_t h) { /* bloom_filter.cpp:72-78 */
+	const uint64_t m = rpto_mask(h);
+	return (words[h & (S - 1)] & m) == m;
+}
+
+int rpto_check_statistics(const uint64_t *words, uint64_t S, int type, const void *min, const void *max,
+                          int has_minmax) {
+	if (!has_minmax) {
+		return 0;
+	}
+	uint64_t range;
+	switch (type) {
+#define RPTO_SMALL(TAG, T, WIDE, TMAX)                                                                                  \
+	case TAG: {                                                                                                    \
+		const T lo = *(const T *)min, hi = *(const T *)max;                                                        \
+		if (lo > hi) {                                                                                             \
+			return 0;                                                                                              \
+		}                                                                                                          \
+		const WIDE d = (WIDE)hi - (WIDE)lo;                                                                        \
+		if (d > (WIDE)(TMAX) || d > 2048) {                                                                        \
+			return 0;                                                                                              \
+		}                                                                                                          \
+		range = (uint64_t)d;                                                                                       \
+		uint64_t hits = 0;                                                                                         \
+		T val = lo;                                                                                                \
+		for (uint64_t i = 0; i <= range; i++) {                                                                    \
+			hits += (uint64_t)lookup_one(words, S, rpto_hash_value(TAG, &val));                                    \
+			val = (T)(val + (T)(i < range));                                                                       \
+		}                                                                                                          \
+		return hits == 0 ? 2 : (hits == range + 1 ? 1 : 0);                                                        \
+	}
+		RPTO_SMALL(RPTO_UINT8, uint8_t, int64_t, UINT8_MAX)
+		RPTO_SMALL(RPTO_UINT16, uint16_t, int64_t, UINT16_MAX)
+		RPTO_SMALL(RPTO_UINT32, uint32_t, int64_t, UINT32_MAX)
+		RPTO_SMALL(RPTO_INT8, int8_t, int64_t, INT8_MAX)
+		RPTO_SMALL(RPTO_INT16, int16_t, int64_t, INT16_MAX)
+		RPTO_SMALL(RPTO_INT32, int32_t, int64_t, INT32_MAX)
+		RPTO_SMALL(RPTO_UINT64, uint64_t, __int128, UINT64_MAX)
+		RPTO_SMALL(RPTO_INT64, int64_t, __int128, INT64_MAX)
+#undef RPTO_SMALL
+	case RPTO_UINT128:
+	case RPTO_INT128: {
+		const uint64_t *a = (const uint64_t *)min, *b = (const uint64_t *)max;
+		unsigned __int128 lo = ((unsigned __int128)a[1] << 64) | a[0], hi = ((unsigned __int128)b[1] << 64) | b[0];
+		unsigned __int128 d;
+		if (type == RPTO_INT128) {
+			if ((__int128)lo > (__int128)hi) {
+				return 0;
+			}
+			/* hi - lo as hugeint: overflow when the true difference exceeds 2^127 - 1 */
+			d = hi - lo;
+			if ((d >> 127) != 0) {
+				return 0;
+			}
+		} else {
+			if (lo > hi) {
+				return 0;
+			}
+			d = hi - lo;
+		}
+		if (d > 2048) {
+			return 0;
+		}
+		range = (uint64_t)d;
+		uint64_t hits = 0;
+		unsigned __int128 val = lo;
+		for (uint64_t i = 0; i <= range; i++) {
+			uint64_t w[2] = {(uint64_t)val, (uint64_t)(val >> 64)};
+			hits += (uint64_t)lookup_one(words, S, rpto_hash_value(type, w));
+			val += (unsigned __int128)(i < range);
+		}
+		return hits == 0 ? 2 : (hits == range + 1 ? 1 : 0);
+	}
+	default:
+		return 0; /* bloom_filter.cpp:193-195: every other physical type */
+	}
+}
+
 uint64_t rpto_fnv1a_words(const uint64_t *w, uint64_t n) {
 	uint64_t h = 0xcbf29ce484222325ULL;
 	for (uint64_t i = 0; i < n; i++) {

@@ -68,6 +68,11 @@ void rpto_insert(uint64_t *words, uint64_t S, const rpto_col_t *cols, int ncols,
 uint64_t rpto_probe(const uint64_t *words, uint64_t S, const rpto_col_t *cols, int ncols, uint64_t count,
                     uint32_t *sel_out);
 
+/* BFTableFilter::CheckStatistics (duckdb bloom_filter.cpp:138-196) for one [min, max]: 0 no pruning, 1 always true,
+ * 2 always false */
+int rpto_check_statistics(const uint64_t *words, uint64_t S, int type, const void *min, const void *max,
+                          int has_minmax);
+
 /* FNV-1a-64 over words (xor then multiply per word) — the checksum SURVEY §8(c) froze */
 uint64_t rpto_fnv1a_words(const uint64_t *w, uint64_t n);
 

@@ -123,6 +123,26 @@ static void TestCreateAndUse(uint32_t est, uint64_t build_rows, bool expect_rebu
 	bf.ExportWords(got.data(), got.size());
 	REQUIRE(memcmp(got.data(), want.data(), want.size() * 8) == 0);
 
+	// zone maps (BFTableFilter::CheckStatistics) of row groups around the key space
+	{
+		std::vector<int64_t> mins, maxs;
+		std::vector<uint8_t> has;
+		uint64_t x = est;
+		for (int g = 0; g < 300; g++) {
+			x = rpto_splitmix64(x);
+			const int64_t a = static_cast<int64_t>(x % (1 << 21)) - 1000;
+			const int64_t w = static_cast<int64_t>((x >> 40) % 2100) - 20; // some inverted, some wider than 2048
+			mins.push_back(a);
+			maxs.push_back(a + w);
+			has.push_back(g % 17 != 0);
+		}
+		std::vector<uint8_t> res(mins.size(), 0xff);
+		bf.CheckStatistics(RPT_INT64, mins.data(), maxs.data(), has.data(), mins.size(), res.data());
+		for (size_t g = 0; g < mins.size(); g++) {
+			REQUIRE(res[g] == rpto_check_statistics(want.data(), want.size(), RPTO_INT64, &mins[g], &maxs[g], has[g]));
+		}
+	}
+
 	// min / max of the valid build rows (UpdateMinMax)
 	int64_t lo = INT64_MAX, hi = INT64_MIN;
 	bool any = false;

@@ -62,6 +62,7 @@ class Oracle:
             "rpto_lookup_hashes": (_u64, [_vp, _u64, _vp, _u64, _vp]),
             "rpto_insert": (None, [_vp, _u64, C.POINTER(Col), _int, _u64]),
             "rpto_probe": (_u64, [_vp, _u64, C.POINTER(Col), _int, _u64, _vp]),
+            "rpto_check_statistics": (_int, [_vp, _u64, _int, _vp, _vp, _int]),
             "rpto_fnv1a_words": (_u64, [_vp, _u64]), "rpto_splitmix64": (_u64, [_u64]),
             "rpto_synth_build_keys": (None, [_vp, _u64, _u64]),
             "rpto_synth_probe_keys": (None, [_vp, _u64, _u64, _u64, C.c_uint32]),
@@ -128,6 +129,18 @@ class Oracle:
         f = self.L.rpto_lookup_hashes(words.ctypes.data, words.shape[0], hashes.ctypes.data, hashes.shape[0],
                                       sel.ctypes.data)
         return sel[:f].copy()
+
+    def check_statistics(self, words, type_id, mins, maxs, has_minmax=None):
+        """BFTableFilter::CheckStatistics per row group (duckdb bloom_filter.cpp:138-196): uint8 codes."""
+        mins, maxs = np.ascontiguousarray(mins), np.ascontiguousarray(maxs)
+        count = mins.shape[0]
+        step = mins.nbytes // count if count else 0
+        out = np.zeros(count, dtype=np.uint8)
+        for i in range(count):
+            out[i] = self.L.rpto_check_statistics(words.ctypes.data, words.shape[0], type_id,
+                                                  mins.ctypes.data + i * step, maxs.ctypes.data + i * step,
+                                                  1 if has_minmax is None else int(has_minmax[i]))
+        return out
 
     def fnv(self, words):
         return self.L.rpto_fnv1a_words(words.ctypes.data, words.shape[0])

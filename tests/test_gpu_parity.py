@@ -776,3 +776,40 @@ def test_cpp_host_mirror(rpt, oracle):
     proc = subprocess.run([path], capture_output=True, text=True, timeout=600)
     assert proc.returncode == 0, proc.stdout + proc.stderr
     assert "host mirror ok" in proc.stdout
+
+
+@pytest.mark.parametrize("type_id", [2, 3, 4, 5, 6, 7, 8, 9, 203, 204])
+def test_check_statistics_zone_maps(rpt, oracle, type_id):
+    """rpt_bf_check_statistics (BFTableFilter::CheckStatistics, duckdb bloom_filter.cpp:138-196) over a batch of
+    row groups vs the oracle, every integral physical type: always-true, always-false and mixed ranges, the
+    type's limits, invalid (min > max) and too-wide ranges, missing statistics, 128-bit carry."""
+    from test_oracle_cpu import INT_TYPES, stats_arrays, stats_cases
+    rng = np.random.default_rng(100 + type_id)
+    _, bits, signed = INT_TYPES[type_id]
+    tmax = (1 << (bits - 1)) - 1 if signed else (1 << bits) - 1
+    # build column: every value of 0..min(3000, tmax) except multiples of 7, plus the type's last values;
+    # values 3001..5000 stay out (always-false ranges, up to false positives — the oracle sees the same words)
+    vals = [v for v in range(0, min(3000, tmax) + 1) if v % 7] + [tmax - k for k in range(min(4, tmax))]
+    if bits == 128:
+        u = [v & ((1 << 128) - 1) for v in vals]
+        data = np.array([[x & 0xFFFFFFFFFFFFFFFF, x >> 64] for x in u], dtype=np.uint64)
+        col = rpt.host_col(data, type=type_id)
+    else:
+        col = rpt.host_col(np.array(vals, dtype=INT_TYPES[type_id][0]))
+    bf = rpt.PTBloomFilter(0).Initialize(len(vals))
+    bf.Insert(col, len(vals))
+    words = bf.ExportWords()
+    pairs = stats_cases(type_id, rng, n_random=400)
+    mins, maxs = stats_arrays(type_id, pairs)
+    has = (rng.random(len(pairs)) < 0.95).astype(np.uint8)
+    got = bf.CheckStatistics(type_id, mins, maxs, has)
+    want = oracle.check_statistics(words, type_id, mins, maxs, has)
+    assert np.array_equal(got, want)
+    assert np.array_equal(bf.CheckStatistics(type_id, mins, maxs), oracle.check_statistics(words, type_id, mins, maxs))
+    if tmax > 5000:
+        assert set(want.tolist()) == {0, 1, 2}
+    assert bf.CheckStatistics(type_id, mins[:0], maxs[:0]).size == 0
+    # a physical type the reference does not prune on
+    f = np.array([1.0, 2.0], dtype=np.float64)
+    assert bf.CheckStatistics(rpt.DOUBLE, f, f).tolist() == [0, 0]
+    bf.close()
