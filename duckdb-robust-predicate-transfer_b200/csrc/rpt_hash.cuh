@@ -165,6 +165,11 @@ __device__ __forceinline__ uint64_t hash_bytes(const uint8_t *p, uint32_t len) {
 	return murmur64(h);
 }
 
+// Internal column type (never crosses the C ABI): `data` holds the entries' 64-bit hashes.  A dictionary vector's
+// entries are hashed once and the rows gather the hashes through the selection — what the reference does with a
+// dictionary's cached hashes (vector_hash.cpp:484-491); same values, fewer string walks.
+constexpr int kTypePrehashed = 0x7001;
+
 // TightLoopHash body for one row (vector_hash.cpp:43-61): NULL rows hash to NULL_HASH.
 __device__ __forceinline__ uint64_t hash_col_row(const DevCol &c, uint64_t row) {
 	const uint64_t idx = c.sel ? static_cast<uint64_t>(__ldg(c.sel + row)) : row;
@@ -209,6 +214,8 @@ __device__ __forceinline__ uint64_t hash_col_row(const DevCol &c, uint64_t row) 
 		const uint32_t e = __ldg(off + idx + 1);
 		return hash_bytes(reinterpret_cast<const uint8_t *>(c.aux) + b, e - b);
 	}
+	case kTypePrehashed: // dictionary entries hashed once (launch_hash_entries); validity is already folded in
+		return __ldg(reinterpret_cast<const unsigned long long *>(c.data) + idx);
 	default:
 		return 0;
 	}

@@ -65,6 +65,10 @@ struct StatsRange {
 cudaError_t launch_check_statistics(const uint64_t *words, uint64_t num_sectors, const StatsRange *ranges, uint64_t count,
                                     uint8_t *results, cudaStream_t stream);
 
+// Hashes of the entries of one column (no selection applied): the dictionary of a dictionary vector, hashed once
+cudaError_t launch_hash_entries(const DeviceInfo &dev, const DevCol &col, uint64_t entries, uint64_t *out,
+                                cudaStream_t stream);
+
 // Column range (UpdateMinMax, physical_create_bf.cpp:82-176).  Keys are order-preserving uint64 images of the
 // values (signed: value ^ 2^63 after sign extension; float/double: sign-magnitude flip); the host decodes them.
 struct MinMaxState {

@@ -54,4 +54,25 @@ cudaError_t launch_check_statistics(const uint64_t *words, uint64_t num_sectors,
 	return cudaGetLastError();
 }
 
+// out[i] = hash of entry i of one column (NULL entries → NULL_HASH): the dictionary of a dictionary vector
+__global__ void __launch_bounds__(256)
+    hash_entries_kernel(const DevCol col, const uint64_t entries, uint64_t *__restrict__ out) {
+	const uint64_t step = static_cast<uint64_t>(gridDim.x) * blockDim.x;
+	for (uint64_t i = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < entries; i += step) {
+		out[i] = hash_col_row(col, i);
+	}
+}
+
+cudaError_t launch_hash_entries(const DeviceInfo &dev, const DevCol &col, uint64_t entries, uint64_t *out,
+                                cudaStream_t stream) {
+	if (entries == 0) {
+		return cudaSuccess;
+	}
+	uint64_t blocks = (entries + 255) / 256;
+	const uint64_t cap = static_cast<uint64_t>(dev.sm_count) * 8;
+	blocks = blocks < cap ? blocks : cap;
+	hash_entries_kernel<<<static_cast<unsigned>(blocks), 256, 0, stream>>>(col, entries, out);
+	return cudaGetLastError();
+}
+
 } // namespace rpt

@@ -339,9 +339,10 @@ def test_filter_sizes(rpt, oracle, est, n):
 
 @pytest.mark.parametrize("est,slices", [(50_000_000, 2), (100_000_000, 4), (300_000_000, 8)])
 def test_filters_beyond_one_l2_slice(rpt, oracle, est, slices):
-    """F = 128 / 256 / 512 MiB: the build runs in sector-range passes; the probe runs in sector-range passes (2 and
-    4 slices) or partitions the keys by slice (8 slices: probe_partition_kernel / probe_bucket_kernel; the whole
-    suite also runs with RPT_PROBE_PARTITION=1, which partitions for every sliced filter).  Ragged probe length;
+    """F = 128 / 256 / 512 MiB: the build runs in sector-range passes; the probe runs in sector-range passes (2
+    slices; 4-byte keys at 4 slices) or partitions the keys by slice (probe_partition_kernel / probe_bucket_kernel:
+    4 and 8 slices; test_probe_dispatch_forced_either_way repeats this test with either path forced at every
+    size).  Ragged probe length;
     a probe column whose keys all fall into one slice overflows the fixed (segment, slice) regions and takes the
     on-the-spot lookups instead."""
     assert oracle.num_sectors(est) == slices << 23
@@ -812,4 +813,78 @@ def test_check_statistics_zone_maps(rpt, oracle, type_id):
     # a physical type the reference does not prune on
     f = np.array([1.0, 2.0], dtype=np.float64)
     assert bf.CheckStatistics(rpt.DOUBLE, f, f).tolist() == [0, 0]
+    bf.close()
+
+
+@pytest.mark.parametrize("mode", ["0", "1"])
+def test_probe_dispatch_forced_either_way(mode):
+    """The dispatch between sector-range passes and the partitioned probe follows measurements; both
+    paths must be right at every sliced filter size, so the large-filter parity tests run again in a child process
+    with RPT_PROBE_PARTITION=0 (passes everywhere) and =1 (partition everywhere).  The knob is read once per
+    process, hence the child."""
+    import os
+    import subprocess
+    import sys
+    if os.environ.get("RPT_TEST_NESTED"):
+        pytest.skip("already inside the child run")
+    env = dict(os.environ, RPT_PROBE_PARTITION=mode, RPT_TEST_NESTED="1")
+    here = os.path.dirname(os.path.abspath(__file__))
+    proc = subprocess.run([sys.executable, "-m", "pytest", os.path.join(here, "test_gpu_parity.py"), "-x", "-q", "-m", "gpu",
+                           "-p", "no:cacheprovider", "-k", "beyond_one or flat_columns_every_regime"],
+                          env=env, capture_output=True, text=True, timeout=900)
+    assert proc.returncode == 0, proc.stdout[-3000:] + proc.stderr[-2000:]
+    assert " passed" in proc.stdout
+
+
+def test_dictionary_varchar_hashed_once(rpt, oracle):
+    """Dictionary vectors (a VARCHAR dictionary seen through a selection, vector_hash.cpp:484-491): the library
+    hashes the dictionary once and the rows gather the hashes.  Same words and selections as hashing row by row
+    (the oracle), NULL dictionary entries included; host columns, device columns, and duckdb::string_t dictionaries;
+    the extra launch shows that the short path was taken, and a dictionary longer than half the rows does not take it."""
+    import torch
+    rng = np.random.default_rng(77)
+    words_list = [b"k%d-%s" % (i, b"x" * int(rng.integers(0, 40))) for i in range(3000)]
+    off, blob = rpt.strings_to_arrow(words_list)
+    dval = random_validity(rng, len(words_list), 0.97)
+    n, m = 120_000, 400_003
+    bsel = rng.integers(0, 1500, n).astype(np.uint32)            # build rows use the first half of the dictionary
+    psel = rng.integers(0, len(words_list), m).astype(np.uint32)
+    build = rpt.host_varchar_col(off, blob, sel=bsel, validity=dval)
+    probe = rpt.host_varchar_col(off, blob, sel=psel, validity=dval)
+    bf = gpu_filter(rpt, n)
+    l0 = bf.launch_count
+    bf.Insert(build, n)
+    assert bf.launch_count - l0 == 2  # hash_entries_kernel + build_kernel
+    words = oracle.new_filter(n)
+    oracle.insert(words, build, n)
+    assert np.array_equal(bf.ExportWords(), words)
+    want = oracle.probe(words, probe, m)
+    assert np.array_equal(bf.LookupSel(probe, m), want)
+    assert 0 < want.size < m
+    # device-resident dictionary column
+    d_off, d_blob = torch.from_numpy(off.astype(np.int32)).cuda(), torch.from_numpy(np.concatenate([blob, np.zeros(8, np.uint8)])).cuda()
+    d_sel, d_val = torch.from_numpy(psel.astype(np.int32)).cuda(), torch.from_numpy(dval.view(np.int64)).cuda()
+    dcol = rpt.device_col(d_off, rpt.VARCHAR, sel=d_sel, validity=d_val, data_len=len(words_list), aux=d_blob,
+                          aux_bytes=blob.size)
+    dsel = torch.zeros(m, dtype=torch.int32, device="cuda")
+    dfound = torch.zeros(1, dtype=torch.int64, device="cuda")
+    bf.LookupSelDevice(dcol, m, dsel, dfound)
+    bf.Sync()
+    torch.cuda.synchronize()
+    f = int(dfound.item())
+    assert f == want.size and np.array_equal(dsel[:f].cpu().numpy().view(np.uint32), want)
+    # scan-side form through an incoming selection: rows are dictionary ids here, output = surviving in_sel entries
+    got = bf.FilterSel(rpt.host_varchar_col(off, blob, validity=dval), psel, m)
+    assert np.array_equal(got, psel[want])
+    # a dictionary longer than half the rows is hashed row by row (one launch fewer); same answer
+    short = 2 * len(words_list) - 1
+    l1 = bf.launch_count
+    got_short = bf.LookupSel(rpt.host_varchar_col(off, blob, sel=psel[:short], validity=dval), short)
+    took = bf.launch_count - l1
+    l2 = bf.launch_count
+    got_long = bf.LookupSel(rpt.host_varchar_col(off, blob, sel=psel[:2 * len(words_list)], validity=dval),
+                            2 * len(words_list))
+    assert bf.launch_count - l2 == took + 1
+    assert np.array_equal(got_short, want[want < short])
+    assert np.array_equal(got_long, want[want < 2 * len(words_list)])
     bf.close()
