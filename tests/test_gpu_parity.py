@@ -888,3 +888,53 @@ def test_dictionary_varchar_hashed_once(rpt, oracle):
     assert np.array_equal(got_short, want[want < short])
     assert np.array_equal(got_long, want[want < 2 * len(words_list)])
     bf.close()
+
+
+def test_concurrent_sink_and_probe_threads(rpt, oracle):
+    """The reference's threading contract: N sink threads Insert into ONE shared filter at the same
+    time (physical_create_bf.cpp:220-227, relaxed fetch_or), later N threads probe the finalized, read-only filter
+    with their own selection buffers (physical_use_bf.hpp:13-25).  Eight host threads do both through one handle:
+    the words equal a sequential build and every thread's selection equals the oracle's."""
+    import threading
+    rng = np.random.default_rng(808)
+    T, per = 8, 150_000
+    keys = rng.integers(-2**62, 2**62, T * per).astype(np.int64)
+    est = T * per
+    bf = gpu_filter(rpt, est)
+    errors = []
+
+    def sink(t):
+        try:
+            part = keys[t * per:(t + 1) * per]
+            for r0 in range(0, per, 30_000):  # several Insert calls per thread, interleaving with the others
+                bf.Insert(rpt.host_col(part[r0:r0 + 30_000]), min(30_000, per - r0))
+        except Exception as e:  # noqa: BLE001
+            errors.append(e)
+
+    threads = [threading.Thread(target=sink, args=(t,)) for t in range(T)]
+    [t.start() for t in threads]
+    [t.join() for t in threads]
+    assert not errors, errors
+    words = oracle.new_filter(est)
+    oracle.insert(words, rpt.host_col(keys), keys.size)
+    assert np.array_equal(bf.ExportWords(), words)
+    assert not bf.Finalize(keys.size)
+
+    probes = [np.where(rng.random(200_003) < 0.2, keys[rng.integers(0, keys.size, 200_003)],
+                       rng.integers(-2**62, 2**62, 200_003)).astype(np.int64) for _ in range(T)]
+    got = [None] * T
+
+    def probe(t):
+        try:
+            for _ in range(3):
+                got[t] = bf.LookupSel(rpt.host_col(probes[t]), probes[t].size)
+        except Exception as e:  # noqa: BLE001
+            errors.append(e)
+
+    threads = [threading.Thread(target=probe, args=(t,)) for t in range(T)]
+    [t.start() for t in threads]
+    [t.join() for t in threads]
+    assert not errors, errors
+    for t in range(T):
+        assert np.array_equal(got[t], oracle.probe(words, rpt.host_col(probes[t]), probes[t].size)), t
+    bf.close()
