@@ -393,23 +393,37 @@ static int stage_host_cols(const rpt_col_t *cols, int ncols, uint64_t r0, uint64
 	return 0;
 }
 
-// Dictionary vectors: a VARCHAR column seen through a selection whose dictionary is at most half as long as the
-// call has rows.  The dictionary is hashed once (launch_hash_entries) and the rows gather the hashes — the
-// reference reaches the same values through the dictionary's cached hashes (vector_hash.cpp:484-491).
-// plan_dictionary allocates (ordered on the staging stream, before the upload event); run_dictionary hashes and
-// swaps the column on the stream that consumes it.
-struct DictPlan {
+// String keys are hashed ahead of the build / probe kernels, which then read a column of 64-bit hashes:
+//  * dictionary vectors — a VARCHAR column seen through a selection whose dictionary is at most half as long as
+//    the call has rows: the dictionary is hashed once (launch_hash_entries) and the rows gather the hashes; the
+//    reference reaches the same values through the dictionary's cached hashes (vector_hash.cpp:484-491);
+//  * flat VARCHAR columns of at least kPrehashMinRows rows: launch_hash_varchar stages offsets and bytes through
+//    shared memory with coalesced loads instead of one dependent load chain per thread.
+// plan_prehash allocates (ordered on the staging stream, before the upload event); run_prehash hashes and swaps
+// the column on the stream that consumes it.
+static constexpr uint64_t kPrehashMinRows = 1ULL << 15;
+struct PrehashPlan {
 	uint64_t *hashes = nullptr;
 	uint64_t entries = 0;
+	bool dictionary = false;
 };
-static int plan_dictionary(const rpt_col_t *cols, int ncols, uint64_t count, const DevCols &dc, Staged *st,
-                           DictPlan *plan) {
-	if (ncols != 1 || !dc.c[0].sel || dc.c[0].type != RPT_VARCHAR) {
+static int plan_prehash(const rpt_col_t *cols, int ncols, uint64_t count, const DevCols &dc, Staged *st,
+                        PrehashPlan *plan) {
+	if (ncols != 1 || dc.c[0].type != RPT_VARCHAR) {
 		return 0;
 	}
-	const uint64_t entries = cols[0].data_len;
-	if (entries == 0 || entries > count / 2) {
-		return 0;
+	uint64_t entries;
+	if (dc.c[0].sel) {
+		entries = cols[0].data_len;
+		if (entries == 0 || entries > count / 2) {
+			return 0;
+		}
+		plan->dictionary = true;
+	} else {
+		if (count < kPrehashMinRows) {
+			return 0;
+		}
+		entries = count;
 	}
 	void *p;
 	RPT_TRY(st->alloc(&p, entries * sizeof(uint64_t)));
@@ -417,13 +431,17 @@ static int plan_dictionary(const rpt_col_t *cols, int ncols, uint64_t count, con
 	plan->entries = entries;
 	return 0;
 }
-static int run_dictionary(const DeviceInfo &dev, const DictPlan &plan, DevCols *dc, cudaStream_t s, int *launches) {
+static int run_prehash(const DeviceInfo &dev, const PrehashPlan &plan, DevCols *dc, cudaStream_t s, int *launches) {
 	if (!plan.hashes) {
 		return 0;
 	}
-	DevCol dict = dc->c[0];
-	dict.sel = nullptr;
-	RPT_CUDA(launch_hash_entries(dev, dict, plan.entries, plan.hashes, s));
+	if (plan.dictionary) {
+		DevCol dict = dc->c[0];
+		dict.sel = nullptr;
+		RPT_CUDA(launch_hash_entries(dev, dict, plan.entries, plan.hashes, s));
+	} else {
+		RPT_CUDA(launch_hash_varchar(dev, dc->c[0], plan.entries, plan.hashes, s));
+	}
 	(*launches)++;
 	dc->c[0].data = plan.hashes;
 	dc->c[0].aux = nullptr;
@@ -672,9 +690,9 @@ static int insert_impl(rpt_bf *bf, const rpt_col_t *cols, int ncols, uint64_t co
 		device_cols_view(cols, ncols, &dc);
 		Staged st;
 		st.stream = pick_stream(bf, stream_in);
-		DictPlan dict;
-		RPT_TRY(plan_dictionary(cols, ncols, count, dc, &st, &dict));
-		RPT_TRY(run_dictionary(bf->dev, dict, &dc, st.stream, &launches));
+		PrehashPlan pre;
+		RPT_TRY(plan_prehash(cols, ncols, count, dc, &st, &pre));
+		RPT_TRY(run_prehash(bf->dev, pre, &dc, st.stream, &launches));
 		RPT_CUDA(launch_build(bf->dev, dc, count, bf->words, bf->num_sectors, pick_stream(bf, stream_in), &launches));
 		RPT_TRY(minmax_hook(bf, dc, count, pick_stream(bf, stream_in), &launches));
 		bf->launches += launches;
@@ -703,11 +721,11 @@ static int insert_impl(rpt_bf *bf, const rpt_col_t *cols, int ncols, uint64_t co
 		st.free_stream = bf->compute;
 		DevCols dc;
 		RPT_TRY(stage_host_cols(cols, ncols, r0, r1, &st, &dc));
-		DictPlan dict;
-		RPT_TRY(plan_dictionary(cols, ncols, r1 - r0, dc, &st, &dict));
+		PrehashPlan pre;
+		RPT_TRY(plan_prehash(cols, ncols, r1 - r0, dc, &st, &pre));
 		RPT_CUDA(cudaEventRecord(sl.uploaded, bf->h2d));
 		RPT_CUDA(cudaStreamWaitEvent(bf->compute, sl.uploaded, 0));
-		RPT_TRY(run_dictionary(bf->dev, dict, &dc, bf->compute, &launches));
+		RPT_TRY(run_prehash(bf->dev, pre, &dc, bf->compute, &launches));
 		RPT_CUDA(launch_build(bf->dev, dc, r1 - r0, bf->words, bf->num_sectors, bf->compute, &launches));
 		RPT_TRY(minmax_hook(bf, dc, r1 - r0, bf->compute, &launches));
 		RPT_CUDA(cudaEventRecord(sl.computed, bf->compute));
@@ -908,9 +926,9 @@ static int probe_impl(const rpt_bf *bf, const rpt_col_t *cols, int ncols, uint64
 		st.stream = s;
 		void *scratch;
 		RPT_TRY(st.alloc(&scratch, probe_scratch_bytes(count, bf->num_sectors)));
-		DictPlan dict;
-		RPT_TRY(plan_dictionary(cols, ncols, count, dc, &st, &dict));
-		RPT_TRY(run_dictionary(bf->dev, dict, &dc, s, &launches));
+		PrehashPlan pre;
+		RPT_TRY(plan_prehash(cols, ncols, count, dc, &st, &pre));
+		RPT_TRY(run_prehash(bf->dev, pre, &dc, s, &launches));
 		if (out_mem == RPT_MEM_DEVICE) { // fully asynchronous
 			RPT_CUDA(launch_probe(bf->dev, dc, count, bf->words, bf->num_sectors, sel_out, found_out, 0, translate,
 			                      scratch, s, &launches));
@@ -993,12 +1011,12 @@ static int probe_impl(const rpt_bf *bf, const rpt_col_t *cols, int ncols, uint64
 			RPT_TRY(stage_host_cols(cols, ncols, r0, r1, &st, &dc));
 			void *scratch;
 			RPT_TRY(st.alloc(&scratch, probe_scratch_bytes(r1 - r0, bf->num_sectors)));
-			DictPlan dict;
-			RPT_TRY(plan_dictionary(cols, ncols, r1 - r0, dc, &st, &dict));
+			PrehashPlan pre;
+			RPT_TRY(plan_prehash(cols, ncols, r1 - r0, dc, &st, &pre));
 			RPT_CUDA(cudaEventRecord(sl.uploaded, mbf->h2d));
 			RPT_CUDA(cudaStreamWaitEvent(mbf->compute, sl.uploaded, 0));
 			RPT_CUDA(cudaStreamWaitEvent(mbf->compute, sl.drained, 0)); // dsel of chunk c-3 has left the device
-			RPT_TRY(run_dictionary(bf->dev, dict, &dc, mbf->compute, &launches));
+			RPT_TRY(run_prehash(bf->dev, pre, &dc, mbf->compute, &launches));
 			const uint32_t *translate = translate_col0 ? dc.c[0].sel : nullptr;
 			RPT_CUDA(launch_probe(bf->dev, dc, r1 - r0, bf->words, bf->num_sectors, sl.dsel, sl.dfound,
 			                      static_cast<uint32_t>(r0), translate, scratch, mbf->compute, &launches));

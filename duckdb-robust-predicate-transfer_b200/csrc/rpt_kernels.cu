@@ -82,17 +82,21 @@ __device__ __forceinline__ bool valid_row(const uint64_t *validity, uint64_t row
 
 // NULLABLE is a compile-time property: the all-valid variant carries no validity code at all (folding the check in
 // at run time cost the sector-range pass 8 registers and 7 % of its time, ncu r1 final vs r1c).
-template <bool NULLABLE>
+// PREHASHED: the column holds 64-bit hashes (strings hashed ahead by hash_varchar_kernel), not keys
+template <bool NULLABLE, bool PREHASHED = false>
 struct FlatU64SrcT { // one flat int64 / uint64 column (validity bitmap iff NULLABLE, no selection), base 16-byte aligned
 	static constexpr bool kNullable = NULLABLE;
 	static constexpr bool kStageable = true; // a segment is 512 contiguous 8-byte keys: cp.async-able
 	static constexpr int kKeyBytes = 8;
 	const uint64_t *keys;
 	const uint64_t *validity; // read iff NULLABLE
+	__device__ __forceinline__ static uint64_t key_hash(uint64_t k) {
+		return PREHASHED ? k : murmur64(k);
+	}
 	// KPU hashes out of one staged 16-byte unit
 	__device__ __forceinline__ static void hash_unit(const uint4 &v, uint64_t *h) {
-		h[0] = murmur64((static_cast<uint64_t>(v.y) << 32) | v.x);
-		h[1] = murmur64((static_cast<uint64_t>(v.w) << 32) | v.z);
+		h[0] = key_hash((static_cast<uint64_t>(v.y) << 32) | v.x);
+		h[1] = key_hash((static_cast<uint64_t>(v.w) << 32) | v.z);
 	}
 	__device__ __forceinline__ const uint64_t *key_ptr() const {
 		return keys;
@@ -101,7 +105,7 @@ struct FlatU64SrcT { // one flat int64 / uint64 column (validity bitmap iff NULL
 		if (NULLABLE && !valid_row(validity, row)) {
 			return kNullHash;
 		}
-		return murmur64(ld_stream_u64(keys + row, pol));
+		return key_hash(ld_stream_u64(keys + row, pol));
 	}
 	// unchecked: rows row0 + r*stride (+0,+1), r < R, all in range.  All R 128-bit loads are issued
 	// before the first hash so that they are in flight together.
@@ -115,8 +119,8 @@ struct FlatU64SrcT { // one flat int64 / uint64 column (validity bitmap iff NULL
 		}
 #pragma unroll
 		for (int r = 0; r < R; r++) {
-			h[2 * r] = murmur64(k[r].x);
-			h[2 * r + 1] = murmur64(k[r].y);
+			h[2 * r] = key_hash(k[r].x);
+			h[2 * r + 1] = key_hash(k[r].y);
 		}
 		if (NULLABLE) {
 #pragma unroll
@@ -1488,6 +1492,12 @@ static inline bool is_flat_u64(const DevCols &cols) {
 	return (c.type == RPT_INT64 || c.type == RPT_UINT64) && !c.sel &&
 	       (reinterpret_cast<uintptr_t>(c.data) & 15u) == 0 && (reinterpret_cast<uintptr_t>(c.validity) & 7u) == 0;
 }
+// A flat column of 64-bit hashes (a string column hashed ahead, rpt_capi.cu plan_prehash) takes the same path
+static inline bool is_flat_prehashed(const DevCols &cols) {
+	const DevCol &c = cols.c[0];
+	return cols.n == 1 && c.type == kTypePrehashed && !c.sel && !c.validity &&
+	       (reinterpret_cast<uintptr_t>(c.data) & 15u) == 0;
+}
 // ... and a single flat 4-byte integer column (INT32 / UINT32; DATE is INT32 physically) its own.
 static inline bool is_flat_u32(const DevCols &cols) {
 	if (cols.n != 1) {
@@ -1561,10 +1571,30 @@ static int partition_mode() {
 	}();
 	return mode;
 }
+// Slices the scratch buffer is sized for (the choice between passes and partition depends on the key source, which
+// the sizing call does not know): every sliced filter unless the partitioned probe is switched off.
 static inline int partition_slices(uint64_t num_sectors) {
 	const int slices = num_sectors > kSliceSectors ? static_cast<int>(num_sectors / kSliceSectors) : 0;
-	const int mode = partition_mode();
-	return (mode == 2 || (mode == 1 && slices >= 4)) ? slices : 0;
+	return partition_mode() == 0 ? 0 : slices;
+}
+// Passes or partition, by measurement (profiles/sweep_r1h.txt, profiles/sweep_r1o_varchar.txt).
+// Returns the number of slices to partition into, 0 for sector-range passes.
+template <class Src>
+static inline int partition_choice(uint64_t num_sectors) {
+	const int slices = partition_slices(num_sectors);
+	if (slices < 2 || partition_mode() == 2) {
+		return slices < 2 ? 0 : slices;
+	}
+	if (!Src::kStageable) {
+		return slices; // generic sources (strings, selections, several columns) hash each row once, not once per pass
+	}
+	if (slices == 2) {
+		return 0; // two passes over a flat column: 4.89 vs 6.08 ms per 1e9 int64 rows
+	}
+	if (slices == 4 && Src::kKeyBytes == 4) {
+		return 0; // four passes over a 4-byte column re-read 16 B per key: 6.92 vs 7.25 ms
+	}
+	return slices;
 }
 static inline int partition_cap(int slices) {
 	return slices == 2 ? PartCfg<2>::CAP : (slices == 4 ? PartCfg<4>::CAP : PartCfg<8>::CAP);
@@ -1623,6 +1653,10 @@ cudaError_t launch_build(const DeviceInfo &dev, const DevCols &cols, uint64_t co
 		SRC src {reinterpret_cast<const PTR_T *>(cols.c[0].data), cols.c[0].validity};                                 \
 		return agg ? launch_build_t<SRC, true>(dev, src, count, words, num_sectors, stream, launches)                  \
 		           : launch_build_t<SRC, false>(dev, src, count, words, num_sectors, stream, launches);                \
+	}
+	if (is_flat_prehashed(cols)) {
+		using PrehashedSrc = FlatU64SrcT<false, true>;
+		RPT_BUILD_FLAT(PrehashedSrc, uint64_t)
 	}
 	if (is_flat_u64(cols)) {
 		if (cols.c[0].validity) {
@@ -1829,11 +1863,7 @@ static cudaError_t launch_probe_src(const DeviceInfo &dev, const Src &src, uint6
 		return smem ? launch_probe_fused<Src, kProbeBlockSmem, true>(RPT_PROBE_ARGS)
 		            : launch_probe_fused<Src, kProbeBlock, false>(RPT_PROBE_ARGS);
 	}
-	int part_slices = smem ? 0 : partition_slices(num_sectors);
-	if (part_slices == 4 && partition_mode() == 1 && Src::kStageable && Src::kKeyBytes == 4) {
-		part_slices = 0; // four passes over a 4-byte column re-read 16 B per key: cheaper than 4 + 6 + 6 plus the placement
-	}
-	switch (part_slices) {
+	switch (smem ? 0 : partition_choice<Src>(num_sectors)) {
 	case 2:
 		return launch_probe_partitioned<Src, 2>(RPT_PROBE_ARGS);
 	case 4:
@@ -1868,6 +1898,10 @@ cudaError_t launch_probe(const DeviceInfo &dev, const DevCols &cols, uint64_t co
 		SRC src {reinterpret_cast<const PTR_T *>(cols.c[0].data), cols.c[0].validity};                                 \
 		return launch_probe_src(dev, src, count, words, num_sectors, sel_out, found_out, row_offset, translate,       \
 		                        scratch, stream, launches);                                                            \
+	}
+	if (is_flat_prehashed(cols)) {
+		using PrehashedSrc = FlatU64SrcT<false, true>;
+		RPT_PROBE_FLAT(PrehashedSrc, uint64_t)
 	}
 	if (is_flat_u64(cols)) {
 		if (cols.c[0].validity) {

@@ -69,6 +69,10 @@ cudaError_t launch_check_statistics(const uint64_t *words, uint64_t num_sectors,
 cudaError_t launch_hash_entries(const DeviceInfo &dev, const DevCol &col, uint64_t entries, uint64_t *out,
                                 cudaStream_t stream);
 
+// out[i] = hash of row i of a flat VARCHAR column (offsets + bytes, optional validity), staged through shared memory
+cudaError_t launch_hash_varchar(const DeviceInfo &dev, const DevCol &col, uint64_t count, uint64_t *out,
+                                cudaStream_t stream);
+
 // Column range (UpdateMinMax, physical_create_bf.cpp:82-176).  Keys are order-preserving uint64 images of the
 // values (signed: value ^ 2^63 after sign extension; float/double: sign-magnitude flip); the host decodes them.
 struct MinMaxState {

@@ -938,3 +938,58 @@ def test_concurrent_sink_and_probe_threads(rpt, oracle):
     for t in range(T):
         assert np.array_equal(got[t], oracle.probe(words, rpt.host_col(probes[t]), probes[t].size)), t
     bf.close()
+
+
+@pytest.mark.parametrize("shape", ["short", "mixed", "long"])
+def test_flat_varchar_staged_hashing(rpt, oracle, shape, torch_cuda):
+    """Flat VARCHAR columns of ≥ 2^15 rows are hashed by hash_varchar_kernel (128-row steps staged through shared
+    memory) ahead of the build / probe kernels.  short: decimal-text keys (every step staged); mixed: lengths 0..70
+    with empty strings and NULLs (steps whose bytes exceed the 4 KiB buffer fall back to global loads); long: 100+
+    byte strings (always the fallback).  Ragged row counts leave a partial last step.  Host and device columns."""
+    import torch
+    rng = np.random.default_rng({"short": 1, "mixed": 2, "long": 3}[shape])
+    n, m = 70_001, 333_337
+
+    def make(count, pool):
+        if shape == "short":
+            strs = [b"%d" % int(v) for v in rng.integers(0, 2**62, count)]
+        elif shape == "mixed":
+            strs = [bytes(rng.integers(97, 123, int(l), dtype=np.uint8)) for l in rng.integers(0, 71, count)]
+        else:
+            strs = [bytes(rng.integers(97, 123, int(l), dtype=np.uint8)) for l in rng.integers(100, 180, count)]
+        if pool is not None:  # every fifth row is a build-side string
+            for i in range(0, count, 5):
+                strs[i] = pool[int(rng.integers(0, len(pool)))]
+        return strs
+
+    bstr = make(n, None)
+    pstr = make(m, bstr)
+    boff, bblob = rpt.strings_to_arrow(bstr)
+    poff, pblob = rpt.strings_to_arrow(pstr)
+    bval = random_validity(rng, n, 0.98)
+    pval = random_validity(rng, m, 0.9)
+    build = rpt.host_varchar_col(boff, bblob, validity=bval)
+    probe = rpt.host_varchar_col(poff, pblob, validity=pval)
+    bf = gpu_filter(rpt, n)
+    l0 = bf.launch_count
+    bf.Insert(build, n)
+    assert bf.launch_count - l0 == 2  # hash_varchar_kernel + build_kernel
+    words = oracle.new_filter(n)
+    oracle.insert(words, build, n)
+    assert np.array_equal(bf.ExportWords(), words)
+    want = oracle.probe(words, probe, m)
+    assert np.array_equal(bf.LookupSel(probe, m), want)
+    assert m // 6 < want.size < m
+    # device-resident column, unaligned byte buffer start (the kernel aligns its copies itself)
+    d_off = torch.from_numpy((poff.astype(np.int64) + 3).astype(np.int32)).cuda()
+    d_blob = torch.from_numpy(np.concatenate([np.zeros(3, np.uint8), pblob, np.zeros(16, np.uint8)])).cuda()
+    d_val = torch.from_numpy(pval.view(np.int64)).cuda()
+    dcol = rpt.device_col(d_off, rpt.VARCHAR, validity=d_val, data_len=m, aux=d_blob, aux_bytes=pblob.size + 3)
+    dsel = torch.zeros(m, dtype=torch.int32, device="cuda")
+    dfound = torch.zeros(1, dtype=torch.int64, device="cuda")
+    bf.LookupSelDevice(dcol, m, dsel, dfound)
+    bf.Sync()
+    torch.cuda.synchronize()
+    f = int(dfound.item())
+    assert f == want.size and np.array_equal(dsel[:f].cpu().numpy().view(np.uint32), want)
+    bf.close()

@@ -13,7 +13,33 @@ m = int(float(sys.argv[1])) if len(sys.argv) > 1 else 1_000_000_000
 reps = int(sys.argv[2]) if len(sys.argv) > 2 else 5
 cases = [int(float(x)) for x in (sys.argv[3] if len(sys.argv) > 3 else "80000,1e7,4e7,1e8").split(",")]
 ppm = int(os.environ.get("SWEEP_PPM", "100000"))
-ktype = os.environ.get("SWEEP_TYPE", "int64")  # int64 | int32 (low 31 bits of the synthetic keys: GenericSrc / 4-byte path)
+ktype = os.environ.get("SWEEP_TYPE", "int64")  # int64 | int32 (low 31 bits of the synthetic keys) | varchar (decimal text of the keys)
+
+
+def decimal_text(x):
+    """int64 tensor (non-negative after masking) → Arrow utf8 layout on the device: (int32 offsets[n+1], uint8 bytes):
+    k2 = decimal text of k1.  Column by column to bound the temporaries."""
+    x = x & 0x7fffffffffffffff
+    n = x.numel()
+    ndig = torch.ones(n, dtype=torch.int64, device=x.device)
+    p = 10
+    for _ in range(18):
+        ndig += (x >= p).to(torch.int64)
+        p *= 10
+    offsets = torch.zeros(n + 1, dtype=torch.int64, device=x.device)
+    torch.cumsum(ndig, 0, out=offsets[1:])
+    total = int(offsets[-1].item())
+    blob = torch.empty(total + 8, dtype=torch.uint8, device=x.device)
+    p = 1
+    for d in range(19):  # digit d counted from the right goes to offsets[i+1] - 1 - d
+        has = ndig > d
+        pos = (offsets[1:] - 1 - d)[has]
+        blob[pos] = ((x[has] // p) % 10 + 48).to(torch.uint8)
+        p *= 10
+        del has, pos
+    return offsets.to(torch.int32), blob, total
+
+
 dev = torch.device("cuda", 0)
 stream = torch.cuda.Stream(device=dev)
 torch.cuda.set_stream(stream)
@@ -32,6 +58,12 @@ for n in cases:
         dk32, dp32 = (dk & 0x7fffffff).to(torch.int32), (dp & 0x7fffffff).to(torch.int32)
         torch.cuda.synchronize()
         kc, pc = rpt.device_col(dk32, rpt.INT32), rpt.device_col(dp32, rpt.INT32)
+    elif ktype == "varchar":
+        ko, kb, kt = decimal_text(dk)
+        po, pb, pt = decimal_text(dp)
+        torch.cuda.synchronize()
+        kc = rpt.device_col(ko, rpt.VARCHAR, aux=kb, aux_bytes=kt, data_len=n)
+        pc = rpt.device_col(po, rpt.VARCHAR, aux=pb, aux_bytes=pt, data_len=m)
     else:
         kc, pc = rpt.device_col(dk, rpt.INT64), rpt.device_col(dp, rpt.INT64)
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
@@ -55,6 +87,8 @@ for n in cases:
     bm, pm = ev[0].elapsed_time(ev[1]) / reps, ev[2].elapsed_time(ev[3]) / reps
     found = int(dfound.item())
     algo = (4 if ktype == "int32" else 8) * m + 4 * found + F
+    if ktype == "varchar":
+        algo = 4 * (m + 1) + pt + 4 * found + F  # offsets + string bytes replace 8·m
     print(f"n={n:>10} F={F / 2**20:8.3f} MiB  build {bm:7.3f} ms {n / bm / 1e6:7.1f} Gkeys/s | probe {pm:7.3f} ms "
           f"{m / pm / 1e6:7.1f} Gkeys/s  {algo / pm / 1e6:7.1f} GB/s algorithmic  found {found}", flush=True)
     bf.close()
