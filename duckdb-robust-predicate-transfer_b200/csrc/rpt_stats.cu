@@ -89,39 +89,30 @@ __device__ __forceinline__ void cp_async_8(void *smem, const void *gmem) {
 	             : "memory");
 }
 
+__device__ __forceinline__ void cp_async_16_cg(void *smem, const void *gmem) {
+	asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(static_cast<uint32_t>(__cvta_generic_to_shared(smem))),
+	             "l"(gmem)
+	             : "memory");
+}
+
+// Hash(string_t) (hash.cpp:77-151) of a string that starts byte_pos bytes into buf (shared memory).  Branch-free
+// on the alignment: block j is cut out of three consecutive 32-bit words with two byte permutes (the selector
+// depends on byte_pos & 3 only); the last, partial block is masked — zero padding, as the reference's tail step.
+// Reads up to 8 bytes past the string (masked out; the buffer is padded).
 __device__ __forceinline__ uint64_t hash_bytes_smem(const uint64_t *buf, uint32_t byte_pos, uint32_t len) {
-	// string_t / hash.cpp:77-151 arithmetic as in hash_bytes(); the string starts byte_pos bytes into buf
 	uint64_t h = 0xe17a1465ULL ^ (static_cast<uint64_t>(len) * 0xc6a4a7935bd1e995ULL);
-	if (len != 0) {
-		const uint32_t a = (byte_pos & 7u) * 8u;
-		const uint64_t *w = buf + (byte_pos >> 3);
-		const uint32_t nwords = ((byte_pos & 7u) + len + 7u) >> 3;
-		uint64_t cur = w[0];
-		uint32_t wi = 1;
-		uint32_t remaining = len;
-		while (remaining >= 8u) {
-			uint64_t blk = cur >> a;
-			if (a != 0) {
-				const uint64_t nxt = w[wi];
-				blk |= nxt << (64u - a);
-				cur = nxt;
-			} else if (wi < nwords) {
-				cur = w[wi];
-			}
-			wi++;
-			h ^= blk;
-			h *= kMurmurK;
-			remaining -= 8u;
-		}
-		if (remaining != 0u) {
-			uint64_t blk = cur >> a;
-			if (a != 0 && wi < nwords) {
-				blk |= w[wi] << (64u - a);
-			}
-			blk &= (~0ULL) >> (64u - remaining * 8u);
-			h ^= blk;
-			h *= kMurmurK;
-		}
+	const uint32_t *w = reinterpret_cast<const uint32_t *>(buf) + (byte_pos >> 2);
+	const uint32_t sel = 0x3210u + 0x1111u * (byte_pos & 3u);
+	uint32_t x0 = w[0];
+	for (uint32_t done = 0; done < len; done += 8u) {
+		const uint32_t x1 = w[1], x2 = w[2];
+		uint64_t blk = (static_cast<uint64_t>(__byte_perm(x1, x2, sel)) << 32) | __byte_perm(x0, x1, sel);
+		const uint32_t rem = len - done; // ≥ 1
+		blk &= (~0ULL) >> (64u - (rem < 8u ? rem : 8u) * 8u);
+		h ^= blk;
+		h *= kMurmurK;
+		x0 = x2;
+		w += 2;
 	}
 	return murmur64(h);
 }
@@ -143,22 +134,27 @@ __device__ __forceinline__ bool var_issue_bytes(uint64_t *buf, const uint32_t *o
 	const uint32_t rows = count - row0 < kVarRows ? static_cast<uint32_t>(count - row0) : kVarRows;
 	const uint32_t b0 = offs[0], b1 = offs[var_off_index(rows)];
 	const uintptr_t first = reinterpret_cast<uintptr_t>(bytes + b0);
-	const uintptr_t base = first & ~static_cast<uintptr_t>(7); // 8-byte aligned start of the copy
+	const uintptr_t base = first & ~static_cast<uintptr_t>(15); // 16-byte aligned start of the copy
 	const uint32_t words = static_cast<uint32_t>((reinterpret_cast<uintptr_t>(bytes + b1) - base + 7) >> 3);
 	*skew = static_cast<uint32_t>(first - base) - b0;
 	if (rows != kVarRows || words > kVarBufWords) {
 		return false;
 	}
-	const uint64_t *g = reinterpret_cast<const uint64_t *>(base);
-	for (uint32_t u = lane; u < words; u += 32u) {
-		cp_async_8(buf + u, g + u);
+	// 16-byte copies; an odd last word goes alone, so nothing past the 8-byte multiple that holds the last byte is read
+	const ulonglong2 *g = reinterpret_cast<const ulonglong2 *>(base);
+	ulonglong2 *d = reinterpret_cast<ulonglong2 *>(buf);
+	for (uint32_t u = lane; u < (words >> 1); u += 32u) {
+		cp_async_16_cg(d + u, g + u);
+	}
+	if ((words & 1u) && lane == 0) {
+		cp_async_8(buf + words - 1, reinterpret_cast<const uint64_t *>(base) + words - 1);
 	}
 	return true;
 }
 
 __global__ void __launch_bounds__(kVarWarps * 32)
     hash_varchar_kernel(const DevCol col, const uint64_t count, uint64_t *__restrict__ out) {
-	__shared__ __align__(16) uint64_t s_buf[kVarWarps][2][kVarBufWords + 1];
+	__shared__ __align__(16) uint64_t s_buf[kVarWarps][2][kVarBufWords + 2];
 	__shared__ uint32_t s_off[kVarWarps][3][kVarOffWords];
 	const uint32_t lane = threadIdx.x & 31u;
 	const uint32_t warp = threadIdx.x >> 5;
