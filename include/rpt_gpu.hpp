@@ -190,6 +190,56 @@ private:
 };
 
 // ------------------------------------------------------------------------------------------------------------
+// Scan-side mirror of duckdb::BFTableFilter (duckdb/src/planner/filter/bloom_filter.cpp:84-196): the filter a
+// forward-pass CREATE_BF pushes into the probe table's scan (physical_create_bf.cpp:321-332).  Same three
+// entry points, on the GPU-resident words.
+// ------------------------------------------------------------------------------------------------------------
+class BFTableFilter {
+public:
+	explicit BFTableFilter(const PTBloomFilter &filter) : filter_(filter) {
+	}
+	// Filter (:94-131).  `keys` is the scan's key vector (no selection of its own); `sel` holds the
+	// approved_count row ids still alive when sel_is_set, and has room for approved_count entries either way.
+	// All rows pass → nothing is touched.  Otherwise sel[0..found) = the surviving row ids (translated back
+	// through the incoming selection, :117-123), sel_is_set = true, approved_count = found.  Returns found.
+	uint64_t Filter(const rpt_col_t &keys, uint32_t *sel, bool &sel_is_set, uint64_t &approved_count) {
+		if (approved_count == 0) {
+			return 0;
+		}
+		if (out_.size() < approved_count) {
+			out_.resize(approved_count); // state.bf_sel (:96-100)
+		}
+		uint64_t found = 0;
+		Check(rpt_bf_filter_sel(filter_.handle(), &keys, sel_is_set ? sel : nullptr, approved_count, out_.data(), &found,
+		                        RPT_MEM_HOST, nullptr));
+		if (found == approved_count) {
+			return approved_count; // :112-115
+		}
+		std::memcpy(sel, out_.data(), found * sizeof(uint32_t));
+		sel_is_set = true;
+		approved_count = found;
+		return found;
+	}
+	// FilterValue (:133-136) on value.Hash()
+	bool FilterValue(uint64_t hash) const {
+		uint8_t hit = 0;
+		Check(rpt_bf_lookup_hashes_host(filter_.handle(), &hash, 1, &hit));
+		return hit != 0;
+	}
+	// CheckStatistics (:138-196) for one row group
+	rpt_prune CheckStatistics(int physical_type, const void *min, const void *max, bool has_minmax = true) const {
+		const uint8_t has = has_minmax ? 1 : 0;
+		uint8_t res = RPT_NO_PRUNING_POSSIBLE;
+		filter_.CheckStatistics(physical_type, min, max, &has, 1, &res);
+		return static_cast<rpt_prune>(res);
+	}
+
+private:
+	const PTBloomFilter &filter_;
+	std::vector<uint32_t> out_;
+};
+
+// ------------------------------------------------------------------------------------------------------------
 // Materialises the key column of successive chunks into one flat pinned column — what
 // `local_state.local_data->Append(chunk)` does for the whole chunk in PhysicalCreateBF::Sink
 // (physical_create_bf.cpp:214-216), restricted to the key column.  Dictionary / sliced vectors are resolved

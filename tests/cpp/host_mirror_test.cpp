@@ -200,6 +200,59 @@ static void TestCreateAndUse(uint32_t est, uint64_t build_rows, bool expect_rebu
 		REQUIRE(f == rpto_probe(want.data(), want.size(), &ocol, 1, probe[i].count, osel.data()));
 		REQUIRE(memcmp(sel.data(), osel.data(), f * 4) == 0);
 	}
+	// scan-side BFTableFilter: a vector of 2048 keys, first unfiltered, then through a selection left by an earlier
+	// table filter; FilterValue and CheckStatistics on single values
+	{
+		rpt::BFTableFilter scan(bf);
+		std::vector<int64_t> vec(rpt::kStandardVectorSize);
+		uint64_t x = 77 + est;
+		for (size_t i = 0; i < vec.size(); i++) {
+			x = rpto_splitmix64(x);
+			vec[i] = (i % 3 == 0) ? build[0].data[build[0].sel.empty() ? i % build[0].count : build[0].sel[i % build[0].count]]
+			                      : static_cast<int64_t>(x >> 2);
+		}
+		rpt_col_t keys {};
+		keys.data = vec.data();
+		keys.type = RPT_INT64;
+		keys.mem = RPT_MEM_HOST;
+		keys.data_len = vec.size();
+		std::vector<uint64_t> hashes(vec.size());
+		rpto_col_t okeys = AsOracle(keys);
+		rpto_hash_columns(&okeys, 1, vec.size(), hashes.data());
+		std::vector<uint32_t> osel(vec.size() + 1), ssel(vec.size());
+		const uint64_t of = rpto_lookup_hashes(want.data(), want.size(), hashes.data(), vec.size(), osel.data());
+		bool is_set = false;
+		uint64_t approved = vec.size();
+		REQUIRE(scan.Filter(keys, ssel.data(), is_set, approved) == of);
+		REQUIRE(approved == of && (is_set || of == vec.size()));
+		REQUIRE(of == vec.size() || memcmp(ssel.data(), osel.data(), of * 4) == 0);
+		// now with an incoming selection: every other row
+		std::vector<uint32_t> in(vec.size() / 2);
+		for (size_t i = 0; i < in.size(); i++) {
+			in[i] = static_cast<uint32_t>(2 * i + 1);
+		}
+		std::vector<uint32_t> expect;
+		for (uint32_t r : in) {
+			const uint64_t h = hashes[r];
+			const uint64_t m = rpto_mask(h);
+			if ((want[h & (want.size() - 1)] & m) == m) {
+				expect.push_back(r);
+			}
+		}
+		is_set = true;
+		approved = in.size();
+		const uint64_t f2 = scan.Filter(keys, in.data(), is_set, approved);
+		REQUIRE(f2 == expect.size() && approved == f2);
+		REQUIRE(f2 == in.size() || memcmp(in.data(), expect.data(), f2 * 4) == 0);
+		for (size_t i = 0; i < 64; i++) {
+			const uint64_t m = rpto_mask(hashes[i]);
+			REQUIRE(scan.FilterValue(hashes[i]) == ((want[hashes[i] & (want.size() - 1)] & m) == m));
+		}
+		const int64_t lo = vec[0] - 3, hi = vec[0] + 3;
+		REQUIRE(scan.CheckStatistics(RPT_INT64, &lo, &hi) ==
+		        rpto_check_statistics(want.data(), want.size(), RPTO_INT64, &lo, &hi, 1));
+		REQUIRE(scan.CheckStatistics(RPT_INT64, &vec[0], &vec[0]) == RPT_FILTER_ALWAYS_TRUE); // a build key
+	}
 	printf("  est=%u rows=%llu S=%llu rebuilt=%d survivors=%llu\n", est, (unsigned long long)build_rows,
 	       (unsigned long long)want.size(), (int)res.rebuilt, (unsigned long long)survivors);
 }
