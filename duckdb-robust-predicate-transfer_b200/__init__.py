@@ -88,6 +88,19 @@ _SIGNATURES = {
     "rpt_bf_peer_merge_phase": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p]),
     "rpt_bf_peer_close": (C.c_int, [C.c_void_p]),
     "rpt_bf_allreduce_or": (C.c_int, [C.POINTER(C.c_void_p), C.c_int]),
+    "rpt_abf_log_blocks_for_rows": (C.c_int, [C.c_uint64, C.POINTER(C.c_int)]),
+    "rpt_abf_create": (C.c_int, [C.POINTER(C.c_void_p), C.c_uint64, C.c_int]),
+    "rpt_abf_destroy": (C.c_int, [C.c_void_p]),
+    "rpt_abf_log_num_blocks": (C.c_int, [C.c_void_p, C.POINTER(C.c_int)]),
+    "rpt_abf_mask_bits": (C.c_int, [C.c_void_p]),
+    "rpt_abf_insert": (C.c_int, [C.c_void_p, C.POINTER(RptCol), C.c_int, C.c_uint64, C.c_void_p]),
+    "rpt_abf_fold": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(C.c_int)]),
+    "rpt_abf_probe": (C.c_int, [C.c_void_p, C.POINTER(RptCol), C.c_int, C.c_uint64, C.c_void_p, C.c_void_p, C.c_int,
+                                C.c_void_p]),
+    "rpt_abf_export_blocks": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64]),
+    "rpt_abf_device_blocks": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p)]),
+    "rpt_abf_sync": (C.c_int, [C.c_void_p]),
+    "rpt_abf_launch_count": (C.c_int, [C.c_void_p, C.POINTER(C.c_longlong)]),
     "rpt_synth_build_keys": (C.c_int, [C.c_void_p, C.c_uint64, C.c_uint64, C.c_int, C.c_void_p]),
     "rpt_synth_probe_keys": (C.c_int, [C.c_void_p, C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint32, C.c_int,
                                        C.c_void_p]),
@@ -369,6 +382,93 @@ class PTBloomFilter:
 
     def PeerClose(self):
         _check(lib().rpt_bf_peer_close(self._h))
+
+
+class BlockedBloomFilter:
+    """The filter the reference's README.md:23-32 describes (Arrow Acero BlockedBloomFilter: 1024-entry mask table,
+    8 bits per key, Fold) over rpt_abf_*.  NOT the reference's code path — parity unpinned; the
+    reference-exact filter is PTBloomFilter above."""
+
+    def __init__(self, device=0):
+        self._h = C.c_void_p(None)
+        self.device = device
+
+    def CreateEmpty(self, num_rows_to_insert):
+        self.close()
+        _check(lib().rpt_abf_create(C.byref(self._h), int(num_rows_to_insert), self.device))
+        return self
+
+    def close(self):
+        if self._h:
+            lib().rpt_abf_destroy(self._h)
+            self._h = C.c_void_p(None)
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    @property
+    def log_num_blocks(self):
+        out = C.c_int(0)
+        _check(lib().rpt_abf_log_num_blocks(self._h, C.byref(out)))
+        return out.value
+
+    @property
+    def launch_count(self):
+        out = C.c_longlong(0)
+        _check(lib().rpt_abf_launch_count(self._h, C.byref(out)))
+        return out.value
+
+    @property
+    def device_blocks(self):
+        out = C.c_void_p(None)
+        _check(lib().rpt_abf_device_blocks(self._h, C.byref(out)))
+        return out.value
+
+    def Insert(self, cols, count, stream=None):
+        arr, n = _col_array(cols)
+        _check(lib().rpt_abf_insert(self._h, arr, n, count, stream))
+
+    def Fold(self, stream=None):
+        """Returns the number of halvings."""
+        out = C.c_int(0)
+        _check(lib().rpt_abf_fold(self._h, stream, C.byref(out)))
+        return out.value
+
+    def Find(self, cols, count):
+        """Ascending row ids of the rows that pass (uint32 numpy array)."""
+        arr, n = _col_array(cols)
+        sel = np.empty(max(count, 1), dtype=np.uint32)
+        found = C.c_uint64(0)
+        _check(lib().rpt_abf_probe(self._h, arr, n, count, sel.ctypes.data, C.addressof(found), MEM_HOST, None))
+        return sel[: found.value]
+
+    def FindDevice(self, cols, count, sel_out_ptr, found_out_ptr, stream=None):
+        arr, n = _col_array(cols)
+        _check(lib().rpt_abf_probe(self._h, arr, n, count, _ptr(sel_out_ptr), _ptr(found_out_ptr), MEM_DEVICE,
+                                   stream))
+
+    def ExportBlocks(self):
+        out = np.empty(1 << self.log_num_blocks, dtype=np.uint64)
+        _check(lib().rpt_abf_export_blocks(self._h, out.ctypes.data, out.shape[0]))
+        return out
+
+    def Sync(self):
+        _check(lib().rpt_abf_sync(self._h))
+
+
+def acero_mask_bits():
+    out = np.zeros(136, dtype=np.uint8)
+    _check(lib().rpt_abf_mask_bits(out.ctypes.data))
+    return out
+
+
+def acero_log_blocks_for_rows(rows):
+    out = C.c_int(0)
+    _check(lib().rpt_abf_log_blocks_for_rows(int(rows), C.byref(out)))
+    return out.value
 
 
 def allreduce_or(filters):

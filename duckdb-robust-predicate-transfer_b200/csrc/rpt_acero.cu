@@ -1,0 +1,312 @@
+// rpt_acero.cu — the README-described filter variant (reference README.md:23-32): an Acero-style blocked bloom
+// filter with a 1024-entry table of 57-bit masks (4–5 bits set), 8 bits per key and Fold (OR the halves together
+// until more than a quarter of the bits are set).
+//
+// NOT ON THE PARITY PATH.  No source, test or vector of this filter exists in the reference at this commit
+// (SURVEY §0): src/bloom_filter.cpp wraps DuckDB's native BloomFilter, which rpt_kernels.cu reproduces bit for
+// bit.  This file follows the published Apache Arrow algorithm the README names (arrow/acero/bloom_filter.{h,cc},
+// Arrow 21: BloomFilterMasks, BlockedBloomFilter::CreateEmpty / mask / block_id / Insert / Find / Fold /
+// SingleFold), fed with the same DuckDB key hashes as the reference path.  Parity is "unpinned": it is checked
+// against oracle/acero_oracle.cpp, an independent CPU restatement of the same published algorithm.
+//
+// Kernels (sm_100a): build (128-bit key loads, red.or.b64 into 64-bit blocks), popcount, fold, and a row-ordered
+// bitmap probe whose output goes through the same scan + compaction kernels as the reference path.
+#include <cuda_runtime.h>
+
+#include <cstdint>
+#include <cstring>
+#include <random>
+
+#include "rpt_kernels.cuh"
+
+namespace rpt {
+namespace acero {
+
+// ---------------------------------------------------------------------------------------------
+// mask table (host): a 1024+56-bit vector in which every 57-bit window holds 4 or 5 set bits; mask i is the
+// window starting at bit i.  Generated like BloomFilterMasks::BloomFilterMasks() — mt19937 seeded with eight
+// zeros, uniform_int_distribution<uint64_t> — so the table equals the one a libstdc++ Arrow build holds.
+// ---------------------------------------------------------------------------------------------
+static inline bool get_bit(const uint8_t *bits, int64_t i) {
+	return (bits[i >> 3] >> (i & 7)) & 1;
+}
+static inline void set_bit(uint8_t *bits, int64_t i) {
+	bits[i >> 3] |= static_cast<uint8_t>(1u << (i & 7));
+}
+
+void generate_mask_bits(uint8_t *out) {
+	std::seed_seq seed {0, 0, 0, 0, 0, 0, 0, 0};
+	std::mt19937 engine(seed);
+	std::uniform_int_distribution<uint64_t> dist;
+	auto random = [&](int lo, int hi) { return lo + dist(engine) % static_cast<uint64_t>(hi - lo + 1); };
+
+	memset(out, 0, kMaskBytes);
+	// the first window: 4 or 5 distinct positions
+	int in_window = static_cast<int>(random(kMinBitsSet, kMaxBitsSet));
+	for (int placed = 0; placed < in_window;) {
+		const int pos = static_cast<int>(random(0, kBitsPerMask - 1));
+		if (!get_bit(out, pos)) {
+			set_bit(out, pos);
+			placed++;
+		}
+	}
+	// slide the window one bit at a time; in_window = set bits of the window that ends at the current bit
+	const int64_t total_bits = kNumMasks + kBitsPerMask - 1;
+	for (int64_t i = kBitsPerMask; i < total_bits; i++) {
+		const int leaving = get_bit(out, i - kBitsPerMask) ? 1 : 0;
+		if (leaving == 1 && in_window == kMinBitsSet) {
+			set_bit(out, i); // forced 1: the window would drop below the minimum
+			continue;
+		}
+		if (leaving == 0 && in_window == kMaxBitsSet) {
+			continue; // forced 0: the window is full
+		}
+		if (random(0, kBitsPerMask * 2 - 1) < static_cast<uint64_t>(kMinBitsSet + kMaxBitsSet)) {
+			set_bit(out, i);
+			if (leaving == 0) {
+				in_window++;
+			}
+		} else if (leaving == 1) {
+			in_window--;
+		}
+	}
+}
+
+void expand_masks(const uint8_t *bits, uint64_t *out) {
+	uint8_t padded[kMaskBytes + 8];
+	memset(padded, 0, sizeof(padded));
+	memcpy(padded, bits, kMaskBytes);
+	for (int i = 0; i < kNumMasks; i++) {
+		uint64_t w;
+		memcpy(&w, padded + i / 8, 8);
+		out[i] = (w >> (i % 8)) & kFullMask;
+	}
+}
+
+// ---------------------------------------------------------------------------------------------
+// device side
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ void stage_masks(uint64_t *s_masks, const uint64_t *__restrict__ masks) {
+	for (uint32_t i = threadIdx.x; i < kNumMasks; i += blockDim.x) {
+		s_masks[i] = __ldg(masks + i);
+	}
+	__syncthreads();
+}
+
+// BlockedBloomFilter::mask(uint64_t hash): low 10 bits pick the mask, the next 6 rotate it
+__device__ __forceinline__ uint64_t key_mask(const uint64_t *s_masks, uint64_t h) {
+	const uint64_t m = s_masks[static_cast<uint32_t>(h) & (kNumMasks - 1)];
+	const uint32_t r = (static_cast<uint32_t>(h) >> kLogNumMasks) & 63u;
+	return (m << r) | (m >> ((64u - r) & 63u));
+}
+// BlockedBloomFilter::block_id: the bits above those
+__device__ __forceinline__ uint64_t key_block(uint64_t h, uint64_t block_mask) {
+	return (h >> (kLogNumMasks + 6)) & block_mask;
+}
+
+__device__ __forceinline__ void red_or(uint64_t *addr, uint64_t v) {
+	asm volatile("red.global.or.b64 [%0], %1;" ::"l"(addr), "l"(v) : "memory");
+}
+
+constexpr int kBlock = 256;
+
+// Build.  FLAT64: one flat, all-valid 8-byte integer column — two keys per 128-bit load, four keys in flight.
+template <bool FLAT64>
+__global__ void __launch_bounds__(kBlock)
+    abf_build_kernel(const DevCols cols, const uint64_t count, uint64_t *__restrict__ blocks, const uint64_t block_mask,
+                     const uint64_t *__restrict__ masks) {
+	__shared__ uint64_t s_masks[kNumMasks];
+	stage_masks(s_masks, masks);
+	const uint64_t tid = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+	const uint64_t nthreads = static_cast<uint64_t>(gridDim.x) * blockDim.x;
+	if (FLAT64) {
+		const ulonglong2 *keys2 = reinterpret_cast<const ulonglong2 *>(cols.c[0].data);
+		const uint64_t pairs = count >> 1;
+		uint64_t i = tid;
+		for (; i + nthreads < pairs; i += 2 * nthreads) {
+			const ulonglong2 a = __ldg(keys2 + i);
+			const ulonglong2 b = __ldg(keys2 + i + nthreads);
+			const uint64_t h0 = murmur64(a.x), h1 = murmur64(a.y), h2 = murmur64(b.x), h3 = murmur64(b.y);
+			red_or(blocks + key_block(h0, block_mask), key_mask(s_masks, h0));
+			red_or(blocks + key_block(h1, block_mask), key_mask(s_masks, h1));
+			red_or(blocks + key_block(h2, block_mask), key_mask(s_masks, h2));
+			red_or(blocks + key_block(h3, block_mask), key_mask(s_masks, h3));
+		}
+		for (; i < pairs; i += nthreads) {
+			const ulonglong2 a = __ldg(keys2 + i);
+			const uint64_t h0 = murmur64(a.x), h1 = murmur64(a.y);
+			red_or(blocks + key_block(h0, block_mask), key_mask(s_masks, h0));
+			red_or(blocks + key_block(h1, block_mask), key_mask(s_masks, h1));
+		}
+		if ((count & 1) && tid == 0) {
+			const uint64_t h = murmur64(__ldg(reinterpret_cast<const unsigned long long *>(cols.c[0].data) + count - 1));
+			red_or(blocks + key_block(h, block_mask), key_mask(s_masks, h));
+		}
+	} else {
+		for (uint64_t row = tid; row < count; row += nthreads) {
+			const uint64_t h = hash_row(cols, row);
+			red_or(blocks + key_block(h, block_mask), key_mask(s_masks, h));
+		}
+	}
+}
+
+// Number of set bits of blocks[0, n) added to *total (Fold's density test)
+__global__ void __launch_bounds__(kBlock)
+    abf_popcount_kernel(const ulonglong2 *__restrict__ blocks2, const uint64_t n2, unsigned long long *total) {
+	uint64_t acc = 0;
+	const uint64_t step = static_cast<uint64_t>(gridDim.x) * blockDim.x;
+	for (uint64_t i = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n2; i += step) {
+		const ulonglong2 v = __ldg(blocks2 + i);
+		acc += __popcll(v.x) + __popcll(v.y);
+	}
+#pragma unroll
+	for (int d = 16; d > 0; d >>= 1) {
+		acc += __shfl_down_sync(0xffffffffu, acc, d);
+	}
+	if ((threadIdx.x & 31) == 0 && acc) {
+		atomicAdd(total, static_cast<unsigned long long>(acc));
+	}
+}
+
+// SingleFold(num_folds): slice 0 |= slices 1 .. 2^num_folds - 1, in place.  Entry i of slice 0 is read and written
+// by one thread only, so there is no ordering to respect between threads.
+__global__ void __launch_bounds__(kBlock)
+    abf_fold_kernel(ulonglong2 *__restrict__ blocks2, const uint64_t slice2, const uint32_t num_slices) {
+	const uint64_t step = static_cast<uint64_t>(gridDim.x) * blockDim.x;
+	for (uint64_t i = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < slice2; i += step) {
+		ulonglong2 acc = blocks2[i];
+		uint32_t s = 1;
+		for (; s + 1 < num_slices; s += 2) { // two independent loads in flight
+			const ulonglong2 a = blocks2[s * slice2 + i];
+			const ulonglong2 b = blocks2[(s + 1) * slice2 + i];
+			acc.x |= a.x | b.x;
+			acc.y |= a.y | b.y;
+		}
+		if (s < num_slices) {
+			const ulonglong2 a = blocks2[s * slice2 + i];
+			acc.x |= a.x;
+			acc.y |= a.y;
+		}
+		blocks2[i] = acc;
+	}
+}
+
+// Probe: Find for every row, answers as a row-ordered bitmap (bit r of the bitmap = row r).  A warp takes kUnroll
+// consecutive 32-row words per iteration: all key loads first, then all block loads, then the ballots.
+// words_padded covers whole 512-row segments so that the compaction kernels never see an uninitialised word.
+constexpr int kUnroll = 4;
+template <bool FLAT64>
+__global__ void __launch_bounds__(kBlock)
+    abf_probe_bitmap_kernel(const DevCols cols, const uint64_t count, const uint64_t words_padded,
+                            const uint64_t *__restrict__ blocks, const uint64_t block_mask,
+                            const uint64_t *__restrict__ masks, uint32_t *__restrict__ bitmap32) {
+	__shared__ uint64_t s_masks[kNumMasks];
+	stage_masks(s_masks, masks);
+	const uint32_t lane = threadIdx.x & 31u;
+	const uint64_t warp = (static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
+	const uint64_t nwarps = (static_cast<uint64_t>(gridDim.x) * blockDim.x) >> 5;
+	const uint64_t groups = (words_padded + kUnroll - 1) / kUnroll;
+	for (uint64_t g = warp; g < groups; g += nwarps) {
+		uint64_t h[kUnroll];
+		bool live[kUnroll];
+#pragma unroll
+		for (int u = 0; u < kUnroll; u++) {
+			const uint64_t row = (g * kUnroll + u) * 32 + lane;
+			live[u] = row < count;
+			h[u] = 0;
+			if (live[u]) {
+				h[u] = FLAT64 ? murmur64(__ldg(reinterpret_cast<const unsigned long long *>(cols.c[0].data) + row))
+				              : hash_row(cols, row);
+			}
+		}
+		uint64_t b[kUnroll];
+#pragma unroll
+		for (int u = 0; u < kUnroll; u++) {
+			b[u] = live[u] ? __ldg(blocks + key_block(h[u], block_mask)) : 0ull;
+		}
+#pragma unroll
+		for (int u = 0; u < kUnroll; u++) {
+			const uint64_t m = key_mask(s_masks, h[u]);
+			const uint32_t word = __ballot_sync(0xffffffffu, live[u] && (b[u] & m) == m);
+			const uint64_t w = g * kUnroll + u;
+			if (lane == 0 && w < words_padded) {
+				bitmap32[w] = word;
+			}
+		}
+	}
+}
+
+static inline unsigned grid_for(const DeviceInfo &dev, uint64_t items, int per_sm) {
+	const uint64_t want = (items + kBlock - 1) / kBlock;
+	const uint64_t cap = static_cast<uint64_t>(dev.sm_count > 0 ? dev.sm_count : 148) * per_sm;
+	return static_cast<unsigned>(want < cap ? (want ? want : 1) : cap);
+}
+
+static inline bool flat64(const DevCols &cols) {
+	const DevCol &c = cols.c[0];
+	return cols.n == 1 && !c.sel && !c.validity && (c.type == RPT_INT64 || c.type == RPT_UINT64) &&
+	       (reinterpret_cast<uintptr_t>(c.data) & 15u) == 0;
+}
+
+cudaError_t launch_build(const DeviceInfo &dev, const DevCols &cols, uint64_t count, uint64_t *blocks,
+                         uint64_t num_blocks, const uint64_t *masks, cudaStream_t stream) {
+	if (count == 0) {
+		return cudaSuccess;
+	}
+	if (flat64(cols)) {
+		abf_build_kernel<true><<<grid_for(dev, count / 4 + 1, 8), kBlock, 0, stream>>>(cols, count, blocks,
+		                                                                              num_blocks - 1, masks);
+	} else {
+		abf_build_kernel<false><<<grid_for(dev, count, 8), kBlock, 0, stream>>>(cols, count, blocks, num_blocks - 1,
+		                                                                        masks);
+	}
+	return cudaGetLastError();
+}
+
+cudaError_t launch_popcount(const DeviceInfo &dev, const uint64_t *blocks, uint64_t num_blocks, uint64_t *total,
+                            cudaStream_t stream) {
+	cudaError_t e = cudaMemsetAsync(total, 0, sizeof(uint64_t), stream);
+	if (e != cudaSuccess) {
+		return e;
+	}
+	abf_popcount_kernel<<<grid_for(dev, num_blocks / 2, 8), kBlock, 0, stream>>>(
+	    reinterpret_cast<const ulonglong2 *>(blocks), num_blocks / 2, reinterpret_cast<unsigned long long *>(total));
+	return cudaGetLastError();
+}
+
+cudaError_t launch_fold(const DeviceInfo &dev, uint64_t *blocks, uint64_t num_blocks, int num_folds,
+                        cudaStream_t stream) {
+	const uint64_t slice = num_blocks >> num_folds;
+	abf_fold_kernel<<<grid_for(dev, slice / 2, 8), kBlock, 0, stream>>>(reinterpret_cast<ulonglong2 *>(blocks),
+	                                                                   slice / 2, 1u << num_folds);
+	return cudaGetLastError();
+}
+
+cudaError_t launch_probe(const DeviceInfo &dev, const DevCols &cols, uint64_t count, const uint64_t *blocks,
+                         uint64_t num_blocks, const uint64_t *masks, uint32_t *sel_out, uint64_t *found_out,
+                         uint32_t row_offset, void *scratch, cudaStream_t stream, int *launches) {
+	if (count == 0) {
+		return cudaMemsetAsync(found_out, 0, sizeof(uint64_t), stream);
+	}
+	uint32_t *bitmap32 = bitmap_words(scratch, count);
+	const uint64_t words_padded = (count + 511) / 512 * 16;
+	const unsigned grid = grid_for(dev, (words_padded + kUnroll - 1) / kUnroll * 32, 8);
+	if (flat64(cols)) {
+		abf_probe_bitmap_kernel<true><<<grid, kBlock, 0, stream>>>(cols, count, words_padded, blocks, num_blocks - 1,
+		                                                           masks, bitmap32);
+	} else {
+		abf_probe_bitmap_kernel<false><<<grid, kBlock, 0, stream>>>(cols, count, words_padded, blocks, num_blocks - 1,
+		                                                            masks, bitmap32);
+	}
+	cudaError_t e = cudaGetLastError();
+	if (e != cudaSuccess) {
+		return e;
+	}
+	if (launches) {
+		(*launches)++;
+	}
+	return launch_bitmap_to_sel(dev, count, sel_out, found_out, row_offset, scratch, stream, launches);
+}
+
+} // namespace acero
+} // namespace rpt

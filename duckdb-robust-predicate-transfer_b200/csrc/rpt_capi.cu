@@ -8,6 +8,7 @@
 #include <cuda_runtime.h>
 
 #include <atomic>
+#include <memory>
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
@@ -1483,5 +1484,289 @@ int rpt_synth_probe_keys(uint64_t *dev_out, uint64_t first, uint64_t count, uint
 	RPT_CUDA(launch_synth_probe(dev_out, first, count, n_build, sel_ppm, reinterpret_cast<cudaStream_t>(stream)));
 	return 0;
 }
+
+// ---------------------------------------------------------------------------------------------
+// README-described filter variant (reference README.md:23-32): Acero-style blocked bloom filter with the
+// 1024-entry mask table and Fold.  NOT on the parity path — see rpt_acero.cu and rpt_gpu.h.
+// ---------------------------------------------------------------------------------------------
+struct rpt_abf {
+	DeviceInfo dev;
+	int log_num_blocks = 0;
+	uint64_t num_blocks = 0;
+	uint64_t *blocks = nullptr;  // allocation keeps its CreateEmpty size; Fold only shrinks num_blocks
+	uint64_t *masks = nullptr;   // kNumMasks expanded 57-bit masks (8 KiB), staged into shared memory by the kernels
+	uint64_t *counter = nullptr; // device scalar (popcount / found)
+	cudaStream_t stream = nullptr;
+	std::atomic<long long> launches {0};
+};
+
+static cudaStream_t abf_stream(const rpt_abf *f, rpt_stream_t s) {
+	return s ? reinterpret_cast<cudaStream_t>(s) : f->stream;
+}
+
+// BlockedBloomFilter::CreateEmpty: 8 bits per key, at least 512 bits, rounded up to a power of two
+static int abf_log_blocks_for_rows(uint64_t rows) {
+	uint64_t min_bits = rows > (1ULL << 58) ? (1ULL << 61) : rows * 8;
+	if (min_bits < 512) {
+		min_bits = 512;
+	}
+	int log_bits = 0;
+	while ((1ULL << log_bits) < min_bits) {
+		log_bits++;
+	}
+	return log_bits - 6;
+}
+
+int rpt_abf_log_blocks_for_rows(uint64_t rows, int *out) {
+	if (!out) {
+		return set_error("null output argument");
+	}
+	*out = abf_log_blocks_for_rows(rows);
+	return 0;
+}
+
+int rpt_abf_mask_bits(uint8_t *out136) {
+	if (!out136) {
+		return set_error("null output argument");
+	}
+	acero::generate_mask_bits(out136);
+	return 0;
+}
+
+int rpt_abf_create(rpt_abf_t **out, uint64_t num_rows, int device) {
+	if (!out) {
+		return set_error("null output argument");
+	}
+	*out = nullptr;
+	const int log_blocks = abf_log_blocks_for_rows(num_rows);
+	if (log_blocks > 32) {
+		return set_error("a filter for %llu rows would need 2^%d blocks", (unsigned long long)num_rows, log_blocks);
+	}
+	std::unique_ptr<rpt_abf> f(new rpt_abf());
+	RPT_TRY(fill_device_info(device, &f->dev));
+	RPT_GUARD(f);
+	f->log_num_blocks = log_blocks;
+	f->num_blocks = 1ULL << log_blocks;
+	RPT_CUDA(cudaStreamCreateWithFlags(&f->stream, cudaStreamNonBlocking));
+	RPT_CUDA(cudaMalloc(reinterpret_cast<void **>(&f->blocks), f->num_blocks * sizeof(uint64_t)));
+	RPT_CUDA(cudaMalloc(reinterpret_cast<void **>(&f->masks), acero::kNumMasks * sizeof(uint64_t)));
+	RPT_CUDA(cudaMalloc(reinterpret_cast<void **>(&f->counter), sizeof(uint64_t)));
+	uint8_t bits[acero::kMaskBytes];
+	std::vector<uint64_t> masks(acero::kNumMasks);
+	acero::generate_mask_bits(bits);
+	acero::expand_masks(bits, masks.data());
+	RPT_CUDA(cudaMemcpyAsync(f->masks, masks.data(), masks.size() * sizeof(uint64_t), cudaMemcpyHostToDevice, f->stream));
+	RPT_CUDA(cudaMemsetAsync(f->blocks, 0, f->num_blocks * sizeof(uint64_t), f->stream));
+	RPT_CUDA(cudaStreamSynchronize(f->stream));
+	*out = f.release();
+	return 0;
+}
+
+int rpt_abf_destroy(rpt_abf_t *f) {
+	if (!f) {
+		return 0;
+	}
+	{
+		RPT_GUARD(f);
+		cudaStreamSynchronize(f->stream);
+		cudaFree(f->blocks);
+		cudaFree(f->masks);
+		cudaFree(f->counter);
+		cudaStreamDestroy(f->stream);
+	}
+	delete f;
+	return 0;
+}
+
+int rpt_abf_log_num_blocks(const rpt_abf_t *f, int *out) {
+	if (!f || !out) {
+		return set_error("null argument");
+	}
+	*out = f->log_num_blocks;
+	return 0;
+}
+
+int rpt_abf_launch_count(const rpt_abf_t *f, long long *out) {
+	if (!f || !out) {
+		return set_error("null argument");
+	}
+	*out = f->launches.load();
+	return 0;
+}
+
+int rpt_abf_sync(const rpt_abf_t *f) {
+	if (!f) {
+		return set_error("null filter handle");
+	}
+	RPT_GUARD(f);
+	RPT_CUDA(cudaStreamSynchronize(f->stream));
+	return 0;
+}
+
+int rpt_abf_device_blocks(const rpt_abf_t *f, uint64_t **dev_ptr_out) {
+	if (!f || !dev_ptr_out) {
+		return set_error("null argument");
+	}
+	*dev_ptr_out = f->blocks;
+	return 0;
+}
+
+// Insert for every row.  Device columns: asynchronous on `stream`.  Host columns: uploaded chunk by chunk on the
+// handle's stream, returns when the rows are in the filter.
+int rpt_abf_insert(rpt_abf_t *f, const rpt_col_t *cols, int ncols, uint64_t count, rpt_stream_t stream) {
+	if (!f) {
+		return set_error("null filter handle");
+	}
+	int mem = 0;
+	RPT_TRY(validate_cols(cols, ncols, count, &mem));
+	if (count == 0) {
+		return 0;
+	}
+	RPT_GUARD(f);
+	cudaStream_t s = abf_stream(f, stream);
+	if (mem == RPT_MEM_DEVICE) {
+		DevCols dc;
+		device_cols_view(cols, ncols, &dc);
+		RPT_CUDA(acero::launch_build(f->dev, dc, count, f->blocks, f->num_blocks, f->masks, s));
+		f->launches += 1;
+		return 0;
+	}
+	const uint64_t chunk = any_sel(cols, ncols) ? count : chunk_rows();
+	for (uint64_t r0 = 0; r0 < count; r0 += chunk) {
+		const uint64_t r1 = r0 + chunk < count ? r0 + chunk : count;
+		Staged st;
+		st.stream = s;
+		DevCols dc;
+		RPT_TRY(stage_host_cols(cols, ncols, r0, r1, &st, &dc));
+		RPT_CUDA(acero::launch_build(f->dev, dc, r1 - r0, f->blocks, f->num_blocks, f->masks, s));
+		f->launches += 1;
+	}
+	RPT_CUDA(cudaStreamSynchronize(s));
+	return 0;
+}
+
+// BlockedBloomFilter::Fold: while fewer than a quarter of the bits are set (and more than 2^4 blocks remain), OR
+// 2^k equal slices into the first one, k chosen so that the expected density stays under a quarter.  Needs the
+// popcount on the host, so it synchronises `stream`.  *num_folds_out = total number of halvings.
+int rpt_abf_fold(rpt_abf_t *f, rpt_stream_t stream, int *num_folds_out) {
+	if (!f) {
+		return set_error("null filter handle");
+	}
+	RPT_GUARD(f);
+	cudaStream_t s = abf_stream(f, stream);
+	int total_folds = 0;
+	for (;;) {
+		if (f->log_num_blocks <= acero::kLogNumBlocksMin) {
+			break;
+		}
+		const uint64_t num_bits = f->num_blocks * 64;
+		uint64_t bits_set = 0;
+		RPT_CUDA(acero::launch_popcount(f->dev, f->blocks, f->num_blocks, f->counter, s));
+		RPT_CUDA(cudaMemcpyAsync(&bits_set, f->counter, sizeof(uint64_t), cudaMemcpyDeviceToHost, s));
+		RPT_CUDA(cudaStreamSynchronize(s));
+		f->launches += 1;
+		if (4 * bits_set >= num_bits) {
+			break;
+		}
+		int num_folds = 1;
+		while ((f->log_num_blocks - num_folds) > acero::kLogNumBlocksMin && (4 * bits_set) < (num_bits >> num_folds)) {
+			num_folds++;
+		}
+		RPT_CUDA(acero::launch_fold(f->dev, f->blocks, f->num_blocks, num_folds, s));
+		f->launches += 1;
+		f->log_num_blocks -= num_folds;
+		f->num_blocks = 1ULL << f->log_num_blocks;
+		total_folds += num_folds;
+	}
+	if (num_folds_out) {
+		*num_folds_out = total_folds;
+	}
+	return 0;
+}
+
+// Find for every row → ascending row ids of the rows that pass.  out_mem = RPT_MEM_DEVICE: device outputs, device
+// columns, asynchronous.  RPT_MEM_HOST: host outputs (columns in either space), returns when sel_out is filled.
+int rpt_abf_probe(const rpt_abf_t *f, const rpt_col_t *cols, int ncols, uint64_t count, uint32_t *sel_out,
+                  uint64_t *found_out, int out_mem, rpt_stream_t stream) {
+	if (!f) {
+		return set_error("null filter handle");
+	}
+	int mem = 0;
+	RPT_TRY(validate_cols(cols, ncols, count, &mem));
+	if (!found_out || (count > 0 && !sel_out)) {
+		return set_error("null output argument");
+	}
+	if (count >= (1ULL << 32)) {
+		return set_error("count %llu does not fit the uint32 selection vector; split the batch",
+		                 (unsigned long long)count);
+	}
+	if (out_mem == RPT_MEM_DEVICE && mem != RPT_MEM_DEVICE) {
+		return set_error("device outputs require device key columns");
+	}
+	RPT_GUARD(f);
+	rpt_abf *mf = const_cast<rpt_abf *>(f);
+	cudaStream_t s = abf_stream(f, stream);
+	int launches = 0;
+	if (out_mem == RPT_MEM_DEVICE) {
+		DevCols dc;
+		device_cols_view(cols, ncols, &dc);
+		Staged st;
+		st.stream = s;
+		void *scratch;
+		RPT_TRY(st.alloc(&scratch, bitmap_scratch_bytes(count)));
+		RPT_CUDA(acero::launch_probe(f->dev, dc, count, f->blocks, f->num_blocks, f->masks, sel_out, found_out, 0,
+		                             scratch, s, &launches));
+		mf->launches += launches;
+		return 0;
+	}
+	*found_out = 0;
+	const uint64_t chunk = (mem == RPT_MEM_DEVICE || any_sel(cols, ncols)) ? count : chunk_rows();
+	uint64_t total = 0;
+	for (uint64_t r0 = 0; r0 < count; r0 += chunk) {
+		const uint64_t r1 = r0 + chunk < count ? r0 + chunk : count;
+		const uint64_t n = r1 - r0;
+		Staged st;
+		st.stream = s;
+		DevCols dc;
+		if (mem == RPT_MEM_DEVICE) {
+			device_cols_view(cols, ncols, &dc);
+		} else {
+			RPT_TRY(stage_host_cols(cols, ncols, r0, r1, &st, &dc));
+		}
+		void *scratch, *dsel, *dfound;
+		RPT_TRY(st.alloc(&scratch, bitmap_scratch_bytes(n)));
+		RPT_TRY(st.alloc(&dsel, n * sizeof(uint32_t)));
+		RPT_TRY(st.alloc(&dfound, sizeof(uint64_t)));
+		RPT_CUDA(acero::launch_probe(f->dev, dc, n, f->blocks, f->num_blocks, f->masks,
+		                             reinterpret_cast<uint32_t *>(dsel), reinterpret_cast<uint64_t *>(dfound),
+		                             static_cast<uint32_t>(r0), scratch, s, &launches));
+		uint64_t found = 0;
+		RPT_CUDA(cudaMemcpyAsync(&found, dfound, sizeof(uint64_t), cudaMemcpyDeviceToHost, s));
+		RPT_CUDA(cudaStreamSynchronize(s));
+		if (found) {
+			RPT_CUDA(cudaMemcpyAsync(sel_out + total, dsel, found * sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+			RPT_CUDA(cudaStreamSynchronize(s));
+		}
+		total += found;
+	}
+	mf->launches += launches;
+	*found_out = total;
+	return 0;
+}
+
+int rpt_abf_export_blocks(const rpt_abf_t *f, uint64_t *host_dst, uint64_t capacity_blocks) {
+	if (!f || !host_dst) {
+		return set_error("null argument");
+	}
+	if (capacity_blocks < f->num_blocks) {
+		return set_error("destination holds %llu blocks, the filter has %llu", (unsigned long long)capacity_blocks,
+		                 (unsigned long long)f->num_blocks);
+	}
+	RPT_GUARD(f);
+	RPT_CUDA(cudaStreamSynchronize(f->stream));
+	RPT_CUDA(cudaMemcpy(host_dst, f->blocks, f->num_blocks * sizeof(uint64_t), cudaMemcpyDeviceToHost));
+	return 0;
+}
+
 
 } // extern "C"

@@ -1925,6 +1925,38 @@ cudaError_t launch_probe(const DeviceInfo &dev, const DevCols &cols, uint64_t co
 	                        stream, launches);
 }
 
+// Row-ordered bitmap → ordered selection vector, for producers outside this file (rpt_acero.cu): the scratch is
+// laid out like a phased probe's (segment offsets, block totals, bitmap); the producer fills bitmap_words() for
+// whole 512-row segments, this counts the segments, scans and compacts.
+size_t bitmap_scratch_bytes(uint64_t count) {
+	return align_up(phased_layout(count).bytes, 256);
+}
+uint32_t *bitmap_words(void *scratch, uint64_t count) {
+	return reinterpret_cast<uint32_t *>(reinterpret_cast<char *>(scratch) + phased_layout(count).off_hitbits);
+}
+cudaError_t launch_bitmap_to_sel(const DeviceInfo &dev, uint64_t count, uint32_t *sel_out, uint64_t *found_out,
+                                 uint32_t row_offset, void *scratch, cudaStream_t stream, int *launches) {
+	const PhasedLayout lay = phased_layout(count);
+	char *base = reinterpret_cast<char *>(scratch);
+	uint32_t *seg_offsets = reinterpret_cast<uint32_t *>(base);
+	uint32_t *block_totals = reinterpret_cast<uint32_t *>(base + lay.off_totals);
+	const uint32_t *bitmap = reinterpret_cast<const uint32_t *>(base + lay.off_hitbits);
+	const uint64_t num_segs = ceil_div(count, kSegRows);
+	count_segments_kernel<<<stream_grid(dev, num_segs, 256), 256, 0, stream>>>(
+	    reinterpret_cast<const uint4 *>(bitmap), num_segs, seg_offsets);
+	const uint64_t nblocks = ceil_div(num_segs, kScanBlock);
+	scan_blocks_kernel<<<static_cast<unsigned>(nblocks), 1024, 0, stream>>>(seg_offsets, num_segs, block_totals);
+	scan_totals_kernel<<<1, 1024, 0, stream>>>(block_totals, static_cast<uint32_t>(nblocks), found_out);
+	const uint64_t cwant = ceil_div((num_segs + 1) / 2, 8ull);
+	const uint64_t ccap = static_cast<uint64_t>(dev.sm_count) * 6;
+	compact_bitmap_kernel<<<static_cast<unsigned>(cwant < ccap ? cwant : ccap), 256, 0, stream>>>(
+	    bitmap, seg_offsets, block_totals, num_segs, sel_out, row_offset, nullptr);
+	if (launches) {
+		(*launches) += 4;
+	}
+	return cudaGetLastError();
+}
+
 cudaError_t launch_or_parts(const DeviceInfo &dev, uint64_t *words, const uint64_t *parts, uint64_t num_sectors,
                             uint64_t nparts, cudaStream_t stream) {
 	const uint64_t nvec = num_sectors >> 1;

@@ -84,6 +84,32 @@ struct MinMaxState {
 cudaError_t launch_minmax(const DeviceInfo &dev, const DevCol &col, uint64_t count, MinMaxState *state,
                           cudaStream_t stream);
 
+// Row-ordered bitmap → ordered selection vector (count_segments + scans + compaction), shared with rpt_acero.cu
+size_t bitmap_scratch_bytes(uint64_t count);
+uint32_t *bitmap_words(void *scratch, uint64_t count);
+cudaError_t launch_bitmap_to_sel(const DeviceInfo &dev, uint64_t count, uint32_t *sel_out, uint64_t *found_out,
+                                 uint32_t row_offset, void *scratch, cudaStream_t stream, int *launches);
+
+// README-described filter variant (reference README.md:23-32; Arrow Acero BlockedBloomFilter) — rpt_acero.cu.
+// Not on the parity path: the reference holds no code for it.
+namespace acero {
+constexpr int kBitsPerMask = 57, kMinBitsSet = 4, kMaxBitsSet = 5, kLogNumMasks = 10, kNumMasks = 1 << kLogNumMasks;
+constexpr int kMaskBytes = (kNumMasks + 64) / 8; // bit vector the 1024 overlapping masks are windows of
+constexpr uint64_t kFullMask = (1ULL << kBitsPerMask) - 1;
+constexpr int kLogNumBlocksMin = 4; // Fold never goes below 2^4 blocks... it stops once log_num_blocks <= 4
+void generate_mask_bits(uint8_t *out /* kMaskBytes */);
+void expand_masks(const uint8_t *bits, uint64_t *out /* kNumMasks */);
+cudaError_t launch_build(const DeviceInfo &dev, const DevCols &cols, uint64_t count, uint64_t *blocks,
+                         uint64_t num_blocks, const uint64_t *masks, cudaStream_t stream);
+cudaError_t launch_popcount(const DeviceInfo &dev, const uint64_t *blocks, uint64_t num_blocks, uint64_t *total,
+                            cudaStream_t stream);
+cudaError_t launch_fold(const DeviceInfo &dev, uint64_t *blocks, uint64_t num_blocks, int num_folds,
+                        cudaStream_t stream);
+cudaError_t launch_probe(const DeviceInfo &dev, const DevCols &cols, uint64_t count, const uint64_t *blocks,
+                         uint64_t num_blocks, const uint64_t *masks, uint32_t *sel_out, uint64_t *found_out,
+                         uint32_t row_offset, void *scratch, cudaStream_t stream, int *launches);
+} // namespace acero
+
 // SURVEY §8(d) synthetic columns
 cudaError_t launch_synth_build(uint64_t *out, uint64_t first, uint64_t count, cudaStream_t stream);
 cudaError_t launch_synth_probe(uint64_t *out, uint64_t first, uint64_t count, uint64_t n_build, uint32_t sel_ppm,

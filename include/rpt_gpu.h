@@ -223,6 +223,43 @@ RPT_API int rpt_synth_build_keys(uint64_t *dev_out, uint64_t first, uint64_t cou
 RPT_API int rpt_synth_probe_keys(uint64_t *dev_out, uint64_t first, uint64_t count, uint64_t n_build,
                                  uint32_t sel_ppm, int device, rpt_stream_t stream);
 
+/* ---- README-described filter variant — PARITY UNPINNED, not the reference's code path ---------
+ * The reference's README.md:23-32 (and BASELINE.json's north_star) describe an Apache-Arrow-Acero
+ * BlockedBloomFilter: one 64-bit block per key, a pre-generated table of 1024 57-bit masks with 4-5
+ * bits set, 8 bits per key, and Fold (OR the halves together until more than 25 % of the bits are
+ * set).  No such code exists in the reference at this commit: src/bloom_filter.cpp wraps
+ * DuckDB's native BloomFilter, which the rpt_bf_* entry points above replace bit for bit.  rpt_abf_*
+ * implements the published Arrow algorithm (arrow/acero/bloom_filter.{h,cc}: BloomFilterMasks,
+ * BlockedBloomFilter::CreateEmpty/mask/block_id/Insert/Find/Fold/SingleFold) over the same DuckDB key
+ * hashes (same rpt_col_t columns, NULL rows hash to NULL_HASH).  It is checked against an independent
+ * CPU restatement (oracle/acero_oracle.cpp), never against the reference, and nothing on the rpt_bf_*
+ * path calls it.  A maintainer who lands the README's filter in src/bloom_filter.cpp would bind these
+ * the way INTEGRATION.md binds rpt_bf_*. */
+typedef struct rpt_abf rpt_abf_t;
+/* CreateEmpty(num_rows): 2^log_num_blocks 64-bit blocks, log = ceil(log2(max(512, 8*num_rows))) - 6 */
+RPT_API int rpt_abf_log_blocks_for_rows(uint64_t rows, int *out);
+RPT_API int rpt_abf_create(rpt_abf_t **out, uint64_t num_rows, int device);
+RPT_API int rpt_abf_destroy(rpt_abf_t *f);
+RPT_API int rpt_abf_log_num_blocks(const rpt_abf_t *f, int *out); /* shrinks with every fold */
+/* The 136-byte bit vector whose 57-bit windows are the 1024 masks (BloomFilterMasks::masks_) */
+RPT_API int rpt_abf_mask_bits(uint8_t *out136);
+/* Insert(hash(row)) for every row.  Device columns: asynchronous on `stream`.  Host columns: returns
+ * when the rows are in the filter. */
+RPT_API int rpt_abf_insert(rpt_abf_t *f, const rpt_col_t *cols, int ncols, uint64_t count, rpt_stream_t stream);
+/* Fold(): synchronises `stream` (the density test needs the popcount on the host).
+ * *num_folds_out (optional) = number of halvings performed. */
+RPT_API int rpt_abf_fold(rpt_abf_t *f, rpt_stream_t stream, int *num_folds_out);
+/* Find(hash(row)) for every row -> ascending row ids of the rows that pass + their number.
+ * out_mem = RPT_MEM_DEVICE: sel_out / found_out are device pointers, columns must be device columns,
+ * asynchronous on `stream`.  RPT_MEM_HOST: host outputs, returns when they are filled. */
+RPT_API int rpt_abf_probe(const rpt_abf_t *f, const rpt_col_t *cols, int ncols, uint64_t count, uint32_t *sel_out,
+                          uint64_t *found_out, int out_mem, rpt_stream_t stream);
+/* Copies the 2^log_num_blocks blocks to the host (after work on a caller's stream, synchronise it first). */
+RPT_API int rpt_abf_export_blocks(const rpt_abf_t *f, uint64_t *host_dst, uint64_t capacity_blocks);
+RPT_API int rpt_abf_device_blocks(const rpt_abf_t *f, uint64_t **dev_ptr_out);
+RPT_API int rpt_abf_sync(const rpt_abf_t *f);
+RPT_API int rpt_abf_launch_count(const rpt_abf_t *f, long long *out);
+
 #ifdef __cplusplus
 }
 #endif

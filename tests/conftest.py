@@ -20,6 +20,13 @@ def oracle():
 
 
 @pytest.fixture(scope="session")
+def acero():
+    """oracle/librpt_oracle_acero.so — checker of the README-described filter variant (parity unpinned)."""
+    import oracle_lib
+    return oracle_lib.acero()
+
+
+@pytest.fixture(scope="session")
 def ref():
     """oracle/_ref/librpt_ref.so — the reference's own sources, when the prebuilt file is present."""
     import oracle_lib

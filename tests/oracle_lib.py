@@ -2,6 +2,7 @@
 
 oracle()  → oracle/librpt_oracle.so   plain-C restatement (built on demand with gcc)
 ref()     → oracle/_ref/librpt_ref.so the reference's own sources (prebuilt where /root/reference exists)
+acero()   → oracle/librpt_oracle_acero.so  restatement of the README-described Arrow-style filter (parity unpinned)
 """
 import ctypes as C
 import os
@@ -252,3 +253,67 @@ def ref():
             return None
         _ref = Ref(path)
     return _ref
+
+
+ACERO_LIB = os.path.join(ORACLE_DIR, "librpt_oracle_acero.so")
+_acero = None
+
+
+class AceroOracle:
+    """oracle/acero_oracle.cpp — checker of the rpt_abf_* variant; works on 64-bit hashes (from Oracle.hash_columns)."""
+
+    def __init__(self, path):
+        L = self.L = C.CDLL(path)
+        sig = {
+            "acero_mask_bits": (None, [_vp]), "acero_mask": (_u64, [_u64]), "acero_log_blocks": (_int, [_u64]),
+            "acero_insert": (None, [_vp, _int, _vp, _u64]), "acero_find": (_u64, [_vp, _int, _vp, _u64, _vp]),
+            "acero_fold": (_int, [_vp, C.POINTER(_int)]),
+        }
+        for name, (res, args) in sig.items():
+            fn = getattr(L, name)
+            fn.restype, fn.argtypes = res, args
+
+    def mask_bits(self):
+        out = np.zeros(136, dtype=np.uint8)
+        self.L.acero_mask_bits(out.ctypes.data)
+        return out
+
+    def mask(self, h):
+        return self.L.acero_mask(h)
+
+    def log_blocks(self, rows):
+        return self.L.acero_log_blocks(rows)
+
+    def new_filter(self, rows):
+        return np.zeros(1 << self.log_blocks(rows), dtype=np.uint64)
+
+    @staticmethod
+    def _log(blocks):
+        return int(blocks.shape[0]).bit_length() - 1
+
+    def insert(self, blocks, hashes):
+        hashes = np.ascontiguousarray(hashes, dtype=np.uint64)
+        self.L.acero_insert(blocks.ctypes.data, self._log(blocks), hashes.ctypes.data, hashes.shape[0])
+
+    def find(self, blocks, hashes):
+        hashes = np.ascontiguousarray(hashes, dtype=np.uint64)
+        sel = np.empty(hashes.shape[0] + 1, dtype=np.uint32)
+        f = self.L.acero_find(blocks.ctypes.data, self._log(blocks), hashes.ctypes.data, hashes.shape[0],
+                              sel.ctypes.data)
+        return sel[:f].copy()
+
+    def fold(self, blocks):
+        """Returns (folded blocks, number of halvings); the input array is modified like the in-place original."""
+        log = _int(self._log(blocks))
+        k = self.L.acero_fold(blocks.ctypes.data, C.byref(log))
+        return blocks[: 1 << log.value].copy(), k
+
+
+def acero():
+    global _acero
+    if _acero is None:
+        src = os.path.join(ORACLE_DIR, "acero_oracle.cpp")
+        if (not os.path.exists(ACERO_LIB)) or os.path.getmtime(src) > os.path.getmtime(ACERO_LIB):
+            subprocess.run(["make", "-C", ORACLE_DIR, "librpt_oracle_acero.so"], check=True, capture_output=True)
+        _acero = AceroOracle(ACERO_LIB)
+    return _acero
