@@ -9,8 +9,10 @@
 // SingleFold), fed with the same DuckDB key hashes as the reference path.  Parity is "unpinned": it is checked
 // against oracle/acero_oracle.cpp, an independent CPU restatement of the same published algorithm.
 //
-// Kernels (sm_100a): build (128-bit key loads, red.or.b64 into 64-bit blocks), popcount, fold, and a row-ordered
-// bitmap probe whose output goes through the same scan + compaction kernels as the reference path.
+// Kernels (sm_100a): build (128-bit key loads, red.or.b64 into 64-bit blocks; block-range passes for filters beyond
+// L2), popcount, fold, and a row-ordered bitmap probe (filter staged in shared memory when it fits, L2-resident
+// block-range passes when it exceeds L2) whose output goes through the same scan + compaction kernels as the
+// reference path.
 #include <cuda_runtime.h>
 
 #include <cstdint>
@@ -114,9 +116,16 @@ constexpr int kBlock = 256;
 template <bool FLAT64>
 __global__ void __launch_bounds__(kBlock)
     abf_build_kernel(const DevCols cols, const uint64_t count, uint64_t *__restrict__ blocks, const uint64_t block_mask,
-                     const uint64_t *__restrict__ masks) {
+                     const uint64_t slice_lo, const uint64_t slice_len, const uint64_t *__restrict__ masks) {
 	__shared__ uint64_t s_masks[kNumMasks];
 	stage_masks(s_masks, masks);
+	// a pass only inserts the keys whose block lies in [slice_lo, slice_lo + slice_len): the slice stays L2-resident
+	auto insert = [&](uint64_t h) {
+		const uint64_t b = key_block(h, block_mask);
+		if (b - slice_lo < slice_len) {
+			red_or(blocks + b, key_mask(s_masks, h));
+		}
+	};
 	const uint64_t tid = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
 	const uint64_t nthreads = static_cast<uint64_t>(gridDim.x) * blockDim.x;
 	if (FLAT64) {
@@ -127,25 +136,25 @@ __global__ void __launch_bounds__(kBlock)
 			const ulonglong2 a = __ldg(keys2 + i);
 			const ulonglong2 b = __ldg(keys2 + i + nthreads);
 			const uint64_t h0 = murmur64(a.x), h1 = murmur64(a.y), h2 = murmur64(b.x), h3 = murmur64(b.y);
-			red_or(blocks + key_block(h0, block_mask), key_mask(s_masks, h0));
-			red_or(blocks + key_block(h1, block_mask), key_mask(s_masks, h1));
-			red_or(blocks + key_block(h2, block_mask), key_mask(s_masks, h2));
-			red_or(blocks + key_block(h3, block_mask), key_mask(s_masks, h3));
+			insert(h0);
+			insert(h1);
+			insert(h2);
+			insert(h3);
 		}
 		for (; i < pairs; i += nthreads) {
 			const ulonglong2 a = __ldg(keys2 + i);
 			const uint64_t h0 = murmur64(a.x), h1 = murmur64(a.y);
-			red_or(blocks + key_block(h0, block_mask), key_mask(s_masks, h0));
-			red_or(blocks + key_block(h1, block_mask), key_mask(s_masks, h1));
+			insert(h0);
+			insert(h1);
 		}
 		if ((count & 1) && tid == 0) {
 			const uint64_t h = murmur64(__ldg(reinterpret_cast<const unsigned long long *>(cols.c[0].data) + count - 1));
-			red_or(blocks + key_block(h, block_mask), key_mask(s_masks, h));
+			insert(h);
 		}
 	} else {
 		for (uint64_t row = tid; row < count; row += nthreads) {
 			const uint64_t h = hash_row(cols, row);
-			red_or(blocks + key_block(h, block_mask), key_mask(s_masks, h));
+			insert(h);
 		}
 	}
 }
@@ -194,13 +203,27 @@ __global__ void __launch_bounds__(kBlock)
 // Probe: Find for every row, answers as a row-ordered bitmap (bit r of the bitmap = row r).  A warp takes kUnroll
 // consecutive 32-row words per iteration: all key loads first, then all block loads, then the ballots.
 // words_padded covers whole 512-row segments so that the compaction kernels never see an uninitialised word.
+//   SMEM   the whole filter (≤ kSmemFilterMaxSectors blocks — what Fold typically leaves of a selective build) is
+//          staged in shared memory next to the mask table;
+//   sliced passes (slice_len < num_blocks): a pass answers the rows whose block lies in its slice, which stays
+//          L2-resident, and ORs into the words of the earlier passes (a word belongs to one warp in every pass).
 constexpr int kUnroll = 4;
-template <bool FLAT64>
-__global__ void __launch_bounds__(kBlock)
+constexpr int kBlockSmem = 512;
+template <bool FLAT64, bool SMEM>
+__global__ void __launch_bounds__(SMEM ? kBlockSmem : kBlock)
     abf_probe_bitmap_kernel(const DevCols cols, const uint64_t count, const uint64_t words_padded,
-                            const uint64_t *__restrict__ blocks, const uint64_t block_mask,
-                            const uint64_t *__restrict__ masks, uint32_t *__restrict__ bitmap32) {
+                            const uint64_t *__restrict__ blocks, const uint64_t block_mask, const uint64_t slice_lo,
+                            const uint64_t slice_len, const int first_pass, const uint64_t *__restrict__ masks,
+                            uint32_t *__restrict__ bitmap32) {
 	__shared__ uint64_t s_masks[kNumMasks];
+	extern __shared__ __align__(16) uint64_t s_blocks[];
+	if (SMEM) {
+		const ulonglong2 *src = reinterpret_cast<const ulonglong2 *>(blocks);
+		ulonglong2 *dst = reinterpret_cast<ulonglong2 *>(s_blocks);
+		for (uint64_t i = threadIdx.x; i < (block_mask + 1) / 2; i += blockDim.x) {
+			dst[i] = __ldg(src + i);
+		}
+	}
 	stage_masks(s_masks, masks);
 	const uint32_t lane = threadIdx.x & 31u;
 	const uint64_t warp = (static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
@@ -219,22 +242,35 @@ __global__ void __launch_bounds__(kBlock)
 				              : hash_row(cols, row);
 			}
 		}
+		uint32_t prev = 0; // lane u < kUnroll holds the word of the earlier passes
+		if (!first_pass && lane < kUnroll && g * kUnroll + lane < words_padded) {
+			prev = bitmap32[g * kUnroll + lane];
+		}
 		uint64_t b[kUnroll];
 #pragma unroll
 		for (int u = 0; u < kUnroll; u++) {
-			b[u] = live[u] ? __ldg(blocks + key_block(h[u], block_mask)) : 0ull;
+			const uint64_t blk = key_block(h[u], block_mask);
+			live[u] = live[u] && (blk - slice_lo < slice_len);
+			b[u] = live[u] ? (SMEM ? s_blocks[blk] : __ldg(blocks + blk)) : 0ull;
 		}
+		uint32_t mine = prev;
 #pragma unroll
 		for (int u = 0; u < kUnroll; u++) {
 			const uint64_t m = key_mask(s_masks, h[u]);
 			const uint32_t word = __ballot_sync(0xffffffffu, live[u] && (b[u] & m) == m);
-			const uint64_t w = g * kUnroll + u;
-			if (lane == 0 && w < words_padded) {
-				bitmap32[w] = word;
+			if (lane == u) {
+				mine |= word;
 			}
+		}
+		if (lane < kUnroll && g * kUnroll + lane < words_padded) {
+			bitmap32[g * kUnroll + lane] = mine;
 		}
 	}
 }
+
+// Filters beyond this many blocks are built / probed in block-range passes of this size (64 MiB, the L2-resident
+// slice size measured for the reference path: profiles/mem_lab_r1.txt)
+constexpr uint64_t kSliceBlocks = kSliceSectors;
 
 static inline unsigned grid_for(const DeviceInfo &dev, uint64_t items, int per_sm) {
 	const uint64_t want = (items + kBlock - 1) / kBlock;
@@ -249,16 +285,25 @@ static inline bool flat64(const DevCols &cols) {
 }
 
 cudaError_t launch_build(const DeviceInfo &dev, const DevCols &cols, uint64_t count, uint64_t *blocks,
-                         uint64_t num_blocks, const uint64_t *masks, cudaStream_t stream) {
+                         uint64_t num_blocks, const uint64_t *masks, cudaStream_t stream, int *launches) {
 	if (count == 0) {
 		return cudaSuccess;
 	}
-	if (flat64(cols)) {
-		abf_build_kernel<true><<<grid_for(dev, count / 4 + 1, 8), kBlock, 0, stream>>>(cols, count, blocks,
-		                                                                              num_blocks - 1, masks);
-	} else {
-		abf_build_kernel<false><<<grid_for(dev, count, 8), kBlock, 0, stream>>>(cols, count, blocks, num_blocks - 1,
-		                                                                        masks);
+	// small builds into large filters gain nothing from passes: every touched line is a compulsory miss anyway
+	const bool sliced = num_blocks > kSliceBlocks && count >= num_blocks / 8;
+	const uint64_t slice = sliced ? kSliceBlocks : num_blocks;
+	const bool flat = flat64(cols);
+	for (uint64_t lo = 0; lo < num_blocks; lo += slice) {
+		if (flat) {
+			abf_build_kernel<true><<<grid_for(dev, count / 4 + 1, 8), kBlock, 0, stream>>>(cols, count, blocks,
+			                                                                              num_blocks - 1, lo, slice, masks);
+		} else {
+			abf_build_kernel<false><<<grid_for(dev, count, 8), kBlock, 0, stream>>>(cols, count, blocks,
+			                                                                        num_blocks - 1, lo, slice, masks);
+		}
+		if (launches) {
+			(*launches)++;
+		}
 	}
 	return cudaGetLastError();
 }
@@ -282,6 +327,49 @@ cudaError_t launch_fold(const DeviceInfo &dev, uint64_t *blocks, uint64_t num_bl
 	return cudaGetLastError();
 }
 
+template <bool FLAT64>
+static cudaError_t launch_probe_t(const DeviceInfo &dev, const DevCols &cols, uint64_t count, const uint64_t *blocks,
+                                  uint64_t num_blocks, const uint64_t *masks, uint32_t *bitmap32, cudaStream_t stream,
+                                  int *launches) {
+	const uint64_t words_padded = (count + 511) / 512 * 16;
+	const uint64_t warps_wanted = (words_padded + kUnroll - 1) / kUnroll;
+	if (num_blocks <= kSmemFilterMaxSectors && count >= (1u << 20)) {
+		auto kern = abf_probe_bitmap_kernel<FLAT64, true>;
+		const size_t smem = num_blocks * sizeof(uint64_t);
+		cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
+		if (e != cudaSuccess) {
+			return e;
+		}
+		int per_sm = 0;
+		e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kBlockSmem, smem);
+		if (e != cudaSuccess) {
+			return e;
+		}
+		if (per_sm < 1) {
+			return cudaErrorLaunchOutOfResources;
+		}
+		uint64_t grid = static_cast<uint64_t>(dev.sm_count) * per_sm; // persistent CTAs, a multiple of the SM count
+		const uint64_t want = (warps_wanted + kBlockSmem / 32 - 1) / (kBlockSmem / 32);
+		grid = grid < want ? grid : want;
+		kern<<<static_cast<unsigned>(grid), kBlockSmem, smem, stream>>>(cols, count, words_padded, blocks,
+		                                                              num_blocks - 1, 0, num_blocks, 1, masks, bitmap32);
+		if (launches) {
+			(*launches)++;
+		}
+		return cudaGetLastError();
+	}
+	const uint64_t slice = num_blocks > kSliceBlocks ? kSliceBlocks : num_blocks;
+	const unsigned grid = grid_for(dev, warps_wanted * 32, 8);
+	for (uint64_t lo = 0; lo < num_blocks; lo += slice) {
+		abf_probe_bitmap_kernel<FLAT64, false><<<grid, kBlock, 0, stream>>>(
+		    cols, count, words_padded, blocks, num_blocks - 1, lo, slice, lo == 0 ? 1 : 0, masks, bitmap32);
+		if (launches) {
+			(*launches)++;
+		}
+	}
+	return cudaGetLastError();
+}
+
 cudaError_t launch_probe(const DeviceInfo &dev, const DevCols &cols, uint64_t count, const uint64_t *blocks,
                          uint64_t num_blocks, const uint64_t *masks, uint32_t *sel_out, uint64_t *found_out,
                          uint32_t row_offset, void *scratch, cudaStream_t stream, int *launches) {
@@ -289,21 +377,11 @@ cudaError_t launch_probe(const DeviceInfo &dev, const DevCols &cols, uint64_t co
 		return cudaMemsetAsync(found_out, 0, sizeof(uint64_t), stream);
 	}
 	uint32_t *bitmap32 = bitmap_words(scratch, count);
-	const uint64_t words_padded = (count + 511) / 512 * 16;
-	const unsigned grid = grid_for(dev, (words_padded + kUnroll - 1) / kUnroll * 32, 8);
-	if (flat64(cols)) {
-		abf_probe_bitmap_kernel<true><<<grid, kBlock, 0, stream>>>(cols, count, words_padded, blocks, num_blocks - 1,
-		                                                           masks, bitmap32);
-	} else {
-		abf_probe_bitmap_kernel<false><<<grid, kBlock, 0, stream>>>(cols, count, words_padded, blocks, num_blocks - 1,
-		                                                            masks, bitmap32);
-	}
-	cudaError_t e = cudaGetLastError();
+	const cudaError_t e = flat64(cols)
+	                          ? launch_probe_t<true>(dev, cols, count, blocks, num_blocks, masks, bitmap32, stream, launches)
+	                          : launch_probe_t<false>(dev, cols, count, blocks, num_blocks, masks, bitmap32, stream, launches);
 	if (e != cudaSuccess) {
 		return e;
-	}
-	if (launches) {
-		(*launches)++;
 	}
 	return launch_bitmap_to_sel(dev, count, sel_out, found_out, row_offset, scratch, stream, launches);
 }

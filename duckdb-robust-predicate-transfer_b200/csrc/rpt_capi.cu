@@ -1627,8 +1627,9 @@ int rpt_abf_insert(rpt_abf_t *f, const rpt_col_t *cols, int ncols, uint64_t coun
 	if (mem == RPT_MEM_DEVICE) {
 		DevCols dc;
 		device_cols_view(cols, ncols, &dc);
-		RPT_CUDA(acero::launch_build(f->dev, dc, count, f->blocks, f->num_blocks, f->masks, s));
-		f->launches += 1;
+		int launches = 0;
+		RPT_CUDA(acero::launch_build(f->dev, dc, count, f->blocks, f->num_blocks, f->masks, s, &launches));
+		f->launches += launches;
 		return 0;
 	}
 	const uint64_t chunk = any_sel(cols, ncols) ? count : chunk_rows();
@@ -1638,8 +1639,9 @@ int rpt_abf_insert(rpt_abf_t *f, const rpt_col_t *cols, int ncols, uint64_t coun
 		st.stream = s;
 		DevCols dc;
 		RPT_TRY(stage_host_cols(cols, ncols, r0, r1, &st, &dc));
-		RPT_CUDA(acero::launch_build(f->dev, dc, r1 - r0, f->blocks, f->num_blocks, f->masks, s));
-		f->launches += 1;
+		int launches = 0;
+		RPT_CUDA(acero::launch_build(f->dev, dc, r1 - r0, f->blocks, f->num_blocks, f->masks, s, &launches));
+		f->launches += launches;
 	}
 	RPT_CUDA(cudaStreamSynchronize(s));
 	return 0;

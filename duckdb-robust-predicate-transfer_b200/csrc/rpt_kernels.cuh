@@ -100,7 +100,7 @@ constexpr int kLogNumBlocksMin = 4; // Fold never goes below 2^4 blocks... it st
 void generate_mask_bits(uint8_t *out /* kMaskBytes */);
 void expand_masks(const uint8_t *bits, uint64_t *out /* kNumMasks */);
 cudaError_t launch_build(const DeviceInfo &dev, const DevCols &cols, uint64_t count, uint64_t *blocks,
-                         uint64_t num_blocks, const uint64_t *masks, cudaStream_t stream);
+                         uint64_t num_blocks, const uint64_t *masks, cudaStream_t stream, int *launches);
 cudaError_t launch_popcount(const DeviceInfo &dev, const uint64_t *blocks, uint64_t num_blocks, uint64_t *total,
                             cudaStream_t stream);
 cudaError_t launch_fold(const DeviceInfo &dev, uint64_t *blocks, uint64_t num_blocks, int num_folds,

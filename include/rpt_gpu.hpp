@@ -503,4 +503,61 @@ private:
 	std::vector<uint32_t> sel_;
 };
 
+// ---------------------------------------------------------------------------------------------------------
+// README-described filter variant (reference README.md:23-32: Arrow Acero BlockedBloomFilter — 1024-entry mask
+// table, 8 bits per key, Fold) over rpt_abf_*.  NOT the reference's code path: src/bloom_filter.cpp wraps DuckDB's
+// native BloomFilter (PTBloomFilter above).  Method names follow arrow::acero::BlockedBloomFilter.  Parity
+// unpinned (rpt_gpu.h).
+// ---------------------------------------------------------------------------------------------------------
+class BlockedBloomFilter {
+public:
+	explicit BlockedBloomFilter(int device = 0) : device_(device) {
+	}
+	~BlockedBloomFilter() {
+		rpt_abf_destroy(handle_);
+	}
+	BlockedBloomFilter(const BlockedBloomFilter &) = delete;
+	BlockedBloomFilter &operator=(const BlockedBloomFilter &) = delete;
+
+	// CreateEmpty(num_rows_to_insert): 8 bits per key, at least 512 bits, power of two
+	void CreateEmpty(uint64_t num_rows_to_insert) {
+		rpt_abf_destroy(handle_);
+		handle_ = nullptr;
+		Check(rpt_abf_create(&handle_, num_rows_to_insert, device_));
+	}
+	// Insert for every row of the key column(s) (DuckDB hashes, NULL rows hash to NULL_HASH)
+	void Insert(const rpt_col_t *cols, int ncols, uint64_t count, rpt_stream_t stream = nullptr) {
+		Check(rpt_abf_insert(handle_, cols, ncols, count, stream));
+	}
+	// Fold(): OR the halves together while fewer than a quarter of the bits are set; returns the halvings done
+	int Fold(rpt_stream_t stream = nullptr) {
+		int folds = 0;
+		Check(rpt_abf_fold(handle_, stream, &folds));
+		return folds;
+	}
+	// Find for every row: ascending row ids of the rows that pass
+	uint64_t Find(const rpt_col_t *cols, int ncols, uint64_t count, uint32_t *sel_out) const {
+		uint64_t found = 0;
+		Check(rpt_abf_probe(handle_, cols, ncols, count, sel_out, &found, RPT_MEM_HOST, nullptr));
+		return found;
+	}
+	int log_num_blocks() const {
+		int v = 0;
+		Check(rpt_abf_log_num_blocks(handle_, &v));
+		return v;
+	}
+	std::vector<uint64_t> Blocks() const {
+		std::vector<uint64_t> out(1ULL << log_num_blocks());
+		Check(rpt_abf_export_blocks(handle_, out.data(), out.size()));
+		return out;
+	}
+	rpt_abf_t *handle() {
+		return handle_;
+	}
+
+private:
+	int device_;
+	rpt_abf_t *handle_ = nullptr;
+};
+
 } // namespace rpt

@@ -43,7 +43,9 @@ def check(rpt, oracle, acero, rows_for_sizing, build_cols, n, probe_cols, m, fol
 
 
 @pytest.mark.parametrize("n,m,oversize", [(50_000, 100_000, 1), (50_001, 99_999, 16), (1, 7, 1), (999, 1025, 64),
-                                           (300_000, 1_000_003, 4)])
+                                           (300_000, 1_000_003, 4),
+                                           (50_000, 1_500_001, 1),      # 64 KiB filter staged in shared memory
+                                           (100_000, 1_200_000, 1)])    # 128 KiB: the largest staged filter
 def test_int64_host_columns(rpt, oracle, acero, n, m, oversize):
     keys = synth_build_keys(0, n)
     probe = synth_probe_keys(0, m, n, 100_000)
@@ -91,6 +93,28 @@ def test_nullable_selected_and_composite(rpt, oracle, acero):
     sel = rng.integers(0, n, m, dtype=np.uint32)
     probe = [rpt.host_col(a, sel=sel, validity=validity, data_len=n), rpt.host_varchar_col(off, data, sel=sel)]
     check(rpt, oracle, acero, n * 32, build, n, probe, m)
+
+
+def test_block_range_passes(rpt, oracle, acero):
+    """256 MiB filter (2^25 blocks): build and probe run in four L2-resident block-range passes."""
+    n, m = 20_000_000, 4_000_000
+    keys = synth_build_keys(0, n)
+    probe = synth_probe_keys(0, m, n, 300_000)
+    f = rpt.BlockedBloomFilter(0).CreateEmpty(n * 8)
+    assert f.log_num_blocks == 25
+    f.Insert(rpt.host_col(keys), n)
+    assert f.launch_count >= 4 * 2                       # 2 host chunks x 4 passes
+    blocks = acero.new_filter(n * 8)
+    acero.insert(blocks, oracle.hash_columns([rpt.host_col(keys)], n))
+    assert np.array_equal(f.ExportBlocks(), blocks)
+    hp = oracle.hash_columns([rpt.host_col(probe)], m)
+    assert np.array_equal(f.Find(rpt.host_col(probe), m), acero.find(blocks, hp))
+    k = f.Fold()
+    folded, want_k = acero.fold(blocks)
+    assert k == want_k and k >= 2
+    assert np.array_equal(f.ExportBlocks(), folded)
+    assert np.array_equal(f.Find(rpt.host_col(probe), m), acero.find(folded, hp))
+    f.close()
 
 
 def test_device_columns_and_property_at_scale(rpt, oracle, acero, torch_cuda):
