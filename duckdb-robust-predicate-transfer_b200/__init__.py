@@ -98,6 +98,7 @@ _SIGNATURES = {
     "rpt_abf_probe": (C.c_int, [C.c_void_p, C.POINTER(RptCol), C.c_int, C.c_uint64, C.c_void_p, C.c_void_p, C.c_int,
                                 C.c_void_p]),
     "rpt_abf_export_blocks": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64]),
+    "rpt_abf_or_parts": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p]),
     "rpt_abf_device_blocks": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p)]),
     "rpt_abf_sync": (C.c_int, [C.c_void_p]),
     "rpt_abf_launch_count": (C.c_int, [C.c_void_p, C.POINTER(C.c_longlong)]),
@@ -449,6 +450,9 @@ class BlockedBloomFilter:
         arr, n = _col_array(cols)
         _check(lib().rpt_abf_probe(self._h, arr, n, count, _ptr(sel_out_ptr), _ptr(found_out_ptr), MEM_DEVICE,
                                    stream))
+
+    def OrParts(self, dev_parts_ptr, nparts, stream=None):
+        _check(lib().rpt_abf_or_parts(self._h, _ptr(dev_parts_ptr), nparts, stream))
 
     def ExportBlocks(self):
         out = np.empty(1 << self.log_num_blocks, dtype=np.uint64)

@@ -1756,6 +1756,22 @@ int rpt_abf_probe(const rpt_abf_t *f, const rpt_col_t *cols, int ncols, uint64_t
 	return 0;
 }
 
+// Multi-GPU merge (SURVEY §8e applied to the variant): blocks |= parts[0 .. nparts), each part a same-sized partial
+// filter on this device (e.g. the receive buffer of an all-gather).  Insert is a plain OR, so the merged blocks
+// equal a single build; Fold runs after the merge, on every rank alike.
+int rpt_abf_or_parts(rpt_abf_t *f, const uint64_t *dev_parts, uint64_t nparts, rpt_stream_t stream) {
+	if (!f || (nparts && !dev_parts)) {
+		return set_error("null argument");
+	}
+	RPT_GUARD(f);
+	if (nparts == 0) {
+		return 0;
+	}
+	RPT_CUDA(launch_or_parts(f->dev, f->blocks, dev_parts, f->num_blocks, nparts, abf_stream(f, stream)));
+	f->launches += 1;
+	return 0;
+}
+
 int rpt_abf_export_blocks(const rpt_abf_t *f, uint64_t *host_dst, uint64_t capacity_blocks) {
 	if (!f || !host_dst) {
 		return set_error("null argument");

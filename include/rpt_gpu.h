@@ -256,6 +256,8 @@ RPT_API int rpt_abf_probe(const rpt_abf_t *f, const rpt_col_t *cols, int ncols, 
                           uint64_t *found_out, int out_mem, rpt_stream_t stream);
 /* Copies the 2^log_num_blocks blocks to the host (after work on a caller's stream, synchronise it first). */
 RPT_API int rpt_abf_export_blocks(const rpt_abf_t *f, uint64_t *host_dst, uint64_t capacity_blocks);
+/* blocks |= parts[0..nparts): same-sized partial filters on this device (multi-GPU merge; fold afterwards) */
+RPT_API int rpt_abf_or_parts(rpt_abf_t *f, const uint64_t *dev_parts, uint64_t nparts, rpt_stream_t stream);
 RPT_API int rpt_abf_device_blocks(const rpt_abf_t *f, uint64_t **dev_ptr_out);
 RPT_API int rpt_abf_sync(const rpt_abf_t *f);
 RPT_API int rpt_abf_launch_count(const rpt_abf_t *f, long long *out);

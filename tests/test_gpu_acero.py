@@ -117,6 +117,28 @@ def test_block_range_passes(rpt, oracle, acero):
     f.close()
 
 
+def test_row_range_shards_merge_to_the_single_build(rpt, torch_cuda):
+    """Two partial filters built from the two halves of the build column, OR-merged, equal the single build."""
+    torch = torch_cuda
+    n = 3_000_001
+    keys = synth_build_keys(0, n)
+    whole = rpt.BlockedBloomFilter(0).CreateEmpty(n * 4)
+    whole.Insert(rpt.host_col(keys), n)
+    half = n // 2
+    a = rpt.BlockedBloomFilter(0).CreateEmpty(n * 4)
+    b = rpt.BlockedBloomFilter(0).CreateEmpty(n * 4)
+    a.Insert(rpt.host_col(keys[:half]), half)
+    b.Insert(rpt.host_col(keys[half:]), n - half)
+    part = torch.from_numpy(b.ExportBlocks().view(np.int64)).to("cuda:0")
+    a.OrParts(part, 1)
+    a.Sync()
+    assert np.array_equal(a.ExportBlocks(), whole.ExportBlocks())
+    assert a.Fold() == whole.Fold()
+    assert np.array_equal(a.ExportBlocks(), whole.ExportBlocks())
+    for f in (whole, a, b):
+        f.close()
+
+
 def test_device_columns_and_property_at_scale(rpt, oracle, acero, torch_cuda):
     """10^7 build / 5·10^7 probe rows on the device; checker on a prefix, Fold == direct small build at full size."""
     torch = torch_cuda
