@@ -203,8 +203,8 @@ __global__ void __launch_bounds__(kBlock)
 // Probe: Find for every row, answers as a row-ordered bitmap (bit r of the bitmap = row r).  A warp takes kUnroll
 // consecutive 32-row words per iteration: all key loads first, then all block loads, then the ballots.
 // words_padded covers whole 512-row segments so that the compaction kernels never see an uninitialised word.
-//   SMEM   the whole filter (≤ kSmemFilterMaxSectors blocks — what Fold typically leaves of a selective build) is
-//          staged in shared memory next to the mask table;
+//   SMEM   the whole filter (≤ kSmemBlocksMax blocks — what Fold leaves of a small selective build) is staged in
+//          shared memory next to the mask table;
 //   sliced passes (slice_len < num_blocks): a pass answers the rows whose block lies in its slice, which stays
 //          L2-resident, and ORs into the words of the earlier passes (a word belongs to one warp in every pass).
 constexpr int kUnroll = 4;
@@ -271,6 +271,14 @@ __global__ void __launch_bounds__(SMEM ? kBlockSmem : kBlock)
 // Filters beyond this many blocks are built / probed in block-range passes of this size (64 MiB, the L2-resident
 // slice size measured for the reference path: profiles/mem_lab_r1.txt)
 constexpr uint64_t kSliceBlocks = kSliceSectors;
+// ... up to this many passes: every pass re-reads the keys, and measured on B200 (profiles/sweep_r1z_acero.txt) 32
+// passes over a 2 GiB filter cost 103 ms per 10^9 probe rows against 26.9 ms for one pass of HBM gathers, while 2
+// passes over 128 MiB cost 8.1 ms against 10.7 ms.  Filters that over-sized are what Fold exists for.
+constexpr uint64_t kMaxPasses = 4;
+// Largest filter the probe stages in shared memory: 32 KiB next to the 8 KiB mask table keeps four 512-thread CTAs
+// (all 64 warps) on an SM.  This kernel hides latency with resident warps, not with staged key buffers: at 128 KiB
+// (one CTA, 16 warps per SM) staging measured 185 Gkeys/s against 301 Gkeys/s for plain L1/L2 hits.
+constexpr uint64_t kSmemBlocksMax = 1ULL << 12;
 
 static inline unsigned grid_for(const DeviceInfo &dev, uint64_t items, int per_sm) {
 	const uint64_t want = (items + kBlock - 1) / kBlock;
@@ -290,7 +298,7 @@ cudaError_t launch_build(const DeviceInfo &dev, const DevCols &cols, uint64_t co
 		return cudaSuccess;
 	}
 	// small builds into large filters gain nothing from passes: every touched line is a compulsory miss anyway
-	const bool sliced = num_blocks > kSliceBlocks && count >= num_blocks / 8;
+	const bool sliced = num_blocks > kSliceBlocks && num_blocks <= kMaxPasses * kSliceBlocks && count >= num_blocks / 8;
 	const uint64_t slice = sliced ? kSliceBlocks : num_blocks;
 	const bool flat = flat64(cols);
 	for (uint64_t lo = 0; lo < num_blocks; lo += slice) {
@@ -333,7 +341,7 @@ static cudaError_t launch_probe_t(const DeviceInfo &dev, const DevCols &cols, ui
                                   int *launches) {
 	const uint64_t words_padded = (count + 511) / 512 * 16;
 	const uint64_t warps_wanted = (words_padded + kUnroll - 1) / kUnroll;
-	if (num_blocks <= kSmemFilterMaxSectors && count >= (1u << 20)) {
+	if (num_blocks <= kSmemBlocksMax && count >= (1u << 20)) {
 		auto kern = abf_probe_bitmap_kernel<FLAT64, true>;
 		const size_t smem = num_blocks * sizeof(uint64_t);
 		cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
@@ -358,7 +366,8 @@ static cudaError_t launch_probe_t(const DeviceInfo &dev, const DevCols &cols, ui
 		}
 		return cudaGetLastError();
 	}
-	const uint64_t slice = num_blocks > kSliceBlocks ? kSliceBlocks : num_blocks;
+	const bool sliced = num_blocks > kSliceBlocks && num_blocks <= kMaxPasses * kSliceBlocks;
+	const uint64_t slice = sliced ? kSliceBlocks : num_blocks;
 	const unsigned grid = grid_for(dev, warps_wanted * 32, 8);
 	for (uint64_t lo = 0; lo < num_blocks; lo += slice) {
 		abf_probe_bitmap_kernel<FLAT64, false><<<grid, kBlock, 0, stream>>>(
