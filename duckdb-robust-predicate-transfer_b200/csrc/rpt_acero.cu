@@ -106,8 +106,38 @@ __device__ __forceinline__ uint64_t key_block(uint64_t h, uint64_t block_mask) {
 	return (h >> (kLogNumMasks + 6)) & block_mask;
 }
 
-__device__ __forceinline__ void red_or(uint64_t *addr, uint64_t v) {
-	asm volatile("red.global.or.b64 [%0], %1;" ::"l"(addr), "l"(v) : "memory");
+// Cache policies as on the reference path (rpt_kernels.cu): keys are read once → L1 no_allocate + L2 evict_first;
+// blocks are re-read at random → L2 evict_last, so that a slice survives the key stream passing through L2
+// (ncu r1z2 without hints: 17.3 GB of DRAM reads per 10^9-row pass for 8 GB of keys, L2 hit rate 38 %).
+__device__ __forceinline__ uint64_t policy_evict_first() {
+	uint64_t p;
+	asm("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
+	return p;
+}
+__device__ __forceinline__ uint64_t policy_evict_last() {
+	uint64_t p;
+	asm("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p));
+	return p;
+}
+__device__ __forceinline__ ulonglong2 ld_keys2(const void *ptr, uint64_t pol) {
+	ulonglong2 v;
+	asm("ld.global.nc.L1::no_allocate.L2::cache_hint.v2.u64 {%0, %1}, [%2], %3;"
+	    : "=l"(v.x), "=l"(v.y)
+	    : "l"(ptr), "l"(pol));
+	return v;
+}
+__device__ __forceinline__ uint64_t ld_key(const void *ptr, uint64_t pol) {
+	uint64_t v;
+	asm("ld.global.nc.L1::no_allocate.L2::cache_hint.u64 %0, [%1], %2;" : "=l"(v) : "l"(ptr), "l"(pol));
+	return v;
+}
+__device__ __forceinline__ uint64_t ld_block(const uint64_t *ptr, uint64_t pol) {
+	uint64_t v;
+	asm("ld.global.nc.L1::no_allocate.L2::cache_hint.u64 %0, [%1], %2;" : "=l"(v) : "l"(ptr), "l"(pol));
+	return v;
+}
+__device__ __forceinline__ void red_or(uint64_t *addr, uint64_t v, uint64_t pol) {
+	asm volatile("red.global.or.L2::cache_hint.b64 [%0], %1, %2;" ::"l"(addr), "l"(v), "l"(pol) : "memory");
 }
 
 constexpr int kBlock = 256;
@@ -120,10 +150,12 @@ __global__ void __launch_bounds__(kBlock)
 	__shared__ uint64_t s_masks[kNumMasks];
 	stage_masks(s_masks, masks);
 	// a pass only inserts the keys whose block lies in [slice_lo, slice_lo + slice_len): the slice stays L2-resident
+	const uint64_t pol_keys = policy_evict_first();
+	const uint64_t pol_blocks = policy_evict_last();
 	auto insert = [&](uint64_t h) {
 		const uint64_t b = key_block(h, block_mask);
 		if (b - slice_lo < slice_len) {
-			red_or(blocks + b, key_mask(s_masks, h));
+			red_or(blocks + b, key_mask(s_masks, h), pol_blocks);
 		}
 	};
 	const uint64_t tid = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
@@ -133,8 +165,8 @@ __global__ void __launch_bounds__(kBlock)
 		const uint64_t pairs = count >> 1;
 		uint64_t i = tid;
 		for (; i + nthreads < pairs; i += 2 * nthreads) {
-			const ulonglong2 a = __ldg(keys2 + i);
-			const ulonglong2 b = __ldg(keys2 + i + nthreads);
+			const ulonglong2 a = ld_keys2(keys2 + i, pol_keys);
+			const ulonglong2 b = ld_keys2(keys2 + i + nthreads, pol_keys);
 			const uint64_t h0 = murmur64(a.x), h1 = murmur64(a.y), h2 = murmur64(b.x), h3 = murmur64(b.y);
 			insert(h0);
 			insert(h1);
@@ -142,7 +174,7 @@ __global__ void __launch_bounds__(kBlock)
 			insert(h3);
 		}
 		for (; i < pairs; i += nthreads) {
-			const ulonglong2 a = __ldg(keys2 + i);
+			const ulonglong2 a = ld_keys2(keys2 + i, pol_keys);
 			const uint64_t h0 = murmur64(a.x), h1 = murmur64(a.y);
 			insert(h0);
 			insert(h1);
@@ -225,6 +257,11 @@ __global__ void __launch_bounds__(SMEM ? kBlockSmem : kBlock)
 		}
 	}
 	stage_masks(s_masks, masks);
+	const uint64_t pol_keys = policy_evict_first();
+	const uint64_t pol_blocks = policy_evict_last();
+	// a filter of at most 256 KiB lives in L1: bypassing it (no_allocate) measured 5.70 ms against 3.64 ms per 10^9
+	// rows at 128 KiB, while from 2 MiB upwards the bypass is the faster one (profiles/sweep_r1z3_acero_hints.txt)
+	const bool via_l1 = block_mask < (1ULL << 15);
 	const uint32_t lane = threadIdx.x & 31u;
 	const uint64_t warp = (static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
 	const uint64_t nwarps = (static_cast<uint64_t>(gridDim.x) * blockDim.x) >> 5;
@@ -238,7 +275,7 @@ __global__ void __launch_bounds__(SMEM ? kBlockSmem : kBlock)
 			live[u] = row < count;
 			h[u] = 0;
 			if (live[u]) {
-				h[u] = FLAT64 ? murmur64(__ldg(reinterpret_cast<const unsigned long long *>(cols.c[0].data) + row))
+				h[u] = FLAT64 ? murmur64(ld_key(reinterpret_cast<const unsigned long long *>(cols.c[0].data) + row, pol_keys))
 				              : hash_row(cols, row);
 			}
 		}
@@ -251,7 +288,7 @@ __global__ void __launch_bounds__(SMEM ? kBlockSmem : kBlock)
 		for (int u = 0; u < kUnroll; u++) {
 			const uint64_t blk = key_block(h[u], block_mask);
 			live[u] = live[u] && (blk - slice_lo < slice_len);
-			b[u] = live[u] ? (SMEM ? s_blocks[blk] : __ldg(blocks + blk)) : 0ull;
+			b[u] = live[u] ? (SMEM ? s_blocks[blk] : (via_l1 ? __ldg(blocks + blk) : ld_block(blocks + blk, pol_blocks))) : 0ull;
 		}
 		uint32_t mine = prev;
 #pragma unroll
