@@ -96,7 +96,7 @@ namespace acero {
 constexpr int kBitsPerMask = 57, kMinBitsSet = 4, kMaxBitsSet = 5, kLogNumMasks = 10, kNumMasks = 1 << kLogNumMasks;
 constexpr int kMaskBytes = (kNumMasks + 64) / 8; // bit vector the 1024 overlapping masks are windows of
 constexpr uint64_t kFullMask = (1ULL << kBitsPerMask) - 1;
-constexpr int kLogNumBlocksMin = 4; // Fold never goes below 2^4 blocks... it stops once log_num_blocks <= 4
+constexpr int kLogNumBlocksMin = 4; // Fold stops once log_num_blocks <= 4
 void generate_mask_bits(uint8_t *out /* kMaskBytes */);
 void expand_masks(const uint8_t *bits, uint64_t *out /* kNumMasks */);
 cudaError_t launch_build(const DeviceInfo &dev, const DevCols &cols, uint64_t count, uint64_t *blocks,
