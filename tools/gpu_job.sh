@@ -1,0 +1,44 @@
+#!/bin/bash
+# One parametrised GPU job script (replaces the per-run gpu_job_r1*.sh files of round 1):
+#   gpurun --timeout N -- 'bash tools/gpu_job.sh <job> [args]'
+# Every job writes into gpurun_out/ (merged back by gpurun) and guards risky steps with its own timeout.
+set -u
+mkdir -p gpurun_out
+job=${1:-help}
+shift || true
+case "$job" in
+part_lab)   # prototype: one-pass partition into shared-memory-sized buckets + shared-memory lookup
+	out=gpurun_out/part_lab_${1:-r2a}.txt
+	: > $out
+	timeout -s KILL 120 tools/part_lab atoms >> $out 2>&1
+	# sectors block kpt rows log2_chunk density fake
+	for cfg in "25 1024 8 1000000000 32 1 1" "25 512 4 1000000000 32 1 1" "25 512 4 1000000000 32 1 0" "25 256 8 1000000000 32 1 0" \
+	           "25 1024 8 1000000000 32 2 0" "25 1024 8 1000000000 27 1 0" "25 1024 8 1000000000 26 1 0" "25 1024 8 1000000000 27 0 0"; do
+		timeout -s KILL 90 tools/part_lab part $cfg >> $out 2>&1
+		echo "rc=$?" >> $out
+	done
+	cat $out
+	;;
+ncu_lab)    # full ncu capture of one prototype kernel: ncu_lab <tag> <kernel regex> <part_lab args...>
+	tag=$1; rx=$2; shift 2
+	timeout -s KILL 120 tools/part_lab "$@" > gpurun_out/ncu_lab_${tag}_plain.log 2>&1 &&
+	timeout -s KILL 900 ncu --set full --clock-control none --import-source on -k regex:$rx -c 1 \
+		-o gpurun_out/ncu_lab_${tag} -f tools/part_lab "$@" > gpurun_out/ncu_lab_${tag}.log 2>&1
+	echo "rc=$?"; tail -3 gpurun_out/ncu_lab_${tag}.log
+	;;
+tests)      # the GPU parity suite
+	timeout 2400 python -m pytest tests -m gpu -x -q > gpurun_out/tests_${1:-r2}.log 2>&1
+	echo "tests rc=$?" >> gpurun_out/tests_${1:-r2}.log
+	tail -15 gpurun_out/tests_${1:-r2}.log
+	;;
+bench)      # default bench line (+ reference arm)
+	tag=${1:-r2}
+	timeout 900 python bench.py > gpurun_out/bench_${tag}.json 2> gpurun_out/bench_${tag}.err
+	echo "bench rc=$?"
+	cut -c1-600 gpurun_out/bench_${tag}.json
+	tail -5 gpurun_out/bench_${tag}.err
+	;;
+*)
+	echo "jobs: part_lab tests bench"
+	;;
+esac

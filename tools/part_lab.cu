@@ -1,0 +1,600 @@
+// part_lab.cu — development microbenchmark (not product): can EVERY large filter be probed as a shared-memory
+// filter?  One-pass software-write-combining radix partition of the probe keys into buckets whose filter slice
+// (128 KiB = 2^14 sectors) fits shared memory, then one shared-memory lookup kernel per bucket.
+//
+//   modes (argv[1]):
+//     atoms   shared-memory atomicAdd rate on 2048 random counters (the partition's claim primitive)
+//     part    partition kernel + lookup kernel, checked against a plain global-memory probe
+//
+//   nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -lineinfo -o tools/part_lab tools/part_lab.cu
+//   tools/part_lab part [log2_sectors=25] [block=1024] [kpt=8] [rows=1e9] [log2_chunk_rows=32] [density=1] [fake=0]
+#include <cuda_runtime.h>
+
+#include <cmath>
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <vector>
+
+#define CK(x)                                                                                                          \
+	do {                                                                                                               \
+		cudaError_t e_ = (x);                                                                                          \
+		if (e_ != cudaSuccess) {                                                                                       \
+			printf("CUDA error %s at %s:%d\n", cudaGetErrorString(e_), __FILE__, __LINE__);                            \
+			exit(1);                                                                                                   \
+		}                                                                                                              \
+	} while (0)
+
+__host__ __device__ inline uint64_t murmur64(uint64_t x) {
+	x ^= x >> 32;
+	x *= 0xd6e8feb86659fd93ULL;
+	x ^= x >> 32;
+	x *= 0xd6e8feb86659fd93ULL;
+	x ^= x >> 32;
+	return x;
+}
+__host__ __device__ inline uint64_t splitmix64(uint64_t x) {
+	uint64_t z = x + 0x9e3779b97f4a7c15ULL;
+	z = (z ^ (z >> 30)) * 0xbf58476d1ce4e5b9ULL;
+	z = (z ^ (z >> 27)) * 0x94d049bb133111ebULL;
+	return z ^ (z >> 31);
+}
+
+__global__ void gen_keys(uint64_t *k, uint64_t n) {
+	for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
+		k[i] = splitmix64(i);
+	}
+}
+// ~75 % of the bits set: a key passes with probability ≈ 0.75^4 ≈ 0.3
+__global__ void fill_filter(uint64_t *f, uint64_t s, int density) {
+	for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < s; i += (uint64_t)gridDim.x * blockDim.x) {
+		const uint64_t a = splitmix64(i * 77 + 1), b = splitmix64(i * 77 + 2);
+		f[i] = density == 0 ? (a | b) : (density == 1 ? a : (a & b)); // 75 / 50 / 25 % of the bits: 32 / 6 / 0.4 % hits
+	}
+}
+
+constexpr int kSliceLog = 14; // sectors per bucket slice: 128 KiB
+constexpr uint64_t kValid = 1ULL << 63;
+
+__device__ __forceinline__ uint32_t test4(uint64_t w, uint32_t p0, uint32_t p1, uint32_t p2, uint32_t p3) {
+	return (uint32_t)(w >> p0) & (uint32_t)(w >> p1) & (uint32_t)(w >> p2) & (uint32_t)(w >> p3) & 1u;
+}
+
+// reference: plain global lookups into a row-ordered bitmap
+__global__ void __launch_bounds__(256) ref_probe(const uint64_t *__restrict__ keys, const uint64_t *__restrict__ filter,
+                                                 uint64_t smask, uint64_t n, uint32_t *bitmap) {
+	for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
+		const uint64_t h = murmur64(keys[i]);
+		const uint32_t hi = (uint32_t)(h >> 32);
+		const uint64_t w = filter[h & smask];
+		const uint32_t hit = test4(w, hi & 63, (hi >> 8) & 63, (hi >> 16) & 63, (hi >> 24) & 63);
+		const uint32_t b = __ballot_sync(0xffffffffu, hit);
+		if ((threadIdx.x & 31) == 0) {
+			bitmap[i >> 5] = b;
+		}
+	}
+}
+
+__global__ void cmp_words(const uint32_t *a, const uint32_t *b, uint64_t n, unsigned long long *diff,
+                          unsigned long long *bits) {
+	unsigned long long d = 0, c = 0;
+	for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
+		d += a[i] != b[i];
+		c += __popc(a[i]);
+	}
+	if (d) {
+		atomicAdd(diff, d);
+	}
+	atomicAdd(bits, c);
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// atoms: every thread does `per_thread` atomicAdd on random counters of a 2048-entry shared array
+// ---------------------------------------------------------------------------------------------------------
+template <int MODE> // 0: atomicAdd with return, 1: plain ld+st (no atomicity; the smem op floor), 2: red (no return),
+                    // 3: __match_any_sync on an 11-bit value, 4: 64-bit random LDS, 5: atomicAdd on 256 counters
+__global__ void __launch_bounds__(1024) atoms_kernel(uint32_t per_thread, uint32_t *sink) {
+	__shared__ uint64_t ctr64[2048];
+	uint32_t *ctr = reinterpret_cast<uint32_t *>(ctr64);
+	for (int i = threadIdx.x; i < 2048; i += blockDim.x) {
+		ctr64[i] = 0;
+	}
+	__syncthreads();
+	uint64_t x = splitmix64(blockIdx.x * 1024ull + threadIdx.x);
+	uint32_t acc = 0;
+	for (uint32_t k = 0; k < per_thread; k += 4) {
+		x = x * 6364136223846793005ULL + 1442695040888963407ULL;
+		const uint64_t r = x >> 16;
+#pragma unroll
+		for (int j = 0; j < 4; j++) {
+			const uint32_t b = (uint32_t)(r >> (11 * j)) & 2047u;
+			if (MODE == 0) {
+				acc += atomicAdd(&ctr[b], 1u);
+			} else if (MODE == 5) {
+				acc += atomicAdd(&ctr[b & 255u], 1u);
+			} else if (MODE == 1) {
+				const uint32_t v = ((volatile uint32_t *)ctr)[b];
+				((volatile uint32_t *)ctr)[b] = v + 1;
+				acc += v;
+			} else if (MODE == 2) {
+				asm volatile("red.shared.add.u32 [%0], 1;" ::"r"((uint32_t)__cvta_generic_to_shared(&ctr[b])) : "memory");
+			} else if (MODE == 3) {
+				acc += __match_any_sync(0xffffffffu, b);
+			} else {
+				acc += (uint32_t)((volatile uint64_t *)ctr64)[b];
+			}
+		}
+	}
+	__syncthreads();
+	if (acc == 0x12345678u || ctr[threadIdx.x] == 0xffffffffu) {
+		sink[0] = acc;
+	}
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// partition: one CTA per SM owns a contiguous row range; per bucket one 64-byte staging line (8 records) in
+// shared memory; a key claims a slot with one shared atomicAdd, the claimer of slot 7 flushes the line to the
+// (CTA, bucket) region in global memory and re-opens it.
+//   record = valid:1 | row-in-CTA-range:25 | 4 × 6 bit positions | sector-in-slice:14
+// ---------------------------------------------------------------------------------------------------------
+struct PartArgs {
+	const uint64_t *keys;
+	uint64_t n;
+	uint64_t rows_per_cta;
+	uint32_t smask;
+	uint32_t nb;        // buckets = (smask + 1) >> kSliceLog
+	uint32_t cap_lines; // lines per (CTA, bucket) region
+	uint64_t *records;  // [cta][bucket][cap_lines][8]
+	uint32_t *counts;   // [cta][bucket] records
+	unsigned long long *overflow;
+	unsigned long long *retries;
+};
+
+__device__ __forceinline__ uint64_t make_record(uint64_t h, uint32_t rowrel) {
+	const uint32_t hi = (uint32_t)(h >> 32) & 0x3f3f3f3fu;
+	const uint32_t pos = (hi & 0x3fu) | ((hi >> 2) & 0xfc0u) | ((hi >> 4) & 0x3f000u) | ((hi >> 6) & 0xfc0000u);
+	const uint32_t lo = ((uint32_t)h & ((1u << kSliceLog) - 1u)) | (pos << kSliceLog); // 14 + 18 of the 24 bits
+	const uint32_t up = (pos >> 18) | (rowrel << 6) | 0x80000000u;
+	return ((uint64_t)up << 32) | lo;
+}
+
+template <int BLOCK, int KPT, bool FAKE = false> // FAKE: no atomics (racy, wrong) — the cost of everything else
+__global__ void __launch_bounds__(BLOCK, 1) part_kernel(const PartArgs a) {
+	extern __shared__ __align__(128) unsigned char s_dyn[];
+	uint64_t *stage = reinterpret_cast<uint64_t *>(s_dyn);                   // nb × 8 records
+	uint32_t *ctr = reinterpret_cast<uint32_t *>(s_dyn + (size_t)a.nb * 64); // claims of the open line
+	uint32_t *lines = ctr + a.nb;                                            // lines flushed so far
+	const uint32_t lane = threadIdx.x & 31u;
+	for (uint32_t i = threadIdx.x; i < a.nb * 8; i += BLOCK) {
+		stage[i] = 0;
+	}
+	for (uint32_t i = threadIdx.x; i < a.nb; i += BLOCK) {
+		ctr[i] = 0;
+		lines[i] = 0;
+	}
+	__syncthreads();
+	const uint64_t row_lo = (uint64_t)blockIdx.x * a.rows_per_cta;
+	const uint64_t row_hi = row_lo + a.rows_per_cta < a.n ? row_lo + a.rows_per_cta : a.n;
+	uint64_t *const my_records = a.records + (uint64_t)blockIdx.x * a.nb * a.cap_lines * 8;
+	uint32_t n_retry = 0, n_over = 0, fake_ctr = threadIdx.x;
+	const uint32_t bshift = kSliceLog;
+
+	for (uint64_t base = row_lo; base < row_hi; base += (uint64_t)BLOCK * KPT) {
+		// KPT keys per thread: KPT/2 coalesced 16-byte loads, all in flight together
+		uint64_t rec[KPT];
+		uint32_t bkt[KPT];
+		uint32_t pending = 0;
+		{
+			ulonglong2 k[KPT / 2];
+#pragma unroll
+			for (int r = 0; r < KPT / 2; r++) {
+				const uint64_t row = base + (uint64_t)r * BLOCK * 2 + threadIdx.x * 2;
+				k[r] = make_ulonglong2(0, 0);
+				if (row + 1 < row_hi) {
+					asm volatile("ld.global.nc.L1::no_allocate.v2.u64 {%0, %1}, [%2];"
+					             : "=l"(k[r].x), "=l"(k[r].y)
+					             : "l"(a.keys + row));
+					pending |= 3u << (2 * r);
+				} else if (row < row_hi) {
+					k[r].x = a.keys[row];
+					pending |= 1u << (2 * r);
+				}
+			}
+#pragma unroll
+			for (int r = 0; r < KPT / 2; r++) {
+				const uint32_t rowrel = (uint32_t)(base - row_lo) + r * BLOCK * 2 + threadIdx.x * 2;
+				const uint64_t h0 = murmur64(k[r].x), h1 = murmur64(k[r].y);
+				rec[2 * r] = make_record(h0, rowrel);
+				rec[2 * r + 1] = make_record(h1, rowrel + 1);
+				bkt[2 * r] = ((uint32_t)h0 & a.smask) >> bshift;
+				bkt[2 * r + 1] = ((uint32_t)h1 & a.smask) >> bshift;
+			}
+		}
+		// claim rounds: a key whose bucket's line is full (awaiting its flush) stays pending for the next round
+		while (true) {
+			uint32_t flush = 0;
+#pragma unroll
+			for (int i = 0; i < KPT; i++) {
+				if ((pending >> i) & 1u) {
+					uint32_t c;
+					if (FAKE) {
+						c = (fake_ctr++) & 7u;
+					} else {
+						c = atomicAdd(&ctr[bkt[i]], 1u);
+					}
+					if (c < 8u) {
+						stage[bkt[i] * 8u + c] = rec[i];
+						pending &= ~(1u << i);
+						flush |= (c == 7u) ? (1u << i) : 0u;
+					}
+				}
+			}
+			__syncwarp();
+			// flush the lines this lane completed
+			while (flush) {
+				const int i = __ffs(flush) - 1;
+				flush &= flush - 1;
+				uint32_t b = 0;
+#pragma unroll
+				for (int j = 0; j < KPT; j++) {
+					b = (j == i) ? bkt[j] : b;
+				}
+				ulonglong2 *line = reinterpret_cast<ulonglong2 *>(stage + b * 8u);
+				ulonglong2 v[4];
+				bool ok;
+				do { // the other seven claimers may still be between their atomicAdd and their store
+					ok = true;
+#pragma unroll
+					for (int q = 0; q < 4; q++) {
+						asm volatile("ld.volatile.shared.v2.u64 {%0, %1}, [%2];"
+						             : "=l"(v[q].x), "=l"(v[q].y)
+						             : "r"((uint32_t)__cvta_generic_to_shared(line + q))
+						             : "memory");
+						ok = ok && (v[q].x & v[q].y & kValid);
+					}
+				} while (!ok && !FAKE);
+#pragma unroll
+				for (int q = 0; q < 4; q++) {
+					line[q] = make_ulonglong2(0, 0);
+				}
+				const uint32_t l = FAKE ? (lines[b] % a.cap_lines) : lines[b];
+				lines[b] = l + 1;
+				__threadfence_block(); // zeroed slots and line count before the line re-opens
+				atomicExch(&ctr[b], 0u);
+				if (l < a.cap_lines) {
+					ulonglong2 *dst = reinterpret_cast<ulonglong2 *>(my_records + ((uint64_t)b * a.cap_lines + l) * 8);
+#pragma unroll
+					for (int q = 0; q < 4; q++) {
+						asm volatile("st.global.cs.v2.u64 [%0], {%1, %2};" ::"l"(dst + q), "l"(v[q].x), "l"(v[q].y)
+						             : "memory");
+					}
+				} else {
+					n_over += 8;
+				}
+			}
+			if (!__any_sync(0xffffffffu, pending != 0u)) {
+				break;
+			}
+			n_retry += __popc(pending);
+		}
+	}
+	__syncthreads();
+	// partial lines
+	for (uint32_t b = threadIdx.x; b < a.nb; b += BLOCK) {
+		const uint32_t c = ctr[b] < 8u ? ctr[b] : 8u; // < 8 by construction
+		uint32_t l = lines[b];
+		if (l > a.cap_lines) {
+			l = a.cap_lines;
+		}
+		uint32_t total = l * 8u;
+		if (c && l < a.cap_lines) {
+			uint64_t *dst = my_records + ((uint64_t)b * a.cap_lines + l) * 8;
+			for (uint32_t j = 0; j < c; j++) {
+				dst[j] = stage[b * 8u + j];
+			}
+			total += c;
+		} else if (c) {
+			n_over += c;
+		}
+		a.counts[(uint64_t)blockIdx.x * a.nb + b] = total;
+	}
+	if (n_over) {
+		atomicAdd(a.overflow, (unsigned long long)n_over);
+	}
+	n_retry = __reduce_add_sync(0xffffffffu, n_retry);
+	if (lane == 0 && n_retry) {
+		atomicAdd(a.retries, (unsigned long long)n_retry);
+	}
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// lookup: persistent CTAs; per bucket the 128 KiB slice arrives in shared memory through ONE bulk copy, then
+// the warps stream the bucket's records region by region and OR hit bits into the row-ordered bitmap.
+// ---------------------------------------------------------------------------------------------------------
+struct LookArgs {
+	const uint64_t *filter;
+	uint32_t nb;
+	uint32_t nparts; // partition CTAs
+	uint32_t cap_lines;
+	uint64_t rows_per_cta;
+	const uint64_t *records;
+	const uint32_t *counts;
+	uint32_t *bitmap;
+};
+
+__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
+	asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"((uint32_t)__cvta_generic_to_shared(bar)), "r"(count)
+	             : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
+	asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"((uint32_t)__cvta_generic_to_shared(bar)),
+	             "r"(bytes)
+	             : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
+	asm volatile("{\n"
+	             ".reg .pred p;\n"
+	             "WAIT_%=:\n"
+	             "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+	             "@p bra DONE_%=;\n"
+	             "bra WAIT_%=;\n"
+	             "DONE_%=:\n"
+	             "}" ::"r"((uint32_t)__cvta_generic_to_shared(bar)),
+	             "r"(parity)
+	             : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void *smem_dst, const void *gmem_src, uint32_t bytes, uint64_t *bar) {
+	asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+	                 (uint32_t)__cvta_generic_to_shared(smem_dst)),
+	             "l"(gmem_src), "r"(bytes), "r"((uint32_t)__cvta_generic_to_shared(bar))
+	             : "memory");
+}
+
+template <int BLOCK, int U> // U 16-byte loads (2 records each) in flight per lane
+__global__ void __launch_bounds__(BLOCK, 1) lookup_kernel(const LookArgs a) {
+	extern __shared__ __align__(128) unsigned char s_dyn[];
+	uint64_t *slice = reinterpret_cast<uint64_t *>(s_dyn);
+	__shared__ __align__(8) uint64_t bar;
+	constexpr uint32_t kSliceBytes = (1u << kSliceLog) * 8u;
+	const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+	constexpr uint32_t NWARPS = BLOCK / 32;
+	if (threadIdx.x == 0) {
+		mbar_init(&bar, 1);
+		asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+	}
+	__syncthreads();
+	uint32_t parity = 0;
+	for (uint32_t b = blockIdx.x; b < a.nb; b += gridDim.x) {
+		if (threadIdx.x == 0) {
+			mbar_expect_tx(&bar, kSliceBytes);
+			bulk_g2s(slice, a.filter + ((uint64_t)b << kSliceLog), kSliceBytes, &bar);
+		}
+		mbar_wait(&bar, parity);
+		parity ^= 1u;
+		for (uint32_t r = warp; r < a.nparts; r += NWARPS) {
+			const uint32_t cnt = a.counts[(uint64_t)r * a.nb + b];
+			const ulonglong2 *src =
+			    reinterpret_cast<const ulonglong2 *>(a.records + ((uint64_t)r * a.nb + b) * a.cap_lines * 8);
+			const uint64_t row_base = (uint64_t)r * a.rows_per_cta;
+			const uint32_t npairs = (cnt + 1) >> 1;
+			for (uint32_t j0 = 0; j0 < npairs; j0 += 32 * U) {
+				ulonglong2 v[U];
+#pragma unroll
+				for (int u = 0; u < U; u++) {
+					const uint32_t j = j0 + u * 32 + lane;
+					v[u] = make_ulonglong2(0, 0);
+					if (j < npairs) {
+						asm volatile("ld.global.nc.L1::no_allocate.v2.u64 {%0, %1}, [%2];"
+						             : "=l"(v[u].x), "=l"(v[u].y)
+						             : "l"(src + j));
+						if (2 * j + 1 >= cnt) {
+							v[u].y = 0;
+						}
+					}
+				}
+				uint64_t w[2 * U];
+#pragma unroll
+				for (int u = 0; u < U; u++) {
+					w[2 * u] = slice[(uint32_t)v[u].x & ((1u << kSliceLog) - 1u)];
+					w[2 * u + 1] = slice[(uint32_t)v[u].y & ((1u << kSliceLog) - 1u)];
+				}
+#pragma unroll
+				for (int u = 0; u < 2 * U; u++) {
+					const uint64_t rec = (u & 1) ? v[u >> 1].y : v[u >> 1].x;
+					const uint32_t lo = (uint32_t)rec, up = (uint32_t)(rec >> 32);
+					const uint32_t hit = test4(w[u], (lo >> 14) & 63u, (lo >> 20) & 63u, lo >> 26, up & 63u) & (up >> 31);
+					if (hit) {
+						const uint64_t row = row_base + ((up >> 6) & 0x1ffffffu);
+						atomicOr(a.bitmap + (row >> 5), 1u << (row & 31u));
+					}
+				}
+			}
+		}
+		__syncthreads(); // every warp is done with the slice before the next bulk copy overwrites it
+	}
+}
+
+static float time_kernel(int reps, void (*fn)(void *), void *arg) {
+	cudaEvent_t e0, e1;
+	CK(cudaEventCreate(&e0));
+	CK(cudaEventCreate(&e1));
+	fn(arg);
+	CK(cudaDeviceSynchronize());
+	CK(cudaEventRecord(e0));
+	for (int i = 0; i < reps; i++) {
+		fn(arg);
+	}
+	CK(cudaEventRecord(e1));
+	CK(cudaEventSynchronize(e1));
+	float ms = 0;
+	CK(cudaEventElapsedTime(&ms, e0, e1));
+	return ms / reps;
+}
+
+struct AtomsRun {
+	int mode;
+	int threads;
+	uint32_t per_thread;
+	uint32_t *sink;
+};
+static void run_atoms(void *p) {
+	AtomsRun *r = (AtomsRun *)p;
+	const int threads = r->threads;
+	switch (r->mode) {
+	case 0: atoms_kernel<0><<<148, threads>>>(r->per_thread, r->sink); break;
+	case 1: atoms_kernel<1><<<148, threads>>>(r->per_thread, r->sink); break;
+	case 2: atoms_kernel<2><<<148, threads>>>(r->per_thread, r->sink); break;
+	case 3: atoms_kernel<3><<<148, threads>>>(r->per_thread, r->sink); break;
+	case 4: atoms_kernel<4><<<148, threads>>>(r->per_thread, r->sink); break;
+	default: atoms_kernel<5><<<148, threads>>>(r->per_thread, r->sink); break;
+	}
+}
+
+struct PartRun {
+	PartArgs pa;
+	LookArgs la;
+	int block, kpt;
+	bool fake;
+	size_t part_smem;
+	uint64_t n_total, chunk_rows;
+	int what; // 0 both, 1 partition only, 2 lookup only
+};
+template <int BLOCK, int KPT>
+static void launch_part(const PartRun *r, const PartArgs &pa) {
+	if (r->fake) {
+		CK(cudaFuncSetAttribute(part_kernel<BLOCK, KPT, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)r->part_smem));
+		part_kernel<BLOCK, KPT, true><<<148, BLOCK, r->part_smem>>>(pa);
+	} else {
+		CK(cudaFuncSetAttribute(part_kernel<BLOCK, KPT, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)r->part_smem));
+		part_kernel<BLOCK, KPT, false><<<148, BLOCK, r->part_smem>>>(pa);
+	}
+}
+static uint64_t rows_per_cta_for(uint64_t n) {
+	return ((n + 147) / 148 + 511) / 512 * 512;
+}
+static void run_part(void *p) {
+	PartRun *r = (PartRun *)p;
+	for (uint64_t c0 = 0; c0 < r->n_total; c0 += r->chunk_rows) {
+		const uint64_t cn = c0 + r->chunk_rows < r->n_total ? r->chunk_rows : r->n_total - c0;
+		PartArgs pa = r->pa;
+		LookArgs la = r->la;
+		pa.keys += c0;
+		pa.n = cn;
+		pa.rows_per_cta = la.rows_per_cta = rows_per_cta_for(cn);
+		la.bitmap += c0 / 32;
+		if (r->what != 2) {
+			if (r->block == 1024 && r->kpt == 8) {
+				launch_part<1024, 8>(r, pa);
+			} else if (r->block == 1024 && r->kpt == 4) {
+				launch_part<1024, 4>(r, pa);
+			} else if (r->block == 512 && r->kpt == 8) {
+				launch_part<512, 8>(r, pa);
+			} else if (r->block == 512 && r->kpt == 4) {
+				launch_part<512, 4>(r, pa);
+			} else {
+				launch_part<256, 8>(r, pa);
+			}
+		}
+		if (r->what != 1) {
+			CK(cudaMemsetAsync(la.bitmap, 0, (cn + 31) / 32 * 4));
+			const size_t smem = (1u << kSliceLog) * 8;
+			CK(cudaFuncSetAttribute(lookup_kernel<1024, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+			lookup_kernel<1024, 4><<<148, 1024, smem>>>(la);
+		}
+	}
+}
+
+int main(int argc, char **argv) {
+	const char *mode = argc > 1 ? argv[1] : "part";
+	if (!strcmp(mode, "atoms")) {
+		uint32_t *sink;
+		CK(cudaMalloc(&sink, 4));
+		const char *names[6] = {"atomicAdd/2048 (return)", "plain ld+st", "red.shared.add", "match_any", "LDS.64 random",
+		                        "atomicAdd/256 (return)"};
+		for (int threads = 256; threads <= 1024; threads *= 2) {
+			for (int m = 0; m < 6; m++) {
+				AtomsRun r {m, threads, 4096, sink};
+				const float ms = time_kernel(5, run_atoms, &r);
+				const double ops = 148.0 * threads * 4096;
+				printf("atoms %4d thr/SM %-24s %.3f ms  %.1f Gops/s  %.2f ops/clk/SM (at 1.9 GHz)\n", threads, names[m], ms,
+				       ops / ms / 1e6, ops / ms / 1e6 / 148 / 1.9);
+			}
+		}
+		return 0;
+	}
+	const int log_sectors = argc > 2 ? atoi(argv[2]) : 25;
+	const int block = argc > 3 ? atoi(argv[3]) : 1024;
+	const int kpt = argc > 4 ? atoi(argv[4]) : 8;
+	const uint64_t n = argc > 5 ? strtoull(argv[5], nullptr, 10) : 1000000000ULL;
+	const int chunk_log = argc > 6 ? atoi(argv[6]) : 32;
+	const int density = argc > 7 ? atoi(argv[7]) : 1;
+	const bool fake = argc > 8 && atoi(argv[8]) != 0;
+	const uint64_t chunk_rows = chunk_log >= 32 ? n : (1ULL << chunk_log);
+	const uint64_t S = 1ULL << log_sectors;
+	const uint32_t nb = (uint32_t)(S >> kSliceLog);
+	const uint32_t nparts = 148;
+	const uint64_t rows_per_cta = rows_per_cta_for(chunk_rows < n ? chunk_rows : n);
+	const double mean = (double)rows_per_cta / nb;
+	const uint32_t cap_lines = (uint32_t)((mean + 6.0 * sqrt(mean) + 16.0) / 8.0) + 1;
+	printf("n=%llu chunk=%llu S=2^%d (%llu MiB) buckets=%u rows/cta=%llu mean/bucket=%.1f cap_lines=%u scratch=%.2f GB block=%d "
+	       "kpt=%d density=%d fake=%d\n",
+	       (unsigned long long)n, (unsigned long long)chunk_rows, log_sectors, (unsigned long long)(S * 8 >> 20), nb,
+	       (unsigned long long)rows_per_cta, mean, cap_lines, (double)nparts * nb * cap_lines * 64 / 1e9, block, kpt, density,
+	       (int)fake);
+	uint64_t *keys, *filter, *records;
+	uint32_t *counts, *bitmap, *bitmap_ref;
+	unsigned long long *stats;
+	const uint64_t bitmap_words = (n + 31) / 32 + 64;
+	CK(cudaMalloc(&keys, n * 8));
+	CK(cudaMalloc(&filter, S * 8));
+	CK(cudaMalloc(&records, (uint64_t)nparts * nb * cap_lines * 64));
+	CK(cudaMalloc(&counts, (uint64_t)nparts * nb * 4));
+	CK(cudaMalloc(&bitmap, bitmap_words * 4));
+	CK(cudaMalloc(&bitmap_ref, bitmap_words * 4));
+	CK(cudaMalloc(&stats, 4 * 8));
+	CK(cudaMemset(stats, 0, 4 * 8));
+	gen_keys<<<148 * 8, 256>>>(keys, n);
+	fill_filter<<<148 * 8, 256>>>(filter, S, density);
+	CK(cudaDeviceSynchronize());
+
+	PartRun r;
+	r.pa = PartArgs {keys, n, rows_per_cta, (uint32_t)(S - 1), nb, cap_lines, records, counts, stats, stats + 1};
+	r.la = LookArgs {filter, nb, nparts, cap_lines, rows_per_cta, records, counts, bitmap};
+	r.block = block;
+	r.kpt = kpt;
+	r.fake = fake;
+	r.part_smem = (size_t)nb * 64 + (size_t)nb * 8;
+	r.n_total = n;
+	r.chunk_rows = chunk_rows;
+
+	unsigned long long hstats[4];
+	if (chunk_rows >= n) { // separate timings only make sense unchunked (the lookup needs its chunk's records)
+		r.what = 1;
+		const float ms_part = time_kernel(3, run_part, &r);
+		CK(cudaMemcpy(hstats, stats, sizeof(hstats), cudaMemcpyDeviceToHost));
+		printf("partition  %.3f ms  %.1f Gkeys/s  (16 B/key: %.2f TB/s)  overflow=%llu retries/run=%.0f (%.3f %% of keys)\n",
+		       ms_part, n / ms_part / 1e6, 16.0 * n / ms_part / 1e9, hstats[0], hstats[1] / 4.0,
+		       100.0 * hstats[1] / 4.0 / n);
+		if (fake) {
+			return 0;
+		}
+		r.what = 2;
+		const float ms_look = time_kernel(3, run_part, &r);
+		printf("lookup     %.3f ms  %.1f Gkeys/s  (8 B/key: %.2f TB/s)\n", ms_look, n / ms_look / 1e6,
+		       8.0 * n / ms_look / 1e9);
+	}
+	r.what = 0;
+	const float ms_both = time_kernel(3, run_part, &r);
+	printf("both       %.3f ms  %.1f Gkeys/s\n", ms_both, n / ms_both / 1e6);
+
+	// correctness against plain global lookups
+	ref_probe<<<148 * 8, 256>>>(keys, filter, S - 1, n & ~31ULL, bitmap_ref);
+	CK(cudaMemset(stats, 0, 4 * 8));
+	cmp_words<<<148 * 4, 256>>>(bitmap, bitmap_ref, n / 32, stats + 2, stats + 3);
+	CK(cudaDeviceSynchronize());
+	CK(cudaMemcpy(hstats, stats, sizeof(hstats), cudaMemcpyDeviceToHost));
+	printf("check      %llu differing bitmap words, %llu hits (%.2f %%)  %s\n", hstats[2], hstats[3],
+	       100.0 * hstats[3] / n, hstats[2] == 0 ? "OK" : "MISMATCH");
+	return hstats[2] == 0 ? 0 : 1;
+}
