@@ -19,6 +19,30 @@ part_lab)   # prototype: one-pass partition into shared-memory-sized buckets + s
 	done
 	cat $out
 	;;
+part2)      # v2 prototype sweep
+	out=gpurun_out/part2_${1:-r2d}.txt
+	: > $out
+	# sectors block kpt rows log2_chunk density slots skew
+	for cfg in "25 1024 4 1000000000 26 1 8 0" "25 1024 2 1000000000 26 1 8 0" "25 768 4 1000000000 26 1 8 0" "25 512 8 1000000000 26 1 8 0" \
+	           "25 1024 4 1000000000 26 0 8 0" "25 1024 4 1000000000 26 2 8 0" "25 1024 4 1000000000 25 1 8 0" \
+	           "24 1024 4 1000000000 26 1 16 0" "24 1024 4 1000000000 26 1 8 0" "25 1024 4 200000000 26 1 8 4" "25 1024 4 200000000 26 1 8 14"; do
+		timeout -s KILL 90 tools/part_lab part2 $cfg >> $out 2>&1
+		echo "rc=$?" >> $out
+	done
+	cat $out
+	;;
+part3)      # v3 prototype sweep
+	out=gpurun_out/part3_${1:-r2e}.txt
+	: > $out
+	# sectors block kpp rows log2_chunk density slots skew
+	for cfg in "25 1024 4 1000000000 27 1 8 0" "25 1024 2 1000000000 27 1 8 0" "25 1024 8 1000000000 27 1 8 0" "25 768 4 1000000000 27 1 8 0" \
+	           "25 1024 4 1000000000 27 0 8 0" "25 1024 4 1000000000 26 1 8 0" \
+	           "24 1024 4 1000000000 27 1 16 0" "24 1024 4 1000000000 27 1 8 0" "25 1024 4 200000000 27 1 8 4" "25 1024 4 200000000 27 1 8 14"; do
+		timeout -s KILL 90 tools/part_lab part3 $cfg >> $out 2>&1
+		echo "rc=$?" >> $out
+	done
+	cat $out
+	;;
 ncu_lab)    # full ncu capture of one prototype kernel: ncu_lab <tag> <kernel regex> <part_lab args...>
 	tag=$1; rx=$2; shift 2
 	timeout -s KILL 120 tools/part_lab "$@" > gpurun_out/ncu_lab_${tag}_plain.log 2>&1 &&

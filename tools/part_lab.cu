@@ -46,6 +46,11 @@ __global__ void gen_keys(uint64_t *k, uint64_t n) {
 		k[i] = splitmix64(i);
 	}
 }
+__global__ void mask_keys(uint64_t *k, uint64_t n, uint64_t m) {
+	for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
+		k[i] &= m;
+	}
+}
 // ~75 % of the bits set: a key passes with probability ≈ 0.75^4 ≈ 0.3
 __global__ void fill_filter(uint64_t *f, uint64_t s, int density) {
 	for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < s; i += (uint64_t)gridDim.x * blockDim.x) {
@@ -415,6 +420,663 @@ __global__ void __launch_bounds__(BLOCK, 1) lookup_kernel(const LookArgs a) {
 	}
 }
 
+
+// =========================================================================================================
+// v2 — what the ncu capture of v1 said (profiles/part_lab_r2.md): the LSU data pipe is the limit (1.74 wavefronts
+// per key, 88 % busy), 1.5 of them spent by the per-lane line flush (4 LDS.128 + 4 STS.128 + 4 STG.128 per line,
+// one wavefront per active lane each), and 110 thread-instructions per key.  Shared atomics are NOT the limit
+// (9 per clock and SM on 2048 random counters).  v2: the flush is done by groups of SLOTS lanes (one lane per
+// record, contiguous LDS.64 / STG.64), right after the key step that completed the line; the bucket word packs
+// {claims:16 | line:16}, so the claim that completes a line also learns where the line goes.
+//   record = valid:1 | row-in-CTA-range:19 | hash bits 32..61 & 0x3f3f3f3f : 30 | sector-in-slice:14
+// =========================================================================================================
+struct Part2Args {
+	const uint64_t *keys;
+	uint64_t n;
+	uint64_t rows_per_cta;
+	uint32_t smask;
+	uint32_t nb;
+	uint32_t cap_lines;
+	uint64_t *records; // [cta][bucket][cap_lines][SLOTS]
+	uint32_t *counts;  // [cta][bucket] records
+	const uint64_t *filter;
+	uint32_t *bitmap;
+	unsigned long long *stats; // [0] records that overflowed their region, [1] failed claims, [2] direct lookups
+};
+
+__device__ __forceinline__ uint64_t make_record2(uint64_t h, uint32_t rowrel) {
+	const uint32_t hm = (uint32_t)(h >> 32) & 0x3f3f3f3fu;
+	const uint32_t lo = ((uint32_t)h & ((1u << kSliceLog) - 1u)) + hm * (1u << kSliceLog);
+	const uint32_t up = (hm >> 18) + rowrel * 4096u + 0x80000000u;
+	return ((uint64_t)up << 32) | lo;
+}
+__device__ __forceinline__ uint32_t record2_hit(uint64_t w, uint32_t lo, uint32_t up) {
+	return test4(w, (lo >> 14) & 63u, (lo >> 22) & 63u, __funnelshift_r(lo, up, 30) & 63u, (up >> 6) & 63u);
+}
+__device__ __forceinline__ void direct_lookup2(const Part2Args &a, uint32_t bucket, uint64_t rec, uint64_t row_lo) {
+	const uint32_t lo = (uint32_t)rec, up = (uint32_t)(rec >> 32);
+	const uint64_t w = a.filter[((uint64_t)bucket << kSliceLog) | (lo & ((1u << kSliceLog) - 1u))];
+	if (record2_hit(w, lo, up)) {
+		const uint64_t row = row_lo + ((up >> 12) & 0x7ffffu);
+		atomicOr(a.bitmap + (row >> 5), 1u << (row & 31u));
+	}
+}
+
+// forward declarations (defined with the lookup kernel below)
+__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count);
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes);
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity);
+__device__ __forceinline__ void bulk_g2s(void *smem_dst, const void *gmem_src, uint32_t bytes, uint64_t *bar);
+
+// KPT = key steps per staged buffer: a warp's keys arrive in warp-private buffers of 32·KPT keys through one bulk
+// copy each (double buffered, one mbarrier per buffer), so the loop body — one key per lane — exists once.
+template <int BLOCK, int KPT, int SLOTS>
+__global__ void __launch_bounds__(BLOCK, 1) part2_kernel(const Part2Args a) {
+	constexpr int NWARPS = BLOCK / 32;
+	constexpr int GROUPS = 32 / SLOTS; // lines flushed per iteration
+	constexpr uint32_t SEG = 32u * KPT; // keys per buffer
+	extern __shared__ __align__(128) unsigned char s_dyn[];
+	uint64_t *stage = reinterpret_cast<uint64_t *>(s_dyn);                          // nb × SLOTS records
+	uint32_t *ctr = reinterpret_cast<uint32_t *>(s_dyn + (size_t)a.nb * SLOTS * 8); // {claims:16 | line:16}
+	const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+	uint32_t *flist = ctr + a.nb + warp * 32;                                       // warp-private
+	uint64_t *kbuf = reinterpret_cast<uint64_t *>(ctr + a.nb + NWARPS * 32) + warp * 2 * SEG;
+	__shared__ __align__(8) uint64_t bars[NWARPS][2];
+	const uint32_t grp = lane / SLOTS, sub = lane % SLOTS;
+	uint32_t lt;
+	asm("mov.u32 %0, %%lanemask_lt;" : "=r"(lt));
+	for (uint32_t i = threadIdx.x; i < a.nb * SLOTS; i += BLOCK) {
+		stage[i] = 0;
+	}
+	for (uint32_t i = threadIdx.x; i < a.nb; i += BLOCK) {
+		ctr[i] = 0;
+	}
+	if (lane == 0) {
+		mbar_init(&bars[warp][0], 1);
+		mbar_init(&bars[warp][1], 1);
+		asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+	}
+	__syncthreads();
+	const uint64_t row_lo = (uint64_t)blockIdx.x * a.rows_per_cta;
+	const uint64_t row_hi = row_lo + a.rows_per_cta < a.n ? row_lo + a.rows_per_cta : a.n;
+	uint64_t *const my_records = a.records + (uint64_t)blockIdx.x * a.nb * a.cap_lines * SLOTS;
+	uint32_t n_fail = 0, n_over = 0, n_direct = 0;
+	const uint64_t nrows = row_hi > row_lo ? row_hi - row_lo : 0;
+	const uint32_t nseg = (uint32_t)((nrows + SEG - 1) / SEG);
+	const uint32_t full_segs = (uint32_t)(nrows / SEG);
+
+	auto issue = [&](uint32_t seg, uint32_t buf) { // lane 0: stage segment `seg` into buffer `buf`
+		if (seg < full_segs) {
+			mbar_expect_tx(&bars[warp][buf], SEG * 8);
+			bulk_g2s(kbuf + buf * SEG, a.keys + row_lo + (uint64_t)seg * SEG, SEG * 8, &bars[warp][buf]);
+		}
+	};
+	uint32_t phase = 0; // bit b = parity to wait for on buffer b
+	if (lane == 0) {
+		issue(warp, 0);
+	}
+	uint32_t buf = 0;
+	for (uint32_t seg = warp; seg < nseg; seg += NWARPS, buf ^= 1u) {
+		if (lane == 0) {
+			issue(seg + NWARPS, buf ^ 1u);
+		}
+		const bool staged = seg < full_segs;
+		if (staged) {
+			mbar_wait(&bars[warp][buf], (phase >> buf) & 1u);
+			phase ^= 1u << buf;
+		}
+#pragma unroll 1
+		for (uint32_t st = 0; st < (uint32_t)KPT; st++) {
+			const uint32_t rowrel = seg * SEG + st * 32u + lane;
+			bool act = rowrel < nrows;
+			uint64_t k = 0;
+			if (staged) {
+				k = kbuf[buf * SEG + st * 32u + lane];
+			} else if (act) {
+				k = a.keys[row_lo + rowrel];
+			}
+			const uint64_t h = murmur64(k);
+			const uint64_t rec = make_record2(h, rowrel);
+			const uint32_t b = ((uint32_t)h & a.smask) >> kSliceLog;
+			uint32_t tries = 0;
+			while (true) {
+				// claim, store, flush the lines this step completed
+				uint32_t old = 0xffffu;
+				if (act) {
+					old = atomicAdd(&ctr[b], 1u);
+				}
+				const uint32_t c = old & 0xffffu;
+				if (c < (uint32_t)SLOTS) {
+					stage[b * SLOTS + c] = rec;
+				}
+				const bool completes = c == (uint32_t)SLOTS - 1u;
+				const uint32_t fl = __ballot_sync(0xffffffffu, completes);
+				if (fl) { // warp-uniform
+					if (completes) {
+						flist[__popc(fl & lt)] = b | ((old >> 16) << 12);
+					}
+					__syncwarp();
+					const uint32_t nfl = __popc(fl);
+					for (uint32_t it = 0; it < nfl; it += GROUPS) {
+						const uint32_t g = it + grp;
+						if (g < nfl) {
+							const uint32_t e = flist[g];
+							const uint32_t fb = e & 4095u, line = e >> 12;
+							const uint32_t saddr = (uint32_t)__cvta_generic_to_shared(stage + fb * SLOTS + sub);
+							uint64_t v;
+							do { // the claimer of this slot may still be between its atomicAdd and its store
+								asm volatile("ld.volatile.shared.u64 %0, [%1];" : "=l"(v) : "r"(saddr) : "memory");
+							} while (!(v >> 63));
+							asm volatile("st.volatile.shared.u64 [%0], %1;" ::"r"(saddr), "l"(0ULL) : "memory");
+							__syncwarp(SLOTS == 32 ? 0xffffffffu : (((1u << SLOTS) - 1u) << (grp * SLOTS)));
+							if (sub == 0) {
+								atomicExch(&ctr[fb], (line + 1u) << 16); // re-opens the line
+							}
+							if (line < a.cap_lines) {
+								uint64_t *dst = my_records + ((uint64_t)fb * a.cap_lines + line) * SLOTS + sub;
+								asm volatile("st.global.cs.u64 [%0], %1;" ::"l"(dst), "l"(v) : "memory");
+							} else { // skew: the (CTA, bucket) region is full — look the record up on the spot
+								direct_lookup2(a, fb, v, row_lo);
+								n_over++;
+							}
+						}
+					}
+					__syncwarp(); // flist is rewritten by the next step
+				}
+				act = act && c >= (uint32_t)SLOTS; // failed: the line was full, awaiting its flush
+				if (!__any_sync(0xffffffffu, act)) {
+					break;
+				}
+				n_fail += act ? 1u : 0u;
+				if (++tries == 3) { // hot bucket = hot sectors: look up on the spot
+					if (act) {
+						direct_lookup2(a, b, rec, row_lo);
+						n_direct++;
+					}
+					break;
+				}
+			}
+		}
+		__syncwarp(); // every lane is done with this buffer before lane 0 refills it (two iterations on)
+	}
+	__syncthreads();
+	// partial lines
+	for (uint32_t b = threadIdx.x; b < a.nb; b += BLOCK) {
+		const uint32_t c = ctr[b] & 0xffffu; // < SLOTS: every full line has been flushed and re-opened
+		uint32_t l = ctr[b] >> 16;
+		uint32_t total = (l < a.cap_lines ? l : a.cap_lines) * SLOTS;
+		for (uint32_t j = 0; j < c && j < (uint32_t)SLOTS; j++) {
+			const uint64_t v = stage[b * SLOTS + j];
+			if (l < a.cap_lines) {
+				my_records[((uint64_t)b * a.cap_lines + l) * SLOTS + j] = v;
+				total++;
+			} else {
+				direct_lookup2(a, b, v, row_lo);
+				n_over++;
+			}
+		}
+		a.counts[(uint64_t)blockIdx.x * a.nb + b] = total;
+	}
+	n_fail = __reduce_add_sync(0xffffffffu, n_fail);
+	n_over = __reduce_add_sync(0xffffffffu, n_over);
+	n_direct = __reduce_add_sync(0xffffffffu, n_direct);
+	if (lane == 0) {
+		if (n_over) {
+			atomicAdd(a.stats, (unsigned long long)n_over);
+		}
+		if (n_fail) {
+			atomicAdd(a.stats + 1, (unsigned long long)n_fail);
+		}
+		if (n_direct) {
+			atomicAdd(a.stats + 2, (unsigned long long)n_direct);
+		}
+	}
+}
+
+template <int BLOCK, int U, int SLOTS>
+__global__ void __launch_bounds__(BLOCK, 1) lookup2_kernel(const LookArgs a) {
+	extern __shared__ __align__(128) unsigned char s_dyn[];
+	uint64_t *slice = reinterpret_cast<uint64_t *>(s_dyn);
+	__shared__ __align__(8) uint64_t bar;
+	constexpr uint32_t kSliceBytes = (1u << kSliceLog) * 8u;
+	const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+	constexpr uint32_t NWARPS = BLOCK / 32;
+	if (threadIdx.x == 0) {
+		mbar_init(&bar, 1);
+		asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+	}
+	__syncthreads();
+	uint32_t parity = 0;
+	for (uint32_t b = blockIdx.x; b < a.nb; b += gridDim.x) {
+		if (threadIdx.x == 0) {
+			mbar_expect_tx(&bar, kSliceBytes);
+			bulk_g2s(slice, a.filter + ((uint64_t)b << kSliceLog), kSliceBytes, &bar);
+		}
+		mbar_wait(&bar, parity);
+		parity ^= 1u;
+		for (uint32_t r = warp; r < a.nparts; r += NWARPS) {
+			const uint32_t cnt = a.counts[(uint64_t)r * a.nb + b];
+			const ulonglong2 *src =
+			    reinterpret_cast<const ulonglong2 *>(a.records + ((uint64_t)r * a.nb + b) * a.cap_lines * SLOTS);
+			const uint64_t row_base = (uint64_t)r * a.rows_per_cta;
+			const uint32_t npairs = (cnt + 1) >> 1;
+			for (uint32_t j0 = 0; j0 < npairs; j0 += 32 * U) {
+				ulonglong2 v[U];
+#pragma unroll
+				for (int u = 0; u < U; u++) {
+					const uint32_t j = j0 + u * 32 + lane;
+					v[u] = make_ulonglong2(0, 0);
+					if (j < npairs) {
+						asm volatile("ld.global.nc.L1::no_allocate.v2.u64 {%0, %1}, [%2];"
+						             : "=l"(v[u].x), "=l"(v[u].y)
+						             : "l"(src + j));
+						if (2 * j + 1 >= cnt) {
+							v[u].y = 0;
+						}
+					}
+				}
+				uint64_t w[2 * U];
+#pragma unroll
+				for (int u = 0; u < U; u++) {
+					w[2 * u] = slice[(uint32_t)v[u].x & ((1u << kSliceLog) - 1u)];
+					w[2 * u + 1] = slice[(uint32_t)v[u].y & ((1u << kSliceLog) - 1u)];
+				}
+#pragma unroll
+				for (int u = 0; u < 2 * U; u++) {
+					const uint64_t rec = (u & 1) ? v[u >> 1].y : v[u >> 1].x;
+					const uint32_t lo = (uint32_t)rec, up = (uint32_t)(rec >> 32);
+					if (record2_hit(w[u], lo, up) & (up >> 31)) {
+						const uint64_t row = row_base + ((up >> 12) & 0x7ffffu);
+						atomicOr(a.bitmap + (row >> 5), 1u << (row & 31u));
+					}
+				}
+			}
+		}
+		__syncthreads();
+	}
+}
+
+static uint64_t rows_per_cta_for(uint64_t n);
+struct Part2Run {
+	Part2Args pa;
+	LookArgs la;
+	int block, kpt, slots;
+	size_t part_smem;
+	uint64_t n_total, chunk_rows;
+	int what;
+};
+template <int BLOCK, int KPT, int SLOTS>
+static void launch_part2(const Part2Run *r, const Part2Args &pa, const LookArgs &la, uint64_t cn) {
+	if (r->what != 2) {
+		CK(cudaFuncSetAttribute(part2_kernel<BLOCK, KPT, SLOTS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+		                        (int)r->part_smem));
+		part2_kernel<BLOCK, KPT, SLOTS><<<148, BLOCK, r->part_smem>>>(pa);
+	}
+	if (r->what != 1) {
+		const size_t smem = (1u << kSliceLog) * 8;
+		CK(cudaFuncSetAttribute(lookup2_kernel<1024, 4, SLOTS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+		lookup2_kernel<1024, 4, SLOTS><<<148, 1024, smem>>>(la);
+	}
+}
+static void run_part2(void *p) {
+	Part2Run *r = (Part2Run *)p;
+	for (uint64_t c0 = 0; c0 < r->n_total; c0 += r->chunk_rows) {
+		const uint64_t cn = c0 + r->chunk_rows < r->n_total ? r->chunk_rows : r->n_total - c0;
+		Part2Args pa = r->pa;
+		LookArgs la = r->la;
+		pa.keys += c0;
+		pa.n = cn;
+		pa.rows_per_cta = la.rows_per_cta = rows_per_cta_for(cn);
+		pa.bitmap = la.bitmap = r->la.bitmap + c0 / 32;
+		// the partition's direct lookups OR into the bitmap too: zero it first
+		CK(cudaMemsetAsync(la.bitmap, 0, (cn + 31) / 32 * 4));
+		const int key = r->block * 1000 + r->kpt * 10 + (r->slots == 8 ? 0 : (r->slots == 16 ? 1 : 2));
+		switch (key) {
+		case 1024 * 1000 + 40: launch_part2<1024, 4, 8>(r, pa, la, cn); break;
+		case 1024 * 1000 + 20: launch_part2<1024, 2, 8>(r, pa, la, cn); break;
+		case 512 * 1000 + 80: launch_part2<512, 8, 8>(r, pa, la, cn); break;
+		case 768 * 1000 + 40: launch_part2<768, 4, 8>(r, pa, la, cn); break;
+		case 1024 * 1000 + 41: launch_part2<1024, 4, 16>(r, pa, la, cn); break;
+		case 1024 * 1000 + 42: launch_part2<1024, 4, 4>(r, pa, la, cn); break;
+		default: printf("no such part2 variant\n"); exit(1);
+		}
+	}
+}
+
+// =========================================================================================================
+// v3 — v2's ncu capture: 203 thread-instructions per key, issue slots 84 % busy: per-step bookkeeping (flush
+// loop, retry loop, one line group per iteration) dominated.  v3 works in phases of KPP keys per lane: all claims
+// of a phase first, then ONE flush loop over every line the phase completed (16 bytes per lane: SLOTS/2 lanes per
+// line), then a retry round for the claims that found their line full.
+//   record = row-in-CTA-range:20 | hm:30 with valid in hm's spare bit 6 | sector-in-slice:14
+//   (hm = hash bits 32..61 & 0x3f3f3f3f: bits 6,7,14,15,22,23 of it are always zero)
+// =========================================================================================================
+__device__ __forceinline__ uint64_t make_record3(uint64_t h, uint32_t rowrel) {
+	const uint32_t hm = (uint32_t)(h >> 32) & 0x3f3f3f3fu;
+	const uint32_t lo = (((uint32_t)h & ((1u << kSliceLog) - 1u)) | (1u << 20)) + hm * (1u << kSliceLog);
+	const uint32_t up = (hm >> 18) + rowrel * 4096u;
+	return ((uint64_t)up << 32) | lo;
+}
+constexpr uint32_t kValid3 = 1u << 20;
+__device__ __forceinline__ void direct_lookup3(const Part2Args &a, uint32_t bucket, uint64_t rec, uint64_t row_lo) {
+	const uint32_t lo = (uint32_t)rec, up = (uint32_t)(rec >> 32);
+	const uint64_t w = a.filter[((uint64_t)bucket << kSliceLog) | (lo & ((1u << kSliceLog) - 1u))];
+	if (record2_hit(w, lo, up)) {
+		const uint64_t row = row_lo + (up >> 12);
+		atomicOr(a.bitmap + (row >> 5), 1u << (row & 31u));
+	}
+}
+
+template <int BLOCK, int KPP, int SLOTS>
+__global__ void __launch_bounds__(BLOCK, 1) part3_kernel(const Part2Args a) {
+	constexpr int NWARPS = BLOCK / 32;
+	constexpr int LPL = SLOTS / 2;     // lanes per line (16 bytes each)
+	constexpr int GROUPS = 32 / LPL;   // lines flushed per iteration
+	constexpr uint32_t SEG = 32u * KPP; // keys per phase and warp
+	extern __shared__ __align__(128) unsigned char s_dyn[];
+	uint64_t *stage = reinterpret_cast<uint64_t *>(s_dyn);                          // nb × SLOTS records
+	uint32_t *ctr = reinterpret_cast<uint32_t *>(s_dyn + (size_t)a.nb * SLOTS * 8); // {claims:16 | line:16}
+	const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+	uint32_t *flist = ctr + a.nb + warp * SEG;                                      // warp-private, ≤ SEG lines per phase
+	uint64_t *kbuf = reinterpret_cast<uint64_t *>(ctr + a.nb + NWARPS * SEG) + warp * 2 * SEG;
+	__shared__ __align__(8) uint64_t bars[NWARPS][2];
+	const uint32_t grp = lane / LPL, sub = lane % LPL;
+	uint32_t lt;
+	asm("mov.u32 %0, %%lanemask_lt;" : "=r"(lt));
+	for (uint32_t i = threadIdx.x; i < a.nb * SLOTS; i += BLOCK) {
+		stage[i] = 0;
+	}
+	for (uint32_t i = threadIdx.x; i < a.nb; i += BLOCK) {
+		ctr[i] = 0;
+	}
+	if (lane == 0) {
+		mbar_init(&bars[warp][0], 1);
+		mbar_init(&bars[warp][1], 1);
+		asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+	}
+	__syncthreads();
+	const uint64_t row_lo = (uint64_t)blockIdx.x * a.rows_per_cta;
+	const uint64_t row_hi = row_lo + a.rows_per_cta < a.n ? row_lo + a.rows_per_cta : a.n;
+	ulonglong2 *const my_records = reinterpret_cast<ulonglong2 *>(a.records + (uint64_t)blockIdx.x * a.nb * a.cap_lines * SLOTS);
+	uint32_t n_fail = 0, n_over = 0, n_direct = 0;
+	const uint64_t nrows = row_hi > row_lo ? row_hi - row_lo : 0;
+	const uint32_t nseg = (uint32_t)((nrows + SEG - 1) / SEG);
+	const uint32_t full_segs = (uint32_t)(nrows / SEG);
+
+	auto issue = [&](uint32_t seg, uint32_t buf) { // lane 0: stage segment `seg` into buffer `buf`
+		if (seg < full_segs) {
+			mbar_expect_tx(&bars[warp][buf], SEG * 8);
+			bulk_g2s(kbuf + buf * SEG, a.keys + row_lo + (uint64_t)seg * SEG, SEG * 8, &bars[warp][buf]);
+		}
+	};
+	uint32_t phase = 0;
+	if (lane == 0) {
+		issue(warp, 0);
+	}
+	uint32_t buf = 0;
+	for (uint32_t seg = warp; seg < nseg; seg += NWARPS, buf ^= 1u) {
+		if (lane == 0) {
+			issue(seg + NWARPS, buf ^ 1u);
+		}
+		const bool staged = seg < full_segs;
+		if (staged) {
+			mbar_wait(&bars[warp][buf], (phase >> buf) & 1u);
+			phase ^= 1u << buf;
+		}
+		uint64_t rec[KPP];
+		uint32_t bkt[KPP];
+		uint32_t pend = 0;
+#pragma unroll
+		for (int i = 0; i < KPP; i++) {
+			const uint32_t rowrel = seg * SEG + i * 32u + lane;
+			const bool act = rowrel < nrows;
+			uint64_t k = 0;
+			if (staged) {
+				k = kbuf[buf * SEG + i * 32u + lane];
+			} else if (act) {
+				k = a.keys[row_lo + rowrel];
+			}
+			const uint64_t h = murmur64(k);
+			rec[i] = make_record3(h, rowrel);
+			bkt[i] = ((uint32_t)h & a.smask) >> kSliceLog;
+			pend |= act ? (1u << i) : 0u;
+		}
+#pragma unroll 1
+		for (int tries = 0;; tries++) {
+			// claims of this round; flist collects the lines they complete
+			uint32_t nfl = 0;
+#pragma unroll
+			for (int i = 0; i < KPP; i++) {
+				const bool want = (pend >> i) & 1u;
+				if (tries == 0 || __any_sync(0xffffffffu, want)) {
+					uint32_t old = 0xffffu;
+					if (want) {
+						old = atomicAdd(&ctr[bkt[i]], 1u);
+					}
+					const uint32_t c = old & 0xffffu;
+					if (c < (uint32_t)SLOTS) {
+						stage[bkt[i] * SLOTS + c] = rec[i];
+						pend &= ~(1u << i);
+					}
+					const bool completes = c == (uint32_t)SLOTS - 1u;
+					const uint32_t fl = __ballot_sync(0xffffffffu, completes);
+					if (completes) {
+						flist[nfl + __popc(fl & lt)] = bkt[i] | ((old >> 16) << 12);
+					}
+					nfl += __popc(fl);
+				}
+			}
+			__syncwarp();
+			for (uint32_t it = 0; it < nfl; it += GROUPS) {
+				const uint32_t g = it + grp;
+				if (g < nfl) {
+					const uint32_t e = flist[g];
+					const uint32_t fb = e & 4095u, line = e >> 12;
+					const uint32_t saddr = (uint32_t)__cvta_generic_to_shared(stage + fb * SLOTS + sub * 2);
+					ulonglong2 v;
+					do { // a claimer of this line may still be between its atomicAdd and its store
+						asm volatile("ld.volatile.shared.v2.u64 {%0, %1}, [%2];" : "=l"(v.x), "=l"(v.y) : "r"(saddr) : "memory");
+					} while (!((uint32_t)v.x & (uint32_t)v.y & kValid3));
+					asm volatile("st.volatile.shared.v2.u64 [%0], {%1, %1};" ::"r"(saddr), "l"(0ULL) : "memory");
+					__syncwarp(LPL == 32 ? 0xffffffffu : (((1u << LPL) - 1u) << (grp * LPL)));
+					if (sub == 0) {
+						atomicExch(&ctr[fb], (line + 1u) << 16); // re-opens the line
+					}
+					if (line < a.cap_lines) {
+						ulonglong2 *dst = my_records + ((uint64_t)fb * a.cap_lines + line) * LPL + sub;
+						asm volatile("st.global.cs.v2.u64 [%0], {%1, %2};" ::"l"(dst), "l"(v.x), "l"(v.y) : "memory");
+					} else { // skew: the (CTA, bucket) region is full — look the records up on the spot
+						direct_lookup3(a, fb, v.x, row_lo);
+						direct_lookup3(a, fb, v.y, row_lo);
+						n_over += 2;
+					}
+				}
+			}
+			__syncwarp(); // flist is rewritten by the next round
+			if (!__any_sync(0xffffffffu, pend != 0u)) {
+				break;
+			}
+			n_fail += __popc(pend);
+			if (tries == 2) { // hot bucket = hot sectors: look up on the spot
+#pragma unroll
+				for (int i = 0; i < KPP; i++) {
+					if ((pend >> i) & 1u) {
+						direct_lookup3(a, bkt[i], rec[i], row_lo);
+						n_direct++;
+					}
+				}
+				break;
+			}
+		}
+	}
+	__syncthreads();
+	// partial lines
+	for (uint32_t b = threadIdx.x; b < a.nb; b += BLOCK) {
+		const uint32_t c = ctr[b] & 0xffffu; // < SLOTS: every full line has been flushed and re-opened
+		uint32_t l = ctr[b] >> 16;
+		uint32_t total = (l < a.cap_lines ? l : a.cap_lines) * SLOTS;
+		for (uint32_t j = 0; j < c && j < (uint32_t)SLOTS; j++) {
+			const uint64_t v = stage[b * SLOTS + j];
+			if (l < a.cap_lines) {
+				a.records[((uint64_t)blockIdx.x * a.nb + b) * a.cap_lines * SLOTS + (uint64_t)l * SLOTS + j] = v;
+				total++;
+			} else {
+				direct_lookup3(a, b, v, row_lo);
+				n_over++;
+			}
+		}
+		a.counts[(uint64_t)blockIdx.x * a.nb + b] = total;
+	}
+	n_fail = __reduce_add_sync(0xffffffffu, n_fail);
+	n_over = __reduce_add_sync(0xffffffffu, n_over);
+	n_direct = __reduce_add_sync(0xffffffffu, n_direct);
+	if (lane == 0) {
+		if (n_over) {
+			atomicAdd(a.stats, (unsigned long long)n_over);
+		}
+		if (n_fail) {
+			atomicAdd(a.stats + 1, (unsigned long long)n_fail);
+		}
+		if (n_direct) {
+			atomicAdd(a.stats + 2, (unsigned long long)n_direct);
+		}
+	}
+}
+
+// lookup v3: a warp's work items = (region, round of 32·U record pairs); the loads of item i+1 are issued before
+// item i is looked up, and the first item's loads before the slice has arrived.
+template <int BLOCK, int U, int SLOTS>
+__global__ void __launch_bounds__(BLOCK, 1) lookup3_kernel(const LookArgs a) {
+	extern __shared__ __align__(128) unsigned char s_dyn[];
+	uint64_t *slice = reinterpret_cast<uint64_t *>(s_dyn);
+	__shared__ __align__(8) uint64_t bar;
+	constexpr uint32_t kSliceBytes = (1u << kSliceLog) * 8u;
+	const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+	constexpr uint32_t NWARPS = BLOCK / 32;
+	if (threadIdx.x == 0) {
+		mbar_init(&bar, 1);
+		asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+	}
+	__syncthreads();
+	uint32_t parity = 0;
+	for (uint32_t b = blockIdx.x; b < a.nb; b += gridDim.x) {
+		if (threadIdx.x == 0) {
+			mbar_expect_tx(&bar, kSliceBytes);
+			bulk_g2s(slice, a.filter + ((uint64_t)b << kSliceLog), kSliceBytes, &bar);
+		}
+		// this warp's regions: warp, warp + NWARPS, ...; lane k holds the count of the k-th one
+		const uint32_t my_r = warp + lane * NWARPS;
+		const uint32_t my_cnt = my_r < a.nparts ? a.counts[(uint64_t)my_r * a.nb + b] : 0u;
+		uint32_t k = 0, j0 = 0; // next item to load
+		uint32_t cnt_k = __shfl_sync(0xffffffffu, my_cnt, 0);
+		auto load_item = [&](ulonglong2 (&v)[U], uint32_t &r_out) -> bool {
+			while (k < 32u && warp + k * NWARPS < a.nparts && j0 >= ((cnt_k + 1u) >> 1)) { // skip finished / empty regions
+				k++;
+				j0 = 0;
+				cnt_k = __shfl_sync(0xffffffffu, my_cnt, k & 31u);
+			}
+			const uint32_t r = warp + k * NWARPS;
+			if (k >= 32u || r >= a.nparts) {
+				return false;
+			}
+			const ulonglong2 *src =
+			    reinterpret_cast<const ulonglong2 *>(a.records + ((uint64_t)r * a.nb + b) * a.cap_lines * SLOTS);
+			const uint32_t npairs = (cnt_k + 1u) >> 1;
+#pragma unroll
+			for (int u = 0; u < U; u++) {
+				const uint32_t j = j0 + u * 32 + lane;
+				v[u] = make_ulonglong2(0, 0);
+				if (j < npairs) {
+					asm volatile("ld.global.nc.L1::no_allocate.v2.u64 {%0, %1}, [%2];"
+					             : "=l"(v[u].x), "=l"(v[u].y)
+					             : "l"(src + j));
+					if (2 * j + 1 >= cnt_k) {
+						v[u].y = 0;
+					}
+				}
+			}
+			r_out = r;
+			j0 += 32 * U;
+			return true;
+		};
+		ulonglong2 cur[U], nxt[U];
+		uint32_t r_cur = 0, r_nxt = 0;
+		bool have = load_item(cur, r_cur);
+		mbar_wait(&bar, parity);
+		parity ^= 1u;
+		while (have) {
+			const bool have_nxt = load_item(nxt, r_nxt);
+			const uint64_t row_base = (uint64_t)r_cur * a.rows_per_cta;
+			uint64_t w[2 * U];
+#pragma unroll
+			for (int u = 0; u < U; u++) {
+				w[2 * u] = slice[(uint32_t)cur[u].x & ((1u << kSliceLog) - 1u)];
+				w[2 * u + 1] = slice[(uint32_t)cur[u].y & ((1u << kSliceLog) - 1u)];
+			}
+#pragma unroll
+			for (int u = 0; u < 2 * U; u++) {
+				const uint64_t rec = (u & 1) ? cur[u >> 1].y : cur[u >> 1].x;
+				const uint32_t lo = (uint32_t)rec, up = (uint32_t)(rec >> 32);
+				if (record2_hit(w[u], lo, up) && (lo & kValid3)) {
+					const uint64_t row = row_base + (up >> 12);
+					atomicOr(a.bitmap + (row >> 5), 1u << (row & 31u));
+				}
+			}
+#pragma unroll
+			for (int u = 0; u < U; u++) {
+				cur[u] = nxt[u];
+			}
+			r_cur = r_nxt;
+			have = have_nxt;
+		}
+		__syncthreads();
+	}
+}
+
+struct Part3Run {
+	Part2Args pa;
+	LookArgs la;
+	int block, kpp, slots;
+	size_t part_smem;
+	uint64_t n_total, chunk_rows;
+	int what;
+};
+template <int BLOCK, int KPP, int SLOTS>
+static void launch_part3(const Part3Run *r, const Part2Args &pa, const LookArgs &la) {
+	if (r->what != 2) {
+		CK(cudaFuncSetAttribute(part3_kernel<BLOCK, KPP, SLOTS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+		                        (int)r->part_smem));
+		part3_kernel<BLOCK, KPP, SLOTS><<<148, BLOCK, r->part_smem>>>(pa);
+	}
+	if (r->what != 1) {
+		const size_t smem = (1u << kSliceLog) * 8;
+		CK(cudaFuncSetAttribute(lookup3_kernel<1024, 4, SLOTS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+		lookup3_kernel<1024, 4, SLOTS><<<148, 1024, smem>>>(la);
+	}
+}
+static void run_part3(void *p) {
+	Part3Run *r = (Part3Run *)p;
+	for (uint64_t c0 = 0; c0 < r->n_total; c0 += r->chunk_rows) {
+		const uint64_t cn = c0 + r->chunk_rows < r->n_total ? r->chunk_rows : r->n_total - c0;
+		Part2Args pa = r->pa;
+		LookArgs la = r->la;
+		pa.keys += c0;
+		pa.n = cn;
+		pa.rows_per_cta = la.rows_per_cta = rows_per_cta_for(cn);
+		pa.bitmap = la.bitmap = r->la.bitmap + c0 / 32;
+		CK(cudaMemsetAsync(la.bitmap, 0, (cn + 31) / 32 * 4));
+		const int key = r->block * 1000 + r->kpp * 10 + (r->slots == 8 ? 0 : 1);
+		switch (key) {
+		case 1024 * 1000 + 40: launch_part3<1024, 4, 8>(r, pa, la); break;
+		case 1024 * 1000 + 20: launch_part3<1024, 2, 8>(r, pa, la); break;
+		case 1024 * 1000 + 80: launch_part3<1024, 8, 8>(r, pa, la); break;
+		case 768 * 1000 + 40: launch_part3<768, 4, 8>(r, pa, la); break;
+		case 1024 * 1000 + 41: launch_part3<1024, 4, 16>(r, pa, la); break;
+		default: printf("no such part3 variant\n"); exit(1);
+		}
+	}
+}
+
 static float time_kernel(int reps, void (*fn)(void *), void *arg) {
 	cudaEvent_t e0, e1;
 	CK(cudaEventCreate(&e0));
@@ -522,6 +1184,85 @@ int main(int argc, char **argv) {
 			}
 		}
 		return 0;
+	}
+	if (!strcmp(mode, "part2") || !strcmp(mode, "part3")) {
+		const bool v3 = !strcmp(mode, "part3");
+		const int log_sectors = argc > 2 ? atoi(argv[2]) : 25;
+		const int block = argc > 3 ? atoi(argv[3]) : 1024;
+		const int kpt = argc > 4 ? atoi(argv[4]) : 8;
+		const uint64_t n = argc > 5 ? strtoull(argv[5], nullptr, 10) : 1000000000ULL;
+		const int chunk_log = argc > 6 ? atoi(argv[6]) : 26;
+		const int density = argc > 7 ? atoi(argv[7]) : 1;
+		const int slots = argc > 8 ? atoi(argv[8]) : 8;
+		const int skew = argc > 9 ? atoi(argv[9]) : 0; // keys &= (2^skew - 1) when > 0: few distinct keys
+		const uint64_t chunk_rows = 1ULL << chunk_log;
+		const uint64_t S = 1ULL << log_sectors;
+		const uint32_t nb = (uint32_t)(S >> kSliceLog);
+		const uint32_t nparts = 148;
+		const uint64_t rows_per_cta = rows_per_cta_for(chunk_rows < n ? chunk_rows : n);
+		if (rows_per_cta > (v3 ? (1u << 20) : (1u << 19))) {
+			printf("chunk too large for the row field\n");
+			return 1;
+		}
+		const double mean = (double)rows_per_cta / nb;
+		const uint32_t cap_lines = (uint32_t)((mean + 6.0 * sqrt(mean) + 2.0 * slots) / slots) + 1;
+		printf("part2 n=%llu chunk=2^%d S=2^%d (%llu MiB) buckets=%u slots=%d rows/cta=%llu mean/bucket=%.1f cap_lines=%u "
+		       "scratch=%.2f GB block=%d kpt=%d density=%d skew=%d\n",
+		       (unsigned long long)n, chunk_log, log_sectors, (unsigned long long)(S * 8 >> 20), nb, slots,
+		       (unsigned long long)rows_per_cta, mean, cap_lines, (double)nparts * nb * cap_lines * slots * 8 / 1e9, block,
+		       kpt, density, skew);
+		uint64_t *keys, *filter, *records;
+		uint32_t *counts, *bitmap, *bitmap_ref;
+		unsigned long long *stats;
+		const uint64_t bitmap_words = (n + 31) / 32 + 64;
+		CK(cudaMalloc(&keys, n * 8));
+		CK(cudaMalloc(&filter, S * 8));
+		CK(cudaMalloc(&records, (uint64_t)nparts * nb * cap_lines * slots * 8));
+		CK(cudaMalloc(&counts, (uint64_t)nparts * nb * 4));
+		CK(cudaMalloc(&bitmap, bitmap_words * 4));
+		CK(cudaMalloc(&bitmap_ref, bitmap_words * 4));
+		CK(cudaMalloc(&stats, 8 * 8));
+		CK(cudaMemset(stats, 0, 8 * 8));
+		gen_keys<<<148 * 8, 256>>>(keys, n);
+		if (skew > 0) {
+			mask_keys<<<148 * 8, 256>>>(keys, n, (1ULL << skew) - 1);
+		}
+		fill_filter<<<148 * 8, 256>>>(filter, S, density);
+		CK(cudaDeviceSynchronize());
+		Part2Run r;
+		r.pa = Part2Args {keys, n, rows_per_cta, (uint32_t)(S - 1), nb, cap_lines, records, counts, filter, bitmap, stats};
+		r.la = LookArgs {filter, nb, nparts, cap_lines, rows_per_cta, records, counts, bitmap};
+		r.block = block;
+		r.kpt = kpt;
+		r.slots = slots;
+		r.part_smem = (size_t)nb * slots * 8 + (size_t)nb * 4 + (block / 32) * 128 + (size_t)(block / 32) * 2 * 32 * kpt * 8;
+		r.n_total = n;
+		r.chunk_rows = chunk_rows;
+		Part3Run r3;
+		r3.pa = r.pa; r3.la = r.la; r3.block = block; r3.kpp = kpt; r3.slots = slots; r3.n_total = n; r3.chunk_rows = chunk_rows;
+		r3.part_smem = (size_t)nb * slots * 8 + (size_t)nb * 4 + (size_t)(block / 32) * 32 * kpt * 4 +
+		               (size_t)(block / 32) * 2 * 32 * kpt * 8;
+		void (*fn)(void *) = v3 ? run_part3 : run_part2;
+		void *arg = v3 ? (void *)&r3 : (void *)&r;
+		unsigned long long hstats[8];
+		r.what = r3.what = 1;
+		const float ms_part = time_kernel(3, fn, arg);
+		CK(cudaMemcpy(hstats, stats, sizeof(hstats), cudaMemcpyDeviceToHost));
+		printf("partition  %.3f ms  %.1f Gkeys/s  (16 B/key: %.2f TB/s)  per run: overflow=%.0f failed claims=%.0f (%.3f %%) "
+		       "direct=%.0f\n",
+		       ms_part, n / ms_part / 1e6, 16.0 * n / ms_part / 1e9, hstats[0] / 4.0, hstats[1] / 4.0,
+		       100.0 * hstats[1] / 4.0 / n, hstats[2] / 4.0);
+		r.what = r3.what = 0;
+		const float ms_both = time_kernel(3, fn, arg);
+		printf("both       %.3f ms  %.1f Gkeys/s  (lookup ~ %.3f ms)\n", ms_both, n / ms_both / 1e6, ms_both - ms_part);
+		ref_probe<<<148 * 8, 256>>>(keys, filter, S - 1, n & ~31ULL, bitmap_ref);
+		CK(cudaMemset(stats, 0, 8 * 8));
+		cmp_words<<<148 * 4, 256>>>(bitmap, bitmap_ref, n / 32, stats + 2, stats + 3);
+		CK(cudaDeviceSynchronize());
+		CK(cudaMemcpy(hstats, stats, sizeof(hstats), cudaMemcpyDeviceToHost));
+		printf("check      %llu differing bitmap words, %llu hits (%.2f %%)  %s\n", hstats[2], hstats[3],
+		       100.0 * hstats[3] / n, hstats[2] == 0 ? "OK" : "MISMATCH");
+		return hstats[2] == 0 ? 0 : 1;
 	}
 	const int log_sectors = argc > 2 ? atoi(argv[2]) : 25;
 	const int block = argc > 3 ? atoi(argv[3]) : 1024;
