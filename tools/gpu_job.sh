@@ -43,6 +43,19 @@ part3)      # v3 prototype sweep
 	done
 	cat $out
 	;;
+part4)      # v4 prototype sweep
+	out=gpurun_out/part4_${1:-r2f}.txt
+	: > $out
+	# sectors block kpp rows log2_chunk density slots skew
+	for cfg in "25 1024 4 1000000000 27 1 8 0" "25 1024 2 1000000000 27 1 8 0" "25 1024 8 1000000000 27 1 8 0" "25 768 4 1000000000 27 1 8 0" \
+	           "25 1024 4 1000000000 27 0 8 0" "25 1024 4 1000000000 26 1 8 0" \
+	           "24 1024 4 1000000000 27 1 16 0" "24 1024 4 1000000000 27 1 8 0" "25 1024 4 200000000 27 1 8 4" "25 1024 4 200000000 27 1 8 14" \
+	           "25 1024 4 16777216 27 1 8 0"; do
+		timeout -s KILL 90 tools/part_lab part4 $cfg >> $out 2>&1
+		echo "rc=$?" >> $out
+	done
+	cat $out
+	;;
 ncu_lab)    # full ncu capture of one prototype kernel: ncu_lab <tag> <kernel regex> <part_lab args...>
 	tag=$1; rx=$2; shift 2
 	timeout -s KILL 120 tools/part_lab "$@" > gpurun_out/ncu_lab_${tag}_plain.log 2>&1 &&

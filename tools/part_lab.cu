@@ -1077,6 +1077,416 @@ static void run_part3(void *p) {
 	}
 }
 
+// =========================================================================================================
+// v4 — v3's source-level ncu page: the claim of one key costs 42 SASS instructions (generic→shared address
+// conversions, reconvergence barriers around every predicated shared access) and the retry round re-runs the
+// whole claim block.  v4: every shared access is inline PTX on a 32-bit shared address with a predicate (no
+// branch), a failed claim is CARRIED into the next phase (one extra claim slot per phase) instead of retried,
+// and one launch covers all row chunks (regions per (chunk, CTA, bucket)); the lookup kernel is bucket-outer /
+// chunk-inner, so a slice is loaded once and the bitmap window in flight stays a chunk or two wide.
+// =========================================================================================================
+struct Part4Args {
+	const uint64_t *keys;
+	uint64_t n;
+	uint64_t chunk_rows;   // rows per chunk (multiple of 148·512 is not required; rows_per_cta covers it)
+	uint64_t rows_per_cta; // rows of a chunk handled by one CTA (multiple of 512)
+	uint32_t nchunks;
+	uint32_t smask;
+	uint32_t nb;
+	uint32_t cap_lines;
+	uint64_t *records; // [bucket][chunk·148 + cta][cap_lines][SLOTS]
+	uint32_t *counts;  // [bucket][chunk·148 + cta]
+	const uint64_t *filter;
+	uint32_t *bitmap;
+	unsigned long long *stats; // [0] region overflow, [1] carried claims, [2] direct lookups
+};
+
+__device__ __forceinline__ uint32_t atoms_add1_pred(uint32_t saddr, bool want) { // returns 0xffff when !want
+	uint32_t old = 0xffffu;
+	asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %2, 0;\n\t@p atom.shared.add.u32 %0, [%1], 1;\n\t}"
+	             : "+r"(old)
+	             : "r"(saddr), "r"((uint32_t)want)
+	             : "memory");
+	return old;
+}
+__device__ __forceinline__ void sts64_pred(uint32_t saddr, uint32_t lo, uint32_t hi, bool pred) {
+	asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %3, 0;\n\t@p st.shared.v2.u32 [%0], {%1, %2};\n\t}" ::"r"(saddr), "r"(lo),
+	             "r"(hi), "r"((uint32_t)pred)
+	             : "memory");
+}
+__device__ __forceinline__ void sts32_pred(uint32_t saddr, uint32_t v, bool pred) {
+	asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %2, 0;\n\t@p st.shared.u32 [%0], %1;\n\t}" ::"r"(saddr), "r"(v),
+	             "r"((uint32_t)pred)
+	             : "memory");
+}
+__device__ __forceinline__ uint32_t lds32(uint32_t saddr) {
+	uint32_t v;
+	asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(saddr) : "memory");
+	return v;
+}
+__device__ __forceinline__ uint2 lds64(uint32_t saddr) {
+	uint2 v;
+	asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(saddr) : "memory");
+	return v;
+}
+__device__ __forceinline__ void direct_lookup4(const Part4Args &a, uint32_t bucket, uint32_t lo, uint32_t up,
+                                               uint64_t row_lo) {
+	const uint64_t w = a.filter[((uint64_t)bucket << kSliceLog) | (lo & ((1u << kSliceLog) - 1u))];
+	if (record2_hit(w, lo, up)) {
+		const uint64_t row = row_lo + (up >> 12);
+		atomicOr(a.bitmap + (row >> 5), 1u << (row & 31u));
+	}
+}
+
+template <int BLOCK, int KPP, int SLOTS>
+__global__ void __launch_bounds__(BLOCK, 1) part4_kernel(const Part4Args a) {
+	constexpr int NWARPS = BLOCK / 32;
+	constexpr int LPL = SLOTS / 2;      // lanes per line (16 bytes each)
+	constexpr int GROUPS = 32 / LPL;    // lines flushed per iteration
+	constexpr uint32_t SEG = 32u * KPP; // keys per phase and warp
+	constexpr uint32_t LINE_BYTES = SLOTS * 8;
+	extern __shared__ __align__(128) unsigned char s_dyn[];
+	__shared__ __align__(8) uint64_t bars[NWARPS][2];
+	const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+	const uint32_t grp = lane / LPL, sub = lane % LPL;
+	// shared layout: [stage nb×LINE_BYTES][ctr nb×4][flist NWARPS×(SEG+32)×4][kbuf NWARPS×2×SEG×8]
+	const uint32_t stage_base = (uint32_t)__cvta_generic_to_shared(s_dyn);
+	const uint32_t ctr_base = stage_base + a.nb * LINE_BYTES;
+	const uint32_t flist_base = ctr_base + a.nb * 4u + warp * (SEG + 32u) * 4u;
+	const uint32_t kbuf_base = ctr_base + a.nb * 4u + NWARPS * (SEG + 32u) * 4u + warp * 2u * SEG * 8u;
+	unsigned char *const kbuf_gen = s_dyn + (kbuf_base - stage_base);
+	uint32_t lt;
+	asm("mov.u32 %0, %%lanemask_lt;" : "=r"(lt));
+	for (uint32_t i = threadIdx.x; i < a.nb * SLOTS; i += BLOCK) {
+		reinterpret_cast<uint64_t *>(s_dyn)[i] = 0;
+	}
+	for (uint32_t i = threadIdx.x; i < a.nb; i += BLOCK) {
+		reinterpret_cast<uint32_t *>(s_dyn + (size_t)a.nb * LINE_BYTES)[i] = 0;
+	}
+	if (lane == 0) {
+		mbar_init(&bars[warp][0], 1);
+		mbar_init(&bars[warp][1], 1);
+		asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+	}
+	__syncthreads();
+	const uint32_t nq = a.nchunks * gridDim.x;
+	const uint64_t bucket_stride = (uint64_t)nq * a.cap_lines * LINE_BYTES; // bytes between two buckets' region sets
+	uint32_t n_carry = 0, n_over = 0, n_direct = 0;
+	uint32_t phase = 0; // bit b: parity to wait for on buffer b
+
+	for (uint32_t chunk = 0; chunk < a.nchunks; chunk++) {
+		const uint64_t chunk_lo = (uint64_t)chunk * a.chunk_rows;
+		const uint64_t chunk_hi = chunk_lo + a.chunk_rows < a.n ? chunk_lo + a.chunk_rows : a.n;
+		const uint64_t row_lo = chunk_lo + (uint64_t)blockIdx.x * a.rows_per_cta;
+		const uint64_t row_hi = row_lo + a.rows_per_cta < chunk_hi ? row_lo + a.rows_per_cta : chunk_hi;
+		const uint64_t nrows = row_hi > row_lo ? row_hi - row_lo : 0;
+		const uint32_t nseg = (uint32_t)((nrows + SEG - 1) / SEG);
+		const uint32_t full_segs = (uint32_t)(nrows / SEG);
+		const uint32_t q = chunk * gridDim.x + blockIdx.x;
+		unsigned char *const my_records = reinterpret_cast<unsigned char *>(a.records) + (uint64_t)q * a.cap_lines * LINE_BYTES;
+
+		auto issue = [&](uint32_t seg, uint32_t buf) { // lane 0: stage segment `seg` into buffer `buf`
+			if (seg < full_segs) {
+				mbar_expect_tx(&bars[warp][buf], SEG * 8);
+				bulk_g2s(kbuf_gen + buf * SEG * 8, a.keys + row_lo + (uint64_t)seg * SEG, SEG * 8, &bars[warp][buf]);
+			}
+		};
+		// carried key (a claim that found its line full): claimed again as an extra slot of the next phase
+		bool c_valid = false;
+		uint32_t c_b = 0, c_lo = 0, c_up = 0;
+		uint32_t nfl = 0;
+		auto claim = [&](const uint32_t b, const uint32_t lo, const uint32_t up, const bool want) -> bool {
+			const uint32_t old = atoms_add1_pred(ctr_base + b * 4u, want);
+			const uint32_t c = old & 0xffffu;
+			const bool ok = c < (uint32_t)SLOTS;
+			sts64_pred(stage_base + b * LINE_BYTES + c * 8u, lo, up, ok);
+			const bool completes = c == (uint32_t)SLOTS - 1u;
+			const uint32_t fl = __ballot_sync(0xffffffffu, completes);
+			sts32_pred(flist_base + (nfl + __popc(fl & lt)) * 4u, b | ((old >> 16) << 12), completes);
+			nfl += __popc(fl);
+			return want && !ok;
+		};
+
+		if (lane == 0) {
+			issue(warp, 0);
+		}
+		uint32_t buf = 0;
+		for (uint32_t seg = warp; seg < nseg; seg += NWARPS, buf ^= 1u) {
+			if (lane == 0) {
+				issue(seg + NWARPS, buf ^ 1u);
+			}
+			const bool staged = seg < full_segs;
+			if (staged) {
+				mbar_wait(&bars[warp][buf], (phase >> buf) & 1u);
+				phase ^= 1u << buf;
+			}
+			nfl = 0;
+			{ // the carried key first
+				const bool failed = claim(c_b, c_lo, c_up, c_valid);
+				n_carry += failed ? 1u : 0u;
+				c_valid = failed;
+			}
+#pragma unroll
+			for (int i = 0; i < KPP; i++) {
+				const uint32_t rowrel = seg * SEG + i * 32u + lane;
+				const bool act = rowrel < nrows;
+				uint64_t k = 0;
+				if (staged) {
+					const uint2 kk = lds64(kbuf_base + buf * SEG * 8u + (i * 32u + lane) * 8u);
+					k = ((uint64_t)kk.y << 32) | kk.x;
+				} else if (act) {
+					k = a.keys[row_lo + rowrel];
+				}
+				const uint64_t h = murmur64(k);
+				const uint32_t hm = (uint32_t)(h >> 32) & 0x3f3f3f3fu;
+				const uint32_t lo = (((uint32_t)h & ((1u << kSliceLog) - 1u)) | kValid3) + hm * (1u << kSliceLog);
+				const uint32_t up = (hm >> 18) + rowrel * 4096u;
+				const uint32_t b = ((uint32_t)h & a.smask) >> kSliceLog;
+				const bool failed = claim(b, lo, up, act);
+				if (failed) {
+					if (!c_valid) {
+						c_valid = true;
+						c_b = b;
+						c_lo = lo;
+						c_up = up;
+					} else { // two failures in one lane and phase: rare — look up on the spot
+						direct_lookup4(a, b, lo, up, row_lo);
+						n_direct++;
+					}
+				}
+			}
+			__syncwarp();
+			for (uint32_t it = 0; it < nfl; it += GROUPS) {
+				const uint32_t g = it + grp;
+				if (g < nfl) {
+					const uint32_t e = lds32(flist_base + g * 4u);
+					const uint32_t fb = e & 4095u, line = e >> 12;
+					const uint32_t saddr = stage_base + fb * LINE_BYTES + sub * 16u;
+					uint4 v;
+					do { // a claimer of this line may still be between its atomicAdd and its store
+						asm volatile("ld.volatile.shared.v4.u32 {%0, %1, %2, %3}, [%4];"
+						             : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+						             : "r"(saddr)
+						             : "memory");
+					} while (!(v.x & v.z & kValid3));
+					asm volatile("st.volatile.shared.v4.u32 [%0], {%1, %1, %1, %1};" ::"r"(saddr), "r"(0u) : "memory");
+					__syncwarp(LPL == 32 ? 0xffffffffu : (((1u << LPL) - 1u) << (grp * LPL)));
+					if (sub == 0) { // re-opens the line
+						uint32_t dummy;
+						asm volatile("atom.shared.exch.b32 %0, [%1], %2;"
+						             : "=r"(dummy)
+						             : "r"(ctr_base + fb * 4u), "r"((line + 1u) << 16)
+						             : "memory");
+					}
+					if (line < a.cap_lines) {
+						unsigned char *dst = my_records + fb * bucket_stride + line * LINE_BYTES + sub * 16u;
+						asm volatile("st.global.cs.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(dst), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w)
+						             : "memory");
+					} else { // skew: the (CTA, bucket) region is full — look the records up on the spot
+						direct_lookup4(a, fb, v.x, v.y, row_lo);
+						direct_lookup4(a, fb, v.z, v.w, row_lo);
+						n_over += 2;
+					}
+				}
+			}
+			__syncwarp(); // flist is rewritten by the next phase
+		}
+		if (c_valid) { // the chunk's last carried key
+			direct_lookup4(a, c_b, c_lo, c_up, row_lo);
+			n_direct++;
+		}
+		__syncthreads();
+		// partial lines of this chunk; the stage and the counters start the next chunk empty
+		for (uint32_t b = threadIdx.x; b < a.nb; b += BLOCK) {
+			uint32_t *ctr = reinterpret_cast<uint32_t *>(s_dyn + (size_t)a.nb * LINE_BYTES) + b;
+			uint64_t *st = reinterpret_cast<uint64_t *>(s_dyn) + b * SLOTS;
+			const uint32_t c = *ctr & 0xffffu; // < SLOTS: every full line has been flushed and re-opened
+			const uint32_t l = *ctr >> 16;
+			uint32_t total = (l < a.cap_lines ? l : a.cap_lines) * SLOTS;
+			for (uint32_t j = 0; j < c && j < (uint32_t)SLOTS; j++) {
+				const uint64_t v = st[j];
+				st[j] = 0;
+				if (l < a.cap_lines) {
+					*reinterpret_cast<uint64_t *>(my_records + b * bucket_stride + l * LINE_BYTES + j * 8u) = v;
+					total++;
+				} else {
+					direct_lookup4(a, b, (uint32_t)v, (uint32_t)(v >> 32), row_lo);
+					n_over++;
+				}
+			}
+			*ctr = 0;
+			a.counts[(uint64_t)b * nq + q] = total;
+		}
+		__syncthreads();
+	}
+	n_carry = __reduce_add_sync(0xffffffffu, n_carry);
+	n_over = __reduce_add_sync(0xffffffffu, n_over);
+	n_direct = __reduce_add_sync(0xffffffffu, n_direct);
+	if (lane == 0) {
+		if (n_over) {
+			atomicAdd(a.stats, (unsigned long long)n_over);
+		}
+		if (n_carry) {
+			atomicAdd(a.stats + 1, (unsigned long long)n_carry);
+		}
+		if (n_direct) {
+			atomicAdd(a.stats + 2, (unsigned long long)n_direct);
+		}
+	}
+}
+
+struct Look4Args {
+	const uint64_t *filter;
+	uint32_t nb;
+	uint32_t nparts;  // partition CTAs
+	uint32_t nchunks;
+	uint32_t cap_lines;
+	uint64_t chunk_rows, rows_per_cta;
+	const uint64_t *records;
+	const uint32_t *counts;
+	uint32_t *bitmap;
+};
+
+// bucket-outer: the slice arrives once per bucket; a warp's items are the regions q = warp, warp + NWARPS, … of
+// the bucket's nchunks·nparts regions (chunk-major, so all warps move through the chunks together and the part of
+// the bitmap being written stays a chunk or two wide); item i+1's records are loaded before item i is looked up.
+template <int BLOCK, int U, int SLOTS>
+__global__ void __launch_bounds__(BLOCK, 1) lookup4_kernel(const Look4Args a) {
+	extern __shared__ __align__(128) unsigned char s_dyn[];
+	uint64_t *slice = reinterpret_cast<uint64_t *>(s_dyn);
+	__shared__ __align__(8) uint64_t bar;
+	constexpr uint32_t kSliceBytes = (1u << kSliceLog) * 8u;
+	const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+	constexpr uint32_t NWARPS = BLOCK / 32;
+	if (threadIdx.x == 0) {
+		mbar_init(&bar, 1);
+		asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+	}
+	__syncthreads();
+	const uint32_t nq = a.nchunks * a.nparts;
+	const uint32_t nitems = warp < nq ? (nq - warp + NWARPS - 1) / NWARPS : 0; // this warp's regions per bucket
+	uint32_t parity = 0;
+	for (uint32_t b = blockIdx.x; b < a.nb; b += gridDim.x) {
+		if (threadIdx.x == 0) {
+			mbar_expect_tx(&bar, kSliceBytes);
+			bulk_g2s(slice, a.filter + ((uint64_t)b << kSliceLog), kSliceBytes, &bar);
+		}
+		const uint32_t *cnts = a.counts + (uint64_t)b * nq;
+		const uint64_t *recs = a.records + (uint64_t)b * nq * a.cap_lines * SLOTS;
+		uint32_t item = 0, j0 = 0; // next load position: region item, pair offset j0
+		uint32_t cnt_reg = 0, cnt_k = 0;
+		auto fetch_cnt = [&]() { // counts of items [item & ~31, +32) live in the lanes
+			if ((item & 31u) == 0u) {
+				const uint32_t it = item + lane;
+				cnt_reg = it < nitems ? cnts[warp + it * NWARPS] : 0u;
+			}
+			cnt_k = __shfl_sync(0xffffffffu, cnt_reg, item & 31u);
+		};
+		if (nitems) {
+			fetch_cnt();
+		}
+		auto load_item = [&](ulonglong2 (&v)[U], uint32_t &q_out) -> bool {
+			while (item < nitems && j0 >= ((cnt_k + 1u) >> 1)) { // region finished (or empty): next one
+				item++;
+				j0 = 0;
+				if (item < nitems) {
+					fetch_cnt();
+				}
+			}
+			if (item >= nitems) {
+				return false;
+			}
+			const uint32_t q = warp + item * NWARPS;
+			const ulonglong2 *src = reinterpret_cast<const ulonglong2 *>(recs + (uint64_t)q * a.cap_lines * SLOTS);
+			const uint32_t npairs = (cnt_k + 1u) >> 1;
+#pragma unroll
+			for (int u = 0; u < U; u++) {
+				const uint32_t j = j0 + u * 32 + lane;
+				v[u] = make_ulonglong2(0, 0);
+				if (j < npairs) {
+					asm volatile("ld.global.nc.L1::no_allocate.v2.u64 {%0, %1}, [%2];"
+					             : "=l"(v[u].x), "=l"(v[u].y)
+					             : "l"(src + j));
+					if (2 * j + 1 >= cnt_k) {
+						v[u].y = 0;
+					}
+				}
+			}
+			q_out = q;
+			j0 += 32 * U;
+			return true;
+		};
+		ulonglong2 cur[U], nxt[U];
+		uint32_t q_cur = 0, q_nxt = 0;
+		bool have = load_item(cur, q_cur);
+		mbar_wait(&bar, parity);
+		parity ^= 1u;
+		while (have) {
+			const bool have_nxt = load_item(nxt, q_nxt);
+			const uint32_t chunk = q_cur / a.nparts, part = q_cur - chunk * a.nparts;
+			const uint64_t row_base = (uint64_t)chunk * a.chunk_rows + (uint64_t)part * a.rows_per_cta;
+			uint64_t w[2 * U];
+#pragma unroll
+			for (int u = 0; u < U; u++) {
+				w[2 * u] = slice[(uint32_t)cur[u].x & ((1u << kSliceLog) - 1u)];
+				w[2 * u + 1] = slice[(uint32_t)cur[u].y & ((1u << kSliceLog) - 1u)];
+			}
+#pragma unroll
+			for (int u = 0; u < 2 * U; u++) {
+				const uint64_t rec = (u & 1) ? cur[u >> 1].y : cur[u >> 1].x;
+				const uint32_t lo = (uint32_t)rec, up = (uint32_t)(rec >> 32);
+				if (record2_hit(w[u], lo, up) && (lo & kValid3)) {
+					const uint64_t row = row_base + (up >> 12);
+					atomicOr(a.bitmap + (row >> 5), 1u << (row & 31u));
+				}
+			}
+#pragma unroll
+			for (int u = 0; u < U; u++) {
+				cur[u] = nxt[u];
+			}
+			q_cur = q_nxt;
+			have = have_nxt;
+		}
+		__syncthreads();
+	}
+}
+
+struct Part4Run {
+	Part4Args pa;
+	Look4Args la;
+	int block, kpp, slots;
+	size_t part_smem;
+	uint64_t bitmap_bytes;
+	int what;
+};
+template <int BLOCK, int KPP, int SLOTS>
+static void launch_part4(const Part4Run *r) {
+	if (r->what != 2) {
+		CK(cudaMemsetAsync(r->pa.bitmap, 0, r->bitmap_bytes)); // the partition's direct lookups OR into it
+		CK(cudaFuncSetAttribute(part4_kernel<BLOCK, KPP, SLOTS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+		                        (int)r->part_smem));
+		part4_kernel<BLOCK, KPP, SLOTS><<<148, BLOCK, r->part_smem>>>(r->pa);
+	}
+	if (r->what != 1) {
+		const size_t smem = (1u << kSliceLog) * 8;
+		CK(cudaFuncSetAttribute(lookup4_kernel<1024, 4, SLOTS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+		lookup4_kernel<1024, 4, SLOTS><<<148, 1024, smem>>>(r->la);
+	}
+}
+static void run_part4(void *p) {
+	Part4Run *r = (Part4Run *)p;
+	const int key = r->block * 1000 + r->kpp * 10 + (r->slots == 8 ? 0 : 1);
+	switch (key) {
+	case 1024 * 1000 + 40: launch_part4<1024, 4, 8>(r); break;
+	case 1024 * 1000 + 20: launch_part4<1024, 2, 8>(r); break;
+	case 1024 * 1000 + 80: launch_part4<1024, 8, 8>(r); break;
+	case 768 * 1000 + 40: launch_part4<768, 4, 8>(r); break;
+	case 512 * 1000 + 40: launch_part4<512, 4, 8>(r); break;
+	case 1024 * 1000 + 41: launch_part4<1024, 4, 16>(r); break;
+	default: printf("no such part4 variant\n"); exit(1);
+	}
+}
+
 static float time_kernel(int reps, void (*fn)(void *), void *arg) {
 	cudaEvent_t e0, e1;
 	CK(cudaEventCreate(&e0));
@@ -1184,6 +1594,84 @@ int main(int argc, char **argv) {
 			}
 		}
 		return 0;
+	}
+	if (!strcmp(mode, "part4")) {
+		const int log_sectors = argc > 2 ? atoi(argv[2]) : 25;
+		const int block = argc > 3 ? atoi(argv[3]) : 1024;
+		const int kpp = argc > 4 ? atoi(argv[4]) : 4;
+		const uint64_t n = argc > 5 ? strtoull(argv[5], nullptr, 10) : 1000000000ULL;
+		const int chunk_log = argc > 6 ? atoi(argv[6]) : 27;
+		const int density = argc > 7 ? atoi(argv[7]) : 1;
+		const int slots = argc > 8 ? atoi(argv[8]) : 8;
+		const int skew = argc > 9 ? atoi(argv[9]) : 0;
+		const uint64_t chunk_rows = 1ULL << chunk_log;
+		const uint64_t S = 1ULL << log_sectors;
+		const uint32_t nb = (uint32_t)(S >> kSliceLog);
+		const uint32_t nparts = 148;
+		const uint32_t nchunks = (uint32_t)((n + chunk_rows - 1) / chunk_rows);
+		const uint64_t rows_per_cta = rows_per_cta_for(chunk_rows < n ? chunk_rows : n);
+		if (rows_per_cta > (1u << 20)) {
+			printf("chunk too large for the row field\n");
+			return 1;
+		}
+		const double mean = (double)rows_per_cta / nb;
+		const uint32_t cap_lines = (uint32_t)((mean + 6.0 * sqrt(mean) + 2.0 * slots) / slots) + 1;
+		const uint64_t nq = (uint64_t)nchunks * nparts;
+		printf("part4 n=%llu chunks=%u x 2^%d S=2^%d (%llu MiB) buckets=%u slots=%d rows/cta=%llu mean/bucket=%.1f cap_lines=%u "
+		       "scratch=%.2f GB block=%d kpp=%d density=%d skew=%d\n",
+		       (unsigned long long)n, nchunks, chunk_log, log_sectors, (unsigned long long)(S * 8 >> 20), nb, slots,
+		       (unsigned long long)rows_per_cta, mean, cap_lines, (double)nq * nb * cap_lines * slots * 8 / 1e9, block, kpp,
+		       density, skew);
+		uint64_t *keys, *filter, *records;
+		uint32_t *counts, *bitmap, *bitmap_ref;
+		unsigned long long *stats;
+		const uint64_t bitmap_words = (n + 31) / 32 + 64;
+		CK(cudaMalloc(&keys, n * 8));
+		CK(cudaMalloc(&filter, S * 8));
+		CK(cudaMalloc(&records, nq * nb * cap_lines * slots * 8));
+		CK(cudaMalloc(&counts, nq * nb * 4));
+		CK(cudaMalloc(&bitmap, bitmap_words * 4));
+		CK(cudaMalloc(&bitmap_ref, bitmap_words * 4));
+		CK(cudaMalloc(&stats, 8 * 8));
+		CK(cudaMemset(stats, 0, 8 * 8));
+		gen_keys<<<148 * 8, 256>>>(keys, n);
+		if (skew > 0) {
+			mask_keys<<<148 * 8, 256>>>(keys, n, (1ULL << skew) - 1);
+		}
+		fill_filter<<<148 * 8, 256>>>(filter, S, density);
+		CK(cudaDeviceSynchronize());
+		Part4Run r;
+		r.pa = Part4Args {keys, n, chunk_rows, rows_per_cta, nchunks, (uint32_t)(S - 1), nb, cap_lines, records, counts,
+		                  filter, bitmap, stats};
+		r.la = Look4Args {filter, nb, nparts, nchunks, cap_lines, chunk_rows, rows_per_cta, records, counts, bitmap};
+		r.block = block;
+		r.kpp = kpp;
+		r.slots = slots;
+		r.part_smem = (size_t)nb * slots * 8 + (size_t)nb * 4 + (size_t)(block / 32) * (32 * kpp + 32) * 4 +
+		              (size_t)(block / 32) * 2 * 32 * kpp * 8;
+		r.bitmap_bytes = bitmap_words * 4;
+		unsigned long long hstats[8];
+		r.what = 1;
+		const float ms_part = time_kernel(3, run_part4, &r);
+		CK(cudaMemcpy(hstats, stats, sizeof(hstats), cudaMemcpyDeviceToHost));
+		printf("partition  %.3f ms  %.1f Gkeys/s  (16 B/key: %.2f TB/s)  per run: overflow=%.0f carried claims=%.0f (%.3f %%) "
+		       "direct=%.0f\n",
+		       ms_part, n / ms_part / 1e6, 16.0 * n / ms_part / 1e9, hstats[0] / 4.0, hstats[1] / 4.0,
+		       100.0 * hstats[1] / 4.0 / n, hstats[2] / 4.0);
+		r.what = 2;
+		const float ms_look = time_kernel(3, run_part4, &r);
+		printf("lookup     %.3f ms  %.1f Gkeys/s  (8 B/key: %.2f TB/s)\n", ms_look, n / ms_look / 1e6, 8.0 * n / ms_look / 1e9);
+		r.what = 0;
+		const float ms_both = time_kernel(3, run_part4, &r);
+		printf("both       %.3f ms  %.1f Gkeys/s\n", ms_both, n / ms_both / 1e6);
+		ref_probe<<<148 * 8, 256>>>(keys, filter, S - 1, n & ~31ULL, bitmap_ref);
+		CK(cudaMemset(stats, 0, 8 * 8));
+		cmp_words<<<148 * 4, 256>>>(bitmap, bitmap_ref, n / 32, stats + 2, stats + 3);
+		CK(cudaDeviceSynchronize());
+		CK(cudaMemcpy(hstats, stats, sizeof(hstats), cudaMemcpyDeviceToHost));
+		printf("check      %llu differing bitmap words, %llu hits (%.2f %%)  %s\n", hstats[2], hstats[3],
+		       100.0 * hstats[3] / n, hstats[2] == 0 ? "OK" : "MISMATCH");
+		return hstats[2] == 0 ? 0 : 1;
 	}
 	if (!strcmp(mode, "part2") || !strcmp(mode, "part3")) {
 		const bool v3 = !strcmp(mode, "part3");
