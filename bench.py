@@ -53,10 +53,15 @@ def parse_args():
                     "at ~1.71 GHz, 114.5 instead of 121 Gkeys/s; profiles/bench_r1h_sustained.json)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
-    ap.add_argument("--cpu-probe-sample", type=int, default=200_000_000)
+    ap.add_argument("--cpu-probe-sample", type=int, default=200_000_000, help="probe rows of the cpu_baseline leg "
+                    "inside the GPU arm (a bounded sample); --impl reference always probes ALL probe rows every step")
+    ap.add_argument("--no-sweep", action="store_true", help="skip detail.sweep (1 %% / 50 %% members, the 16 MiB "
+                    "L2-resident companion, config 3); N=1 only, outside the timed steps")
+    ap.add_argument("--no-config3", action="store_true")
+    ap.add_argument("--sustain-s", type=float, default=2.0, help="detail.sustained: after the timed steps, this many "
+                    "seconds of untimed back-to-back steps, then the same K steps timed again (power-capped clocks)")
     ap.add_argument("--merge", default="auto", choices=["auto", "peer", "allgather"])
-    ap.add_argument("--sweep", action="store_true", help="also time probe at 1 %% and 50 %% selectivity and the "
-                    "L2-resident companion filter (reported under 'detail'; N=1 only)")
+    ap.add_argument("--sweep", action="store_true", help="(default since round 2; kept for old command lines)")
     return ap.parse_args()
 
 
@@ -146,9 +151,10 @@ class ClockSampler:
 # ---------------------------------------------------------------------------------------------------------
 # CPU arm: the reference's own loops (oracle/_ref) or the oracle port, on the host cores
 # ---------------------------------------------------------------------------------------------------------
-def cpu_run(args, steps, warmup):
-    """Returns (value Gkeys/s for the full workload shape, info dict).  One step = build ALL build rows into a
-    fresh filter + probe a bounded sample of the probe column; the probe time is scaled to the full row count."""
+def cpu_run(args, steps, warmup, full_probe):
+    """Returns (value Gkeys/s, seconds per step, info dict).  One step = build ALL build rows into a fresh filter +
+    probe the probe column: all of it (full_probe, the --impl reference arm: nothing is extrapolated) or its first
+    --cpu-probe-sample rows scaled to the full row count (the bounded cpu_baseline leg of the GPU arm)."""
     import numpy as np
     import oracle_lib
     oracle = oracle_lib.oracle()
@@ -157,31 +163,38 @@ def cpu_run(args, steps, warmup):
     eng = ref if ref is not None else oracle
     cores = os.cpu_count() or 1
     n, m = args.build_rows, args.probe_rows
-    ms = min(m, args.cpu_probe_sample)
+    ms = m if full_probe else min(m, args.cpu_probe_sample)
     keys = oracle.synth_build_keys(0, n).view(np.int64)
     probe = oracle.synth_probe_keys(0, ms, n, args.sel_ppm).view(np.int64)
     S = oracle.num_sectors(n)
-    tb, tp, found = [], [], 0
+    tb, tp, tw, found = [], [], [], 0
     for it in range(warmup + steps):
         words = np.zeros(S, dtype=np.uint64)
         t0 = time.perf_counter()
         b = eng.bench_build(words, keys, cores)
         p, found = eng.bench_probe(words, probe, cores)
-        _ = time.perf_counter() - t0
+        wall = time.perf_counter() - t0
         if it >= warmup:
             tb.append(b)
             tp.append(p)
+            tw.append(wall)
     tb_med = sorted(tb)[len(tb) // 2]
     tp_med = sorted(tp)[len(tp) // 2]
-    t_full = tb_med + tp_med * (m / ms)
-    value = (n + m) / t_full / 1e9
-    info = {"value": value, "unit": UNIT, "cores": cores, "kind": kind,
-            "sample": f"build all {n} keys on {cores} threads into one shared {S * 8 >> 20} MiB filter (median "
-                      f"{tb_med:.3f} s) + probe the first {ms} of {m} probe rows (median {tp_med:.3f} s, scaled x"
-                      f"{m / ms:.1f}); 2048-row chunks, relaxed fetch_or, private selection buffers",
+    if full_probe:
+        t_step = sum(tw) / len(tw)  # wall clock of a whole step, averaged over the K steps actually run
+        sample = (f"every step builds all {n} keys on {cores} threads into one shared {S * 8 >> 20} MiB filter (median "
+                  f"{tb_med:.3f} s) and probes ALL {m} probe rows (median {tp_med:.3f} s); nothing extrapolated; "
+                  "2048-row chunks, relaxed fetch_or, private selection buffers")
+    else:
+        t_step = tb_med + tp_med * (m / ms)
+        sample = (f"build all {n} keys on {cores} threads into one shared {S * 8 >> 20} MiB filter (median "
+                  f"{tb_med:.3f} s) + probe the first {ms} of {m} probe rows (median {tp_med:.3f} s, scaled x"
+                  f"{m / ms:.1f}); 2048-row chunks, relaxed fetch_or, private selection buffers")
+    value = (n + m) / t_step / 1e9
+    info = {"value": value, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample,
             "build_gkeys_s": n / tb_med / 1e9, "probe_gkeys_s": ms / tp_med / 1e9,
-            "probe_sample_found": int(found)}
-    return value, t_full, info
+            "probe_rows_timed": int(ms), "probe_found": int(found)}
+    return value, t_step, info
 
 
 def run_reference(args):
@@ -189,13 +202,13 @@ def run_reference(args):
     if rank != 0:
         return 0
     steps, warmup = max(1, args.steps), max(0, args.warmup)
-    value, t_full, info = cpu_run(args, steps, warmup)
+    value, t_full, info = cpu_run(args, steps, warmup, full_probe=True)
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
         "steps": steps, "warmup": warmup,
         "ms_per_step": t_full * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "u64", "data": "synthetic",
-        "config": workload_config(args, 1), "cpu_baseline": info,
+        "config": workload_config(args, max(1, args.gpus)), "cpu_baseline": info,
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -204,12 +217,24 @@ def run_reference(args):
     return 0
 
 
+def filter_sectors(rows):
+    """S of BloomFilter::Initialize (duckdb/src/planner/filter/bloom_filter.cpp:7-9,17-19) — plain arithmetic, so that
+    both arms can describe the workload without loading anything."""
+    bits = max(512, 12 * rows)
+    p2 = 1 << (bits - 1).bit_length()
+    return min(p2 >> 6, 1 << 26)
+
+
 def workload_config(args, world):
+    """The SAME dict from both arms (the driver compares them)."""
+    S = filter_sectors(args.build_rows)
+    merge = "none" if world == 1 else ("peer" if args.merge == "auto" else args.merge)
     return {"workload": "config 2: single-key int64 bloom build 100M keys / probe 1B keys, synthetic uniform "
                         "(SURVEY §8d splitmix64 generators)",
             "build_rows_total": args.build_rows, "probe_rows_per_gpu": args.probe_rows,
-            "member_fraction_ppm": args.sel_ppm, "filter_sectors": None, "filter_mib": None,
+            "member_fraction_ppm": args.sel_ppm, "filter_sectors": S, "filter_mib": (S * 8) >> 20,
             "sharding": f"build column row-range sharded over {world} rank(s), OR-merged; probe shard-local",
+            "merge": merge,
             "l2_policy": "inputs larger than L2 (8 GB key column + 256 MiB filter per step); no flush needed"}
 
 
@@ -349,6 +374,34 @@ def run_b200(args):
     if not ordered or members != members_kept:
         raise SystemExit(f"bench parity check failed on rank {rank}: {parity}")
 
+    # ---- bit-exactness of the (merged) filter, not timed: FNV-1a-64 of the words (SURVEY §8c recipe) must be the
+    # same on every rank and equal to a filter built on THIS GPU alone from all n build keys (SURVEY §8e:
+    # "N-shard filter bytes == 1-shard filter bytes") ----
+    fnv = sb.bf.Checksum()
+    if world > 1:
+        dk_all = torch.empty(n, dtype=torch.int64, device=dev)
+        rpt.synth_build_keys(dk_all, 0, n, device=local_rank, stream=sh)
+        single = rpt.PTBloomFilter(local_rank).Initialize(n)
+        single.Insert(rpt.device_col(dk_all, rpt.INT64), n, sh)
+        torch.cuda.synchronize()
+        fnv_single = single.Checksum()
+        single.close()
+        del dk_all
+        halves = torch.tensor([fnv >> 32, fnv & 0xffffffff, fnv_single >> 32, fnv_single & 0xffffffff],
+                              dtype=torch.int64, device=dev)
+        lo_t, hi_t = halves.clone(), halves.clone()
+        dist.all_reduce(lo_t, op=dist.ReduceOp.MIN)
+        dist.all_reduce(hi_t, op=dist.ReduceOp.MAX)
+        ranks_agree = bool((lo_t == hi_t).all().item())
+    else:
+        fnv_single, ranks_agree = fnv, True
+    parity["filter_fnv1a"] = f"0x{fnv:016x}"
+    parity["filter_fnv1a_single_gpu_build"] = f"0x{fnv_single:016x}"
+    parity["ranks_agree"] = ranks_agree
+    if fnv != fnv_single or not ranks_agree:
+        raise SystemExit(f"bench parity check failed on rank {rank}: merged filter checksum 0x{fnv:016x}, single-GPU "
+                         f"build 0x{fnv_single:016x}, ranks agree: {ranks_agree}")
+
     # ---- roofline of the dominant kernel (probe) ----
     peak, peak_src = load_peaks()
     algo_bytes = 8 * m + 4 * found + F
@@ -377,8 +430,29 @@ def run_b200(args):
               "probe_gkeys_s": world * m / (probe_ms_max * 1e-3) / 1e9,
               "found_rank0": found, "filter_sectors": S, "filter_mib": F >> 20, "parity": parity}
 
-    # ---- optional sweep (N=1): other selectivities, L2-resident companion ----
-    if args.sweep and world == 1:
+    # ---- sustained figure: the timed region above is a fraction of a second (burst clocks); the same K steps after
+    # --sustain-s seconds of back-to-back untimed steps run in the power/clock state of a long job ----
+    if args.sustain_s > 0:
+        spin = int(min(2000, max(1, args.sustain_s / max(ms_per_step * 1e-3, 1e-4))))
+        sampler2 = ClockSampler(local_rank)
+        for _ in range(spin):
+            step()
+        barrier()
+        sampler2.start()
+        s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s0.record(stream)
+        for _ in range(args.steps):
+            step()
+        s1.record(stream)
+        barrier()
+        clocks2 = sampler2.stop()
+        sus_ms = max_over_ranks(s0.elapsed_time(s1)) / args.steps
+        detail["sustained"] = {"value": keys_per_step / (sus_ms * 1e-3) / 1e9, "unit": UNIT, "ms_per_step": sus_ms,
+                               "untimed_spin_steps": spin, "clocks": clocks2}
+
+    # ---- sweep (N=1, outside the timed steps): BASELINE config 2's other selectivities, the L2-resident companion
+    # (SURVEY §8d "2-L2"), and config 3 ----
+    if world == 1 and not args.no_sweep:
         detail["sweep"] = sweep(rpt, torch, dev, local_rank, sb, dp, dsel, dfound, n, m, sh, stream, peak)
 
     # ---- e2e: host buffers through the C ABI, copies inside the timed region ----
@@ -387,19 +461,25 @@ def run_b200(args):
         e2e = run_e2e(args, rpt, torch, dist, dev, local_rank, world, rank, sb, dk, dp, n, m, n_local, sh, barrier,
                       max_over_ranks, found)
 
+    if world == 1 and not args.no_sweep and not args.no_config3:
+        del dk, dp, dsel
+        torch.cuda.empty_cache()
+        detail["config3"] = config3(rpt, torch, dev, local_rank, sh, stream, peak)
+        dk = dp = dsel = None
+        torch.cuda.empty_cache()
+
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
         del dk, dp, dsel
         torch.cuda.empty_cache()
         try:
-            _, _, cpu = cpu_run(args, steps=1, warmup=0)
+            _, _, cpu = cpu_run(args, steps=1, warmup=0, full_probe=False)
         except Exception as exc:  # the baseline must not take the GPU numbers down with it
             cpu = {"value": None, "unit": UNIT, "cores": os.cpu_count(), "kind": "port", "sample": f"failed: {exc}"}
 
     if rank == 0:
         cfg = workload_config(args, world)
-        cfg["filter_sectors"], cfg["filter_mib"] = S, F >> 20
-        cfg["merge"] = sb.merge if world > 1 else "none"
+        assert cfg["filter_sectors"] == S and cfg["merge"] == (sb.merge if world > 1 else "none")
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
@@ -453,6 +533,135 @@ def sweep(rpt, torch, dev, local_rank, sb, dp, dsel, dfound, n, m, sh, stream, p
     small.close()
     rpt.synth_probe_keys(dp, 0, m, n, 100_000, device=local_rank, stream=sh)
     torch.cuda.synchronize()
+    return out
+
+
+def config3(rpt, torch, dev, local_rank, sh, stream, peak, n=50_000_000, m=500_000_000, ppm=100_000):
+    """BASELINE config 3 as the reference executes it: a two-column join key (int64 k1, varchar k2 =
+    decimal text of k1) is TWO independent single-column filters (physical_create_bf.cpp:221-227); a USE_BF probes
+    filter 1 with the whole chunk and filter 2 with filter 1's survivors (physical_use_bf.cpp:137-180).  Run twice:
+    est_rows = n (right-sized) and est_rows = n/5, where the resize rule of Finalize (physical_create_bf.cpp:386-406)
+    fires and both filters are re-allocated and re-hashed (src/bloom_filter.cpp:34-58) — the reference has no fold."""
+    import ctypes as C
+    out = {"build_rows": n, "probe_rows": m, "member_fraction_ppm": ppm,
+           "shape": "2 x single-column filter (int64, varchar decimal text); filter 2 probes filter 1's survivors"}
+    BATCH = 200_000_000  # the VARCHAR layout has 32-bit offsets: a call carries < 4 GiB of string bytes
+    k1 = torch.empty(n, dtype=torch.int64, device=dev)
+    p1 = torch.empty(m, dtype=torch.int64, device=dev)
+    rpt.synth_build_keys(k1, 0, n, device=local_rank, stream=sh)
+    rpt.synth_probe_keys(p1, 0, m, n, ppm, device=local_rank, stream=sh)
+    torch.cuda.synchronize()
+    ko, kb, kbytes = rpt.synth_decimal_text(k1)
+    c_k1 = rpt.device_col(k1, rpt.INT64)
+    c_k2 = rpt.device_col(ko, rpt.VARCHAR, aux=kb, aux_bytes=kbytes, data_len=n)
+    batches, pbytes = [], 0
+    for r0 in range(0, m, BATCH):
+        r1 = min(r0 + BATCH, m)
+        po, pb, nb = rpt.synth_decimal_text(p1[r0:r1])
+        batches.append((r0, r1 - r0, rpt.device_col(p1[r0:r1], rpt.INT64),
+                        rpt.device_col(po, rpt.VARCHAR, aux=pb, aux_bytes=nb, data_len=r1 - r0), nb))
+        pbytes += nb
+    torch.cuda.synchronize()
+    out["probe_batches"] = [b[1] for b in batches]
+    sel1 = torch.empty(BATCH, dtype=torch.int32, device=dev)
+    sel2 = torch.empty(m, dtype=torch.int32, device=dev)
+    found = torch.zeros(2, dtype=torch.int64, device=dev)
+    f1, f2 = rpt.PTBloomFilter(local_rank), rpt.PTBloomFilter(local_rank)
+    for label, est in (("est_rows_exact", n), ("est_rows_under_5x", n // 5)):
+        f1.Initialize(est)
+        f2.Initialize(est)
+
+        def build():
+            f1.Reset(est, sh)
+            f2.Reset(est, sh)
+            f1.Insert(c_k1, n, sh)
+            f2.Insert(c_k2, n, sh)
+            r1 = f1.Finalize(n, c_k1, n, sh)   # resize rule; rebuilds from the whole column when it fires
+            r2 = f2.Finalize(n, c_k2, n, sh)
+            return r1, r2
+
+        def probe(times=None):
+            n1_total = n2_total = 0
+            for r0, mb, c_p1, c_p2, _ in batches:
+                ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+                ev[0].record(stream)
+                f1.LookupSelDevice(c_p1, mb, sel1, found[0:1], sh)
+                ev[1].record(stream)
+                n1 = int(found[0].item())   # the operator learns the survivor count between the two filters
+                rpt._check(rpt.lib().rpt_bf_filter_sel(f2._h, C.byref(c_p2.raw), sel1.data_ptr(), n1,
+                                                       sel2[n2_total:].data_ptr(), found[1:2].data_ptr(), rpt.MEM_DEVICE,
+                                                       sh))
+                ev[2].record(stream)
+                n2 = int(found[1].item())
+                sel2[n2_total:n2_total + n2] += r0     # batch-relative → column row ids (not timed as probe work)
+                if times is not None:
+                    torch.cuda.synchronize()
+                    times[0] += ev[0].elapsed_time(ev[1])
+                    times[1] += ev[1].elapsed_time(ev[2])
+                n1_total += n1
+                n2_total += n2
+            return n1_total, n2_total
+
+        build()
+        probe()
+        torch.cuda.synchronize()
+        reps = 3
+        tb = 0.0
+        tp = [0.0, 0.0]
+        for _ in range(reps):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
+            r1, r2 = build()
+            e1.record(stream)
+            torch.cuda.synchronize()
+            tb += e0.elapsed_time(e1) / reps
+            n1, n2 = probe(tp)
+        tp1, tp2 = tp[0] / reps, tp[1] / reps
+        s2 = sel2[:n2].long() & 0xFFFFFFFF
+        members = p1 >= 0
+        ok = bool((s2[1:] > s2[:-1]).all().item()) and int(members[s2].sum().item()) == int(members.sum().item())
+        del members, s2
+        if not ok:
+            raise SystemExit(f"config 3 ({label}): selection not ascending or a member row was dropped")
+        F1, F2 = f1.num_sectors * 8, f2.num_sectors * 8
+        nbat = len(batches)
+        b1 = 8 * m + 4 * n1 + nbat * F1                       # SURVEY §8d: keys + selection + filter once per call
+        b2 = 4 * n1 + 4 * n1 + int(pbytes * (n1 / m)) + 4 * n2 + nbat * F2   # in-selection + offsets + bytes of the survivors
+        bb = 8 * n + 4 * (n + 1) + kbytes + 2 * (F1 + F2)
+        out[label] = {
+            "est_rows": est, "rebuilt": [bool(r1), bool(r2)], "filter_mib": [F1 >> 20, F2 >> 20],
+            "filter_fnv1a": [f"0x{f1.Checksum():016x}", f"0x{f2.Checksum():016x}"],
+            "build_ms": tb, "build_gkeys_s": 2 * n / tb / 1e6,
+            "probe_int64_ms": tp1, "probe_int64_gkeys_s": m / tp1 / 1e6, "found_filter1": n1,
+            "probe_varchar_survivors_ms": tp2, "found_both": n2,
+            "probe_gkeys_s": m / (tp1 + tp2) / 1e6,
+            "roofline": {"bound": "hbm", "unit": "GB/s", "peak": peak,
+                         "probe_int64": {"algorithmic_bytes": b1, "achieved": b1 / tp1 / 1e6, "frac": b1 / tp1 / 1e6 / peak},
+                         "probe_varchar_survivors": {"algorithmic_bytes": b2, "achieved": b2 / tp2 / 1e6,
+                                                     "frac": b2 / tp2 / 1e6 / peak},
+                         "build": {"algorithmic_bytes": bb, "achieved": bb / tb / 1e6, "frac": bb / tb / 1e6 / peak}},
+        }
+    # the varchar column probed on its own, all m rows (the staged string-hash kernel + the flat pre-hashed path)
+    def probe_varchar():
+        total = 0
+        for r0, mb, _, c_p2, _ in batches:
+            f2.LookupSelDevice(c_p2, mb, sel2, found[1:2], sh)
+            total += int(found[1].item())
+        return total
+    probe_varchar()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    e0.record(stream)
+    for _ in range(3):
+        nv = probe_varchar()
+    e1.record(stream)
+    torch.cuda.synchronize()
+    tv = e0.elapsed_time(e1) / 3
+    bv = 4 * (m + len(batches)) + pbytes + 4 * nv + len(batches) * f2.num_sectors * 8
+    out["probe_varchar_all_rows"] = {"ms": tv, "gkeys_s": m / tv / 1e6, "found": nv, "algorithmic_bytes": bv,
+                                     "achieved_gbs": bv / tv / 1e6, "frac": bv / tv / 1e6 / peak}
+    f1.close()
+    f2.close()
     return out
 
 

@@ -102,6 +102,8 @@ _SIGNATURES = {
     "rpt_abf_device_blocks": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p)]),
     "rpt_abf_sync": (C.c_int, [C.c_void_p]),
     "rpt_abf_launch_count": (C.c_int, [C.c_void_p, C.POINTER(C.c_longlong)]),
+    "rpt_bf_checksum": (C.c_int, [C.c_void_p, C.POINTER(C.c_uint64)]),
+    "rpt_bf_words_generation": (C.c_int, [C.c_void_p, C.POINTER(C.c_uint64)]),
     "rpt_synth_build_keys": (C.c_int, [C.c_void_p, C.c_uint64, C.c_uint64, C.c_int, C.c_void_p]),
     "rpt_synth_probe_keys": (C.c_int, [C.c_void_p, C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint32, C.c_int,
                                        C.c_void_p]),
@@ -355,6 +357,14 @@ class PTBloomFilter:
         _check(lib().rpt_bf_export_words(self._h, words.ctypes.data, words.shape[0]))
         return words
 
+    def Checksum(self):
+        """FNV-1a-64 over the filter words (SURVEY §8c recipe)."""
+        return self._get(lib().rpt_bf_checksum, C.c_uint64)
+
+    @property
+    def words_generation(self):
+        return self._get(lib().rpt_bf_words_generation, C.c_uint64)
+
     def ImportWords(self, words):
         words = np.ascontiguousarray(words, dtype=np.uint64)
         _check(lib().rpt_bf_import_words(self._h, words.ctypes.data, words.shape[0]))
@@ -509,3 +519,31 @@ class PinnedArray:
 
 
 from .sharded import ShardedBloomFilter, shard_range  # noqa: E402,F401
+
+
+def synth_decimal_text(x):
+    """SURVEY §8(d) config 3's second key column: k2 = decimal text of k1 (1–19 bytes).  int64 torch tensor on a CUDA
+    device (bit 63 is masked off) → Arrow utf8 layout on the same device: (int32 offsets[n+1], uint8 bytes, total
+    bytes).  Digit column by digit column, to bound the temporaries; benchmark / test input only."""
+    import torch
+    x = x & 0x7fffffffffffffff
+    n = x.numel()
+    ndig = torch.ones(n, dtype=torch.int64, device=x.device)
+    p = 10
+    for _ in range(18):
+        ndig += (x >= p).to(torch.int64)
+        p *= 10
+    offsets = torch.zeros(n + 1, dtype=torch.int64, device=x.device)
+    torch.cumsum(ndig, 0, out=offsets[1:])
+    total = int(offsets[-1].item())
+    if total >= 2**32:
+        raise RptError("string bytes exceed the 32-bit offsets of the VARCHAR layout")
+    blob = torch.zeros(total + 8, dtype=torch.uint8, device=x.device)
+    p = 1
+    for d in range(19):  # digit d counted from the right goes to offsets[i+1] - 1 - d
+        has = ndig > d
+        pos = (offsets[1:] - 1 - d)[has]
+        blob[pos] = ((x[has] // p) % 10 + 48).to(torch.uint8)
+        p *= 10
+        del has, pos
+    return offsets.to(torch.int32), blob, total

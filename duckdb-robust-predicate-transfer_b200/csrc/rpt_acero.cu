@@ -381,7 +381,7 @@ static cudaError_t launch_probe_t(const DeviceInfo &dev, const DevCols &cols, ui
 	if (num_blocks <= kSmemBlocksMax && count >= (1u << 20)) {
 		auto kern = abf_probe_bitmap_kernel<FLAT64, true>;
 		const size_t smem = num_blocks * sizeof(uint64_t);
-		cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
+		cudaError_t e = ensure_max_dyn_smem<abf_probe_bitmap_kernel<FLAT64, true>>(dev);
 		if (e != cudaSuccess) {
 			return e;
 		}

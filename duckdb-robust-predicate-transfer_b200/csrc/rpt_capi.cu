@@ -15,6 +15,8 @@
 #include <cstring>
 #include <ctime>
 #include <mutex>
+#include <new>
+#include <stdexcept>
 #include <string>
 #include <type_traits>
 #include <vector>
@@ -46,6 +48,20 @@ static int set_error(const char *fmt, ...) {
 			return set_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, __LINE__);              \
 		}                                                                                                              \
 	} while (0)
+
+// No C++ exception crosses the C ABI: allocation failures inside a body (std::vector, new) come back as a status.
+template <class F>
+static int guarded(F &&body) noexcept {
+	try {
+		return body();
+	} catch (const std::bad_alloc &) {
+		return set_error("out of host memory");
+	} catch (const std::exception &e) {
+		return set_error("internal error: %s", e.what());
+	} catch (...) {
+		return set_error("internal error: unknown exception");
+	}
+}
 
 #define RPT_TRY(expr)                                                                                                  \
 	do {                                                                                                               \
@@ -97,6 +113,7 @@ struct rpt_bf {
 	uint64_t num_sectors = 0;
 	uint64_t sized_for_rows = 0;
 	uint64_t *words = nullptr;
+	uint64_t words_capacity = 0;       // sectors allocated (grow-only: a re-size to fewer sectors reuses the buffer)
 	cudaStream_t stream = nullptr;     // handle's own stream
 	// host-column pipeline (RPT_MEM_HOST calls): uploads, kernels and downloads run on three streams chained by
 	// events, with kPipeSlots chunks in flight; everything here is created once per handle and reused
@@ -115,6 +132,7 @@ struct rpt_bf {
 	std::atomic<int> has_data {0};
 	std::atomic<int> finalized {0};
 	std::atomic<long long> launches {0};
+	std::atomic<uint64_t> words_generation {0}; // bumped whenever `words` is reallocated (stale peer mappings)
 	// fused column range (rpt_bf_minmax_*)
 	MinMaxState *mm_dev = nullptr;
 	int mm_type = 0;
@@ -154,13 +172,6 @@ static int fill_device_info(int device, DeviceInfo *out) {
 		return set_error("device %d is sm_%d%d; librpt_gpu is built for sm_100a (B200) only", device, prop.major,
 		                 prop.minor);
 	}
-	// scratch comes from the stream-ordered allocator: keep freed blocks in the pool across synchronisations
-	// instead of returning them to the driver (the default release threshold is 0)
-	cudaMemPool_t pool;
-	if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) {
-		uint64_t keep = ~0ULL;
-		cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
-	}
 	// L2 set-aside for persisting (evict_last) lines: the filter slice of a pass lives there, out of reach of the
 	// key stream.  RPT_L2_PERSIST_MIB overrides (0 = leave the device default).
 	{
@@ -179,6 +190,29 @@ static int fill_device_info(int device, DeviceInfo *out) {
 	out->sm_count = prop.multiProcessorCount;
 	out->l2_bytes = prop.l2CacheSize;
 	out->smem_optin = prop.sharedMemPerBlockOptin;
+	return 0;
+}
+
+// Scratch and staging come from a PRIVATE stream-ordered pool per device (freed blocks stay in the pool across
+// synchronisations: release threshold = max) — the host application's default pool is left alone.
+static int library_pool(int device, cudaMemPool_t *out) {
+	static std::mutex mu;
+	static cudaMemPool_t pools[64] = {};
+	std::lock_guard<std::mutex> lock(mu);
+	if (device < 0 || device >= 64) {
+		return set_error("device %d out of range", device);
+	}
+	if (!pools[device]) {
+		cudaMemPoolProps props = {};
+		props.allocType = cudaMemAllocationTypePinned;
+		props.handleTypes = cudaMemHandleTypeNone;
+		props.location.type = cudaMemLocationTypeDevice;
+		props.location.id = device;
+		RPT_CUDA(cudaMemPoolCreate(&pools[device], &props));
+		uint64_t keep = ~0ULL;
+		RPT_CUDA(cudaMemPoolSetAttribute(pools[device], cudaMemPoolAttrReleaseThreshold, &keep));
+	}
+	*out = pools[device];
 	return 0;
 }
 
@@ -241,14 +275,26 @@ static int validate_cols(const rpt_col_t *cols, int ncols, uint64_t count, int *
 struct Staged {
 	cudaStream_t stream = nullptr;      // allocations and uploads are ordered on this stream
 	cudaStream_t free_stream = nullptr; // releases are ordered on this one (the consumer); default = stream
+	// set once the consumer stream has been made to wait for the uploads (cudaStreamWaitEvent on `uploaded`):
+	// until then a release on free_stream could overtake copies still in flight on `stream`
+	bool handed_over = false;
+	int device = -1;
 	std::vector<void *> dev_allocs;
 	~Staged() {
+		if (free_stream && free_stream != stream && !handed_over && !dev_allocs.empty()) {
+			cudaStreamSynchronize(stream); // error path: the uploads finish before their buffers are released
+		}
 		for (void *p : dev_allocs) {
 			cudaFreeAsync(p, free_stream ? free_stream : stream);
 		}
 	}
 	int alloc(void **out, size_t bytes) {
-		RPT_CUDA(cudaMallocAsync(out, bytes ? bytes : 8, stream));
+		if (device < 0) {
+			RPT_CUDA(cudaGetDevice(&device));
+		}
+		cudaMemPool_t pool;
+		RPT_TRY(library_pool(device, &pool));
+		RPT_CUDA(cudaMallocFromPoolAsync(out, bytes ? bytes : 8, pool, stream));
 		dev_allocs.push_back(*out);
 		return 0;
 	}
@@ -306,21 +352,39 @@ static bool any_sel(const rpt_col_t *cols, int ncols) {
 }
 
 // duckdb::string_t (string_type.hpp:24): uint32 length, then 12 inlined bytes, or a 4-byte prefix
-// followed by a pointer.  Gathers entries [e0, e1) into Arrow-style offsets + bytes.
-static void gather_string_t(const void *data, uint64_t e0, uint64_t e1, std::vector<uint32_t> *offsets,
+// followed by a pointer.  Gathers entries [e0, e1) into Arrow-style offsets + bytes.  The payload of an entry is
+// read only when the entry is valid (validity bit set, or no validity) AND referenced (`used` bit set, or no
+// selection): DuckDB leaves the string_t of a NULL row undefined, and the reference never looks at it
+// (TightLoopHash: `is_null ? NULL_HASH : Hash(input)`, vector_hash.cpp:43-61).  Skipped entries get length 0.
+static void gather_string_t(const void *data, uint64_t e0, uint64_t e1, const uint64_t *validity,
+                            const std::vector<uint64_t> *used, std::vector<uint32_t> *offsets,
                             std::vector<uint8_t> *bytes) {
 	const uint8_t *base = reinterpret_cast<const uint8_t *>(data);
+	auto live = [&](uint64_t e) {
+		if (validity && !((validity[e >> 6] >> (e & 63)) & 1ULL)) {
+			return false;
+		}
+		return !used || (((*used)[e >> 6] >> (e & 63)) & 1ULL);
+	};
 	offsets->resize(e1 - e0 + 1);
 	uint64_t total = 0;
 	for (uint64_t e = e0; e < e1; e++) {
-		uint32_t len;
-		memcpy(&len, base + e * 16, 4);
 		(*offsets)[e - e0] = static_cast<uint32_t>(total);
-		total += len;
+		if (live(e)) {
+			uint32_t len;
+			memcpy(&len, base + e * 16, 4);
+			total += len;
+		}
+	}
+	if (total > 0xffffffffULL) {
+		throw std::length_error("string bytes of one call exceed the 32-bit offsets; split the batch");
 	}
 	(*offsets)[e1 - e0] = static_cast<uint32_t>(total);
 	bytes->resize(total);
 	for (uint64_t e = e0; e < e1; e++) {
+		if (!live(e)) {
+			continue;
+		}
 		uint32_t len;
 		memcpy(&len, base + e * 16, 4);
 		const uint8_t *src;
@@ -377,7 +441,20 @@ static int stage_host_cols(const rpt_col_t *cols, int ncols, uint64_t r0, uint64
 		} else if (c.type == RPT_STRING_T) {
 			std::vector<uint32_t> offsets;
 			std::vector<uint8_t> bytes;
-			gather_string_t(c.data, e0, e1, &offsets, &bytes);
+			std::vector<uint64_t> used; // entries some row of the call references (selection vectors only)
+			if (c.sel) {
+				used.assign((ne + 63) >> 6, 0);
+				for (uint64_t i = 0; i < n; i++) {
+					const uint64_t e = c.sel[i];
+					if (e >= ne) {
+						return set_error("column %d: selection entry %llu is outside data_len %llu", j,
+						                 (unsigned long long)e, (unsigned long long)ne);
+					}
+					used[e >> 6] |= 1ULL << (e & 63);
+				}
+			}
+			// validity is indexed by entry; the chunk's words start at entry e0 (e0 % 64 == 0)
+			gather_string_t(c.data, e0, e1, c.validity, c.sel ? &used : nullptr, &offsets, &bytes);
 			void *po, *pb;
 			RPT_TRY(st->upload(&po, offsets.data(), offsets.size() * sizeof(uint32_t)));
 			RPT_TRY(st->upload(&pb, bytes.data(), bytes.size(), 8));
@@ -502,14 +579,22 @@ int rpt_bf_sectors_for_rows(uint64_t rows, uint64_t *out) {
 static int allocate_words(rpt_bf *bf, uint64_t rows) {
 	uint64_t s;
 	RPT_TRY(sectors_for_rows(rows, &s));
-	if (s != bf->num_sectors || !bf->words) {
+	if (s > bf->words_capacity || !bf->words) {
+		// BloomFilter::Initialize re-allocates on every call (bloom_filter.cpp:21); here the buffer only ever grows —
+		// cudaFree / cudaMalloc of a 128-512 MiB block cost milliseconds each (measured: a rebuild that re-sizes two
+		// filters took 21 ms with them, against 1.1 ms of kernels)
 		if (bf->words) {
 			RPT_CUDA(cudaFree(bf->words)); // implicit device sync: no kernel still touches the old words
 			bf->words = nullptr;
+			bf->words_capacity = 0;
 		}
 		RPT_CUDA(cudaMalloc(&bf->words, s * sizeof(uint64_t)));
-		bf->num_sectors = s;
+		bf->words_capacity = s;
+		bf->words_generation++; // IPC / peer mappings of the old allocation are stale, even at an equal address
+	} else if (s != bf->num_sectors) {
+		RPT_CUDA(cudaDeviceSynchronize()); // kernels on other streams may still read the words with the old S
 	}
+	bf->num_sectors = s;
 	bf->sized_for_rows = rows;
 	// std::fill_n(bf, num_sectors, 0), bloom_filter.cpp:24
 	RPT_CUDA(cudaMemsetAsync(bf->words, 0, s * sizeof(uint64_t), bf->stream));
@@ -531,7 +616,10 @@ int rpt_bf_create(rpt_bf_t **out, uint64_t est_rows, int device) {
 	if (device < 0 || device >= ndev) {
 		return set_error("device %d out of range [0, %d)", device, ndev);
 	}
-	rpt_bf *bf = new rpt_bf();
+	rpt_bf *bf = new (std::nothrow) rpt_bf();
+	if (!bf) {
+		return set_error("out of host memory");
+	}
 	int rc = fill_device_info(device, &bf->dev);
 	if (rc == 0) {
 		DeviceGuard guard(device);
@@ -608,12 +696,13 @@ int rpt_bf_reset(rpt_bf_t *bf, uint64_t est_rows, rpt_stream_t stream) {
 	RPT_GUARD(bf);
 	uint64_t s;
 	RPT_TRY(sectors_for_rows(est_rows, &s));
-	if (s != bf->num_sectors || !bf->words) {
+	if (s > bf->words_capacity || !bf->words) {
 		if (stream) {
 			RPT_CUDA(cudaStreamSynchronize(reinterpret_cast<cudaStream_t>(stream)));
 		}
 		RPT_TRY(allocate_words(bf, est_rows));
 	} else {
+		bf->num_sectors = s; // fits the buffer: stream-ordered like every other use of the words on `stream`
 		bf->sized_for_rows = est_rows;
 		RPT_CUDA(cudaMemsetAsync(bf->words, 0, s * sizeof(uint64_t), pick_stream(bf, stream)));
 	}
@@ -668,14 +757,14 @@ int rpt_bf_sync(const rpt_bf_t *bf) {
 // ---------------------------------------------------------------------------------------------
 // build
 // ---------------------------------------------------------------------------------------------
-// UpdateMinMax next to the insert (physical_create_bf.cpp:229-239): folds the chunk's valid rows into the range.
-static int minmax_hook(rpt_bf *bf, const DevCols &dc, uint64_t count, cudaStream_t stream, int *launches) {
+// UpdateMinMax next to the insert (physical_create_bf.cpp:229-239): when range tracking is on for this column's
+// physical type, the build kernel itself folds the chunk's valid rows into the range (template flag MM of
+// build_kernel) — the keys are read once, no second pass.
+static MinMaxState *minmax_target(rpt_bf *bf, const DevCols &dc) {
 	if (!bf->mm_active.load() || dc.n != 1 || dc.c[0].type != bf->mm_type) {
-		return 0;
+		return nullptr;
 	}
-	RPT_CUDA(launch_minmax(bf->dev, dc.c[0], count, bf->mm_dev, stream));
-	(*launches)++;
-	return 0;
+	return bf->mm_dev;
 }
 
 static int insert_impl(rpt_bf *bf, const rpt_col_t *cols, int ncols, uint64_t count, rpt_stream_t stream_in) {
@@ -693,9 +782,9 @@ static int insert_impl(rpt_bf *bf, const rpt_col_t *cols, int ncols, uint64_t co
 		st.stream = pick_stream(bf, stream_in);
 		PrehashPlan pre;
 		RPT_TRY(plan_prehash(cols, ncols, count, dc, &st, &pre));
+		MinMaxState *mm = minmax_target(bf, dc);
 		RPT_TRY(run_prehash(bf->dev, pre, &dc, st.stream, &launches));
-		RPT_CUDA(launch_build(bf->dev, dc, count, bf->words, bf->num_sectors, pick_stream(bf, stream_in), &launches));
-		RPT_TRY(minmax_hook(bf, dc, count, pick_stream(bf, stream_in), &launches));
+		RPT_CUDA(launch_build(bf->dev, dc, count, bf->words, bf->num_sectors, pick_stream(bf, stream_in), &launches, mm));
 		bf->launches += launches;
 		return 0;
 	}
@@ -726,9 +815,10 @@ static int insert_impl(rpt_bf *bf, const rpt_col_t *cols, int ncols, uint64_t co
 		RPT_TRY(plan_prehash(cols, ncols, r1 - r0, dc, &st, &pre));
 		RPT_CUDA(cudaEventRecord(sl.uploaded, bf->h2d));
 		RPT_CUDA(cudaStreamWaitEvent(bf->compute, sl.uploaded, 0));
+		st.handed_over = true;
+		MinMaxState *mm = minmax_target(bf, dc); // before run_prehash may retype the column
 		RPT_TRY(run_prehash(bf->dev, pre, &dc, bf->compute, &launches));
-		RPT_CUDA(launch_build(bf->dev, dc, r1 - r0, bf->words, bf->num_sectors, bf->compute, &launches));
-		RPT_TRY(minmax_hook(bf, dc, r1 - r0, bf->compute, &launches));
+		RPT_CUDA(launch_build(bf->dev, dc, r1 - r0, bf->words, bf->num_sectors, bf->compute, &launches, mm));
 		RPT_CUDA(cudaEventRecord(sl.computed, bf->compute));
 	}
 	bf->launches += launches;
@@ -745,7 +835,7 @@ int rpt_bf_insert(rpt_bf_t *bf, const rpt_col_t *cols, int ncols, uint64_t count
 		return set_error("null filter handle");
 	}
 	RPT_GUARD(bf);
-	return insert_impl(bf, cols, ncols, count, stream);
+	return guarded([&] { return insert_impl(bf, cols, ncols, count, stream); });
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -871,7 +961,7 @@ int rpt_bf_reinitialize_and_rehash(rpt_bf_t *bf, uint64_t actual_rows, const rpt
 	if (count == 0) {                          // :42-44
 		return 0;
 	}
-	return insert_impl(bf, cols, ncols, count, stream); // :46-57
+	return guarded([&] { return insert_impl(bf, cols, ncols, count, stream); }); // :46-57
 }
 
 int rpt_bf_finalize(rpt_bf_t *bf, uint64_t actual_rows, const rpt_col_t *cols, int ncols, uint64_t count,
@@ -1060,7 +1150,7 @@ int rpt_bf_probe(const rpt_bf_t *bf, const rpt_col_t *cols, int ncols, uint64_t 
 		return set_error("null filter handle");
 	}
 	RPT_GUARD(bf);
-	return probe_impl(bf, cols, ncols, count, sel_out, found_out, out_mem, stream, false);
+	return guarded([&] { return probe_impl(bf, cols, ncols, count, sel_out, found_out, out_mem, stream, false); });
 }
 
 int rpt_bf_filter_sel(const rpt_bf_t *bf, const rpt_col_t *key, const uint32_t *in_sel, uint64_t approved_count,
@@ -1079,10 +1169,11 @@ int rpt_bf_filter_sel(const rpt_bf_t *bf, const rpt_col_t *key, const uint32_t *
 		}
 		col.sel = in_sel; // HashInternal slices the keys by `sel` (bloom_filter.cpp:84-92)
 	}
-	return probe_impl(bf, &col, 1, approved_count, sel_out, found_out, mem, stream, in_sel != nullptr);
+	return guarded(
+	    [&] { return probe_impl(bf, &col, 1, approved_count, sel_out, found_out, mem, stream, in_sel != nullptr); });
 }
 
-int rpt_bf_lookup_hashes_host(const rpt_bf_t *bf, const uint64_t *hashes, uint64_t count, uint8_t *hits) {
+static int rpt_bf_lookup_hashes_host_body(const rpt_bf_t *bf, const uint64_t *hashes, uint64_t count, uint8_t *hits) {
 	if (!bf || (count && (!hashes || !hits))) {
 		return set_error("null argument");
 	}
@@ -1101,6 +1192,9 @@ int rpt_bf_lookup_hashes_host(const rpt_bf_t *bf, const uint64_t *hashes, uint64
 	RPT_CUDA(cudaMemcpyAsync(hits, dhits, count, cudaMemcpyDeviceToHost, st.stream));
 	RPT_CUDA(cudaStreamSynchronize(st.stream));
 	return 0;
+}
+int rpt_bf_lookup_hashes_host(const rpt_bf_t *bf, const uint64_t *hashes, uint64_t count, uint8_t *hits) {
+	return guarded([&] { return rpt_bf_lookup_hashes_host_body(bf, hashes, count, hits); });
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -1157,7 +1251,7 @@ inline unsigned __int128 max_difference(int type) {
 } // namespace
 } // extern "C++"
 
-int rpt_bf_check_statistics(const rpt_bf_t *bf, int type, const void *mins, const void *maxs,
+static int rpt_bf_check_statistics_body(const rpt_bf_t *bf, int type, const void *mins, const void *maxs,
                             const uint8_t *has_minmax, uint64_t count, uint8_t *results_out) {
 	if (!bf || (count && (!mins || !maxs || !results_out))) {
 		return set_error("null argument");
@@ -1248,6 +1342,10 @@ int rpt_bf_check_statistics(const rpt_bf_t *bf, int type, const void *mins, cons
 	RPT_CUDA(cudaStreamSynchronize(st.stream));
 	return 0;
 }
+int rpt_bf_check_statistics(const rpt_bf_t *bf, int type, const void *mins, const void *maxs,
+                            const uint8_t *has_minmax, uint64_t count, uint8_t *results_out) {
+	return guarded([&] { return rpt_bf_check_statistics_body(bf, type, mins, maxs, has_minmax, count, results_out); });
+}
 
 // ---------------------------------------------------------------------------------------------
 // filter words
@@ -1283,6 +1381,34 @@ int rpt_bf_import_words(rpt_bf_t *bf, const uint64_t *host_src, uint64_t num_wor
 	return 0;
 }
 
+// FNV-1a-64 over the S words, one xor-then-multiply per WORD (SURVEY §8c's recipe for the known answers): the
+// recurrence is sequential, so the words are brought to the host and folded there.  A checksum of the result, not
+// part of the build / probe path.
+int rpt_bf_checksum(const rpt_bf_t *bf, uint64_t *fnv1a_out) {
+	if (!bf || !fnv1a_out) {
+		return set_error("null argument");
+	}
+	RPT_GUARD(bf);
+	return guarded([&]() -> int {
+		std::vector<uint64_t> host(bf->num_sectors);
+		RPT_TRY(rpt_bf_export_words(bf, host.data(), host.size()));
+		uint64_t h = 0xcbf29ce484222325ULL;
+		for (uint64_t w : host) {
+			h = (h ^ w) * 0x100000001b3ULL;
+		}
+		*fnv1a_out = h;
+		return 0;
+	});
+}
+
+int rpt_bf_words_generation(const rpt_bf_t *bf, uint64_t *out) {
+	if (!bf || !out) {
+		return set_error("null argument");
+	}
+	*out = bf->words_generation.load();
+	return 0;
+}
+
 // ---------------------------------------------------------------------------------------------
 // multi-GPU OR-merge
 // ---------------------------------------------------------------------------------------------
@@ -1311,7 +1437,7 @@ int rpt_bf_ipc_export(const rpt_bf_t *bf, void *handle64) {
 	return 0;
 }
 
-int rpt_bf_peer_open(rpt_bf_t *bf, const void *handles64, int nranks, int rank) {
+static int rpt_bf_peer_open_body(rpt_bf_t *bf, const void *handles64, int nranks, int rank) {
 	if (!bf || !handles64) {
 		return set_error("null argument");
 	}
@@ -1336,6 +1462,9 @@ int rpt_bf_peer_open(rpt_bf_t *bf, const void *handles64, int nranks, int rank) 
 		bf->peer_ipc[r] = true;
 	}
 	return 0;
+}
+int rpt_bf_peer_open(rpt_bf_t *bf, const void *handles64, int nranks, int rank) {
+	return guarded([&] { return rpt_bf_peer_open_body(bf, handles64, nranks, rank); });
 }
 
 // slice r of an S-word filter split N ways (even word boundaries for the 128-bit accesses)
@@ -1429,6 +1558,7 @@ int rpt_bf_allreduce_or(rpt_bf_t **per_gpu, int ngpu) {
 					cudaGetLastError();
 				}
 			}
+			RPT_TRY(rpt_bf_peer_close(per_gpu[i])); // IPC mappings opened earlier (rpt_bf_peer_open) are released first
 			per_gpu[i]->peer_words.assign(ngpu, nullptr);
 			per_gpu[i]->peer_ipc.assign(ngpu, false);
 			per_gpu[i]->peer_rank = i;
@@ -1455,7 +1585,7 @@ int rpt_bf_allreduce_or(rpt_bf_t **per_gpu, int ngpu) {
 		}
 		return 0;
 	};
-	const int rc = body();
+	const int rc = guarded(body);
 	cudaSetDevice(prev);
 	return rc;
 }

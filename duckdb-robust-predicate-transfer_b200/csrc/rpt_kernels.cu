@@ -69,6 +69,120 @@ __device__ __forceinline__ uint32_t lanemask_lt() {
 }
 
 // ---------------------------------------------------------------------------------------------
+// min / max of a key column (UpdateMinMax, reference src/operators/physical_create_bf.cpp:82-176): the build
+// side's per-column range, which the reference computes chunk by chunk next to the insert loop (:229-239).
+// Here it is FUSED into build_kernel (template flag MM): the keys are read once, every thread folds its valid
+// (non-NULL, :93-95) rows into a running range, and a CTA issues one atomicMin/atomicMax pair at exit.
+// Values are mapped to order-preserving unsigned 64-bit keys so that one pair serves every numeric type;
+// NaNs are counted, not ordered (see rpt_gpu.h).
+// ---------------------------------------------------------------------------------------------
+struct MinMaxAcc {
+	uint64_t lo = ~0ULL, hi = 0;
+	uint32_t any = 0, nan = 0;
+	__device__ __forceinline__ void fold(uint64_t key) {
+		lo = key < lo ? key : lo;
+		hi = key > hi ? key : hi;
+		any = 1;
+	}
+};
+constexpr uint64_t kSignBit = 1ULL << 63;
+
+__device__ __forceinline__ bool minmax_key(const DevCol &c, uint64_t idx, uint64_t *key, bool *nan) {
+	constexpr uint64_t kSign = 1ULL << 63;
+	*nan = false;
+	switch (c.type) {
+	case RPT_BOOL:
+	case RPT_UINT8:
+		*key = __ldg(reinterpret_cast<const unsigned char *>(c.data) + idx);
+		return true;
+	case RPT_INT8:
+		*key = static_cast<uint64_t>(static_cast<int64_t>(__ldg(reinterpret_cast<const signed char *>(c.data) + idx))) ^ kSign;
+		return true;
+	case RPT_UINT16:
+		*key = __ldg(reinterpret_cast<const unsigned short *>(c.data) + idx);
+		return true;
+	case RPT_INT16:
+		*key = static_cast<uint64_t>(static_cast<int64_t>(__ldg(reinterpret_cast<const short *>(c.data) + idx))) ^ kSign;
+		return true;
+	case RPT_UINT32:
+		*key = __ldg(reinterpret_cast<const uint32_t *>(c.data) + idx);
+		return true;
+	case RPT_INT32:
+		*key = static_cast<uint64_t>(static_cast<int64_t>(__ldg(reinterpret_cast<const int *>(c.data) + idx))) ^ kSign;
+		return true;
+	case RPT_UINT64:
+		*key = __ldg(reinterpret_cast<const unsigned long long *>(c.data) + idx);
+		return true;
+	case RPT_INT64:
+		*key = __ldg(reinterpret_cast<const unsigned long long *>(c.data) + idx) ^ kSign;
+		return true;
+	case RPT_FLOAT: {
+		const uint32_t b = __ldg(reinterpret_cast<const uint32_t *>(c.data) + idx);
+		if ((b & 0x7fffffffu) > 0x7f800000u) {
+			*nan = true;
+			return false;
+		}
+		const uint32_t o = (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+		*key = o;
+		return true;
+	}
+	case RPT_DOUBLE: {
+		const uint64_t b = __ldg(reinterpret_cast<const unsigned long long *>(c.data) + idx);
+		if ((b & ~kSign) > 0x7ff0000000000000ULL) {
+			*nan = true;
+			return false;
+		}
+		*key = (b & kSign) ? ~b : (b | kSign);
+		return true;
+	}
+	default:
+		return false;
+	}
+}
+
+
+// CTA-wide reduction of the threads' ranges, one atomic pair per CTA
+template <int BLOCK>
+__device__ __forceinline__ void minmax_commit(MinMaxAcc acc, MinMaxState *state) {
+	__shared__ uint64_t s_lo[BLOCK / 32], s_hi[BLOCK / 32];
+	__shared__ uint32_t s_flags[BLOCK / 32];
+#pragma unroll
+	for (int d = 16; d > 0; d >>= 1) {
+		const uint64_t olo = __shfl_xor_sync(0xffffffffu, acc.lo, d);
+		const uint64_t ohi = __shfl_xor_sync(0xffffffffu, acc.hi, d);
+		acc.lo = olo < acc.lo ? olo : acc.lo;
+		acc.hi = ohi > acc.hi ? ohi : acc.hi;
+	}
+	const uint32_t any = __any_sync(0xffffffffu, acc.any) ? 1u : 0u;
+	const uint32_t nan = __any_sync(0xffffffffu, acc.nan) ? 2u : 0u;
+	const uint32_t warp = threadIdx.x >> 5;
+	if ((threadIdx.x & 31u) == 0) {
+		s_lo[warp] = acc.lo;
+		s_hi[warp] = acc.hi;
+		s_flags[warp] = any | nan;
+	}
+	__syncthreads();
+	if (threadIdx.x == 0) {
+		uint64_t lo = ~0ULL, hi = 0;
+		uint32_t flags = 0;
+#pragma unroll
+		for (int w = 0; w < BLOCK / 32; w++) {
+			lo = s_lo[w] < lo ? s_lo[w] : lo;
+			hi = s_hi[w] > hi ? s_hi[w] : hi;
+			flags |= s_flags[w];
+		}
+		if (flags & 1u) {
+			atomicMin(reinterpret_cast<unsigned long long *>(&state->min_key), static_cast<unsigned long long>(lo));
+			atomicMax(reinterpret_cast<unsigned long long *>(&state->max_key), static_cast<unsigned long long>(hi));
+			atomicOr(&state->has_value, 1u);
+		}
+		if (flags & 2u) {
+			atomicOr(&state->has_nan, 1u);
+		}
+	}
+}
+
+// ---------------------------------------------------------------------------------------------
 // key sources.  load2(row0, count, h0, h1) hashes rows row0 and row0+1 (row0 is even) and
 // returns a 2-bit validity (rows ≥ count are invalid and must not be read).
 // ---------------------------------------------------------------------------------------------
@@ -109,9 +223,10 @@ struct FlatU64SrcT { // one flat int64 / uint64 column (validity bitmap iff NULL
 	}
 	// unchecked: rows row0 + r*stride (+0,+1), r < R, all in range.  All R 128-bit loads are issued
 	// before the first hash so that they are in flight together.
-	template <int R>
-	__device__ __forceinline__ void load_rounds(uint64_t row0, uint64_t stride, uint64_t pol,
-	                                            uint64_t (&h)[2 * R]) const {
+	// MM: the raw keys are also folded into the running column range (mm_signed: INT64, else UINT64)
+	template <int R, bool MM = false>
+	__device__ __forceinline__ void load_rounds(uint64_t row0, uint64_t stride, uint64_t pol, uint64_t (&h)[2 * R],
+	                                            MinMaxAcc *acc = nullptr, bool mm_signed = false) const {
 		ulonglong2 k[R];
 #pragma unroll
 		for (int r = 0; r < R; r++) {
@@ -122,14 +237,35 @@ struct FlatU64SrcT { // one flat int64 / uint64 column (validity bitmap iff NULL
 			h[2 * r] = key_hash(k[r].x);
 			h[2 * r + 1] = key_hash(k[r].y);
 		}
+		const uint64_t flip = mm_signed ? kSignBit : 0ULL;
 		if (NULLABLE) {
 #pragma unroll
 			for (int r = 0; r < R; r++) {
 				const uint32_t v = valid_pair(validity, row0 + r * stride);
 				h[2 * r] = (v & 1u) ? h[2 * r] : kNullHash;
 				h[2 * r + 1] = (v & 2u) ? h[2 * r + 1] : kNullHash;
+				if (MM) {
+					if (v & 1u) {
+						acc->fold(k[r].x ^ flip);
+					}
+					if (v & 2u) {
+						acc->fold(k[r].y ^ flip);
+					}
+				}
+			}
+		} else if (MM) {
+#pragma unroll
+			for (int r = 0; r < R; r++) {
+				acc->fold(k[r].x ^ flip);
+				acc->fold(k[r].y ^ flip);
 			}
 		}
+	}
+	__device__ __forceinline__ void fold_minmax(uint64_t row, uint64_t pol, MinMaxAcc *acc, bool mm_signed) const {
+		if (NULLABLE && !valid_row(validity, row)) {
+			return;
+		}
+		acc->fold(ld_stream_u64(keys + row, pol) ^ (mm_signed ? kSignBit : 0ULL));
 	}
 	__device__ __forceinline__ uint32_t load2(uint64_t row0, uint64_t count, uint64_t pol, uint64_t &h0,
 	                                          uint64_t &h1) const {
@@ -182,9 +318,14 @@ struct FlatU32SrcT {
 		}
 		return murmur64(ld_stream_u32(keys + row, pol));
 	}
-	template <int R>
-	__device__ __forceinline__ void load_rounds(uint64_t row0, uint64_t stride, uint64_t pol,
-	                                            uint64_t (&h)[2 * R]) const {
+	// order-preserving 64-bit image of a 4-byte key: sign-extended ^ 2^63 (INT32) or zero-extended (UINT32)
+	__device__ __forceinline__ static uint64_t mm_key(uint32_t k, bool mm_signed) {
+		return mm_signed ? (static_cast<uint64_t>(static_cast<int64_t>(static_cast<int32_t>(k))) ^ kSignBit)
+		                 : static_cast<uint64_t>(k);
+	}
+	template <int R, bool MM = false>
+	__device__ __forceinline__ void load_rounds(uint64_t row0, uint64_t stride, uint64_t pol, uint64_t (&h)[2 * R],
+	                                            MinMaxAcc *acc = nullptr, bool mm_signed = false) const {
 		uint2 k[R];
 #pragma unroll
 		for (int r = 0; r < R; r++) {
@@ -201,8 +342,28 @@ struct FlatU32SrcT {
 				const uint32_t v = valid_pair(validity, row0 + r * stride);
 				h[2 * r] = (v & 1u) ? h[2 * r] : kNullHash;
 				h[2 * r + 1] = (v & 2u) ? h[2 * r + 1] : kNullHash;
+				if (MM) {
+					if (v & 1u) {
+						acc->fold(mm_key(k[r].x, mm_signed));
+					}
+					if (v & 2u) {
+						acc->fold(mm_key(k[r].y, mm_signed));
+					}
+				}
+			}
+		} else if (MM) {
+#pragma unroll
+			for (int r = 0; r < R; r++) {
+				acc->fold(mm_key(k[r].x, mm_signed));
+				acc->fold(mm_key(k[r].y, mm_signed));
 			}
 		}
+	}
+	__device__ __forceinline__ void fold_minmax(uint64_t row, uint64_t pol, MinMaxAcc *acc, bool mm_signed) const {
+		if (NULLABLE && !valid_row(validity, row)) {
+			return;
+		}
+		acc->fold(mm_key(ld_stream_u32(keys + row, pol), mm_signed));
 	}
 	__device__ __forceinline__ uint32_t load2(uint64_t row0, uint64_t count, uint64_t pol, uint64_t &h0,
 	                                          uint64_t &h1) const {
@@ -236,14 +397,31 @@ struct GenericSrc { // any type / sel / validity / multi-column combination
 	__device__ __forceinline__ uint64_t hash_at(uint64_t row, uint64_t) const {
 		return hash_row(cols, row);
 	}
-	template <int R>
-	__device__ __forceinline__ void load_rounds(uint64_t row0, uint64_t stride, uint64_t,
-	                                            uint64_t (&h)[2 * R]) const {
+	template <int R, bool MM = false>
+	__device__ __forceinline__ void load_rounds(uint64_t row0, uint64_t stride, uint64_t pol, uint64_t (&h)[2 * R],
+	                                            MinMaxAcc *acc = nullptr, bool mm_signed = false) const {
 #pragma unroll
 		for (int r = 0; r < R; r++) {
 			h[2 * r] = hash_row(cols, row0 + r * stride);
 			h[2 * r + 1] = hash_row(cols, row0 + r * stride + 1);
+			if (MM) { // the value was just read by hash_row: this re-read is an L1 hit
+				fold_minmax(row0 + r * stride, pol, acc, mm_signed);
+				fold_minmax(row0 + r * stride + 1, pol, acc, mm_signed);
+			}
 		}
+	}
+	__device__ __forceinline__ void fold_minmax(uint64_t row, uint64_t, MinMaxAcc *acc, bool) const {
+		const DevCol &c = cols.c[0];
+		const uint64_t idx = c.sel ? static_cast<uint64_t>(__ldg(c.sel + row)) : row;
+		if (c.validity && !((__ldg(c.validity + (idx >> 6)) >> (idx & 63)) & 1ULL)) {
+			return; // NULL rows are skipped (physical_create_bf.cpp:93-95)
+		}
+		uint64_t key;
+		bool nan;
+		if (minmax_key(c, idx, &key, &nan)) {
+			acc->fold(key);
+		}
+		acc->nan |= nan ? 1u : 0u;
 	}
 	__device__ __forceinline__ uint32_t load2(uint64_t row0, uint64_t count, uint64_t, uint64_t &h0,
 	                                          uint64_t &h1) const {
@@ -279,25 +457,36 @@ __device__ __forceinline__ void red_or_u64(unsigned long long *ptr, uint64_t mas
 
 // AGG: lanes of a warp that hit the same sector OR their masks first and issue one reduction
 // (worth it only for small filters or duplicate-heavy keys).
-template <class Src, bool AGG>
+template <class Src, bool AGG, bool MM>
 __global__ void __launch_bounds__(kBuildBlock)
     build_kernel(const Src src, unsigned long long *__restrict__ filter, const uint32_t sector_mask,
-                 const uint64_t count, const uint32_t slice_lo, const uint32_t slice_len) {
+                 const uint64_t count, const uint32_t slice_lo, const uint32_t slice_len, MinMaxState *mm_state,
+                 const bool mm_signed) {
 	const uint64_t pol = policy_evict_first();
 	const uint64_t pol_filter = policy_evict_last();
 	const uint64_t step = static_cast<uint64_t>(gridDim.x) * kBuildBlock * 2 * kBuildUnroll;
+	MinMaxAcc acc;
 	for (uint64_t base = static_cast<uint64_t>(blockIdx.x) * kBuildBlock * 2 * kBuildUnroll; base < count;
 	     base += step) {
 		uint64_t h[2 * kBuildUnroll];
 		uint32_t valid = 0;
 		if (base + static_cast<uint64_t>(kBuildBlock) * 2 * kBuildUnroll <= count) { // block-uniform
-			src.template load_rounds<kBuildUnroll>(base + threadIdx.x * 2, kBuildBlock * 2, pol, h);
+			src.template load_rounds<kBuildUnroll, MM>(base + threadIdx.x * 2, kBuildBlock * 2, pol, h, &acc, mm_signed);
 			valid = (1u << (2 * kBuildUnroll)) - 1u;
 		} else {
 #pragma unroll
 			for (int u = 0; u < kBuildUnroll; u++) {
 				const uint64_t row0 = base + static_cast<uint64_t>(u) * kBuildBlock * 2 + threadIdx.x * 2;
-				valid |= src.load2(row0, count, pol, h[2 * u], h[2 * u + 1]) << (2 * u);
+				const uint32_t v = src.load2(row0, count, pol, h[2 * u], h[2 * u + 1]);
+				valid |= v << (2 * u);
+				if (MM) {
+					if (v & 1u) {
+						src.fold_minmax(row0, pol, &acc, mm_signed);
+					}
+					if (v & 2u) {
+						src.fold_minmax(row0 + 1, pol, &acc, mm_signed);
+					}
+				}
 			}
 		}
 #pragma unroll
@@ -319,6 +508,9 @@ __global__ void __launch_bounds__(kBuildBlock)
 				red_or_u64(filter + sector, mask, pol_filter);
 			}
 		}
+	}
+	if (MM) {
+		minmax_commit<kBuildBlock>(acc, mm_state);
 	}
 }
 
@@ -1343,104 +1535,6 @@ __global__ void __launch_bounds__(256)
 	}
 }
 
-// ---------------------------------------------------------------------------------------------
-// min / max of a key column (UpdateMinMax, reference src/operators/physical_create_bf.cpp:82-176): the build
-// side's per-column range, which the reference computes chunk by chunk next to the insert loop (:229-239).
-// Values are mapped to order-preserving unsigned 64-bit keys so that one atomicMin/atomicMax pair serves
-// every numeric type; NULL rows are skipped (:93-95); NaNs are counted, not ordered (see rpt_gpu.h).
-// ---------------------------------------------------------------------------------------------
-__device__ __forceinline__ bool minmax_key(const DevCol &c, uint64_t idx, uint64_t *key, bool *nan) {
-	constexpr uint64_t kSign = 1ULL << 63;
-	*nan = false;
-	switch (c.type) {
-	case RPT_BOOL:
-	case RPT_UINT8:
-		*key = __ldg(reinterpret_cast<const unsigned char *>(c.data) + idx);
-		return true;
-	case RPT_INT8:
-		*key = static_cast<uint64_t>(static_cast<int64_t>(__ldg(reinterpret_cast<const signed char *>(c.data) + idx))) ^ kSign;
-		return true;
-	case RPT_UINT16:
-		*key = __ldg(reinterpret_cast<const unsigned short *>(c.data) + idx);
-		return true;
-	case RPT_INT16:
-		*key = static_cast<uint64_t>(static_cast<int64_t>(__ldg(reinterpret_cast<const short *>(c.data) + idx))) ^ kSign;
-		return true;
-	case RPT_UINT32:
-		*key = __ldg(reinterpret_cast<const uint32_t *>(c.data) + idx);
-		return true;
-	case RPT_INT32:
-		*key = static_cast<uint64_t>(static_cast<int64_t>(__ldg(reinterpret_cast<const int *>(c.data) + idx))) ^ kSign;
-		return true;
-	case RPT_UINT64:
-		*key = __ldg(reinterpret_cast<const unsigned long long *>(c.data) + idx);
-		return true;
-	case RPT_INT64:
-		*key = __ldg(reinterpret_cast<const unsigned long long *>(c.data) + idx) ^ kSign;
-		return true;
-	case RPT_FLOAT: {
-		const uint32_t b = __ldg(reinterpret_cast<const uint32_t *>(c.data) + idx);
-		if ((b & 0x7fffffffu) > 0x7f800000u) {
-			*nan = true;
-			return false;
-		}
-		const uint32_t o = (b & 0x80000000u) ? ~b : (b | 0x80000000u);
-		*key = o;
-		return true;
-	}
-	case RPT_DOUBLE: {
-		const uint64_t b = __ldg(reinterpret_cast<const unsigned long long *>(c.data) + idx);
-		if ((b & ~kSign) > 0x7ff0000000000000ULL) {
-			*nan = true;
-			return false;
-		}
-		*key = (b & kSign) ? ~b : (b | kSign);
-		return true;
-	}
-	default:
-		return false;
-	}
-}
-
-__global__ void __launch_bounds__(256) minmax_kernel(const DevCol col, const uint64_t count, MinMaxState *state) {
-	uint64_t lo = ~0ULL, hi = 0;
-	uint32_t any = 0, nans = 0;
-	const uint64_t step = static_cast<uint64_t>(gridDim.x) * blockDim.x;
-	for (uint64_t row = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x; row < count; row += step) {
-		const uint64_t idx = col.sel ? static_cast<uint64_t>(__ldg(col.sel + row)) : row;
-		if (col.validity && !((__ldg(col.validity + (idx >> 6)) >> (idx & 63)) & 1ULL)) {
-			continue;
-		}
-		uint64_t key;
-		bool nan;
-		if (minmax_key(col, idx, &key, &nan)) {
-			lo = key < lo ? key : lo;
-			hi = key > hi ? key : hi;
-			any = 1;
-		}
-		nans |= nan ? 1u : 0u;
-	}
-#pragma unroll
-	for (int d = 16; d > 0; d >>= 1) {
-		const uint64_t olo = __shfl_xor_sync(0xffffffffu, lo, d);
-		const uint64_t ohi = __shfl_xor_sync(0xffffffffu, hi, d);
-		lo = olo < lo ? olo : lo;
-		hi = ohi > hi ? ohi : hi;
-	}
-	any = __any_sync(0xffffffffu, any);
-	nans = __any_sync(0xffffffffu, nans);
-	if ((threadIdx.x & 31u) == 0) {
-		if (any) {
-			atomicMin(reinterpret_cast<unsigned long long *>(&state->min_key), static_cast<unsigned long long>(lo));
-			atomicMax(reinterpret_cast<unsigned long long *>(&state->max_key), static_cast<unsigned long long>(hi));
-			atomicOr(&state->has_value, 1u);
-		}
-		if (nans) {
-			atomicOr(&state->has_nan, 1u);
-		}
-	}
-}
-
 __host__ __device__ __forceinline__ uint64_t splitmix64(uint64_t x) {
 	uint64_t z = x + 0x9e3779b97f4a7c15ULL;
 	z = (z ^ (z >> 30)) * 0xbf58476d1ce4e5b9ULL;
@@ -1616,12 +1710,13 @@ size_t probe_scratch_bytes(uint64_t count, uint64_t num_sectors) {
 	return align_up(phased_layout(count).bytes, 256) + (slices ? partition_scratch_bytes(count, slices) : 0);
 }
 
-template <class Src, bool AGG>
-static cudaError_t launch_build_t(const DeviceInfo &dev, const Src &src, uint64_t count, uint64_t *words,
-                                  uint64_t num_sectors, cudaStream_t stream, int *launches) {
+template <class Src, bool AGG, bool MM>
+static cudaError_t launch_build_mm(const DeviceInfo &dev, const Src &src, uint64_t count, uint64_t *words,
+                                   uint64_t num_sectors, MinMaxState *mm, bool mm_signed, cudaStream_t stream,
+                                   int *launches) {
 	const uint64_t per_block = static_cast<uint64_t>(kBuildBlock) * 2 * kBuildUnroll;
 	int per_sm = 0;
-	cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, build_kernel<Src, AGG>, kBuildBlock, 0);
+	cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, build_kernel<Src, AGG, MM>, kBuildBlock, 0);
 	if (e != cudaSuccess) {
 		return e;
 	}
@@ -1633,49 +1728,69 @@ static cudaError_t launch_build_t(const DeviceInfo &dev, const Src &src, uint64_
 	const uint64_t slice = slice_sectors_for(num_sectors);
 	for (uint64_t lo = 0; lo < num_sectors; lo += slice) {
 		const uint64_t len = lo + slice < num_sectors ? slice : num_sectors - lo;
-		build_kernel<Src, AGG><<<static_cast<unsigned>(grid), kBuildBlock, 0, stream>>>(
-		    src, reinterpret_cast<unsigned long long *>(words), static_cast<uint32_t>(num_sectors - 1), count,
-		    static_cast<uint32_t>(lo), static_cast<uint32_t>(len));
+		if (MM && lo != 0) { // the column range is folded in by the first sector-range pass only
+			build_kernel<Src, AGG, false><<<static_cast<unsigned>(grid), kBuildBlock, 0, stream>>>(
+			    src, reinterpret_cast<unsigned long long *>(words), static_cast<uint32_t>(num_sectors - 1), count,
+			    static_cast<uint32_t>(lo), static_cast<uint32_t>(len), nullptr, false);
+		} else {
+			build_kernel<Src, AGG, MM><<<static_cast<unsigned>(grid), kBuildBlock, 0, stream>>>(
+			    src, reinterpret_cast<unsigned long long *>(words), static_cast<uint32_t>(num_sectors - 1), count,
+			    static_cast<uint32_t>(lo), static_cast<uint32_t>(len), mm, mm_signed);
+		}
 		if (launches) {
 			(*launches)++;
 		}
 	}
 	return cudaGetLastError();
 }
+template <class Src, bool AGG>
+static cudaError_t launch_build_t(const DeviceInfo &dev, const Src &src, uint64_t count, uint64_t *words,
+                                  uint64_t num_sectors, MinMaxState *mm, bool mm_signed, cudaStream_t stream,
+                                  int *launches) {
+	return mm ? launch_build_mm<Src, AGG, true>(dev, src, count, words, num_sectors, mm, mm_signed, stream, launches)
+	          : launch_build_mm<Src, AGG, false>(dev, src, count, words, num_sectors, nullptr, false, stream, launches);
+}
 
+// mm (optional): the build also folds the (single) key column's valid rows into *mm — UpdateMinMax fused into the
+// insert pass (physical_create_bf.cpp:220-239).  Ignored for several key columns and for pre-hashed columns.
 cudaError_t launch_build(const DeviceInfo &dev, const DevCols &cols, uint64_t count, uint64_t *words,
-                         uint64_t num_sectors, cudaStream_t stream, int *launches) {
+                         uint64_t num_sectors, cudaStream_t stream, int *launches, MinMaxState *mm) {
 	if (count == 0) {
 		return cudaSuccess;
 	}
+	if (cols.n != 1) {
+		mm = nullptr;
+	}
 	// warp-aggregate only where same-sector collisions inside a warp are likely
 	const bool agg = num_sectors <= 4096;
-#define RPT_BUILD_FLAT(SRC, PTR_T)                                                                                      \
+	const bool mm_signed = cols.c[0].type == RPT_INT64 || cols.c[0].type == RPT_INT32;
+#define RPT_BUILD_FLAT(SRC, PTR_T, MMPTR)                                                                               \
 	{                                                                                                                  \
 		SRC src {reinterpret_cast<const PTR_T *>(cols.c[0].data), cols.c[0].validity};                                 \
-		return agg ? launch_build_t<SRC, true>(dev, src, count, words, num_sectors, stream, launches)                  \
-		           : launch_build_t<SRC, false>(dev, src, count, words, num_sectors, stream, launches);                \
+		return agg ? launch_build_t<SRC, true>(dev, src, count, words, num_sectors, MMPTR, mm_signed, stream, launches) \
+		           : launch_build_t<SRC, false>(dev, src, count, words, num_sectors, MMPTR, mm_signed, stream,         \
+		                                        launches);                                                             \
 	}
 	if (is_flat_prehashed(cols)) {
 		using PrehashedSrc = FlatU64SrcT<false, true>;
-		RPT_BUILD_FLAT(PrehashedSrc, uint64_t)
+		RPT_BUILD_FLAT(PrehashedSrc, uint64_t, nullptr)
 	}
 	if (is_flat_u64(cols)) {
 		if (cols.c[0].validity) {
-			RPT_BUILD_FLAT(FlatU64SrcT<true>, uint64_t)
+			RPT_BUILD_FLAT(FlatU64SrcT<true>, uint64_t, mm)
 		}
-		RPT_BUILD_FLAT(FlatU64SrcT<false>, uint64_t)
+		RPT_BUILD_FLAT(FlatU64SrcT<false>, uint64_t, mm)
 	}
 	if (is_flat_u32(cols)) {
 		if (cols.c[0].validity) {
-			RPT_BUILD_FLAT(FlatU32SrcT<true>, uint32_t)
+			RPT_BUILD_FLAT(FlatU32SrcT<true>, uint32_t, mm)
 		}
-		RPT_BUILD_FLAT(FlatU32SrcT<false>, uint32_t)
+		RPT_BUILD_FLAT(FlatU32SrcT<false>, uint32_t, mm)
 	}
 #undef RPT_BUILD_FLAT
 	GenericSrc src {cols};
-	return agg ? launch_build_t<GenericSrc, true>(dev, src, count, words, num_sectors, stream, launches)
-	           : launch_build_t<GenericSrc, false>(dev, src, count, words, num_sectors, stream, launches);
+	return agg ? launch_build_t<GenericSrc, true>(dev, src, count, words, num_sectors, mm, mm_signed, stream, launches)
+	           : launch_build_t<GenericSrc, false>(dev, src, count, words, num_sectors, mm, mm_signed, stream, launches);
 }
 
 // Small probes: the fused look-back kernel (one launch + one memset).
@@ -1690,7 +1805,7 @@ static cudaError_t launch_probe_fused(const DeviceInfo &dev, const Src &src, uin
 	const size_t smem = SMEM ? num_sectors * sizeof(uint64_t) : 0;
 	cudaError_t e;
 	if (SMEM) {
-		e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
+		e = ensure_max_dyn_smem<probe_kernel<Src, kProbeRounds, BLOCK, SMEM>>(dev);
 		if (e != cudaSuccess) {
 			return e;
 		}
@@ -1736,7 +1851,7 @@ static cudaError_t launch_probe_phased(const DeviceInfo &dev, const Src &src, ui
 	const uint64_t num_segs = ceil_div(count, kSegRows);
 	const size_t smem = (Src::kStageable ? static_cast<size_t>(BLOCK / 32) * 2 * kSegRows * Src::kKeyBytes : 0) +
 	                    (SMEM ? num_sectors * sizeof(uint64_t) : 0);
-	cudaError_t e = cudaFuncSetAttribute(pass, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
+	cudaError_t e = ensure_max_dyn_smem<probe_bitmap_kernel<Src, BLOCK, MINB, UNITS, SMEM, SLICED>>(dev);
 	if (e != cudaSuccess) {
 		return e;
 	}
@@ -1794,7 +1909,7 @@ static cudaError_t launch_probe_partitioned(const DeviceInfo &dev, const Src &sr
 	auto bucket = probe_bucket_kernel<CAP>;
 	const uint64_t num_segs = ceil_div(count, kSegRows);
 	const size_t smem = static_cast<size_t>(BLOCK / 32) * PartSmem<Src, P>::WARP_BYTES;
-	cudaError_t e = cudaFuncSetAttribute(part, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
+	cudaError_t e = ensure_max_dyn_smem<probe_partition_kernel<Src, BLOCK, P>>(dev);
 	if (e != cudaSuccess) {
 		return e;
 	}
@@ -1981,15 +2096,6 @@ cudaError_t launch_lookup_hashes(const uint64_t *words, uint64_t num_sectors, co
 	}
 	lookup_hashes_kernel<<<static_cast<unsigned>(ceil_div(count, 256)), 256, 0, stream>>>(words, num_sectors - 1,
 	                                                                                      hashes, count, hits);
-	return cudaGetLastError();
-}
-
-cudaError_t launch_minmax(const DeviceInfo &dev, const DevCol &col, uint64_t count, MinMaxState *state,
-                          cudaStream_t stream) {
-	if (count == 0) {
-		return cudaSuccess;
-	}
-	minmax_kernel<<<stream_grid(dev, count, 256), 256, 0, stream>>>(col, count, state);
 	return cudaGetLastError();
 }
 

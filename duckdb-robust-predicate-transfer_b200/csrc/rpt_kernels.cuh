@@ -3,6 +3,7 @@
 #pragma once
 #include <cuda_runtime.h>
 
+#include <atomic>
 #include <cstdint>
 
 #include "rpt_hash.cuh"
@@ -16,6 +17,29 @@ struct DeviceInfo {
 	size_t smem_optin = 0;
 };
 
+// cudaFuncAttributeMaxDynamicSharedMemorySize is raised ONCE per kernel instantiation and device, to the most the
+// device allows next to the kernel's static shared memory.  Every caller sets the same value, so concurrent
+// launches of differently sized filters cannot lower the limit under each other (a per-launch, per-size call could).
+template <auto Kern>
+inline cudaError_t ensure_max_dyn_smem(const DeviceInfo &dev) {
+	static std::atomic<uint64_t> done {0};
+	const uint64_t bit = 1ULL << (static_cast<unsigned>(dev.device) & 63u);
+	if (done.load(std::memory_order_acquire) & bit) {
+		return cudaSuccess;
+	}
+	cudaFuncAttributes attr;
+	cudaError_t e = cudaFuncGetAttributes(&attr, Kern);
+	if (e != cudaSuccess) {
+		return e;
+	}
+	const long long room = static_cast<long long>(dev.smem_optin) - static_cast<long long>(attr.sharedSizeBytes);
+	e = cudaFuncSetAttribute(Kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(room > 0 ? room : 0));
+	if (e == cudaSuccess) {
+		done.fetch_or(bit, std::memory_order_release);
+	}
+	return e;
+}
+
 // Largest filter (in 64-bit sectors) that is staged in shared memory by the probe kernel.
 constexpr uint64_t kSmemFilterMaxSectors = 1ULL << 14; // 128 KiB
 // Filters larger than this are built / probed in sector-range passes of this many sectors, each of which
@@ -25,9 +49,19 @@ constexpr uint64_t kSliceSectors = 1ULL << 23;
 // Scratch the probe kernel needs for `count` rows: tile descriptors + ticket counter (bytes).
 size_t probe_scratch_bytes(uint64_t count, uint64_t num_sectors);
 
+// Column range (UpdateMinMax, physical_create_bf.cpp:82-176).  Keys are order-preserving uint64 images of the
+// values (signed: value ^ 2^63 after sign extension; float/double: sign-magnitude flip); the host decodes them.
+// The reduction is fused into the build kernel (launch_build's `mm` argument): the keys are read once.
+struct MinMaxState {
+	uint64_t min_key; // initialised to ~0
+	uint64_t max_key; // initialised to 0
+	uint32_t has_value;
+	uint32_t has_nan;
+};
+
 // Build: filter[h & (S-1)] |= GetMask(h) for every row (InsertHashes, bloom_filter.cpp:43-48,63-70).
 cudaError_t launch_build(const DeviceInfo &dev, const DevCols &cols, uint64_t count, uint64_t *words,
-                         uint64_t num_sectors, cudaStream_t stream, int *launches);
+                         uint64_t num_sectors, cudaStream_t stream, int *launches, MinMaxState *mm = nullptr);
 
 // Probe: ascending row ids of passing rows → sel_out, count → *found_out (LookupHashes,
 // bloom_filter.cpp:50-61,72-78).  `scratch` holds probe_scratch_bytes(count) bytes; it is zeroed
@@ -72,17 +106,6 @@ cudaError_t launch_hash_entries(const DeviceInfo &dev, const DevCol &col, uint64
 // out[i] = hash of row i of a flat VARCHAR column (offsets + bytes, optional validity), staged through shared memory
 cudaError_t launch_hash_varchar(const DeviceInfo &dev, const DevCol &col, uint64_t count, uint64_t *out,
                                 cudaStream_t stream);
-
-// Column range (UpdateMinMax, physical_create_bf.cpp:82-176).  Keys are order-preserving uint64 images of the
-// values (signed: value ^ 2^63 after sign extension; float/double: sign-magnitude flip); the host decodes them.
-struct MinMaxState {
-	uint64_t min_key; // initialised to ~0
-	uint64_t max_key; // initialised to 0
-	uint32_t has_value;
-	uint32_t has_nan;
-};
-cudaError_t launch_minmax(const DeviceInfo &dev, const DevCol &col, uint64_t count, MinMaxState *state,
-                          cudaStream_t stream);
 
 // Row-ordered bitmap → ordered selection vector (count_segments + scans + compaction), shared with rpt_acero.cu
 size_t bitmap_scratch_bytes(uint64_t count);

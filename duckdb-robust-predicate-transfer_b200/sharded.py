@@ -123,10 +123,12 @@ class ShardedBloomFilter:
 
     def Reset(self, est_num_rows, stream=None):
         self._release(stream)
-        before = self.bf.device_words if hasattr(self.bf, "device_words") else None
+        # a reallocation (even one that lands on the same address) makes every peer's IPC mapping of the old words
+        # stale: compare the library's generation counter, not the pointer
+        before = getattr(self.bf, "words_generation", None)
         self.bf.Reset(est_num_rows, stream)
-        after = self.bf.device_words if hasattr(self.bf, "device_words") else None
-        if before != after:
+        after = getattr(self.bf, "words_generation", None)
+        if before != after or before is None:
             self._peer_open_for = None
         self.merged = False
         return self
@@ -177,7 +179,7 @@ class ShardedBloomFilter:
     def _merge_on(self, stream, has_local=0, defer_release=False):
         import torch
         if self.merge == "peer":
-            words = self.bf.device_words
+            words = (self.bf.device_words, getattr(self.bf, "words_generation", 0))
             if self._peer_open_for != words:
                 blob = torch.frombuffer(bytearray(self.bf.IpcExport()), dtype=torch.uint8).cuda(self.device)
                 allb = torch.empty(self.world * 64, dtype=torch.uint8, device=blob.device)

@@ -139,7 +139,8 @@ RPT_API int rpt_bf_finalize(rpt_bf_t *bf, uint64_t actual_rows, const rpt_col_t 
  *      PhysicalCreateBF::Sink runs on every chunk next to the insert (:229-239) ----------------------------- */
 /* Starts (or restarts) range tracking for a key column of the given physical type: from now on every
  * single-column rpt_bf_insert / rehash of that type also folds the column's valid (non-NULL) rows into a running
- * min / max on the device (one extra streaming kernel on the same stream, no host work per chunk).
+ * min / max on the device — inside the build kernel itself (the keys are read once, as Sink reads a chunk once for
+ * the insert and for UpdateMinMax; no extra kernel, no host work per chunk).
  * Supported: the fixed-width numeric physical types (BOOL…UINT64, FLOAT, DOUBLE; DATE and TIMESTAMP are INT32 /
  * INT64 physically).  VARCHAR ranges stay on the host. */
 RPT_API int rpt_bf_minmax_begin(rpt_bf_t *bf, int type);
@@ -188,6 +189,13 @@ RPT_API int rpt_bf_check_statistics(const rpt_bf_t *bf, int type, const void *mi
 RPT_API int rpt_bf_export_words(const rpt_bf_t *bf, uint64_t *host_dst, uint64_t capacity_words);
 /* H2D replace of the S words (e.g. a filter built by CPU sink threads); marks has_data_. */
 RPT_API int rpt_bf_import_words(rpt_bf_t *bf, const uint64_t *host_src, uint64_t num_words);
+/* FNV-1a-64 over the S words (xor-then-multiply per 64-bit word, offset 0xcbf29ce484222325, prime 0x100000001b3):
+ * SURVEY §8(c)'s recipe, the "fnv1a_words" of tests/golden/ref_vectors.json, and what the ranks compare after a
+ * multi-GPU merge (bench.py). */
+RPT_API int rpt_bf_checksum(const rpt_bf_t *bf, uint64_t *fnv1a_out);
+/* Bumped whenever the words are reallocated (rpt_bf_reset / rehash to another S — or to the same S at a recycled
+ * address): peers that mapped the old allocation through rpt_bf_ipc_export must re-open when it changes. */
+RPT_API int rpt_bf_words_generation(const rpt_bf_t *bf, uint64_t *out);
 /* Raw device pointer to the words (for collective plumbing); valid until destroy / rebuild. */
 RPT_API int rpt_bf_device_words(const rpt_bf_t *bf, uint64_t **dev_ptr_out);
 RPT_API int rpt_bf_sync(const rpt_bf_t *bf); /* wait for all work enqueued on the handle's own stream */

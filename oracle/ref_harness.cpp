@@ -15,6 +15,9 @@
  *                                                HashOp::NULL_HASH, CombineHashScalar, TightLoopHash,
  *                                                TightLoopCombineHash                (:16-61,:364-385)
  *   duckdb/src/common/constants.cpp              NextPowerOfTwo                      (:30-47)
+ *   duckdb/src/planner/filter/bloom_filter.cpp   TemplatedCheckStatistics<T>          (:138-169), with
+ *   duckdb/src/function/scalar/operator/subtract.cpp   TrySubtractOperator::Operation<T> (:98-175) and
+ *   duckdb/src/common/types/{hugeint,uhugeint}.cpp     the 128-bit integer arithmetic
  *
  * What cannot be compiled this way (needs the whole engine: BufferManager, DataChunk,
  * ColumnDataCollection, PhysicalOperator): BloomFilter::Initialize's allocation,
@@ -25,7 +28,57 @@
  * The fake `Vector` / `BloomFilter` objects below only carry the fields the reference loops read
  * (Vector::data; BloomFilter::{bf,num_sectors,bitmask}); -fno-access-control lets the harness set them.
  */
+/* Zone-map pruning (BFTableFilter::CheckStatistics → TemplatedCheckStatistics<T>, bloom_filter.cpp:138-196): the
+ * function template is compiled UNMODIFIED from the reference file included below — the TrySubtractOperator
+ * overflow rule, the `range_typed > 2048` cut, the `val += i < range` walk and Hash(val) per type are the
+ * reference's.  Only where the range comes from is faked: NumericStats::HasMinMax / GetMin<T> / GetMax<T> normally
+ * read a BaseStatistics through duckdb::Value (the whole engine); here they return the harness' current range.
+ * The explicit specialisations have to be visible before the template that uses them is instantiated. */
+#include "duckdb/storage/statistics/numeric_stats.hpp"
+#include "duckdb/common/types/hugeint.hpp"
+#include "duckdb/common/types/uhugeint.hpp"
+namespace rpt_ref_fake {
+struct Range {
+	bool has_minmax;
+	unsigned char min[16], max[16];
+};
+static thread_local Range g_range;
+} // namespace rpt_ref_fake
+namespace duckdb {
+#define RPT_REF_MINMAX(T)                                                                                              \
+	template <>                                                                                                        \
+	T NumericStats::GetMin<T>(const BaseStatistics &) {                                                                \
+		T v;                                                                                                           \
+		memcpy(&v, rpt_ref_fake::g_range.min, sizeof(T));                                                              \
+		return v;                                                                                                      \
+	}                                                                                                                  \
+	template <>                                                                                                        \
+	T NumericStats::GetMax<T>(const BaseStatistics &) {                                                                \
+		T v;                                                                                                           \
+		memcpy(&v, rpt_ref_fake::g_range.max, sizeof(T));                                                              \
+		return v;                                                                                                      \
+	}
+RPT_REF_MINMAX(uint8_t)
+RPT_REF_MINMAX(uint16_t)
+RPT_REF_MINMAX(uint32_t)
+RPT_REF_MINMAX(uint64_t)
+RPT_REF_MINMAX(uhugeint_t)
+RPT_REF_MINMAX(int8_t)
+RPT_REF_MINMAX(int16_t)
+RPT_REF_MINMAX(int32_t)
+RPT_REF_MINMAX(int64_t)
+RPT_REF_MINMAX(hugeint_t)
+#undef RPT_REF_MINMAX
+bool NumericStats::HasMinMax(const BaseStatistics &) {
+	return rpt_ref_fake::g_range.has_minmax;
+}
+} // namespace duckdb
+
 #include "/root/reference/duckdb/src/planner/filter/bloom_filter.cpp"
+/* TrySubtractOperator::Operation<T> (subtract.cpp:98-175) and the 128-bit integer arithmetic it and the walk use */
+#include "/root/reference/duckdb/src/function/scalar/operator/subtract.cpp"
+#include "/root/reference/duckdb/src/common/types/hugeint.cpp"
+#include "/root/reference/duckdb/src/common/types/uhugeint.cpp"
 #include "/root/reference/duckdb/src/common/types/hash.cpp"
 #include "/root/reference/duckdb/src/common/vector_operations/vector_hash.cpp"
 #include "/root/reference/duckdb/src/common/constants.cpp"
@@ -51,6 +104,17 @@ string Exception::ConstructMessageRecursive(const string &msg, std::vector<Excep
 template <>
 ExceptionFormatValue ExceptionFormatValue::CreateFormatValue(const PhysicalType &) {
 	throw std::runtime_error("rpt ref harness: reference error path (PhysicalType)");
+}
+ExceptionFormatValue::ExceptionFormatValue(int64_t) { // NumericCast's "value out of range" message
+	throw std::runtime_error("rpt ref harness: reference error path (numeric cast)");
+}
+template <>
+ExceptionFormatValue ExceptionFormatValue::CreateFormatValue(const hugeint_t &) {
+	throw std::runtime_error("rpt ref harness: reference error path (hugeint)");
+}
+template <>
+ExceptionFormatValue ExceptionFormatValue::CreateFormatValue(const uhugeint_t &) {
+	throw std::runtime_error("rpt ref harness: reference error path (uhugeint)");
 }
 template <>
 ExceptionFormatValue ExceptionFormatValue::CreateFormatValue(const idx_t &) {
@@ -245,6 +309,53 @@ REF_API uint64_t ref_lookup_hashes(const uint64_t *words, uint64_t num_sectors, 
 	FakeVector v(const_cast<uint64_t *>(hashes));
 	SelectionVector selv(sel);
 	return f.get().LookupHashes(v.get(), selv, n);
+}
+
+/* BFTableFilter::CheckStatistics' type switch (bloom_filter.cpp:171-196) over the reference's own template.
+ * min / max: one value of the physical type (16 bytes {lower, upper} for the 128-bit types).
+ * Returns FilterPropagateResult: 0 NO_PRUNING_POSSIBLE, 1 FILTER_ALWAYS_TRUE, 2 FILTER_ALWAYS_FALSE. */
+REF_API int ref_check_statistics(const uint64_t *words, uint64_t num_sectors, int type, const void *min,
+                                 const void *max, int has_minmax) {
+	FakeFilter f(const_cast<uint64_t *>(words), num_sectors);
+	alignas(16) static unsigned char no_stats[256]; // never read: every accessor is faked above
+	const BaseStatistics &stats = *reinterpret_cast<const BaseStatistics *>(no_stats);
+	rpt_ref_fake::g_range.has_minmax = has_minmax != 0;
+	size_t width = 0;
+	switch (static_cast<PhysicalType>(type)) {
+	case PhysicalType::UINT8: case PhysicalType::INT8: width = 1; break;
+	case PhysicalType::UINT16: case PhysicalType::INT16: width = 2; break;
+	case PhysicalType::UINT32: case PhysicalType::INT32: width = 4; break;
+	case PhysicalType::UINT64: case PhysicalType::INT64: width = 8; break;
+	case PhysicalType::UINT128: case PhysicalType::INT128: width = 16; break;
+	default: break;
+	}
+	memcpy(rpt_ref_fake::g_range.min, min, width);
+	memcpy(rpt_ref_fake::g_range.max, max, width);
+	const BloomFilter &bf = f.get();
+	switch (static_cast<PhysicalType>(type)) { // bloom_filter.cpp:171-196
+	case PhysicalType::UINT8:
+		return static_cast<int>(TemplatedCheckStatistics<uint8_t>(bf, stats));
+	case PhysicalType::UINT16:
+		return static_cast<int>(TemplatedCheckStatistics<uint16_t>(bf, stats));
+	case PhysicalType::UINT32:
+		return static_cast<int>(TemplatedCheckStatistics<uint32_t>(bf, stats));
+	case PhysicalType::UINT64:
+		return static_cast<int>(TemplatedCheckStatistics<uint64_t>(bf, stats));
+	case PhysicalType::UINT128:
+		return static_cast<int>(TemplatedCheckStatistics<uhugeint_t>(bf, stats));
+	case PhysicalType::INT8:
+		return static_cast<int>(TemplatedCheckStatistics<int8_t>(bf, stats));
+	case PhysicalType::INT16:
+		return static_cast<int>(TemplatedCheckStatistics<int16_t>(bf, stats));
+	case PhysicalType::INT32:
+		return static_cast<int>(TemplatedCheckStatistics<int32_t>(bf, stats));
+	case PhysicalType::INT64:
+		return static_cast<int>(TemplatedCheckStatistics<int64_t>(bf, stats));
+	case PhysicalType::INT128:
+		return static_cast<int>(TemplatedCheckStatistics<hugeint_t>(bf, stats));
+	default:
+		return static_cast<int>(FilterPropagateResult::NO_PRUNING_POSSIBLE);
+	}
 }
 
 REF_API int ref_lookup_one(const uint64_t *words, uint64_t num_sectors, uint64_t hash) {

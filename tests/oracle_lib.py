@@ -179,6 +179,7 @@ class Ref:
             "ref_insert_hashes": (None, [_vp, _u64, _vp, _u64]),
             "ref_lookup_hashes": (_u64, [_vp, _u64, _vp, _u64, _vp]),
             "ref_lookup_one": (_int, [_vp, _u64, _u64]),
+            "ref_check_statistics": (_int, [_vp, _u64, _int, _vp, _vp, _int]),
             "ref_bench_build_i64": (C.c_double, [_vp, _u64, _vp, _u64, _int]),
             "ref_bench_probe_i64": (C.c_double, [_vp, _u64, _vp, _u64, _int, C.POINTER(_u64)]),
         }
@@ -188,6 +189,18 @@ class Ref:
 
     def hash_value(self, type_id, arr):
         return self.L.ref_hash_value(type_id, arr.ctypes.data)
+
+    def check_statistics(self, words, type_id, mins, maxs, has_minmax=None):
+        """The reference's own TemplatedCheckStatistics<T> (duckdb bloom_filter.cpp:138-196), one row group at a time."""
+        mins, maxs = np.ascontiguousarray(mins), np.ascontiguousarray(maxs)
+        count = mins.shape[0]
+        step = mins.nbytes // count if count else 0
+        out = np.zeros(count, dtype=np.uint8)
+        for i in range(count):
+            out[i] = self.L.ref_check_statistics(words.ctypes.data, words.shape[0], type_id,
+                                                 mins.ctypes.data + i * step, maxs.ctypes.data + i * step,
+                                                 1 if has_minmax is None else int(has_minmax[i]))
+        return out
 
     def hash_string(self, b):
         return self.L.ref_hash_string(b, len(b))

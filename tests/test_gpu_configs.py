@@ -129,3 +129,99 @@ def test_config4_star_join_cascade(rpt, oracle):
     assert sel.size < m // 20  # the cascade prunes most of the fact table before the joins
     for bf, _ in filters:
         bf.close()
+
+
+def test_config3_full_size_against_oracle(rpt, oracle):
+    """BASELINE config 3 at full size: 5·10^7 build rows (k1 int64, k2 = decimal text of k1) → two
+    single-column 128 MiB filters, built once with est_rows = 5·10^7 and once with est_rows = 10^7 (the resize rule
+    of PhysicalCreateBF::Finalize, physical_create_bf.cpp:386-406, re-allocates and re-hashes both,
+    src/bloom_filter.cpp:34-58); 5·10^8 probe rows at 10 % members, filter 2 on filter 1's survivors.
+    Words of both filters equal the oracle's; the selection vectors equal the oracle's on two 2·10^7-row windows;
+    size-independent properties (ascending, every member kept) on the whole."""
+    import ctypes as C
+    import torch
+    assert torch.cuda.is_available()
+    n, m, ppm = 50_000_000, 500_000_000, 100_000
+    dev = "cuda:0"
+    k1 = torch.empty(n, dtype=torch.int64, device=dev)
+    rpt.synth_build_keys(k1, 0, n)
+    torch.cuda.synchronize()
+    ko, kb, kbytes = rpt.synth_decimal_text(k1)
+    torch.cuda.synchronize()
+    c_k1 = rpt.device_col(k1, rpt.INT64)
+    c_k2 = rpt.device_col(ko, rpt.VARCHAR, aux=kb, aux_bytes=kbytes, data_len=n)
+    # the oracle's copy of the build side (the generated text is spot-checked against Python's formatting)
+    h_k1 = k1.cpu().numpy()
+    h_ko, h_kb = ko.cpu().numpy().view(np.uint32), kb.cpu().numpy()[:kbytes]
+    for i in (0, 1, 12345, n - 1):
+        assert h_kb[h_ko[i]:h_ko[i + 1]].tobytes() == b"%d" % int(h_k1[i])
+    w1 = oracle.new_filter(n)
+    oracle.bench_build(w1, h_k1, 8)
+    w2 = oracle.new_filter(n)
+    oracle.insert(w2, [rpt.host_varchar_col(h_ko, h_kb)], n)
+
+    f1, f2 = rpt.PTBloomFilter(0), rpt.PTBloomFilter(0)
+    for est in (n, n // 5):
+        f1.Initialize(est)
+        f2.Initialize(est)
+        f1.Insert(c_k1, n)
+        f2.Insert(c_k2, n)
+        rebuilt = (f1.Finalize(n, c_k1, n), f2.Finalize(n, c_k2, n))
+        assert rebuilt == (est != n, est != n) and rebuilt[0] == oracle.needs_rebuild(est, n)
+        assert f1.num_sectors == f2.num_sectors == 1 << 24
+        assert np.array_equal(f1.ExportWords(), w1), est
+        assert np.array_equal(f2.ExportWords(), w2), est
+    del h_k1, h_ko, h_kb
+
+    p1 = torch.empty(m, dtype=torch.int64, device=dev)
+    rpt.synth_probe_keys(p1, 0, m, n, ppm)
+    torch.cuda.synchronize()
+    BATCH = 200_000_000  # 32-bit VARCHAR offsets: a call carries < 4 GiB of string bytes
+    sel1 = torch.empty(BATCH, dtype=torch.int32, device=dev)
+    sel2 = torch.empty(BATCH, dtype=torch.int32, device=dev)
+    found = torch.zeros(2, dtype=torch.int64, device=dev)
+    all1, all2, texts = [], [], {}
+    for r0 in range(0, m, BATCH):
+        r1 = min(r0 + BATCH, m)
+        mb = r1 - r0
+        po, pb, pbytes = rpt.synth_decimal_text(p1[r0:r1])
+        texts[r0] = (po, pb)
+        c_p1 = rpt.device_col(p1[r0:r1], rpt.INT64)
+        c_p2 = rpt.device_col(po, rpt.VARCHAR, aux=pb, aux_bytes=pbytes, data_len=mb)
+        torch.cuda.synchronize()
+        f1.LookupSelDevice(c_p1, mb, sel1, found[0:1])
+        f1.Sync()
+        n1 = int(found[0].item())
+        rpt._check(rpt.lib().rpt_bf_filter_sel(f2._h, C.byref(c_p2.raw), sel1.data_ptr(), n1, sel2.data_ptr(),
+                                               found[1:2].data_ptr(), rpt.MEM_DEVICE, None))
+        f2.Sync()
+        n2 = int(found[1].item())
+        all1.append((sel1[:n1].long() & 0xFFFFFFFF) + r0)
+        all2.append((sel2[:n2].long() & 0xFFFFFFFF) + r0)
+    s1, s2 = torch.cat(all1), torch.cat(all2)
+    n1, n2 = s1.numel(), s2.numel()
+    assert bool((s1[1:] > s1[:-1]).all()) and bool((s2[1:] > s2[:-1]).all())
+    member = p1 >= 0
+    n_member = int(member.sum().item())
+    assert int(member[s2].sum().item()) == n_member          # no false negatives through the cascade
+    assert n_member <= n2 <= n1 < n_member + (m - n_member) // 200
+    del member
+    W = 2 * 10**7
+    for start in (0, m - W):
+        r0 = start // BATCH * BATCH
+        po, pb = texts[r0]
+        a0 = start - r0
+        hp1 = p1[start:start + W].cpu().numpy()
+        b0, b1 = int(po[a0].item()), int(po[a0 + W].item())
+        hoff = (po[a0:a0 + W + 1].cpu().numpy().view(np.uint32).astype(np.int64) - b0).astype(np.uint32)
+        hblob = pb[b0:b1].cpu().numpy()
+        c1 = rpt.host_col(hp1)
+        want1 = oracle.probe(w1, [c1], W)
+        got1 = (s1[(s1 >= start) & (s1 < start + W)] - start).cpu().numpy().astype(np.uint32)
+        assert np.array_equal(got1, want1), start
+        c2 = rpt.host_varchar_col(hoff, hblob, sel=want1)
+        want2 = want1[oracle.probe(w2, [c2], want1.size)]   # BFTableFilter::Filter translates through the incoming sel
+        got2 = (s2[(s2 >= start) & (s2 < start + W)] - start).cpu().numpy().astype(np.uint32)
+        assert np.array_equal(got2, want2), start
+    f1.close()
+    f2.close()

@@ -993,3 +993,132 @@ def test_flat_varchar_staged_hashing(rpt, oracle, shape, torch_cuda):
     f = int(dfound.item())
     assert f == want.size and np.array_equal(dsel[:f].cpu().numpy().view(np.uint32), want)
     bf.close()
+
+
+# ---------------------------------------------------------------------------------------------------------
+# round 2: NULL / unreferenced string_t payloads, concurrent handles of different sizes, fused min/max, checksum
+# ---------------------------------------------------------------------------------------------------------
+def test_string_t_null_rows_with_poisoned_payload(rpt, oracle):
+    """A NULL row's string_t is undefined in DuckDB and the reference never reads it (TightLoopHash:
+    `is_null ? NULL_HASH : Hash(input)`, vector_hash.cpp:43-61).  The NULL entries here carry 0xFF in every byte
+    (a 4 GiB length and a wild pointer): the library must not dereference them, flat or through a selection."""
+    rng = np.random.default_rng(4301)
+    n = 6007
+    offs, blob = random_strings(rng, n, max_len=30)
+    strs = [blob[offs[i]:offs[i + 1]].tobytes() for i in range(n)]
+    arr, keep = make_string_t(strs)
+    valid_bits = rng.random(n) < 0.8
+    validity = np.zeros((n + 63) // 64, dtype=np.uint64)
+    for i in np.nonzero(valid_bits)[0]:
+        validity[i >> 6] |= np.uint64(1) << np.uint64(i & 63)
+    for i in np.nonzero(~valid_bits)[0]:
+        arr[i * 16:(i + 1) * 16] = 0xFF
+    col = rpt.KeyCol(rpt.RptCol(arr.ctypes.data, None, None, validity.ctypes.data, n, 0, rpt.STRING_T, rpt.MEM_HOST),
+                     (arr, keep, validity))
+    ref_col = rpt.host_varchar_col(offs, blob, validity=validity)
+    want = oracle.new_filter(n)
+    oracle.insert(want, [ref_col], n)
+    bf = gpu_filter(rpt, n)
+    bf.Insert(col, n)
+    assert np.array_equal(bf.ExportWords(), want)
+    assert np.array_equal(bf.LookupSel(col, n), oracle.probe(want, [ref_col], n))
+    # through a selection that references only some entries: the unreferenced ones are poisoned as well
+    m = 3001
+    sel = rng.choice(np.nonzero(valid_bits)[0], size=m).astype(np.uint32)
+    arr2 = arr.copy()
+    unref = np.ones(n, dtype=bool)
+    unref[sel] = False
+    for i in np.nonzero(unref)[0]:
+        arr2[i * 16:(i + 1) * 16] = 0xFF
+    col2 = rpt.KeyCol(rpt.RptCol(arr2.ctypes.data, None, sel.ctypes.data, None, n, 0, rpt.STRING_T, rpt.MEM_HOST),
+                      (arr2, keep, sel))
+    ref2 = rpt.host_varchar_col(offs, blob, sel=sel)
+    assert np.array_equal(bf.LookupSel(col2, m), oracle.probe(want, [ref2], m))
+    # a selection entry beyond data_len is an error, not a wild read
+    bad = sel.copy()
+    bad[7] = n + 5
+    col3 = rpt.KeyCol(rpt.RptCol(arr2.ctypes.data, None, bad.ctypes.data, None, n, 0, rpt.STRING_T, rpt.MEM_HOST),
+                      (arr2, keep, bad))
+    with pytest.raises(rpt.RptError):
+        bf.LookupSel(col3, m)
+    bf.close()
+
+
+def test_concurrent_probes_on_handles_of_different_sizes(rpt, oracle):
+    """Two README-sized filters of different S (both shared-memory staged) probed from two host threads at the same
+    time: the dynamic shared-memory limit of the kernels is raised once to the device maximum, never per launch to
+    this filter's size, so one thread cannot lower it under the other's launch."""
+    import threading
+    rng = np.random.default_rng(909)
+    sizes = [3000, 80000]  # S = 2^10 and 2^14 sectors
+    filters, words, probes = [], [], []
+    for est in sizes:
+        keys = rng.integers(-2**62, 2**62, est).astype(np.int64)
+        bf = gpu_filter(rpt, est)
+        bf.Insert(rpt.host_col(keys), est)
+        w = oracle.new_filter(est)
+        oracle.insert(w, rpt.host_col(keys), est)
+        assert np.array_equal(bf.ExportWords(), w)
+        filters.append(bf)
+        words.append(w)
+        probes.append(np.where(rng.random(600_011) < 0.3, keys[rng.integers(0, est, 600_011)],
+                               rng.integers(-2**62, 2**62, 600_011)).astype(np.int64))
+    errors, got = [], [None, None]
+
+    def run(t):
+        try:
+            for _ in range(20):
+                got[t] = filters[t].LookupSel(rpt.host_col(probes[t]), probes[t].size)
+        except Exception as e:  # noqa: BLE001
+            errors.append(e)
+
+    threads = [threading.Thread(target=run, args=(t,)) for t in range(2)]
+    [t.start() for t in threads]
+    [t.join() for t in threads]
+    assert not errors, errors
+    for t in range(2):
+        assert np.array_equal(got[t], oracle.probe(words[t], rpt.host_col(probes[t]), probes[t].size))
+        filters[t].close()
+
+
+def test_minmax_is_fused_into_the_build_kernel(rpt, torch_cuda):
+    """UpdateMinMax runs next to the insert on the same chunk (physical_create_bf.cpp:220-239): with range tracking on,
+    a single-column insert launches exactly as many kernels as without (the range is folded in by build_kernel)."""
+    torch = torch_cuda
+    n = 3_000_017
+    keys = torch.randint(-2**62, 2**62, (n,), dtype=torch.int64, device="cuda:0")
+    plain = gpu_filter(rpt, n)
+    plain.Insert(rpt.device_col(keys, rpt.INT64), n)
+    plain.Sync()
+    tracked = gpu_filter(rpt, n)
+    tracked.MinMaxBegin(rpt.INT64)
+    tracked.Insert(rpt.device_col(keys, rpt.INT64), n)
+    has, nan, lo, hi = tracked.MinMaxGet()
+    assert has and not nan and int(lo) == int(keys.min().item()) and int(hi) == int(keys.max().item())
+    assert tracked.launch_count == plain.launch_count
+    assert np.array_equal(tracked.ExportWords(), plain.ExportWords())
+    # a filter large enough for sector-range passes: the range is folded in once, by the first pass
+    big = gpu_filter(rpt, 100_000_000)
+    big.MinMaxBegin(rpt.INT64)
+    big.Insert(rpt.device_col(keys, rpt.INT64), n)
+    has, nan, lo, hi = big.MinMaxGet()
+    assert has and int(lo) == int(keys.min().item()) and int(hi) == int(keys.max().item())
+    for f in (plain, tracked, big):
+        f.close()
+
+
+def test_checksum_known_answers(rpt):
+    """rpt_bf_checksum = FNV-1a-64 per word (xor, then multiply), the recipe of SURVEY §8(c) and of the golden
+    vectors' "fnv1a_words" (test_golden_filters ties that fold to reference-made filters) — equal to the test
+    helper's fold of the exported words.  (The survey's own checksum value
+    for this filter could not be reproduced by anyone, see tests/test_oracle_cpu.py; the words are pinned directly.)"""
+    n = 100_000
+    bf = gpu_filter(rpt, n)
+    bf.Insert(rpt.host_col(np.arange(n, dtype=np.int64) * 2), n)
+    assert bf.Checksum() == fnv_words(bf.ExportWords())
+    g0 = bf.words_generation
+    bf.Reset(n)
+    assert bf.words_generation == g0          # same S: nothing reallocated
+    bf.Reset(10 * n)
+    assert bf.words_generation == g0 + 1      # new S: peers must re-open their mappings
+    bf.close()
