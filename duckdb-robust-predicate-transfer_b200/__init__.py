@@ -102,6 +102,9 @@ _SIGNATURES = {
     "rpt_abf_device_blocks": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p)]),
     "rpt_abf_sync": (C.c_int, [C.c_void_p]),
     "rpt_abf_launch_count": (C.c_int, [C.c_void_p, C.POINTER(C.c_longlong)]),
+    "rpt_bf_peer_merge_range": (C.c_int, [C.c_void_p, C.c_int, C.c_uint64, C.c_uint64, C.c_void_p]),
+    "rpt_bf_slice_sectors": (C.c_int, [C.POINTER(C.c_uint64)]),
+    "rpt_bf_set_slice_events": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p), C.c_int]),
     "rpt_bf_checksum": (C.c_int, [C.c_void_p, C.POINTER(C.c_uint64)]),
     "rpt_bf_words_generation": (C.c_int, [C.c_void_p, C.POINTER(C.c_uint64)]),
     "rpt_synth_build_keys": (C.c_int, [C.c_void_p, C.c_uint64, C.c_uint64, C.c_int, C.c_void_p]),
@@ -129,6 +132,12 @@ def lib():
 def _check(rc):
     if rc != 0:
         raise RptError(lib().rpt_gpu_last_error().decode("utf-8", "replace"))
+
+
+def slice_sectors():
+    out = C.c_uint64(0)
+    _check(lib().rpt_bf_slice_sectors(C.byref(out)))
+    return out.value
 
 
 def device_count():
@@ -390,6 +399,14 @@ class PTBloomFilter:
 
     def PeerMergePhase(self, phase, stream=None):
         _check(lib().rpt_bf_peer_merge_phase(self._h, phase, stream))
+
+    def PeerMergeRange(self, phase, first_sector, nsectors, stream=None):
+        _check(lib().rpt_bf_peer_merge_range(self._h, phase, first_sector, nsectors, stream))
+
+    def SetSliceEvents(self, events):
+        """events: raw cudaEvent_t handles (ints), one per 64 MiB slice; [] clears the gates."""
+        arr = (C.c_void_p * max(len(events), 1))(*[C.c_void_p(int(e)) for e in events])
+        _check(lib().rpt_bf_set_slice_events(self._h, arr, len(events)))
 
     def PeerClose(self):
         _check(lib().rpt_bf_peer_close(self._h))

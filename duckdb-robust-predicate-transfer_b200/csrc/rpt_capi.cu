@@ -137,6 +137,8 @@ struct rpt_bf {
 	MinMaxState *mm_dev = nullptr;
 	int mm_type = 0;
 	std::atomic<int> mm_active {0};
+	// slice gates of an overlapped multi-GPU merge (rpt_bf_set_slice_events); n == 0: none
+	SliceGate gate {{nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr}, 0};
 	// peer merge state
 	std::vector<uint64_t *> peer_words;
 	std::vector<bool> peer_ipc;
@@ -1022,7 +1024,7 @@ static int probe_impl(const rpt_bf *bf, const rpt_col_t *cols, int ncols, uint64
 		RPT_TRY(run_prehash(bf->dev, pre, &dc, s, &launches));
 		if (out_mem == RPT_MEM_DEVICE) { // fully asynchronous
 			RPT_CUDA(launch_probe(bf->dev, dc, count, bf->words, bf->num_sectors, sel_out, found_out, 0, translate,
-			                      scratch, s, &launches));
+			                      scratch, s, &launches, bf->gate.n ? &bf->gate : nullptr));
 			mbf->launches += launches;
 			return 0;
 		}
@@ -1030,7 +1032,8 @@ static int probe_impl(const rpt_bf *bf, const rpt_col_t *cols, int ncols, uint64
 		RPT_TRY(st.alloc(&dsel, count * sizeof(uint32_t)));
 		RPT_TRY(st.alloc(&dfound, sizeof(uint64_t)));
 		RPT_CUDA(launch_probe(bf->dev, dc, count, bf->words, bf->num_sectors, reinterpret_cast<uint32_t *>(dsel),
-		                      reinterpret_cast<uint64_t *>(dfound), 0, translate, scratch, s, &launches));
+		                      reinterpret_cast<uint64_t *>(dfound), 0, translate, scratch, s, &launches,
+		                      bf->gate.n ? &bf->gate : nullptr));
 		mbf->launches += launches;
 		RPT_CUDA(cudaMemcpyAsync(found_out, dfound, sizeof(uint64_t), cudaMemcpyDeviceToHost, s));
 		RPT_CUDA(cudaStreamSynchronize(s));
@@ -1475,18 +1478,13 @@ static void peer_slice(uint64_t S, int n, int r, uint64_t *off, uint64_t *len) {
 	*len = b - a;
 }
 
-int rpt_bf_peer_merge_phase(rpt_bf_t *bf, int phase, rpt_stream_t stream) {
-	if (!bf) {
-		return set_error("null filter handle");
-	}
-	if (bf->peer_rank < 0) {
-		return set_error("rpt_bf_peer_open has not been called");
-	}
-	RPT_GUARD(bf);
-	cudaStream_t s = pick_stream(bf, stream);
+// One phase of the two-phase merge restricted to the sectors [first, first + nsectors): inside the range rank r owns
+// the r-th of N sub-slices.  Phase 0 (reduce-scatter-OR): my sub-slice |= every peer's copy of it, read over NVLink.
+// Phase 1 (all-gather): pull every other rank's reduced sub-slice.
+static int peer_merge_range(rpt_bf *bf, int phase, uint64_t first, uint64_t nsectors, cudaStream_t s) {
 	const int n = static_cast<int>(bf->peer_words.size());
 	const int rank = bf->peer_rank;
-	if (phase == 0) { // reduce-scatter-OR: my slice |= every peer's copy of my slice, read over NVLink
+	if (phase == 0) {
 		PtrList srcs;
 		srcs.n = 0;
 		for (int r = 0; r < n; r++) {
@@ -1495,24 +1493,69 @@ int rpt_bf_peer_merge_phase(rpt_bf_t *bf, int phase, rpt_stream_t stream) {
 			}
 		}
 		uint64_t off, len;
-		peer_slice(bf->num_sectors, n, rank, &off, &len);
-		RPT_CUDA(launch_or_ptrs(bf->dev, bf->words, srcs, off, len, s));
+		peer_slice(nsectors, n, rank, &off, &len);
+		RPT_CUDA(launch_or_ptrs(bf->dev, bf->words, srcs, first + off, len, s));
 		bf->launches += 1;
 		return 0;
 	}
-	if (phase == 1) { // all-gather: pull every other rank's reduced slice
+	if (phase == 1) {
 		for (int k = 1; k < n; k++) {
 			const int r = (rank + k) % n; // staggered so that ranks do not all read the same peer at once
 			uint64_t off, len;
-			peer_slice(bf->num_sectors, n, r, &off, &len);
+			peer_slice(nsectors, n, r, &off, &len);
 			if (len) {
-				RPT_CUDA(cudaMemcpyAsync(bf->words + off, bf->peer_words[r] + off, len * sizeof(uint64_t),
+				RPT_CUDA(cudaMemcpyAsync(bf->words + first + off, bf->peer_words[r] + first + off, len * sizeof(uint64_t),
 				                         cudaMemcpyDeviceToDevice, s));
 			}
 		}
 		return 0;
 	}
 	return set_error("phase must be 0 or 1");
+}
+
+int rpt_bf_peer_merge_phase(rpt_bf_t *bf, int phase, rpt_stream_t stream) {
+	if (!bf) {
+		return set_error("null filter handle");
+	}
+	if (bf->peer_rank < 0) {
+		return set_error("rpt_bf_peer_open has not been called");
+	}
+	RPT_GUARD(bf);
+	return peer_merge_range(bf, phase, 0, bf->num_sectors, pick_stream(bf, stream));
+}
+
+int rpt_bf_peer_merge_range(rpt_bf_t *bf, int phase, uint64_t first_sector, uint64_t nsectors, rpt_stream_t stream) {
+	if (!bf) {
+		return set_error("null filter handle");
+	}
+	if (bf->peer_rank < 0) {
+		return set_error("rpt_bf_peer_open has not been called");
+	}
+	if ((first_sector & 1) || (nsectors & 1) || first_sector + nsectors > bf->num_sectors) {
+		return set_error("sector range [%llu, +%llu) must be even-aligned and inside the filter",
+		                 (unsigned long long)first_sector, (unsigned long long)nsectors);
+	}
+	RPT_GUARD(bf);
+	return peer_merge_range(bf, phase, first_sector, nsectors, pick_stream(bf, stream));
+}
+
+int rpt_bf_slice_sectors(uint64_t *out) {
+	if (!out) {
+		return set_error("null argument");
+	}
+	*out = kSliceSectors;
+	return 0;
+}
+
+int rpt_bf_set_slice_events(rpt_bf_t *bf, void *const *events, int n) {
+	if (!bf || n < 0 || n > 8 || (n > 0 && !events)) {
+		return set_error("rpt_bf_set_slice_events: n must be in [0, 8]");
+	}
+	for (int i = 0; i < 8; i++) {
+		bf->gate.ev[i] = i < n ? reinterpret_cast<cudaEvent_t>(events[i]) : nullptr;
+	}
+	bf->gate.n = n;
+	return 0;
 }
 
 int rpt_bf_peer_close(rpt_bf_t *bf) {

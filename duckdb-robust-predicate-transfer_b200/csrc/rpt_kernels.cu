@@ -1793,6 +1793,30 @@ cudaError_t launch_build(const DeviceInfo &dev, const DevCols &cols, uint64_t co
 	           : launch_build_t<GenericSrc, false>(dev, src, count, words, num_sectors, mm, mm_signed, stream, launches);
 }
 
+// Slice gates (multi-GPU merge overlapped with the probe, rpt_bf_set_slice_events): events[s] fires when sectors
+// [s·kSliceSectors, (s+1)·kSliceSectors) of the filter hold their final (merged) words.  A probe launcher makes the
+// stream wait for slice s right before the first kernel that reads it: the partition kernel only looks slice 0 up,
+// bucket kernel s only slice s, sector-range pass p only slice p — so the merge of the later slices runs on another
+// stream underneath the partition kernel.
+static thread_local const SliceGate *t_gate = nullptr;
+static cudaError_t wait_slices(cudaStream_t stream, int first, int last /* inclusive; <0: all */) {
+	if (!t_gate || t_gate->n == 0) {
+		return cudaSuccess;
+	}
+	if (last < 0 || last >= t_gate->n) {
+		last = t_gate->n - 1;
+	}
+	for (int s = first; s <= last; s++) {
+		if (t_gate->ev[s]) {
+			const cudaError_t e = cudaStreamWaitEvent(stream, t_gate->ev[s], 0);
+			if (e != cudaSuccess) {
+				return e;
+			}
+		}
+	}
+	return cudaSuccess;
+}
+
 // Small probes: the fused look-back kernel (one launch + one memset).
 template <class Src, int BLOCK, bool SMEM>
 static cudaError_t launch_probe_fused(const DeviceInfo &dev, const Src &src, uint64_t count, const uint64_t *words,
@@ -1824,6 +1848,10 @@ static cudaError_t launch_probe_fused(const DeviceInfo &dev, const Src &src, uin
 	}
 	uint64_t *desc = reinterpret_cast<uint64_t *>(scratch);
 	unsigned int *ticket = reinterpret_cast<unsigned int *>(desc + num_tiles);
+	e = wait_slices(stream, 0, -1);
+	if (e != cudaSuccess) {
+		return e;
+	}
 	e = cudaMemsetAsync(scratch, 0, (num_tiles + 1) * sizeof(uint64_t), stream);
 	if (e != cudaSuccess) {
 		return e;
@@ -1878,6 +1906,12 @@ static cudaError_t launch_probe_phased(const DeviceInfo &dev, const Src &src, ui
 	for (uint64_t lo = 0; lo < num_sectors; lo += slice) {
 		const uint64_t len = lo + slice < num_sectors ? slice : num_sectors - lo;
 		const bool last = lo + slice >= num_sectors;
+		// a pass reads the sectors [lo, lo + len): the gates of the 64 MiB slices it touches
+		e = wait_slices(stream, static_cast<int>(lo / kSliceSectors),
+		                SLICED ? static_cast<int>((lo + len - 1) / kSliceSectors) : -1);
+		if (e != cudaSuccess) {
+			return e;
+		}
 		pass<<<static_cast<unsigned>(grid), BLOCK, smem, stream>>>(src, words, sector_mask, count, num_segs,
 		                                                          static_cast<uint32_t>(lo), static_cast<uint32_t>(len),
 		                                                          bitmap, lo == 0 ? 1 : 0, last ? seg_offsets : nullptr);
@@ -1933,6 +1967,10 @@ static cudaError_t launch_probe_partitioned(const DeviceInfo &dev, const Src &sr
 	uint16_t *bucket_counts = reinterpret_cast<uint16_t *>(extra);
 	uint2 *buckets = reinterpret_cast<uint2 *>(extra + align_up((P - 1) * num_segs * sizeof(uint16_t), 256));
 	const uint64_t bucket_stride = num_segs * CAP;
+	e = wait_slices(stream, 0, 0); // the partition kernel looks up slice-0 keys only
+	if (e != cudaSuccess) {
+		return e;
+	}
 	part<<<static_cast<unsigned>(grid), BLOCK, smem, stream>>>(src, words, static_cast<uint32_t>(num_sectors - 1), count,
 	                                                          num_segs, bitmap, buckets, bucket_stride, bucket_counts);
 	int bper_sm = 0;
@@ -1944,6 +1982,10 @@ static cudaError_t launch_probe_partitioned(const DeviceInfo &dev, const Src &sr
 	const uint64_t bwant = ceil_div(num_segs, 8);
 	bgrid = bgrid < bwant ? bgrid : bwant;
 	for (int s = 1; s < P; s++) {
+		e = wait_slices(stream, s, s);
+		if (e != cudaSuccess) {
+			return e;
+		}
 		bucket<<<static_cast<unsigned>(bgrid), 256, 0, stream>>>(buckets + (s - 1) * bucket_stride,
 		                                                        bucket_counts + (s - 1) * num_segs, num_segs, words,
 		                                                        static_cast<uint32_t>(s) << kSliceShift,
@@ -2006,9 +2048,24 @@ static cudaError_t launch_probe_src(const DeviceInfo &dev, const Src &src, uint6
 #undef RPT_PROBE_ARGS
 }
 
+static cudaError_t launch_probe_gated(const DeviceInfo &dev, const DevCols &cols, uint64_t count, const uint64_t *words,
+                                      uint64_t num_sectors, uint32_t *sel_out, uint64_t *found_out, uint32_t row_offset,
+                                      const uint32_t *translate, void *scratch, cudaStream_t stream, int *launches);
+
 cudaError_t launch_probe(const DeviceInfo &dev, const DevCols &cols, uint64_t count, const uint64_t *words,
                          uint64_t num_sectors, uint32_t *sel_out, uint64_t *found_out, uint32_t row_offset,
-                         const uint32_t *translate, void *scratch, cudaStream_t stream, int *launches) {
+                         const uint32_t *translate, void *scratch, cudaStream_t stream, int *launches,
+                         const SliceGate *gate) {
+	t_gate = gate;
+	const cudaError_t e = launch_probe_gated(dev, cols, count, words, num_sectors, sel_out, found_out, row_offset,
+	                                         translate, scratch, stream, launches);
+	t_gate = nullptr;
+	return e;
+}
+
+static cudaError_t launch_probe_gated(const DeviceInfo &dev, const DevCols &cols, uint64_t count, const uint64_t *words,
+                                      uint64_t num_sectors, uint32_t *sel_out, uint64_t *found_out, uint32_t row_offset,
+                                      const uint32_t *translate, void *scratch, cudaStream_t stream, int *launches) {
 	if (count == 0) {
 		return cudaMemsetAsync(found_out, 0, sizeof(uint64_t), stream);
 	}

@@ -67,9 +67,16 @@ cudaError_t launch_build(const DeviceInfo &dev, const DevCols &cols, uint64_t co
 // bloom_filter.cpp:50-61,72-78).  `scratch` holds probe_scratch_bytes(count) bytes; it is zeroed
 // here.  row_offset is added to every emitted row id; translate (optional) maps a row id through
 // an incoming selection (BFTableFilter::Filter, bloom_filter.cpp:117-123).
+// gate (optional): per-64-MiB-slice events the probe waits for right before the first kernel that reads the slice
+// (multi-GPU merge overlapped with the probe).
+struct SliceGate {
+	cudaEvent_t ev[8]; // S ≤ 2^26 sectors = 8 slices of kSliceSectors
+	int n;
+};
 cudaError_t launch_probe(const DeviceInfo &dev, const DevCols &cols, uint64_t count, const uint64_t *words,
                          uint64_t num_sectors, uint32_t *sel_out, uint64_t *found_out, uint32_t row_offset,
-                         const uint32_t *translate, void *scratch, cudaStream_t stream, int *launches);
+                         const uint32_t *translate, void *scratch, cudaStream_t stream, int *launches,
+                         const SliceGate *gate = nullptr);
 
 // words[i] |= parts[p*S + i] for p < nparts
 cudaError_t launch_or_parts(const DeviceInfo &dev, uint64_t *words, const uint64_t *parts, uint64_t num_sectors,

@@ -20,6 +20,8 @@ memory (rpt_bf_peer_*), `allgather` = NCCL all-gather of the partial filters + o
 `engine` is the object that provides PTBloomFilter; the default is this package (CUDA, no CPU fallback).
 The CPU test-suite injects an oracle-backed stand-in so that the host logic here runs under gloo.
 """
+import os
+
 import numpy as np
 
 
@@ -108,6 +110,9 @@ class ShardedBloomFilter:
             return
         import torch
         self._release_pending = False
+        if getattr(self, "_side_pending", False):  # an overlapped merge may still be pulling slices on its stream
+            torch.cuda.current_stream().wait_stream(self._merge_stream)
+            self._side_pending = False
         self.device_barrier()
         if stream is None:
             torch.cuda.current_stream().synchronize()
@@ -187,6 +192,40 @@ class ShardedBloomFilter:
                 raw = allb.cpu().numpy().tobytes()
                 self.bf.PeerOpen([raw[64 * r:64 * (r + 1)] for r in range(self.world)], self.rank)
                 self._peer_open_for = words
+            S = self.bf.num_sectors
+            slice_sectors = self.engine.slice_sectors() if hasattr(self.engine, "slice_sectors") else S
+            nslices = -(-S // slice_sectors)
+            overlap = defer_release and nslices > 1 and hasattr(self.bf, "PeerMergeRange") and \
+                os.environ.get("RPT_MERGE_OVERLAP", "1") != "0"
+            if overlap:
+                # Slice by slice on a side stream; the probe that follows on the main stream waits per slice
+                # (rpt_bf_set_slice_events): its partition kernel needs slice 0 only, so the merge of slices 1.. runs
+                # underneath it instead of in front of it.
+                main = torch.cuda.current_stream()
+                if not hasattr(self, "_merge_stream"):
+                    self._merge_stream = torch.cuda.Stream(device=torch.device("cuda", self.device))
+                    self._slice_events = [torch.cuda.Event() for _ in range(8)]
+                side = self._merge_stream
+                side.wait_stream(main)            # my partial filter is complete
+                with torch.cuda.stream(side):
+                    if self._any_data is None:    # every rank's partial filter is complete (+ the has-data flag)
+                        total = self._flag_barrier(has_local)
+                    else:
+                        total = None
+                        self.device_barrier()
+                    for sl in range(nslices):
+                        lo = sl * slice_sectors
+                        ln = min(slice_sectors, S - lo)
+                        self.bf.PeerMergeRange(0, lo, ln, side.cuda_stream)
+                        self.device_barrier()     # slice sl is reduced on every rank
+                        self.bf.PeerMergeRange(1, lo, ln, side.cuda_stream)
+                        self._slice_events[sl].record(side)
+                self.bf.SetSliceEvents([self._slice_events[sl].cuda_event for sl in range(nslices)])
+                self._side_pending = True         # the next mutation of the words waits for the side stream
+                self._release_pending = True
+                if total is not None:
+                    self._any_data = True if has_local else int(total.item()) > 0
+                return
             if self._any_data is None:            # every partial filter is complete (+ the has-data flag)
                 total = self._flag_barrier(has_local)
                 self._any_data = True if has_local else int(total.item()) > 0

@@ -219,6 +219,17 @@ RPT_API int rpt_bf_ipc_export(const rpt_bf_t *bf, void *handle64);
 RPT_API int rpt_bf_peer_open(rpt_bf_t *bf, const void *handles64, int nranks, int rank);
 RPT_API int rpt_bf_peer_merge_phase(rpt_bf_t *bf, int phase, rpt_stream_t stream);
 RPT_API int rpt_bf_peer_close(rpt_bf_t *bf);
+/* The same two phases restricted to the sectors [first_sector, first_sector + nsectors) (both even): the merge can
+ * then proceed slice by slice on a side stream while the probe already runs — see rpt_bf_set_slice_events. */
+RPT_API int rpt_bf_peer_merge_range(rpt_bf_t *bf, int phase, uint64_t first_sector, uint64_t nsectors,
+                                    rpt_stream_t stream);
+/* Sectors per slice of the large-filter probe paths (2^23 = 64 MiB). */
+RPT_API int rpt_bf_slice_sectors(uint64_t *out);
+/* Overlapping the merge with the probe: events[s] (cudaEvent_t, n ≤ 8) is recorded by the caller once slice s
+ * (sectors [s·slice, (s+1)·slice)) holds its merged words.  Until cleared (n = 0), every probe on this handle makes
+ * its stream wait for events[s] right before the first kernel that reads slice s — the partition kernel needs slice 0
+ * only, the s-th bucket kernel / sector-range pass only slice s — instead of requiring the whole merge up front. */
+RPT_API int rpt_bf_set_slice_events(rpt_bf_t *bf, void *const *events, int n);
 /* One process driving several GPUs (the DuckDB-extension deployment): OR-allreduce in place over
  * peer access; all filters must have the same S. */
 RPT_API int rpt_bf_allreduce_or(rpt_bf_t **per_gpu, int ngpu);

@@ -63,6 +63,15 @@ ncu_lab)    # full ncu capture of one prototype kernel: ncu_lab <tag> <kernel re
 		-o gpurun_out/ncu_lab_${tag} -f tools/part_lab "$@" > gpurun_out/ncu_lab_${tag}.log 2>&1
 	echo "rc=$?"; tail -3 gpurun_out/ncu_lab_${tag}.log
 	;;
+e2e)        # configs 1 / 4 / 5 through DuckDB + the GPU-backed reference extension, diffed against plain DuckDB
+	tag=${1:-r2}
+	timeout 900 python integration/e2e/run_e2e.py --ext gpu > gpurun_out/e2e_${tag}_default.jsonl 2>&1
+	echo "e2e default rc=$?"; cat gpurun_out/e2e_${tag}_default.jsonl | cut -c1-600
+	timeout 1500 python integration/e2e/run_e2e.py --ext gpu --tpch-sf ${2:-10} --job-scale ${3:-4} --live-baseline --only config > gpurun_out/e2e_${tag}_large.jsonl 2>&1
+	echo "e2e large rc=$?"; cat gpurun_out/e2e_${tag}_large.jsonl | cut -c1-600
+	timeout 900 python integration/e2e/run_e2e.py --ext stock --tpch-sf ${2:-10} --job-scale ${3:-4} --out gpurun_out/stock > gpurun_out/e2e_${tag}_large_stock.jsonl 2>&1
+	cat gpurun_out/e2e_${tag}_large_stock.jsonl | cut -c1-300
+	;;
 tests)      # the GPU parity suite
 	timeout 2400 python -m pytest tests -m gpu -x -q > gpurun_out/tests_${1:-r2}.log 2>&1
 	echo "tests rc=$?" >> gpurun_out/tests_${1:-r2}.log
