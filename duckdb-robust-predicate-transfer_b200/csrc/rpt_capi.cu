@@ -1113,7 +1113,8 @@ static int probe_impl(const rpt_bf *bf, const rpt_col_t *cols, int ncols, uint64
 			RPT_TRY(run_prehash(bf->dev, pre, &dc, mbf->compute, &launches));
 			const uint32_t *translate = translate_col0 ? dc.c[0].sel : nullptr;
 			RPT_CUDA(launch_probe(bf->dev, dc, r1 - r0, bf->words, bf->num_sectors, sl.dsel, sl.dfound,
-			                      static_cast<uint32_t>(r0), translate, scratch, mbf->compute, &launches));
+			                      static_cast<uint32_t>(r0), translate, scratch, mbf->compute, &launches,
+			                      bf->gate.n ? &bf->gate : nullptr));
 			RPT_CUDA(cudaMemcpyAsync(sl.hfound, sl.dfound, sizeof(uint64_t), cudaMemcpyDeviceToHost, mbf->compute));
 			RPT_CUDA(cudaEventRecord(sl.computed, mbf->compute));
 			sl.pending = true;

@@ -933,7 +933,8 @@ __global__ void __launch_bounds__(BLOCK, 2)
     probe_partition_kernel(const Src src, const uint64_t *__restrict__ filter, const uint32_t sector_mask,
                            const uint64_t count, const uint64_t num_segs, uint16_t *__restrict__ bitmap16,
                            uint2 *__restrict__ buckets, const uint64_t bucket_stride /* records per slice array */,
-                           uint16_t *__restrict__ bucket_counts /* (P-1) × num_segs */) {
+                           uint16_t *__restrict__ bucket_counts /* (P-1) × num_segs */,
+                           uint32_t *__restrict__ ovf_list /* [0] = count, [1 + i] = i-th overflowed segment */) {
 	constexpr int NWARPS = BLOCK / 32;
 	constexpr bool STAGED = Src::kStageable;
 	using Geo = StageGeo<Src::kKeyBytes>;
@@ -1124,6 +1125,12 @@ __global__ void __launch_bounds__(BLOCK, 2)
 					const uint32_t sector = static_cast<uint32_t>(h[i]) & sector_mask;
 					hits |= sector_test(__ldg(filter + sector), static_cast<uint32_t>(h[i] >> 32)) << i;
 				}
+				// Under an overlapped multi-GPU merge (slice gates) this kernel may only trust slice 0: the lookups
+				// above may have read slices whose merge is still in flight, so the segment is also put on the list
+				// that probe_overflow_kernel re-evaluates behind every gate.
+				if (ovf_list != nullptr && lane == 0) {
+					ovf_list[1u + atomicAdd(ovf_list, 1u)] = static_cast<uint32_t>(cur);
+				}
 			}
 			hits &= valid;
 			if (staged_seg) {
@@ -1156,6 +1163,34 @@ __global__ void __launch_bounds__(BLOCK, 2)
 	}
 	if (STAGED) {
 		cp_async_wait<0>();
+	}
+}
+
+// Segments the partition kernel could not place (a region would have overflowed: skewed keys): warp per listed
+// segment, every key hashed again from the source and looked up wherever its sector lies.  Runs after the bucket
+// kernels, i.e. behind every slice gate; the hot sectors of skewed keys are L2 hits.
+template <class Src>
+__global__ void __launch_bounds__(256)
+    probe_overflow_kernel(const Src src, const uint64_t *__restrict__ filter, const uint32_t sector_mask,
+                          const uint64_t count, const uint32_t *__restrict__ overflow, uint16_t *__restrict__ bitmap16) {
+	const uint32_t lane = threadIdx.x & 31u;
+	const uint64_t pol_keys = policy_evict_first();
+	const uint32_t n = __ldg(overflow);
+	const uint32_t warp_global = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+	const uint32_t num_warps = (gridDim.x * blockDim.x) >> 5;
+	for (uint32_t i = warp_global; i < n; i += num_warps) {
+		const uint64_t seg = __ldg(overflow + 1 + i);
+		const uint64_t row0 = seg * kSegRows + lane * 16;
+		uint32_t hits = 0;
+#pragma unroll 4
+		for (int k = 0; k < 16; k++) {
+			if (row0 + k < count) {
+				const uint64_t h = src.hash_at(row0 + k, pol_keys);
+				const uint32_t sector = static_cast<uint32_t>(h) & sector_mask;
+				hits |= sector_test(__ldg(filter + sector), static_cast<uint32_t>(h >> 32)) << k;
+			}
+		}
+		bitmap16[seg * 32 + lane] = static_cast<uint16_t>(hits);
 	}
 }
 
@@ -1695,10 +1730,11 @@ static inline int partition_choice(uint64_t num_sectors) {
 static inline int partition_cap(int slices) {
 	return slices == 2 ? PartCfg<2>::CAP : (slices == 4 ? PartCfg<4>::CAP : PartCfg<8>::CAP);
 }
-// extra scratch behind the phased layout: [bucket counts u16 × (P-1)·segs][records 8 B × (P-1)·segs·CAP]
+// extra scratch behind the phased layout:
+// [bucket counts u16 × (P-1)·segs][overflow list u32 × (1 + segs)][records 8 B × (P-1)·segs·CAP]
 static size_t partition_scratch_bytes(uint64_t count, int slices) {
 	const uint64_t num_segs = ceil_div(count, kSegRows);
-	return align_up((slices - 1) * num_segs * sizeof(uint16_t), 256) +
+	return align_up((slices - 1) * num_segs * sizeof(uint16_t), 256) + align_up((num_segs + 1) * sizeof(uint32_t), 256) +
 	       (slices - 1) * num_segs * partition_cap(slices) * sizeof(uint2);
 }
 
@@ -1804,6 +1840,11 @@ static cudaError_t wait_slices(cudaStream_t stream, int first, int last /* inclu
 		return cudaSuccess;
 	}
 	if (last < 0 || last >= t_gate->n) {
+		last = t_gate->n - 1;
+	}
+	static const bool gate_all = getenv("RPT_GATE_ALL") != nullptr; // debugging: every kernel waits for every slice
+	if (gate_all) {
+		first = 0;
 		last = t_gate->n - 1;
 	}
 	for (int s = first; s <= last; s++) {
@@ -1956,6 +1997,18 @@ static cudaError_t launch_probe_partitioned(const DeviceInfo &dev, const Src &sr
 		return cudaErrorLaunchOutOfResources;
 	}
 	uint64_t grid = static_cast<uint64_t>(dev.sm_count) * per_sm;
+	const bool gated = t_gate != nullptr && t_gate->n > 0;
+	if (gated) {
+		// The persistent CTAs of this kernel fill every SM's register file (2 × 256 threads × 128 registers), so the
+		// merge kernels of the later slices, which become runnable while it runs, would find no SM to start on and
+		// the "overlap" would serialise behind it.  A slightly smaller grid leaves a few SMs half empty for them.
+		static const int pct = [] {
+			const char *e = getenv("RPT_GATED_GRID_PCT");
+			const int v = e ? atoi(e) : 94;
+			return v < 10 ? 10 : (v > 100 ? 100 : v);
+		}();
+		grid = grid * pct / 100;
+	}
 	const uint64_t want = ceil_div(num_segs, BLOCK / 32);
 	grid = grid < want ? grid : want;
 	const PhasedLayout lay = phased_layout(count);
@@ -1965,14 +2018,23 @@ static cudaError_t launch_probe_partitioned(const DeviceInfo &dev, const Src &sr
 	uint16_t *bitmap = reinterpret_cast<uint16_t *>(base + lay.off_hitbits);
 	char *extra = base + align_up(lay.bytes, 256);
 	uint16_t *bucket_counts = reinterpret_cast<uint16_t *>(extra);
-	uint2 *buckets = reinterpret_cast<uint2 *>(extra + align_up((P - 1) * num_segs * sizeof(uint16_t), 256));
+	extra += align_up((P - 1) * num_segs * sizeof(uint16_t), 256);
+	uint32_t *overflow = reinterpret_cast<uint32_t *>(extra);
+	uint2 *buckets = reinterpret_cast<uint2 *>(extra + align_up((num_segs + 1) * sizeof(uint32_t), 256));
 	const uint64_t bucket_stride = num_segs * CAP;
+	if (gated) {
+		e = cudaMemsetAsync(overflow, 0, sizeof(uint32_t), stream);
+		if (e != cudaSuccess) {
+			return e;
+		}
+	}
 	e = wait_slices(stream, 0, 0); // the partition kernel looks up slice-0 keys only
 	if (e != cudaSuccess) {
 		return e;
 	}
 	part<<<static_cast<unsigned>(grid), BLOCK, smem, stream>>>(src, words, static_cast<uint32_t>(num_sectors - 1), count,
-	                                                          num_segs, bitmap, buckets, bucket_stride, bucket_counts);
+	                                                          num_segs, bitmap, buckets, bucket_stride, bucket_counts,
+	                                                          gated ? overflow : nullptr);
 	int bper_sm = 0;
 	e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bper_sm, bucket, 256, 0);
 	if (e != cudaSuccess) {
@@ -1991,6 +2053,10 @@ static cudaError_t launch_probe_partitioned(const DeviceInfo &dev, const Src &sr
 		                                                        static_cast<uint32_t>(s) << kSliceShift,
 		                                                        reinterpret_cast<uint32_t *>(bitmap));
 	}
+	if (gated) { // overflowed segments (normally a handful) once more, behind every slice gate by now
+		probe_overflow_kernel<Src><<<static_cast<unsigned>(dev.sm_count), 256, 0, stream>>>(
+		    src, words, static_cast<uint32_t>(num_sectors - 1), count, overflow, bitmap);
+	}
 	count_segments_kernel<<<stream_grid(dev, num_segs, 256), 256, 0, stream>>>(
 	    reinterpret_cast<const uint4 *>(bitmap), num_segs, seg_offsets);
 	const uint64_t nblocks = ceil_div(num_segs, kScanBlock);
@@ -2001,7 +2067,7 @@ static cudaError_t launch_probe_partitioned(const DeviceInfo &dev, const Src &sr
 	compact_bitmap_kernel<<<static_cast<unsigned>(cwant < ccap ? cwant : ccap), 256, 0, stream>>>(
 	    reinterpret_cast<const uint32_t *>(bitmap), seg_offsets, block_totals, num_segs, sel_out, row_offset, translate);
 	if (launches) {
-		(*launches) += P + 4;
+		(*launches) += P + 4 + (gated ? 1 : 0);
 	}
 	return cudaGetLastError();
 }

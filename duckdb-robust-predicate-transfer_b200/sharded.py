@@ -195,12 +195,16 @@ class ShardedBloomFilter:
             S = self.bf.num_sectors
             slice_sectors = self.engine.slice_sectors() if hasattr(self.engine, "slice_sectors") else S
             nslices = -(-S // slice_sectors)
+            # Overlapped variant (RPT_MERGE_OVERLAP=1; OFF by default — measured, it does not pay: the probe's partition
+            # kernel is DRAM-bound and fills every SM, so the merge of the later slices only moves into the probe:
+            # N=2 8.34-8.37 ms per step overlapped vs 8.36 ms plain, N=8 9.11 vs 8.50 ms;
+            # profiles/merge_overlap_r2.md).
             overlap = defer_release and nslices > 1 and hasattr(self.bf, "PeerMergeRange") and \
-                os.environ.get("RPT_MERGE_OVERLAP", "1") != "0"
+                os.environ.get("RPT_MERGE_OVERLAP", "0") == "1"
             if overlap:
                 # Slice by slice on a side stream; the probe that follows on the main stream waits per slice
-                # (rpt_bf_set_slice_events): its partition kernel needs slice 0 only, so the merge of slices 1.. runs
-                # underneath it instead of in front of it.
+                # (rpt_bf_set_slice_events): its partition kernel needs slice 0 only, so the merge of slices 1.. is
+                # enqueued underneath it instead of in front of it.
                 main = torch.cuda.current_stream()
                 if not hasattr(self, "_merge_stream"):
                     self._merge_stream = torch.cuda.Stream(device=torch.device("cuda", self.device))

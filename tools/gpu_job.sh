@@ -72,6 +72,31 @@ e2e)        # configs 1 / 4 / 5 through DuckDB + the GPU-backed reference extens
 	timeout 900 python integration/e2e/run_e2e.py --ext stock --tpch-sf ${2:-10} --job-scale ${3:-4} --out gpurun_out/stock > gpurun_out/e2e_${tag}_large_stock.jsonl 2>&1
 	cat gpurun_out/e2e_${tag}_large_stock.jsonl | cut -c1-300
 	;;
+pcie)       # raw pinned H2D/D2H with N concurrent processes: pcie <tag> <maxN>
+	tag=$1; maxn=$2
+	: > gpurun_out/pcie_matrix_${tag}.jsonl
+	for n in 1 2 4 8; do
+		[ $n -le $maxn ] || continue
+		timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port 29521 \
+			tools/pcie_matrix.py 2>/dev/null | grep "^{" >> gpurun_out/pcie_matrix_${tag}.jsonl
+	done
+	nvidia-smi topo -m > gpurun_out/topo_${tag}.txt 2>&1; lscpu | head -25 >> gpurun_out/topo_${tag}.txt
+	cat gpurun_out/pcie_matrix_${tag}.jsonl | cut -c1-900
+	;;
+benchN)     # multi-GPU bench under torchrun: benchN <tag> <N> [extra bench args]
+	tag=$1; n=$2; shift 2
+	timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port 29517 \
+		bench.py --gpus $n --no-cpu "$@" > gpurun_out/bench_${tag}_n${n}.json 2> gpurun_out/bench_${tag}_n${n}.err
+	echo "benchN rc=$?"; cut -c1-300 gpurun_out/bench_${tag}_n${n}.json; tail -5 gpurun_out/bench_${tag}_n${n}.err
+	python - <<PY
+import json
+try:
+    d = json.loads(open("gpurun_out/bench_${tag}_n${n}.json").read())
+    print({k: d[k] for k in ("value", "ms_per_step", "n_gpus")}, d["detail"]["build_ms"], d["detail"]["merge_ms"], d["detail"]["probe_ms"], d["detail"]["parity"], d.get("e2e", {}).get("value"), d["detail"].get("sustained", {}).get("value"))
+except Exception as e:
+    print("no line:", e)
+PY
+	;;
 tests)      # the GPU parity suite
 	timeout 2400 python -m pytest tests -m gpu -x -q > gpurun_out/tests_${1:-r2}.log 2>&1
 	echo "tests rc=$?" >> gpurun_out/tests_${1:-r2}.log
