@@ -877,6 +877,143 @@ __global__ void __launch_bounds__(BLOCK, MINB)
 	}
 }
 
+// ---- shared-memory filters, flat key columns: bulk-copy (TMA) staging, 24 warps per SM ---------------------------
+// Regime 1 (F ≤ 128 KiB) of a staged source.  probe_bitmap_kernel's 8 KiB of cp.async double buffer per warp leave
+// room for 12 warps next to a 128 KiB filter, and with 3 warps per scheduler the kernel was issue/latency-bound
+// (ncu r1w: 59 % issue, 4.8 TB/s).  Here the filter arrives through ONE bulk copy per CTA (cp.async.bulk, SASS
+// UBLKCP) and a warp's keys through bulk copies of HALF segments (256 rows) into two 2 KiB buffers, each guarded by
+// its own mbarrier and refilled by one elected lane as soon as the warp has consumed it — 4 KiB per warp, 24 warps.
+// Lane l owns rows 8l … 8l+7 of a half, i.e. one BYTE of the row-ordered bitmap; its 16-byte units are read in the
+// rotated order of StageGeo (bank-conflict-free LDS.128) and the 8-bit hit mask is rotated back.
+__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
+	asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(static_cast<uint32_t>(__cvta_generic_to_shared(bar))),
+	             "r"(count)
+	             : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
+	asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(
+	                 static_cast<uint32_t>(__cvta_generic_to_shared(bar))),
+	             "r"(bytes)
+	             : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
+	asm volatile("{\n"
+	             ".reg .pred p;\n"
+	             "WAIT_%=:\n"
+	             "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+	             "@p bra DONE_%=;\n"
+	             "bra WAIT_%=;\n"
+	             "DONE_%=:\n"
+	             "}" ::"r"(static_cast<uint32_t>(__cvta_generic_to_shared(bar))),
+	             "r"(parity)
+	             : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void *smem_dst, const void *gmem_src, uint32_t bytes, uint64_t *bar,
+                                         uint64_t pol) {
+	asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;" ::
+	                 "r"(static_cast<uint32_t>(__cvta_generic_to_shared(smem_dst))),
+	             "l"(gmem_src), "r"(bytes), "r"(static_cast<uint32_t>(__cvta_generic_to_shared(bar))), "l"(pol)
+	             : "memory");
+}
+
+constexpr int kSmemProbeWarps = 24;
+constexpr uint32_t kHalfRows = 256;
+
+template <class Src, int NWARPS>
+__global__ void __launch_bounds__(NWARPS * 32, 1)
+    probe_smem_kernel(const Src src, const uint64_t *__restrict__ filter, const uint32_t sector_mask, const uint64_t count,
+                      const uint64_t num_segs, uint8_t *__restrict__ bitmap8, uint32_t *__restrict__ seg_counts) {
+	static_assert(Src::kStageable, "flat key columns only");
+	constexpr int KB = Src::kKeyBytes;
+	constexpr int KPU = 16 / KB;                     // keys per 16-byte unit
+	constexpr uint32_t HALF_BYTES = kHalfRows * KB;  // 2048 / 1024
+	constexpr int LU = 8 / KPU;                      // 16-byte units a lane owns per half: 4 / 2
+	extern __shared__ __align__(128) unsigned char s_dyn[];
+	__shared__ __align__(8) uint64_t s_bars[NWARPS][2];
+	__shared__ __align__(8) uint64_t s_fbar;
+	const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+	const uint32_t filter_bytes = (sector_mask + 1u) * 8u;
+	const uint64_t *const s_filter = reinterpret_cast<const uint64_t *>(s_dyn);
+	unsigned char *const kbuf = s_dyn + filter_bytes + warp * 2u * HALF_BYTES;
+	const uint64_t pol_keys = policy_evict_first();
+	const uint64_t pol_filter = policy_evict_last();
+	if (threadIdx.x == 0) {
+		mbar_init(&s_fbar, 1);
+	}
+	if (lane == 0) {
+		mbar_init(&s_bars[warp][0], 1);
+		mbar_init(&s_bars[warp][1], 1);
+	}
+	asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+	__syncthreads();
+	if (threadIdx.x == 0) { // the whole filter: one bulk copy
+		mbar_expect_tx(&s_fbar, filter_bytes);
+		bulk_g2s(s_dyn, filter, filter_bytes, &s_fbar, pol_filter);
+	}
+	const uint64_t full_segs = count / kSegRows;
+	const uint64_t stride = static_cast<uint64_t>(gridDim.x) * NWARPS;
+	const unsigned char *const keys = reinterpret_cast<const unsigned char *>(src.key_ptr());
+	auto issue = [&](uint64_t seg, uint32_t h) { // elected lane: stage half h of segment seg
+		if (seg < full_segs) {
+			mbar_expect_tx(&s_bars[warp][h], HALF_BYTES);
+			bulk_g2s(kbuf + h * HALF_BYTES, keys + (seg * kSegRows + h * kHalfRows) * KB, HALF_BYTES, &s_bars[warp][h],
+			         pol_keys);
+		}
+	};
+	const uint64_t seg0 = static_cast<uint64_t>(blockIdx.x) * NWARPS + warp;
+	if (lane == 0) {
+		issue(seg0, 0);
+		issue(seg0, 1);
+	}
+	mbar_wait(&s_fbar, 0);
+	const uint32_t rot = LU == 4 ? ((lane >> 1) & 3u) : ((lane >> 2) & 1u);
+	uint32_t phase = 0;
+	for (uint64_t seg = seg0; seg < num_segs; seg += stride) {
+		uint32_t total = 0;
+#pragma unroll
+		for (uint32_t h = 0; h < 2; h++) {
+			uint32_t hits = 0;
+			if (seg < full_segs) {
+				mbar_wait(&s_bars[warp][h], (phase >> h) & 1u);
+				phase ^= 1u << h;
+				const uint4 *mine = reinterpret_cast<const uint4 *>(kbuf + h * HALF_BYTES) + lane * LU;
+				uint64_t hh[8];
+#pragma unroll
+				for (int u = 0; u < LU; u++) {
+					Src::hash_unit(mine[(u + rot) & (LU - 1)], hh + u * KPU);
+				}
+				if (Src::kNullable) {
+					const uint32_t v = __ldg(reinterpret_cast<const unsigned char *>(src.validity) + seg * 64 + h * 32 + lane);
+					const uint32_t twice = v | (v << 8); // slot i holds logical bit (i + KPU·rot) mod 8: rotate right
+					null_fix<8>(hh, (twice >> (KPU * rot)) & 0xffu, 0);
+				}
+				hits = test_batch<8, true, false>(hh, filter, s_filter, sector_mask, pol_filter, 0u, 0u);
+				const uint32_t twice = hits | (hits << 8); // slot order → row order: rotate left by KPU·rot
+				hits = (twice >> (8u - KPU * rot)) & 0xffu;
+				__syncwarp(); // every lane's keys are consumed: the buffer may be refilled
+				if (lane == 0) {
+					issue(seg + stride, h);
+				}
+			} else { // the partial last segment: straight from global memory
+				const uint64_t row0 = seg * kSegRows + h * kHalfRows + lane * 8u;
+#pragma unroll
+				for (int i = 0; i < 8; i++) {
+					if (row0 + i < count) {
+						const uint64_t hv = src.hash_at(row0 + i, pol_keys);
+						hits |= sector_test(s_filter[static_cast<uint32_t>(hv) & sector_mask], static_cast<uint32_t>(hv >> 32)) << i;
+					}
+				}
+			}
+			bitmap8[seg * 64 + h * 32 + lane] = static_cast<uint8_t>(hits);
+			total += __popc(hits);
+		}
+		total = __reduce_add_sync(0xffffffffu, total);
+		if (lane == 0) {
+			seg_counts[seg] = total;
+		}
+	}
+}
+
 // ---- filters beyond one L2-resident slice: partition once, then probe slice by slice -----------------------
 // The sector-range passes above re-read the 8-byte key column once per slice (4× at F = 256 MiB: ncu r1c 42 GB
 // of DRAM traffic for 8.7 GB of algorithmic bytes, each pass DRAM-bound).  This path reads the keys ONCE:
@@ -1913,11 +2050,52 @@ static cudaError_t launch_probe_phased(const DeviceInfo &dev, const Src &src, ui
                                        uint64_t num_sectors, uint32_t *sel_out, uint64_t *found_out,
                                        uint32_t row_offset, const uint32_t *translate, void *scratch,
                                        cudaStream_t stream, int *launches) {
-	// shared-memory filter: one CTA per SM at the top size, so the CTA is as large as the key buffers allow
-	// (12 warps × 8 KiB next to a 128 KiB filter; 8 warps issued at 59 %, ncu profiles/ncu_smem_r1w.md)
+	const uint64_t num_segs = ceil_div(count, kSegRows);
+	if constexpr (SMEM && Src::kStageable) {
+		// regime 1 of a flat column: bulk-copy staged kernel, 24 warps next to the filter
+		constexpr int NW = kSmemProbeWarps;
+		cudaError_t e = ensure_max_dyn_smem<probe_smem_kernel<Src, NW>>(dev);
+		if (e != cudaSuccess) {
+			return e;
+		}
+		const size_t smem = num_sectors * sizeof(uint64_t) + static_cast<size_t>(NW) * 2 * kHalfRows * Src::kKeyBytes;
+		int per_sm = 0;
+		e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, probe_smem_kernel<Src, NW>, NW * 32, smem);
+		if (e != cudaSuccess) {
+			return e;
+		}
+		if (per_sm < 1) {
+			return cudaErrorLaunchOutOfResources;
+		}
+		uint64_t grid = static_cast<uint64_t>(dev.sm_count) * per_sm;
+		const uint64_t want = ceil_div(num_segs, NW);
+		grid = grid < want ? grid : want;
+		const PhasedLayout lay = phased_layout(count);
+		char *base = reinterpret_cast<char *>(scratch);
+		uint32_t *seg_offsets = reinterpret_cast<uint32_t *>(base);
+		uint32_t *block_totals = reinterpret_cast<uint32_t *>(base + lay.off_totals);
+		uint8_t *bitmap = reinterpret_cast<uint8_t *>(base + lay.off_hitbits);
+		e = wait_slices(stream, 0, -1);
+		if (e != cudaSuccess) {
+			return e;
+		}
+		probe_smem_kernel<Src, NW><<<static_cast<unsigned>(grid), NW * 32, smem, stream>>>(
+		    src, words, static_cast<uint32_t>(num_sectors - 1), count, num_segs, bitmap, seg_offsets);
+		const uint64_t nblocks = ceil_div(num_segs, kScanBlock);
+		scan_blocks_kernel<<<static_cast<unsigned>(nblocks), 1024, 0, stream>>>(seg_offsets, num_segs, block_totals);
+		scan_totals_kernel<<<1, 1024, 0, stream>>>(block_totals, static_cast<uint32_t>(nblocks), found_out);
+		const uint64_t cwant = ceil_div((num_segs + 1) / 2, 8ull);
+		const uint64_t ccap = static_cast<uint64_t>(dev.sm_count) * 6;
+		compact_bitmap_kernel<<<static_cast<unsigned>(cwant < ccap ? cwant : ccap), 256, 0, stream>>>(
+		    reinterpret_cast<const uint32_t *>(bitmap), seg_offsets, block_totals, num_segs, sel_out, row_offset, translate);
+		if (launches) {
+			(*launches) += 4;
+		}
+		return cudaGetLastError();
+	} else {
+	// shared-memory filter of a generic source: one CTA per SM at the top size
 	constexpr int BLOCK = SMEM ? kProbeBlockSmemPhased : kProbeBlock;
 	auto pass = probe_bitmap_kernel<Src, BLOCK, MINB, UNITS, SMEM, SLICED>;
-	const uint64_t num_segs = ceil_div(count, kSegRows);
 	const size_t smem = (Src::kStageable ? static_cast<size_t>(BLOCK / 32) * 2 * kSegRows * Src::kKeyBytes : 0) +
 	                    (SMEM ? num_sectors * sizeof(uint64_t) : 0);
 	cudaError_t e = ensure_max_dyn_smem<probe_bitmap_kernel<Src, BLOCK, MINB, UNITS, SMEM, SLICED>>(dev);
@@ -1971,6 +2149,7 @@ static cudaError_t launch_probe_phased(const DeviceInfo &dev, const Src &src, ui
 		(*launches) += 3;
 	}
 	return cudaGetLastError();
+	}
 }
 
 template <class Src, int P>

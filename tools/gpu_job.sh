@@ -56,6 +56,13 @@ part4)      # v4 prototype sweep
 	done
 	cat $out
 	;;
+ncu_py)     # full ncu capture of product kernels: ncu_py <tag> <kernel regex> <skip> <count> <python script + args...>
+	tag=$1; rx=$2; skip=$3; cnt=$4; shift 4
+	timeout 300 python "$@" > gpurun_out/ncu_${tag}_plain.log 2>&1 &&
+	timeout 1200 ncu --set full --clock-control none --import-source on -k regex:$rx -s $skip -c $cnt \
+		-o gpurun_out/ncu_${tag} -f python "$@" > gpurun_out/ncu_${tag}.log 2>&1
+	echo "rc=$?"; tail -3 gpurun_out/ncu_${tag}.log
+	;;
 ncu_lab)    # full ncu capture of one prototype kernel: ncu_lab <tag> <kernel regex> <part_lab args...>
 	tag=$1; rx=$2; shift 2
 	timeout -s KILL 120 tools/part_lab "$@" > gpurun_out/ncu_lab_${tag}_plain.log 2>&1 &&
