@@ -68,6 +68,8 @@ _SIGNATURES = {
                                   C.POINTER(C.c_int), C.c_void_p]),
     "rpt_bf_probe": (C.c_int, [C.c_void_p, C.POINTER(RptCol), C.c_int, C.c_uint64, C.c_void_p, C.c_void_p, C.c_int,
                                C.c_void_p]),
+    "rpt_bf_probe_u64_noalloc": (C.c_int, [C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p,
+                                           C.c_int, C.c_void_p]),
     "rpt_bf_filter_sel": (C.c_int, [C.c_void_p, C.POINTER(RptCol), C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p,
                                     C.c_int, C.c_void_p]),
     "rpt_bf_lookup_hashes_host": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p]),
@@ -288,6 +290,12 @@ class PTBloomFilter:
         arr, n = _col_array(cols)
         _check(lib().rpt_bf_probe(self._h, arr, n, count, _ptr(sel_out_ptr), _ptr(found_out_ptr), MEM_DEVICE,
                                   stream))
+
+    def LookupSelNoAlloc(self, keys_ptr, count, sel_out_ptr, found_out_ptr, stream=None):
+        """rpt_bf_probe_u64_noalloc: the allocation-free probe of one non-NULL 64-bit device key column (no reference
+        counterpart; count <= NOALLOC_MAX_ROWS; calls on one device share a static scratch and must not overlap)."""
+        _check(lib().rpt_bf_probe_u64_noalloc(self.device_words, self.num_sectors, _ptr(keys_ptr), count,
+                                              _ptr(sel_out_ptr), _ptr(found_out_ptr), self.device, stream))
 
     def FilterSel(self, key, in_sel, approved_count):
         """BFTableFilter::Filter (duckdb bloom_filter.cpp:94-131) on host buffers."""

@@ -6,7 +6,7 @@ import subprocess
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.environ.get("RPT_GPU_LIB") or os.path.join(HERE, "librpt_gpu.so")
-SOURCES = ["rpt_kernels.cu", "rpt_stats.cu", "rpt_acero.cu", "rpt_capi.cu"]
+SOURCES = ["rpt_kernels.cu", "rpt_stats.cu", "rpt_acero.cu", "rpt_capi.cu", "rpt_noalloc.cu"]
 HEADERS = ["rpt_hash.cuh", "rpt_kernels.cuh", os.path.join("..", "..", "include", "rpt_gpu.h")]
 
 NVCC_FLAGS = [

@@ -41,6 +41,13 @@ static int set_error(const char *fmt, ...) {
 	return 1;
 }
 
+// for the library's other translation units (rpt_noalloc.cu): same thread-local message, same status
+namespace rpt {
+int report_error(const char *msg) {
+	return set_error("%s", msg);
+}
+} // namespace rpt
+
 #define RPT_CUDA(expr)                                                                                                 \
 	do {                                                                                                               \
 		cudaError_t _e = (expr);                                                                                       \

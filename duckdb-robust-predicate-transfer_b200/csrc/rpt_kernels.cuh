@@ -145,4 +145,7 @@ cudaError_t launch_synth_build(uint64_t *out, uint64_t first, uint64_t count, cu
 cudaError_t launch_synth_probe(uint64_t *out, uint64_t first, uint64_t count, uint64_t n_build, uint32_t sel_ppm,
                                cudaStream_t stream);
 
+// sets rpt_gpu_last_error() from another translation unit of the library (defined in rpt_capi.cu); returns 1
+int report_error(const char *msg);
+
 } // namespace rpt

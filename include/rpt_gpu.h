@@ -162,6 +162,19 @@ RPT_API int rpt_bf_minmax_get(const rpt_bf_t *bf, int *has_value, int *has_nan, 
  *     are filled (key columns may be host or device). */
 RPT_API int rpt_bf_probe(const rpt_bf_t *bf, const rpt_col_t *cols, int ncols, uint64_t count, uint32_t *sel_out,
                          uint64_t *found_out, int out_mem, rpt_stream_t stream);
+/* Allocation-free probe.  NO COUNTERPART IN THE REFERENCE: added for callers
+ * that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Same result as rpt_bf_probe with one non-NULL 64-bit integer key column in device memory and device outputs
+ * (ascending row ids to dev_sel_out[0..found), found to *dev_found_out), asynchronous on `stream` of `device`; the
+ * filter is passed as its words (rpt_bf_device_words) and sector count (rpt_bf_num_sectors, a power of two).
+ * Calls no cudaMalloc / cudaFree / allocating routine: the scratch (bitmap + block counts, 2 MiB + 32 KiB) is a
+ * static __device__ array that every GPU which loads the library holds until exit.  count > RPT_NOALLOC_MAX_ROWS is
+ * rejected with an error (split the batch, or use rpt_bf_probe).  All calls on a device SHARE the array: calls that
+ * overlap on the GPU (different streams or threads) race; order them on one stream or with events. */
+#define RPT_NOALLOC_MAX_ROWS (1ull << 24)
+RPT_API int rpt_bf_probe_u64_noalloc(const uint64_t *dev_words, uint64_t num_sectors, const uint64_t *dev_keys,
+                                     uint64_t count, uint32_t *dev_sel_out, uint64_t *dev_found_out, int device,
+                                     rpt_stream_t stream);
 /* Scan-side form: BFTableFilter::Filter (duckdb bloom_filter.cpp:94-131).  The key column is read
  * through an incoming selection `in_sel` (approved_count entries, may be NULL = identity) and the
  * output is translated back through it: sel_out[k] = in_sel[flat_k] (lines :117-123). */
