@@ -1039,12 +1039,16 @@ __global__ void __launch_bounds__(NWARPS * 32, 1)
 constexpr uint32_t kSliceShift = 23; // log2(kSliceSectors)
 static_assert((1ULL << kSliceShift) == kSliceSectors, "record layout assumes 2^23-sector slices");
 
-template <int P>
+// INLINE0: the keys of slice 0 are looked up by the partition kernel itself (P-1 bucket regions per segment);
+// otherwise slice 0 is a bucket like the others (P regions, no filter access in the partition kernel).
+template <int P, bool INLINE0 = true>
 struct PartCfg {
-	static_assert(P == 2 || P == 4 || P == 8, "S is a power of two: 2, 4 or 8 slices of 64 MiB");
+	static_assert(P == 2 || P == 4 || P == 8, "S is a power of two: 2, 4 or 8 slices");
 	// records per (segment, slice) region; expectation 512/P, σ = sqrt(512·(1/P)(1-1/P)): +5.6σ / +4.1σ / +4.3σ
 	static constexpr int CAP = P == 2 ? 320 : (P == 4 ? 168 : 96);
-	static constexpr int STAGE_BYTES = (P - 1) * CAP * 8;
+	static constexpr int FIRST = INLINE0 ? 1 : 0; // first slice that has a bucket
+	static constexpr int REGIONS = P - FIRST;
+	static constexpr int STAGE_BYTES = REGIONS * CAP * 8;
 	static constexpr int NCNT = P <= 4 ? 1 : 2; // per-lane counters: 8 bits per slice, four slices per register
 };
 
@@ -1052,11 +1056,12 @@ struct PartCfg {
 // stage.  When the stage fits into one key buffer it ALIASES the buffer of the segment being processed (its
 // keys are in registers by then), which keeps a warp at 8 KiB.  Two CTAs per SM: at three (80 registers) the
 // sixteen hashes spill, and the spill traffic on the LSU costs more than the extra warps hide (9.0 vs 7.3 ms).
-template <class Src, int P>
+template <class Src, int P, bool INLINE0 = true>
 struct PartSmem {
 	static constexpr int KEY_SEG_BYTES = Src::kStageable ? static_cast<int>(kSegRows) * Src::kKeyBytes : 0;
-	static constexpr bool ALIAS = Src::kStageable && PartCfg<P>::STAGE_BYTES <= KEY_SEG_BYTES;
-	static constexpr int WARP_BYTES = 2 * KEY_SEG_BYTES + (ALIAS ? 0 : (PartCfg<P>::STAGE_BYTES + 15) / 16 * 16);
+	static constexpr bool ALIAS = Src::kStageable && PartCfg<P, INLINE0>::STAGE_BYTES <= KEY_SEG_BYTES;
+	static constexpr int WARP_BYTES =
+	    2 * KEY_SEG_BYTES + (ALIAS ? 0 : (PartCfg<P, INLINE0>::STAGE_BYTES + 15) / 16 * 16);
 };
 
 __device__ __forceinline__ uint32_t shl_clamp(uint32_t v, uint32_t s) { // PTX shl.b32: a shift ≥ 32 yields 0
@@ -1065,7 +1070,7 @@ __device__ __forceinline__ uint32_t shl_clamp(uint32_t v, uint32_t s) { // PTX s
 	return d;
 }
 
-template <class Src, int BLOCK, int P>
+template <class Src, int BLOCK, int P, int SHIFT = kSliceShift, bool INLINE0 = true>
 __global__ void __launch_bounds__(BLOCK, 2)
     probe_partition_kernel(const Src src, const uint64_t *__restrict__ filter, const uint32_t sector_mask,
                            const uint64_t count, const uint64_t num_segs, uint16_t *__restrict__ bitmap16,
@@ -1075,10 +1080,12 @@ __global__ void __launch_bounds__(BLOCK, 2)
 	constexpr int NWARPS = BLOCK / 32;
 	constexpr bool STAGED = Src::kStageable;
 	using Geo = StageGeo<Src::kKeyBytes>;
-	using Smem = PartSmem<Src, P>;
+	using Smem = PartSmem<Src, P, INLINE0>;
+	using Cfg = PartCfg<P, INLINE0>;
 	constexpr int SEG_UNITS = Geo::SEG_UNITS;
-	constexpr int CAP = PartCfg<P>::CAP;
-	constexpr int NCNT = PartCfg<P>::NCNT;
+	constexpr int CAP = Cfg::CAP;
+	constexpr int NCNT = Cfg::NCNT;
+	constexpr int FIRST = Cfg::FIRST;
 	extern __shared__ __align__(128) unsigned char s_dyn[];
 	const uint32_t lane = threadIdx.x & 31u;
 	const uint32_t warp = threadIdx.x >> 5;
@@ -1086,7 +1093,9 @@ __global__ void __launch_bounds__(BLOCK, 2)
 	uint4 *const my_buf = reinterpret_cast<uint4 *>(my_smem);
 	const uint64_t pol_keys = policy_evict_first();
 	const uint64_t pol_filter = policy_evict_last();
-	warm_slice(filter, 0u, 1u << kSliceShift, BLOCK);
+	if (INLINE0) {
+		warm_slice(filter, 0u, 1u << SHIFT, BLOCK);
+	}
 	const uint64_t stride = static_cast<uint64_t>(gridDim.x) * NWARPS;
 	const uint64_t full_segs = count / kSegRows;
 	const uint32_t rot = Geo::rot(lane);
@@ -1150,13 +1159,16 @@ __global__ void __launch_bounds__(BLOCK, 2)
 				for (int i = 0; i < 8; i++) {
 					const uint32_t sector = static_cast<uint32_t>(h[lo + i]) & sector_mask;
 					w0[i] = 0;
-					if ((sector >> kSliceShift) == 0u) {
+					if (INLINE0 && (sector >> SHIFT) == 0u) {
 						w0[i] = ld_filter_word(filter + sector, pol_filter);
 					}
 				}
 			};
 			auto tests = [&](const int lo) -> uint32_t {
 				uint32_t r = 0;
+				if (!INLINE0) {
+					return 0u;
+				}
 #pragma unroll
 				for (int i = 7; i >= 0; i--) {
 					r = r * 2u + sector_test_fma(w0[i], static_cast<uint32_t>(h[lo + i] >> 32));
@@ -1172,7 +1184,7 @@ __global__ void __launch_bounds__(BLOCK, 2)
 #pragma unroll
 			for (int i = 0; i < 16; i++) {
 				const uint32_t sector = static_cast<uint32_t>(h[i]) & sector_mask;
-				const uint32_t sh = (sector >> (kSliceShift - 3)) & ((P - 1u) << 3); // 8 · slice
+				const uint32_t sh = (sector >> (SHIFT - 3)) & ((P - 1u) << 3); // 8 · slice
 				if (NCNT == 1) {
 					cnt[0] += 1u << sh;
 				} else {
@@ -1208,13 +1220,14 @@ __global__ void __launch_bounds__(BLOCK, 2)
 				return (s & 2) ? t >> 16 : t & 0xffffu;
 			};
 #pragma unroll
-			for (int s = 1; s < P; s++) { // the regions of slices ≥ 1 hold CAP records; slice 0 has none
+			for (int s = FIRST; s < P; s++) { // a bucket region holds CAP records (INLINE0: slice 0 has none)
 				overflow |= slice_total(s) > static_cast<uint32_t>(CAP);
 			}
 			if (lane == 0) {
 #pragma unroll
-				for (int s = 1; s < P; s++) {
-					bucket_counts[(s - 1) * num_segs + cur] = overflow ? uint16_t(0) : static_cast<uint16_t>(slice_total(s));
+				for (int s = FIRST; s < P; s++) {
+					bucket_counts[(s - FIRST) * num_segs + cur] =
+					    overflow ? uint16_t(0) : static_cast<uint16_t>(slice_total(s));
 				}
 			}
 			uint32_t hits = 0;
@@ -1225,7 +1238,7 @@ __global__ void __launch_bounds__(BLOCK, 2)
 					for (int k = 0; k < 8; k++) {
 						const int i = lo + k;
 						const uint32_t sector = static_cast<uint32_t>(h[i]) & sector_mask;
-						const uint32_t sh = (sector >> (kSliceShift - 3)) & ((P - 1u) << 3);
+						const uint32_t sh = (sector >> (SHIFT - 3)) & ((P - 1u) << 3);
 						const uint32_t shr = sh & 31u;
 						uint32_t rank, pos;
 						if (NCNT == 1) {
@@ -1240,13 +1253,13 @@ __global__ void __launch_bounds__(BLOCK, 2)
 							pos = static_cast<uint32_t>((up ? base[1] : base[0]) >> (2u * shr)) & 0xffffu;
 						}
 						pos += rank;
-						if (sh != 0u) {
+						if (!INLINE0 || sh != 0u) {
 							const uint32_t row9 =
 							    lane * 16u + (((i / Geo::KPU + unit_rot) & (Geo::U - 1)) * Geo::KPU) + (i % Geo::KPU);
-							// byte offset of record `pos` of slice s: ((s-1)·CAP + pos)·8 with 8·s = sh
-							const uint32_t off = mul_lo_u32(sh, CAP) + pos * 8u - CAP * 8u;
+							// byte offset of record `pos` of slice s: ((s-FIRST)·CAP + pos)·8 with 8·s = sh
+							const uint32_t off = mul_lo_u32(sh, CAP) + pos * 8u - FIRST * CAP * 8u;
 							*reinterpret_cast<uint2 *>(reinterpret_cast<unsigned char *>(stage) + off) =
-							    make_uint2((sector & ((1u << kSliceShift) - 1u)) | (row9 << kSliceShift),
+							    make_uint2((sector & ((1u << SHIFT) - 1u)) | (row9 << SHIFT),
 							               static_cast<uint32_t>(h[i] >> 32));
 						}
 					}
@@ -1279,10 +1292,10 @@ __global__ void __launch_bounds__(BLOCK, 2)
 			__syncwarp();
 			if (!overflow) {
 #pragma unroll
-				for (int s = 1; s < P; s++) {
+				for (int s = FIRST; s < P; s++) {
 					const uint32_t total = slice_total(s);
-					const uint4 *sv = reinterpret_cast<const uint4 *>(stage + (s - 1) * CAP);
-					uint4 *dv = reinterpret_cast<uint4 *>(buckets + (s - 1) * bucket_stride + cur * CAP);
+					const uint4 *sv = reinterpret_cast<const uint4 *>(stage + (s - FIRST) * CAP);
+					uint4 *dv = reinterpret_cast<uint4 *>(buckets + (s - FIRST) * bucket_stride + cur * CAP);
 					for (uint32_t j = lane; 2u * j < total; j += 32u) {
 						// an odd count copies one stale record: it stays inside the region, unread.  evict_first: the
 						// record traffic must not push slice 0 of the filter out of L2
@@ -1333,7 +1346,7 @@ __global__ void __launch_bounds__(256)
 
 // One slice's bucket: warp per segment region; all record loads, then all filter loads, are issued before the
 // first test.  ITER = ceil(CAP / 32) records per lane.
-template <int CAP>
+template <int CAP, int SHIFT = kSliceShift>
 __global__ void __launch_bounds__(256)
     probe_bucket_kernel(const uint2 *__restrict__ bucket, const uint16_t *__restrict__ counts, const uint64_t num_segs,
                         const uint64_t *__restrict__ filter, const uint32_t slice_lo, uint32_t *__restrict__ bitmap32) {
@@ -1341,7 +1354,7 @@ __global__ void __launch_bounds__(256)
 	const uint32_t lane = threadIdx.x & 31u;
 	const uint64_t pol_rec = policy_evict_first();
 	const uint64_t pol_filter = policy_evict_last();
-	warm_slice(filter, slice_lo, 1u << kSliceShift, 256);
+	warm_slice(filter, slice_lo, 1u << SHIFT, 256);
 	const uint64_t *const slice = filter + slice_lo;
 	const uint64_t warp_global = (static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
 	const uint64_t num_warps = (static_cast<uint64_t>(gridDim.x) * blockDim.x) >> 5;
@@ -1363,13 +1376,13 @@ __global__ void __launch_bounds__(256)
 		for (int k = 0; k < ITER; k++) {
 			w[k] = 0;
 			if (lane + 32u * k < c) {
-				w[k] = ld_filter_word(slice + (rec[k].x & ((1u << kSliceShift) - 1u)), pol_filter);
+				w[k] = ld_filter_word(slice + (rec[k].x & ((1u << SHIFT) - 1u)), pol_filter);
 			}
 		}
 #pragma unroll
 		for (int k = 0; k < ITER; k++) {
 			if (sector_test_fma(w[k], rec[k].y)) { // an all-zero word (no record) passes nothing
-				const uint32_t row9 = rec[k].x >> kSliceShift;
+				const uint32_t row9 = rec[k].x >> SHIFT;
 				atomicOr(bitmap32 + seg * 16 + (row9 >> 5), 1u << (row9 & 31u));
 			}
 		}
@@ -1867,12 +1880,38 @@ static inline int partition_choice(uint64_t num_sectors) {
 static inline int partition_cap(int slices) {
 	return slices == 2 ? PartCfg<2>::CAP : (slices == 4 ? PartCfg<4>::CAP : PartCfg<8>::CAP);
 }
-// extra scratch behind the phased layout:
-// [bucket counts u16 × (P-1)·segs][overflow list u32 × (1 + segs)][records 8 B × (P-1)·segs·CAP]
-static size_t partition_scratch_bytes(uint64_t count, int slices) {
+// Variants of the partitioned probe (experiments): RPT_PART_SLICE_MIB=32 partitions a filter of up
+// to 256 MiB into 32-MiB slices (twice as many, each certain to stay L2-resident); RPT_PART_INLINE0=0 makes slice 0 a
+// bucket like the others (no filter access, no L2 competition in the partition kernel).
+struct PartPlan {
+	int slices; // P
+	int shift;  // log2(sectors per slice)
+	bool inline0;
+};
+static PartPlan partition_plan(uint64_t num_sectors, int slices64) {
+	static const int env_mib = [] {
+		const char *e = getenv("RPT_PART_SLICE_MIB");
+		return e ? atoi(e) : 64;
+	}();
+	static const bool env_inline0 = [] {
+		const char *e = getenv("RPT_PART_INLINE0");
+		return e ? atoi(e) != 0 : true;
+	}();
+	PartPlan plan {slices64, static_cast<int>(kSliceShift), env_inline0};
+	if (env_mib == 32 && slices64 >= 2 && slices64 <= 4 && (num_sectors >> (kSliceShift - 1)) <= 8) {
+		plan.slices = static_cast<int>(num_sectors >> (kSliceShift - 1));
+		plan.shift = static_cast<int>(kSliceShift) - 1;
+	}
+	return plan;
+}
+// extra scratch behind the phased layout (R = bucket regions per segment, P or P-1):
+// [bucket counts u16 × R·segs][overflow list u32 × (1 + segs)][records 8 B × R·segs·CAP]
+static size_t partition_scratch_bytes(uint64_t count, uint64_t num_sectors, int slices64) {
 	const uint64_t num_segs = ceil_div(count, kSegRows);
-	return align_up((slices - 1) * num_segs * sizeof(uint16_t), 256) + align_up((num_segs + 1) * sizeof(uint32_t), 256) +
-	       (slices - 1) * num_segs * partition_cap(slices) * sizeof(uint2);
+	const PartPlan plan = partition_plan(num_sectors, slices64);
+	const uint64_t regions = plan.slices - (plan.inline0 ? 1 : 0);
+	return align_up(regions * num_segs * sizeof(uint16_t), 256) + align_up((num_segs + 1) * sizeof(uint32_t), 256) +
+	       regions * num_segs * partition_cap(plan.slices) * sizeof(uint2);
 }
 
 size_t probe_scratch_bytes(uint64_t count, uint64_t num_sectors) {
@@ -1880,7 +1919,7 @@ size_t probe_scratch_bytes(uint64_t count, uint64_t num_sectors) {
 		return (ceil_div(count, kProbeTileKeys) + 2) * sizeof(uint64_t); // look-back descriptors + ticket
 	}
 	const int slices = partition_slices(num_sectors);
-	return align_up(phased_layout(count).bytes, 256) + (slices ? partition_scratch_bytes(count, slices) : 0);
+	return align_up(phased_layout(count).bytes, 256) + (slices ? partition_scratch_bytes(count, num_sectors, slices) : 0);
 }
 
 template <class Src, bool AGG, bool MM>
@@ -2152,18 +2191,21 @@ static cudaError_t launch_probe_phased(const DeviceInfo &dev, const Src &src, ui
 	}
 }
 
-template <class Src, int P>
+template <class Src, int P, int SHIFT = kSliceShift, bool INLINE0 = true>
 static cudaError_t launch_probe_partitioned(const DeviceInfo &dev, const Src &src, uint64_t count,
                                             const uint64_t *words, uint64_t num_sectors, uint32_t *sel_out,
                                             uint64_t *found_out, uint32_t row_offset, const uint32_t *translate,
                                             void *scratch, cudaStream_t stream, int *launches) {
 	constexpr int BLOCK = kProbeBlock;
-	constexpr int CAP = PartCfg<P>::CAP;
-	auto part = probe_partition_kernel<Src, BLOCK, P>;
-	auto bucket = probe_bucket_kernel<CAP>;
+	using Cfg = PartCfg<P, INLINE0>;
+	constexpr int CAP = Cfg::CAP;
+	constexpr int FIRST = Cfg::FIRST;
+	constexpr int REGIONS = Cfg::REGIONS;
+	auto part = probe_partition_kernel<Src, BLOCK, P, SHIFT, INLINE0>;
+	auto bucket = probe_bucket_kernel<CAP, SHIFT>;
 	const uint64_t num_segs = ceil_div(count, kSegRows);
-	const size_t smem = static_cast<size_t>(BLOCK / 32) * PartSmem<Src, P>::WARP_BYTES;
-	cudaError_t e = ensure_max_dyn_smem<probe_partition_kernel<Src, BLOCK, P>>(dev);
+	const size_t smem = static_cast<size_t>(BLOCK / 32) * PartSmem<Src, P, INLINE0>::WARP_BYTES;
+	cudaError_t e = ensure_max_dyn_smem<probe_partition_kernel<Src, BLOCK, P, SHIFT, INLINE0>>(dev);
 	if (e != cudaSuccess) {
 		return e;
 	}
@@ -2197,7 +2239,7 @@ static cudaError_t launch_probe_partitioned(const DeviceInfo &dev, const Src &sr
 	uint16_t *bitmap = reinterpret_cast<uint16_t *>(base + lay.off_hitbits);
 	char *extra = base + align_up(lay.bytes, 256);
 	uint16_t *bucket_counts = reinterpret_cast<uint16_t *>(extra);
-	extra += align_up((P - 1) * num_segs * sizeof(uint16_t), 256);
+	extra += align_up(REGIONS * num_segs * sizeof(uint16_t), 256);
 	uint32_t *overflow = reinterpret_cast<uint32_t *>(extra);
 	uint2 *buckets = reinterpret_cast<uint2 *>(extra + align_up((num_segs + 1) * sizeof(uint32_t), 256));
 	const uint64_t bucket_stride = num_segs * CAP;
@@ -2207,9 +2249,13 @@ static cudaError_t launch_probe_partitioned(const DeviceInfo &dev, const Src &sr
 			return e;
 		}
 	}
-	e = wait_slices(stream, 0, 0); // the partition kernel looks up slice-0 keys only
-	if (e != cudaSuccess) {
-		return e;
+	// gates are per 64-MiB slice (kSliceShift); slice s of this plan lies in gate slice (s << SHIFT) >> kSliceShift
+	auto gate_of = [](int s) { return static_cast<int>((static_cast<uint64_t>(s) << SHIFT) >> kSliceShift); };
+	if (INLINE0) {
+		e = wait_slices(stream, 0, 0); // the partition kernel looks up slice-0 keys only
+		if (e != cudaSuccess) {
+			return e;
+		}
 	}
 	part<<<static_cast<unsigned>(grid), BLOCK, smem, stream>>>(src, words, static_cast<uint32_t>(num_sectors - 1), count,
 	                                                          num_segs, bitmap, buckets, bucket_stride, bucket_counts,
@@ -2222,14 +2268,14 @@ static cudaError_t launch_probe_partitioned(const DeviceInfo &dev, const Src &sr
 	uint64_t bgrid = static_cast<uint64_t>(dev.sm_count) * (bper_sm > 0 ? bper_sm : 1);
 	const uint64_t bwant = ceil_div(num_segs, 8);
 	bgrid = bgrid < bwant ? bgrid : bwant;
-	for (int s = 1; s < P; s++) {
-		e = wait_slices(stream, s, s);
+	for (int s = FIRST; s < P; s++) {
+		e = wait_slices(stream, gate_of(s), gate_of(s));
 		if (e != cudaSuccess) {
 			return e;
 		}
-		bucket<<<static_cast<unsigned>(bgrid), 256, 0, stream>>>(buckets + (s - 1) * bucket_stride,
-		                                                        bucket_counts + (s - 1) * num_segs, num_segs, words,
-		                                                        static_cast<uint32_t>(s) << kSliceShift,
+		bucket<<<static_cast<unsigned>(bgrid), 256, 0, stream>>>(buckets + (s - FIRST) * bucket_stride,
+		                                                        bucket_counts + (s - FIRST) * num_segs, num_segs, words,
+		                                                        static_cast<uint32_t>(s) << SHIFT,
 		                                                        reinterpret_cast<uint32_t *>(bitmap));
 	}
 	if (gated) { // overflowed segments (normally a handful) once more, behind every slice gate by now
@@ -2246,7 +2292,7 @@ static cudaError_t launch_probe_partitioned(const DeviceInfo &dev, const Src &sr
 	compact_bitmap_kernel<<<static_cast<unsigned>(cwant < ccap ? cwant : ccap), 256, 0, stream>>>(
 	    reinterpret_cast<const uint32_t *>(bitmap), seg_offsets, block_totals, num_segs, sel_out, row_offset, translate);
 	if (launches) {
-		(*launches) += P + 4 + (gated ? 1 : 0);
+		(*launches) += 1 + REGIONS + 4 + (gated ? 1 : 0);
 	}
 	return cudaGetLastError();
 }
@@ -2269,7 +2315,24 @@ static cudaError_t launch_probe_src(const DeviceInfo &dev, const Src &src, uint6
 		return smem ? launch_probe_fused<Src, kProbeBlockSmem, true>(RPT_PROBE_ARGS)
 		            : launch_probe_fused<Src, kProbeBlock, false>(RPT_PROBE_ARGS);
 	}
-	switch (smem ? 0 : partition_choice<Src>(num_sectors)) {
+	const int slices64 = smem ? 0 : partition_choice<Src>(num_sectors);
+	if constexpr (Src::kStageable && Src::kKeyBytes == 8 && !Src::kNullable) { // experiment variants: flat 8-byte keys only
+		if (slices64 >= 2) {
+			const PartPlan plan = partition_plan(num_sectors, slices64);
+			constexpr int kHalf = static_cast<int>(kSliceShift) - 1;
+			if (plan.shift == kHalf && plan.slices == 8) {
+				return plan.inline0 ? launch_probe_partitioned<Src, 8, kHalf, true>(RPT_PROBE_ARGS)
+				                    : launch_probe_partitioned<Src, 8, kHalf, false>(RPT_PROBE_ARGS);
+			}
+			if (plan.shift == kHalf && plan.slices == 4 && plan.inline0) {
+				return launch_probe_partitioned<Src, 4, kHalf, true>(RPT_PROBE_ARGS);
+			}
+			if (plan.shift == static_cast<int>(kSliceShift) && plan.slices == 4 && !plan.inline0) {
+				return launch_probe_partitioned<Src, 4, static_cast<int>(kSliceShift), false>(RPT_PROBE_ARGS);
+			}
+		}
+	}
+	switch (slices64) {
 	case 2:
 		return launch_probe_partitioned<Src, 2>(RPT_PROBE_ARGS);
 	case 4:

@@ -104,6 +104,18 @@ except Exception as e:
     print("no line:", e)
 PY
 	;;
+partvar)    # partitioned-probe variants (32 MiB slices, slice 0 as a bucket): partvar <tag>
+	out=gpurun_out/partvar_${1:-r2x}.txt
+	: > $out
+	for knobs in "" "RPT_PART_SLICE_MIB=32" "RPT_PART_INLINE0=0" "RPT_PART_SLICE_MIB=32 RPT_PART_INLINE0=0"; do
+		echo "== knobs: ${knobs:-default}" >> $out
+		env $knobs timeout -s KILL 300 python tools/probe_sweep.py 1e9 5 1e8 >> $out 2>&1
+		echo "rc=$?" >> $out
+		env $knobs SWEEP_PPM=500000 timeout -s KILL 300 python tools/probe_sweep.py 1e9 5 1e8 >> $out 2>&1
+		echo "rc=$?" >> $out
+	done
+	cat $out
+	;;
 tests)      # the GPU parity suite
 	timeout 2400 python -m pytest tests -m gpu -x -q > gpurun_out/tests_${1:-r2}.log 2>&1
 	echo "tests rc=$?" >> gpurun_out/tests_${1:-r2}.log
