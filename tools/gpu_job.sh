@@ -116,6 +116,18 @@ partvar)    # partitioned-probe variants (32 MiB slices, slice 0 as a bucket): p
 	done
 	cat $out
 	;;
+partpipe)   # chunk-pipelined partitioned probe (partition of chunk c+1 beside the buckets of chunk c): partpipe <tag>
+	out=gpurun_out/partpipe_${1:-r2y}.txt
+	: > $out
+	for knobs in "" "RPT_PART_PIPE=8" "RPT_PART_PIPE=8 RPT_PART_INLINE0=0" "RPT_PART_PIPE=8 RPT_PART_INLINE0=0 RPT_PART_PIPE_BCTAS=2" \
+	             "RPT_PART_PIPE=8 RPT_PART_INLINE0=0 RPT_PART_PIPE_BCTAS=4" "RPT_PART_PIPE=4 RPT_PART_INLINE0=0" "RPT_PART_PIPE=16 RPT_PART_INLINE0=0" \
+	             "RPT_PART_PIPE=8 RPT_PART_PIPE_BCTAS=2" "RPT_PART_PIPE=16" "RPT_PART_PIPE=8 RPT_PART_PIPE_PCTAS=2 RPT_PART_PIPE_BCTAS=6"; do
+		echo "== knobs: ${knobs:-default}" >> $out
+		env $knobs timeout -s KILL 300 python tools/probe_sweep.py 1e9 5 1e8 >> $out 2>&1
+		echo "rc=$?" >> $out
+	done
+	cat $out
+	;;
 tests)      # the GPU parity suite
 	timeout 2400 python -m pytest tests -m gpu -x -q > gpurun_out/tests_${1:-r2}.log 2>&1
 	echo "tests rc=$?" >> gpurun_out/tests_${1:-r2}.log
