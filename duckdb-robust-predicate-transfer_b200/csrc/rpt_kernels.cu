@@ -1076,8 +1076,7 @@ __global__ void __launch_bounds__(BLOCK, 2)
                            const uint64_t count, const uint64_t num_segs, uint16_t *__restrict__ bitmap16,
                            uint2 *__restrict__ buckets, const uint64_t bucket_stride /* records per slice array */,
                            uint16_t *__restrict__ bucket_counts /* (P-1) × num_segs */,
-                           uint32_t *__restrict__ ovf_list /* [0] = count, [1 + i] = i-th overflowed segment */,
-                           const uint64_t seg_begin, const uint64_t seg_end /* this launch's segments */) {
+                           uint32_t *__restrict__ ovf_list /* [0] = count, [1 + i] = i-th overflowed segment */) {
 	constexpr int NWARPS = BLOCK / 32;
 	constexpr bool STAGED = Src::kStageable;
 	using Geo = StageGeo<Src::kKeyBytes>;
@@ -1104,10 +1103,10 @@ __global__ void __launch_bounds__(BLOCK, 2)
 	constexpr uint64_t kNone = ~0ULL;
 	uint64_t cur = kNone;
 	uint32_t par = 1;
-	for (uint64_t nxt = seg_begin + static_cast<uint64_t>(blockIdx.x) * NWARPS + warp;; nxt += stride) {
+	for (uint64_t nxt = static_cast<uint64_t>(blockIdx.x) * NWARPS + warp;; nxt += stride) {
 		if (STAGED) {
 			__syncwarp(); // the buffer overwritten next (keys and, when aliased, records) is no longer read
-			if (nxt < full_segs && nxt < seg_end) {
+			if (nxt < full_segs) {
 				const uint4 *g = reinterpret_cast<const uint4 *>(src.key_ptr()) + nxt * SEG_UNITS + lane;
 				uint4 *s = my_buf + (par ^ 1u) * SEG_UNITS + lane;
 #pragma unroll
@@ -1306,7 +1305,7 @@ __global__ void __launch_bounds__(BLOCK, 2)
 			}
 			__syncwarp(); // the stage is rewritten by the next segment (or, aliased, by the key prefetch after it)
 		}
-		if (nxt >= seg_end) {
+		if (nxt >= num_segs) {
 			break;
 		}
 		cur = nxt;
@@ -1350,8 +1349,7 @@ __global__ void __launch_bounds__(256)
 template <int CAP, int SHIFT = kSliceShift>
 __global__ void __launch_bounds__(256)
     probe_bucket_kernel(const uint2 *__restrict__ bucket, const uint16_t *__restrict__ counts, const uint64_t num_segs,
-                        const uint64_t *__restrict__ filter, const uint32_t slice_lo, uint32_t *__restrict__ bitmap32,
-                        const uint64_t seg_begin, const uint64_t seg_end) {
+                        const uint64_t *__restrict__ filter, const uint32_t slice_lo, uint32_t *__restrict__ bitmap32) {
 	constexpr int ITER = (CAP + 31) / 32;
 	const uint32_t lane = threadIdx.x & 31u;
 	const uint64_t pol_rec = policy_evict_first();
@@ -1360,7 +1358,7 @@ __global__ void __launch_bounds__(256)
 	const uint64_t *const slice = filter + slice_lo;
 	const uint64_t warp_global = (static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
 	const uint64_t num_warps = (static_cast<uint64_t>(gridDim.x) * blockDim.x) >> 5;
-	for (uint64_t seg = seg_begin + warp_global; seg < seg_end; seg += num_warps) {
+	for (uint64_t seg = warp_global; seg < num_segs; seg += num_warps) {
 		const uint32_t c = __ldg(counts + seg);
 		const uint2 *rec_base = bucket + seg * CAP;
 		uint2 rec[ITER];
@@ -2193,36 +2191,6 @@ static cudaError_t launch_probe_phased(const DeviceInfo &dev, const Src &src, ui
 	}
 }
 
-// Chunk pipeline of the partitioned probe (experiment, RPT_PART_PIPE=K): the segments are cut into K chunks; the
-// partition kernel of chunk c+1 (DRAM-bound) runs on one internal stream while the bucket kernels of chunk c
-// (bound by the L1TEX gather rate) run on another, each with a grid that leaves room for the other on every SM.
-struct PipeRes {
-	cudaStream_t sp = nullptr, sb = nullptr;
-	cudaEvent_t fork = nullptr, join = nullptr, done[16] = {};
-};
-static cudaError_t pipe_resources(int device, PipeRes **out) {
-	static thread_local PipeRes res[64];
-	PipeRes &r = res[device & 63];
-	if (!r.sp) {
-		cudaError_t e = cudaStreamCreateWithFlags(&r.sp, cudaStreamNonBlocking);
-		if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&r.sb, cudaStreamNonBlocking);
-		if (e == cudaSuccess) e = cudaEventCreateWithFlags(&r.fork, cudaEventDisableTiming);
-		if (e == cudaSuccess) e = cudaEventCreateWithFlags(&r.join, cudaEventDisableTiming);
-		for (int i = 0; i < 16 && e == cudaSuccess; i++) {
-			e = cudaEventCreateWithFlags(&r.done[i], cudaEventDisableTiming);
-		}
-		if (e != cudaSuccess) {
-			return e;
-		}
-	}
-	*out = &r;
-	return cudaSuccess;
-}
-static int env_int(const char *name, int dflt) {
-	const char *e = getenv(name);
-	return e ? atoi(e) : dflt;
-}
-
 template <class Src, int P, int SHIFT = kSliceShift, bool INLINE0 = true>
 static cudaError_t launch_probe_partitioned(const DeviceInfo &dev, const Src &src, uint64_t count,
                                             const uint64_t *words, uint64_t num_sectors, uint32_t *sel_out,
@@ -2289,45 +2257,9 @@ static cudaError_t launch_probe_partitioned(const DeviceInfo &dev, const Src &sr
 			return e;
 		}
 	}
-	static const int pipe_chunks = env_int("RPT_PART_PIPE", 0);
-	const bool piped = !gated && pipe_chunks >= 2 && pipe_chunks <= 16 && num_segs >= 64ull * pipe_chunks;
-	if (piped) {
-		static const int p_ctas = env_int("RPT_PART_PIPE_PCTAS", 1);
-		static const int b_ctas = env_int("RPT_PART_PIPE_BCTAS", 3);
-		PipeRes *r = nullptr;
-		e = pipe_resources(dev.device, &r);
-		if (e != cudaSuccess) {
-			return e;
-		}
-		const uint64_t per_chunk = align_up(ceil_div(num_segs, pipe_chunks), 8);
-		const unsigned pgrid = static_cast<unsigned>(dev.sm_count * (p_ctas < per_sm ? p_ctas : per_sm));
-		const unsigned bgrid_p = static_cast<unsigned>(dev.sm_count * b_ctas);
-		cudaEventRecord(r->fork, stream);
-		cudaStreamWaitEvent(r->sp, r->fork, 0);
-		cudaStreamWaitEvent(r->sb, r->fork, 0);
-		for (int c = 0; c < pipe_chunks; c++) {
-			const uint64_t lo = c * per_chunk, hi = lo + per_chunk < num_segs ? lo + per_chunk : num_segs;
-			if (lo >= hi) {
-				break;
-			}
-			part<<<pgrid, BLOCK, smem, r->sp>>>(src, words, static_cast<uint32_t>(num_sectors - 1), count, num_segs, bitmap,
-			                                   buckets, bucket_stride, bucket_counts, nullptr, lo, hi);
-			cudaEventRecord(r->done[c], r->sp);
-			cudaStreamWaitEvent(r->sb, r->done[c], 0);
-			for (int s = FIRST; s < P; s++) {
-				bucket<<<bgrid_p, 256, 0, r->sb>>>(buckets + (s - FIRST) * bucket_stride,
-				                                   bucket_counts + (s - FIRST) * num_segs, num_segs, words,
-				                                   static_cast<uint32_t>(s) << SHIFT, reinterpret_cast<uint32_t *>(bitmap),
-				                                   lo, hi);
-			}
-		}
-		cudaEventRecord(r->join, r->sb);
-		cudaStreamWaitEvent(stream, r->join, 0);
-	} else {
 	part<<<static_cast<unsigned>(grid), BLOCK, smem, stream>>>(src, words, static_cast<uint32_t>(num_sectors - 1), count,
 	                                                          num_segs, bitmap, buckets, bucket_stride, bucket_counts,
-	                                                          gated ? overflow : nullptr, 0, num_segs);
-	}
+	                                                          gated ? overflow : nullptr);
 	int bper_sm = 0;
 	e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bper_sm, bucket, 256, 0);
 	if (e != cudaSuccess) {
@@ -2336,7 +2268,7 @@ static cudaError_t launch_probe_partitioned(const DeviceInfo &dev, const Src &sr
 	uint64_t bgrid = static_cast<uint64_t>(dev.sm_count) * (bper_sm > 0 ? bper_sm : 1);
 	const uint64_t bwant = ceil_div(num_segs, 8);
 	bgrid = bgrid < bwant ? bgrid : bwant;
-	for (int s = FIRST; s < P && !piped; s++) {
+	for (int s = FIRST; s < P; s++) {
 		e = wait_slices(stream, gate_of(s), gate_of(s));
 		if (e != cudaSuccess) {
 			return e;
@@ -2344,7 +2276,7 @@ static cudaError_t launch_probe_partitioned(const DeviceInfo &dev, const Src &sr
 		bucket<<<static_cast<unsigned>(bgrid), 256, 0, stream>>>(buckets + (s - FIRST) * bucket_stride,
 		                                                        bucket_counts + (s - FIRST) * num_segs, num_segs, words,
 		                                                        static_cast<uint32_t>(s) << SHIFT,
-		                                                        reinterpret_cast<uint32_t *>(bitmap), 0, num_segs);
+		                                                        reinterpret_cast<uint32_t *>(bitmap));
 	}
 	if (gated) { // overflowed segments (normally a handful) once more, behind every slice gate by now
 		probe_overflow_kernel<Src><<<static_cast<unsigned>(dev.sm_count), 256, 0, stream>>>(

@@ -116,7 +116,7 @@ partvar)    # partitioned-probe variants (32 MiB slices, slice 0 as a bucket): p
 	done
 	cat $out
 	;;
-partpipe)   # chunk-pipelined partitioned probe (partition of chunk c+1 beside the buckets of chunk c): partpipe <tag>
+partpipe)   # chunk-pipelined partitioned probe (code as of commit 0fbcbed, removed afterwards): partpipe <tag>
 	out=gpurun_out/partpipe_${1:-r2y}.txt
 	: > $out
 	for knobs in "" "RPT_PART_PIPE=8" "RPT_PART_PIPE=8 RPT_PART_INLINE0=0" "RPT_PART_PIPE=8 RPT_PART_INLINE0=0 RPT_PART_PIPE_BCTAS=2" \
