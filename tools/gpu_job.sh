@@ -140,7 +140,29 @@ bench)      # default bench line (+ reference arm)
 	cut -c1-600 gpurun_out/bench_${tag}.json
 	tail -5 gpurun_out/bench_${tag}.err
 	;;
+evidence)   # round-end evidence: tests, both bench arms, then the ncu launch list of the same bench command
+	tag=${1:-r2}
+	timeout 2400 python -m pytest tests -m gpu -x -q > gpurun_out/tests_${tag}.log 2>&1
+	echo "tests rc=$?" | tee -a gpurun_out/tests_${tag}.log
+	tail -3 gpurun_out/tests_${tag}.log
+	timeout 900 python bench.py --impl reference > gpurun_out/bench_${tag}_reference.json 2> gpurun_out/bench_${tag}_reference.err
+	echo "reference arm rc=$?"
+	timeout 900 python bench.py > gpurun_out/bench_${tag}.json 2> gpurun_out/bench_${tag}.err
+	echo "bench rc=$?"
+	cut -c1-400 gpurun_out/bench_${tag}.json
+	cmd="python bench.py --steps 2 --warmup 3 --no-sweep --no-config3 --no-cpu --no-e2e --sustain-s 0"
+	timeout 600 $cmd > gpurun_out/bench_${tag}_short.json 2> gpurun_out/bench_${tag}_short.err
+	rc=$?
+	echo "short bench rc=$rc"
+	if [ $rc -eq 0 ]; then
+		timeout 1200 ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum --clock-control none -c 600 \
+			--csv --log-file gpurun_out/launches_${tag}.csv $cmd > gpurun_out/ncu_${tag}.log 2>&1
+		echo "ncu rc=$?"
+		python tools/launch_summary.py gpurun_out/launches_${tag}.csv > gpurun_out/launches_${tag}.md 2>&1
+		head -30 gpurun_out/launches_${tag}.md
+	fi
+	;;
 *)
-	echo "jobs: part_lab tests bench"
+	echo "jobs: part_lab tests bench evidence"
 	;;
 esac
