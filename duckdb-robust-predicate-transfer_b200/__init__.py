@@ -109,6 +109,8 @@ _SIGNATURES = {
     "rpt_bf_set_slice_events": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p), C.c_int]),
     "rpt_bf_checksum": (C.c_int, [C.c_void_p, C.POINTER(C.c_uint64)]),
     "rpt_bf_words_generation": (C.c_int, [C.c_void_p, C.POINTER(C.c_uint64)]),
+    "rpt_bf_set_prefilter": (C.c_int, [C.c_void_p, C.c_int]),
+    "rpt_bf_prefilter_info": (C.c_int, [C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_double)]),
     "rpt_synth_build_keys": (C.c_int, [C.c_void_p, C.c_uint64, C.c_uint64, C.c_int, C.c_void_p]),
     "rpt_synth_probe_keys": (C.c_int, [C.c_void_p, C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint32, C.c_int,
                                        C.c_void_p]),
@@ -381,6 +383,16 @@ class PTBloomFilter:
     @property
     def words_generation(self):
         return self._get(lib().rpt_bf_words_generation, C.c_uint64)
+
+    def SetPrefilter(self, mode):
+        """Folded pre-filter of large probes (rpt_gpu.h): -1 library default, 0 off, 1 by density, 2 always."""
+        _check(lib().rpt_bf_set_prefilter(self._h, int(mode)))
+
+    def PrefilterInfo(self):
+        """(state, pass_rate): state 0 = no fold for the current words, 1 = in use, 2 = made but too dense."""
+        state, rate = C.c_int(0), C.c_double(1.0)
+        _check(lib().rpt_bf_prefilter_info(self._h, C.byref(state), C.byref(rate)))
+        return state.value, rate.value
 
     def ImportWords(self, words):
         words = np.ascontiguousarray(words, dtype=np.uint64)

@@ -140,6 +140,26 @@ struct rpt_bf {
 	std::atomic<int> finalized {0};
 	std::atomic<long long> launches {0};
 	std::atomic<uint64_t> words_generation {0}; // bumped whenever `words` is reallocated (stale peer mappings)
+	// Folded pre-filter of the words (probes of 256 / 512 MiB filters, rpt_kernels.cuh Prefilter): built lazily by
+	// the first large probe after a mutation, on that probe's stream; content_version is bumped by every entry point
+	// that may change the words (or hands out their address), fold_version is the version the fold was made from.
+	std::mutex fold_mu;
+	uint64_t *folded = nullptr;        // kSliceSectors words (64 MiB), allocated on first use
+	uint64_t *fold_pop_dev = nullptr;  // set bits of the folded filter
+	uint64_t *fold_pop_host = nullptr; // pinned copy
+	std::atomic<uint64_t> content_version {1};
+	uint64_t fold_version = 0;
+	double fold_pass = 1.0;            // estimated share of non-member keys that survive the folded filter
+	std::atomic<int> fold_mode {-1};   // rpt_bf_set_prefilter: -1 = library default (RPT_PREFILTER)
+	// feedback: the pre-filtered partition counts the rows it saw and the rows that survived the folded filter
+	// (members + its false positives); when too many survive, the pre-filter costs more than it saves and the
+	// following probes of this handle go without it for a while (ensure_prefilter)
+	uint64_t *fold_stats_dev = nullptr;  // [rows, survivors]
+	uint64_t *fold_stats_host = nullptr; // pinned copy
+	cudaEvent_t fold_stats_ev = nullptr;
+	bool fold_stats_pending = false;
+	double fold_alive = -1.0;            // survivors / rows of the last measured probe (< 0: none)
+	int fold_holdoff = 0;                // large probes left to run without the pre-filter
 	// fused column range (rpt_bf_minmax_*)
 	MinMaxState *mm_dev = nullptr;
 	int mm_type = 0;
@@ -605,6 +625,7 @@ static int allocate_words(rpt_bf *bf, uint64_t rows) {
 	}
 	bf->num_sectors = s;
 	bf->sized_for_rows = rows;
+	bf->content_version++;
 	// std::fill_n(bf, num_sectors, 0), bloom_filter.cpp:24
 	RPT_CUDA(cudaMemsetAsync(bf->words, 0, s * sizeof(uint64_t), bf->stream));
 	RPT_CUDA(cudaStreamSynchronize(bf->stream));
@@ -672,6 +693,24 @@ int rpt_bf_destroy(rpt_bf_t *bf) {
 	if (bf->mm_dev) {
 		cudaFree(bf->mm_dev);
 	}
+	if (bf->folded) {
+		cudaFree(bf->folded);
+	}
+	if (bf->fold_pop_dev) {
+		cudaFree(bf->fold_pop_dev);
+	}
+	if (bf->fold_pop_host) {
+		cudaFreeHost(bf->fold_pop_host);
+	}
+	if (bf->fold_stats_dev) {
+		cudaFree(bf->fold_stats_dev);
+	}
+	if (bf->fold_stats_host) {
+		cudaFreeHost(bf->fold_stats_host);
+	}
+	if (bf->fold_stats_ev) {
+		cudaEventDestroy(bf->fold_stats_ev);
+	}
 	for (cudaStream_t s : {bf->stream, bf->h2d, bf->compute, bf->d2h}) {
 		if (s) {
 			cudaStreamSynchronize(s);
@@ -713,6 +752,7 @@ int rpt_bf_reset(rpt_bf_t *bf, uint64_t est_rows, rpt_stream_t stream) {
 	} else {
 		bf->num_sectors = s; // fits the buffer: stream-ordered like every other use of the words on `stream`
 		bf->sized_for_rows = est_rows;
+		bf->content_version++;
 		RPT_CUDA(cudaMemsetAsync(bf->words, 0, s * sizeof(uint64_t), pick_stream(bf, stream)));
 	}
 	bf->has_data.store(0);
@@ -733,7 +773,8 @@ RPT_GETTER(rpt_bf_sized_for_rows, uint64_t, bf->sized_for_rows)
 RPT_GETTER(rpt_bf_is_empty, int, bf->has_data.load() ? 0 : 1)
 RPT_GETTER(rpt_bf_is_finalized, int, bf->finalized.load())
 RPT_GETTER(rpt_bf_device, int, bf->dev.device)
-RPT_GETTER(rpt_bf_device_words, uint64_t *, bf->words)
+// whoever holds the address may write the words (NCCL all-gather targets, tests): the folded pre-filter is stale
+RPT_GETTER(rpt_bf_device_words, uint64_t *, (const_cast<rpt_bf_t *>(bf)->content_version++, bf->words))
 
 int rpt_bf_launch_count(const rpt_bf_t *bf, long long *out) {
 	if (!bf || !out) {
@@ -783,6 +824,7 @@ static int insert_impl(rpt_bf *bf, const rpt_col_t *cols, int ncols, uint64_t co
 		return 0; // src/bloom_filter.cpp:71-74: no-op, has_data_ untouched
 	}
 	bf->has_data.store(1); // src/bloom_filter.cpp:75
+	bf->content_version++;
 	int launches = 0;
 	if (mem == RPT_MEM_DEVICE) {
 		DevCols dc;
@@ -998,6 +1040,117 @@ int rpt_bf_finalize(rpt_bf_t *bf, uint64_t actual_rows, const rpt_col_t *cols, i
 // ---------------------------------------------------------------------------------------------
 // probe
 // ---------------------------------------------------------------------------------------------
+// Folded pre-filter for probes of 256 / 512 MiB filters (rpt_kernels.cuh Prefilter; DESIGN.md §4 regime 3c).  The
+// fold is made lazily, by the first probe of ≥ 2^22 rows after a change of the words, on that probe's stream (so it
+// is ordered behind the inserts / merges the caller ordered the probe behind); the stream is synchronised once so
+// that the host can read the folded filter's bit density and decide: the pre-filter is used while the estimated
+// share of non-member keys that survive it stays ≤ RPT_PREFILTER_MAX_PASS (default 0.5).  Results never depend on
+// it — a key the folded filter rejects cannot pass the real one.  RPT_PREFILTER=0 switches it off, =2 forces it.
+static int prefilter_mode() {
+	static const int mode = [] {
+		const char *e = getenv("RPT_PREFILTER");
+		return e ? atoi(e) : 1;
+	}();
+	return mode;
+}
+static double prefilter_max_pass() {
+	static const double v = [] {
+		const char *e = getenv("RPT_PREFILTER_MAX_PASS");
+		return e ? atof(e) : 0.5;
+	}();
+	return v;
+}
+
+static double prefilter_max_alive() {
+	static const double v = [] {
+		const char *e = getenv("RPT_PREFILTER_MAX_ALIVE");
+		return e ? atof(e) : 0.30;
+	}();
+	return v;
+}
+
+// *measure: the caller must call prefilter_measured(bf, stream) behind the last launch_probe of this call
+static int ensure_prefilter(rpt_bf *bf, uint64_t count, cudaStream_t s, Prefilter *out, bool *use, bool *measure,
+                            int *launches) {
+	*use = false;
+	*measure = false;
+	const int own = bf->fold_mode.load();
+	const int mode = own >= 0 ? own : prefilter_mode();
+	if (mode == 0 || bf->gate.n != 0 || !prefilter_applicable(bf->num_sectors) || count <= (1ULL << 18)) {
+		return 0;
+	}
+	const double max_pass = prefilter_max_pass();
+	std::lock_guard<std::mutex> lock(bf->fold_mu);
+	// feedback of an earlier pre-filtered probe, once its counters have arrived
+	if (bf->fold_stats_pending && cudaEventQuery(bf->fold_stats_ev) == cudaSuccess) {
+		bf->fold_stats_pending = false;
+		const uint64_t rows = bf->fold_stats_host[0], alive = bf->fold_stats_host[1];
+		if (rows >= (1ULL << 20) && alive <= rows) {
+			bf->fold_alive = static_cast<double>(alive) / static_cast<double>(rows);
+		}
+	}
+	cudaGetLastError(); // cudaErrorNotReady of the query is not an error
+	if (mode == 1 && count >= (1ULL << 22)) {
+		if (bf->fold_holdoff > 0) {
+			bf->fold_holdoff--;
+			return 0;
+		}
+		if (bf->fold_alive > prefilter_max_alive()) {
+			// measured (profiles/prefilter_r2q.txt): with a third of the rows surviving, the pre-filtered partition and
+			// its fuller buckets take as long as the plain partition; beyond, longer.  Try again 16 large probes on.
+			bf->fold_alive = -1.0;
+			bf->fold_holdoff = 15;
+			return 0;
+		}
+	}
+	const uint64_t version = bf->content_version.load();
+	if (bf->fold_version != version) {
+		if (count < (1ULL << 22) && mode != 2) {
+			return 0; // a small probe does not pay for a fold (read S words, write 64 MiB)
+		}
+		if (!bf->folded) {
+			RPT_CUDA(cudaMalloc(&bf->folded, kSliceSectors * sizeof(uint64_t)));
+			RPT_CUDA(cudaMalloc(&bf->fold_pop_dev, sizeof(uint64_t)));
+			RPT_CUDA(cudaMallocHost(&bf->fold_pop_host, sizeof(uint64_t)));
+			RPT_CUDA(cudaMalloc(&bf->fold_stats_dev, 2 * sizeof(uint64_t)));
+			RPT_CUDA(cudaMallocHost(&bf->fold_stats_host, 2 * sizeof(uint64_t)));
+			RPT_CUDA(cudaEventCreateWithFlags(&bf->fold_stats_ev, cudaEventDisableTiming));
+		}
+		RPT_CUDA(launch_fold(bf->dev, bf->words, bf->num_sectors, bf->folded, kSliceSectors, bf->fold_pop_dev, s));
+		RPT_CUDA(cudaMemcpyAsync(bf->fold_pop_host, bf->fold_pop_dev, sizeof(uint64_t), cudaMemcpyDeviceToHost, s));
+		RPT_CUDA(cudaStreamSynchronize(s)); // the fold is complete before its version is published to other threads
+		(*launches)++;
+		const double d = static_cast<double>(*bf->fold_pop_host) / (64.0 * static_cast<double>(kSliceSectors));
+		// a key sets 4 bit positions, 3 distinct ones with probability ≈ 0.09 (two of its 6-bit fields collide)
+		bf->fold_pass = 0.91 * d * d * d * d + 0.09 * d * d * d;
+		bf->fold_version = version;
+		if (trace_on()) {
+			fprintf(stderr, "[rpt trace] fold: %llu -> %llu sectors, density %.4f, estimated pass rate %.4f\n",
+			        (unsigned long long)bf->num_sectors, (unsigned long long)kSliceSectors, d, bf->fold_pass);
+		}
+	}
+	if (bf->fold_pass <= max_pass || mode == 2) {
+		out->folded = bf->folded;
+		out->sectors = kSliceSectors;
+		out->stats = nullptr;
+		if (!bf->fold_stats_pending && count >= (1ULL << 22)) { // one measurement in flight at a time
+			RPT_CUDA(cudaMemsetAsync(bf->fold_stats_dev, 0, 2 * sizeof(uint64_t), s));
+			out->stats = bf->fold_stats_dev;
+			bf->fold_stats_pending = true; // until prefilter_measured's event has fired
+			*measure = true;
+		}
+		*use = true;
+	}
+	return 0;
+}
+// behind the last pre-filtered launch of a call that was told to measure: bring the counters to the host
+static int prefilter_measured(rpt_bf *bf, cudaStream_t s) {
+	std::lock_guard<std::mutex> lock(bf->fold_mu);
+	RPT_CUDA(cudaMemcpyAsync(bf->fold_stats_host, bf->fold_stats_dev, 2 * sizeof(uint64_t), cudaMemcpyDeviceToHost, s));
+	RPT_CUDA(cudaEventRecord(bf->fold_stats_ev, s));
+	return 0;
+}
+
 // translate_col0: emit in_sel[flat] instead of flat (BFTableFilter::Filter, bloom_filter.cpp:117-123);
 // the incoming selection is cols[0].sel.
 static int probe_impl(const rpt_bf *bf, const rpt_col_t *cols, int ncols, uint64_t count, uint32_t *sel_out,
@@ -1024,14 +1177,21 @@ static int probe_impl(const rpt_bf *bf, const rpt_col_t *cols, int ncols, uint64
 		const uint32_t *translate = translate_col0 ? dc.c[0].sel : nullptr;
 		Staged st;
 		st.stream = s;
+		Prefilter fold;
+		bool use_fold = false, measure = false;
+		RPT_TRY(ensure_prefilter(mbf, count, s, &fold, &use_fold, &measure, &launches));
+		const Prefilter *foldp = use_fold ? &fold : nullptr;
 		void *scratch;
-		RPT_TRY(st.alloc(&scratch, probe_scratch_bytes(count, bf->num_sectors)));
+		RPT_TRY(st.alloc(&scratch, probe_scratch_bytes(count, bf->num_sectors, use_fold)));
 		PrehashPlan pre;
 		RPT_TRY(plan_prehash(cols, ncols, count, dc, &st, &pre));
 		RPT_TRY(run_prehash(bf->dev, pre, &dc, s, &launches));
-		if (out_mem == RPT_MEM_DEVICE) { // fully asynchronous
+		if (out_mem == RPT_MEM_DEVICE) { // asynchronous (but for the one-off fold of a large filter, ensure_prefilter)
 			RPT_CUDA(launch_probe(bf->dev, dc, count, bf->words, bf->num_sectors, sel_out, found_out, 0, translate,
-			                      scratch, s, &launches, bf->gate.n ? &bf->gate : nullptr));
+			                      scratch, s, &launches, bf->gate.n ? &bf->gate : nullptr, foldp));
+			if (measure) {
+				RPT_TRY(prefilter_measured(mbf, s));
+			}
 			mbf->launches += launches;
 			return 0;
 		}
@@ -1040,7 +1200,10 @@ static int probe_impl(const rpt_bf *bf, const rpt_col_t *cols, int ncols, uint64
 		RPT_TRY(st.alloc(&dfound, sizeof(uint64_t)));
 		RPT_CUDA(launch_probe(bf->dev, dc, count, bf->words, bf->num_sectors, reinterpret_cast<uint32_t *>(dsel),
 		                      reinterpret_cast<uint64_t *>(dfound), 0, translate, scratch, s, &launches,
-		                      bf->gate.n ? &bf->gate : nullptr));
+		                      bf->gate.n ? &bf->gate : nullptr, foldp));
+		if (measure) {
+			RPT_TRY(prefilter_measured(mbf, s));
+		}
 		mbf->launches += launches;
 		RPT_CUDA(cudaMemcpyAsync(found_out, dfound, sizeof(uint64_t), cudaMemcpyDeviceToHost, s));
 		RPT_CUDA(cudaStreamSynchronize(s));
@@ -1084,6 +1247,10 @@ static int probe_impl(const rpt_bf *bf, const rpt_col_t *cols, int ncols, uint64
 			break; // a single chunk uses slot 0 only
 		}
 	}
+	Prefilter fold;
+	bool use_fold = false, measure = false;
+	RPT_TRY(ensure_prefilter(mbf, count, mbf->compute, &fold, &use_fold, &measure, &launches)); // by the call's row count
+	const Prefilter *foldp = use_fold ? &fold : nullptr;
 	uint64_t total = 0;
 	auto drain = [&](uint64_t c) -> int { // chunk c's kernel finished → send its survivors out
 		rpt_bf::PipeSlot &sl = mbf->slot[c % kSlots];
@@ -1111,7 +1278,7 @@ static int probe_impl(const rpt_bf *bf, const rpt_col_t *cols, int ncols, uint64
 			DevCols dc;
 			RPT_TRY(stage_host_cols(cols, ncols, r0, r1, &st, &dc));
 			void *scratch;
-			RPT_TRY(st.alloc(&scratch, probe_scratch_bytes(r1 - r0, bf->num_sectors)));
+			RPT_TRY(st.alloc(&scratch, probe_scratch_bytes(r1 - r0, bf->num_sectors, use_fold)));
 			PrehashPlan pre;
 			RPT_TRY(plan_prehash(cols, ncols, r1 - r0, dc, &st, &pre));
 			RPT_CUDA(cudaEventRecord(sl.uploaded, mbf->h2d));
@@ -1121,13 +1288,16 @@ static int probe_impl(const rpt_bf *bf, const rpt_col_t *cols, int ncols, uint64
 			const uint32_t *translate = translate_col0 ? dc.c[0].sel : nullptr;
 			RPT_CUDA(launch_probe(bf->dev, dc, r1 - r0, bf->words, bf->num_sectors, sl.dsel, sl.dfound,
 			                      static_cast<uint32_t>(r0), translate, scratch, mbf->compute, &launches,
-			                      bf->gate.n ? &bf->gate : nullptr));
+			                      bf->gate.n ? &bf->gate : nullptr, foldp));
 			RPT_CUDA(cudaMemcpyAsync(sl.hfound, sl.dfound, sizeof(uint64_t), cudaMemcpyDeviceToHost, mbf->compute));
 			RPT_CUDA(cudaEventRecord(sl.computed, mbf->compute));
 			sl.pending = true;
 			if (c >= static_cast<uint64_t>(kSlots - 1)) {
 				RPT_TRY(drain(c - (kSlots - 1))); // frees the slot the next chunk will use
 			}
+		}
+		if (measure) {
+			RPT_TRY(prefilter_measured(mbf, mbf->compute));
 		}
 		for (uint64_t d = c >= static_cast<uint64_t>(kSlots - 1) ? c - (kSlots - 1) : 0; d < c; d++) {
 			RPT_TRY(drain(d));
@@ -1386,6 +1556,7 @@ int rpt_bf_import_words(rpt_bf_t *bf, const uint64_t *host_src, uint64_t num_wor
 		                 (unsigned long long)bf->num_sectors);
 	}
 	RPT_GUARD(bf);
+	bf->content_version++;
 	RPT_CUDA(cudaMemcpyAsync(bf->words, host_src, num_words * sizeof(uint64_t), cudaMemcpyHostToDevice, bf->stream));
 	RPT_CUDA(cudaStreamSynchronize(bf->stream));
 	bf->has_data.store(1);
@@ -1431,6 +1602,7 @@ int rpt_bf_or_parts(rpt_bf_t *bf, const uint64_t *dev_parts, uint64_t nparts, rp
 	if (nparts == 0) {
 		return 0;
 	}
+	bf->content_version++;
 	RPT_CUDA(launch_or_parts(bf->dev, bf->words, dev_parts, bf->num_sectors, nparts, pick_stream(bf, stream)));
 	bf->launches += 1;
 	return 0;
@@ -1492,6 +1664,7 @@ static void peer_slice(uint64_t S, int n, int r, uint64_t *off, uint64_t *len) {
 static int peer_merge_range(rpt_bf *bf, int phase, uint64_t first, uint64_t nsectors, cudaStream_t s) {
 	const int n = static_cast<int>(bf->peer_words.size());
 	const int rank = bf->peer_rank;
+	bf->content_version++;
 	if (phase == 0) {
 		PtrList srcs;
 		srcs.n = 0;

@@ -62,6 +62,10 @@ __device__ __forceinline__ void st_stream_v4(void *ptr, const uint4 v, uint64_t 
 	             "r"(v.w), "l"(pol)
 	             : "memory");
 }
+__device__ __forceinline__ void st_stream_v2(void *ptr, const uint2 v, uint64_t pol) {
+	asm volatile("st.global.L2::cache_hint.v2.b32 [%0], {%1, %2}, %3;" ::"l"(ptr), "r"(v.x), "r"(v.y), "l"(pol)
+	             : "memory");
+}
 __device__ __forceinline__ uint32_t lanemask_lt() {
 	uint32_t m;
 	asm("mov.u32 %0, %%lanemask_lt;" : "=r"(m));
@@ -1041,14 +1045,19 @@ static_assert((1ULL << kSliceShift) == kSliceSectors, "record layout assumes 2^2
 
 // INLINE0: the keys of slice 0 are looked up by the partition kernel itself (P-1 bucket regions per segment);
 // otherwise slice 0 is a bucket like the others (P regions, no filter access in the partition kernel).
-template <int P, bool INLINE0 = true>
+template <int P, bool INLINE0 = true, bool PRE = false>
 struct PartCfg {
 	static_assert(P == 2 || P == 4 || P == 8, "S is a power of two: 2, 4 or 8 slices");
+	static_assert(!PRE || !INLINE0, "the pre-filtered partition keeps slice 0 as a bucket");
 	// records per (segment, slice) region; expectation 512/P, σ = sqrt(512·(1/P)(1-1/P)): +5.6σ / +4.1σ / +4.3σ
 	static constexpr int CAP = P == 2 ? 320 : (P == 4 ? 168 : 96);
 	static constexpr int FIRST = INLINE0 ? 1 : 0; // first slice that has a bucket
 	static constexpr int REGIONS = P - FIRST;
-	static constexpr int STAGE_BYTES = REGIONS * CAP * 8;
+	// The shared-memory stage of a warp holds one CAP-sized area per region — or, PRE, the regions PACKED one behind
+	// the other (a segment has 512 keys, so 4 KiB always suffice and the stage aliases the key buffer: with a separate
+	// 5.3-KiB stage a warp took 13.5 KiB, 217 KiB per SM, and the L1 that was left could not keep the folded-filter
+	// gathers in flight — 16.5 ms per 10^9 keys instead of 4).
+	static constexpr int STAGE_BYTES = PRE ? static_cast<int>(kSegRows) * 8 : REGIONS * CAP * 8;
 	static constexpr int NCNT = P <= 4 ? 1 : 2; // per-lane counters: 8 bits per slice, four slices per register
 };
 
@@ -1056,12 +1065,12 @@ struct PartCfg {
 // stage.  When the stage fits into one key buffer it ALIASES the buffer of the segment being processed (its
 // keys are in registers by then), which keeps a warp at 8 KiB.  Two CTAs per SM: at three (80 registers) the
 // sixteen hashes spill, and the spill traffic on the LSU costs more than the extra warps hide (9.0 vs 7.3 ms).
-template <class Src, int P, bool INLINE0 = true>
+template <class Src, int P, bool INLINE0 = true, bool PRE = false>
 struct PartSmem {
 	static constexpr int KEY_SEG_BYTES = Src::kStageable ? static_cast<int>(kSegRows) * Src::kKeyBytes : 0;
-	static constexpr bool ALIAS = Src::kStageable && PartCfg<P, INLINE0>::STAGE_BYTES <= KEY_SEG_BYTES;
+	static constexpr bool ALIAS = Src::kStageable && PartCfg<P, INLINE0, PRE>::STAGE_BYTES <= KEY_SEG_BYTES;
 	static constexpr int WARP_BYTES =
-	    2 * KEY_SEG_BYTES + (ALIAS ? 0 : (PartCfg<P, INLINE0>::STAGE_BYTES + 15) / 16 * 16);
+	    2 * KEY_SEG_BYTES + (ALIAS ? 0 : (PartCfg<P, INLINE0, PRE>::STAGE_BYTES + 15) / 16 * 16);
 };
 
 __device__ __forceinline__ uint32_t shl_clamp(uint32_t v, uint32_t s) { // PTX shl.b32: a shift ≥ 32 yields 0
@@ -1070,18 +1079,24 @@ __device__ __forceinline__ uint32_t shl_clamp(uint32_t v, uint32_t s) { // PTX s
 	return d;
 }
 
-template <class Src, int BLOCK, int P, int SHIFT = kSliceShift, bool INLINE0 = true>
+// PRE: every key is first tested against the FOLDED filter (folded[i] = OR of the words i + j·(fold_mask+1), one
+// L2-resident slice: fold_kernel below).  A key whose four bits are not all set in the folded word cannot have them
+// set in its own word, so it is dropped on the spot; only the survivors (members + the folded filter's false
+// positives) become records and meet the real filter in the bucket kernels.
+template <class Src, int BLOCK, int P, int SHIFT = kSliceShift, bool INLINE0 = true, bool PRE = false>
 __global__ void __launch_bounds__(BLOCK, 2)
     probe_partition_kernel(const Src src, const uint64_t *__restrict__ filter, const uint32_t sector_mask,
                            const uint64_t count, const uint64_t num_segs, uint16_t *__restrict__ bitmap16,
                            uint2 *__restrict__ buckets, const uint64_t bucket_stride /* records per slice array */,
                            uint16_t *__restrict__ bucket_counts /* (P-1) × num_segs */,
-                           uint32_t *__restrict__ ovf_list /* [0] = count, [1 + i] = i-th overflowed segment */) {
+                           uint32_t *__restrict__ ovf_list /* [0] = count, [1 + i] = i-th overflowed segment */,
+                           const uint64_t *__restrict__ folded = nullptr, const uint32_t fold_mask = 0,
+                           unsigned long long *__restrict__ pre_stats = nullptr /* PRE: [0] += rows, [1] += survivors */) {
 	constexpr int NWARPS = BLOCK / 32;
 	constexpr bool STAGED = Src::kStageable;
 	using Geo = StageGeo<Src::kKeyBytes>;
-	using Smem = PartSmem<Src, P, INLINE0>;
-	using Cfg = PartCfg<P, INLINE0>;
+	using Smem = PartSmem<Src, P, INLINE0, PRE>;
+	using Cfg = PartCfg<P, INLINE0, PRE>;
 	constexpr int SEG_UNITS = Geo::SEG_UNITS;
 	constexpr int CAP = Cfg::CAP;
 	constexpr int NCNT = Cfg::NCNT;
@@ -1093,9 +1108,12 @@ __global__ void __launch_bounds__(BLOCK, 2)
 	uint4 *const my_buf = reinterpret_cast<uint4 *>(my_smem);
 	const uint64_t pol_keys = policy_evict_first();
 	const uint64_t pol_filter = policy_evict_last();
-	if (INLINE0) {
+	if (PRE) {
+		warm_slice(folded, 0u, fold_mask + 1u, BLOCK);
+	} else if (INLINE0) {
 		warm_slice(filter, 0u, 1u << SHIFT, BLOCK);
 	}
+	constexpr bool MASKED = PRE || !INLINE0; // keys outside `alive` are neither counted nor written as records
 	const uint64_t stride = static_cast<uint64_t>(gridDim.x) * NWARPS;
 	const uint64_t full_segs = count / kSegRows;
 	const uint32_t rot = Geo::rot(lane);
@@ -1103,6 +1121,7 @@ __global__ void __launch_bounds__(BLOCK, 2)
 	constexpr uint64_t kNone = ~0ULL;
 	uint64_t cur = kNone;
 	uint32_t par = 1;
+	uint32_t seen_rows = 0, seen_alive = 0; // PRE: this lane's rows and folded-filter survivors (feedback for the host)
 	for (uint64_t nxt = static_cast<uint64_t>(blockIdx.x) * NWARPS + warp;; nxt += stride) {
 		if (STAGED) {
 			__syncwarp(); // the buffer overwritten next (keys and, when aliased, records) is no longer read
@@ -1150,6 +1169,13 @@ __global__ void __launch_bounds__(BLOCK, 2)
 			uint2 *const stage = reinterpret_cast<uint2 *>(
 			    my_smem + (Smem::ALIAS ? par * Smem::KEY_SEG_BYTES : 2 * Smem::KEY_SEG_BYTES));
 			const uint32_t unit_rot = staged_seg ? rot : 0u;
+			// slot-order mask of the keys that still need the real filter (PRE: survivors of the folded filter)
+			uint32_t alive = valid;
+			if (PRE) {
+				alive &= test_batch<16, false, false>(h, folded, nullptr, fold_mask, pol_filter, 0u, 0u);
+				seen_rows += __popc(valid);
+				seen_alive += __popc(alive);
+			}
 
 			// pass 1: per-lane counts of the keys of every slice (8-bit fields); the slice-0 lookups of the first
 			// eight keys are issued (the second eight follow in pass 2, behind the records of the first eight)
@@ -1159,8 +1185,9 @@ __global__ void __launch_bounds__(BLOCK, 2)
 				for (int i = 0; i < 8; i++) {
 					const uint32_t sector = static_cast<uint32_t>(h[lo + i]) & sector_mask;
 					w0[i] = 0;
-					if (INLINE0 && (sector >> SHIFT) == 0u) {
-						w0[i] = ld_filter_word(filter + sector, pol_filter);
+					if (INLINE0 && (sector >> SHIFT) == 0u && (!PRE || ((alive >> (lo + i)) & 1u))) {
+						// PRE: the few real slice-0 words must not push the folded filter out of L2
+						w0[i] = ld_filter_word(filter + sector, PRE ? pol_keys : pol_filter);
 					}
 				}
 			};
@@ -1185,11 +1212,12 @@ __global__ void __launch_bounds__(BLOCK, 2)
 			for (int i = 0; i < 16; i++) {
 				const uint32_t sector = static_cast<uint32_t>(h[i]) & sector_mask;
 				const uint32_t sh = (sector >> (SHIFT - 3)) & ((P - 1u) << 3); // 8 · slice
+				const uint32_t one = MASKED ? (alive >> i) & 1u : 1u; // dropped keys and rows past the end are not counted
 				if (NCNT == 1) {
-					cnt[0] += 1u << sh;
+					cnt[0] += one << sh;
 				} else {
-					cnt[0] += shl_clamp(1u, sh);
-					cnt[1] += shl_clamp(1u, sh ^ 32u);
+					cnt[0] += shl_clamp(one, sh);
+					cnt[1] += shl_clamp(one, sh ^ 32u);
 				}
 			}
 			// warp scan on 16-bit fields; base[j] = exclusive prefixes of slices 4j..4j+3 as one 64-bit word
@@ -1230,6 +1258,27 @@ __global__ void __launch_bounds__(BLOCK, 2)
 					    overflow ? uint16_t(0) : static_cast<uint16_t>(slice_total(s));
 				}
 			}
+			// PRE: the regions are packed in the stage — region s starts at the number of records of the slices before it
+			// (warp-uniform); adding that to the 16-bit fields of `base` makes a record's position stage-absolute
+			uint32_t stage_first[PRE ? P : 1];
+			if (PRE) {
+				uint32_t run = 0;
+				uint64_t add[NCNT];
+#pragma unroll
+				for (int j = 0; j < NCNT; j++) {
+					add[j] = 0;
+				}
+#pragma unroll
+				for (int s = 0; s < P; s++) {
+					stage_first[s] = run;
+					add[s >> 2] |= static_cast<uint64_t>(run) << (16 * (s & 3));
+					run += slice_total(s);
+				}
+#pragma unroll
+				for (int j = 0; j < NCNT; j++) {
+					base[j] += add[j]; // no carries: prefix + start ≤ 512
+				}
+			}
 			uint32_t hits = 0;
 			if (!overflow) { // warp-uniform; the usual case
 				// pass 2: records into the stage.  position = exclusive base of the slice + rank inside the lane
@@ -1240,24 +1289,26 @@ __global__ void __launch_bounds__(BLOCK, 2)
 						const uint32_t sector = static_cast<uint32_t>(h[i]) & sector_mask;
 						const uint32_t sh = (sector >> (SHIFT - 3)) & ((P - 1u) << 3);
 						const uint32_t shr = sh & 31u;
+						const uint32_t one = MASKED ? (alive >> i) & 1u : 1u;
 						uint32_t rank, pos;
 						if (NCNT == 1) {
 							rank = (cnt[0] >> shr) & 0xffu;
-							cnt[0] += 1u << shr;
+							cnt[0] += one << shr;
 							pos = static_cast<uint32_t>(base[0] >> (2u * shr)) & 0xffffu;
 						} else {
 							const bool up = sh >= 32u;
 							rank = ((up ? cnt[1] : cnt[0]) >> shr) & 0xffu;
-							cnt[0] += up ? 0u : 1u << shr;
-							cnt[1] += up ? 1u << shr : 0u;
+							cnt[0] += up ? 0u : one << shr;
+							cnt[1] += up ? one << shr : 0u;
 							pos = static_cast<uint32_t>((up ? base[1] : base[0]) >> (2u * shr)) & 0xffffu;
 						}
 						pos += rank;
-						if (!INLINE0 || sh != 0u) {
+						if ((!INLINE0 || sh != 0u) && one) {
 							const uint32_t row9 =
 							    lane * 16u + (((i / Geo::KPU + unit_rot) & (Geo::U - 1)) * Geo::KPU) + (i % Geo::KPU);
-							// byte offset of record `pos` of slice s: ((s-FIRST)·CAP + pos)·8 with 8·s = sh
-							const uint32_t off = mul_lo_u32(sh, CAP) + pos * 8u - FIRST * CAP * 8u;
+							// byte offset of record `pos` of slice s: ((s-FIRST)·CAP + pos)·8 with 8·s = sh (PRE: pos is
+							// already stage-absolute)
+							const uint32_t off = PRE ? pos * 8u : mul_lo_u32(sh, CAP) + pos * 8u - FIRST * CAP * 8u;
 							*reinterpret_cast<uint2 *>(reinterpret_cast<unsigned char *>(stage) + off) =
 							    make_uint2((sector & ((1u << SHIFT) - 1u)) | (row9 << SHIFT),
 							               static_cast<uint32_t>(h[i] >> 32));
@@ -1294,6 +1345,14 @@ __global__ void __launch_bounds__(BLOCK, 2)
 #pragma unroll
 				for (int s = FIRST; s < P; s++) {
 					const uint32_t total = slice_total(s);
+					if (PRE) { // packed regions start at any record: 8-byte copies (few records per region)
+						const uint2 *sv = stage + stage_first[s];
+						uint2 *dv = buckets + s * bucket_stride + cur * CAP;
+						for (uint32_t j = lane; j < total; j += 32u) {
+							st_stream_v2(dv + j, sv[j], pol_keys);
+						}
+						continue;
+					}
 					const uint4 *sv = reinterpret_cast<const uint4 *>(stage + (s - FIRST) * CAP);
 					uint4 *dv = reinterpret_cast<uint4 *>(buckets + (s - FIRST) * bucket_stride + cur * CAP);
 					for (uint32_t j = lane; 2u * j < total; j += 32u) {
@@ -1313,6 +1372,14 @@ __global__ void __launch_bounds__(BLOCK, 2)
 	}
 	if (STAGED) {
 		cp_async_wait<0>();
+	}
+	if (PRE && pre_stats != nullptr) {
+		seen_rows = __reduce_add_sync(0xffffffffu, seen_rows);
+		seen_alive = __reduce_add_sync(0xffffffffu, seen_alive);
+		if (lane == 0) {
+			atomicAdd(pre_stats, static_cast<unsigned long long>(seen_rows));
+			atomicAdd(pre_stats + 1, static_cast<unsigned long long>(seen_alive));
+		}
 	}
 }
 
@@ -1386,6 +1453,105 @@ __global__ void __launch_bounds__(256)
 				atomicOr(bitmap32 + seg * 16 + (row9 >> 5), 1u << (row9 & 31u));
 			}
 		}
+	}
+}
+
+// Bucket kernel of the pre-filtered partition (PRE): regions are sparse (a handful of survivors per segment and
+// slice instead of 512/P), so a warp takes FOUR consecutive regions at a time — their counts, then their first 32
+// records, then the filter words are in flight together — and only a region with more than 32 records (a segment
+// full of members) loops.
+template <int CAP, int SHIFT = kSliceShift>
+__global__ void __launch_bounds__(256)
+    probe_bucket_sparse_kernel(const uint2 *__restrict__ bucket, const uint16_t *__restrict__ counts,
+                               const uint64_t num_segs, const uint64_t *__restrict__ filter, const uint32_t slice_lo,
+                               uint32_t *__restrict__ bitmap32) {
+	constexpr int R = 4;
+	const uint32_t lane = threadIdx.x & 31u;
+	const uint64_t pol_rec = policy_evict_first();
+	const uint64_t pol_filter = policy_evict_last();
+	warm_slice(filter, slice_lo, 1u << SHIFT, 256);
+	const uint64_t *const slice = filter + slice_lo;
+	const uint64_t warp_global = (static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
+	const uint64_t num_warps = (static_cast<uint64_t>(gridDim.x) * blockDim.x) >> 5;
+	for (uint64_t seg0 = warp_global * R; seg0 < num_segs; seg0 += num_warps * R) {
+		uint32_t c[R];
+#pragma unroll
+		for (int r = 0; r < R; r++) {
+			c[r] = seg0 + r < num_segs ? __ldg(counts + seg0 + r) : 0u;
+		}
+		uint2 rec[R];
+#pragma unroll
+		for (int r = 0; r < R; r++) {
+			rec[r] = make_uint2(0u, 0u);
+			if (lane < c[r]) {
+				const uint64_t v = ld_stream_u64(bucket + (seg0 + r) * CAP + lane, pol_rec);
+				rec[r] = make_uint2(static_cast<uint32_t>(v), static_cast<uint32_t>(v >> 32));
+			}
+		}
+		uint64_t w[R];
+#pragma unroll
+		for (int r = 0; r < R; r++) {
+			w[r] = 0; // an all-zero word (no record) passes nothing
+			if (lane < c[r]) {
+				w[r] = ld_filter_word(slice + (rec[r].x & ((1u << SHIFT) - 1u)), pol_filter);
+			}
+		}
+#pragma unroll
+		for (int r = 0; r < R; r++) {
+			if (sector_test_fma(w[r], rec[r].y)) {
+				const uint32_t row9 = rec[r].x >> SHIFT;
+				atomicOr(bitmap32 + (seg0 + r) * 16 + (row9 >> 5), 1u << (row9 & 31u));
+			}
+		}
+#pragma unroll
+		for (int r = 0; r < R; r++) {
+			for (uint32_t j = lane + 32u; j < c[r]; j += 32u) { // warp-uniform bound: rare
+				const uint64_t v = ld_stream_u64(bucket + (seg0 + r) * CAP + j, pol_rec);
+				const uint32_t x = static_cast<uint32_t>(v);
+				const uint64_t word = ld_filter_word(slice + (x & ((1u << SHIFT) - 1u)), pol_filter);
+				if (sector_test_fma(word, static_cast<uint32_t>(v >> 32))) {
+					const uint32_t row9 = x >> SHIFT;
+					atomicOr(bitmap32 + (seg0 + r) * 16 + (row9 >> 5), 1u << (row9 & 31u));
+				}
+			}
+		}
+	}
+}
+
+// folded[i] = OR over j of words[i + j·fold_sectors] (i < fold_sectors), and the number of set bits of the folded
+// filter (→ the share of non-members that will survive it).  128-bit loads, one slice after the other per thread.
+__global__ void __launch_bounds__(256)
+    fold_kernel(const ulonglong2 *__restrict__ words, const uint64_t fold_vecs, const uint32_t nslices,
+                ulonglong2 *__restrict__ folded, unsigned long long *__restrict__ popcount_out) {
+	__shared__ unsigned long long s_pop[8];
+	unsigned long long pop = 0;
+	const uint64_t step = static_cast<uint64_t>(gridDim.x) * blockDim.x;
+	for (uint64_t i = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < fold_vecs; i += step) {
+		ulonglong2 acc = make_ulonglong2(0ULL, 0ULL);
+#pragma unroll 4
+		for (uint32_t j = 0; j < nslices; j++) {
+			const ulonglong2 v = __ldcs(words + i + j * fold_vecs);
+			acc.x |= v.x;
+			acc.y |= v.y;
+		}
+		folded[i] = acc;
+		pop += __popcll(acc.x) + __popcll(acc.y);
+	}
+#pragma unroll
+	for (int d = 16; d > 0; d >>= 1) {
+		pop += __shfl_xor_sync(0xffffffffu, pop, d);
+	}
+	if ((threadIdx.x & 31u) == 0) {
+		s_pop[threadIdx.x >> 5] = pop;
+	}
+	__syncthreads();
+	if (threadIdx.x == 0) {
+		unsigned long long t = 0;
+#pragma unroll
+		for (int w = 0; w < 8; w++) {
+			t += s_pop[w];
+		}
+		atomicAdd(popcount_out, t);
 	}
 }
 
@@ -1877,6 +2043,10 @@ static inline int partition_choice(uint64_t num_sectors) {
 	}
 	return slices;
 }
+// Filters the folded pre-filter exists for: 4 or 8 slices of 64 MiB (256 / 512 MiB)
+bool prefilter_applicable(uint64_t num_sectors) {
+	return num_sectors == 4 * kSliceSectors || num_sectors == 8 * kSliceSectors;
+}
 static inline int partition_cap(int slices) {
 	return slices == 2 ? PartCfg<2>::CAP : (slices == 4 ? PartCfg<4>::CAP : PartCfg<8>::CAP);
 }
@@ -1906,20 +2076,27 @@ static PartPlan partition_plan(uint64_t num_sectors, int slices64) {
 }
 // extra scratch behind the phased layout (R = bucket regions per segment, P or P-1):
 // [bucket counts u16 × R·segs][overflow list u32 × (1 + segs)][records 8 B × R·segs·CAP]
-static size_t partition_scratch_bytes(uint64_t count, uint64_t num_sectors, int slices64) {
+static size_t partition_scratch_bytes(uint64_t count, uint64_t num_sectors, int slices64, bool prefilter) {
 	const uint64_t num_segs = ceil_div(count, kSegRows);
-	const PartPlan plan = partition_plan(num_sectors, slices64);
+	PartPlan plan = partition_plan(num_sectors, slices64);
+	if (prefilter) { // the pre-filtered partition: 64-MiB slices, slice 0 a bucket like the others
+		plan = PartPlan {slices64, static_cast<int>(kSliceShift), false};
+	}
 	const uint64_t regions = plan.slices - (plan.inline0 ? 1 : 0);
 	return align_up(regions * num_segs * sizeof(uint16_t), 256) + align_up((num_segs + 1) * sizeof(uint32_t), 256) +
 	       regions * num_segs * partition_cap(plan.slices) * sizeof(uint2);
 }
 
-size_t probe_scratch_bytes(uint64_t count, uint64_t num_sectors) {
+size_t probe_scratch_bytes(uint64_t count, uint64_t num_sectors, bool prefilter) {
 	if (count <= kFusedMaxKeys) {
 		return (ceil_div(count, kProbeTileKeys) + 2) * sizeof(uint64_t); // look-back descriptors + ticket
 	}
-	const int slices = partition_slices(num_sectors);
-	return align_up(phased_layout(count).bytes, 256) + (slices ? partition_scratch_bytes(count, num_sectors, slices) : 0);
+	int slices = partition_slices(num_sectors);
+	if (prefilter && prefilter_applicable(num_sectors)) {
+		slices = static_cast<int>(num_sectors / kSliceSectors);
+	}
+	return align_up(phased_layout(count).bytes, 256) +
+	       (slices ? partition_scratch_bytes(count, num_sectors, slices, prefilter) : 0);
 }
 
 template <class Src, bool AGG, bool MM>
@@ -2191,21 +2368,23 @@ static cudaError_t launch_probe_phased(const DeviceInfo &dev, const Src &src, ui
 	}
 }
 
-template <class Src, int P, int SHIFT = kSliceShift, bool INLINE0 = true>
+static thread_local const Prefilter *t_pre = nullptr;
+
+template <class Src, int P, int SHIFT = kSliceShift, bool INLINE0 = true, bool PRE = false>
 static cudaError_t launch_probe_partitioned(const DeviceInfo &dev, const Src &src, uint64_t count,
                                             const uint64_t *words, uint64_t num_sectors, uint32_t *sel_out,
                                             uint64_t *found_out, uint32_t row_offset, const uint32_t *translate,
                                             void *scratch, cudaStream_t stream, int *launches) {
 	constexpr int BLOCK = kProbeBlock;
-	using Cfg = PartCfg<P, INLINE0>;
+	using Cfg = PartCfg<P, INLINE0, PRE>;
 	constexpr int CAP = Cfg::CAP;
 	constexpr int FIRST = Cfg::FIRST;
 	constexpr int REGIONS = Cfg::REGIONS;
-	auto part = probe_partition_kernel<Src, BLOCK, P, SHIFT, INLINE0>;
-	auto bucket = probe_bucket_kernel<CAP, SHIFT>;
+	auto part = probe_partition_kernel<Src, BLOCK, P, SHIFT, INLINE0, PRE>;
+	auto bucket = PRE ? probe_bucket_sparse_kernel<CAP, SHIFT> : probe_bucket_kernel<CAP, SHIFT>;
 	const uint64_t num_segs = ceil_div(count, kSegRows);
-	const size_t smem = static_cast<size_t>(BLOCK / 32) * PartSmem<Src, P, INLINE0>::WARP_BYTES;
-	cudaError_t e = ensure_max_dyn_smem<probe_partition_kernel<Src, BLOCK, P, SHIFT, INLINE0>>(dev);
+	const size_t smem = static_cast<size_t>(BLOCK / 32) * PartSmem<Src, P, INLINE0, PRE>::WARP_BYTES;
+	cudaError_t e = ensure_max_dyn_smem<probe_partition_kernel<Src, BLOCK, P, SHIFT, INLINE0, PRE>>(dev);
 	if (e != cudaSuccess) {
 		return e;
 	}
@@ -2257,16 +2436,18 @@ static cudaError_t launch_probe_partitioned(const DeviceInfo &dev, const Src &sr
 			return e;
 		}
 	}
-	part<<<static_cast<unsigned>(grid), BLOCK, smem, stream>>>(src, words, static_cast<uint32_t>(num_sectors - 1), count,
-	                                                          num_segs, bitmap, buckets, bucket_stride, bucket_counts,
-	                                                          gated ? overflow : nullptr);
+	part<<<static_cast<unsigned>(grid), BLOCK, smem, stream>>>(
+	    src, words, static_cast<uint32_t>(num_sectors - 1), count, num_segs, bitmap, buckets, bucket_stride, bucket_counts,
+	    gated ? overflow : nullptr, PRE ? t_pre->folded : nullptr,
+	    PRE ? static_cast<uint32_t>(t_pre->sectors - 1) : 0u,
+	    PRE ? reinterpret_cast<unsigned long long *>(t_pre->stats) : nullptr);
 	int bper_sm = 0;
 	e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bper_sm, bucket, 256, 0);
 	if (e != cudaSuccess) {
 		return e;
 	}
 	uint64_t bgrid = static_cast<uint64_t>(dev.sm_count) * (bper_sm > 0 ? bper_sm : 1);
-	const uint64_t bwant = ceil_div(num_segs, 8);
+	const uint64_t bwant = ceil_div(num_segs, PRE ? 32 : 8); // the sparse kernel takes four regions per warp
 	bgrid = bgrid < bwant ? bgrid : bwant;
 	for (int s = FIRST; s < P; s++) {
 		e = wait_slices(stream, gate_of(s), gate_of(s));
@@ -2314,6 +2495,14 @@ static cudaError_t launch_probe_src(const DeviceInfo &dev, const Src &src, uint6
 	if (count <= kFusedMaxKeys) {
 		return smem ? launch_probe_fused<Src, kProbeBlockSmem, true>(RPT_PROBE_ARGS)
 		            : launch_probe_fused<Src, kProbeBlock, false>(RPT_PROBE_ARGS);
+	}
+	if (t_pre != nullptr && prefilter_applicable(num_sectors) && t_pre->sectors == kSliceSectors &&
+	    (t_gate == nullptr || t_gate->n == 0)) {
+		// folded pre-filter: slice 0 is a bucket like the others (the partition kernel touches the folded filter only)
+		if (num_sectors == 4 * kSliceSectors) {
+			return launch_probe_partitioned<Src, 4, static_cast<int>(kSliceShift), false, true>(RPT_PROBE_ARGS);
+		}
+		return launch_probe_partitioned<Src, 8, static_cast<int>(kSliceShift), false, true>(RPT_PROBE_ARGS);
 	}
 	const int slices64 = smem ? 0 : partition_choice<Src>(num_sectors);
 	if constexpr (Src::kStageable && Src::kKeyBytes == 8 && !Src::kNullable) { // experiment variants: flat 8-byte keys only
@@ -2363,11 +2552,13 @@ static cudaError_t launch_probe_gated(const DeviceInfo &dev, const DevCols &cols
 cudaError_t launch_probe(const DeviceInfo &dev, const DevCols &cols, uint64_t count, const uint64_t *words,
                          uint64_t num_sectors, uint32_t *sel_out, uint64_t *found_out, uint32_t row_offset,
                          const uint32_t *translate, void *scratch, cudaStream_t stream, int *launches,
-                         const SliceGate *gate) {
+                         const SliceGate *gate, const Prefilter *pre) {
 	t_gate = gate;
+	t_pre = pre;
 	const cudaError_t e = launch_probe_gated(dev, cols, count, words, num_sectors, sel_out, found_out, row_offset,
 	                                         translate, scratch, stream, launches);
 	t_gate = nullptr;
+	t_pre = nullptr;
 	return e;
 }
 
@@ -2434,6 +2625,19 @@ cudaError_t launch_bitmap_to_sel(const DeviceInfo &dev, uint64_t count, uint32_t
 	if (launches) {
 		(*launches) += 4;
 	}
+	return cudaGetLastError();
+}
+
+cudaError_t launch_fold(const DeviceInfo &dev, const uint64_t *words, uint64_t num_sectors, uint64_t *folded,
+                        uint64_t fold_sectors, uint64_t *popcount_out, cudaStream_t stream) {
+	cudaError_t e = cudaMemsetAsync(popcount_out, 0, sizeof(uint64_t), stream);
+	if (e != cudaSuccess) {
+		return e;
+	}
+	const uint64_t vecs = fold_sectors >> 1;
+	fold_kernel<<<stream_grid(dev, vecs, 256), 256, 0, stream>>>(
+	    reinterpret_cast<const ulonglong2 *>(words), vecs, static_cast<uint32_t>(num_sectors / fold_sectors),
+	    reinterpret_cast<ulonglong2 *>(folded), reinterpret_cast<unsigned long long *>(popcount_out));
 	return cudaGetLastError();
 }
 

@@ -47,7 +47,8 @@ constexpr uint64_t kSmemFilterMaxSectors = 1ULL << 14; // 128 KiB
 constexpr uint64_t kSliceSectors = 1ULL << 23;
 
 // Scratch the probe kernel needs for `count` rows: tile descriptors + ticket counter (bytes).
-size_t probe_scratch_bytes(uint64_t count, uint64_t num_sectors);
+// prefilter: the probe will be given a folded pre-filter (launch_probe's `pre`), whose partition uses one more region
+size_t probe_scratch_bytes(uint64_t count, uint64_t num_sectors, bool prefilter = false);
 
 // Column range (UpdateMinMax, physical_create_bf.cpp:82-176).  Keys are order-preserving uint64 images of the
 // values (signed: value ^ 2^63 after sign extension; float/double: sign-magnitude flip); the host decodes them.
@@ -73,10 +74,21 @@ struct SliceGate {
 	cudaEvent_t ev[8]; // S ≤ 2^26 sectors = 8 slices of kSliceSectors
 	int n;
 };
+// pre (optional): the folded pre-filter of `words` (launch_fold below).  Filters of 256 / 512 MiB then take the
+// pre-filtered partition: every key meets the L2-resident folded filter first and only its survivors are looked up
+// in the real words — same answers (a key the folded filter rejects cannot pass the real one), far fewer records.
+struct Prefilter {
+	const uint64_t *folded; // `sectors` words: folded[i] = OR of words[i + j·sectors]
+	uint64_t sectors;       // kSliceSectors
+	uint64_t *stats;        // optional device counters: [0] += rows probed, [1] += rows that survived the folded filter
+};
+bool prefilter_applicable(uint64_t num_sectors);
+cudaError_t launch_fold(const DeviceInfo &dev, const uint64_t *words, uint64_t num_sectors, uint64_t *folded,
+                        uint64_t fold_sectors, uint64_t *popcount_out, cudaStream_t stream);
 cudaError_t launch_probe(const DeviceInfo &dev, const DevCols &cols, uint64_t count, const uint64_t *words,
                          uint64_t num_sectors, uint32_t *sel_out, uint64_t *found_out, uint32_t row_offset,
                          const uint32_t *translate, void *scratch, cudaStream_t stream, int *launches,
-                         const SliceGate *gate = nullptr);
+                         const SliceGate *gate = nullptr, const Prefilter *pre = nullptr);
 
 // words[i] |= parts[p*S + i] for p < nparts
 cudaError_t launch_or_parts(const DeviceInfo &dev, uint64_t *words, const uint64_t *parts, uint64_t num_sectors,

@@ -162,6 +162,19 @@ RPT_API int rpt_bf_minmax_get(const rpt_bf_t *bf, int *has_value, int *has_nan, 
  *     are filled (key columns may be host or device). */
 RPT_API int rpt_bf_probe(const rpt_bf_t *bf, const rpt_col_t *cols, int ncols, uint64_t count, uint32_t *sel_out,
                          uint64_t *found_out, int out_mem, rpt_stream_t stream);
+/* Folded pre-filter of large probes.  No counterpart in the reference — an accelerator of LookupHashes
+ * (duckdb bloom_filter.cpp:50-61) that never changes its answers.  For filters of 256 / 512 MiB (4 or 8 L2-sized
+ * slices) a probe call of >= 2^22 rows first ORs the slices into one 64-MiB "folded" filter (once per content of the
+ * words; made again after any insert / reset / merge / import): a key whose four bits are not all set in the folded
+ * word cannot have them set in its own word, so every key meets the L2-resident folded filter first and only its
+ * survivors are looked up in the real words.  The fold costs one read of the words plus one stream synchronisation
+ * (the host reads the folded filter's bit density and switches the pre-filter off when more than half of the
+ * non-member keys would survive it).
+ *   mode: -1 library default (environment RPT_PREFILTER, default 1), 0 never, 1 by density, 2 always (tests).
+ *   rpt_bf_prefilter_info: *state_out = 0 no fold made for the current words, 1 made and in use, 2 made but too dense;
+ *   *pass_rate_out = estimated share of non-member keys that survive the folded filter. */
+RPT_API int rpt_bf_set_prefilter(rpt_bf_t *bf, int mode);
+RPT_API int rpt_bf_prefilter_info(const rpt_bf_t *bf, int *state_out, double *pass_rate_out);
 /* Allocation-free probe.  NO COUNTERPART IN THE REFERENCE: added for callers
  * that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
  * Same result as rpt_bf_probe with one non-NULL 64-bit integer key column in device memory and device outputs

@@ -128,6 +128,33 @@ partpipe)   # chunk-pipelined partitioned probe (code as of commit 0fbcbed, remo
 	done
 	cat $out
 	;;
+prefilter)  # folded pre-filter: its tests, then on/off sweeps at config 2 (1 %, 10 %, 50 %) and at 512 MiB: prefilter <tag>
+	tag=${1:-r2p}
+	timeout 1200 python -m pytest tests/test_gpu_prefilter.py -x -q > gpurun_out/tests_prefilter_${tag}.log 2>&1
+	echo "prefilter tests rc=$?" | tee -a gpurun_out/tests_prefilter_${tag}.log
+	tail -25 gpurun_out/tests_prefilter_${tag}.log
+	out=gpurun_out/prefilter_${tag}.txt
+	: > $out
+	for knobs in "" "RPT_PREFILTER=0"; do
+		for ppm in 100000 10000 500000; do
+			echo "== knobs: ${knobs:-default} ppm=$ppm" >> $out
+			env $knobs SWEEP_PPM=$ppm timeout -s KILL 300 python tools/probe_sweep.py 1e9 5 1e8 >> $out 2>&1
+			echo "rc=$?" >> $out
+		done
+	done
+	for knobs in "" "RPT_PREFILTER=0" "RPT_PREFILTER=2"; do
+		echo "== knobs: ${knobs:-default} 512 MiB" >> $out
+		env $knobs timeout -s KILL 300 python tools/probe_sweep.py 1e9 3 1.8e8,3e8 >> $out 2>&1
+		echo "rc=$?" >> $out
+	done
+	grep -v "^rc=0" $out
+	cmd="python tools/probe_sweep.py 1e9 1 1e8"
+	timeout 900 ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum --clock-control none -c 200 \
+		--csv --log-file gpurun_out/launches_prefilter_${tag}.csv $cmd > gpurun_out/ncu_prefilter_${tag}.log 2>&1
+	echo "ncu rc=$?"
+	python tools/launch_summary.py gpurun_out/launches_prefilter_${tag}.csv > gpurun_out/launches_prefilter_${tag}.md 2>&1
+	head -30 gpurun_out/launches_prefilter_${tag}.md
+	;;
 tests)      # the GPU parity suite
 	timeout 2400 python -m pytest tests -m gpu -x -q > gpurun_out/tests_${1:-r2}.log 2>&1
 	echo "tests rc=$?" >> gpurun_out/tests_${1:-r2}.log

@@ -44,7 +44,7 @@ dev = torch.device("cuda", 0)
 stream = torch.cuda.Stream(device=dev)
 torch.cuda.set_stream(stream)
 sh = stream.cuda_stream
-knobs = {k: os.environ[k] for k in ("RPT_PROBE_UNITS", "RPT_SLICE_MIB", "RPT_GPU_LIB", "RPT_PROBE_PARTITION", "RPT_PART_MINB", "RPT_PART_STORE", "RPT_L2_PERSIST_MIB") if k in os.environ}
+knobs = {k: os.environ[k] for k in ("RPT_PROBE_UNITS", "RPT_SLICE_MIB", "RPT_GPU_LIB", "RPT_PROBE_PARTITION", "RPT_PART_MINB", "RPT_PART_STORE", "RPT_L2_PERSIST_MIB", "RPT_PREFILTER", "RPT_PRE_INLINE0", "RPT_PREFILTER_MAX_PASS") if k in os.environ}
 print(f"# m={m} reps={reps} ppm={ppm} type={ktype} knobs={knobs}", flush=True)
 dp = torch.empty(m, dtype=torch.int64, device=dev)
 dsel = torch.empty(m, dtype=torch.int32, device=dev)
@@ -89,7 +89,19 @@ for n in cases:
     algo = (4 if ktype == "int32" else 8) * m + 4 * found + F
     if ktype == "varchar":
         algo = 4 * (m + 1) + pt + 4 * found + F  # offsets + string bytes replace 8·m
+    # whole steps (reset + build + probe): what bench.py times; includes the fold of a pre-filtered probe
+    ev2 = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+    ev2[0].record(stream)
+    for _ in range(reps):
+        bf.Reset(n, sh)
+        bf.Insert(kc, n, sh)
+        bf.LookupSelDevice(pc, m, dsel, dfound, sh)
+    ev2[1].record(stream)
+    torch.cuda.synchronize()
+    sm = ev2[0].elapsed_time(ev2[1]) / reps
+    pre = bf.PrefilterInfo()
     print(f"n={n:>10} F={F / 2**20:8.3f} MiB  build {bm:7.3f} ms {n / bm / 1e6:7.1f} Gkeys/s | probe {pm:7.3f} ms "
-          f"{m / pm / 1e6:7.1f} Gkeys/s  {algo / pm / 1e6:7.1f} GB/s algorithmic  found {found}", flush=True)
+          f"{m / pm / 1e6:7.1f} Gkeys/s  {algo / pm / 1e6:7.1f} GB/s algorithmic  found {found} | step {sm:7.3f} ms "
+          f"prefilter state {pre[0]} pass {pre[1]:.4f}", flush=True)
     bf.close()
     del dk
