@@ -406,8 +406,12 @@ def run_b200(args):
     peak, peak_src = load_peaks()
     algo_bytes = 8 * m + 4 * found + F
     achieved = algo_bytes / (probe_ms * 1e-3) / 1e9
-    roofline = {"kernel": "rpt_bf_probe = probe_partition_kernel<FlatU64SrcT<0>,256,4> + 3 x probe_bucket_kernel<168> + "
-                          "count_segments/scan_blocks/scan_totals + compact_bitmap_kernel", "bound": "hbm", "achieved": achieved, "peak": peak,
+    pre_state, pre_pass = sb.bf.PrefilterInfo()
+    kernels = ("rpt_bf_probe = fold_kernel (once per build) + probe_fold_kernel<FlatU64SrcT<0>,24,4> + 4 x probe_bucket_half_kernel<4> + "
+               "count_segments/scan_blocks/scan_totals + compact_bitmap_kernel" if pre_state == 1 else
+               "rpt_bf_probe = probe_partition_kernel<FlatU64SrcT<0>,256,4> + 3 x probe_bucket_kernel<168> + "
+               "count_segments/scan_blocks/scan_totals + compact_bitmap_kernel")
+    roofline = {"kernel": kernels, "bound": "hbm", "achieved": achieved, "peak": peak,
                 "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": algo_bytes, "launch_ms": probe_ms,
                 "bytes_per_key": algo_bytes / m,
@@ -420,6 +424,8 @@ def run_b200(args):
         try:
             with open(traffic_path) as f:
                 tr = json.load(f)
+            if pre_state != 1 and "without_prefilter" in tr:
+                tr = tr["without_prefilter"]
             roofline["traffic"] = tr.get("dram_bytes_per_launch")
             roofline["traffic_source"] = tr.get("source")
         except Exception:
@@ -428,7 +434,10 @@ def run_b200(args):
     detail = {"build_ms": build_ms_max, "merge_ms": merge_ms_max, "probe_ms": probe_ms_max,
               "build_gkeys_s": n / (build_ms_max * 1e-3) / 1e9,
               "probe_gkeys_s": world * m / (probe_ms_max * 1e-3) / 1e9,
-              "found_rank0": found, "filter_sectors": S, "filter_mib": F >> 20, "parity": parity}
+              "found_rank0": found, "filter_sectors": S, "filter_mib": F >> 20, "parity": parity,
+              "prefilter": {"state": pre_state, "estimated_pass_rate_of_non_members": pre_pass,
+                            "note": "folded pre-filter of the probe (rpt_gpu.h rpt_bf_set_prefilter): 1 = in use, "
+                                    "0 = none, 2 = made but too dense"}}
 
     # ---- sustained figure: the timed region above is a fraction of a second (burst clocks); the same K steps after
     # --sustain-s seconds of back-to-back untimed steps run in the power/clock state of a long job ----

@@ -1053,6 +1053,14 @@ static int prefilter_mode() {
 	}();
 	return mode;
 }
+// size of the folded filter: one L2-resident slice (64 MiB); RPT_FOLD_MIB=32 folds twice as far (experiments)
+static uint64_t fold_sectors() {
+	static const uint64_t v = [] {
+		const char *e = getenv("RPT_FOLD_MIB");
+		return e && atoi(e) == 32 ? kSliceSectors / 2 : kSliceSectors;
+	}();
+	return v;
+}
 static double prefilter_max_pass() {
 	static const double v = [] {
 		const char *e = getenv("RPT_PREFILTER_MAX_PASS");
@@ -1109,29 +1117,29 @@ static int ensure_prefilter(rpt_bf *bf, uint64_t count, cudaStream_t s, Prefilte
 			return 0; // a small probe does not pay for a fold (read S words, write 64 MiB)
 		}
 		if (!bf->folded) {
-			RPT_CUDA(cudaMalloc(&bf->folded, kSliceSectors * sizeof(uint64_t)));
+			RPT_CUDA(cudaMalloc(&bf->folded, kSliceSectors * sizeof(uint64_t))); // holds either fold size
 			RPT_CUDA(cudaMalloc(&bf->fold_pop_dev, sizeof(uint64_t)));
 			RPT_CUDA(cudaMallocHost(&bf->fold_pop_host, sizeof(uint64_t)));
 			RPT_CUDA(cudaMalloc(&bf->fold_stats_dev, 2 * sizeof(uint64_t)));
 			RPT_CUDA(cudaMallocHost(&bf->fold_stats_host, 2 * sizeof(uint64_t)));
 			RPT_CUDA(cudaEventCreateWithFlags(&bf->fold_stats_ev, cudaEventDisableTiming));
 		}
-		RPT_CUDA(launch_fold(bf->dev, bf->words, bf->num_sectors, bf->folded, kSliceSectors, bf->fold_pop_dev, s));
+		RPT_CUDA(launch_fold(bf->dev, bf->words, bf->num_sectors, bf->folded, fold_sectors(), bf->fold_pop_dev, s));
 		RPT_CUDA(cudaMemcpyAsync(bf->fold_pop_host, bf->fold_pop_dev, sizeof(uint64_t), cudaMemcpyDeviceToHost, s));
 		RPT_CUDA(cudaStreamSynchronize(s)); // the fold is complete before its version is published to other threads
 		(*launches)++;
-		const double d = static_cast<double>(*bf->fold_pop_host) / (64.0 * static_cast<double>(kSliceSectors));
+		const double d = static_cast<double>(*bf->fold_pop_host) / (64.0 * static_cast<double>(fold_sectors()));
 		// a key sets 4 bit positions, 3 distinct ones with probability ≈ 0.09 (two of its 6-bit fields collide)
 		bf->fold_pass = 0.91 * d * d * d * d + 0.09 * d * d * d;
 		bf->fold_version = version;
 		if (trace_on()) {
 			fprintf(stderr, "[rpt trace] fold: %llu -> %llu sectors, density %.4f, estimated pass rate %.4f\n",
-			        (unsigned long long)bf->num_sectors, (unsigned long long)kSliceSectors, d, bf->fold_pass);
+			        (unsigned long long)bf->num_sectors, (unsigned long long)fold_sectors(), d, bf->fold_pass);
 		}
 	}
 	if (bf->fold_pass <= max_pass || mode == 2) {
 		out->folded = bf->folded;
-		out->sectors = kSliceSectors;
+		out->sectors = fold_sectors();
 		out->stats = nullptr;
 		if (!bf->fold_stats_pending && count >= (1ULL << 22)) { // one measurement in flight at a time
 			RPT_CUDA(cudaMemsetAsync(bf->fold_stats_dev, 0, 2 * sizeof(uint64_t), s));
@@ -1148,6 +1156,34 @@ static int prefilter_measured(rpt_bf *bf, cudaStream_t s) {
 	std::lock_guard<std::mutex> lock(bf->fold_mu);
 	RPT_CUDA(cudaMemcpyAsync(bf->fold_stats_host, bf->fold_stats_dev, 2 * sizeof(uint64_t), cudaMemcpyDeviceToHost, s));
 	RPT_CUDA(cudaEventRecord(bf->fold_stats_ev, s));
+	return 0;
+}
+
+int rpt_bf_set_prefilter(rpt_bf_t *bf, int mode) {
+	if (!bf) {
+		return set_error("null filter handle");
+	}
+	if (mode < -1 || mode > 2) {
+		return set_error("prefilter mode must be -1 (default), 0 (off), 1 (by density) or 2 (always)");
+	}
+	std::lock_guard<std::mutex> lock(bf->fold_mu);
+	bf->fold_mode.store(mode);
+	bf->fold_alive = -1.0; // forget the feedback of the probes so far
+	bf->fold_holdoff = 0;
+	return 0;
+}
+
+int rpt_bf_prefilter_info(const rpt_bf_t *bf, int *state_out, double *pass_rate_out) {
+	if (!bf || !state_out || !pass_rate_out) {
+		return set_error("null argument");
+	}
+	rpt_bf *m = const_cast<rpt_bf *>(bf);
+	std::lock_guard<std::mutex> lock(m->fold_mu);
+	const bool made = m->fold_version == m->content_version.load();
+	const int own = m->fold_mode.load();
+	const int mode = own >= 0 ? own : prefilter_mode();
+	*state_out = !made ? 0 : ((m->fold_pass <= prefilter_max_pass() || mode == 2) && mode != 0 ? 1 : 2);
+	*pass_rate_out = made ? m->fold_pass : 1.0;
 	return 0;
 }
 

@@ -1555,6 +1555,450 @@ __global__ void __launch_bounds__(256)
 	}
 }
 
+// ---- pre-filtered probe of flat key columns (regime 3c): fold → survivors → per-slice lookups --------------------
+// probe_fold_kernel   the staging of probe_smem_kernel (bulk copies of HALF segments, one mbarrier per buffer, 4 KiB
+//                     per warp) with the lookup going to the L2-resident FOLDED filter instead of shared memory.  A
+//                     lane owns 8 keys of a half; the keys that survive the folded filter (members + its false
+//                     positives, ≈ 17 % at config 2) become 8-byte records {sector-in-slice : 23 | row-in-half : 8,
+//                     hash bits 63..32}, counting-sorted by slice inside the warp (8-bit per-lane counts, one warp scan
+//                     on 16-bit fields) into the half buffer just consumed, PACKED slice after slice, and copied out to
+//                     the half's 256-record region; ends[half·P + s] = end of slice s's records inside the region.
+//                     No region can overflow (a half has 256 keys), so there is no fallback path.
+// probe_bucket_half_kernel  once per slice: the slice's records of four halves at a time → real filter word → test →
+//                     RED.OR into the row-ordered bitmap (which probe_fold_kernel zeroed).
+// ncu of the first pre-filtered version (the 512-row partition kernel with a folded test in front, still used for
+// generic sources): 72 instructions per key, 15 warps per SM, issue 36 % — latency-bound.  This one: 8 keys per lane
+// and no 16-hash register block, so 24+ warps per SM fit.
+template <int P>
+struct FoldCfg {
+	static constexpr int NCNT = P <= 4 ? 1 : 2; // per-lane counters: 8 bits per slice, four slices per register
+};
+
+template <class Src, int NWARPS, int P>
+__global__ void __launch_bounds__(NWARPS * 32, 1)
+    probe_fold_kernel(const Src src, const uint64_t *__restrict__ folded, const uint32_t fold_mask,
+                      const uint32_t sector_mask, const uint64_t count, const uint64_t num_segs,
+                      uint8_t *__restrict__ bitmap8, uint2 *__restrict__ records /* 256 per half */,
+                      uint16_t *__restrict__ ends /* P per half */, unsigned long long *__restrict__ pre_stats) {
+	static_assert(Src::kStageable, "flat key columns only");
+	constexpr int KB = Src::kKeyBytes;
+	constexpr int KPU = 16 / KB;                    // keys per 16-byte unit
+	constexpr uint32_t HALF_BYTES = kHalfRows * KB; // 2048 / 1024
+	constexpr int LU = 8 / KPU;                     // 16-byte units a lane owns per half: 4 / 2
+	constexpr uint32_t STAGE_BYTES = kHalfRows * 8; // up to 256 records
+	constexpr bool ALIAS = HALF_BYTES >= STAGE_BYTES; // the records overwrite the keys they came from
+	constexpr uint32_t WARP_BYTES = 2 * HALF_BYTES + (ALIAS ? 0 : STAGE_BYTES);
+	constexpr int NCNT = FoldCfg<P>::NCNT;
+	constexpr uint32_t SHIFT = kSliceShift;
+	extern __shared__ __align__(128) unsigned char s_dyn[];
+	__shared__ __align__(8) uint64_t s_bars[NWARPS][2];
+	const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+	unsigned char *const kbuf = s_dyn + warp * WARP_BYTES;
+	const uint64_t pol_keys = policy_evict_first();
+	const uint64_t pol_filter = policy_evict_last();
+	if (lane == 0) {
+		mbar_init(&s_bars[warp][0], 1);
+		mbar_init(&s_bars[warp][1], 1);
+	}
+	asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+	__syncthreads();
+	warm_slice(folded, 0u, fold_mask + 1u, NWARPS * 32);
+	const uint64_t full_segs = count / kSegRows;
+	const uint64_t stride = static_cast<uint64_t>(gridDim.x) * NWARPS;
+	const unsigned char *const keys = reinterpret_cast<const unsigned char *>(src.key_ptr());
+	auto issue = [&](uint64_t seg, uint32_t h) { // elected lane: stage half h of segment seg
+		if (seg < full_segs) {
+			mbar_expect_tx(&s_bars[warp][h], HALF_BYTES);
+			bulk_g2s(kbuf + h * HALF_BYTES, keys + (seg * kSegRows + h * kHalfRows) * KB, HALF_BYTES, &s_bars[warp][h],
+			         pol_keys);
+		}
+	};
+	const uint64_t seg0 = static_cast<uint64_t>(blockIdx.x) * NWARPS + warp;
+	if (lane == 0) {
+		issue(seg0, 0);
+		issue(seg0, 1);
+	}
+	const uint32_t rot = LU == 4 ? ((lane >> 1) & 3u) : ((lane >> 2) & 1u);
+	uint32_t phase = 0;
+	uint32_t seen_rows = 0, seen_alive = 0;
+	for (uint64_t seg = seg0; seg < num_segs; seg += stride) {
+#pragma unroll
+		for (uint32_t h = 0; h < 2; h++) {
+			const bool staged = seg < full_segs;
+			uint64_t hh[8];
+			uint32_t valid = 0xffu; // slot order
+			if (staged) {
+				mbar_wait(&s_bars[warp][h], (phase >> h) & 1u);
+				phase ^= 1u << h;
+				const uint4 *mine = reinterpret_cast<const uint4 *>(kbuf + h * HALF_BYTES) + lane * LU;
+#pragma unroll
+				for (int u = 0; u < LU; u++) {
+					Src::hash_unit(mine[(u + rot) & (LU - 1)], hh + u * KPU);
+				}
+				if (Src::kNullable) {
+					const uint32_t v = __ldg(reinterpret_cast<const unsigned char *>(src.validity) + seg * 64 + h * 32 + lane);
+					const uint32_t twice = v | (v << 8); // slot i holds logical bit (i + KPU·rot) mod 8: rotate right
+					null_fix<8>(hh, (twice >> (KPU * rot)) & 0xffu, 0);
+				}
+			} else { // the partial last segment: straight from global memory, slots in row order
+				const uint64_t row0 = seg * kSegRows + h * kHalfRows + lane * 8u;
+				valid = 0;
+#pragma unroll
+				for (int i = 0; i < 8; i++) {
+					hh[i] = 0;
+					if (row0 + i < count) {
+						hh[i] = src.hash_at(row0 + i, pol_keys);
+						valid |= 1u << i;
+					}
+				}
+			}
+			const uint32_t alive = test_batch<8, false, false>(hh, folded, nullptr, fold_mask, pol_filter, 0u, 0u) & valid;
+			seen_rows += __popc(valid);
+			seen_alive += __popc(alive);
+			const uint64_t half = seg * 2 + h;
+			bitmap8[half * 32 + lane] = 0; // the bucket kernels OR the hits in
+			if (ALIAS && staged) {
+				__syncwarp(); // every lane has its keys in registers: the buffer becomes the record stage
+			}
+			uint2 *const stage = reinterpret_cast<uint2 *>(kbuf + (ALIAS ? h * HALF_BYTES : 2 * HALF_BYTES));
+			// per-lane counts of the survivors of every slice (8-bit fields)
+			uint32_t cnt[NCNT];
+#pragma unroll
+			for (int j = 0; j < NCNT; j++) {
+				cnt[j] = 0;
+			}
+#pragma unroll
+			for (int i = 0; i < 8; i++) {
+				const uint32_t sector = static_cast<uint32_t>(hh[i]) & sector_mask;
+				const uint32_t sh = (sector >> (SHIFT - 3)) & ((P - 1u) << 3); // 8 · slice
+				const uint32_t one = (alive >> i) & 1u;
+				if (NCNT == 1) {
+					cnt[0] += one << sh;
+				} else {
+					cnt[0] += shl_clamp(one, sh);
+					cnt[1] += shl_clamp(one, sh ^ 32u);
+				}
+			}
+			// warp scan on 16-bit fields; base[j] = exclusive prefixes of slices 4j..4j+3 as one 64-bit word
+			uint64_t base[NCNT];
+			uint32_t tot[NCNT][2];
+#pragma unroll
+			for (int j = 0; j < NCNT; j++) {
+				const uint32_t own0 = cnt[j] & 0x00ff00ffu, own1 = (cnt[j] >> 8) & 0x00ff00ffu;
+				uint32_t e0 = own0, e1 = own1;
+#pragma unroll
+				for (int d = 1; d < 32; d <<= 1) {
+					const uint32_t t0 = __shfl_up_sync(0xffffffffu, e0, d);
+					const uint32_t t1 = __shfl_up_sync(0xffffffffu, e1, d);
+					e0 += lane >= static_cast<uint32_t>(d) ? t0 : 0u;
+					e1 += lane >= static_cast<uint32_t>(d) ? t1 : 0u;
+				}
+				tot[j][0] = __shfl_sync(0xffffffffu, e0, 31);
+				tot[j][1] = __shfl_sync(0xffffffffu, e1, 31);
+				e0 -= own0;
+				e1 -= own1;
+				base[j] = (static_cast<uint64_t>((e0 >> 16) | (e1 & 0xffff0000u)) << 32) | ((e0 & 0xffffu) | (e1 << 16));
+				cnt[j] = 0; // reused below as the lane's running per-slice rank
+			}
+			auto slice_total = [&](int s) -> uint32_t {
+				const uint32_t t = tot[s >> 2][s & 1];
+				return (s & 2) ? t >> 16 : t & 0xffffu;
+			};
+			// the slices' records are packed one behind the other: slice s starts where slice s-1 ends (warp-uniform)
+			uint32_t run = 0;
+			uint64_t endw[NCNT];
+#pragma unroll
+			for (int j = 0; j < NCNT; j++) {
+				uint64_t add = 0;
+				endw[j] = 0;
+#pragma unroll
+				for (int k = 0; k < 4 && 4 * j + k < P; k++) {
+					add |= static_cast<uint64_t>(run) << (16 * k);
+					run += slice_total(4 * j + k);
+					endw[j] |= static_cast<uint64_t>(run) << (16 * k);
+				}
+				base[j] += add; // no carries: prefix + start ≤ 256
+			}
+			if (lane == 0) {
+				uint64_t *e = reinterpret_cast<uint64_t *>(ends + half * P); // P = 4 or 8: 8-byte aligned
+#pragma unroll
+				for (int j = 0; j < NCNT; j++) {
+					e[j] = endw[j];
+				}
+			}
+			const uint32_t unit_rot = staged ? rot : 0u;
+#pragma unroll
+			for (int i = 0; i < 8; i++) {
+				const uint32_t sector = static_cast<uint32_t>(hh[i]) & sector_mask;
+				const uint32_t sh = (sector >> (SHIFT - 3)) & ((P - 1u) << 3);
+				const uint32_t shr = sh & 31u;
+				const uint32_t one = (alive >> i) & 1u;
+				uint32_t rank, pos;
+				if (NCNT == 1) {
+					rank = (cnt[0] >> shr) & 0xffu;
+					cnt[0] += one << shr;
+					pos = static_cast<uint32_t>(base[0] >> (2u * shr)) & 0xffffu;
+				} else {
+					const bool up = sh >= 32u;
+					rank = ((up ? cnt[1] : cnt[0]) >> shr) & 0xffu;
+					cnt[0] += up ? 0u : one << shr;
+					cnt[1] += up ? one << shr : 0u;
+					pos = static_cast<uint32_t>((up ? base[1] : base[0]) >> (2u * shr)) & 0xffffu;
+				}
+				if (one) {
+					const uint32_t row8 = lane * 8u + (((i / KPU + unit_rot) & (LU - 1)) * KPU) + (i % KPU);
+					stage[pos + rank] =
+					    make_uint2((sector & ((1u << SHIFT) - 1u)) | (row8 << SHIFT), static_cast<uint32_t>(hh[i] >> 32));
+				}
+			}
+			__syncwarp();
+			{
+				uint2 *dv = records + half * kHalfRows;
+				for (uint32_t j = lane; j < run; j += 32u) {
+					st_stream_v2(dv + j, stage[j], pol_keys);
+				}
+			}
+			__syncwarp(); // the stage has been read: the buffer may be refilled (aliased) / rewritten by the next half
+			if (staged && lane == 0) {
+				issue(seg + stride, h);
+			}
+		}
+	}
+	if (pre_stats != nullptr) {
+		seen_rows = __reduce_add_sync(0xffffffffu, seen_rows);
+		seen_alive = __reduce_add_sync(0xffffffffu, seen_alive);
+		if (lane == 0) {
+			atomicAdd(pre_stats, static_cast<unsigned long long>(seen_rows));
+			atomicAdd(pre_stats + 1, static_cast<unsigned long long>(seen_alive));
+		}
+	}
+}
+
+// probe_fold_direct_kernel: the same step with NO shared memory at all.  What bounds the folded-filter gathers is the
+// number of them an SM keeps in flight, and that number follows the L1's size: every outstanding line holds an L1
+// line (measured: 217 KiB of shared memory per SM → 16.5 ms per 10^9 keys, 128 KiB → 5.4 ms, 96 KiB → 4.7 ms —
+// each time ≈ (L1 lines) / latency).  So the keys come straight into registers (lane l owns rows l, l+32, …, l+224
+// of a half: eight coalesced loads, all in flight before the first hash) and the survivors' records leave as
+// 8-byte stores at their sorted positions (the L2 merges a region's stores).  Any key source.
+template <class Src, int P, int MINB>
+__global__ void __launch_bounds__(256, MINB)
+    probe_fold_direct_kernel(const Src src, const uint64_t *__restrict__ folded, const uint32_t fold_mask,
+                             const uint32_t sector_mask, const uint64_t count, const uint64_t num_halves,
+                             uint32_t *__restrict__ bitmap32, uint2 *__restrict__ records /* 256 per half */,
+                             uint16_t *__restrict__ ends /* P per half */, unsigned long long *__restrict__ pre_stats) {
+	constexpr int NCNT = FoldCfg<P>::NCNT;
+	constexpr uint32_t SHIFT = kSliceShift;
+	const uint32_t lane = threadIdx.x & 31u;
+	const uint64_t pol_keys = policy_evict_first();
+	const uint64_t pol_filter = policy_evict_last();
+	warm_slice(folded, 0u, fold_mask + 1u, 256);
+	const uint64_t warp_global = (static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
+	const uint64_t num_warps = (static_cast<uint64_t>(gridDim.x) * blockDim.x) >> 5;
+	uint32_t seen_rows = 0, seen_alive = 0;
+	for (uint64_t half = warp_global; half < num_halves; half += num_warps) {
+		const uint64_t row0 = half * kHalfRows + lane;
+		uint64_t hh[8];
+		uint32_t valid = 0xffu;
+		if ((half + 1) * kHalfRows <= count) { // warp-uniform
+#pragma unroll
+			for (int i = 0; i < 8; i++) {
+				hh[i] = src.hash_at(row0 + 32u * i, pol_keys);
+			}
+		} else {
+			valid = 0;
+#pragma unroll
+			for (int i = 0; i < 8; i++) {
+				hh[i] = 0;
+				if (row0 + 32u * i < count) {
+					hh[i] = src.hash_at(row0 + 32u * i, pol_keys);
+					valid |= 1u << i;
+				}
+			}
+		}
+		const uint32_t alive = test_batch<8, false, false>(hh, folded, nullptr, fold_mask, pol_filter, 0u, 0u) & valid;
+		seen_rows += __popc(valid);
+		seen_alive += __popc(alive);
+		if (lane < 8) {
+			bitmap32[half * 8 + lane] = 0; // the bucket kernels OR the hits in
+		}
+		uint32_t cnt[NCNT];
+#pragma unroll
+		for (int j = 0; j < NCNT; j++) {
+			cnt[j] = 0;
+		}
+#pragma unroll
+		for (int i = 0; i < 8; i++) {
+			const uint32_t sector = static_cast<uint32_t>(hh[i]) & sector_mask;
+			const uint32_t sh = (sector >> (SHIFT - 3)) & ((P - 1u) << 3); // 8 · slice
+			const uint32_t one = (alive >> i) & 1u;
+			if (NCNT == 1) {
+				cnt[0] += one << sh;
+			} else {
+				cnt[0] += shl_clamp(one, sh);
+				cnt[1] += shl_clamp(one, sh ^ 32u);
+			}
+		}
+		uint64_t base[NCNT];
+		uint32_t tot[NCNT][2];
+#pragma unroll
+		for (int j = 0; j < NCNT; j++) {
+			const uint32_t own0 = cnt[j] & 0x00ff00ffu, own1 = (cnt[j] >> 8) & 0x00ff00ffu;
+			uint32_t e0 = own0, e1 = own1;
+#pragma unroll
+			for (int d = 1; d < 32; d <<= 1) {
+				const uint32_t t0 = __shfl_up_sync(0xffffffffu, e0, d);
+				const uint32_t t1 = __shfl_up_sync(0xffffffffu, e1, d);
+				e0 += lane >= static_cast<uint32_t>(d) ? t0 : 0u;
+				e1 += lane >= static_cast<uint32_t>(d) ? t1 : 0u;
+			}
+			tot[j][0] = __shfl_sync(0xffffffffu, e0, 31);
+			tot[j][1] = __shfl_sync(0xffffffffu, e1, 31);
+			e0 -= own0;
+			e1 -= own1;
+			base[j] = (static_cast<uint64_t>((e0 >> 16) | (e1 & 0xffff0000u)) << 32) | ((e0 & 0xffffu) | (e1 << 16));
+			cnt[j] = 0;
+		}
+		auto slice_total = [&](int s) -> uint32_t {
+			const uint32_t t = tot[s >> 2][s & 1];
+			return (s & 2) ? t >> 16 : t & 0xffffu;
+		};
+		uint32_t run = 0;
+		uint64_t endw[NCNT];
+#pragma unroll
+		for (int j = 0; j < NCNT; j++) {
+			uint64_t add = 0;
+			endw[j] = 0;
+#pragma unroll
+			for (int k = 0; k < 4 && 4 * j + k < P; k++) {
+				add |= static_cast<uint64_t>(run) << (16 * k);
+				run += slice_total(4 * j + k);
+				endw[j] |= static_cast<uint64_t>(run) << (16 * k);
+			}
+			base[j] += add;
+		}
+		if (lane == 0) {
+			uint64_t *e = reinterpret_cast<uint64_t *>(ends + half * P);
+#pragma unroll
+			for (int j = 0; j < NCNT; j++) {
+				e[j] = endw[j];
+			}
+		}
+		uint2 *const region = records + half * kHalfRows;
+#pragma unroll
+		for (int i = 0; i < 8; i++) {
+			const uint32_t sector = static_cast<uint32_t>(hh[i]) & sector_mask;
+			const uint32_t sh = (sector >> (SHIFT - 3)) & ((P - 1u) << 3);
+			const uint32_t shr = sh & 31u;
+			const uint32_t one = (alive >> i) & 1u;
+			uint32_t rank, pos;
+			if (NCNT == 1) {
+				rank = (cnt[0] >> shr) & 0xffu;
+				cnt[0] += one << shr;
+				pos = static_cast<uint32_t>(base[0] >> (2u * shr)) & 0xffffu;
+			} else {
+				const bool up = sh >= 32u;
+				rank = ((up ? cnt[1] : cnt[0]) >> shr) & 0xffu;
+				cnt[0] += up ? 0u : one << shr;
+				cnt[1] += up ? one << shr : 0u;
+				pos = static_cast<uint32_t>((up ? base[1] : base[0]) >> (2u * shr)) & 0xffffu;
+			}
+			if (one) {
+				const uint32_t row8 = lane + 32u * i;
+				st_stream_v2(region + pos + rank,
+				             make_uint2((sector & ((1u << SHIFT) - 1u)) | (row8 << SHIFT), static_cast<uint32_t>(hh[i] >> 32)),
+				             pol_keys);
+			}
+		}
+	}
+	if (pre_stats != nullptr) {
+		seen_rows = __reduce_add_sync(0xffffffffu, seen_rows);
+		seen_alive = __reduce_add_sync(0xffffffffu, seen_alive);
+		if (lane == 0) {
+			atomicAdd(pre_stats, static_cast<unsigned long long>(seen_rows));
+			atomicAdd(pre_stats + 1, static_cast<unsigned long long>(seen_alive));
+		}
+	}
+}
+
+// One slice's survivors.  A slice's share of a half is a dozen records, and the kernel is nothing but a chain of
+// three dependent loads (bounds → records → filter words), so a warp step covers SIXTEEN halves: eight lanes per half,
+// four halves per round, four rounds, up to 24 records of each half in flight (K = 3); a half with more records of
+// the slice (rich in members) loops.  Earlier versions, one half per 32 lanes and four halves per step: 0.56 ms per
+// slice at 32 warps per SM, 0.46 ms at 64 (profiles/prefilter_r2r.txt, prefilter_r2s.txt) — latency-bound.
+template <int P>
+__global__ void __launch_bounds__(256, 3)
+    probe_bucket_half_kernel(const uint2 *__restrict__ records, const uint16_t *__restrict__ ends, const uint64_t num_halves,
+                             const uint64_t *__restrict__ filter, const uint32_t s /* slice */,
+                             uint32_t *__restrict__ bitmap32) {
+	constexpr int T = 4, K = 3;
+	constexpr uint32_t SHIFT = kSliceShift;
+	const uint32_t lane = threadIdx.x & 31u;
+	const uint32_t group = lane >> 3, q = lane & 7u;
+	const uint64_t pol_rec = policy_evict_first();
+	const uint64_t pol_filter = policy_evict_last();
+	warm_slice(filter, s << SHIFT, 1u << SHIFT, 256);
+	const uint64_t *const slice = filter + (static_cast<uint64_t>(s) << SHIFT);
+	const uint64_t warp_global = (static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
+	const uint64_t num_warps = (static_cast<uint64_t>(gridDim.x) * blockDim.x) >> 5;
+	auto apply = [&](uint64_t half, uint64_t v, uint64_t word) {
+		const uint32_t x = static_cast<uint32_t>(v);
+		if (sector_test_fma(word, static_cast<uint32_t>(v >> 32))) { // an all-zero word (no record) passes nothing
+			const uint32_t row8 = x >> SHIFT;
+			atomicOr(bitmap32 + half * 8 + (row8 >> 5), 1u << (row8 & 31u));
+		}
+	};
+	for (uint64_t h0 = warp_global * (4 * T); h0 < num_halves; h0 += num_warps * (4 * T)) {
+		uint32_t lo[T], hi[T];
+#pragma unroll
+		for (int t = 0; t < T; t++) {
+			const uint64_t half = h0 + t * 4 + group;
+			lo[t] = hi[t] = 0;
+			if (half < num_halves) {
+				hi[t] = __ldg(ends + half * P + s);
+				lo[t] = s ? __ldg(ends + half * P + s - 1) : 0u;
+			}
+		}
+		uint64_t rec[T][K];
+#pragma unroll
+		for (int t = 0; t < T; t++) {
+#pragma unroll
+			for (int k = 0; k < K; k++) {
+				const uint32_t j = lo[t] + q + 8u * k;
+				rec[t][k] = 0;
+				if (j < hi[t]) {
+					rec[t][k] = ld_stream_u64(records + (h0 + t * 4 + group) * kHalfRows + j, pol_rec);
+				}
+			}
+		}
+		uint64_t w[T][K];
+#pragma unroll
+		for (int t = 0; t < T; t++) {
+#pragma unroll
+			for (int k = 0; k < K; k++) {
+				w[t][k] = 0;
+				if (lo[t] + q + 8u * k < hi[t]) {
+					w[t][k] = ld_filter_word(slice + (static_cast<uint32_t>(rec[t][k]) & ((1u << SHIFT) - 1u)), pol_filter);
+				}
+			}
+		}
+#pragma unroll
+		for (int t = 0; t < T; t++) {
+#pragma unroll
+			for (int k = 0; k < K; k++) {
+				apply(h0 + t * 4 + group, rec[t][k], w[t][k]);
+			}
+		}
+#pragma unroll
+		for (int t = 0; t < T; t++) {
+			for (uint32_t j = lo[t] + q + 8u * K; j < hi[t]; j += 8u) { // halves rich in members
+				const uint64_t half = h0 + t * 4 + group;
+				const uint64_t v = ld_stream_u64(records + half * kHalfRows + j, pol_rec);
+				apply(half, v, ld_filter_word(slice + (static_cast<uint32_t>(v) & ((1u << SHIFT) - 1u)), pol_filter));
+			}
+		}
+	}
+}
+
 // seg_counts[seg] = number of set bits among the segment's 512 bitmap bits
 __global__ void __launch_bounds__(256)
     count_segments_kernel(const uint4 *__restrict__ bitmap128, const uint64_t num_segs, uint32_t *__restrict__ seg_counts) {
@@ -2478,6 +2922,153 @@ static cudaError_t launch_probe_partitioned(const DeviceInfo &dev, const Src &sr
 	return cudaGetLastError();
 }
 
+// Pre-filtered probe of a flat key column (probe_fold_kernel + one probe_bucket_half_kernel per slice).
+// Scratch behind the phased layout: [ends u16 × P × halves][records 8 B × 256 × halves] — inside what
+// partition_scratch_bytes(prefilter) reserves for the generic pre-filtered partition.
+template <class Src, int P, int NW>
+static cudaError_t launch_probe_folded_nw(const DeviceInfo &dev, const Src &src, uint64_t count, const uint64_t *words,
+                                          uint64_t num_sectors, uint32_t *sel_out, uint64_t *found_out,
+                                          uint32_t row_offset, const uint32_t *translate, void *scratch,
+                                          cudaStream_t stream, int *launches) {
+	constexpr int KB = Src::kKeyBytes;
+	constexpr uint32_t HALF_BYTES = kHalfRows * KB;
+	constexpr uint32_t WARP_BYTES = 2 * HALF_BYTES + (HALF_BYTES >= kHalfRows * 8 ? 0 : kHalfRows * 8);
+	auto kern = probe_fold_kernel<Src, NW, P>;
+	const size_t smem = static_cast<size_t>(NW) * WARP_BYTES;
+	cudaError_t e = ensure_max_dyn_smem<probe_fold_kernel<Src, NW, P>>(dev);
+	if (e != cudaSuccess) {
+		return e;
+	}
+	int per_sm = 0;
+	e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, NW * 32, smem);
+	if (e != cudaSuccess) {
+		return e;
+	}
+	if (per_sm < 1) {
+		return cudaErrorLaunchOutOfResources;
+	}
+	const uint64_t num_segs = ceil_div(count, kSegRows);
+	const uint64_t num_halves = num_segs * 2;
+	uint64_t grid = static_cast<uint64_t>(dev.sm_count) * per_sm;
+	const uint64_t want = ceil_div(num_segs, NW);
+	grid = grid < want ? grid : want;
+	const PhasedLayout lay = phased_layout(count);
+	char *base = reinterpret_cast<char *>(scratch);
+	uint32_t *seg_offsets = reinterpret_cast<uint32_t *>(base);
+	uint32_t *block_totals = reinterpret_cast<uint32_t *>(base + lay.off_totals);
+	uint8_t *bitmap = reinterpret_cast<uint8_t *>(base + lay.off_hitbits);
+	char *extra = base + align_up(lay.bytes, 256);
+	uint16_t *ends = reinterpret_cast<uint16_t *>(extra);
+	uint2 *records = reinterpret_cast<uint2 *>(extra + align_up(num_halves * P * sizeof(uint16_t), 256));
+	kern<<<static_cast<unsigned>(grid), NW * 32, smem, stream>>>(
+	    src, t_pre->folded, static_cast<uint32_t>(t_pre->sectors - 1), static_cast<uint32_t>(num_sectors - 1), count,
+	    num_segs, bitmap, records, ends, reinterpret_cast<unsigned long long *>(t_pre->stats));
+	auto bucket = probe_bucket_half_kernel<P>;
+	int bper_sm = 0;
+	e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bper_sm, bucket, 256, 0);
+	if (e != cudaSuccess) {
+		return e;
+	}
+	uint64_t bgrid = static_cast<uint64_t>(dev.sm_count) * (bper_sm > 0 ? bper_sm : 1);
+	const uint64_t bwant = ceil_div(num_halves, 128); // sixteen halves per warp step, eight warps per CTA
+	bgrid = bgrid < bwant ? bgrid : bwant;
+	for (int s = 0; s < P; s++) {
+		bucket<<<static_cast<unsigned>(bgrid), 256, 0, stream>>>(records, ends, num_halves, words, static_cast<uint32_t>(s),
+		                                                        reinterpret_cast<uint32_t *>(bitmap));
+	}
+	count_segments_kernel<<<stream_grid(dev, num_segs, 256), 256, 0, stream>>>(
+	    reinterpret_cast<const uint4 *>(bitmap), num_segs, seg_offsets);
+	const uint64_t nblocks = ceil_div(num_segs, kScanBlock);
+	scan_blocks_kernel<<<static_cast<unsigned>(nblocks), 1024, 0, stream>>>(seg_offsets, num_segs, block_totals);
+	scan_totals_kernel<<<1, 1024, 0, stream>>>(block_totals, static_cast<uint32_t>(nblocks), found_out);
+	const uint64_t cwant = ceil_div((num_segs + 1) / 2, 8ull);
+	const uint64_t ccap = static_cast<uint64_t>(dev.sm_count) * 6;
+	compact_bitmap_kernel<<<static_cast<unsigned>(cwant < ccap ? cwant : ccap), 256, 0, stream>>>(
+	    reinterpret_cast<const uint32_t *>(bitmap), seg_offsets, block_totals, num_segs, sel_out, row_offset, translate);
+	if (launches) {
+		(*launches) += 1 + P + 4;
+	}
+	return cudaGetLastError();
+}
+template <class Src, int P, int MINB>
+static cudaError_t launch_probe_folded_direct(const DeviceInfo &dev, const Src &src, uint64_t count,
+                                              const uint64_t *words, uint64_t num_sectors, uint32_t *sel_out,
+                                              uint64_t *found_out, uint32_t row_offset, const uint32_t *translate,
+                                              void *scratch, cudaStream_t stream, int *launches) {
+	auto kern = probe_fold_direct_kernel<Src, P, MINB>;
+	int per_sm = 0;
+	cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 256, 0);
+	if (e != cudaSuccess) {
+		return e;
+	}
+	if (per_sm < 1) {
+		return cudaErrorLaunchOutOfResources;
+	}
+	const uint64_t num_segs = ceil_div(count, kSegRows);
+	const uint64_t num_halves = num_segs * 2;
+	uint64_t grid = static_cast<uint64_t>(dev.sm_count) * per_sm;
+	const uint64_t want = ceil_div(num_halves, 8);
+	grid = grid < want ? grid : want;
+	const PhasedLayout lay = phased_layout(count);
+	char *base = reinterpret_cast<char *>(scratch);
+	uint32_t *seg_offsets = reinterpret_cast<uint32_t *>(base);
+	uint32_t *block_totals = reinterpret_cast<uint32_t *>(base + lay.off_totals);
+	uint8_t *bitmap = reinterpret_cast<uint8_t *>(base + lay.off_hitbits);
+	char *extra = base + align_up(lay.bytes, 256);
+	uint16_t *ends = reinterpret_cast<uint16_t *>(extra);
+	uint2 *records = reinterpret_cast<uint2 *>(extra + align_up(num_halves * P * sizeof(uint16_t), 256));
+	kern<<<static_cast<unsigned>(grid), 256, 0, stream>>>(
+	    src, t_pre->folded, static_cast<uint32_t>(t_pre->sectors - 1), static_cast<uint32_t>(num_sectors - 1), count,
+	    num_halves, reinterpret_cast<uint32_t *>(bitmap), records, ends,
+	    reinterpret_cast<unsigned long long *>(t_pre->stats));
+	auto bucket = probe_bucket_half_kernel<P>;
+	int bper_sm = 0;
+	e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bper_sm, bucket, 256, 0);
+	if (e != cudaSuccess) {
+		return e;
+	}
+	uint64_t bgrid = static_cast<uint64_t>(dev.sm_count) * (bper_sm > 0 ? bper_sm : 1);
+	const uint64_t bwant = ceil_div(num_halves, 128);
+	bgrid = bgrid < bwant ? bgrid : bwant;
+	for (int s = 0; s < P; s++) {
+		bucket<<<static_cast<unsigned>(bgrid), 256, 0, stream>>>(records, ends, num_halves, words, static_cast<uint32_t>(s),
+		                                                        reinterpret_cast<uint32_t *>(bitmap));
+	}
+	count_segments_kernel<<<stream_grid(dev, num_segs, 256), 256, 0, stream>>>(
+	    reinterpret_cast<const uint4 *>(bitmap), num_segs, seg_offsets);
+	const uint64_t nblocks = ceil_div(num_segs, kScanBlock);
+	scan_blocks_kernel<<<static_cast<unsigned>(nblocks), 1024, 0, stream>>>(seg_offsets, num_segs, block_totals);
+	scan_totals_kernel<<<1, 1024, 0, stream>>>(block_totals, static_cast<uint32_t>(nblocks), found_out);
+	const uint64_t cwant = ceil_div((num_segs + 1) / 2, 8ull);
+	const uint64_t ccap = static_cast<uint64_t>(dev.sm_count) * 6;
+	compact_bitmap_kernel<<<static_cast<unsigned>(cwant < ccap ? cwant : ccap), 256, 0, stream>>>(
+	    reinterpret_cast<const uint32_t *>(bitmap), seg_offsets, block_totals, num_segs, sel_out, row_offset, translate);
+	if (launches) {
+		(*launches) += 1 + P + 4;
+	}
+	return cudaGetLastError();
+}
+template <class Src, int P>
+static cudaError_t launch_probe_folded(const DeviceInfo &dev, const Src &src, uint64_t count, const uint64_t *words,
+                                       uint64_t num_sectors, uint32_t *sel_out, uint64_t *found_out, uint32_t row_offset,
+                                       const uint32_t *translate, void *scratch, cudaStream_t stream, int *launches) {
+	static const int nw = [] { // warps per CTA (one CTA per SM): RPT_FOLD_WARPS = 16 | 24 | 32
+		const char *e = getenv("RPT_FOLD_WARPS");
+		const int v = e ? atoi(e) : 24;
+		return v == 16 || v == 32 ? v : 24;
+	}();
+	if (nw == 16) {
+		return launch_probe_folded_nw<Src, P, 16>(dev, src, count, words, num_sectors, sel_out, found_out, row_offset,
+		                                          translate, scratch, stream, launches);
+	}
+	if (nw == 32) {
+		return launch_probe_folded_nw<Src, P, 32>(dev, src, count, words, num_sectors, sel_out, found_out, row_offset,
+		                                          translate, scratch, stream, launches);
+	}
+	return launch_probe_folded_nw<Src, P, 24>(dev, src, count, words, num_sectors, sel_out, found_out, row_offset,
+	                                          translate, scratch, stream, launches);
+}
+
 static int probe_units() {
 	static const int units = [] {
 		const char *e = getenv("RPT_PROBE_UNITS");
@@ -2496,9 +3087,32 @@ static cudaError_t launch_probe_src(const DeviceInfo &dev, const Src &src, uint6
 		return smem ? launch_probe_fused<Src, kProbeBlockSmem, true>(RPT_PROBE_ARGS)
 		            : launch_probe_fused<Src, kProbeBlock, false>(RPT_PROBE_ARGS);
 	}
-	if (t_pre != nullptr && prefilter_applicable(num_sectors) && t_pre->sectors == kSliceSectors &&
+	if (t_pre != nullptr && prefilter_applicable(num_sectors) && t_pre->sectors <= kSliceSectors &&
 	    (t_gate == nullptr || t_gate->n == 0)) {
-		// folded pre-filter: slice 0 is a bucket like the others (the partition kernel touches the folded filter only)
+		// folded pre-filter.  Flat key columns: probe_fold_kernel (half-segment staging, survivors only); generic
+		// sources: the 512-row partition kernel with the folded test in front (slice 0 is a bucket like the others,
+		// so that kernel touches the folded filter only).  RPT_FOLD_KERNEL=0 sends flat columns there too.
+		static const int fold_kernel_choice = [] { // 0: partition kernel, 1: bulk-copy staging, 2/3: no shared memory
+			const char *e = getenv("RPT_FOLD_KERNEL");
+			return e ? atoi(e) : 1;
+		}();
+		if (fold_kernel_choice >= 2) {
+			if (num_sectors == 4 * kSliceSectors) {
+				return fold_kernel_choice == 2 ? launch_probe_folded_direct<Src, 4, 4>(RPT_PROBE_ARGS)
+				                               : launch_probe_folded_direct<Src, 4, 3>(RPT_PROBE_ARGS);
+			}
+			return fold_kernel_choice == 2 ? launch_probe_folded_direct<Src, 8, 4>(RPT_PROBE_ARGS)
+			                               : launch_probe_folded_direct<Src, 8, 3>(RPT_PROBE_ARGS);
+		}
+		if constexpr (Src::kStageable) {
+			const bool half_kernel = fold_kernel_choice == 1;
+			if (half_kernel) {
+				if (num_sectors == 4 * kSliceSectors) {
+					return launch_probe_folded<Src, 4>(RPT_PROBE_ARGS);
+				}
+				return launch_probe_folded<Src, 8>(RPT_PROBE_ARGS);
+			}
+		}
 		if (num_sectors == 4 * kSliceSectors) {
 			return launch_probe_partitioned<Src, 4, static_cast<int>(kSliceShift), false, true>(RPT_PROBE_ARGS);
 		}

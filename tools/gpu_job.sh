@@ -135,10 +135,11 @@ prefilter)  # folded pre-filter: its tests, then on/off sweeps at config 2 (1 %,
 	tail -25 gpurun_out/tests_prefilter_${tag}.log
 	out=gpurun_out/prefilter_${tag}.txt
 	: > $out
-	for knobs in "" "RPT_PREFILTER=0"; do
+	for knobs in "" "RPT_FOLD_KERNEL=2" "RPT_FOLD_KERNEL=3" "RPT_FOLD_KERNEL=0" "RPT_FOLD_MIB=32" "RPT_FOLD_KERNEL=2 RPT_FOLD_MIB=32" "RPT_PREFILTER=0"; do
 		for ppm in 100000 10000 500000; do
+			case "$knobs" in RPT_FOLD_KERNEL=[03]*|RPT_FOLD_MIB*|*MIB=32) [ $ppm = 100000 ] || continue;; esac
 			echo "== knobs: ${knobs:-default} ppm=$ppm" >> $out
-			env $knobs SWEEP_PPM=$ppm timeout -s KILL 300 python tools/probe_sweep.py 1e9 5 1e8 >> $out 2>&1
+			env $knobs RPT_PREFILTER_MAX_ALIVE=2 SWEEP_PPM=$ppm timeout -s KILL 300 python tools/probe_sweep.py 1e9 5 1e8 >> $out 2>&1
 			echo "rc=$?" >> $out
 		done
 	done
