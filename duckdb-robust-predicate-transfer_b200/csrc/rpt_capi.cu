@@ -8,6 +8,7 @@
 #include <cuda_runtime.h>
 
 #include <atomic>
+#include <cmath>
 #include <memory>
 #include <cstdarg>
 #include <cstdio>
@@ -150,6 +151,11 @@ struct rpt_bf {
 	std::atomic<uint64_t> content_version {1};
 	uint64_t fold_version = 0;
 	double fold_pass = 1.0;            // estimated share of non-member keys that survive the folded filter
+	// rows inserted since the words were last zeroed, while inserts are all that happened to them (-1: unknown — an
+	// import, a merge, or the address was handed out): lets the host estimate the fold's density WITHOUT waiting
+	std::atomic<long long> rows_inserted {0};
+	cudaEvent_t fold_ready = nullptr;  // recorded behind the fold kernel; every pre-filtered probe waits for it
+	bool fold_pop_pending = false;     // the fold's measured bit count is on its way to fold_pop_host
 	std::atomic<int> fold_mode {-1};   // rpt_bf_set_prefilter: -1 = library default (RPT_PREFILTER)
 	// feedback: the pre-filtered partition counts the rows it saw and the rows that survived the folded filter
 	// (members + its false positives); when too many survive, the pre-filter costs more than it saves and the
@@ -626,6 +632,7 @@ static int allocate_words(rpt_bf *bf, uint64_t rows) {
 	bf->num_sectors = s;
 	bf->sized_for_rows = rows;
 	bf->content_version++;
+	bf->rows_inserted.store(0);
 	// std::fill_n(bf, num_sectors, 0), bloom_filter.cpp:24
 	RPT_CUDA(cudaMemsetAsync(bf->words, 0, s * sizeof(uint64_t), bf->stream));
 	RPT_CUDA(cudaStreamSynchronize(bf->stream));
@@ -711,6 +718,9 @@ int rpt_bf_destroy(rpt_bf_t *bf) {
 	if (bf->fold_stats_ev) {
 		cudaEventDestroy(bf->fold_stats_ev);
 	}
+	if (bf->fold_ready) {
+		cudaEventDestroy(bf->fold_ready);
+	}
 	for (cudaStream_t s : {bf->stream, bf->h2d, bf->compute, bf->d2h}) {
 		if (s) {
 			cudaStreamSynchronize(s);
@@ -753,6 +763,7 @@ int rpt_bf_reset(rpt_bf_t *bf, uint64_t est_rows, rpt_stream_t stream) {
 		bf->num_sectors = s; // fits the buffer: stream-ordered like every other use of the words on `stream`
 		bf->sized_for_rows = est_rows;
 		bf->content_version++;
+		bf->rows_inserted.store(0);
 		RPT_CUDA(cudaMemsetAsync(bf->words, 0, s * sizeof(uint64_t), pick_stream(bf, stream)));
 	}
 	bf->has_data.store(0);
@@ -774,7 +785,8 @@ RPT_GETTER(rpt_bf_is_empty, int, bf->has_data.load() ? 0 : 1)
 RPT_GETTER(rpt_bf_is_finalized, int, bf->finalized.load())
 RPT_GETTER(rpt_bf_device, int, bf->dev.device)
 // whoever holds the address may write the words (NCCL all-gather targets, tests): the folded pre-filter is stale
-RPT_GETTER(rpt_bf_device_words, uint64_t *, (const_cast<rpt_bf_t *>(bf)->content_version++, bf->words))
+RPT_GETTER(rpt_bf_device_words, uint64_t *,
+           (const_cast<rpt_bf_t *>(bf)->content_version++, const_cast<rpt_bf_t *>(bf)->rows_inserted.store(-1), bf->words))
 
 int rpt_bf_launch_count(const rpt_bf_t *bf, long long *out) {
 	if (!bf || !out) {
@@ -825,6 +837,9 @@ static int insert_impl(rpt_bf *bf, const rpt_col_t *cols, int ncols, uint64_t co
 	}
 	bf->has_data.store(1); // src/bloom_filter.cpp:75
 	bf->content_version++;
+	if (bf->rows_inserted.load() >= 0) {
+		bf->rows_inserted += static_cast<long long>(count);
+	}
 	int launches = 0;
 	if (mem == RPT_MEM_DEVICE) {
 		DevCols dc;
@@ -1042,10 +1057,12 @@ int rpt_bf_finalize(rpt_bf_t *bf, uint64_t actual_rows, const rpt_col_t *cols, i
 // ---------------------------------------------------------------------------------------------
 // Folded pre-filter for probes of 256 / 512 MiB filters (rpt_kernels.cuh Prefilter; DESIGN.md §4 regime 3c).  The
 // fold is made lazily, by the first probe of ≥ 2^22 rows after a change of the words, on that probe's stream (so it
-// is ordered behind the inserts / merges the caller ordered the probe behind); the stream is synchronised once so
-// that the host can read the folded filter's bit density and decide: the pre-filter is used while the estimated
-// share of non-member keys that survive it stays ≤ RPT_PREFILTER_MAX_PASS (default 0.5).  Results never depend on
-// it — a key the folded filter rejects cannot pass the real one.  RPT_PREFILTER=0 switches it off, =2 forces it.
+// is ordered behind the inserts / merges the caller ordered the probe behind); probes on other streams wait for its
+// event.  Whether it is used depends on how many non-member keys would survive it (≤ RPT_PREFILTER_MAX_PASS, default
+// 0.5), which follows from the fold's bit density: estimated from the number of rows inserted since the words were
+// zeroed (no host synchronisation; the fold kernel's own bit count replaces the estimate once it has arrived), or,
+// for imported / merged words, read from the fold after one stream synchronisation.  Results never depend on any of
+// this — a key the folded filter rejects cannot pass the real one.  RPT_PREFILTER=0 switches it off, =2 forces it.
 static int prefilter_mode() {
 	static const int mode = [] {
 		const char *e = getenv("RPT_PREFILTER");
@@ -1053,13 +1070,10 @@ static int prefilter_mode() {
 	}();
 	return mode;
 }
-// size of the folded filter: one L2-resident slice (64 MiB); RPT_FOLD_MIB=32 folds twice as far (experiments)
+// size of the folded filter: one L2-resident slice (64 MiB).  A 32-MiB fold would be fully resident but lets 35 % of
+// the non-members through at config 2's density: 8.1 ms against 6.2 ms (profiles/prefilter_r2u.txt)
 static uint64_t fold_sectors() {
-	static const uint64_t v = [] {
-		const char *e = getenv("RPT_FOLD_MIB");
-		return e && atoi(e) == 32 ? kSliceSectors / 2 : kSliceSectors;
-	}();
-	return v;
+	return kSliceSectors;
 }
 static double prefilter_max_pass() {
 	static const double v = [] {
@@ -1069,12 +1083,19 @@ static double prefilter_max_pass() {
 	return v;
 }
 
-static double prefilter_max_alive() {
+// Share of a probe's rows beyond which the pre-filter stops paying (measured, profiles/prefilter_r2v.txt): at four
+// slices the pre-filtered and the plain partition meet at ≈ 30 % survivors (17 %: 6.3 against 7.4 ms; 54 %: 10.4
+// against 8.3 ms), at eight slices — where the plain partition writes 7/8 of the keys as records — at ≈ 45 % (36 %:
+// 8.5 against 9.4 ms; 66 %: 10.9 against 9.6 ms).  RPT_PREFILTER_MAX_ALIVE overrides both.
+static double prefilter_max_alive(uint64_t num_sectors) {
 	static const double v = [] {
 		const char *e = getenv("RPT_PREFILTER_MAX_ALIVE");
-		return e ? atof(e) : 0.30;
+		return e ? atof(e) : -1.0;
 	}();
-	return v;
+	if (v >= 0) {
+		return v;
+	}
+	return num_sectors > 4 * kSliceSectors ? 0.45 : 0.30;
 }
 
 // *measure: the caller must call prefilter_measured(bf, stream) behind the last launch_probe of this call
@@ -1103,7 +1124,7 @@ static int ensure_prefilter(rpt_bf *bf, uint64_t count, cudaStream_t s, Prefilte
 			bf->fold_holdoff--;
 			return 0;
 		}
-		if (bf->fold_alive > prefilter_max_alive()) {
+		if (bf->fold_alive > prefilter_max_alive(bf->num_sectors)) {
 			// measured (profiles/prefilter_r2q.txt): with a third of the rows surviving, the pre-filtered partition and
 			// its fuller buckets take as long as the plain partition; beyond, longer.  Try again 16 large probes on.
 			bf->fold_alive = -1.0;
@@ -1112,32 +1133,59 @@ static int ensure_prefilter(rpt_bf *bf, uint64_t count, cudaStream_t s, Prefilte
 		}
 	}
 	const uint64_t version = bf->content_version.load();
+	if (bf->fold_pop_pending && cudaEventQuery(bf->fold_ready) == cudaSuccess) { // the measured density has arrived
+		bf->fold_pop_pending = false;
+		if (bf->fold_version == version) {
+			const double d = static_cast<double>(*bf->fold_pop_host) / (64.0 * static_cast<double>(fold_sectors()));
+			bf->fold_pass = 0.91 * d * d * d * d + 0.09 * d * d * d;
+		}
+	}
+	cudaGetLastError();
 	if (bf->fold_version != version) {
 		if (count < (1ULL << 22) && mode != 2) {
 			return 0; // a small probe does not pay for a fold (read S words, write 64 MiB)
 		}
 		if (!bf->folded) {
-			RPT_CUDA(cudaMalloc(&bf->folded, kSliceSectors * sizeof(uint64_t))); // holds either fold size
+			RPT_CUDA(cudaMalloc(&bf->folded, kSliceSectors * sizeof(uint64_t)));
 			RPT_CUDA(cudaMalloc(&bf->fold_pop_dev, sizeof(uint64_t)));
 			RPT_CUDA(cudaMallocHost(&bf->fold_pop_host, sizeof(uint64_t)));
 			RPT_CUDA(cudaMalloc(&bf->fold_stats_dev, 2 * sizeof(uint64_t)));
 			RPT_CUDA(cudaMallocHost(&bf->fold_stats_host, 2 * sizeof(uint64_t)));
 			RPT_CUDA(cudaEventCreateWithFlags(&bf->fold_stats_ev, cudaEventDisableTiming));
+			RPT_CUDA(cudaEventCreateWithFlags(&bf->fold_ready, cudaEventDisableTiming));
+		}
+		if (bf->fold_pop_pending) { // an earlier fold's count is still in flight into the same pinned word
+			RPT_CUDA(cudaEventSynchronize(bf->fold_ready));
+			bf->fold_pop_pending = false;
 		}
 		RPT_CUDA(launch_fold(bf->dev, bf->words, bf->num_sectors, bf->folded, fold_sectors(), bf->fold_pop_dev, s));
 		RPT_CUDA(cudaMemcpyAsync(bf->fold_pop_host, bf->fold_pop_dev, sizeof(uint64_t), cudaMemcpyDeviceToHost, s));
-		RPT_CUDA(cudaStreamSynchronize(s)); // the fold is complete before its version is published to other threads
+		RPT_CUDA(cudaEventRecord(bf->fold_ready, s)); // probes on other streams wait for this event, not the host
 		(*launches)++;
-		const double d = static_cast<double>(*bf->fold_pop_host) / (64.0 * static_cast<double>(fold_sectors()));
+		const long long rows = bf->rows_inserted.load();
+		double d;
+		if (rows >= 0) {
+			// only inserts since the words were zeroed: a key sets 4 of a word's 64 bits (with repetition), so a bit of
+			// the folded filter is still clear with probability (1 - (1 - (63/64)^4) / FS)^rows.  Duplicate keys make
+			// this an over-estimate of the density — the cautious side; the measured count replaces it when it arrives.
+			d = 1.0 - exp(-static_cast<double>(rows) * 0.061052 / static_cast<double>(fold_sectors()));
+			bf->fold_pop_pending = true;
+		} else {
+			// imported or merged words: nothing to estimate from — wait for the fold and read its bit count
+			RPT_CUDA(cudaStreamSynchronize(s));
+			d = static_cast<double>(*bf->fold_pop_host) / (64.0 * static_cast<double>(fold_sectors()));
+		}
 		// a key sets 4 bit positions, 3 distinct ones with probability ≈ 0.09 (two of its 6-bit fields collide)
 		bf->fold_pass = 0.91 * d * d * d * d + 0.09 * d * d * d;
 		bf->fold_version = version;
 		if (trace_on()) {
-			fprintf(stderr, "[rpt trace] fold: %llu -> %llu sectors, density %.4f, estimated pass rate %.4f\n",
-			        (unsigned long long)bf->num_sectors, (unsigned long long)fold_sectors(), d, bf->fold_pass);
+			fprintf(stderr, "[rpt trace] fold: %llu -> %llu sectors, density %.4f (%s), estimated pass rate %.4f\n",
+			        (unsigned long long)bf->num_sectors, (unsigned long long)fold_sectors(), d,
+			        rows >= 0 ? "from the row count" : "measured", bf->fold_pass);
 		}
 	}
 	if (bf->fold_pass <= max_pass || mode == 2) {
+		RPT_CUDA(cudaStreamWaitEvent(s, bf->fold_ready, 0)); // a no-op on the stream that made the fold
 		out->folded = bf->folded;
 		out->sectors = fold_sectors();
 		out->stats = nullptr;
@@ -1593,6 +1641,7 @@ int rpt_bf_import_words(rpt_bf_t *bf, const uint64_t *host_src, uint64_t num_wor
 	}
 	RPT_GUARD(bf);
 	bf->content_version++;
+	bf->rows_inserted.store(-1);
 	RPT_CUDA(cudaMemcpyAsync(bf->words, host_src, num_words * sizeof(uint64_t), cudaMemcpyHostToDevice, bf->stream));
 	RPT_CUDA(cudaStreamSynchronize(bf->stream));
 	bf->has_data.store(1);
@@ -1639,6 +1688,7 @@ int rpt_bf_or_parts(rpt_bf_t *bf, const uint64_t *dev_parts, uint64_t nparts, rp
 		return 0;
 	}
 	bf->content_version++;
+	bf->rows_inserted.store(-1);
 	RPT_CUDA(launch_or_parts(bf->dev, bf->words, dev_parts, bf->num_sectors, nparts, pick_stream(bf, stream)));
 	bf->launches += 1;
 	return 0;
@@ -1701,6 +1751,7 @@ static int peer_merge_range(rpt_bf *bf, int phase, uint64_t first, uint64_t nsec
 	const int n = static_cast<int>(bf->peer_words.size());
 	const int rank = bf->peer_rank;
 	bf->content_version++;
+	bf->rows_inserted.store(-1);
 	if (phase == 0) {
 		PtrList srcs;
 		srcs.n = 0;

@@ -1045,19 +1045,14 @@ static_assert((1ULL << kSliceShift) == kSliceSectors, "record layout assumes 2^2
 
 // INLINE0: the keys of slice 0 are looked up by the partition kernel itself (P-1 bucket regions per segment);
 // otherwise slice 0 is a bucket like the others (P regions, no filter access in the partition kernel).
-template <int P, bool INLINE0 = true, bool PRE = false>
+template <int P, bool INLINE0 = true>
 struct PartCfg {
 	static_assert(P == 2 || P == 4 || P == 8, "S is a power of two: 2, 4 or 8 slices");
-	static_assert(!PRE || !INLINE0, "the pre-filtered partition keeps slice 0 as a bucket");
 	// records per (segment, slice) region; expectation 512/P, σ = sqrt(512·(1/P)(1-1/P)): +5.6σ / +4.1σ / +4.3σ
 	static constexpr int CAP = P == 2 ? 320 : (P == 4 ? 168 : 96);
 	static constexpr int FIRST = INLINE0 ? 1 : 0; // first slice that has a bucket
 	static constexpr int REGIONS = P - FIRST;
-	// The shared-memory stage of a warp holds one CAP-sized area per region — or, PRE, the regions PACKED one behind
-	// the other (a segment has 512 keys, so 4 KiB always suffice and the stage aliases the key buffer: with a separate
-	// 5.3-KiB stage a warp took 13.5 KiB, 217 KiB per SM, and the L1 that was left could not keep the folded-filter
-	// gathers in flight — 16.5 ms per 10^9 keys instead of 4).
-	static constexpr int STAGE_BYTES = PRE ? static_cast<int>(kSegRows) * 8 : REGIONS * CAP * 8;
+	static constexpr int STAGE_BYTES = REGIONS * CAP * 8;
 	static constexpr int NCNT = P <= 4 ? 1 : 2; // per-lane counters: 8 bits per slice, four slices per register
 };
 
@@ -1065,12 +1060,12 @@ struct PartCfg {
 // stage.  When the stage fits into one key buffer it ALIASES the buffer of the segment being processed (its
 // keys are in registers by then), which keeps a warp at 8 KiB.  Two CTAs per SM: at three (80 registers) the
 // sixteen hashes spill, and the spill traffic on the LSU costs more than the extra warps hide (9.0 vs 7.3 ms).
-template <class Src, int P, bool INLINE0 = true, bool PRE = false>
+template <class Src, int P, bool INLINE0 = true>
 struct PartSmem {
 	static constexpr int KEY_SEG_BYTES = Src::kStageable ? static_cast<int>(kSegRows) * Src::kKeyBytes : 0;
-	static constexpr bool ALIAS = Src::kStageable && PartCfg<P, INLINE0, PRE>::STAGE_BYTES <= KEY_SEG_BYTES;
+	static constexpr bool ALIAS = Src::kStageable && PartCfg<P, INLINE0>::STAGE_BYTES <= KEY_SEG_BYTES;
 	static constexpr int WARP_BYTES =
-	    2 * KEY_SEG_BYTES + (ALIAS ? 0 : (PartCfg<P, INLINE0, PRE>::STAGE_BYTES + 15) / 16 * 16);
+	    2 * KEY_SEG_BYTES + (ALIAS ? 0 : (PartCfg<P, INLINE0>::STAGE_BYTES + 15) / 16 * 16);
 };
 
 __device__ __forceinline__ uint32_t shl_clamp(uint32_t v, uint32_t s) { // PTX shl.b32: a shift ≥ 32 yields 0
@@ -1079,24 +1074,18 @@ __device__ __forceinline__ uint32_t shl_clamp(uint32_t v, uint32_t s) { // PTX s
 	return d;
 }
 
-// PRE: every key is first tested against the FOLDED filter (folded[i] = OR of the words i + j·(fold_mask+1), one
-// L2-resident slice: fold_kernel below).  A key whose four bits are not all set in the folded word cannot have them
-// set in its own word, so it is dropped on the spot; only the survivors (members + the folded filter's false
-// positives) become records and meet the real filter in the bucket kernels.
-template <class Src, int BLOCK, int P, int SHIFT = kSliceShift, bool INLINE0 = true, bool PRE = false>
+template <class Src, int BLOCK, int P, int SHIFT = kSliceShift, bool INLINE0 = true>
 __global__ void __launch_bounds__(BLOCK, 2)
     probe_partition_kernel(const Src src, const uint64_t *__restrict__ filter, const uint32_t sector_mask,
                            const uint64_t count, const uint64_t num_segs, uint16_t *__restrict__ bitmap16,
                            uint2 *__restrict__ buckets, const uint64_t bucket_stride /* records per slice array */,
                            uint16_t *__restrict__ bucket_counts /* (P-1) × num_segs */,
-                           uint32_t *__restrict__ ovf_list /* [0] = count, [1 + i] = i-th overflowed segment */,
-                           const uint64_t *__restrict__ folded = nullptr, const uint32_t fold_mask = 0,
-                           unsigned long long *__restrict__ pre_stats = nullptr /* PRE: [0] += rows, [1] += survivors */) {
+                           uint32_t *__restrict__ ovf_list /* [0] = count, [1 + i] = i-th overflowed segment */) {
 	constexpr int NWARPS = BLOCK / 32;
 	constexpr bool STAGED = Src::kStageable;
 	using Geo = StageGeo<Src::kKeyBytes>;
-	using Smem = PartSmem<Src, P, INLINE0, PRE>;
-	using Cfg = PartCfg<P, INLINE0, PRE>;
+	using Smem = PartSmem<Src, P, INLINE0>;
+	using Cfg = PartCfg<P, INLINE0>;
 	constexpr int SEG_UNITS = Geo::SEG_UNITS;
 	constexpr int CAP = Cfg::CAP;
 	constexpr int NCNT = Cfg::NCNT;
@@ -1108,12 +1097,10 @@ __global__ void __launch_bounds__(BLOCK, 2)
 	uint4 *const my_buf = reinterpret_cast<uint4 *>(my_smem);
 	const uint64_t pol_keys = policy_evict_first();
 	const uint64_t pol_filter = policy_evict_last();
-	if (PRE) {
-		warm_slice(folded, 0u, fold_mask + 1u, BLOCK);
-	} else if (INLINE0) {
+	if (INLINE0) {
 		warm_slice(filter, 0u, 1u << SHIFT, BLOCK);
 	}
-	constexpr bool MASKED = PRE || !INLINE0; // keys outside `alive` are neither counted nor written as records
+	constexpr bool MASKED = !INLINE0; // slice 0 is a bucket: rows past the end must not become slice-0 records
 	const uint64_t stride = static_cast<uint64_t>(gridDim.x) * NWARPS;
 	const uint64_t full_segs = count / kSegRows;
 	const uint32_t rot = Geo::rot(lane);
@@ -1121,7 +1108,6 @@ __global__ void __launch_bounds__(BLOCK, 2)
 	constexpr uint64_t kNone = ~0ULL;
 	uint64_t cur = kNone;
 	uint32_t par = 1;
-	uint32_t seen_rows = 0, seen_alive = 0; // PRE: this lane's rows and folded-filter survivors (feedback for the host)
 	for (uint64_t nxt = static_cast<uint64_t>(blockIdx.x) * NWARPS + warp;; nxt += stride) {
 		if (STAGED) {
 			__syncwarp(); // the buffer overwritten next (keys and, when aliased, records) is no longer read
@@ -1169,13 +1155,7 @@ __global__ void __launch_bounds__(BLOCK, 2)
 			uint2 *const stage = reinterpret_cast<uint2 *>(
 			    my_smem + (Smem::ALIAS ? par * Smem::KEY_SEG_BYTES : 2 * Smem::KEY_SEG_BYTES));
 			const uint32_t unit_rot = staged_seg ? rot : 0u;
-			// slot-order mask of the keys that still need the real filter (PRE: survivors of the folded filter)
-			uint32_t alive = valid;
-			if (PRE) {
-				alive &= test_batch<16, false, false>(h, folded, nullptr, fold_mask, pol_filter, 0u, 0u);
-				seen_rows += __popc(valid);
-				seen_alive += __popc(alive);
-			}
+			const uint32_t alive = valid; // slot-order mask of the rows that exist
 
 			// pass 1: per-lane counts of the keys of every slice (8-bit fields); the slice-0 lookups of the first
 			// eight keys are issued (the second eight follow in pass 2, behind the records of the first eight)
@@ -1185,9 +1165,8 @@ __global__ void __launch_bounds__(BLOCK, 2)
 				for (int i = 0; i < 8; i++) {
 					const uint32_t sector = static_cast<uint32_t>(h[lo + i]) & sector_mask;
 					w0[i] = 0;
-					if (INLINE0 && (sector >> SHIFT) == 0u && (!PRE || ((alive >> (lo + i)) & 1u))) {
-						// PRE: the few real slice-0 words must not push the folded filter out of L2
-						w0[i] = ld_filter_word(filter + sector, PRE ? pol_keys : pol_filter);
+					if (INLINE0 && (sector >> SHIFT) == 0u) {
+						w0[i] = ld_filter_word(filter + sector, pol_filter);
 					}
 				}
 			};
@@ -1258,27 +1237,6 @@ __global__ void __launch_bounds__(BLOCK, 2)
 					    overflow ? uint16_t(0) : static_cast<uint16_t>(slice_total(s));
 				}
 			}
-			// PRE: the regions are packed in the stage — region s starts at the number of records of the slices before it
-			// (warp-uniform); adding that to the 16-bit fields of `base` makes a record's position stage-absolute
-			uint32_t stage_first[PRE ? P : 1];
-			if (PRE) {
-				uint32_t run = 0;
-				uint64_t add[NCNT];
-#pragma unroll
-				for (int j = 0; j < NCNT; j++) {
-					add[j] = 0;
-				}
-#pragma unroll
-				for (int s = 0; s < P; s++) {
-					stage_first[s] = run;
-					add[s >> 2] |= static_cast<uint64_t>(run) << (16 * (s & 3));
-					run += slice_total(s);
-				}
-#pragma unroll
-				for (int j = 0; j < NCNT; j++) {
-					base[j] += add[j]; // no carries: prefix + start ≤ 512
-				}
-			}
 			uint32_t hits = 0;
 			if (!overflow) { // warp-uniform; the usual case
 				// pass 2: records into the stage.  position = exclusive base of the slice + rank inside the lane
@@ -1306,9 +1264,8 @@ __global__ void __launch_bounds__(BLOCK, 2)
 						if ((!INLINE0 || sh != 0u) && one) {
 							const uint32_t row9 =
 							    lane * 16u + (((i / Geo::KPU + unit_rot) & (Geo::U - 1)) * Geo::KPU) + (i % Geo::KPU);
-							// byte offset of record `pos` of slice s: ((s-FIRST)·CAP + pos)·8 with 8·s = sh (PRE: pos is
-							// already stage-absolute)
-							const uint32_t off = PRE ? pos * 8u : mul_lo_u32(sh, CAP) + pos * 8u - FIRST * CAP * 8u;
+							// byte offset of record `pos` of slice s: ((s-FIRST)·CAP + pos)·8 with 8·s = sh
+							const uint32_t off = mul_lo_u32(sh, CAP) + pos * 8u - FIRST * CAP * 8u;
 							*reinterpret_cast<uint2 *>(reinterpret_cast<unsigned char *>(stage) + off) =
 							    make_uint2((sector & ((1u << SHIFT) - 1u)) | (row9 << SHIFT),
 							               static_cast<uint32_t>(h[i] >> 32));
@@ -1345,14 +1302,6 @@ __global__ void __launch_bounds__(BLOCK, 2)
 #pragma unroll
 				for (int s = FIRST; s < P; s++) {
 					const uint32_t total = slice_total(s);
-					if (PRE) { // packed regions start at any record: 8-byte copies (few records per region)
-						const uint2 *sv = stage + stage_first[s];
-						uint2 *dv = buckets + s * bucket_stride + cur * CAP;
-						for (uint32_t j = lane; j < total; j += 32u) {
-							st_stream_v2(dv + j, sv[j], pol_keys);
-						}
-						continue;
-					}
 					const uint4 *sv = reinterpret_cast<const uint4 *>(stage + (s - FIRST) * CAP);
 					uint4 *dv = reinterpret_cast<uint4 *>(buckets + (s - FIRST) * bucket_stride + cur * CAP);
 					for (uint32_t j = lane; 2u * j < total; j += 32u) {
@@ -1372,14 +1321,6 @@ __global__ void __launch_bounds__(BLOCK, 2)
 	}
 	if (STAGED) {
 		cp_async_wait<0>();
-	}
-	if (PRE && pre_stats != nullptr) {
-		seen_rows = __reduce_add_sync(0xffffffffu, seen_rows);
-		seen_alive = __reduce_add_sync(0xffffffffu, seen_alive);
-		if (lane == 0) {
-			atomicAdd(pre_stats, static_cast<unsigned long long>(seen_rows));
-			atomicAdd(pre_stats + 1, static_cast<unsigned long long>(seen_alive));
-		}
 	}
 }
 
@@ -1456,68 +1397,6 @@ __global__ void __launch_bounds__(256)
 	}
 }
 
-// Bucket kernel of the pre-filtered partition (PRE): regions are sparse (a handful of survivors per segment and
-// slice instead of 512/P), so a warp takes FOUR consecutive regions at a time — their counts, then their first 32
-// records, then the filter words are in flight together — and only a region with more than 32 records (a segment
-// full of members) loops.
-template <int CAP, int SHIFT = kSliceShift>
-__global__ void __launch_bounds__(256)
-    probe_bucket_sparse_kernel(const uint2 *__restrict__ bucket, const uint16_t *__restrict__ counts,
-                               const uint64_t num_segs, const uint64_t *__restrict__ filter, const uint32_t slice_lo,
-                               uint32_t *__restrict__ bitmap32) {
-	constexpr int R = 4;
-	const uint32_t lane = threadIdx.x & 31u;
-	const uint64_t pol_rec = policy_evict_first();
-	const uint64_t pol_filter = policy_evict_last();
-	warm_slice(filter, slice_lo, 1u << SHIFT, 256);
-	const uint64_t *const slice = filter + slice_lo;
-	const uint64_t warp_global = (static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
-	const uint64_t num_warps = (static_cast<uint64_t>(gridDim.x) * blockDim.x) >> 5;
-	for (uint64_t seg0 = warp_global * R; seg0 < num_segs; seg0 += num_warps * R) {
-		uint32_t c[R];
-#pragma unroll
-		for (int r = 0; r < R; r++) {
-			c[r] = seg0 + r < num_segs ? __ldg(counts + seg0 + r) : 0u;
-		}
-		uint2 rec[R];
-#pragma unroll
-		for (int r = 0; r < R; r++) {
-			rec[r] = make_uint2(0u, 0u);
-			if (lane < c[r]) {
-				const uint64_t v = ld_stream_u64(bucket + (seg0 + r) * CAP + lane, pol_rec);
-				rec[r] = make_uint2(static_cast<uint32_t>(v), static_cast<uint32_t>(v >> 32));
-			}
-		}
-		uint64_t w[R];
-#pragma unroll
-		for (int r = 0; r < R; r++) {
-			w[r] = 0; // an all-zero word (no record) passes nothing
-			if (lane < c[r]) {
-				w[r] = ld_filter_word(slice + (rec[r].x & ((1u << SHIFT) - 1u)), pol_filter);
-			}
-		}
-#pragma unroll
-		for (int r = 0; r < R; r++) {
-			if (sector_test_fma(w[r], rec[r].y)) {
-				const uint32_t row9 = rec[r].x >> SHIFT;
-				atomicOr(bitmap32 + (seg0 + r) * 16 + (row9 >> 5), 1u << (row9 & 31u));
-			}
-		}
-#pragma unroll
-		for (int r = 0; r < R; r++) {
-			for (uint32_t j = lane + 32u; j < c[r]; j += 32u) { // warp-uniform bound: rare
-				const uint64_t v = ld_stream_u64(bucket + (seg0 + r) * CAP + j, pol_rec);
-				const uint32_t x = static_cast<uint32_t>(v);
-				const uint64_t word = ld_filter_word(slice + (x & ((1u << SHIFT) - 1u)), pol_filter);
-				if (sector_test_fma(word, static_cast<uint32_t>(v >> 32))) {
-					const uint32_t row9 = x >> SHIFT;
-					atomicOr(bitmap32 + (seg0 + r) * 16 + (row9 >> 5), 1u << (row9 & 31u));
-				}
-			}
-		}
-	}
-}
-
 // folded[i] = OR over j of words[i + j·fold_sectors] (i < fold_sectors), and the number of set bits of the folded
 // filter (→ the share of non-members that will survive it).  128-bit loads, one slice after the other per thread.
 __global__ void __launch_bounds__(256)
@@ -1566,9 +1445,9 @@ __global__ void __launch_bounds__(256)
 //                     No region can overflow (a half has 256 keys), so there is no fallback path.
 // probe_bucket_half_kernel  once per slice: the slice's records of four halves at a time → real filter word → test →
 //                     RED.OR into the row-ordered bitmap (which probe_fold_kernel zeroed).
-// ncu of the first pre-filtered version (the 512-row partition kernel with a folded test in front, still used for
-// generic sources): 72 instructions per key, 15 warps per SM, issue 36 % — latency-bound.  This one: 8 keys per lane
-// and no 16-hash register block, so 24+ warps per SM fit.
+// ncu of the first pre-filtered version (probe_partition_kernel with a folded test in front, commit 4d0fd14): 72
+// instructions per key, 15 warps per SM, issue 36 % — latency-bound, 5.4 ms per 10^9 keys.  This one: 8 keys per
+// lane and no 16-hash register block, so 24 warps per SM fit: 4.7 ms, L1TEX 81 % busy (profiles/ncu_fold_r2u.md).
 template <int P>
 struct FoldCfg {
 	static constexpr int NCNT = P <= 4 ? 1 : 2; // per-lane counters: 8 bits per slice, four slices per register
@@ -1779,7 +1658,10 @@ __global__ void __launch_bounds__(NWARPS * 32, 1)
 // line (measured: 217 KiB of shared memory per SM → 16.5 ms per 10^9 keys, 128 KiB → 5.4 ms, 96 KiB → 4.7 ms —
 // each time ≈ (L1 lines) / latency).  So the keys come straight into registers (lane l owns rows l, l+32, …, l+224
 // of a half: eight coalesced loads, all in flight before the first hash) and the survivors' records leave as
-// 8-byte stores at their sorted positions (the L2 merges a region's stores).  Any key source.
+// 8-byte stores at their sorted positions (the L2 merges a region's stores).  Any key source; used for the generic
+// ones (several columns, selections, dictionaries), which cannot be staged by bulk copies: two key columns, 4·10^8
+// rows, F = 256 MiB: 6.3 ms against 9.2 ms without the pre-filter (profiles/prefilter_r2v.txt).  For flat columns
+// probe_fold_kernel is faster (6.2 against 6.5 ms per 10^9 rows).
 template <class Src, int P, int MINB>
 __global__ void __launch_bounds__(256, MINB)
     probe_fold_direct_kernel(const Src src, const uint64_t *__restrict__ folded, const uint32_t fold_mask,
@@ -1947,25 +1829,32 @@ __global__ void __launch_bounds__(256, 3)
 			atomicOr(bitmap32 + half * 8 + (row8 >> 5), 1u << (row8 & 31u));
 		}
 	};
-	for (uint64_t h0 = warp_global * (4 * T); h0 < num_halves; h0 += num_warps * (4 * T)) {
-		uint32_t lo[T], hi[T];
+	// the bounds of the NEXT step are loaded one step ahead (lo | hi << 16): two dependent loads per step, not three
+	uint32_t lh[T];
+	auto bounds = [&](uint64_t h0, uint32_t (&b)[T]) {
 #pragma unroll
 		for (int t = 0; t < T; t++) {
 			const uint64_t half = h0 + t * 4 + group;
-			lo[t] = hi[t] = 0;
+			b[t] = 0;
 			if (half < num_halves) {
-				hi[t] = __ldg(ends + half * P + s);
-				lo[t] = s ? __ldg(ends + half * P + s - 1) : 0u;
+				const uint32_t h = __ldg(ends + half * P + s);
+				const uint32_t l = s ? __ldg(ends + half * P + s - 1) : 0u;
+				b[t] = l | (h << 16);
 			}
 		}
+	};
+	bounds(warp_global * (4 * T), lh);
+	for (uint64_t h0 = warp_global * (4 * T); h0 < num_halves; h0 += num_warps * (4 * T)) {
+		uint32_t next[T];
+		bounds(h0 + num_warps * (4 * T), next);
 		uint64_t rec[T][K];
 #pragma unroll
 		for (int t = 0; t < T; t++) {
 #pragma unroll
 			for (int k = 0; k < K; k++) {
-				const uint32_t j = lo[t] + q + 8u * k;
+				const uint32_t j = (lh[t] & 0xffffu) + q + 8u * k;
 				rec[t][k] = 0;
-				if (j < hi[t]) {
+				if (j < (lh[t] >> 16)) {
 					rec[t][k] = ld_stream_u64(records + (h0 + t * 4 + group) * kHalfRows + j, pol_rec);
 				}
 			}
@@ -1976,7 +1865,7 @@ __global__ void __launch_bounds__(256, 3)
 #pragma unroll
 			for (int k = 0; k < K; k++) {
 				w[t][k] = 0;
-				if (lo[t] + q + 8u * k < hi[t]) {
+				if ((lh[t] & 0xffffu) + q + 8u * k < (lh[t] >> 16)) {
 					w[t][k] = ld_filter_word(slice + (static_cast<uint32_t>(rec[t][k]) & ((1u << SHIFT) - 1u)), pol_filter);
 				}
 			}
@@ -1990,11 +1879,15 @@ __global__ void __launch_bounds__(256, 3)
 		}
 #pragma unroll
 		for (int t = 0; t < T; t++) {
-			for (uint32_t j = lo[t] + q + 8u * K; j < hi[t]; j += 8u) { // halves rich in members
+			for (uint32_t j = (lh[t] & 0xffffu) + q + 8u * K; j < (lh[t] >> 16); j += 8u) { // halves rich in members
 				const uint64_t half = h0 + t * 4 + group;
 				const uint64_t v = ld_stream_u64(records + half * kHalfRows + j, pol_rec);
 				apply(half, v, ld_filter_word(slice + (static_cast<uint32_t>(v) & ((1u << SHIFT) - 1u)), pol_filter));
 			}
+		}
+#pragma unroll
+		for (int t = 0; t < T; t++) {
+			lh[t] = next[t];
 		}
 	}
 }
@@ -2176,6 +2069,20 @@ __global__ void __launch_bounds__(256)
 		word = word_n;
 		off = off_n;
 	}
+}
+
+static inline uint64_t ceil_div(uint64_t a, uint64_t b);
+// bitmap → selection vector: segment counts are in seg_offsets (exclusive, per scan block) and block_totals
+static void launch_compact(const DeviceInfo &dev, const uint32_t *bitmap, const uint32_t *seg_offsets,
+                           const uint32_t *block_totals, uint64_t num_segs, uint32_t *sel_out, uint32_t row_offset,
+                           const uint32_t *translate, cudaStream_t stream) {
+	// 8 warps per CTA, one chunk per warp iteration; 32 KiB of runs per CTA: 6 CTAs per SM.  (A variant that stores
+	// the row ids straight from the lanes, without the staged run: 0.31 against 0.26 ms at 10 % survivors and 2.4 ms
+	// slower at 50 % — profiles/prefilter_r2v.txt.)
+	const uint64_t cwant = ceil_div((num_segs + 1) / 2, 8ull);
+	const uint64_t ccap = static_cast<uint64_t>(dev.sm_count) * 6;
+	compact_bitmap_kernel<<<static_cast<unsigned>(cwant < ccap ? cwant : ccap), 256, 0, stream>>>(
+	    bitmap, seg_offsets, block_totals, num_segs, sel_out, row_offset, translate);
 }
 
 // Small probes (≤ kFusedMaxKeys): one launch; tiles are chained with a decoupled look-back.
@@ -2520,27 +2427,29 @@ static PartPlan partition_plan(uint64_t num_sectors, int slices64) {
 }
 // extra scratch behind the phased layout (R = bucket regions per segment, P or P-1):
 // [bucket counts u16 × R·segs][overflow list u32 × (1 + segs)][records 8 B × R·segs·CAP]
-static size_t partition_scratch_bytes(uint64_t count, uint64_t num_sectors, int slices64, bool prefilter) {
+static size_t partition_scratch_bytes(uint64_t count, uint64_t num_sectors, int slices64) {
 	const uint64_t num_segs = ceil_div(count, kSegRows);
-	PartPlan plan = partition_plan(num_sectors, slices64);
-	if (prefilter) { // the pre-filtered partition: 64-MiB slices, slice 0 a bucket like the others
-		plan = PartPlan {slices64, static_cast<int>(kSliceShift), false};
-	}
+	const PartPlan plan = partition_plan(num_sectors, slices64);
 	const uint64_t regions = plan.slices - (plan.inline0 ? 1 : 0);
 	return align_up(regions * num_segs * sizeof(uint16_t), 256) + align_up((num_segs + 1) * sizeof(uint32_t), 256) +
 	       regions * num_segs * partition_cap(plan.slices) * sizeof(uint2);
+}
+// extra scratch of a pre-filtered probe behind the phased layout: [ends u16 × P × halves][records 8 B × 256 × halves]
+static size_t folded_scratch_bytes(uint64_t count, uint64_t num_sectors) {
+	const uint64_t num_halves = 2 * ceil_div(count, kSegRows);
+	const uint64_t slices = num_sectors / kSliceSectors;
+	return align_up(num_halves * slices * sizeof(uint16_t), 256) + num_halves * kHalfRows * sizeof(uint2);
 }
 
 size_t probe_scratch_bytes(uint64_t count, uint64_t num_sectors, bool prefilter) {
 	if (count <= kFusedMaxKeys) {
 		return (ceil_div(count, kProbeTileKeys) + 2) * sizeof(uint64_t); // look-back descriptors + ticket
 	}
-	int slices = partition_slices(num_sectors);
 	if (prefilter && prefilter_applicable(num_sectors)) {
-		slices = static_cast<int>(num_sectors / kSliceSectors);
+		return align_up(phased_layout(count).bytes, 256) + folded_scratch_bytes(count, num_sectors);
 	}
-	return align_up(phased_layout(count).bytes, 256) +
-	       (slices ? partition_scratch_bytes(count, num_sectors, slices, prefilter) : 0);
+	const int slices = partition_slices(num_sectors);
+	return align_up(phased_layout(count).bytes, 256) + (slices ? partition_scratch_bytes(count, num_sectors, slices) : 0);
 }
 
 template <class Src, bool AGG, bool MM>
@@ -2744,10 +2653,7 @@ static cudaError_t launch_probe_phased(const DeviceInfo &dev, const Src &src, ui
 		const uint64_t nblocks = ceil_div(num_segs, kScanBlock);
 		scan_blocks_kernel<<<static_cast<unsigned>(nblocks), 1024, 0, stream>>>(seg_offsets, num_segs, block_totals);
 		scan_totals_kernel<<<1, 1024, 0, stream>>>(block_totals, static_cast<uint32_t>(nblocks), found_out);
-		const uint64_t cwant = ceil_div((num_segs + 1) / 2, 8ull);
-		const uint64_t ccap = static_cast<uint64_t>(dev.sm_count) * 6;
-		compact_bitmap_kernel<<<static_cast<unsigned>(cwant < ccap ? cwant : ccap), 256, 0, stream>>>(
-		    reinterpret_cast<const uint32_t *>(bitmap), seg_offsets, block_totals, num_segs, sel_out, row_offset, translate);
+		launch_compact(dev, reinterpret_cast<const uint32_t *>(bitmap), seg_offsets, block_totals, num_segs, sel_out, row_offset, translate, stream);
 		if (launches) {
 			(*launches) += 4;
 		}
@@ -2801,10 +2707,7 @@ static cudaError_t launch_probe_phased(const DeviceInfo &dev, const Src &src, ui
 	const uint64_t nblocks = ceil_div(num_segs, kScanBlock);
 	scan_blocks_kernel<<<static_cast<unsigned>(nblocks), 1024, 0, stream>>>(seg_offsets, num_segs, block_totals);
 	scan_totals_kernel<<<1, 1024, 0, stream>>>(block_totals, static_cast<uint32_t>(nblocks), found_out);
-	const uint64_t cwant = ceil_div((num_segs + 1) / 2, 8ull); // 8 warps per CTA, one chunk per warp iteration
-	const uint64_t ccap = static_cast<uint64_t>(dev.sm_count) * 6; // 32 KiB of runs per CTA: 6 CTAs per SM
-	compact_bitmap_kernel<<<static_cast<unsigned>(cwant < ccap ? cwant : ccap), 256, 0, stream>>>(
-	    reinterpret_cast<const uint32_t *>(bitmap), seg_offsets, block_totals, num_segs, sel_out, row_offset, translate);
+	launch_compact(dev, reinterpret_cast<const uint32_t *>(bitmap), seg_offsets, block_totals, num_segs, sel_out, row_offset, translate, stream);
 	if (launches) {
 		(*launches) += 3;
 	}
@@ -2814,21 +2717,21 @@ static cudaError_t launch_probe_phased(const DeviceInfo &dev, const Src &src, ui
 
 static thread_local const Prefilter *t_pre = nullptr;
 
-template <class Src, int P, int SHIFT = kSliceShift, bool INLINE0 = true, bool PRE = false>
+template <class Src, int P, int SHIFT = kSliceShift, bool INLINE0 = true>
 static cudaError_t launch_probe_partitioned(const DeviceInfo &dev, const Src &src, uint64_t count,
                                             const uint64_t *words, uint64_t num_sectors, uint32_t *sel_out,
                                             uint64_t *found_out, uint32_t row_offset, const uint32_t *translate,
                                             void *scratch, cudaStream_t stream, int *launches) {
 	constexpr int BLOCK = kProbeBlock;
-	using Cfg = PartCfg<P, INLINE0, PRE>;
+	using Cfg = PartCfg<P, INLINE0>;
 	constexpr int CAP = Cfg::CAP;
 	constexpr int FIRST = Cfg::FIRST;
 	constexpr int REGIONS = Cfg::REGIONS;
-	auto part = probe_partition_kernel<Src, BLOCK, P, SHIFT, INLINE0, PRE>;
-	auto bucket = PRE ? probe_bucket_sparse_kernel<CAP, SHIFT> : probe_bucket_kernel<CAP, SHIFT>;
+	auto part = probe_partition_kernel<Src, BLOCK, P, SHIFT, INLINE0>;
+	auto bucket = probe_bucket_kernel<CAP, SHIFT>;
 	const uint64_t num_segs = ceil_div(count, kSegRows);
-	const size_t smem = static_cast<size_t>(BLOCK / 32) * PartSmem<Src, P, INLINE0, PRE>::WARP_BYTES;
-	cudaError_t e = ensure_max_dyn_smem<probe_partition_kernel<Src, BLOCK, P, SHIFT, INLINE0, PRE>>(dev);
+	const size_t smem = static_cast<size_t>(BLOCK / 32) * PartSmem<Src, P, INLINE0>::WARP_BYTES;
+	cudaError_t e = ensure_max_dyn_smem<probe_partition_kernel<Src, BLOCK, P, SHIFT, INLINE0>>(dev);
 	if (e != cudaSuccess) {
 		return e;
 	}
@@ -2880,18 +2783,16 @@ static cudaError_t launch_probe_partitioned(const DeviceInfo &dev, const Src &sr
 			return e;
 		}
 	}
-	part<<<static_cast<unsigned>(grid), BLOCK, smem, stream>>>(
-	    src, words, static_cast<uint32_t>(num_sectors - 1), count, num_segs, bitmap, buckets, bucket_stride, bucket_counts,
-	    gated ? overflow : nullptr, PRE ? t_pre->folded : nullptr,
-	    PRE ? static_cast<uint32_t>(t_pre->sectors - 1) : 0u,
-	    PRE ? reinterpret_cast<unsigned long long *>(t_pre->stats) : nullptr);
+	part<<<static_cast<unsigned>(grid), BLOCK, smem, stream>>>(src, words, static_cast<uint32_t>(num_sectors - 1), count,
+	                                                          num_segs, bitmap, buckets, bucket_stride, bucket_counts,
+	                                                          gated ? overflow : nullptr);
 	int bper_sm = 0;
 	e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bper_sm, bucket, 256, 0);
 	if (e != cudaSuccess) {
 		return e;
 	}
 	uint64_t bgrid = static_cast<uint64_t>(dev.sm_count) * (bper_sm > 0 ? bper_sm : 1);
-	const uint64_t bwant = ceil_div(num_segs, PRE ? 32 : 8); // the sparse kernel takes four regions per warp
+	const uint64_t bwant = ceil_div(num_segs, 8);
 	bgrid = bgrid < bwant ? bgrid : bwant;
 	for (int s = FIRST; s < P; s++) {
 		e = wait_slices(stream, gate_of(s), gate_of(s));
@@ -2912,46 +2813,23 @@ static cudaError_t launch_probe_partitioned(const DeviceInfo &dev, const Src &sr
 	const uint64_t nblocks = ceil_div(num_segs, kScanBlock);
 	scan_blocks_kernel<<<static_cast<unsigned>(nblocks), 1024, 0, stream>>>(seg_offsets, num_segs, block_totals);
 	scan_totals_kernel<<<1, 1024, 0, stream>>>(block_totals, static_cast<uint32_t>(nblocks), found_out);
-	const uint64_t cwant = ceil_div((num_segs + 1) / 2, 8ull);
-	const uint64_t ccap = static_cast<uint64_t>(dev.sm_count) * 6;
-	compact_bitmap_kernel<<<static_cast<unsigned>(cwant < ccap ? cwant : ccap), 256, 0, stream>>>(
-	    reinterpret_cast<const uint32_t *>(bitmap), seg_offsets, block_totals, num_segs, sel_out, row_offset, translate);
+	launch_compact(dev, reinterpret_cast<const uint32_t *>(bitmap), seg_offsets, block_totals, num_segs, sel_out, row_offset, translate, stream);
 	if (launches) {
 		(*launches) += 1 + REGIONS + 4 + (gated ? 1 : 0);
 	}
 	return cudaGetLastError();
 }
 
-// Pre-filtered probe of a flat key column (probe_fold_kernel + one probe_bucket_half_kernel per slice).
-// Scratch behind the phased layout: [ends u16 × P × halves][records 8 B × 256 × halves] — inside what
-// partition_scratch_bytes(prefilter) reserves for the generic pre-filtered partition.
-template <class Src, int P, int NW>
-static cudaError_t launch_probe_folded_nw(const DeviceInfo &dev, const Src &src, uint64_t count, const uint64_t *words,
-                                          uint64_t num_sectors, uint32_t *sel_out, uint64_t *found_out,
-                                          uint32_t row_offset, const uint32_t *translate, void *scratch,
-                                          cudaStream_t stream, int *launches) {
-	constexpr int KB = Src::kKeyBytes;
-	constexpr uint32_t HALF_BYTES = kHalfRows * KB;
-	constexpr uint32_t WARP_BYTES = 2 * HALF_BYTES + (HALF_BYTES >= kHalfRows * 8 ? 0 : kHalfRows * 8);
-	auto kern = probe_fold_kernel<Src, NW, P>;
-	const size_t smem = static_cast<size_t>(NW) * WARP_BYTES;
-	cudaError_t e = ensure_max_dyn_smem<probe_fold_kernel<Src, NW, P>>(dev);
-	if (e != cudaSuccess) {
-		return e;
-	}
-	int per_sm = 0;
-	e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, NW * 32, smem);
-	if (e != cudaSuccess) {
-		return e;
-	}
-	if (per_sm < 1) {
-		return cudaErrorLaunchOutOfResources;
-	}
+// Pre-filtered probe (regime 3c): probe_fold_kernel (flat key columns) or probe_fold_direct_kernel (generic sources),
+// then one probe_bucket_half_kernel per slice, then counts / scans / compaction.
+// Scratch behind the phased layout: [ends u16 × P × halves][records 8 B × 256 × halves] (folded_scratch_bytes).
+constexpr int kFoldWarps = 24; // per CTA, one CTA per SM: measured 16 / 24 / 32 → 7.56 / 7.23 / 7.58 ms per probe (r2r)
+template <class Src, int P>
+static cudaError_t launch_probe_folded(const DeviceInfo &dev, const Src &src, uint64_t count, const uint64_t *words,
+                                       uint64_t num_sectors, uint32_t *sel_out, uint64_t *found_out, uint32_t row_offset,
+                                       const uint32_t *translate, void *scratch, cudaStream_t stream, int *launches) {
 	const uint64_t num_segs = ceil_div(count, kSegRows);
 	const uint64_t num_halves = num_segs * 2;
-	uint64_t grid = static_cast<uint64_t>(dev.sm_count) * per_sm;
-	const uint64_t want = ceil_div(num_segs, NW);
-	grid = grid < want ? grid : want;
 	const PhasedLayout lay = phased_layout(count);
 	char *base = reinterpret_cast<char *>(scratch);
 	uint32_t *seg_offsets = reinterpret_cast<uint32_t *>(base);
@@ -2960,9 +2838,48 @@ static cudaError_t launch_probe_folded_nw(const DeviceInfo &dev, const Src &src,
 	char *extra = base + align_up(lay.bytes, 256);
 	uint16_t *ends = reinterpret_cast<uint16_t *>(extra);
 	uint2 *records = reinterpret_cast<uint2 *>(extra + align_up(num_halves * P * sizeof(uint16_t), 256));
-	kern<<<static_cast<unsigned>(grid), NW * 32, smem, stream>>>(
-	    src, t_pre->folded, static_cast<uint32_t>(t_pre->sectors - 1), static_cast<uint32_t>(num_sectors - 1), count,
-	    num_segs, bitmap, records, ends, reinterpret_cast<unsigned long long *>(t_pre->stats));
+	const uint32_t fold_mask = static_cast<uint32_t>(t_pre->sectors - 1);
+	const uint32_t sector_mask = static_cast<uint32_t>(num_sectors - 1);
+	unsigned long long *stats = reinterpret_cast<unsigned long long *>(t_pre->stats);
+	cudaError_t e;
+	int per_sm = 0;
+	if constexpr (Src::kStageable) {
+		constexpr int NW = kFoldWarps;
+		constexpr uint32_t HALF_BYTES = kHalfRows * Src::kKeyBytes;
+		constexpr uint32_t WARP_BYTES = 2 * HALF_BYTES + (HALF_BYTES >= kHalfRows * 8 ? 0 : kHalfRows * 8);
+		auto kern = probe_fold_kernel<Src, NW, P>;
+		const size_t smem = static_cast<size_t>(NW) * WARP_BYTES;
+		e = ensure_max_dyn_smem<probe_fold_kernel<Src, NW, P>>(dev);
+		if (e != cudaSuccess) {
+			return e;
+		}
+		e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, NW * 32, smem);
+		if (e != cudaSuccess) {
+			return e;
+		}
+		if (per_sm < 1) {
+			return cudaErrorLaunchOutOfResources;
+		}
+		uint64_t grid = static_cast<uint64_t>(dev.sm_count) * per_sm;
+		const uint64_t want = ceil_div(num_segs, NW);
+		grid = grid < want ? grid : want;
+		kern<<<static_cast<unsigned>(grid), NW * 32, smem, stream>>>(src, t_pre->folded, fold_mask, sector_mask, count,
+		                                                           num_segs, bitmap, records, ends, stats);
+	} else {
+		auto kern = probe_fold_direct_kernel<Src, P, 4>;
+		e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 256, 0);
+		if (e != cudaSuccess) {
+			return e;
+		}
+		if (per_sm < 1) {
+			return cudaErrorLaunchOutOfResources;
+		}
+		uint64_t grid = static_cast<uint64_t>(dev.sm_count) * per_sm;
+		const uint64_t want = ceil_div(num_halves, 8);
+		grid = grid < want ? grid : want;
+		kern<<<static_cast<unsigned>(grid), 256, 0, stream>>>(src, t_pre->folded, fold_mask, sector_mask, count, num_halves,
+		                                                     reinterpret_cast<uint32_t *>(bitmap), records, ends, stats);
+	}
 	auto bucket = probe_bucket_half_kernel<P>;
 	int bper_sm = 0;
 	e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bper_sm, bucket, 256, 0);
@@ -2981,92 +2898,12 @@ static cudaError_t launch_probe_folded_nw(const DeviceInfo &dev, const Src &src,
 	const uint64_t nblocks = ceil_div(num_segs, kScanBlock);
 	scan_blocks_kernel<<<static_cast<unsigned>(nblocks), 1024, 0, stream>>>(seg_offsets, num_segs, block_totals);
 	scan_totals_kernel<<<1, 1024, 0, stream>>>(block_totals, static_cast<uint32_t>(nblocks), found_out);
-	const uint64_t cwant = ceil_div((num_segs + 1) / 2, 8ull);
-	const uint64_t ccap = static_cast<uint64_t>(dev.sm_count) * 6;
-	compact_bitmap_kernel<<<static_cast<unsigned>(cwant < ccap ? cwant : ccap), 256, 0, stream>>>(
-	    reinterpret_cast<const uint32_t *>(bitmap), seg_offsets, block_totals, num_segs, sel_out, row_offset, translate);
+	launch_compact(dev, reinterpret_cast<const uint32_t *>(bitmap), seg_offsets, block_totals, num_segs, sel_out, row_offset,
+	               translate, stream);
 	if (launches) {
 		(*launches) += 1 + P + 4;
 	}
 	return cudaGetLastError();
-}
-template <class Src, int P, int MINB>
-static cudaError_t launch_probe_folded_direct(const DeviceInfo &dev, const Src &src, uint64_t count,
-                                              const uint64_t *words, uint64_t num_sectors, uint32_t *sel_out,
-                                              uint64_t *found_out, uint32_t row_offset, const uint32_t *translate,
-                                              void *scratch, cudaStream_t stream, int *launches) {
-	auto kern = probe_fold_direct_kernel<Src, P, MINB>;
-	int per_sm = 0;
-	cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 256, 0);
-	if (e != cudaSuccess) {
-		return e;
-	}
-	if (per_sm < 1) {
-		return cudaErrorLaunchOutOfResources;
-	}
-	const uint64_t num_segs = ceil_div(count, kSegRows);
-	const uint64_t num_halves = num_segs * 2;
-	uint64_t grid = static_cast<uint64_t>(dev.sm_count) * per_sm;
-	const uint64_t want = ceil_div(num_halves, 8);
-	grid = grid < want ? grid : want;
-	const PhasedLayout lay = phased_layout(count);
-	char *base = reinterpret_cast<char *>(scratch);
-	uint32_t *seg_offsets = reinterpret_cast<uint32_t *>(base);
-	uint32_t *block_totals = reinterpret_cast<uint32_t *>(base + lay.off_totals);
-	uint8_t *bitmap = reinterpret_cast<uint8_t *>(base + lay.off_hitbits);
-	char *extra = base + align_up(lay.bytes, 256);
-	uint16_t *ends = reinterpret_cast<uint16_t *>(extra);
-	uint2 *records = reinterpret_cast<uint2 *>(extra + align_up(num_halves * P * sizeof(uint16_t), 256));
-	kern<<<static_cast<unsigned>(grid), 256, 0, stream>>>(
-	    src, t_pre->folded, static_cast<uint32_t>(t_pre->sectors - 1), static_cast<uint32_t>(num_sectors - 1), count,
-	    num_halves, reinterpret_cast<uint32_t *>(bitmap), records, ends,
-	    reinterpret_cast<unsigned long long *>(t_pre->stats));
-	auto bucket = probe_bucket_half_kernel<P>;
-	int bper_sm = 0;
-	e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bper_sm, bucket, 256, 0);
-	if (e != cudaSuccess) {
-		return e;
-	}
-	uint64_t bgrid = static_cast<uint64_t>(dev.sm_count) * (bper_sm > 0 ? bper_sm : 1);
-	const uint64_t bwant = ceil_div(num_halves, 128);
-	bgrid = bgrid < bwant ? bgrid : bwant;
-	for (int s = 0; s < P; s++) {
-		bucket<<<static_cast<unsigned>(bgrid), 256, 0, stream>>>(records, ends, num_halves, words, static_cast<uint32_t>(s),
-		                                                        reinterpret_cast<uint32_t *>(bitmap));
-	}
-	count_segments_kernel<<<stream_grid(dev, num_segs, 256), 256, 0, stream>>>(
-	    reinterpret_cast<const uint4 *>(bitmap), num_segs, seg_offsets);
-	const uint64_t nblocks = ceil_div(num_segs, kScanBlock);
-	scan_blocks_kernel<<<static_cast<unsigned>(nblocks), 1024, 0, stream>>>(seg_offsets, num_segs, block_totals);
-	scan_totals_kernel<<<1, 1024, 0, stream>>>(block_totals, static_cast<uint32_t>(nblocks), found_out);
-	const uint64_t cwant = ceil_div((num_segs + 1) / 2, 8ull);
-	const uint64_t ccap = static_cast<uint64_t>(dev.sm_count) * 6;
-	compact_bitmap_kernel<<<static_cast<unsigned>(cwant < ccap ? cwant : ccap), 256, 0, stream>>>(
-	    reinterpret_cast<const uint32_t *>(bitmap), seg_offsets, block_totals, num_segs, sel_out, row_offset, translate);
-	if (launches) {
-		(*launches) += 1 + P + 4;
-	}
-	return cudaGetLastError();
-}
-template <class Src, int P>
-static cudaError_t launch_probe_folded(const DeviceInfo &dev, const Src &src, uint64_t count, const uint64_t *words,
-                                       uint64_t num_sectors, uint32_t *sel_out, uint64_t *found_out, uint32_t row_offset,
-                                       const uint32_t *translate, void *scratch, cudaStream_t stream, int *launches) {
-	static const int nw = [] { // warps per CTA (one CTA per SM): RPT_FOLD_WARPS = 16 | 24 | 32
-		const char *e = getenv("RPT_FOLD_WARPS");
-		const int v = e ? atoi(e) : 24;
-		return v == 16 || v == 32 ? v : 24;
-	}();
-	if (nw == 16) {
-		return launch_probe_folded_nw<Src, P, 16>(dev, src, count, words, num_sectors, sel_out, found_out, row_offset,
-		                                          translate, scratch, stream, launches);
-	}
-	if (nw == 32) {
-		return launch_probe_folded_nw<Src, P, 32>(dev, src, count, words, num_sectors, sel_out, found_out, row_offset,
-		                                          translate, scratch, stream, launches);
-	}
-	return launch_probe_folded_nw<Src, P, 24>(dev, src, count, words, num_sectors, sel_out, found_out, row_offset,
-	                                          translate, scratch, stream, launches);
 }
 
 static int probe_units() {
@@ -3089,34 +2926,10 @@ static cudaError_t launch_probe_src(const DeviceInfo &dev, const Src &src, uint6
 	}
 	if (t_pre != nullptr && prefilter_applicable(num_sectors) && t_pre->sectors <= kSliceSectors &&
 	    (t_gate == nullptr || t_gate->n == 0)) {
-		// folded pre-filter.  Flat key columns: probe_fold_kernel (half-segment staging, survivors only); generic
-		// sources: the 512-row partition kernel with the folded test in front (slice 0 is a bucket like the others,
-		// so that kernel touches the folded filter only).  RPT_FOLD_KERNEL=0 sends flat columns there too.
-		static const int fold_kernel_choice = [] { // 0: partition kernel, 1: bulk-copy staging, 2/3: no shared memory
-			const char *e = getenv("RPT_FOLD_KERNEL");
-			return e ? atoi(e) : 1;
-		}();
-		if (fold_kernel_choice >= 2) {
-			if (num_sectors == 4 * kSliceSectors) {
-				return fold_kernel_choice == 2 ? launch_probe_folded_direct<Src, 4, 4>(RPT_PROBE_ARGS)
-				                               : launch_probe_folded_direct<Src, 4, 3>(RPT_PROBE_ARGS);
-			}
-			return fold_kernel_choice == 2 ? launch_probe_folded_direct<Src, 8, 4>(RPT_PROBE_ARGS)
-			                               : launch_probe_folded_direct<Src, 8, 3>(RPT_PROBE_ARGS);
-		}
-		if constexpr (Src::kStageable) {
-			const bool half_kernel = fold_kernel_choice == 1;
-			if (half_kernel) {
-				if (num_sectors == 4 * kSliceSectors) {
-					return launch_probe_folded<Src, 4>(RPT_PROBE_ARGS);
-				}
-				return launch_probe_folded<Src, 8>(RPT_PROBE_ARGS);
-			}
-		}
 		if (num_sectors == 4 * kSliceSectors) {
-			return launch_probe_partitioned<Src, 4, static_cast<int>(kSliceShift), false, true>(RPT_PROBE_ARGS);
+			return launch_probe_folded<Src, 4>(RPT_PROBE_ARGS);
 		}
-		return launch_probe_partitioned<Src, 8, static_cast<int>(kSliceShift), false, true>(RPT_PROBE_ARGS);
+		return launch_probe_folded<Src, 8>(RPT_PROBE_ARGS);
 	}
 	const int slices64 = smem ? 0 : partition_choice<Src>(num_sectors);
 	if constexpr (Src::kStageable && Src::kKeyBytes == 8 && !Src::kNullable) { // experiment variants: flat 8-byte keys only
@@ -3232,10 +3045,7 @@ cudaError_t launch_bitmap_to_sel(const DeviceInfo &dev, uint64_t count, uint32_t
 	const uint64_t nblocks = ceil_div(num_segs, kScanBlock);
 	scan_blocks_kernel<<<static_cast<unsigned>(nblocks), 1024, 0, stream>>>(seg_offsets, num_segs, block_totals);
 	scan_totals_kernel<<<1, 1024, 0, stream>>>(block_totals, static_cast<uint32_t>(nblocks), found_out);
-	const uint64_t cwant = ceil_div((num_segs + 1) / 2, 8ull);
-	const uint64_t ccap = static_cast<uint64_t>(dev.sm_count) * 6;
-	compact_bitmap_kernel<<<static_cast<unsigned>(cwant < ccap ? cwant : ccap), 256, 0, stream>>>(
-	    bitmap, seg_offsets, block_totals, num_segs, sel_out, row_offset, nullptr);
+	launch_compact(dev, bitmap, seg_offsets, block_totals, num_segs, sel_out, row_offset, nullptr, stream);
 	if (launches) {
 		(*launches) += 4;
 	}

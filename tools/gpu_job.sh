@@ -128,27 +128,33 @@ partpipe)   # chunk-pipelined partitioned probe (code as of commit 0fbcbed, remo
 	done
 	cat $out
 	;;
-prefilter)  # folded pre-filter: its tests, then on/off sweeps at config 2 (1 %, 10 %, 50 %) and at 512 MiB: prefilter <tag>
+prefilter)  # folded pre-filter: the whole GPU suite, then on/off sweeps at config 2 (1 %, 10 %, 50 %), 512 MiB, other key types: prefilter <tag>
 	tag=${1:-r2p}
-	timeout 1200 python -m pytest tests/test_gpu_prefilter.py -x -q > gpurun_out/tests_prefilter_${tag}.log 2>&1
-	echo "prefilter tests rc=$?" | tee -a gpurun_out/tests_prefilter_${tag}.log
-	tail -25 gpurun_out/tests_prefilter_${tag}.log
+	timeout 2400 python -m pytest tests -m gpu -x -q > gpurun_out/tests_${tag}.log 2>&1
+	echo "tests rc=$?" | tee -a gpurun_out/tests_${tag}.log
+	tail -5 gpurun_out/tests_${tag}.log
 	out=gpurun_out/prefilter_${tag}.txt
 	: > $out
-	for knobs in "" "RPT_FOLD_KERNEL=2" "RPT_FOLD_KERNEL=3" "RPT_FOLD_KERNEL=0" "RPT_FOLD_MIB=32" "RPT_FOLD_KERNEL=2 RPT_FOLD_MIB=32" "RPT_PREFILTER=0"; do
+	for knobs in "" "RPT_PREFILTER=0"; do
 		for ppm in 100000 10000 500000; do
-			case "$knobs" in RPT_FOLD_KERNEL=[03]*|RPT_FOLD_MIB*|*MIB=32) [ $ppm = 100000 ] || continue;; esac
 			echo "== knobs: ${knobs:-default} ppm=$ppm" >> $out
-			env $knobs RPT_PREFILTER_MAX_ALIVE=2 SWEEP_PPM=$ppm timeout -s KILL 300 python tools/probe_sweep.py 1e9 5 1e8 >> $out 2>&1
+			env $knobs SWEEP_PPM=$ppm timeout -s KILL 300 python tools/probe_sweep.py 1e9 5 1e8 >> $out 2>&1
 			echo "rc=$?" >> $out
 		done
 	done
-	for knobs in "" "RPT_PREFILTER=0" "RPT_PREFILTER=2"; do
+	for knobs in "" "RPT_PREFILTER=0"; do
 		echo "== knobs: ${knobs:-default} 512 MiB" >> $out
 		env $knobs timeout -s KILL 300 python tools/probe_sweep.py 1e9 3 1.8e8,3e8 >> $out 2>&1
 		echo "rc=$?" >> $out
 	done
-	grep -v "^rc=0" $out
+	for typ in two int32 varchar; do
+		for knobs in "" "RPT_PREFILTER=0"; do
+			echo "== knobs: ${knobs:-default} type=$typ" >> $out
+			env $knobs SWEEP_TYPE=$typ timeout -s KILL 400 python tools/probe_sweep.py 4e8 3 1e8 >> $out 2>&1
+			echo "rc=$?" >> $out
+		done
+	done
+	grep -v "^rc=0\|^# m=" $out
 	cmd="python tools/probe_sweep.py 1e9 1 1e8"
 	timeout 900 ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum --clock-control none -c 200 \
 		--csv --log-file gpurun_out/launches_prefilter_${tag}.csv $cmd > gpurun_out/ncu_prefilter_${tag}.log 2>&1

@@ -58,6 +58,11 @@ for n in cases:
         dk32, dp32 = (dk & 0x7fffffff).to(torch.int32), (dp & 0x7fffffff).to(torch.int32)
         torch.cuda.synchronize()
         kc, pc = rpt.device_col(dk32, rpt.INT32), rpt.device_col(dp32, rpt.INT32)
+    elif ktype == "two":  # two key columns (generic source): (k, low 31 bits of k)
+        dk32, dp32 = (dk & 0x7fffffff).to(torch.int32), (dp & 0x7fffffff).to(torch.int32)
+        torch.cuda.synchronize()
+        kc = [rpt.device_col(dk, rpt.INT64), rpt.device_col(dk32, rpt.INT32)]
+        pc = [rpt.device_col(dp, rpt.INT64), rpt.device_col(dp32, rpt.INT32)]
     elif ktype == "varchar":
         ko, kb, kt = decimal_text(dk)
         po, pb, pt = decimal_text(dp)
@@ -86,7 +91,7 @@ for n in cases:
     F = bf.num_sectors * 8
     bm, pm = ev[0].elapsed_time(ev[1]) / reps, ev[2].elapsed_time(ev[3]) / reps
     found = int(dfound.item())
-    algo = (4 if ktype == "int32" else 8) * m + 4 * found + F
+    algo = (4 if ktype == "int32" else (12 if ktype == "two" else 8)) * m + 4 * found + F
     if ktype == "varchar":
         algo = 4 * (m + 1) + pt + 4 * found + F  # offsets + string bytes replace 8·m
     # whole steps (reset + build + probe): what bench.py times; includes the fold of a pre-filtered probe
