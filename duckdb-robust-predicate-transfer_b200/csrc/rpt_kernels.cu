@@ -2445,11 +2445,18 @@ size_t probe_scratch_bytes(uint64_t count, uint64_t num_sectors, bool prefilter)
 	if (count <= kFusedMaxKeys) {
 		return (ceil_div(count, kProbeTileKeys) + 2) * sizeof(uint64_t); // look-back descriptors + ticket
 	}
-	if (prefilter && prefilter_applicable(num_sectors)) {
-		return align_up(phased_layout(count).bytes, 256) + folded_scratch_bytes(count, num_sectors);
-	}
 	const int slices = partition_slices(num_sectors);
-	return align_up(phased_layout(count).bytes, 256) + (slices ? partition_scratch_bytes(count, num_sectors, slices) : 0);
+	size_t extra = slices ? partition_scratch_bytes(count, num_sectors, slices) : 0;
+	if (prefilter_applicable(num_sectors)) {
+		// One size for the pre-filtered and the plain probe of a filter, whichever a call takes: a handle whose probes
+		// alternate between them (feedback, rpt_bf_set_prefilter) then asks the stream-ordered pool for the same block
+		// every time.  With two sizes (8.03 / 8.33 GB per 10^9 rows) a long run of one followed by the other left calls
+		// 20 ms slower for dozens of calls (bench.py after its sustained spin: profiles/bench_r2y.json).
+		const size_t folded = folded_scratch_bytes(count, num_sectors);
+		extra = extra > folded ? extra : folded;
+	}
+	(void)prefilter;
+	return align_up(phased_layout(count).bytes, 256) + extra;
 }
 
 template <class Src, bool AGG, bool MM>
