@@ -89,6 +89,11 @@ _SIGNATURES = {
     "rpt_bf_peer_open": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int]),
     "rpt_bf_peer_merge_phase": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p]),
     "rpt_bf_peer_close": (C.c_int, [C.c_void_p]),
+    "rpt_bf_peer_flags_export": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "rpt_bf_peer_flags_open": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int]),
+    "rpt_bf_peer_allreduce": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p]),
+    "rpt_bf_peer_release": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "rpt_bf_peer_any_data": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(C.c_int)]),
     "rpt_bf_allreduce_or": (C.c_int, [C.POINTER(C.c_void_p), C.c_int]),
     "rpt_abf_log_blocks_for_rows": (C.c_int, [C.c_uint64, C.POINTER(C.c_int)]),
     "rpt_abf_create": (C.c_int, [C.POINTER(C.c_void_p), C.c_uint64, C.c_int]),
@@ -430,6 +435,27 @@ class PTBloomFilter:
 
     def PeerClose(self):
         _check(lib().rpt_bf_peer_close(self._h))
+
+    # the whole OR-allreduce owned by the library (barrier words + stream memory operations, rpt_gpu.h)
+    def PeerFlagsExport(self):
+        buf = C.create_string_buffer(64)
+        _check(lib().rpt_bf_peer_flags_export(self._h, buf))
+        return buf.raw
+
+    def PeerFlagsOpen(self, handles, rank):
+        blob = b"".join(handles)
+        _check(lib().rpt_bf_peer_flags_open(self._h, blob, len(handles), rank))
+
+    def PeerAllreduce(self, has_local_data, stream=None):
+        _check(lib().rpt_bf_peer_allreduce(self._h, int(bool(has_local_data)), stream))
+
+    def PeerRelease(self, stream=None):
+        _check(lib().rpt_bf_peer_release(self._h, stream))
+
+    def PeerAnyData(self, stream=None):
+        out = C.c_int(0)
+        _check(lib().rpt_bf_peer_any_data(self._h, stream, C.byref(out)))
+        return bool(out.value)
 
 
 class BlockedBloomFilter:

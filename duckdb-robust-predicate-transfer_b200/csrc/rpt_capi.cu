@@ -5,6 +5,7 @@
 // staging host key columns through chunked, double-buffered H2D/D2H pipelines, and launching the
 // kernels of rpt_kernels.cu.  There is no CPU fallback anywhere in this file: every compute entry
 // point ends in a kernel launch or fails.
+#include <cuda.h>
 #include <cuda_runtime.h>
 
 #include <atomic>
@@ -176,6 +177,14 @@ struct rpt_bf {
 	std::vector<uint64_t *> peer_words;
 	std::vector<bool> peer_ipc;
 	int peer_rank = -1;
+	// library-owned collective (rpt_bf_peer_allreduce): 3 phases × 16 ranks of 32-bit barrier words in device memory
+	// (phase 0 "my partial filter is complete" + has-data bit, 1 "my slice is reduced", 2 "I have pulled every slice");
+	// peers store into my words over their IPC mappings, I wait on my own
+	uint32_t *sync_flags = nullptr;
+	std::vector<uint32_t *> peer_flags; // [rank] → that rank's flag block (mine included)
+	std::vector<bool> peer_flags_ipc;
+	uint32_t sync_epoch = 0;
+	bool sync_release_pending = false;
 };
 
 struct DeviceGuard {
@@ -694,6 +703,14 @@ int rpt_bf_destroy(rpt_bf_t *bf) {
 	}
 	DeviceGuard guard(bf->dev.device);
 	rpt_bf_peer_close(bf);
+	for (size_t r = 0; r < bf->peer_flags.size(); r++) {
+		if (bf->peer_flags_ipc[r] && bf->peer_flags[r]) {
+			cudaIpcCloseMemHandle(bf->peer_flags[r]);
+		}
+	}
+	if (bf->sync_flags) {
+		cudaFree(bf->sync_flags);
+	}
 	if (bf->words) {
 		cudaFree(bf->words);
 	}
@@ -1838,6 +1855,183 @@ int rpt_bf_peer_close(rpt_bf_t *bf) {
 	bf->peer_words.clear();
 	bf->peer_ipc.clear();
 	bf->peer_rank = -1;
+	return 0;
+}
+
+// ---- the whole OR-allreduce between processes, owned by the library ---------------------------------------------
+// Barriers are 32-bit words in device memory: a rank signals by storing the merge's epoch into its slot of every
+// peer's flag block (one tiny kernel over the IPC mappings, release at system scope) and waits for its own slots with
+// cuStreamWaitValue32 (a stream memory operation: no kernel runs, nothing polls; a one-CTA polling kernel stands in
+// where the driver entry point is missing).  Everything is enqueued on the caller's stream; the host never waits.
+constexpr int kSyncRanks = 16, kSyncPhases = 3;
+
+int rpt_bf_peer_flags_export(rpt_bf_t *bf, void *handle64) {
+	if (!bf || !handle64) {
+		return set_error("null argument");
+	}
+	RPT_GUARD(bf);
+	if (!bf->sync_flags) {
+		RPT_CUDA(cudaMalloc(&bf->sync_flags, kSyncRanks * kSyncPhases * sizeof(uint32_t)));
+		RPT_CUDA(cudaMemset(bf->sync_flags, 0, kSyncRanks * kSyncPhases * sizeof(uint32_t)));
+	}
+	cudaIpcMemHandle_t h;
+	RPT_CUDA(cudaIpcGetMemHandle(&h, bf->sync_flags));
+	memcpy(handle64, &h, sizeof(h));
+	return 0;
+}
+
+static int rpt_bf_peer_flags_open_body(rpt_bf_t *bf, const void *handles64, int nranks, int rank) {
+	if (!bf || !handles64) {
+		return set_error("null argument");
+	}
+	if (nranks < 1 || nranks > kSyncRanks || rank < 0 || rank >= nranks) {
+		return set_error("nranks must be in [1,16] and rank in [0,nranks)");
+	}
+	if (!bf->sync_flags) {
+		return set_error("rpt_bf_peer_flags_export has not been called on this handle");
+	}
+	if (!bf->peer_flags.empty()) {
+		return set_error("the flag blocks of this handle are already open");
+	}
+	RPT_GUARD(bf);
+	bf->peer_flags.assign(nranks, nullptr);
+	bf->peer_flags_ipc.assign(nranks, false);
+	for (int r = 0; r < nranks; r++) {
+		if (r == rank) {
+			bf->peer_flags[r] = bf->sync_flags;
+			continue;
+		}
+		cudaIpcMemHandle_t h;
+		memcpy(&h, reinterpret_cast<const uint8_t *>(handles64) + 64 * r, sizeof(h));
+		void *p = nullptr;
+		RPT_CUDA(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+		bf->peer_flags[r] = reinterpret_cast<uint32_t *>(p);
+		bf->peer_flags_ipc[r] = true;
+	}
+	return 0;
+}
+int rpt_bf_peer_flags_open(rpt_bf_t *bf, const void *handles64, int nranks, int rank) {
+	return guarded([&] { return rpt_bf_peer_flags_open_body(bf, handles64, nranks, rank); });
+}
+
+typedef CUresult (*WaitValue32Fn)(CUstream, CUdeviceptr, cuuint32_t, unsigned int);
+static WaitValue32Fn wait_value32() {
+	static const WaitValue32Fn fn = [] {
+		if (getenv("RPT_SYNC_POLL") != nullptr) { // force the polling kernel (tests)
+			return static_cast<WaitValue32Fn>(nullptr);
+		}
+		void *p = nullptr;
+		cudaDriverEntryPointQueryResult st;
+		if (cudaGetDriverEntryPoint("cuStreamWaitValue32", &p, cudaEnableDefault, &st) != cudaSuccess ||
+		    st != cudaDriverEntryPointSuccess) {
+			cudaGetLastError();
+			p = nullptr;
+		}
+		return reinterpret_cast<WaitValue32Fn>(p);
+	}();
+	return fn;
+}
+// my slot in every peer's block of `phase` := value
+static int sync_signal(rpt_bf *bf, int phase, uint32_t value, cudaStream_t s) {
+	FlagList dst;
+	dst.n = 0;
+	const int n = static_cast<int>(bf->peer_flags.size());
+	for (int r = 0; r < n; r++) {
+		if (r != bf->peer_rank) {
+			dst.p[dst.n++] = bf->peer_flags[r] + phase * kSyncRanks + bf->peer_rank;
+		}
+	}
+	RPT_CUDA(launch_signal_flags(dst, value, s));
+	bf->launches += 1;
+	return 0;
+}
+// every peer's slot in my block of `phase` >= value (epochs only grow; bit 0 of a phase-0 word is the has-data flag)
+static int sync_wait(rpt_bf *bf, int phase, uint32_t value, cudaStream_t s) {
+	const int n = static_cast<int>(bf->peer_flags.size());
+	uint32_t *mine = bf->sync_flags + phase * kSyncRanks;
+	if (WaitValue32Fn wait = wait_value32()) {
+		for (int r = 0; r < n; r++) {
+			if (r != bf->peer_rank) {
+				const CUresult rc = wait(reinterpret_cast<CUstream>(s), reinterpret_cast<CUdeviceptr>(mine + r), value,
+				                         CU_STREAM_WAIT_VALUE_GEQ);
+				if (rc != CUDA_SUCCESS) {
+					return set_error("cuStreamWaitValue32 failed (%d)", static_cast<int>(rc));
+				}
+			}
+		}
+		return 0;
+	}
+	RPT_CUDA(launch_wait_flags(mine, n, bf->peer_rank, value, s));
+	bf->launches += 1;
+	return 0;
+}
+
+static int rpt_bf_peer_allreduce_body(rpt_bf_t *bf, int has_local_data, rpt_stream_t stream) {
+	if (!bf) {
+		return set_error("null filter handle");
+	}
+	if (bf->peer_rank < 0 || bf->peer_flags.size() != bf->peer_words.size()) {
+		return set_error("rpt_bf_peer_open and rpt_bf_peer_flags_open must both have been called with the same ranks");
+	}
+	RPT_GUARD(bf);
+	cudaStream_t s = pick_stream(bf, stream);
+	if (bf->sync_release_pending) { // the peers of the previous merge have pulled my slice before I touch the words again
+		RPT_TRY(sync_wait(bf, 2, bf->sync_epoch << 1, s));
+		bf->sync_release_pending = false;
+	}
+	const uint32_t v = ++bf->sync_epoch << 1;
+	RPT_TRY(sync_signal(bf, 0, v | (has_local_data ? 1u : 0u), s)); // my partial filter is complete
+	RPT_TRY(sync_wait(bf, 0, v, s));
+	RPT_TRY(peer_merge_range(bf, 0, 0, bf->num_sectors, s));        // my slice |= every peer's copy of it
+	RPT_TRY(sync_signal(bf, 1, v, s));                              // my slice is reduced
+	RPT_TRY(sync_wait(bf, 1, v, s));
+	RPT_TRY(peer_merge_range(bf, 1, 0, bf->num_sectors, s));        // pull the other ranks' reduced slices
+	RPT_TRY(sync_signal(bf, 2, v, s));                              // I have pulled: my peers may overwrite theirs
+	bf->sync_release_pending = true; // due before MY next mutation of the words: rpt_bf_peer_release
+	if (has_local_data) {
+		bf->has_data.store(1);
+	}
+	return 0;
+}
+int rpt_bf_peer_allreduce(rpt_bf_t *bf, int has_local_data, rpt_stream_t stream) {
+	return guarded([&] { return rpt_bf_peer_allreduce_body(bf, has_local_data, stream); });
+}
+
+int rpt_bf_peer_release(rpt_bf_t *bf, rpt_stream_t stream) {
+	if (!bf) {
+		return set_error("null filter handle");
+	}
+	if (!bf->sync_release_pending) {
+		return 0;
+	}
+	RPT_GUARD(bf);
+	RPT_TRY(sync_wait(bf, 2, bf->sync_epoch << 1, pick_stream(bf, stream)));
+	bf->sync_release_pending = false;
+	return 0;
+}
+
+int rpt_bf_peer_any_data(rpt_bf_t *bf, rpt_stream_t stream, int *out) {
+	if (!bf || !out) {
+		return set_error("null argument");
+	}
+	if (bf->peer_flags.empty()) {
+		return set_error("rpt_bf_peer_flags_open has not been called");
+	}
+	RPT_GUARD(bf);
+	cudaStream_t s = pick_stream(bf, stream);
+	uint32_t host[kSyncRanks];
+	RPT_CUDA(cudaMemcpyAsync(host, bf->sync_flags, sizeof(host), cudaMemcpyDeviceToHost, s));
+	RPT_CUDA(cudaStreamSynchronize(s));
+	int any = bf->has_data.load();
+	for (size_t r = 0; r < bf->peer_flags.size(); r++) {
+		if (static_cast<int>(r) != bf->peer_rank && (host[r] >> 1) == bf->sync_epoch) {
+			any |= static_cast<int>(host[r] & 1u);
+		}
+	}
+	if (any) {
+		bf->has_data.store(1);
+	}
+	*out = any;
 	return 0;
 }
 

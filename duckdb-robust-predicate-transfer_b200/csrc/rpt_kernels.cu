@@ -1625,6 +1625,8 @@ __global__ void __launch_bounds__(NWARPS * 32, 1)
 					pos = static_cast<uint32_t>((up ? base[1] : base[0]) >> (2u * shr)) & 0xffffu;
 				}
 				if (one) {
+					// (holding a lane's first two survivors back and storing them with two warp-wide instructions instead
+					// of eight nearly empty ones was measured: 6.46 against 6.26 ms per 10^9 keys — not adopted)
 					const uint32_t row8 = lane * 8u + (((i / KPU + unit_rot) & (LU - 1)) * KPU) + (i % KPU);
 					stage[pos + rank] =
 					    make_uint2((sector & ((1u << SHIFT) - 1u)) | (row8 << SHIFT), static_cast<uint32_t>(hh[i] >> 32));
@@ -3077,6 +3079,38 @@ cudaError_t launch_or_parts(const DeviceInfo &dev, uint64_t *words, const uint64
 	const uint64_t nvec = num_sectors >> 1;
 	or_parts_kernel<<<stream_grid(dev, nvec, 256), 256, 0, stream>>>(
 	    reinterpret_cast<ulonglong2 *>(words), reinterpret_cast<const ulonglong2 *>(parts), nvec, nparts);
+	return cudaGetLastError();
+}
+
+// Cross-process barrier words of the library-owned merge (rpt_bf_peer_allreduce): one thread per peer stores `value`
+// into that peer's flag word with system-scope release semantics (everything this GPU wrote before — earlier kernels
+// on the stream — is visible to whoever sees the flag), over the peer's IPC mapping.
+__global__ void signal_flags_kernel(const FlagList dst, const uint32_t value) {
+	if (threadIdx.x < static_cast<unsigned>(dst.n)) {
+		__threadfence_system();
+		asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(dst.p[threadIdx.x]), "r"(value) : "memory");
+	}
+}
+// Fallback of cuStreamWaitValue32 (driver entry point not available): one thread per flag polls its LOCAL word until
+// it is >= value.  Peers signal before they wait, so the poll cannot deadlock; it occupies one small CTA.
+__global__ void wait_flags_kernel(const uint32_t *flags, const int n, const int skip, const uint32_t value) {
+	const int t = threadIdx.x;
+	if (t < n && t != skip) {
+		uint32_t v;
+		do {
+			asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(flags + t) : "memory");
+		} while (static_cast<int32_t>(v - value) < 0);
+	}
+}
+cudaError_t launch_signal_flags(const FlagList &dst, uint32_t value, cudaStream_t stream) {
+	if (dst.n == 0) {
+		return cudaSuccess;
+	}
+	signal_flags_kernel<<<1, 32, 0, stream>>>(dst, value);
+	return cudaGetLastError();
+}
+cudaError_t launch_wait_flags(const uint32_t *flags, int n, int skip, uint32_t value, cudaStream_t stream) {
+	wait_flags_kernel<<<1, 32, 0, stream>>>(flags, n, skip, value);
 	return cudaGetLastError();
 }
 

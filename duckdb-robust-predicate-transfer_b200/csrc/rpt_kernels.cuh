@@ -102,6 +102,15 @@ struct PtrList {
 cudaError_t launch_or_ptrs(const DeviceInfo &dev, uint64_t *words, const PtrList &srcs, uint64_t off, uint64_t len,
                            cudaStream_t stream);
 
+// barrier flags of the library-owned peer merge (rpt_bf_peer_allreduce): store `value` into every listed (peer) word
+struct FlagList {
+	uint32_t *p[16];
+	int n;
+};
+cudaError_t launch_signal_flags(const FlagList &dst, uint32_t value, cudaStream_t stream);
+// poll flags[t] (t < n, t != skip) until each is >= value (fallback of cuStreamWaitValue32)
+cudaError_t launch_wait_flags(const uint32_t *flags, int n, int skip, uint32_t value, cudaStream_t stream);
+
 // LookupOne on pre-hashed values (BFTableFilter::FilterValue / CheckStatistics)
 cudaError_t launch_lookup_hashes(const uint64_t *words, uint64_t num_sectors, const uint64_t *hashes, uint64_t count,
                                  uint8_t *hits, cudaStream_t stream);

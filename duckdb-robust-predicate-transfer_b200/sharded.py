@@ -69,6 +69,10 @@ class ShardedBloomFilter:
         self._peer_open_for = None
         self.merged = False
         self._release_pending = False  # peers may still be pulling my reduced slice (see _release)
+        # The library owns the whole collective (rpt_bf_peer_allreduce: barrier words in device memory, stream memory
+        # operations) when the engine has it; RPT_MERGE_LIB=0 keeps the phase-by-phase form with NCCL barriers below.
+        self._lib_merge = hasattr(self.bf, "PeerAllreduce") and os.environ.get("RPT_MERGE_LIB", "1") != "0"
+        self._flags_open = False
 
     # -- plumbing ------------------------------------------------------------------------------------
     def _scalar_device(self):
@@ -113,7 +117,11 @@ class ShardedBloomFilter:
         if getattr(self, "_side_pending", False):  # an overlapped merge may still be pulling slices on its stream
             torch.cuda.current_stream().wait_stream(self._merge_stream)
             self._side_pending = False
-        self.device_barrier()
+        if getattr(self, "_lib_release", False):   # the merge was the library's: so is its last barrier
+            self._lib_release = False
+            self.bf.PeerRelease(torch.cuda.current_stream().cuda_stream)
+        else:
+            self.device_barrier()
         if stream is None:
             torch.cuda.current_stream().synchronize()
 
@@ -201,6 +209,24 @@ class ShardedBloomFilter:
             # profiles/merge_overlap_r2.md).
             overlap = defer_release and nslices > 1 and hasattr(self.bf, "PeerMergeRange") and \
                 os.environ.get("RPT_MERGE_OVERLAP", "0") == "1"
+            if self._lib_merge and not overlap and self._any_data is None:
+                if not self._flags_open:  # once per handle: the barrier words do not move when the filter is re-sized
+                    blob = torch.frombuffer(bytearray(self.bf.PeerFlagsExport()), dtype=torch.uint8).cuda(self.device)
+                    allb = torch.empty(self.world * 64, dtype=torch.uint8, device=blob.device)
+                    self.dist.all_gather_into_tensor(allb, blob, group=self.group)
+                    raw = allb.cpu().numpy().tobytes()
+                    self.bf.PeerFlagsOpen([raw[64 * r:64 * (r + 1)] for r in range(self.world)], self.rank)
+                    self._flags_open = True
+                run_stream = stream if stream is not None else torch.cuda.current_stream().cuda_stream
+                self.bf.PeerAllreduce(has_local, run_stream)
+                # only a rank without rows of its own has to wait to learn whether anybody had some
+                self._any_data = True if has_local else self.bf.PeerAnyData(run_stream)
+                if defer_release:
+                    self._release_pending = True
+                    self._lib_release = True
+                else:
+                    self.bf.PeerRelease(run_stream)
+                return
             if overlap:
                 # Slice by slice on a side stream; the probe that follows on the main stream waits per slice
                 # (rpt_bf_set_slice_events): its partition kernel needs slice 0 only, so the merge of slices 1.. is

@@ -247,6 +247,21 @@ RPT_API int rpt_bf_ipc_export(const rpt_bf_t *bf, void *handle64);
 RPT_API int rpt_bf_peer_open(rpt_bf_t *bf, const void *handles64, int nranks, int rank);
 RPT_API int rpt_bf_peer_merge_phase(rpt_bf_t *bf, int phase, rpt_stream_t stream);
 RPT_API int rpt_bf_peer_close(rpt_bf_t *bf);
+/* The same OR-allreduce as ONE call that owns its barriers (no counterpart in the reference).  Every
+ * rank exports a small block of barrier words (rpt_bf_peer_flags_export, once per handle), the handles are
+ * exchanged like the filters' (rpt_bf_peer_flags_open), and rpt_bf_peer_allreduce enqueues the whole collective on
+ * `stream`: signal "my partial filter is complete" (+ has_local_data) → wait for every peer → reduce-scatter-OR of
+ * my slice over NVLink → signal → wait → pull the peers' reduced slices → signal "pulled".  Signals are stores into
+ * the peers' words over the IPC mappings, waits are stream memory operations (cuStreamWaitValue32) on the rank's own
+ * words: no NCCL call, no host synchronisation, nothing polls.  The last barrier ("everybody has pulled my slice")
+ * is not needed by the probes that follow; it is taken by the next rpt_bf_peer_allreduce or by rpt_bf_peer_release,
+ * which the caller invokes before it changes the words again (rpt_bf_reset / rpt_bf_insert).  rpt_bf_peer_any_data
+ * (synchronises `stream`) tells whether any rank held data — PTBloomFilter::IsEmpty of the merged filter. */
+RPT_API int rpt_bf_peer_flags_export(rpt_bf_t *bf, void *handle64);
+RPT_API int rpt_bf_peer_flags_open(rpt_bf_t *bf, const void *handles64, int nranks, int rank);
+RPT_API int rpt_bf_peer_allreduce(rpt_bf_t *bf, int has_local_data, rpt_stream_t stream);
+RPT_API int rpt_bf_peer_release(rpt_bf_t *bf, rpt_stream_t stream);
+RPT_API int rpt_bf_peer_any_data(rpt_bf_t *bf, rpt_stream_t stream, int *out);
 /* The same two phases restricted to the sectors [first_sector, first_sector + nsectors) (both even): the merge can
  * then proceed slice by slice on a side stream while the probe already runs — see rpt_bf_set_slice_events. */
 RPT_API int rpt_bf_peer_merge_range(rpt_bf_t *bf, int phase, uint64_t first_sector, uint64_t nsectors,
