@@ -222,3 +222,53 @@ def test_other_key_sources(rpt, oracle, torch_cuda):
     assert np.array_equal(sel.cpu().numpy().view(np.uint32),
                           oracle.probe(words, [rpt.host_varchar_col(poffs, pblob)], m))
     bf.close()
+
+
+def test_concurrent_probes_share_one_fold(rpt, oracle, torch_cuda):
+    """Eight host threads probe one large filter at the same time, each on its own stream (the reference's
+    ExecuteInternal threading contract): the first one to arrive folds the filter, the others wait for the fold's
+    event; every thread gets the selection vector of the plain path."""
+    import threading
+    torch = torch_cuda
+    n = 4_000_000
+    keys = synth_build_keys(0, n)
+    bf = rpt.PTBloomFilter(0).Initialize(EST_256)
+    bf.Insert(rpt.host_col(keys), n)
+    m = (1 << 22) + 99
+    probes, cols, want = [], [], []
+    for t in range(8):
+        p = synth_probe_keys(t * m, m, n, 200000)
+        d = torch.from_numpy(p.view(np.int64)).cuda()
+        probes.append(d)
+        cols.append(rpt.device_col(d, rpt.INT64))
+    bf.SetPrefilter(0)
+    for t in range(8):
+        want.append(probe_device(torch, bf, cols[t], m))
+    bf.SetPrefilter(1)
+    bf.Insert(rpt.host_col(keys[:1000]), 1000)  # same words, new version: the fold has to be made again
+    torch.cuda.synchronize()
+    got, errors = [None] * 8, []
+
+    def work(t):
+        try:
+            s = torch.cuda.Stream()
+            dsel = torch.empty(m, dtype=torch.int32, device="cuda")
+            dfound = torch.zeros(1, dtype=torch.int64, device="cuda")
+            torch.cuda.synchronize()
+            for _ in range(3):
+                bf.LookupSelDevice(cols[t], m, dsel, dfound, s.cuda_stream)
+            s.synchronize()
+            got[t] = dsel[:int(dfound.item())].clone()
+        except Exception as e:  # noqa: BLE001 - reported below
+            errors.append(repr(e))
+
+    threads = [threading.Thread(target=work, args=(t,)) for t in range(8)]
+    for th in threads:
+        th.start()
+    for th in threads:
+        th.join()
+    assert not errors, errors
+    assert bf.PrefilterInfo()[0] == 1
+    for t in range(8):
+        assert got[t].shape == want[t].shape and bool((got[t] == want[t]).all()), t
+    bf.close()
