@@ -1634,6 +1634,8 @@ __global__ void __launch_bounds__(NWARPS * 32, 1)
 			}
 			__syncwarp();
 			{
+				// (copying every slice's run to its own 64-byte-aligned start — to save the bucket kernels the DRAM atom
+				// a misaligned run costs — makes this kernel pay more than they save: 6.64 against 6.26 ms per 10^9 keys)
 				uint2 *dv = records + half * kHalfRows;
 				for (uint32_t j = lane; j < run; j += 32u) {
 					st_stream_v2(dv + j, stage[j], pol_keys);
