@@ -164,7 +164,8 @@ struct rpt_bf {
 	uint64_t *fold_stats_dev = nullptr;  // [rows, survivors]
 	uint64_t *fold_stats_host = nullptr; // pinned copy
 	cudaEvent_t fold_stats_ev = nullptr;
-	bool fold_stats_pending = false;
+	bool fold_stats_pending = false;     // a probe is counting (or about to); its counters are not on the host yet
+	bool fold_stats_recorded = false;    // ... and fold_stats_ev has been recorded behind that probe's kernels
 	double fold_alive = -1.0;            // survivors / rows of the last measured probe (< 0: none)
 	int fold_holdoff = 0;                // large probes left to run without the pre-filter
 	// fused column range (rpt_bf_minmax_*)
@@ -1128,7 +1129,7 @@ static int ensure_prefilter(rpt_bf *bf, uint64_t count, cudaStream_t s, Prefilte
 	const double max_pass = prefilter_max_pass();
 	std::lock_guard<std::mutex> lock(bf->fold_mu);
 	// feedback of an earlier pre-filtered probe, once its counters have arrived
-	if (bf->fold_stats_pending && cudaEventQuery(bf->fold_stats_ev) == cudaSuccess) {
+	if (bf->fold_stats_pending && bf->fold_stats_recorded && cudaEventQuery(bf->fold_stats_ev) == cudaSuccess) {
 		bf->fold_stats_pending = false;
 		const uint64_t rows = bf->fold_stats_host[0], alive = bf->fold_stats_host[1];
 		if (rows >= (1ULL << 20) && alive <= rows) {
@@ -1210,6 +1211,7 @@ static int ensure_prefilter(rpt_bf *bf, uint64_t count, cudaStream_t s, Prefilte
 			RPT_CUDA(cudaMemsetAsync(bf->fold_stats_dev, 0, 2 * sizeof(uint64_t), s));
 			out->stats = bf->fold_stats_dev;
 			bf->fold_stats_pending = true; // until prefilter_measured's event has fired
+			bf->fold_stats_recorded = false;
 			*measure = true;
 		}
 		*use = true;
@@ -1221,6 +1223,7 @@ static int prefilter_measured(rpt_bf *bf, cudaStream_t s) {
 	std::lock_guard<std::mutex> lock(bf->fold_mu);
 	RPT_CUDA(cudaMemcpyAsync(bf->fold_stats_host, bf->fold_stats_dev, 2 * sizeof(uint64_t), cudaMemcpyDeviceToHost, s));
 	RPT_CUDA(cudaEventRecord(bf->fold_stats_ev, s));
+	bf->fold_stats_recorded = true;
 	return 0;
 }
 
