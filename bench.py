@@ -47,7 +47,10 @@ def parse_args():
     ap.add_argument("--build-rows", type=int, default=100_000_000)
     ap.add_argument("--probe-rows", type=int, default=1_000_000_000, help="probe rows per GPU")
     ap.add_argument("--sel-ppm", type=int, default=100_000, help="member fraction of the probe column in ppm (10 %%)")
-    ap.add_argument("--e2e-steps", type=int, default=2)
+    ap.add_argument("--e2e-steps", type=int, default=3)
+    ap.add_argument("--e2e-warmup", type=int, default=3, help="untimed e2e steps before the timed ones (the first "
+                    "host-column calls after the device-column legs grow the stream-ordered pool and the pipeline's "
+                    "buffers: 1.3 s, then 0.2 s, then the steady 0.17 s per step — profiles/bench_r2y.json)")
     ap.add_argument("--clock-warmup-s", type=float, default=0.0, help="extra untimed steps for this many seconds "
                     "before the timed region (sustained-load measurement: the step then runs under sw_power_cap "
                     "at ~1.71 GHz, 114.5 instead of 121 Gkeys/s; profiles/bench_r1h_sustained.json)")
@@ -704,7 +707,8 @@ def run_e2e(args, rpt, torch, dist, dev, local_rank, world, rank, sb, dk, dp, n,
         rpt._check(rpt.lib().rpt_bf_probe(sb.bf._h, C.byref(probe_col.raw), 1, m, hsel.ptr, C.addressof(found),
                                           rpt.MEM_HOST, None))  # H2D keys, probe kernels, D2H selection vector
 
-    step()  # warm-up (pinned staging, allocator pools)
+    for _ in range(max(1, args.e2e_warmup)):  # warm-up (pinned staging, allocator pools, the pipeline's slots)
+        step()
     barrier()
     t0 = time.perf_counter()
     for _ in range(args.e2e_steps):
@@ -717,7 +721,7 @@ def run_e2e(args, rpt, torch, dist, dev, local_rank, world, rank, sb, dk, dp, n,
     keys_per_step = n + world * m
     out = {"value": keys_per_step / dt / 1e9, "unit": UNIT, "ms_per_step": dt * 1e3,
            "h2d_bytes_per_step": 8 * n_local + 8 * m, "d2h_bytes_per_step": 4 * int(found.value) + 8,
-           "steps": args.e2e_steps,
+           "steps": args.e2e_steps, "warmup": max(1, args.e2e_warmup),
            "note": "per rank: pinned host key columns → rpt_bf_insert / rpt_bf_probe (C ABI, RPT_MEM_HOST) → host "
                    "selection vector; PCIe-bound"}
     hk.free()

@@ -1371,6 +1371,7 @@ static int probe_impl(const rpt_bf *bf, const rpt_col_t *cols, int ncols, uint64
 		sl.pending = false;
 		return 0;
 	};
+	double t_stage = 0, t_alloc = 0, t_launch = 0, t_drain = 0; // host time per part (RPT_TRACE)
 	auto run = [&]() -> int {
 		uint64_t c = 0;
 		for (uint64_t r0 = 0; r0 < count; r0 += chunk, c++) {
@@ -1380,9 +1381,18 @@ static int probe_impl(const rpt_bf *bf, const rpt_col_t *cols, int ncols, uint64
 			st.stream = mbf->h2d;
 			st.free_stream = mbf->compute;
 			DevCols dc;
+			double t = trace_on() ? now_ms() : 0;
 			RPT_TRY(stage_host_cols(cols, ncols, r0, r1, &st, &dc));
+			if (trace_on()) {
+				t_stage += now_ms() - t;
+				t = now_ms();
+			}
 			void *scratch;
 			RPT_TRY(st.alloc(&scratch, probe_scratch_bytes(r1 - r0, bf->num_sectors, use_fold)));
+			if (trace_on()) {
+				t_alloc += now_ms() - t;
+				t = now_ms();
+			}
 			PrehashPlan pre;
 			RPT_TRY(plan_prehash(cols, ncols, r1 - r0, dc, &st, &pre));
 			RPT_CUDA(cudaEventRecord(sl.uploaded, mbf->h2d));
@@ -1396,8 +1406,15 @@ static int probe_impl(const rpt_bf *bf, const rpt_col_t *cols, int ncols, uint64
 			RPT_CUDA(cudaMemcpyAsync(sl.hfound, sl.dfound, sizeof(uint64_t), cudaMemcpyDeviceToHost, mbf->compute));
 			RPT_CUDA(cudaEventRecord(sl.computed, mbf->compute));
 			sl.pending = true;
+			if (trace_on()) {
+				t_launch += now_ms() - t;
+				t = now_ms();
+			}
 			if (c >= static_cast<uint64_t>(kSlots - 1)) {
 				RPT_TRY(drain(c - (kSlots - 1))); // frees the slot the next chunk will use
+			}
+			if (trace_on()) {
+				t_drain += now_ms() - t;
 			}
 		}
 		if (measure) {
@@ -1408,8 +1425,10 @@ static int probe_impl(const rpt_bf *bf, const rpt_col_t *cols, int ncols, uint64
 		}
 		RPT_CUDA(cudaStreamSynchronize(mbf->d2h));
 		if (trace_on()) {
-			fprintf(stderr, "[rpt trace] probe host: %llu rows, %llu chunk(s), found %llu, %.3f ms\n",
-			        (unsigned long long)count, (unsigned long long)c, (unsigned long long)total, now_ms() - t0);
+			fprintf(stderr, "[rpt trace] probe host: %llu rows, %llu chunk(s), found %llu, %.3f ms (host time: stage + "
+			        "upload calls %.1f, scratch alloc %.1f, launches %.1f, waiting for chunks %.1f; pre-filter %d)\n",
+			        (unsigned long long)count, (unsigned long long)c, (unsigned long long)total, now_ms() - t0, t_stage,
+			        t_alloc, t_launch, t_drain, use_fold ? 1 : 0);
 		}
 		return 0;
 	};

@@ -923,7 +923,9 @@ __device__ __forceinline__ void bulk_g2s(void *smem_dst, const void *gmem_src, u
 constexpr int kSmemProbeWarps = 24;
 constexpr uint32_t kHalfRows = 256;
 
-template <class Src, int NWARPS>
+// GLOBAL: the same staging with the filter left in global memory (an L2-resident filter of up to one slice, regime 2):
+// only the key buffers take shared memory, so the L1 keeps 156 KiB for the gathers in flight.
+template <class Src, int NWARPS, bool GLOBAL = false>
 __global__ void __launch_bounds__(NWARPS * 32, 1)
     probe_smem_kernel(const Src src, const uint64_t *__restrict__ filter, const uint32_t sector_mask, const uint64_t count,
                       const uint64_t num_segs, uint8_t *__restrict__ bitmap8, uint32_t *__restrict__ seg_counts) {
@@ -936,7 +938,7 @@ __global__ void __launch_bounds__(NWARPS * 32, 1)
 	__shared__ __align__(8) uint64_t s_bars[NWARPS][2];
 	__shared__ __align__(8) uint64_t s_fbar;
 	const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
-	const uint32_t filter_bytes = (sector_mask + 1u) * 8u;
+	const uint32_t filter_bytes = GLOBAL ? 0u : (sector_mask + 1u) * 8u;
 	const uint64_t *const s_filter = reinterpret_cast<const uint64_t *>(s_dyn);
 	unsigned char *const kbuf = s_dyn + filter_bytes + warp * 2u * HALF_BYTES;
 	const uint64_t pol_keys = policy_evict_first();
@@ -950,9 +952,12 @@ __global__ void __launch_bounds__(NWARPS * 32, 1)
 	}
 	asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
 	__syncthreads();
-	if (threadIdx.x == 0) { // the whole filter: one bulk copy
+	if (!GLOBAL && threadIdx.x == 0) { // the whole filter: one bulk copy
 		mbar_expect_tx(&s_fbar, filter_bytes);
 		bulk_g2s(s_dyn, filter, filter_bytes, &s_fbar, pol_filter);
+	}
+	if (GLOBAL) {
+		warm_slice(filter, 0u, sector_mask + 1u, NWARPS * 32);
 	}
 	const uint64_t full_segs = count / kSegRows;
 	const uint64_t stride = static_cast<uint64_t>(gridDim.x) * NWARPS;
@@ -969,7 +974,9 @@ __global__ void __launch_bounds__(NWARPS * 32, 1)
 		issue(seg0, 0);
 		issue(seg0, 1);
 	}
-	mbar_wait(&s_fbar, 0);
+	if (!GLOBAL) {
+		mbar_wait(&s_fbar, 0);
+	}
 	const uint32_t rot = LU == 4 ? ((lane >> 1) & 3u) : ((lane >> 2) & 1u);
 	uint32_t phase = 0;
 	for (uint64_t seg = seg0; seg < num_segs; seg += stride) {
@@ -991,7 +998,7 @@ __global__ void __launch_bounds__(NWARPS * 32, 1)
 					const uint32_t twice = v | (v << 8); // slot i holds logical bit (i + KPU·rot) mod 8: rotate right
 					null_fix<8>(hh, (twice >> (KPU * rot)) & 0xffu, 0);
 				}
-				hits = test_batch<8, true, false>(hh, filter, s_filter, sector_mask, pol_filter, 0u, 0u);
+				hits = test_batch<8, !GLOBAL, false>(hh, filter, s_filter, sector_mask, pol_filter, 0u, 0u);
 				const uint32_t twice = hits | (hits << 8); // slot order → row order: rotate left by KPU·rot
 				hits = (twice >> (8u - KPU * rot)) & 0xffu;
 				__syncwarp(); // every lane's keys are consumed: the buffer may be refilled
@@ -1004,7 +1011,9 @@ __global__ void __launch_bounds__(NWARPS * 32, 1)
 				for (int i = 0; i < 8; i++) {
 					if (row0 + i < count) {
 						const uint64_t hv = src.hash_at(row0 + i, pol_keys);
-						hits |= sector_test(s_filter[static_cast<uint32_t>(hv) & sector_mask], static_cast<uint32_t>(hv >> 32)) << i;
+						const uint32_t sector = static_cast<uint32_t>(hv) & sector_mask;
+						const uint64_t word = GLOBAL ? ld_filter_word(filter + sector, pol_filter) : s_filter[sector];
+						hits |= sector_test(word, static_cast<uint32_t>(hv >> 32)) << i;
 					}
 				}
 			}
@@ -2631,16 +2640,26 @@ static cudaError_t launch_probe_phased(const DeviceInfo &dev, const Src &src, ui
                                        uint32_t row_offset, const uint32_t *translate, void *scratch,
                                        cudaStream_t stream, int *launches) {
 	const uint64_t num_segs = ceil_div(count, kSegRows);
-	if constexpr (SMEM && Src::kStageable) {
-		// regime 1 of a flat column: bulk-copy staged kernel, 24 warps next to the filter
+	// Regime 2 (one L2-resident slice) of a flat column also takes the bulk-copy staged kernel, with the filter left in
+	// global memory: 4.02 against 4.16 ms per 10^9 rows at 64 MiB, equal at 16 MiB (both a few per cent above the
+	// one-gather-per-clock floor plus the compaction).  RPT_L2_KERNEL=0: probe_bitmap_kernel (cp.async staging).
+	static const bool l2_bulk = [] {
+		const char *e = getenv("RPT_L2_KERNEL");
+		return !e || atoi(e) != 0;
+	}();
+	if constexpr ((SMEM || !SLICED) && Src::kStageable) {
+	if (SMEM || l2_bulk) {
+		// regime 1 of a flat column: bulk-copy staged kernel, 24 warps next to the filter (regime 2: filter in L2)
 		constexpr int NW = kSmemProbeWarps;
-		cudaError_t e = ensure_max_dyn_smem<probe_smem_kernel<Src, NW>>(dev);
+		constexpr bool GLOBAL = !SMEM;
+		cudaError_t e = ensure_max_dyn_smem<probe_smem_kernel<Src, NW, GLOBAL>>(dev);
 		if (e != cudaSuccess) {
 			return e;
 		}
-		const size_t smem = num_sectors * sizeof(uint64_t) + static_cast<size_t>(NW) * 2 * kHalfRows * Src::kKeyBytes;
+		const size_t smem = (GLOBAL ? 0 : num_sectors * sizeof(uint64_t)) +
+		                    static_cast<size_t>(NW) * 2 * kHalfRows * Src::kKeyBytes;
 		int per_sm = 0;
-		e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, probe_smem_kernel<Src, NW>, NW * 32, smem);
+		e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, probe_smem_kernel<Src, NW, GLOBAL>, NW * 32, smem);
 		if (e != cudaSuccess) {
 			return e;
 		}
@@ -2659,7 +2678,7 @@ static cudaError_t launch_probe_phased(const DeviceInfo &dev, const Src &src, ui
 		if (e != cudaSuccess) {
 			return e;
 		}
-		probe_smem_kernel<Src, NW><<<static_cast<unsigned>(grid), NW * 32, smem, stream>>>(
+		probe_smem_kernel<Src, NW, GLOBAL><<<static_cast<unsigned>(grid), NW * 32, smem, stream>>>(
 		    src, words, static_cast<uint32_t>(num_sectors - 1), count, num_segs, bitmap, seg_offsets);
 		const uint64_t nblocks = ceil_div(num_segs, kScanBlock);
 		scan_blocks_kernel<<<static_cast<unsigned>(nblocks), 1024, 0, stream>>>(seg_offsets, num_segs, block_totals);
@@ -2669,7 +2688,9 @@ static cudaError_t launch_probe_phased(const DeviceInfo &dev, const Src &src, ui
 			(*launches) += 4;
 		}
 		return cudaGetLastError();
-	} else {
+	}
+	}
+	{
 	// shared-memory filter of a generic source: one CTA per SM at the top size
 	constexpr int BLOCK = SMEM ? kProbeBlockSmemPhased : kProbeBlock;
 	auto pass = probe_bitmap_kernel<Src, BLOCK, MINB, UNITS, SMEM, SLICED>;
