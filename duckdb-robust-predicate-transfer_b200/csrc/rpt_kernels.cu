@@ -925,10 +925,15 @@ constexpr uint32_t kHalfRows = 256;
 
 // GLOBAL: the same staging with the filter left in global memory (an L2-resident filter of up to one slice, regime 2):
 // only the key buffers take shared memory, so the L1 keeps 156 KiB for the gathers in flight.
-template <class Src, int NWARPS, bool GLOBAL = false>
+// SLICED (with GLOBAL): one sector-range pass of regime 3 — only the keys whose sector lies in [slice_lo, slice_lo +
+// slice_len) are looked up, their hits are ORed into the bitmap bytes of the earlier passes (a byte belongs to the
+// same lane in every pass), and the last pass (seg_counts != nullptr) leaves the segment counts.
+template <class Src, int NWARPS, bool GLOBAL = false, bool SLICED = false>
 __global__ void __launch_bounds__(NWARPS * 32, 1)
     probe_smem_kernel(const Src src, const uint64_t *__restrict__ filter, const uint32_t sector_mask, const uint64_t count,
-                      const uint64_t num_segs, uint8_t *__restrict__ bitmap8, uint32_t *__restrict__ seg_counts) {
+                      const uint64_t num_segs, uint8_t *__restrict__ bitmap8, uint32_t *__restrict__ seg_counts,
+                      const uint32_t slice_lo = 0, const uint32_t slice_len = 0, const int first_pass = 1) {
+	static_assert(!SLICED || GLOBAL, "sector-range passes are for filters in global memory");
 	static_assert(Src::kStageable, "flat key columns only");
 	constexpr int KB = Src::kKeyBytes;
 	constexpr int KPU = 16 / KB;                     // keys per 16-byte unit
@@ -957,7 +962,7 @@ __global__ void __launch_bounds__(NWARPS * 32, 1)
 		bulk_g2s(s_dyn, filter, filter_bytes, &s_fbar, pol_filter);
 	}
 	if (GLOBAL) {
-		warm_slice(filter, 0u, sector_mask + 1u, NWARPS * 32);
+		warm_slice(filter, SLICED ? slice_lo : 0u, SLICED ? slice_len : sector_mask + 1u, NWARPS * 32);
 	}
 	const uint64_t full_segs = count / kSegRows;
 	const uint64_t stride = static_cast<uint64_t>(gridDim.x) * NWARPS;
@@ -984,6 +989,10 @@ __global__ void __launch_bounds__(NWARPS * 32, 1)
 #pragma unroll
 		for (uint32_t h = 0; h < 2; h++) {
 			uint32_t hits = 0;
+			uint32_t earlier = 0; // hits of the earlier sector-range passes
+			if (SLICED && !first_pass) {
+				earlier = bitmap8[seg * 64 + h * 32 + lane];
+			}
 			if (seg < full_segs) {
 				mbar_wait(&s_bars[warp][h], (phase >> h) & 1u);
 				phase ^= 1u << h;
@@ -998,7 +1007,7 @@ __global__ void __launch_bounds__(NWARPS * 32, 1)
 					const uint32_t twice = v | (v << 8); // slot i holds logical bit (i + KPU·rot) mod 8: rotate right
 					null_fix<8>(hh, (twice >> (KPU * rot)) & 0xffu, 0);
 				}
-				hits = test_batch<8, !GLOBAL, false>(hh, filter, s_filter, sector_mask, pol_filter, 0u, 0u);
+				hits = test_batch<8, !GLOBAL, SLICED>(hh, filter, s_filter, sector_mask, pol_filter, slice_lo, slice_len);
 				const uint32_t twice = hits | (hits << 8); // slot order → row order: rotate left by KPU·rot
 				hits = (twice >> (8u - KPU * rot)) & 0xffu;
 				__syncwarp(); // every lane's keys are consumed: the buffer may be refilled
@@ -1012,17 +1021,22 @@ __global__ void __launch_bounds__(NWARPS * 32, 1)
 					if (row0 + i < count) {
 						const uint64_t hv = src.hash_at(row0 + i, pol_keys);
 						const uint32_t sector = static_cast<uint32_t>(hv) & sector_mask;
-						const uint64_t word = GLOBAL ? ld_filter_word(filter + sector, pol_filter) : s_filter[sector];
-						hits |= sector_test(word, static_cast<uint32_t>(hv >> 32)) << i;
+						if (!SLICED || sector - slice_lo < slice_len) {
+							const uint64_t word = GLOBAL ? ld_filter_word(filter + sector, pol_filter) : s_filter[sector];
+							hits |= sector_test(word, static_cast<uint32_t>(hv >> 32)) << i;
+						}
 					}
 				}
 			}
+			hits |= earlier;
 			bitmap8[seg * 64 + h * 32 + lane] = static_cast<uint8_t>(hits);
 			total += __popc(hits);
 		}
-		total = __reduce_add_sync(0xffffffffu, total);
-		if (lane == 0) {
-			seg_counts[seg] = total;
+		if (!SLICED || seg_counts != nullptr) {
+			total = __reduce_add_sync(0xffffffffu, total);
+			if (lane == 0) {
+				seg_counts[seg] = total;
+			}
 		}
 	}
 }
@@ -2640,26 +2654,30 @@ static cudaError_t launch_probe_phased(const DeviceInfo &dev, const Src &src, ui
                                        uint32_t row_offset, const uint32_t *translate, void *scratch,
                                        cudaStream_t stream, int *launches) {
 	const uint64_t num_segs = ceil_div(count, kSegRows);
-	// Regime 2 (one L2-resident slice) of a flat column also takes the bulk-copy staged kernel, with the filter left in
-	// global memory: 4.02 against 4.16 ms per 10^9 rows at 64 MiB, equal at 16 MiB (both a few per cent above the
-	// one-gather-per-clock floor plus the compaction).  RPT_L2_KERNEL=0: probe_bitmap_kernel (cp.async staging).
+	// Regimes 2 and 3 (one L2-resident slice; sector-range passes) of a flat column also take the bulk-copy staged
+	// kernel, with the filter left in global memory: 4.02 against 4.16 ms per 10^9 rows at 64 MiB, equal at 16 MiB
+	// (both a few per cent above the one-gather-per-clock floor plus the compaction); two passes at 128 MiB 4.69
+	// against 4.88 ms.  RPT_L2_KERNEL=0: probe_bitmap_kernel (cp.async staging).
 	static const bool l2_bulk = [] {
 		const char *e = getenv("RPT_L2_KERNEL");
 		return !e || atoi(e) != 0;
 	}();
-	if constexpr ((SMEM || !SLICED) && Src::kStageable) {
+	if constexpr (Src::kStageable) {
 	if (SMEM || l2_bulk) {
-		// regime 1 of a flat column: bulk-copy staged kernel, 24 warps next to the filter (regime 2: filter in L2)
+		// regime 1 of a flat column: bulk-copy staged kernel, 24 warps next to the filter (regimes 2 and 3: the filter
+		// stays in global memory, one launch per sector-range slice)
 		constexpr int NW = kSmemProbeWarps;
 		constexpr bool GLOBAL = !SMEM;
-		cudaError_t e = ensure_max_dyn_smem<probe_smem_kernel<Src, NW, GLOBAL>>(dev);
+		constexpr bool PASSES = SLICED && !SMEM;
+		cudaError_t e = ensure_max_dyn_smem<probe_smem_kernel<Src, NW, GLOBAL, PASSES>>(dev);
 		if (e != cudaSuccess) {
 			return e;
 		}
 		const size_t smem = (GLOBAL ? 0 : num_sectors * sizeof(uint64_t)) +
 		                    static_cast<size_t>(NW) * 2 * kHalfRows * Src::kKeyBytes;
 		int per_sm = 0;
-		e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, probe_smem_kernel<Src, NW, GLOBAL>, NW * 32, smem);
+		e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, probe_smem_kernel<Src, NW, GLOBAL, PASSES>, NW * 32,
+		                                                  smem);
 		if (e != cudaSuccess) {
 			return e;
 		}
@@ -2674,18 +2692,26 @@ static cudaError_t launch_probe_phased(const DeviceInfo &dev, const Src &src, ui
 		uint32_t *seg_offsets = reinterpret_cast<uint32_t *>(base);
 		uint32_t *block_totals = reinterpret_cast<uint32_t *>(base + lay.off_totals);
 		uint8_t *bitmap = reinterpret_cast<uint8_t *>(base + lay.off_hitbits);
-		e = wait_slices(stream, 0, -1);
-		if (e != cudaSuccess) {
-			return e;
+		const uint64_t slice = PASSES ? slice_sectors_for(num_sectors) : num_sectors;
+		int passes = 0;
+		for (uint64_t lo = 0; lo < num_sectors; lo += slice, passes++) {
+			const uint64_t len = lo + slice < num_sectors ? slice : num_sectors - lo;
+			const bool last = lo + slice >= num_sectors;
+			e = wait_slices(stream, static_cast<int>(lo / kSliceSectors),
+			                PASSES ? static_cast<int>((lo + len - 1) / kSliceSectors) : -1);
+			if (e != cudaSuccess) {
+				return e;
+			}
+			probe_smem_kernel<Src, NW, GLOBAL, PASSES><<<static_cast<unsigned>(grid), NW * 32, smem, stream>>>(
+			    src, words, static_cast<uint32_t>(num_sectors - 1), count, num_segs, bitmap, last ? seg_offsets : nullptr,
+			    static_cast<uint32_t>(lo), static_cast<uint32_t>(len), lo == 0 ? 1 : 0);
 		}
-		probe_smem_kernel<Src, NW, GLOBAL><<<static_cast<unsigned>(grid), NW * 32, smem, stream>>>(
-		    src, words, static_cast<uint32_t>(num_sectors - 1), count, num_segs, bitmap, seg_offsets);
 		const uint64_t nblocks = ceil_div(num_segs, kScanBlock);
 		scan_blocks_kernel<<<static_cast<unsigned>(nblocks), 1024, 0, stream>>>(seg_offsets, num_segs, block_totals);
 		scan_totals_kernel<<<1, 1024, 0, stream>>>(block_totals, static_cast<uint32_t>(nblocks), found_out);
 		launch_compact(dev, reinterpret_cast<const uint32_t *>(bitmap), seg_offsets, block_totals, num_segs, sel_out, row_offset, translate, stream);
 		if (launches) {
-			(*launches) += 4;
+			(*launches) += 3 + passes;
 		}
 		return cudaGetLastError();
 	}
