@@ -174,6 +174,21 @@ public:
 	void ExportWords(uint64_t *dst, uint64_t capacity_words) const {
 		Check(rpt_bf_export_words(bf_, dst, capacity_words));
 	}
+	// Folded pre-filter of large probes (no reference counterpart; rpt_gpu.h): -1 library default, 0 off, 1 by
+	// density, 2 always.  Never changes LookupSel's result.
+	void SetPrefilter(int mode) {
+		Check(rpt_bf_set_prefilter(bf_, mode));
+	}
+	// state: 0 no fold for the current words, 1 in use, 2 made but too dense
+	int PrefilterState(double *pass_rate = nullptr) const {
+		int state = 0;
+		double rate = 1.0;
+		Check(rpt_bf_prefilter_info(bf_, &state, &rate));
+		if (pass_rate) {
+			*pass_rate = rate;
+		}
+		return state;
+	}
 	// BFTableFilter::CheckStatistics (duckdb bloom_filter.cpp:138-196) for `count` row groups at once: mins/maxs are
 	// arrays of the column's physical type, results receive enum rpt_prune codes
 	void CheckStatistics(int physical_type, const void *mins, const void *maxs, const uint8_t *has_minmax,
