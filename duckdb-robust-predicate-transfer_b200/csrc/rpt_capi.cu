@@ -117,6 +117,18 @@ static int sectors_for_rows(uint64_t rows, uint64_t *out) {
 // ---------------------------------------------------------------------------------------------
 // handle
 // ---------------------------------------------------------------------------------------------
+// Device memory of one pipeline slot of the host-column calls: the staged key columns and the probe scratch of a chunk
+// are carved out of it instead of being allocated from the stream-ordered pool chunk by chunk.  (With pool
+// allocations on the upload stream and releases on the compute stream, the first host-column calls after a run of
+// device-column calls spent up to a second in cudaMallocFromPoolAsync growing the pool — bench.py's e2e leg swung
+// between 161 and 330 ms per step, profiles/bench_r2final.json before this.)  Grow-only: a call that needs more than
+// a slot holds falls back to the pool for the excess and the slot is re-sized when the next call starts.
+struct SlotArena {
+	char *base = nullptr;
+	size_t cap = 0;
+	size_t want = 0; // the most one chunk has asked for so far
+};
+
 struct rpt_bf {
 	DeviceInfo dev;
 	uint64_t num_sectors = 0;
@@ -134,6 +146,7 @@ struct rpt_bf {
 		uint64_t *hfound = nullptr; // pinned host copy of it
 		cudaEvent_t uploaded = nullptr, computed = nullptr, drained = nullptr;
 		bool pending = false;
+		SlotArena arena;            // staging + scratch of the chunk in this slot
 	};
 	std::mutex pipe_mu; // host-column calls on one handle take turns (device-column calls never touch the pipeline)
 	cudaStream_t h2d = nullptr, compute = nullptr, d2h = nullptr;
@@ -325,7 +338,12 @@ struct Staged {
 	bool handed_over = false;
 	int device = -1;
 	std::vector<void *> dev_allocs;
+	SlotArena *arena = nullptr; // host-column pipeline: carve from the slot's memory first (never freed here)
+	size_t arena_used = 0, asked = 0;
 	~Staged() {
+		if (arena && asked > arena->want) {
+			arena->want = asked;
+		}
 		if (free_stream && free_stream != stream && !handed_over && !dev_allocs.empty()) {
 			cudaStreamSynchronize(stream); // error path: the uploads finish before their buffers are released
 		}
@@ -336,6 +354,15 @@ struct Staged {
 	int alloc(void **out, size_t bytes) {
 		if (device < 0) {
 			RPT_CUDA(cudaGetDevice(&device));
+		}
+		if (arena) {
+			const size_t sz = ((bytes ? bytes : 8) + 255) / 256 * 256;
+			asked += sz;
+			if (arena_used + sz <= arena->cap) {
+				*out = arena->base + arena_used;
+				arena_used += sz;
+				return 0;
+			}
 		}
 		cudaMemPool_t pool;
 		RPT_TRY(library_pool(device, &pool));
@@ -754,6 +781,9 @@ int rpt_bf_destroy(rpt_bf_t *bf) {
 		if (sl.dsel) {
 			cudaFree(sl.dsel);
 		}
+		if (sl.arena.base) {
+			cudaFree(sl.arena.base);
+		}
 		if (sl.dfound) {
 			cudaFree(sl.dfound);
 		}
@@ -847,6 +877,25 @@ static MinMaxState *minmax_target(rpt_bf *bf, const DevCols &dc) {
 	return bf->mm_dev;
 }
 
+// Start of a host-column call (pipe_mu held, the pipeline idle): slots whose last chunks asked for more device memory
+// than they hold are re-sized, so that from the second call of a kind on nothing is allocated chunk by chunk.
+static int grow_slot_arenas(rpt_bf *bf) {
+	for (auto &sl : bf->slot) {
+		SlotArena &a = sl.arena;
+		if (a.want > a.cap) {
+			if (a.base) {
+				RPT_CUDA(cudaFree(a.base)); // implicit device synchronisation
+				a.base = nullptr;
+				a.cap = 0;
+			}
+			const size_t cap = (a.want + (a.want >> 4) + 0xfffff) & ~static_cast<size_t>(0xfffff); // +6 %, whole MiB
+			RPT_CUDA(cudaMalloc(&a.base, cap));
+			a.cap = cap;
+		}
+	}
+	return 0;
+}
+
 static int insert_impl(rpt_bf *bf, const rpt_col_t *cols, int ncols, uint64_t count, rpt_stream_t stream_in) {
 	int mem = 0;
 	RPT_TRY(validate_cols(cols, ncols, count, &mem));
@@ -882,6 +931,7 @@ static int insert_impl(rpt_bf *bf, const rpt_col_t *cols, int ncols, uint64_t co
 	} else {
 		RPT_CUDA(cudaStreamSynchronize(bf->stream)); // a zero-fill enqueued by rpt_bf_reset(NULL stream)
 	}
+	RPT_TRY(grow_slot_arenas(bf));
 	const uint64_t chunk = any_sel(cols, ncols) ? count : chunk_rows();
 	uint64_t c = 0;
 	for (uint64_t r0 = 0; r0 < count; r0 += chunk, c++) {
@@ -893,6 +943,7 @@ static int insert_impl(rpt_bf *bf, const rpt_col_t *cols, int ncols, uint64_t co
 		Staged st;
 		st.stream = bf->h2d;
 		st.free_stream = bf->compute;
+		st.arena = &sl.arena;
 		DevCols dc;
 		RPT_TRY(stage_host_cols(cols, ncols, r0, r1, &st, &dc));
 		PrehashPlan pre;
@@ -1334,6 +1385,7 @@ static int probe_impl(const rpt_bf *bf, const rpt_col_t *cols, int ncols, uint64
 		return 0;
 	}
 	constexpr int kSlots = rpt_bf::kPipeSlots;
+	RPT_TRY(grow_slot_arenas(mbf));
 	const uint64_t chunk = any_sel(cols, ncols) ? count : chunk_rows();
 	const uint64_t cap = chunk < count ? chunk : count;
 	for (auto &sl : mbf->slot) { // grow-only device selection buffers, kept for the next call
@@ -1380,6 +1432,7 @@ static int probe_impl(const rpt_bf *bf, const rpt_col_t *cols, int ncols, uint64
 			Staged st;
 			st.stream = mbf->h2d;
 			st.free_stream = mbf->compute;
+			st.arena = &sl.arena;
 			DevCols dc;
 			double t = trace_on() ? now_ms() : 0;
 			RPT_TRY(stage_host_cols(cols, ncols, r0, r1, &st, &dc));
