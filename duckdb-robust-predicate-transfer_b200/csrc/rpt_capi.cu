@@ -917,7 +917,12 @@ static int insert_impl(rpt_bf *bf, const rpt_col_t *cols, int ncols, uint64_t co
 		RPT_TRY(plan_prehash(cols, ncols, count, dc, &st, &pre));
 		MinMaxState *mm = minmax_target(bf, dc);
 		RPT_TRY(run_prehash(bf->dev, pre, &dc, st.stream, &launches));
-		RPT_CUDA(launch_build(bf->dev, dc, count, bf->words, bf->num_sectors, pick_stream(bf, stream_in), &launches, mm));
+		void *hashes = nullptr;
+		if (const size_t hb = build_scratch_bytes(dc, count, bf->num_sectors)) {
+			RPT_TRY(st.alloc(&hashes, hb));
+		}
+		RPT_CUDA(launch_build(bf->dev, dc, count, bf->words, bf->num_sectors, pick_stream(bf, stream_in), &launches, mm,
+		                      reinterpret_cast<uint64_t *>(hashes)));
 		bf->launches += launches;
 		return 0;
 	}
@@ -948,12 +953,17 @@ static int insert_impl(rpt_bf *bf, const rpt_col_t *cols, int ncols, uint64_t co
 		RPT_TRY(stage_host_cols(cols, ncols, r0, r1, &st, &dc));
 		PrehashPlan pre;
 		RPT_TRY(plan_prehash(cols, ncols, r1 - r0, dc, &st, &pre));
+		void *hashes = nullptr; // ordered on the upload stream, like the staged columns: before the `uploaded` event
+		if (const size_t hb = build_scratch_bytes(dc, r1 - r0, bf->num_sectors)) {
+			RPT_TRY(st.alloc(&hashes, hb));
+		}
 		RPT_CUDA(cudaEventRecord(sl.uploaded, bf->h2d));
 		RPT_CUDA(cudaStreamWaitEvent(bf->compute, sl.uploaded, 0));
 		st.handed_over = true;
 		MinMaxState *mm = minmax_target(bf, dc); // before run_prehash may retype the column
 		RPT_TRY(run_prehash(bf->dev, pre, &dc, bf->compute, &launches));
-		RPT_CUDA(launch_build(bf->dev, dc, r1 - r0, bf->words, bf->num_sectors, bf->compute, &launches, mm));
+		RPT_CUDA(launch_build(bf->dev, dc, r1 - r0, bf->words, bf->num_sectors, bf->compute, &launches, mm,
+		                      reinterpret_cast<uint64_t *>(hashes)));
 		RPT_CUDA(cudaEventRecord(sl.computed, bf->compute));
 	}
 	bf->launches += launches;

@@ -14,7 +14,9 @@
 // so the selection vector is written once.
 #include "rpt_kernels.cuh"
 
+#include <algorithm>
 #include <cstdlib>
+#include <type_traits>
 
 namespace rpt {
 
@@ -461,11 +463,14 @@ __device__ __forceinline__ void red_or_u64(unsigned long long *ptr, uint64_t mas
 
 // AGG: lanes of a warp that hit the same sector OR their masks first and issue one reduction
 // (worth it only for small filters or duplicate-heavy keys).
-template <class Src, bool AGG, bool MM>
+// WH: the first sector-range pass of a sliced build also writes every row's hash to hash_out; the later passes then
+// read that column (FlatU64SrcT<false, true>: 8 bytes per row, no key decoding, no murmur, no NULL handling) instead of
+// hashing the key columns again — a pass of a sliced build is issue/ALU-bound on exactly that work.
+template <class Src, bool AGG, bool MM, bool WH = false>
 __global__ void __launch_bounds__(kBuildBlock)
     build_kernel(const Src src, unsigned long long *__restrict__ filter, const uint32_t sector_mask,
                  const uint64_t count, const uint32_t slice_lo, const uint32_t slice_len, MinMaxState *mm_state,
-                 const bool mm_signed) {
+                 const bool mm_signed, uint64_t *__restrict__ hash_out = nullptr) {
 	const uint64_t pol = policy_evict_first();
 	const uint64_t pol_filter = policy_evict_last();
 	const uint64_t step = static_cast<uint64_t>(gridDim.x) * kBuildBlock * 2 * kBuildUnroll;
@@ -477,12 +482,27 @@ __global__ void __launch_bounds__(kBuildBlock)
 		if (base + static_cast<uint64_t>(kBuildBlock) * 2 * kBuildUnroll <= count) { // block-uniform
 			src.template load_rounds<kBuildUnroll, MM>(base + threadIdx.x * 2, kBuildBlock * 2, pol, h, &acc, mm_signed);
 			valid = (1u << (2 * kBuildUnroll)) - 1u;
+			if (WH) {
+#pragma unroll
+				for (int u = 0; u < kBuildUnroll; u++) {
+					const uint64_t row0 = base + static_cast<uint64_t>(u) * kBuildBlock * 2 + threadIdx.x * 2;
+					*reinterpret_cast<ulonglong2 *>(hash_out + row0) = make_ulonglong2(h[2 * u], h[2 * u + 1]);
+				}
+			}
 		} else {
 #pragma unroll
 			for (int u = 0; u < kBuildUnroll; u++) {
 				const uint64_t row0 = base + static_cast<uint64_t>(u) * kBuildBlock * 2 + threadIdx.x * 2;
 				const uint32_t v = src.load2(row0, count, pol, h[2 * u], h[2 * u + 1]);
 				valid |= v << (2 * u);
+				if (WH) {
+					if (v & 1u) {
+						hash_out[row0] = h[2 * u];
+					}
+					if (v & 2u) {
+						hash_out[row0 + 1] = h[2 * u + 1];
+					}
+				}
 				if (MM) {
 					if (v & 1u) {
 						src.fold_minmax(row0, pol, &acc, mm_signed);
@@ -2486,11 +2506,68 @@ size_t probe_scratch_bytes(uint64_t count, uint64_t num_sectors, bool prefilter)
 	return align_up(phased_layout(count).bytes, 256) + extra;
 }
 
+// scratch of a sliced build: one 64-bit hash per row, written by the first sector-range pass, read by the others
+// Generic sources only (several key columns, selections, dictionaries: hashing a row is the expensive part — two key
+// columns, 10^8 rows, F = 256 MiB: 1.64 against 3.15 ms).  For a flat column the extra 8 bytes per row written and
+// read back cost more than the murmur they save (int64: 1.32 against 0.97 ms; profiles/build_hash_once_r2.txt).
+static thread_local uint64_t *t_hash_scratch = nullptr;
+size_t build_scratch_bytes(const DevCols &cols, uint64_t count, uint64_t num_sectors) {
+	static const bool on = [] {
+		const char *e = getenv("RPT_BUILD_HASH_ONCE");
+		return !e || atoi(e) != 0;
+	}();
+	if (!on || slice_sectors_for(num_sectors) >= num_sectors || count < (1ULL << 20)) {
+		return 0;
+	}
+	if (is_flat_prehashed(cols) || is_flat_u64(cols) || is_flat_u32(cols)) {
+		return 0;
+	}
+	if (cols.n == 1 && cols.c[0].type == RPT_VARCHAR && !cols.c[0].sel) {
+		return 0; // a flat string column is hashed ahead (hash_varchar_kernel) and then is a flat column of hashes
+	}
+	return count * sizeof(uint64_t);
+}
+
 template <class Src, bool AGG, bool MM>
 static cudaError_t launch_build_mm(const DeviceInfo &dev, const Src &src, uint64_t count, uint64_t *words,
                                    uint64_t num_sectors, MinMaxState *mm, bool mm_signed, cudaStream_t stream,
                                    int *launches) {
 	const uint64_t per_block = static_cast<uint64_t>(kBuildBlock) * 2 * kBuildUnroll;
+	if constexpr (!AGG && !Src::kStageable) {
+		if (t_hash_scratch != nullptr && slice_sectors_for(num_sectors) < num_sectors) {
+			// hash once: pass 0 reduces its slice and writes the hashes, the other passes run on the hash column
+			using HashSrc = FlatU64SrcT<false, true>;
+			int p0 = 0, p1 = 0;
+			cudaError_t e0 = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&p0, build_kernel<Src, false, MM, true>, kBuildBlock, 0);
+			if (e0 == cudaSuccess) {
+				e0 = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&p1, build_kernel<HashSrc, false, false>, kBuildBlock, 0);
+			}
+			if (e0 != cudaSuccess) {
+				return e0;
+			}
+			const uint64_t want = ceil_div(count, per_block);
+			const uint64_t g0 = std::min<uint64_t>(want, static_cast<uint64_t>(dev.sm_count) * (p0 > 0 ? p0 : 1) * 4);
+			const uint64_t g1 = std::min<uint64_t>(want, static_cast<uint64_t>(dev.sm_count) * (p1 > 0 ? p1 : 1) * 4);
+			const uint64_t slice = slice_sectors_for(num_sectors);
+			const HashSrc hsrc {t_hash_scratch, nullptr};
+			for (uint64_t lo = 0; lo < num_sectors; lo += slice) {
+				const uint64_t len = lo + slice < num_sectors ? slice : num_sectors - lo;
+				if (lo == 0) {
+					build_kernel<Src, false, MM, true><<<static_cast<unsigned>(g0), kBuildBlock, 0, stream>>>(
+					    src, reinterpret_cast<unsigned long long *>(words), static_cast<uint32_t>(num_sectors - 1), count, 0u,
+					    static_cast<uint32_t>(len), mm, mm_signed, t_hash_scratch);
+				} else {
+					build_kernel<HashSrc, false, false><<<static_cast<unsigned>(g1), kBuildBlock, 0, stream>>>(
+					    hsrc, reinterpret_cast<unsigned long long *>(words), static_cast<uint32_t>(num_sectors - 1), count,
+					    static_cast<uint32_t>(lo), static_cast<uint32_t>(len), nullptr, false);
+				}
+				if (launches) {
+					(*launches)++;
+				}
+			}
+			return cudaGetLastError();
+		}
+	}
 	int per_sm = 0;
 	cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, build_kernel<Src, AGG, MM>, kBuildBlock, 0);
 	if (e != cudaSuccess) {
@@ -2529,8 +2606,18 @@ static cudaError_t launch_build_t(const DeviceInfo &dev, const Src &src, uint64_
 
 // mm (optional): the build also folds the (single) key column's valid rows into *mm — UpdateMinMax fused into the
 // insert pass (physical_create_bf.cpp:220-239).  Ignored for several key columns and for pre-hashed columns.
+static cudaError_t launch_build_inner(const DeviceInfo &dev, const DevCols &cols, uint64_t count, uint64_t *words,
+                                      uint64_t num_sectors, cudaStream_t stream, int *launches, MinMaxState *mm);
 cudaError_t launch_build(const DeviceInfo &dev, const DevCols &cols, uint64_t count, uint64_t *words,
-                         uint64_t num_sectors, cudaStream_t stream, int *launches, MinMaxState *mm) {
+                         uint64_t num_sectors, cudaStream_t stream, int *launches, MinMaxState *mm,
+                         uint64_t *hash_scratch) {
+	t_hash_scratch = hash_scratch;
+	const cudaError_t e = launch_build_inner(dev, cols, count, words, num_sectors, stream, launches, mm);
+	t_hash_scratch = nullptr;
+	return e;
+}
+static cudaError_t launch_build_inner(const DeviceInfo &dev, const DevCols &cols, uint64_t count, uint64_t *words,
+                                      uint64_t num_sectors, cudaStream_t stream, int *launches, MinMaxState *mm) {
 	if (count == 0) {
 		return cudaSuccess;
 	}

@@ -61,8 +61,13 @@ struct MinMaxState {
 };
 
 // Build: filter[h & (S-1)] |= GetMask(h) for every row (InsertHashes, bloom_filter.cpp:43-48,63-70).
+// hash_scratch (optional, build_scratch_bytes(cols, count, num_sectors) bytes when that is not 0): a build of a
+// generic key source in several sector-range passes hashes the rows once, in its first pass, and runs the other
+// passes on the hashes.
+size_t build_scratch_bytes(const DevCols &cols, uint64_t count, uint64_t num_sectors);
 cudaError_t launch_build(const DeviceInfo &dev, const DevCols &cols, uint64_t count, uint64_t *words,
-                         uint64_t num_sectors, cudaStream_t stream, int *launches, MinMaxState *mm = nullptr);
+                         uint64_t num_sectors, cudaStream_t stream, int *launches, MinMaxState *mm = nullptr,
+                         uint64_t *hash_scratch = nullptr);
 
 // Probe: ascending row ids of passing rows → sel_out, count → *found_out (LookupHashes,
 // bloom_filter.cpp:50-61,72-78).  `scratch` holds probe_scratch_bytes(count) bytes; it is zeroed
